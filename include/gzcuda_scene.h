@@ -1,0 +1,130 @@
+/*
+ * gzcuda_scene.h — flat (structure-of-arrays) description of a batch of
+ * independent Gazebo/ODE worlds.  Plain C, plain pointers and sizes.
+ *
+ * This is the data a Gazebo-side binding hands to libgzcuda when it mirrors the
+ * ODE objects that gazebo::physics::ODEPhysics owns (reference, read-only:
+ *   dxBody   deps/opende/src/objects.h:157-186
+ *   dxGeom   deps/opende/src/collision_kernel.h:96-183, collision_std.h
+ *   dxJoint  deps/opende/src/joints/joint.h, hinge.h, fixed.h
+ *   dxWorld / dxQuickStepParameters  deps/opende/src/objects.h:98-127,189-207
+ *   surface parameters  gazebo/physics/ode/ODESurfaceParams.cc:28-31).
+ * The same struct feeds the CPU oracle harness (oracle/ref_harness.cpp), which
+ * turns it into real ODE objects through the reference's C API, so both sides
+ * see identical inputs.
+ *
+ * Indexing: all arrays are concatenated over worlds; world w owns bodies
+ * [body_off[w], body_off[w+1]), geoms [geom_off[w], geom_off[w+1]) and joints
+ * [joint_off[w], joint_off[w+1]).  geom_body / joint_body1 / joint_body2 hold
+ * WORLD-LOCAL body indices (0 .. nb_w-1) or -1 for "no body" (static geom /
+ * joint to the world frame).
+ */
+#ifndef GZCUDA_SCENE_H
+#define GZCUDA_SCENE_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* geom_type — the five primitives north_star names (dSphereClass, dBoxClass,
+ * dCapsuleClass, dCylinderClass, dPlaneClass; include/gazebo/ode/collision.h). */
+enum { GZ_GEOM_SPHERE = 0, GZ_GEOM_BOX = 1, GZ_GEOM_CAPSULE = 2,
+       GZ_GEOM_CYLINDER = 3, GZ_GEOM_PLANE = 4 };
+
+/* joint_type (dJointTypeHinge, dJointTypeFixed, …; contact joints are created
+ * by the collide stage every step and never appear in the scene). */
+enum { GZ_JOINT_HINGE = 1, GZ_JOINT_FIXED = 2, GZ_JOINT_BALL = 3,
+       GZ_JOINT_SLIDER = 4, GZ_JOINT_UNIVERSAL = 5 };
+
+/* body_flags bits */
+enum { GZ_BODY_NO_GRAVITY   = 1,   /* dxBodyNoGravity (ODELink::SetGravityMode(false)) */
+       GZ_BODY_AUTO_DISABLE = 2,   /* dxBodyAutoDisable (ODELink.cc:70-77: jointless, sensorless models) */
+       GZ_BODY_DISABLED     = 4,   /* dxBodyDisabled: initial state, updated by the step */
+       GZ_BODY_NO_GYRO      = 8 }; /* clear dxBodyGyroscopic (set by default, ode.cpp:302) */
+
+/* joint_param[] slots (dxJointLimitMotor, joints/joint.cpp:470-484; erp/cfm joint.cpp:66-67) */
+enum { GZ_JP_LOSTOP = 0, GZ_JP_HISTOP = 1, GZ_JP_VEL = 2, GZ_JP_FMAX = 3,
+       GZ_JP_FUDGE = 4, GZ_JP_BOUNCE = 5, GZ_JP_NORMAL_CFM = 6,
+       GZ_JP_STOP_ERP = 7, GZ_JP_STOP_CFM = 8,
+       GZ_JP_ERP = 9,      /* joint erp, < 0 = use world erp */
+       GZ_JP_CFM = 10,     /* joint cfm, < 0 = use world cfm */
+       GZ_JP_COUNT = 12 };
+
+/* geom_surf[] slots (ODESurfaceParams + FrictionPyramid) */
+enum { GZ_SF_MU = 0, GZ_SF_MU2 = 1, GZ_SF_KP = 2, GZ_SF_KD = 3,
+       GZ_SF_SLIP1 = 4, GZ_SF_SLIP2 = 5, GZ_SF_BOUNCE = 6, GZ_SF_BOUNCE_VEL = 7,
+       GZ_SF_COUNT = 8 };
+
+/* World-level parameters, shared by every world of a batch
+ * (ODEPhysics::Load, gazebo/physics/ode/ODEPhysics.cc:175-243; dWorldCreate
+ * defaults deps/opende/src/ode.cpp:1625-1688). */
+typedef struct gz_params {
+  double gravity[3];
+  double step_size;                  /* h = max_step_size */
+  double erp, cfm;                   /* world->global_erp / global_cfm */
+  double sor_w;                      /* qs.w */
+  int    iters;                      /* qs.num_iterations (SDF <iters>) */
+  int    friction_iters;             /* qs.friction_iterations (default 10) */
+  double contact_max_correcting_vel; /* world->contactp.max_vel */
+  double contact_surface_layer;      /* world->contactp.min_depth */
+  int    max_contacts;               /* ODEPhysics::GetMaxContacts (SDF default 20) */
+  double warm_start;                 /* qs.warm_start (0.5) */
+  double smooth_contacts;            /* qs.smooth_contacts (0.01) */
+  double contact_sor_scale;          /* qs.contact_sor_scale (0.25) */
+  /* auto-disable defaults copied into bodies (ODEPhysics.cc:208-216; thresholds are stored squared) */
+  int    adis_idle_steps;
+  double adis_idle_time;
+  double adis_linear_threshold_sq;
+  double adis_angular_threshold_sq;
+  /* damping thresholds (squared speeds, ode.cpp:1678-1679) */
+  double damping_linear_threshold_sq;
+  double damping_angular_threshold_sq;
+} gz_params;
+
+typedef struct gz_scene {
+  int n_worlds;
+  const int *body_off;      /* [n_worlds+1] */
+  const int *geom_off;      /* [n_worlds+1] */
+  const int *joint_off;     /* [n_worlds+1] */
+
+  /* ---- bodies (dxBody) ---- */
+  const double *body_pos;      /* [nb][3]  centre of mass, world frame */
+  const double *body_quat;     /* [nb][4]  (w,x,y,z) */
+  const double *body_lvel;     /* [nb][3] */
+  const double *body_avel;     /* [nb][3] */
+  const double *body_mass;     /* [nb] */
+  const double *body_inertia;  /* [nb][6]  Ixx Iyy Izz Ixy Ixz Iyz, body frame, about the CoM */
+  const int    *body_flags;    /* [nb] GZ_BODY_* */
+  const double *body_damping;  /* [nb][2]  linear_scale, angular_scale; 0 = flag clear (ode.cpp:1069-1077) */
+  const double *body_contactp; /* [nb][2]  max_vel, min_depth (dBodySetMaxVel/MinDepth, ODELink.cc:357-392) */
+
+  /* ---- geoms (dxGeom + Gazebo surface) ---- */
+  const int    *geom_type;     /* [ng] GZ_GEOM_* */
+  const int    *geom_body;     /* [ng] world-local body index, -1 = static */
+  const int    *geom_space;    /* [ng] world-local id of the dSimpleSpace holding it (one per model, ODEModel.cc:26) */
+  const double *geom_dims;     /* [ng][4] box lx,ly,lz | sphere r | capsule/cylinder r,length | plane a,b,c,d */
+  const double *geom_pos;      /* [ng][3] offset from the body frame (dGeomSetOffsetPosition) or world pose if static */
+  const double *geom_quat;     /* [ng][4] same, rotation */
+  const unsigned *geom_category_bits; /* [ng] */
+  const unsigned *geom_collide_bits;  /* [ng] */
+  const unsigned *geom_collide_bitmask; /* [ng] Gazebo surface collideBitmask (ODEPhysics.cc:1016-1018) */
+  const int    *geom_max_contacts;    /* [ng] Collision::GetMaxContacts */
+  const double *geom_surf;     /* [ng][GZ_SF_COUNT] */
+  const double *geom_fdir1;    /* [ng][3] friction direction in the geom's link frame, 0 = unset */
+
+  /* ---- persistent joints ---- */
+  const int    *joint_type;    /* [nj] GZ_JOINT_* */
+  const int    *joint_body1;   /* [nj] world-local, never -1 */
+  const int    *joint_body2;   /* [nj] world-local or -1 (attached to the world) */
+  const double *joint_anchor1; /* [nj][3] body-1 frame (hinge/ball anchor1; fixed: offset) */
+  const double *joint_anchor2; /* [nj][3] body-2 frame (or world frame when body2 = -1) */
+  const double *joint_axis1;   /* [nj][3] body-1 frame */
+  const double *joint_axis2;   /* [nj][3] body-2 frame (or world) */
+  const double *joint_qrel;    /* [nj][4] initial relative rotation body1 -> body2 */
+  const double *joint_param;   /* [nj][GZ_JP_COUNT] */
+} gz_scene;
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GZCUDA_SCENE_H */

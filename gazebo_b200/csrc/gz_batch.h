@@ -1,0 +1,140 @@
+// gz_batch.h — device-resident state of a batch of independent worlds.
+//
+// Layout in HBM: one record array per object kind, concatenated
+// over worlds, each record a small contiguous struct of doubles/ints so a
+// thread-per-object kernel reads whole 32-byte sectors and a CTA-per-world
+// kernel reads one contiguous slab.  Per-step products (pairs, contacts,
+// constraint rows) live in per-world slabs of fixed capacity.
+//
+// Mirrors (reference, read-only): dxBody deps/opende/src/objects.h:157-186,
+// dxGeom collision_kernel.h:96-183, dxJointHinge joints/hinge.h:31-51,
+// dContact include/gazebo/ode/contact.h:56-105, the row arrays of
+// dxQuickStepper deps/opende/src/quickstep.cpp:262-325.
+#pragma once
+#include "../../include/gzcuda_scene.h"
+
+namespace gz {
+
+struct Body {
+  double pos[3];
+  double q[4];
+  double R[9];
+  double lvel[3], avel[3];
+  double facc[3], tacc[3];
+  double mass, invMass;
+  double I[9], invI[9];        // body frame
+  double lin_damp, ang_damp;   // scale; 0 = flag clear
+  double max_vel, min_depth;   // dxBody::contactp
+  double adis_timeleft;
+  int adis_stepsleft;
+  int flags;                   // GZ_BODY_*
+  int world;
+  int joint_begin, joint_end;  // slice of body_joint[] (persistent joints touching this body, joint order)
+};
+
+// per-step scratch of a body
+struct BodyStep {
+  double invMOI[9];
+  double caccel[6], caccel_erp[6];
+  int label;      // island label = lowest world-local body index of the component
+  int active;     // in an island stepped this step
+  int has_contact;  // touched by a contact joint this step (dxBody::firstjoint != NULL test)
+  int pad;
+};
+
+struct Geom {
+  double dims[4];
+  double opos[3];    // offset in body frame, or world pose if static
+  double oR[9];
+  double pos[3];     // final pose (dxGeom::final_posr)
+  double R[9];
+  double aabb[6];
+  double surf[GZ_SF_COUNT];
+  double fdir1[3];
+  int type, body, space, world;   // body: GLOBAL body index or -1
+  unsigned cat, col, scat, scol;  // geom bits and the bits of its space (ODECollision.cc:161-176)
+  unsigned bitmask;
+  int max_contacts;
+};
+
+struct Joint {
+  double anchor1[3], anchor2[3], axis1[3], axis2[3], qrel[4];
+  double param[GZ_JP_COUNT];
+  double lambda[6], lambda_erp[6];
+  double cum_angle;
+  double limit_err;
+  double pd[6];      // amplitude, frequency, phase, kp, kd, torque clamp (<=0 off)
+  int type, b1, b2;  // GLOBAL body indices, b2 = -1 for the world
+  int limit;         // dxJointLimitMotor::limit
+  int m;             // rows this step (0 = not in an active island)
+  int row0;          // first row (world-local)
+  int world, pad;
+};
+
+struct Contact {
+  double pos[3], normal[3], depth;
+  double mu, mu2, soft_erp, soft_cfm, slip1, slip2, bounce, bounce_vel;
+  double fdir1[3];
+  int g1, g2;        // GLOBAL geom indices (canonical: g1 < g2)
+  int b1, b2;        // GLOBAL body indices after dJointAttach's swap (b1 >= 0)
+  int reverse;       // dJOINT_REVERSE
+  int has_fdir1;
+  int row0, pad;
+};
+
+// One constraint row: 40 doubles = 320 B.
+struct Row {
+  double J[12];      // scaled by Ad after the prologue (quickstep_pgs_lcp.cpp:1091-1107)
+  double iMJ[12];
+  double rhs, rhs_erp, Adcfm, Ad;
+  double lo, hi;
+  double lambda, lambda_erp;
+  double c, cfm, c_v_max;
+  double pad0;
+  int b1, b2;        // WORLD-LOCAL body indices, b2 = -1
+  int findex;        // -1 bilateral, -2 contact normal, >=0 absolute (world-local) row of the normal
+  int src;           // joint index (>=0, global) or ~contact index (global) for write-back
+  int t1a, t2a, t1f, t2f;   // dataflow tickets (see k_pgs.cuh)
+  int next_a, next_f;       // per-executor queues, all-rows sweeps / friction-only sweeps
+  int owner, pad1;
+};
+
+struct WorldInfo {
+  int body0, nb, geom0, ng, joint0, nj;
+  int pair0, pair_cap, contact0, contact_cap, row0, row_cap;
+  int bj0;   // unused
+  int pad;
+};
+
+struct WorldStep {
+  int n_pairs, n_contacts, m, n_fric;
+  int overflow;     // bit0 pairs, bit1 contacts, bit2 rows
+  int num_contacts_stat;
+  int pad[2];
+  double rms_residual[4];
+  double rms_dlambda[4];
+};
+
+struct DevBatch {
+  int n_worlds, nb, ng, nj;
+  int max_nb, max_ng, max_nj, max_pair_cap, max_contact_cap, max_row_cap;
+  long step_index;
+  gz_params p;
+  WorldInfo *world;
+  WorldStep *wstep;
+  Body *body;
+  BodyStep *bstep;
+  int *body_joint;       // CSR payload: global joint indices per body, ascending
+  Geom *geom;
+  Joint *joint;
+  int *pair;             // [pairs][2] global geom indices
+  int *pair_nc;          // contacts of each pair after Gazebo's truncation
+  double *pair_contact;  // [pairs][8][7]  pos, normal, depth
+  Contact *contact;
+  Row *row;
+  int *order;            // per world slab: order[k] = world-local row index
+  int *qhead;            // per world: [2][max executors] queue heads (all / friction)
+  int *scratch;          // per world int scratch (row counts etc.)
+};
+
+}  // namespace gz

@@ -1,0 +1,592 @@
+// gzcuda.cu — C ABI (include/gzcuda.h) over the sm_100a kernels: batch construction,
+// per-step launch sequence, state exchange.  There is NO CPU fallback: every entry
+// point that computes needs a CUDA device and fails with GZCUDA_E_CUDA without one.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/gzcuda.h"
+#include "k_collide.cuh"
+#include "k_pgs.cuh"
+
+using namespace gz;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess)                                                               \
+      return fail(GZCUDA_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));    \
+  } while (0)
+
+struct gzcuda_batch {
+  DevBatch d;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  std::vector<void *> allocs;
+  std::vector<WorldInfo> h_world;
+  float last_ms = 0;
+  long last_launches = 0;
+  bool stage_valid = false;
+  bool have_pd = false;
+  int pgs_threads = 32;
+  size_t pgs_smem = 0;
+};
+
+// ---- host restatement of dInvertPDMatrix for n = 3 (deps/opende/src/matrix.cpp:124-228) ----
+static bool invert_pd3(const double A[9], double Ainv[9]) {
+  double L[9];
+  memcpy(L, A, sizeof(L));
+  double recip[3];
+  for (int i = 0; i < 3; i++) {
+    for (int j = 0; j < i; j++) {
+      double sum = L[3 * i + j];
+      for (int k = 0; k < j; k++) sum -= L[3 * i + k] * L[3 * j + k];
+      L[3 * i + j] = sum * recip[j];
+    }
+    double sum = L[3 * i + i];
+    for (int k = 0; k < i; k++) sum -= L[3 * i + k] * L[3 * i + k];
+    if (sum <= 0.0) return false;
+    double s = sqrt(sum);
+    L[3 * i + i] = s;
+    recip[i] = 1.0 / s;
+  }
+  for (int c = 0; c < 3; c++) {
+    double X[3] = {0, 0, 0}, y[3];
+    X[c] = 1.0;
+    for (int i = 0; i < 3; i++) {
+      double sum = 0.0;
+      for (int k = 0; k < i; k++) sum += L[3 * i + k] * y[k];
+      y[i] = (X[i] - sum) / L[3 * i + i];
+    }
+    for (int i = 2; i >= 0; i--) {
+      double sum = 0.0;
+      for (int k = i + 1; k < 3; k++) sum += L[3 * k + i] * X[k];
+      X[i] = (y[i] - sum) / L[3 * i + i];
+    }
+    for (int k = 0; k < 3; k++) Ainv[3 * k + c] = X[k];
+  }
+  return true;
+}
+
+template <class T>
+static int dev_alloc(gzcuda_batch *b, T **p, size_t n) {
+  if (n == 0) n = 1;
+  CK(cudaMalloc((void **)p, n * sizeof(T)));
+  CK(cudaMemset(*p, 0, n * sizeof(T)));
+  b->allocs.push_back(*p);
+  return 0;
+}
+template <class T>
+static int dev_upload(gzcuda_batch *b, T **p, const std::vector<T> &v) {
+  int rc = dev_alloc(b, p, v.size());
+  if (rc) return rc;
+  if (!v.empty()) CK(cudaMemcpy(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+extern "C" {
+
+int gzcuda_version(void) { return 100; }
+const char *gzcuda_last_error(void) { return g_err.c_str(); }
+int gzcuda_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+void gzcuda_batch_destroy(gzcuda_batch *b) {
+  if (!b) return;
+  cudaSetDevice(b->device);
+  if (b->stream) cudaStreamSynchronize(b->stream);
+  for (void *p : b->allocs) cudaFree(p);
+  if (b->ev0) cudaEventDestroy(b->ev0);
+  if (b->ev1) cudaEventDestroy(b->ev1);
+  for (auto &e : b->evs) if (e) cudaEventDestroy(e);
+  if (b->stream) cudaStreamDestroy(b->stream);
+  delete b;
+}
+
+static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
+  const int W = sc->n_worlds;
+  const int nb = sc->body_off[W], ng = sc->geom_off[W], nj = sc->joint_off[W];
+  DevBatch &d = b->d;
+  memset(&d, 0, sizeof(d));
+  d.n_worlds = W; d.nb = nb; d.ng = ng; d.nj = nj; d.p = *p; d.step_index = 0;
+
+  std::vector<Body> hb(nb);
+  std::vector<Geom> hg(ng);
+  std::vector<Joint> hj(nj);
+  std::vector<WorldInfo> hw(W);
+  std::vector<int> bj;                  // CSR payload
+  std::vector<std::vector<int>> adj(nb);
+
+  for (int w = 0; w < W; w++) {
+    for (int j = sc->joint_off[w]; j < sc->joint_off[w + 1]; j++) {
+      Joint &J = hj[j];
+      memset(&J, 0, sizeof(J));
+      J.type = sc->joint_type[j];
+      if (J.type != GZ_JOINT_HINGE && J.type != GZ_JOINT_FIXED)
+        return fail(GZCUDA_E_INVALID, "joint type not supported (hinge and fixed are)");
+      const int nbw = sc->body_off[w + 1] - sc->body_off[w];
+      if (sc->joint_body1[j] < 0 || sc->joint_body1[j] >= nbw || sc->joint_body2[j] >= nbw)
+        return fail(GZCUDA_E_INVALID, "joint body index out of range");
+      J.b1 = sc->body_off[w] + sc->joint_body1[j];
+      J.b2 = sc->joint_body2[j] >= 0 ? sc->body_off[w] + sc->joint_body2[j] : -1;
+      for (int k = 0; k < 3; k++) {
+        J.anchor1[k] = sc->joint_anchor1[3 * j + k]; J.anchor2[k] = sc->joint_anchor2[3 * j + k];
+        J.axis1[k] = sc->joint_axis1[3 * j + k]; J.axis2[k] = sc->joint_axis2[3 * j + k];
+      }
+      for (int k = 0; k < 4; k++) J.qrel[k] = sc->joint_qrel[4 * j + k];
+      for (int k = 0; k < GZ_JP_COUNT; k++) J.param[k] = sc->joint_param[GZ_JP_COUNT * j + k];
+      J.world = w;
+      adj[J.b1].push_back(j);
+      if (J.b2 >= 0) adj[J.b2].push_back(j);
+    }
+  }
+  for (int w = 0; w < W; w++) {
+    for (int i = sc->body_off[w]; i < sc->body_off[w + 1]; i++) {
+      Body &B = hb[i];
+      memset(&B, 0, sizeof(B));
+      for (int k = 0; k < 3; k++) {
+        B.pos[k] = sc->body_pos[3 * i + k]; B.lvel[k] = sc->body_lvel[3 * i + k]; B.avel[k] = sc->body_avel[3 * i + k];
+      }
+      for (int k = 0; k < 4; k++) B.q[k] = sc->body_quat[4 * i + k];
+      normalize4(B.q);          // dBodySetQuaternion (ode.cpp:414-427)
+      q_to_R(B.q, B.R);
+      B.mass = sc->body_mass[i];
+      if (!(B.mass > 0)) return fail(GZCUDA_E_INVALID, "body mass must be > 0");
+      B.invMass = 1.0 / B.mass;
+      const double *I = sc->body_inertia + 6 * i;   // dMassSetParameters (mass.cpp)
+      B.I[0] = I[0]; B.I[4] = I[1]; B.I[8] = I[2];
+      B.I[1] = B.I[3] = I[3]; B.I[2] = B.I[6] = I[4]; B.I[5] = B.I[7] = I[5];
+      if (!invert_pd3(B.I, B.invI)) {                // dBodySetMass falls back to identity (ode.cpp:535-538)
+        for (int k = 0; k < 9; k++) B.invI[k] = (k % 4 == 0) ? 1.0 : 0.0;
+      }
+      B.lin_damp = sc->body_damping[2 * i]; B.ang_damp = sc->body_damping[2 * i + 1];
+      B.max_vel = sc->body_contactp[2 * i]; B.min_depth = sc->body_contactp[2 * i + 1];
+      B.flags = sc->body_flags[i];
+      B.adis_stepsleft = p->adis_idle_steps;   // dBodySetAutoDisableDefaults (ode.cpp:925-941)
+      B.adis_timeleft = p->adis_idle_time;
+      B.world = w;
+      B.joint_begin = (int)bj.size();
+      for (int j : adj[i]) bj.push_back(j);   // ascending joint index (joints were visited in order)
+      B.joint_end = (int)bj.size();
+    }
+  }
+  int max_nb = 0, max_ng = 0, max_nj = 0, max_pc = 0, max_cc = 0, max_rc = 0;
+  long pair_tot = 0, contact_tot = 0, row_tot = 0;
+  for (int w = 0; w < W; w++) {
+    const int g0 = sc->geom_off[w], g1 = sc->geom_off[w + 1];
+    int nspace = 0;
+    for (int g = g0; g < g1; g++) nspace = std::max(nspace, sc->geom_space[g] + 1);
+    std::vector<unsigned> scat(nspace, 0), scol(nspace, 0);
+    for (int g = g0; g < g1; g++) {   // the last geom added to a space leaves its bits on the space
+      scat[sc->geom_space[g]] = sc->geom_category_bits[g];
+      scol[sc->geom_space[g]] = sc->geom_collide_bits[g];
+    }
+    for (int g = g0; g < g1; g++) {
+      Geom &G = hg[g];
+      memset(&G, 0, sizeof(G));
+      G.type = sc->geom_type[g];
+      if (G.type < GZ_GEOM_SPHERE || G.type > GZ_GEOM_PLANE) return fail(GZCUDA_E_INVALID, "unknown geom type");
+      const int nbw = sc->body_off[w + 1] - sc->body_off[w];
+      if (sc->geom_body[g] >= nbw) return fail(GZCUDA_E_INVALID, "geom body index out of range");
+      G.body = sc->geom_body[g] >= 0 ? sc->body_off[w] + sc->geom_body[g] : -1;
+      G.space = sc->geom_space[g];
+      G.world = w;
+      for (int k = 0; k < 4; k++) G.dims[k] = sc->geom_dims[4 * g + k];
+      if (G.type == GZ_GEOM_PLANE) {   // make_sure_plane_normal_has_unit_length (plane.cpp:49-65)
+        double *pp = G.dims;
+        double l = pp[0] * pp[0] + pp[1] * pp[1] + pp[2] * pp[2];
+        if (l > 0) { l = recip_sqrt(l); pp[0] *= l; pp[1] *= l; pp[2] *= l; pp[3] *= l; }
+        else { pp[0] = 1; pp[1] = 0; pp[2] = 0; pp[3] = 0; }
+        G.body = -1;
+      }
+      for (int k = 0; k < 3; k++) { G.opos[k] = sc->geom_pos[3 * g + k]; G.fdir1[k] = sc->geom_fdir1[3 * g + k]; }
+      q_to_R(sc->geom_quat + 4 * g, G.oR);   // dGeomSetOffsetQuaternion / dGeomSetQuaternion: dQtoR, no normalisation
+      for (int k = 0; k < GZ_SF_COUNT; k++) G.surf[k] = sc->geom_surf[GZ_SF_COUNT * g + k];
+      G.cat = sc->geom_category_bits[g]; G.col = sc->geom_collide_bits[g];
+      G.scat = scat[G.space]; G.scol = scol[G.space];
+      G.bitmask = sc->geom_collide_bitmask[g];
+      G.max_contacts = sc->geom_max_contacts[g];
+    }
+    // static upper bound on candidate pairs of this world
+    const int n = g1 - g0;
+    long np = 0;
+    const long np_limit = 32L * n;
+    for (int i = g0; i < g1 && np <= np_limit; i++)
+      for (int j = i + 1; j < g1; j++) {
+        const Geom &a = hg[i], &c = hg[j];
+        if (a.space == c.space) continue;
+        if (((a.scat & c.scol) || (c.scat & a.scol)) == 0) continue;
+        if (a.body == c.body && a.body >= 0) continue;
+        if (((a.cat & c.col) || (c.cat & a.col)) == 0) continue;
+        np++;
+      }
+    WorldInfo &wi = hw[w];
+    wi.body0 = sc->body_off[w]; wi.nb = sc->body_off[w + 1] - wi.body0;
+    wi.geom0 = g0; wi.ng = n;
+    wi.joint0 = sc->joint_off[w]; wi.nj = sc->joint_off[w + 1] - wi.joint0;
+    wi.pair_cap = (int)std::max(1L, std::min(np, np_limit));
+    wi.contact_cap = std::min(8 * wi.pair_cap, std::max(64, 24 * n));
+    wi.row_cap = 6 * wi.nj + 3 * wi.contact_cap;
+    wi.pair0 = (int)pair_tot; wi.contact0 = (int)contact_tot; wi.row0 = (int)row_tot;
+    pair_tot += wi.pair_cap; contact_tot += wi.contact_cap; row_tot += wi.row_cap;
+    if (row_tot > 0x7fffffffL) return fail(GZCUDA_E_INVALID, "batch too large (row slab index overflow)");
+    max_nb = std::max(max_nb, wi.nb); max_ng = std::max(max_ng, wi.ng); max_nj = std::max(max_nj, wi.nj);
+    max_pc = std::max(max_pc, wi.pair_cap); max_cc = std::max(max_cc, wi.contact_cap);
+    max_rc = std::max(max_rc, wi.row_cap);
+  }
+  d.max_nb = max_nb; d.max_ng = max_ng; d.max_nj = max_nj;
+  d.max_pair_cap = max_pc; d.max_contact_cap = max_cc; d.max_row_cap = max_rc;
+  if (max_nb > 512) return fail(GZCUDA_E_INVALID, "worlds with more than 512 bodies need the streaming solver (not built yet)");
+  b->h_world = hw;
+
+  int rc;
+  if ((rc = dev_upload(b, &d.world, hw))) return rc;
+  if ((rc = dev_alloc(b, &d.wstep, (size_t)W))) return rc;
+  if ((rc = dev_upload(b, &d.body, hb))) return rc;
+  if ((rc = dev_alloc(b, &d.bstep, (size_t)nb))) return rc;
+  if ((rc = dev_upload(b, &d.body_joint, bj))) return rc;
+  if ((rc = dev_upload(b, &d.geom, hg))) return rc;
+  if ((rc = dev_upload(b, &d.joint, hj))) return rc;
+  if ((rc = dev_alloc(b, &d.pair, (size_t)2 * pair_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.pair_nc, (size_t)pair_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.pair_contact, (size_t)56 * pair_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.contact, (size_t)contact_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.row, (size_t)row_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.order, (size_t)row_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)2 * max_rc + 4 * max_nb)))) return rc;
+
+  int E = ((std::max(max_nb, 1) + 15) / 16) * 16;
+  b->pgs_threads = 2 * E;
+  b->pgs_smem = ((size_t)13 * max_nb + 2 + (size_t)9 * E) * sizeof(double);
+  if (b->pgs_smem > 48 * 1024)
+    CK(cudaFuncSetAttribute(k_pgs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
+  return 0;
+}
+
+gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params, int device) {
+  if (!scene || !params || scene->n_worlds <= 0) { fail(GZCUDA_E_INVALID, "null or empty scene"); return nullptr; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    fail(GZCUDA_E_CUDA, "no CUDA device: libgzcuda has no CPU fallback");
+    return nullptr;
+  }
+  if (device < 0 || device >= ndev) { fail(GZCUDA_E_INVALID, "device index out of range"); return nullptr; }
+  if (cudaSetDevice(device) != cudaSuccess) { fail(GZCUDA_E_CUDA, "cudaSetDevice failed"); return nullptr; }
+  gzcuda_batch *b = new gzcuda_batch;
+  b->device = device;
+  bool ok = cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaEventCreate(&b->ev0) == cudaSuccess && cudaEventCreate(&b->ev1) == cudaSuccess;
+  for (auto &e : b->evs) ok = ok && cudaEventCreate(&e) == cudaSuccess;
+  if (!ok) { fail(GZCUDA_E_CUDA, "stream/event creation failed"); gzcuda_batch_destroy(b); return nullptr; }
+  if (build(b, scene, params) != 0) { gzcuda_batch_destroy(b); return nullptr; }
+  return b;
+}
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+static int launch_collision(gzcuda_batch *b) {
+  DevBatch &d = b->d;
+  const int W = d.n_worlds, T = 128;
+  k_geom<<<cdiv(std::max(d.ng, 1), T), T, 0, b->stream>>>(d);
+  k_broadphase<<<W, T, (d.max_ng + 1) * sizeof(int), b->stream>>>(d);
+  k_narrow<<<dim3(cdiv(d.max_pair_cap, T), W), T, 0, b->stream>>>(d);
+  k_contacts<<<W, T, 0, b->stream>>>(d);
+  b->last_launches += 4;
+  return 0;
+}
+
+static int launch_physics(gzcuda_batch *b, bool stage_events) {
+  DevBatch &d = b->d;
+  const int W = d.n_worlds, T = 128;
+  k_island<<<W, T, 0, b->stream>>>(d);
+  k_bodyprep<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
+  k_info1<<<W, T, 0, b->stream>>>(d);
+  if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
+  k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
+  k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
+  k_order<<<W, T, 0, b->stream>>>(d);
+  if (stage_events) cudaEventRecord(b->evs[2], b->stream);
+  k_pgs<<<W, b->pgs_threads, b->pgs_smem, b->stream>>>(d);
+  if (stage_events) cudaEventRecord(b->evs[3], b->stream);
+  if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
+  k_integrate<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
+  b->last_launches += 8;
+  return 0;
+}
+
+int gzcuda_batch_step(gzcuda_batch *b, int n_steps) {
+  if (!b || n_steps < 0) return fail(GZCUDA_E_INVALID, "bad batch or step count");
+  CK(cudaSetDevice(b->device));
+  b->last_launches = 0;
+  CK(cudaEventRecord(b->ev0, b->stream));
+  for (int s = 0; s < n_steps; s++) {
+    const bool last = (s == n_steps - 1);
+    if (last) cudaEventRecord(b->evs[0], b->stream);
+    if (b->have_pd) {
+      k_control<<<cdiv(std::max(b->d.nb, 1), 128), 128, 0, b->stream>>>(b->d);
+      b->last_launches++;
+    }
+    launch_collision(b);
+    if (last) cudaEventRecord(b->evs[1], b->stream);
+    launch_physics(b, last);
+    if (last) cudaEventRecord(b->evs[4], b->stream);
+    b->d.step_index++;
+  }
+  CK(cudaEventRecord(b->ev1, b->stream));
+  b->stage_valid = n_steps > 0;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int gzcuda_batch_update_collision(gzcuda_batch *b) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  CK(cudaSetDevice(b->device));
+  launch_collision(b);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int gzcuda_batch_update_physics(gzcuda_batch *b) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  CK(cudaSetDevice(b->device));
+  launch_physics(b, false);
+  b->d.step_index++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int gzcuda_world_step(gzcuda_batch *b, double step_size) {
+  if (!b || !(step_size > 0)) return 0;
+  b->d.p.step_size = step_size;
+  if (gzcuda_batch_update_physics(b) != 0) return 0;
+  return gzcuda_batch_sync(b) == 0 ? 1 : 0;
+}
+
+int gzcuda_batch_sync(gzcuda_batch *b) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+static int check_overflow(gzcuda_batch *b) {
+  std::vector<WorldStep> ws(b->d.n_worlds);
+  CK(cudaMemcpy(ws.data(), b->d.wstep, ws.size() * sizeof(WorldStep), cudaMemcpyDeviceToHost));
+  for (size_t w = 0; w < ws.size(); w++)
+    if (ws[w].overflow) {
+      char buf[128];
+      snprintf(buf, sizeof(buf), "world %zu overflowed a per-world slab (mask %d)", w, ws[w].overflow);
+      return fail(GZCUDA_E_CAPACITY, buf);
+    }
+  return 0;
+}
+
+int gzcuda_batch_get_body_state(gzcuda_batch *b, double *pos, double *quat, double *lvel, double *avel) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<Body> hb(b->d.nb);
+  CK(cudaMemcpy(hb.data(), b->d.body, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < b->d.nb; i++) {
+    for (int k = 0; k < 3; k++) {
+      if (pos) pos[3 * i + k] = hb[i].pos[k];
+      if (lvel) lvel[3 * i + k] = hb[i].lvel[k];
+      if (avel) avel[3 * i + k] = hb[i].avel[k];
+    }
+    if (quat) for (int k = 0; k < 4; k++) quat[4 * i + k] = hb[i].q[k];
+  }
+  return check_overflow(b);
+}
+
+int gzcuda_batch_set_body_state(gzcuda_batch *b, int first, int count, const double *pos,
+                                const double *quat, const double *lvel, const double *avel) {
+  if (!b || first < 0 || count < 0 || first + count > b->d.nb) return fail(GZCUDA_E_INVALID, "bad body range");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<Body> hb(count);
+  if (count == 0) return 0;
+  CK(cudaMemcpy(hb.data(), b->d.body + first, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < count; i++) {
+    for (int k = 0; k < 3; k++) {
+      if (pos) hb[i].pos[k] = pos[3 * i + k];
+      if (lvel) hb[i].lvel[k] = lvel[3 * i + k];
+      if (avel) hb[i].avel[k] = avel[3 * i + k];
+    }
+    if (quat) {
+      for (int k = 0; k < 4; k++) hb[i].q[k] = quat[4 * i + k];
+      normalize4(hb[i].q);
+      q_to_R(hb[i].q, hb[i].R);
+    }
+  }
+  CK(cudaMemcpy(b->d.body + first, hb.data(), hb.size() * sizeof(Body), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int gzcuda_batch_add_body_wrench(gzcuda_batch *b, const double *force, const double *torque) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<Body> hb(b->d.nb);
+  CK(cudaMemcpy(hb.data(), b->d.body, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < b->d.nb; i++)
+    for (int k = 0; k < 3; k++) {
+      if (force) hb[i].facc[k] += force[3 * i + k];
+      if (torque) hb[i].tacc[k] += torque[3 * i + k];
+    }
+  CK(cudaMemcpy(b->d.body, hb.data(), hb.size() * sizeof(Body), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int gzcuda_batch_get_body_flags(gzcuda_batch *b, int *flags) {
+  if (!b || !flags) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<Body> hb(b->d.nb);
+  CK(cudaMemcpy(hb.data(), b->d.body, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < b->d.nb; i++) flags[i] = hb[i].flags & GZ_BODY_DISABLED;
+  return 0;
+}
+
+int gzcuda_batch_set_joint_param(gzcuda_batch *b, int joint, int slot, double value) {
+  if (!b || joint < 0 || joint >= b->d.nj || slot < 0 || slot >= GZ_JP_COUNT) return fail(GZCUDA_E_INVALID, "bad joint/slot");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  CK(cudaMemcpy(&b->d.joint[joint].param[slot], &value, sizeof(double), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int gzcuda_batch_get_joint_state(gzcuda_batch *b, double *lambda, double *lambda_erp, double *cum_angle) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<Joint> hj(b->d.nj);
+  if (b->d.nj) CK(cudaMemcpy(hj.data(), b->d.joint, hj.size() * sizeof(Joint), cudaMemcpyDeviceToHost));
+  for (int j = 0; j < b->d.nj; j++) {
+    for (int k = 0; k < 6; k++) {
+      if (lambda) lambda[6 * j + k] = hj[j].lambda[k];
+      if (lambda_erp) lambda_erp[6 * j + k] = hj[j].lambda_erp[k];
+    }
+    if (cum_angle) cum_angle[j] = hj[j].cum_angle;
+  }
+  return 0;
+}
+
+int gzcuda_batch_set_hinge_pd(gzcuda_batch *b, const double *pd) {
+  if (!b || !pd) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<Joint> hj(b->d.nj);
+  if (b->d.nj == 0) return 0;
+  CK(cudaMemcpy(hj.data(), b->d.joint, hj.size() * sizeof(Joint), cudaMemcpyDeviceToHost));
+  bool any = false;
+  for (int j = 0; j < b->d.nj; j++) {
+    for (int k = 0; k < 6; k++) hj[j].pd[k] = pd[6 * j + k];
+    any = any || pd[6 * j + 5] > 0;
+  }
+  CK(cudaMemcpy(b->d.joint, hj.data(), hj.size() * sizeof(Joint), cudaMemcpyHostToDevice));
+  b->have_pd = any;
+  return 0;
+}
+
+int gzcuda_batch_get_stats(gzcuda_batch *b, double *rms_residual, int *num_contacts, int *num_rows) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<WorldStep> ws(b->d.n_worlds);
+  CK(cudaMemcpy(ws.data(), b->d.wstep, ws.size() * sizeof(WorldStep), cudaMemcpyDeviceToHost));
+  for (int w = 0; w < b->d.n_worlds; w++) {
+    if (rms_residual) for (int k = 0; k < 4; k++) rms_residual[4 * w + k] = ws[w].rms_residual[k];
+    if (num_contacts) num_contacts[w] = ws[w].n_contacts;
+    if (num_rows) num_rows[w] = ws[w].m;
+  }
+  return 0;
+}
+
+int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double v) {
+  if (!b || !key) return fail(GZCUDA_E_INVALID, "null argument");
+  gz_params &p = b->d.p;
+  std::string k(key);
+  if (k == "iters") p.iters = (int)v;
+  else if (k == "sor") p.sor_w = v;
+  else if (k == "cfm") p.cfm = v;
+  else if (k == "erp") p.erp = v;
+  else if (k == "contact_max_correcting_vel") p.contact_max_correcting_vel = v;
+  else if (k == "contact_surface_layer") p.contact_surface_layer = v;
+  else if (k == "max_contacts") p.max_contacts = (int)v;
+  else if (k == "friction_iters") p.friction_iters = (int)v;
+  else if (k == "warm_start_factor") p.warm_start = v;
+  else if (k == "contact_residual_smoothing") p.smooth_contacts = v;
+  else if (k == "contact_sor_scale") p.contact_sor_scale = v;
+  else if (k == "max_step_size") p.step_size = v;
+  else return fail(GZCUDA_E_INVALID, "unknown parameter key: " + k);
+  return 0;
+}
+
+int gzcuda_batch_get_pairs(gzcuda_batch *b, int world, int *pairs, int cap) {
+  if (!b || world < 0 || world >= b->d.n_worlds) return fail(GZCUDA_E_INVALID, "bad world");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  WorldStep ws;
+  CK(cudaMemcpy(&ws, b->d.wstep + world, sizeof(ws), cudaMemcpyDeviceToHost));
+  const WorldInfo &wi = b->h_world[world];
+  std::vector<int> hp(2 * (size_t)ws.n_pairs);
+  if (ws.n_pairs) CK(cudaMemcpy(hp.data(), b->d.pair + 2 * (size_t)wi.pair0, hp.size() * sizeof(int), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < ws.n_pairs && i < cap; i++) {
+    pairs[2 * i] = hp[2 * i] - wi.geom0;
+    pairs[2 * i + 1] = hp[2 * i + 1] - wi.geom0;
+  }
+  return ws.n_pairs;
+}
+
+int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *data, int cap) {
+  if (!b || world < 0 || world >= b->d.n_worlds) return fail(GZCUDA_E_INVALID, "bad world");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  WorldStep ws;
+  CK(cudaMemcpy(&ws, b->d.wstep + world, sizeof(ws), cudaMemcpyDeviceToHost));
+  const WorldInfo &wi = b->h_world[world];
+  std::vector<Contact> hc(ws.n_contacts);
+  if (ws.n_contacts) CK(cudaMemcpy(hc.data(), b->d.contact + wi.contact0, hc.size() * sizeof(Contact), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < ws.n_contacts && i < cap; i++) {
+    geoms[2 * i] = hc[i].g1 - wi.geom0;
+    geoms[2 * i + 1] = hc[i].g2 - wi.geom0;
+    for (int k = 0; k < 3; k++) { data[7 * i + k] = hc[i].pos[k]; data[7 * i + 3 + k] = hc[i].normal[k]; }
+    data[7 * i + 6] = hc[i].depth;
+  }
+  return ws.n_contacts;
+}
+
+int gzcuda_batch_last_step_ms(gzcuda_batch *b, float *ms, long *launches) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  float t = 0;
+  CK(cudaEventElapsedTime(&t, b->ev0, b->ev1));
+  b->last_ms = t;
+  if (ms) *ms = t;
+  if (launches) *launches = b->last_launches;
+  return 0;
+}
+
+int gzcuda_batch_stage_ms(gzcuda_batch *b, float ms[4]) {
+  if (!b || !ms) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  if (!b->stage_valid) return fail(GZCUDA_E_INVALID, "no step has run yet");
+  for (int k = 0; k < 4; k++) CK(cudaEventElapsedTime(&ms[k], b->evs[k], b->evs[k + 1]));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,299 @@
+// k_collide.cuh — ODEPhysics::UpdateCollision on the device:
+//   k_geom        final geom pose + AABB         (dxGeom::computePosr collision_kernel.cpp:462-475,
+//                                                  computeAABB box.cpp:60 sphere.cpp:59 capsule.cpp:60
+//                                                  cylinder.cpp:59 plane.cpp:80)
+//   k_broadphase  candidate pairs per world       (dxHashSpace::collide collision_space.cpp:427-593,
+//                                                  dSpaceCollide2 :778-843, collideAABBs
+//                                                  collision_space_internal.h:48-82,
+//                                                  ODEPhysics::CollisionCallback ODEPhysics.cc:948-1008)
+//   k_narrow      dCollide + Gazebo truncation    (collision_kernel.cpp:293-340, ODEPhysics.cc:1046-1091)
+//   k_contacts    ordered compaction + surface    (ODEPhysics.cc:1094-1329, dJointAttach ode.cpp:1417-1465)
+//
+// Pair order is canonical: (lower geom index, higher geom index), ascending — the
+// deterministic row-order mode of north_star; the oracle harness sorts the reference's
+// pairs the same way.  The pair SET equals the reference's: the hash space is an exact
+// AABB-overlap test between the model spaces followed by geom-vs-geom AABB tests.
+#pragma once
+#include "k_boxbox.cuh"
+
+namespace gz {
+
+__global__ void k_geom(DevBatch B) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B.ng) return;
+  Geom &g = B.geom[i];
+  if (g.type == GZ_GEOM_PLANE) {
+    // dxPlane::computeAABB: half-space box for axis-aligned normals (float _dequal overload)
+    const double *p = g.dims;
+    double a[6] = {-GZ_INF, GZ_INF, -GZ_INF, GZ_INF, -GZ_INF, GZ_INF};
+    bool z0 = fabsf((float)p[0] - 0.0f) <= 1e-6f, z1 = fabsf((float)p[1] - 0.0f) <= 1e-6f,
+         z2 = fabsf((float)p[2] - 0.0f) <= 1e-6f;
+    if (z1 && z2) { a[0] = (p[0] > 0) ? -GZ_INF : -p[3]; a[1] = (p[0] > 0) ? p[3] : GZ_INF; }
+    else if (z0 && z2) { a[2] = (p[1] > 0) ? -GZ_INF : -p[3]; a[3] = (p[1] > 0) ? p[3] : GZ_INF; }
+    else if (z0 && z1) { a[4] = (p[2] > 0) ? -GZ_INF : -p[3]; a[5] = (p[2] > 0) ? p[3] : GZ_INF; }
+    for (int k = 0; k < 6; k++) g.aabb[k] = a[k];
+    return;
+  }
+  double pos[3], R[9];
+  if (g.body >= 0) {
+    const Body &b = B.body[g.body];
+    mul0_331(pos, b.R, g.opos);
+    pos[0] += b.pos[0]; pos[1] += b.pos[1]; pos[2] += b.pos[2];
+    mul0_333(R, b.R, g.oR);
+  } else {
+    for (int k = 0; k < 3; k++) pos[k] = g.opos[k];
+    for (int k = 0; k < 9; k++) R[k] = g.oR[k];
+  }
+  double xr, yr, zr;
+  if (g.type == GZ_GEOM_BOX) {
+    const double *s = g.dims;
+    xr = 0.5 * (fabs(R[0] * s[0]) + fabs(R[1] * s[1]) + fabs(R[2] * s[2]));
+    yr = 0.5 * (fabs(R[3] * s[0]) + fabs(R[4] * s[1]) + fabs(R[5] * s[2]));
+    zr = 0.5 * (fabs(R[6] * s[0]) + fabs(R[7] * s[1]) + fabs(R[8] * s[2]));
+  } else if (g.type == GZ_GEOM_SPHERE) {
+    xr = yr = zr = g.dims[0];
+  } else if (g.type == GZ_GEOM_CAPSULE) {
+    double r = g.dims[0], lz = g.dims[1];
+    xr = fabs(R[2] * lz) * 0.5 + r;
+    yr = fabs(R[5] * lz) * 0.5 + r;
+    zr = fabs(R[8] * lz) * 0.5 + r;
+  } else {  // cylinder
+    double r = g.dims[0], lz = g.dims[1];
+    xr = fabs(R[0] * r) + fabs(R[1] * r) + 0.5 * fabs(R[2] * lz);
+    yr = fabs(R[3] * r) + fabs(R[4] * r) + 0.5 * fabs(R[5] * lz);
+    zr = fabs(R[6] * r) + fabs(R[7] * r) + 0.5 * fabs(R[8] * lz);
+  }
+  for (int k = 0; k < 3; k++) g.pos[k] = pos[k];
+  for (int k = 0; k < 9; k++) g.R[k] = R[k];
+  g.aabb[0] = pos[0] - xr; g.aabb[1] = pos[0] + xr;
+  g.aabb[2] = pos[1] - yr; g.aabb[3] = pos[1] + yr;
+  g.aabb[4] = pos[2] - zr; g.aabb[5] = pos[2] + zr;
+}
+
+// Are two bodies joined by a persistent (non-contact) joint?  dAreConnectedExcluding
+// (ode.cpp:1610-1618) walks body1's joint list; here the per-body CSR of persistent joints.
+__device__ inline bool bodies_connected(const DevBatch &B, int b1, int b2) {
+  const Body &a = B.body[b1];
+  for (int k = a.joint_begin; k < a.joint_end; k++) {
+    const Joint &j = B.joint[B.body_joint[k]];
+    if ((j.b1 == b1 && j.b2 == b2) || (j.b1 == b2 && j.b2 == b1)) return true;
+  }
+  return false;
+}
+
+__device__ inline bool pair_passes(const DevBatch &B, const Geom &g1, const Geom &g2) {
+  if (g1.space == g2.space) return false;   // same dSimpleSpace: never tested at the top level
+  // space-level collideAABBs: category/collide bits of the two spaces
+  if (((g1.scat & g2.scol) || (g2.scat & g1.scol)) == 0) return false;
+  // geom-level collideAABBs
+  if (g1.body == g2.body && g1.body >= 0) return false;
+  if (((g1.cat & g2.col) || (g2.cat & g1.col)) == 0) return false;
+  const double *a = g1.aabb, *b = g2.aabb;
+  if (a[0] > b[1] || a[1] < b[0] || a[2] > b[3] || a[3] < b[2] || a[4] > b[5] || a[5] < b[4]) return false;
+  // CollisionCallback: joint-connected bodies, then the both-disabled rule
+  int b1 = g1.body, b2 = g2.body;
+  if (b1 >= 0 && b2 >= 0 && bodies_connected(B, b1, b2)) return false;
+  bool e1 = b1 >= 0 ? !(B.body[b1].flags & GZ_BODY_DISABLED) : false;
+  bool e2 = b2 >= 0 ? !(B.body[b2].flags & GZ_BODY_DISABLED) : false;
+  if (g1.cat != 2u && g2.cat != 2u &&   // GZ_SENSOR_COLLIDE
+      ((b1 >= 0 && b2 >= 0 && !e1 && !e2) || (b2 < 0 && b1 >= 0 && !e1) || (b1 < 0 && b2 >= 0 && !e2)))
+    return false;
+  return true;
+}
+
+// One CTA per world.  Two passes over the (i<j) pair matrix, one warp per row i:
+// count, block-wide exclusive scan of the row counts, then ordered emission with
+// warp ballots.  Output is sorted by (i, j) by construction.
+__global__ void k_broadphase(DevBatch B) {
+  extern __shared__ int sh[];
+  const int w = blockIdx.x;
+  const WorldInfo wi = B.world[w];
+  const int n = wi.ng;
+  int *rowcnt = sh;            // [n+1]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const Geom *G = B.geom + wi.geom0;
+  for (int i = warp; i < n; i += nwarp) {
+    int c = 0;
+    for (int j0 = i + 1; j0 < n; j0 += 32) {
+      int j = j0 + lane;
+      bool hit = (j < n) && pair_passes(B, G[i], G[j]);
+      c += __popc(__ballot_sync(0xffffffffu, hit));
+    }
+    if (lane == 0) rowcnt[i] = c;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {   // n is small (<= a few hundred); serial scan is negligible
+    int acc = 0;
+    for (int i = 0; i < n; i++) { int c = rowcnt[i]; rowcnt[i] = acc; acc += c; }
+    rowcnt[n] = acc;
+    WorldStep &ws = B.wstep[w];
+    ws.overflow = 0;
+    if (acc > wi.pair_cap) { ws.overflow |= 1; acc = wi.pair_cap; }
+    ws.n_pairs = acc;
+  }
+  __syncthreads();
+  for (int i = warp; i < n; i += nwarp) {
+    int base = rowcnt[i];
+    for (int j0 = i + 1; j0 < n; j0 += 32) {
+      int j = j0 + lane;
+      bool hit = (j < n) && pair_passes(B, G[i], G[j]);
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (hit) {
+        int k = base + __popc(m & ((1u << lane) - 1));
+        if (k < wi.pair_cap) {
+          B.pair[2 * (wi.pair0 + k)] = wi.geom0 + i;
+          B.pair[2 * (wi.pair0 + k) + 1] = wi.geom0 + j;
+        }
+      }
+      base += __popc(m);
+    }
+  }
+}
+
+// dCollide's class-pair table (collision_kernel.cpp:168-269).  Returns contacts with the
+// normal convention of dCollide(g1, g2): reversed entries call fn(g2, g1) and flip normals.
+__device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) {
+  int t1 = g1.type, t2 = g2.type;
+  int n = 0;
+  bool rev = false;
+  if (t1 == GZ_GEOM_SPHERE && t2 == GZ_GEOM_SPHERE) n = col_sphere_sphere(g1, g2, o);
+  else if (t1 == GZ_GEOM_SPHERE && t2 == GZ_GEOM_BOX) n = col_sphere_box(g1, g2, o);
+  else if (t1 == GZ_GEOM_BOX && t2 == GZ_GEOM_SPHERE) { n = col_sphere_box(g2, g1, o); rev = true; }
+  else if (t1 == GZ_GEOM_SPHERE && t2 == GZ_GEOM_PLANE) n = col_sphere_plane(g1, g2, o);
+  else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_SPHERE) { n = col_sphere_plane(g2, g1, o); rev = true; }
+  else if (t1 == GZ_GEOM_BOX && t2 == GZ_GEOM_BOX) n = col_box_box(g1, g2, o);
+  else if (t1 == GZ_GEOM_BOX && t2 == GZ_GEOM_PLANE) n = col_box_plane(g1, g2, o);
+  else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_BOX) { n = col_box_plane(g2, g1, o); rev = true; }
+  else if (t1 == GZ_GEOM_CAPSULE && t2 == GZ_GEOM_PLANE) n = col_capsule_plane(g1, g2, o);
+  else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_CAPSULE) { n = col_capsule_plane(g2, g1, o); rev = true; }
+  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_PLANE) n = col_cylinder_plane(g1, g2, o);
+  else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_plane(g2, g1, o); rev = true; }
+  else n = 0;   // pairs not implemented yet are listed in DESIGN.md (capsule/cylinder vs non-plane)
+  if (rev)
+    for (int i = 0; i < n; i++) { o.nrm[i][0] = -o.nrm[i][0]; o.nrm[i][1] = -o.nrm[i][1]; o.nrm[i][2] = -o.nrm[i][2]; }
+  return n;
+}
+
+// grid (ceil(max_pair_cap / blockDim), n_worlds): one thread per candidate pair
+__global__ void k_narrow(DevBatch B) {
+  const int w = blockIdx.y;
+  const WorldInfo wi = B.world[w];
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= B.wstep[w].n_pairs) return;
+  const int pi = wi.pair0 + k;
+  const Geom &g1 = B.geom[B.pair[2 * pi]];
+  const Geom &g2 = B.geom[B.pair[2 * pi + 1]];
+  int numc = 0;
+  // ODEPhysics::Collide: collide bitmask, maxCollide
+  if ((g1.bitmask & g2.bitmask) != 0) {
+    unsigned maxCollide = 250;
+    if (B.p.max_contacts > 0 && B.p.max_contacts < 250) maxCollide = B.p.max_contacts;
+    if ((unsigned)g1.max_contacts < maxCollide) maxCollide = g1.max_contacts;
+    if ((unsigned)g2.max_contacts < maxCollide) maxCollide = g2.max_contacts;
+    COut o;
+    numc = collide_dispatch(g1, g2, o);
+    int idx[8];
+    for (int i = 0; i < 8; i++) idx[i] = i;
+    if (maxCollide > 0 && (unsigned)numc > maxCollide) {
+      double mx = o.depth[maxCollide - 1];
+      for (unsigned i = maxCollide; i < (unsigned)numc; ++i)
+        if (o.depth[i] > mx) { mx = o.depth[i]; idx[maxCollide - 1] = i; }
+      numc = maxCollide;
+    }
+    double *out = B.pair_contact + (size_t)pi * 56;
+    for (int c = 0; c < numc; c++) {
+      int s = idx[c];
+      for (int i = 0; i < 3; i++) { out[7 * c + i] = o.pos[s][i]; out[7 * c + 3 + i] = o.nrm[s][i]; }
+      out[7 * c + 6] = o.depth[s];
+    }
+  }
+  B.pair_nc[pi] = numc;
+}
+
+// One CTA per world: exclusive scan of per-pair contact counts, then one thread per pair
+// writes its contacts (with the combined surface parameters) at the scanned offset.
+__global__ void k_contacts(DevBatch B) {
+  extern __shared__ int sh[];
+  const int w = blockIdx.x;
+  const WorldInfo wi = B.world[w];
+  WorldStep &ws = B.wstep[w];
+  const int np = ws.n_pairs;
+  __shared__ int carry;
+  __shared__ int warp_sums[32];
+  if (threadIdx.x == 0) carry = 0;
+  for (int b = threadIdx.x; b < wi.nb; b += blockDim.x) B.bstep[wi.body0 + b].has_contact = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const double h = B.p.step_size;
+  for (int k0 = 0; k0 < np; k0 += blockDim.x) {
+    int k = k0 + threadIdx.x;
+    int c = (k < np) ? B.pair_nc[wi.pair0 + k] : 0;
+    // block exclusive scan
+    int v = c;
+    for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
+    if (lane == 31) warp_sums[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+      int s = (lane < nwarp) ? warp_sums[lane] : 0;
+      for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, s, d); if (lane >= d) s += t; }
+      warp_sums[lane] = s;
+    }
+    __syncthreads();
+    int off = carry + (v - c) + (warp > 0 ? warp_sums[warp - 1] : 0);
+    int total = warp_sums[nwarp - 1];
+    if (c > 0) {
+      const int pi = wi.pair0 + k;
+      const int gi1 = B.pair[2 * pi], gi2 = B.pair[2 * pi + 1];
+      const Geom &g1 = B.geom[gi1];
+      const Geom &g2 = B.geom[gi2];
+      // surface combination, ODEPhysics.cc:1108-1258
+      double kp = 1.0 / (1.0 / g1.surf[GZ_SF_KP] + 1.0 / g2.surf[GZ_SF_KP]);
+      double kd = g1.surf[GZ_SF_KD] + g2.surf[GZ_SF_KD];
+      double soft_erp = (h * kp) / (h * kp + kd);
+      double soft_cfm = 1.0 / (h * kp + kd);
+      double fd[3] = {g1.fdir1[0], g1.fdir1[1], g1.fdir1[2]};
+      bool fdset = (fd[0] != 0 || fd[1] != 0 || fd[2] != 0);
+      const Geom *fg = &g1;
+      bool fd2set = (g2.fdir1[0] != 0 || g2.fdir1[1] != 0 || g2.fdir1[2] != 0);
+      if (fd2set && (!fdset || g1.surf[GZ_SF_MU] > g2.surf[GZ_SF_MU])) {
+        fd[0] = g2.fdir1[0]; fd[1] = g2.fdir1[1]; fd[2] = g2.fdir1[2];
+        fg = &g2; fdset = true;
+      }
+      double fdw[3] = {0, 0, 0};
+      if (fdset) mul0_331(fdw, fg->R, fd);
+      double mu = fmin(g1.surf[GZ_SF_MU], g2.surf[GZ_SF_MU]);
+      double mu2 = fmin(g1.surf[GZ_SF_MU2], g2.surf[GZ_SF_MU2]);
+      double slip1 = g1.surf[GZ_SF_SLIP1] + g2.surf[GZ_SF_SLIP1];
+      double slip2 = g1.surf[GZ_SF_SLIP2] + g2.surf[GZ_SF_SLIP2];
+      slip1 *= c; slip2 *= c;
+      double bounce = fmin(g1.surf[GZ_SF_BOUNCE], g2.surf[GZ_SF_BOUNCE]);
+      double bounce_vel = fmin(g1.surf[GZ_SF_BOUNCE_VEL], g2.surf[GZ_SF_BOUNCE_VEL]);
+      // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
+      int b1 = g1.body, b2 = g2.body, reverse = 0;
+      if (b1 < 0) { b1 = b2; b2 = -1; reverse = 1; }
+      const double *src = B.pair_contact + (size_t)pi * 56;
+      for (int j = 0; j < c; j++) {
+        int ci = off + j;
+        if (ci >= wi.contact_cap) break;
+        Contact &C = B.contact[wi.contact0 + ci];
+        for (int i = 0; i < 3; i++) { C.pos[i] = src[7 * j + i]; C.normal[i] = src[7 * j + 3 + i]; C.fdir1[i] = fdw[i]; }
+        C.depth = src[7 * j + 6];
+        C.mu = mu; C.mu2 = mu2; C.soft_erp = soft_erp; C.soft_cfm = soft_cfm;
+        C.slip1 = slip1; C.slip2 = slip2; C.bounce = bounce; C.bounce_vel = bounce_vel;
+        C.g1 = gi1; C.g2 = gi2; C.b1 = b1; C.b2 = b2; C.reverse = reverse; C.has_fdir1 = fdset ? 1 : 0;
+      }
+      if (b1 >= 0) B.bstep[b1].has_contact = 1;
+      if (b2 >= 0) B.bstep[b2].has_contact = 1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    int nc = carry;
+    if (nc > wi.contact_cap) { ws.overflow |= 2; nc = wi.contact_cap; }
+    ws.n_contacts = nc;
+  }
+}
+
+}  // namespace gz

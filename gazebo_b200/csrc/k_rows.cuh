@@ -1,0 +1,214 @@
+// k_rows.cuh — everything of dWorldQuickStep that comes before the PGS sweeps:
+//   k_control    plugin stand-in: PD-tracked sinusoid -> dJointAddHingeTorque (hinge.cpp:390-409)
+//   k_island     dInternalHandleAutoDisabling (util.cpp:116-252) + island membership
+//                (BuildIslandsAndEstimateStepperMemoryRequirements util.cpp:408-558)
+//   k_bodyprep   world-frame inverse inertia, gyroscopic torque, gravity (quickstep.cpp:113-195)
+//   k_info1      getInfo1 row counts + row offsets (quickstep.cpp:200-236, hinge.cpp:53-78,
+//                contact.cpp:46-76, fixed.cpp:52-57)
+//   k_rows_joint / k_rows_contact   getInfo2 (hinge.cpp:81-180, joint.cpp:93-134,212-265,
+//                573-750, fixed.cpp:59-110, contact.cpp:79-438) and findex rebasing
+//                (quickstep.cpp:369-374)
+//   k_rowfinish  rhs / rhs_erp / cfm scaling (quickstep.cpp:403-443), warm start (:473-495),
+//                iMJ, Ad, J scaling (quickstep_pgs_lcp.cpp:985-1107)
+#pragma once
+#include "gz_math.cuh"
+#include "gz_batch.h"
+
+namespace gz {
+
+// getHingeAngle (joint.cpp:442-465) + getHingeAngleFromRelativeQuat (:391-432)
+__device__ inline double hinge_angle(const DevBatch &B, const Joint &j) {
+  double qrel[4];
+  const Body &b1 = B.body[j.b1];
+  if (j.b2 >= 0) {
+    double qq[4];
+    qmul1(qq, b1.q, B.body[j.b2].q);
+    qmul2(qrel, qq, j.qrel);
+  } else {
+    qmul3(qrel, b1.q, j.qrel);
+  }
+  double cost2 = qrel[0];
+  double sint2 = sqrt(qrel[1] * qrel[1] + qrel[2] * qrel[2] + qrel[3] * qrel[3]);
+  double theta = (dot3(qrel + 1, j.axis1) >= 0) ? (2 * atan2(sint2, cost2)) : (2 * atan2(sint2, -cost2));
+  if (theta > 3.14159265358979323846) theta -= 2 * 3.14159265358979323846;
+  return -theta;
+}
+
+// One thread per body: adds the PD torque of every hinge touching the body, in joint order
+// (the order dBodyAddTorque calls arrive in when the host loops over joints).
+__global__ void k_control(DevBatch B) {
+  int bi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bi >= B.nb) return;
+  Body &b = B.body[bi];
+  const double t = (double)B.step_index * B.p.step_size;
+  for (int k = b.joint_begin; k < b.joint_end; k++) {
+    const Joint &j = B.joint[B.body_joint[k]];
+    if (j.type != GZ_JOINT_HINGE || !(j.pd[5] > 0)) continue;
+    double target = j.pd[0] * sin(2.0 * 3.14159265358979323846 * j.pd[1] * t + j.pd[2]);
+    double ang = hinge_angle(B, j);
+    double angle = shortest_angular_distance_update(j.cum_angle, ang);   // dJointGetHingeAngle
+    const Body &b1 = B.body[j.b1];
+    double axis[3];
+    mul0_331(axis, b1.R, j.axis1);
+    double rate = dot3(axis, b1.avel);                                     // dJointGetHingeAngleRate
+    if (j.b2 >= 0) rate -= dot3(axis, B.body[j.b2].avel);
+    double tau = j.pd[3] * (target - angle) - j.pd[4] * rate;
+    if (tau > j.pd[5]) tau = j.pd[5];
+    if (tau < -j.pd[5]) tau = -j.pd[5];
+    axis[0] *= tau; axis[1] *= tau; axis[2] *= tau;
+    if (j.b1 == bi) { b.tacc[0] += axis[0]; b.tacc[1] += axis[1]; b.tacc[2] += axis[2]; }
+    else            { b.tacc[0] += -axis[0]; b.tacc[1] += -axis[1]; b.tacc[2] += -axis[2]; }
+  }
+}
+
+// One CTA per world.
+__global__ void k_island(DevBatch B) {
+  const int w = blockIdx.x;
+  const WorldInfo wi = B.world[w];
+  const WorldStep &ws = B.wstep[w];
+  const double h = B.p.step_size;
+  __shared__ int changed;
+  // 1. auto-disable (average_samples = 1: the instantaneous velocity is the average)
+  for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) {
+    Body &b = B.body[wi.body0 + i];
+    BodyStep &bs = B.bstep[wi.body0 + i];
+    bs.label = i;
+    bool has_joint = (b.joint_end > b.joint_begin) || bs.has_contact;
+    if (has_joint && (b.flags & (GZ_BODY_AUTO_DISABLE | GZ_BODY_DISABLED)) == GZ_BODY_AUTO_DISABLE) {
+      int idle = 1;
+      double av_l = dot3(b.lvel, b.lvel);
+      if (av_l > B.p.adis_linear_threshold_sq) idle = 0;
+      else {
+        double av_a = dot3(b.avel, b.avel);
+        if (av_a > B.p.adis_angular_threshold_sq) idle = 0;
+      }
+      if (idle) { b.adis_stepsleft--; b.adis_timeleft -= h; }
+      else { b.adis_stepsleft = B.p.adis_idle_steps; b.adis_timeleft = B.p.adis_idle_time; }
+      if (b.adis_stepsleft <= 0 && b.adis_timeleft <= 0) {
+        b.flags |= GZ_BODY_DISABLED;
+        for (int k = 0; k < 3; k++) { b.lvel[k] = 0; b.avel[k] = 0; }
+      }
+    }
+  }
+  __syncthreads();
+  // 2. connected components over two-body joints (persistent + contact): min-label propagation
+  for (;;) {
+    if (threadIdx.x == 0) changed = 0;
+    __syncthreads();
+    for (int k = threadIdx.x; k < wi.nj + ws.n_contacts; k += blockDim.x) {
+      int b1, b2;
+      if (k < wi.nj) { const Joint &j = B.joint[wi.joint0 + k]; b1 = j.b1; b2 = j.b2; }
+      else { const Contact &c = B.contact[wi.contact0 + (k - wi.nj)]; b1 = c.b1; b2 = c.b2; }
+      if (b2 < 0) continue;
+      int *l1 = &B.bstep[b1].label, *l2 = &B.bstep[b2].label;
+      int a = *(volatile int *)l1, b = *(volatile int *)l2;
+      if (a < b) { atomicMin(l2, a); changed = 1; }
+      else if (b < a) { atomicMin(l1, b); changed = 1; }
+    }
+    __syncthreads();
+    int c = changed;
+    __syncthreads();
+    if (!c) break;
+  }
+  // 3. a component is stepped iff it holds an enabled body; every body in it is re-enabled
+  for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) B.bstep[wi.body0 + i].active = 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) {
+    if (!(B.body[wi.body0 + i].flags & GZ_BODY_DISABLED))
+      B.bstep[wi.body0 + B.bstep[wi.body0 + i].label].active = 1;   // benign race: all write 1
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) {
+    BodyStep &bs = B.bstep[wi.body0 + i];
+    int act = B.bstep[wi.body0 + bs.label].active;
+    if (bs.label != i) bs.active = act;
+    if (act) B.body[wi.body0 + i].flags &= ~GZ_BODY_DISABLED;
+  }
+}
+
+// One thread per body (active bodies only).
+__global__ void k_bodyprep(DevBatch B) {
+  int bi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bi >= B.nb) return;
+  BodyStep &bs = B.bstep[bi];
+  for (int k = 0; k < 6; k++) { bs.caccel[k] = 0; bs.caccel_erp[k] = 0; }
+  if (!bs.active) return;
+  Body &b = B.body[bi];
+  double tmp[9], MOI[9];
+  mul2_333(tmp, b.invI, b.R);
+  mul0_333(bs.invMOI, b.R, tmp);
+  if (!(b.flags & GZ_BODY_NO_GYRO)) {
+    mul2_333(tmp, b.I, b.R);
+    mul0_333(MOI, b.R, tmp);
+    double t3[3], cr[3];
+    mul0_331(t3, MOI, b.avel);
+    cross3(cr, b.avel, t3);
+    b.tacc[0] = b.tacc[0] - cr[0]; b.tacc[1] = b.tacc[1] - cr[1]; b.tacc[2] = b.tacc[2] - cr[2];
+  }
+  if (!(b.flags & GZ_BODY_NO_GRAVITY)) {
+    for (int k = 0; k < 3; k++)
+      if (!dequal(B.p.gravity[k], 0.0)) b.facc[k] += b.mass * B.p.gravity[k];
+  }
+}
+
+// One CTA per world: row count per joint (with the hinge's cumulative-angle side effect),
+// exclusive scan -> Joint::row0; contacts follow with 3 rows each.
+__global__ void k_info1(DevBatch B) {
+  const int w = blockIdx.x;
+  const WorldInfo wi = B.world[w];
+  WorldStep &ws = B.wstep[w];
+  __shared__ int carry;
+  __shared__ int warp_sums[32];
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int k0 = 0; k0 < wi.nj; k0 += blockDim.x) {
+    int k = k0 + threadIdx.x;
+    int m = 0;
+    if (k < wi.nj) {
+      Joint &j = B.joint[wi.joint0 + k];
+      if (B.bstep[j.b1].active) {
+        if (j.type == GZ_JOINT_HINGE) {
+          m = (j.param[GZ_JP_FMAX] > 0) ? 6 : 5;
+          double lo = j.param[GZ_JP_LOSTOP], hi = j.param[GZ_JP_HISTOP];
+          if (lo <= hi) {
+            double angle = hinge_angle(B, j);
+            j.cum_angle = shortest_angular_distance_update(j.cum_angle, angle);
+            // dxJointLimitMotor::testRotationalLimit (joint.cpp:553-571)
+            if (j.cum_angle <= lo) { j.limit = 1; j.limit_err = j.cum_angle - lo; m = 6; }
+            else if (j.cum_angle >= hi) { j.limit = 2; j.limit_err = j.cum_angle - hi; m = 6; }
+            else j.limit = 0;
+          }
+        } else if (j.type == GZ_JOINT_FIXED) {
+          m = 6;
+        }
+      }
+      j.m = m;
+    }
+    int v = m;
+    for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
+    if (lane == 31) warp_sums[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+      int s = (lane < nwarp) ? warp_sums[lane] : 0;
+      for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, s, d); if (lane >= d) s += t; }
+      warp_sums[lane] = s;
+    }
+    __syncthreads();
+    if (k < wi.nj) B.joint[wi.joint0 + k].row0 = carry + (v - m) + (warp > 0 ? warp_sums[warp - 1] : 0);
+    int total = warp_sums[nwarp - 1];
+    __syncthreads();
+    if (threadIdx.x == 0) carry += total;
+    __syncthreads();
+  }
+  const int mj = carry;
+  for (int c = threadIdx.x; c < ws.n_contacts; c += blockDim.x) B.contact[wi.contact0 + c].row0 = mj + 3 * c;
+  if (threadIdx.x == 0) {
+    int m = mj + 3 * ws.n_contacts;
+    if (m > wi.row_cap) { ws.overflow |= 4; m = 0; }
+    ws.m = m;
+    ws.n_fric = 2 * ws.n_contacts;
+  }
+}
+
+}  // namespace gz

@@ -1,0 +1,221 @@
+// k_rows2.cuh — getInfo2 for persistent joints and contacts, then the row prologue.
+// See the header of k_rows.cuh for the reference line map.
+#pragma once
+#include "k_rows.cuh"
+
+namespace gz {
+
+__device__ inline void row_init(Row &r, int lb1, int lb2, double cfm, double cvmax, int src) {
+  for (int k = 0; k < 12; k++) r.J[k] = 0;
+  r.c = 0; r.cfm = cfm; r.lo = -GZ_INF; r.hi = GZ_INF; r.findex = -1; r.c_v_max = cvmax;
+  r.b1 = lb1; r.b2 = lb2; r.src = src;
+}
+
+// dxJointLimitMotor::addLimot, rotational case (joint.cpp:573-750).  Returns 1 if a row was written.
+__device__ inline int add_limot_rot(DevBatch &B, Joint &j, Row &r, const double *ax1, double fps) {
+  const double fmax = j.param[GZ_JP_FMAX], vel = j.param[GZ_JP_VEL];
+  const double lostop = j.param[GZ_JP_LOSTOP], histop = j.param[GZ_JP_HISTOP];
+  int powered = fmax > 0;
+  const int limit = j.limit;
+  if (!(powered || limit)) return 0;
+  for (int k = 0; k < 3; k++) r.J[3 + k] = ax1[k];
+  if (j.b2 >= 0) for (int k = 0; k < 3; k++) r.J[9 + k] = -ax1[k];
+  if (limit && dequal(lostop, histop)) powered = 0;
+  if (powered) {
+    r.cfm = j.param[GZ_JP_NORMAL_CFM];
+    if (!limit) {
+      r.c = vel; r.lo = -fmax; r.hi = fmax;
+    } else {
+      double fm = fmax;
+      if ((vel > 0) || (dequal(vel, 0.0) && limit == 2)) fm = -fm;
+      if ((limit == 1 && vel > 0) || (limit == 2 && vel < 0)) fm *= j.param[GZ_JP_FUDGE];
+      // dBodyAddTorque on both bodies from inside getInfo2.  Several powered hinges at
+      // their stops on one body would make the summation order matter; atomics keep it
+      // race-free (order then differs from the reference in the last bit only).
+      Body &b1 = B.body[j.b1];
+      atomicAdd(&b1.tacc[0], -fm * ax1[0]); atomicAdd(&b1.tacc[1], -fm * ax1[1]); atomicAdd(&b1.tacc[2], -fm * ax1[2]);
+      if (j.b2 >= 0) {
+        Body &b2 = B.body[j.b2];
+        atomicAdd(&b2.tacc[0], fm * ax1[0]); atomicAdd(&b2.tacc[1], fm * ax1[1]); atomicAdd(&b2.tacc[2], fm * ax1[2]);
+      }
+    }
+  }
+  if (limit) {
+    double k = fps * j.param[GZ_JP_STOP_ERP];
+    r.c = -k * j.limit_err;
+    r.cfm = j.param[GZ_JP_STOP_CFM];
+    if (dequal(lostop, histop)) { r.lo = -GZ_INF; r.hi = GZ_INF; }
+    else {
+      if (limit == 1) { r.lo = 0; r.hi = GZ_INF; } else { r.lo = -GZ_INF; r.hi = 0; }
+      const double bounce = j.param[GZ_JP_BOUNCE];
+      if (bounce > 0) {
+        double vvel = dot3(B.body[j.b1].avel, ax1);
+        if (j.b2 >= 0) vvel -= dot3(B.body[j.b2].avel, ax1);
+        if (limit == 1) {
+          if (vel < 0) { double newc = -bounce * vvel; if (newc > r.c) r.c = newc; }
+        } else {
+          if (vvel > 0) { double newc = -bounce * vvel; if (newc < r.c) r.c = newc; }
+        }
+      }
+    }
+  }
+  return 1;
+}
+
+// One thread per persistent joint.
+__global__ void k_rows_joint(DevBatch B) {
+  int ji = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ji >= B.nj) return;
+  Joint &j = B.joint[ji];
+  if (j.m == 0) return;
+  const WorldInfo wi = B.world[j.world];
+  Row *rows = B.row + wi.row0 + j.row0;
+  const Body &b1 = B.body[j.b1];
+  const Body *b2 = j.b2 >= 0 ? &B.body[j.b2] : nullptr;
+  const int lb1 = j.b1 - wi.body0, lb2 = j.b2 >= 0 ? j.b2 - wi.body0 : -1;
+  const double fps = 1.0 / B.p.step_size;
+  double erp = B.p.erp;
+  if (j.param[GZ_JP_ERP] >= 0) erp = j.param[GZ_JP_ERP];
+  for (int r = 0; r < j.m; r++) row_init(rows[r], lb1, lb2, B.p.cfm, B.p.contact_max_correcting_vel, ji);
+  if (j.type == GZ_JOINT_HINGE) {
+    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 5; r++) rows[r].cfm = j.param[GZ_JP_CFM];
+    // setBall (joint.cpp:93-134)
+    double a1[3], a2[3];
+    rows[0].J[0] = 1; rows[1].J[1] = 1; rows[2].J[2] = 1;
+    mul0_331(a1, b1.R, j.anchor1);
+    // dSetCrossMatrixMinus(J1a, a1)
+    rows[0].J[3 + 1] = a1[2];  rows[0].J[3 + 2] = -a1[1];
+    rows[1].J[3 + 0] = -a1[2]; rows[1].J[3 + 2] = a1[0];
+    rows[2].J[3 + 0] = a1[1];  rows[2].J[3 + 1] = -a1[0];
+    const double k = fps * erp;
+    if (b2) {
+      rows[0].J[6] = -1; rows[1].J[7] = -1; rows[2].J[8] = -1;
+      mul0_331(a2, b2->R, j.anchor2);
+      // dSetCrossMatrixPlus(J2a, a2)
+      rows[0].J[9 + 1] = -a2[2]; rows[0].J[9 + 2] = a2[1];
+      rows[1].J[9 + 0] = a2[2];  rows[1].J[9 + 2] = -a2[0];
+      rows[2].J[9 + 0] = -a2[1]; rows[2].J[9 + 1] = a2[0];
+      for (int i = 0; i < 3; i++) rows[i].c = k * (a2[i] + b2->pos[i] - a1[i] - b1.pos[i]);
+    } else {
+      for (int i = 0; i < 3; i++) rows[i].c = k * (j.anchor2[i] - a1[i] - b1.pos[i]);
+    }
+    double ax1[3], p[3], q[3];
+    mul0_331(ax1, b1.R, j.axis1);
+    plane_space(ax1, p, q);
+    for (int i = 0; i < 3; i++) { rows[3].J[3 + i] = p[i]; rows[4].J[3 + i] = q[i]; }
+    if (b2) for (int i = 0; i < 3; i++) { rows[3].J[9 + i] = -p[i]; rows[4].J[9 + i] = -q[i]; }
+    double ax2[3], bb[3];
+    if (b2) mul0_331(ax2, b2->R, j.axis2);
+    else { ax2[0] = j.axis2[0]; ax2[1] = j.axis2[1]; ax2[2] = j.axis2[2]; }
+    cross3(bb, ax1, ax2);
+    rows[3].c = k * dot3(bb, p);
+    rows[4].c = k * dot3(bb, q);
+    if (j.m == 6) add_limot_rot(B, j, rows[5], ax1, fps);
+  } else if (j.type == GZ_JOINT_FIXED) {
+    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 6; r++) rows[r].cfm = j.param[GZ_JP_CFM];
+    // setFixedOrientation(rows 3..5) (joint.cpp:212-265)
+    rows[3].J[3] = 1; rows[4].J[4] = 1; rows[5].J[5] = 1;
+    if (b2) { rows[3].J[9] = -1; rows[4].J[10] = -1; rows[5].J[11] = -1; }
+    double qerr[4], e[3];
+    if (b2) { double qq[4]; qmul1(qq, b1.q, b2->q); qmul2(qerr, qq, j.qrel); }
+    else qmul3(qerr, b1.q, j.qrel);
+    if (qerr[0] < 0) { qerr[1] = -qerr[1]; qerr[2] = -qerr[2]; qerr[3] = -qerr[3]; }
+    mul0_331(e, b1.R, qerr + 1);
+    const double k = fps * erp;
+    rows[3].c = 2 * k * e[0]; rows[4].c = 2 * k * e[1]; rows[5].c = 2 * k * e[2];
+    // position rows (fixed.cpp:82-109); anchor1 holds dxJointFixed::offset
+    rows[0].J[0] = 1; rows[1].J[1] = 1; rows[2].J[2] = 1;
+    double ofs[3];
+    mul0_331(ofs, b1.R, j.anchor1);
+    if (b2) {
+      // dSetCrossMatrixPlus(J1a, ofs)
+      rows[0].J[3 + 1] = -ofs[2]; rows[0].J[3 + 2] = ofs[1];
+      rows[1].J[3 + 0] = ofs[2];  rows[1].J[3 + 2] = -ofs[0];
+      rows[2].J[3 + 0] = -ofs[1]; rows[2].J[3 + 1] = ofs[0];
+      rows[0].J[6] = -1; rows[1].J[7] = -1; rows[2].J[8] = -1;
+      for (int i = 0; i < 3; i++) rows[i].c = k * (b2->pos[i] - b1.pos[i] + ofs[i]);
+    } else {
+      for (int i = 0; i < 3; i++) rows[i].c = k * (j.anchor1[i] - b1.pos[i]);
+    }
+  }
+}
+
+// One thread per contact: dxJointContact::getInfo2 with Gazebo's mode flags
+// (Bounce | Mu2 | SoftERP | SoftCFM | Approx1 | Approx3 | Slip1 | Slip2 [| FDir1]).
+__global__ void k_rows_contact(DevBatch B) {
+  const int w = blockIdx.y;
+  const WorldInfo wi = B.world[w];
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ci >= B.wstep[w].n_contacts || B.wstep[w].m == 0) return;
+  const Contact &C = B.contact[wi.contact0 + ci];
+  Row *rows = B.row + wi.row0 + C.row0;
+  const Body &b1 = B.body[C.b1];
+  const Body *b2 = C.b2 >= 0 ? &B.body[C.b2] : nullptr;
+  const int lb1 = C.b1 - wi.body0, lb2 = C.b2 >= 0 ? C.b2 - wi.body0 : -1;
+  const double fps = 1.0 / B.p.step_size;
+  for (int r = 0; r < 3; r++)
+    row_init(rows[r], lb1, lb2, B.p.cfm, B.p.contact_max_correcting_vel, ~(wi.contact0 + ci));
+  double normal[3];
+  if (C.reverse) { normal[0] = -C.normal[0]; normal[1] = -C.normal[1]; normal[2] = -C.normal[2]; }
+  else { normal[0] = C.normal[0]; normal[1] = C.normal[1]; normal[2] = C.normal[2]; }
+  double c1[3], c2[3] = {0, 0, 0};
+  for (int i = 0; i < 3; i++) c1[i] = C.pos[i] - b1.pos[i];
+  Row &r0 = rows[0];
+  for (int i = 0; i < 3; i++) r0.J[i] = normal[i];
+  cross3(r0.J + 3, c1, normal);
+  if (b2) {
+    for (int i = 0; i < 3; i++) { c2[i] = C.pos[i] - b2->pos[i]; r0.J[6 + i] = -normal[i]; }
+    cross3(r0.J + 9, c2, normal);
+    r0.J[9] = -r0.J[9]; r0.J[10] = -r0.J[10]; r0.J[11] = -r0.J[11];
+  }
+  // every body carries contactp (ODELink::UpdateSurface always calls dBodySetMaxVel/MinDepth)
+  double min_min_depth = b2 ? fmin(b1.min_depth, b2->min_depth) : b1.min_depth;
+  double depth = C.depth - min_min_depth;
+  if (depth < 0) depth = 0;
+  r0.cfm = C.soft_cfm;
+  const double motionN = 0;
+  const double local_erp = C.soft_erp;
+  const double k = fps * local_erp;
+  const double pushout = k * depth + motionN;
+  r0.c = pushout;
+  double maxvel = b2 ? fmin(b1.max_vel, b2->max_vel) : b1.max_vel;
+  if (maxvel > B.p.contact_max_correcting_vel) maxvel = B.p.contact_max_correcting_vel;
+  r0.c_v_max = maxvel;
+  {  // dContactBounce
+    double outgoing = dot3(r0.J, b1.lvel) + dot3(r0.J + 3, b1.avel);
+    if (b2) outgoing += dot3(r0.J + 6, b2->lvel) + dot3(r0.J + 9, b2->avel);
+    outgoing -= motionN;
+    if (C.bounce_vel >= 0 && (-outgoing) > C.bounce_vel) {
+      double newc = -C.bounce * outgoing + motionN;
+      if (newc > r0.c) r0.c = newc;
+    }
+  }
+  r0.lo = 0; r0.hi = GZ_INF; r0.findex = -2;
+  double mu = C.mu < 0 ? 0 : C.mu, mu2 = C.mu2 < 0 ? 0 : C.mu2;
+  double t1[3], t2[3];
+  if (C.has_fdir1) {
+    t1[0] = C.fdir1[0]; t1[1] = C.fdir1[1]; t1[2] = C.fdir1[2];
+    cross3(t2, normal, t1);
+    if (dequal(t2[0], 0.0) && dequal(t2[1], 0.0) && dequal(t2[2], 0.0)) plane_space(normal, t1, t2);
+  } else {
+    plane_space(normal, t1, t2);
+  }
+  const int abs_normal_row = C.row0;   // findex rebasing (quickstep.cpp:369-374)
+  for (int f = 0; f < 2; f++) {
+    Row &r = rows[1 + f];
+    const double *t = f ? t2 : t1;
+    for (int i = 0; i < 3; i++) r.J[i] = t[i];
+    cross3(r.J + 3, c1, t);
+    if (b2) {
+      for (int i = 0; i < 3; i++) r.J[6 + i] = -t[i];
+      cross3(r.J + 9, c2, t);
+      r.J[9] = -r.J[9]; r.J[10] = -r.J[10]; r.J[11] = -r.J[11];
+    }
+    double m = f ? mu2 : mu;
+    r.lo = -m; r.hi = m;
+    r.findex = abs_normal_row;
+    r.cfm = f ? C.slip2 : C.slip1;
+  }
+}
+
+}  // namespace gz

@@ -1,0 +1,108 @@
+/*
+ * gzcuda.h — C ABI of libgzcuda, the B200 (sm_100a) implementation of Gazebo's
+ * per-step ODE physics path.  Plain C: opaque handle, plain pointers and sizes.
+ *
+ * Each entry point names the reference interface it replaces (file:line under
+ * the ci-group/gazebo tree).  INTEGRATION.md shows the ODEPhysics-side binding.
+ * All functions return 0 on success or a negative GZCUDA_E* code; the message is
+ * available from gzcuda_last_error().  Nothing throws across the boundary
+ * (the reference's step function returns int and never throws either,
+ * deps/opende/src/ode.cpp:1980-1995).
+ *
+ * Threading: like ODEPhysics::UpdateCollision/UpdatePhysics, which run on the
+ * world's RunLoop thread under physicsUpdateMutex (ODEPhysics.cc:370,413), a batch
+ * must be driven by one host thread at a time.  Different batches (e.g. one per GPU)
+ * may be driven from different threads.
+ */
+#ifndef GZCUDA_H
+#define GZCUDA_H
+
+#include "gzcuda_scene.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GZCUDA_OK            0
+#define GZCUDA_E_INVALID    -1   /* bad argument / unsupported geom or joint type */
+#define GZCUDA_E_CUDA       -2   /* CUDA runtime error (no device, launch failure, ...) */
+#define GZCUDA_E_CAPACITY   -3   /* a per-world pair / contact / row slab overflowed */
+
+typedef struct gzcuda_batch gzcuda_batch;
+
+/* Library / device */
+int         gzcuda_version(void);
+const char *gzcuda_last_error(void);
+int         gzcuda_device_count(void);
+
+/* World construction: replaces ODEPhysics::ODEPhysics + Load (ODEPhysics.cc:140-243) and
+ * the dBodyCreate / dCreate<Geom> / dJointCreate<Type> calls of ODELink::Init (ODELink.cc:63-134),
+ * ODE<Shape>Shape::Init and ODEJoint::Load/Attach (ODEJoint.cc:83-216) for a batch of
+ * independent worlds on one device.  All scene arrays are copied. */
+gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params, int device);
+void          gzcuda_batch_destroy(gzcuda_batch *b);
+
+/* One world step for every world of the batch, n_steps times, without host interaction:
+ * ODEPhysics::UpdateCollision (ODEPhysics.cc:366-404) followed by ODEPhysics::UpdatePhysics
+ * (:407-453) = dWorldQuickStep (deps/opende/src/ode.cpp:1980-1995).  Asynchronous on the
+ * batch's stream; gzcuda_batch_sync or any getter waits for completion. */
+int gzcuda_batch_step(gzcuda_batch *b, int n_steps);
+/* The two halves, for callers that need Events::beforePhysicsUpdate between them
+ * (gazebo/physics/World.cc:755-786). */
+int gzcuda_batch_update_collision(gzcuda_batch *b);   /* ODEPhysics::UpdateCollision */
+int gzcuda_batch_update_physics(gzcuda_batch *b);     /* ODEPhysics::UpdatePhysics   */
+/* Drop-in for the step-function pointer `int (*physicsStepFunc)(dxWorld*, dReal)`
+ * (gazebo/physics/ode/ODEPhysicsPrivate.hh:65): returns 1 on success, 0 on failure. */
+int gzcuda_world_step(gzcuda_batch *b, double step_size);
+int gzcuda_batch_sync(gzcuda_batch *b);
+
+/* Body state, arrays over all bodies of the batch in scene order.
+ * dBodyGetPosition/Quaternion/LinearVel/AngularVel read by ODELink::MoveCallback
+ * (ODELink.cc:142-178); any pointer may be NULL. */
+int gzcuda_batch_get_body_state(gzcuda_batch *b, double *pos, double *quat, double *lvel, double *avel);
+/* dBodySetPosition/Quaternion/LinearVel/AngularVel (ODELink::OnPoseChange ODELink.cc:245-278,
+ * ODELink::SetLinearVel/SetAngularVel); bodies [first, first+count). */
+int gzcuda_batch_set_body_state(gzcuda_batch *b, int first, int count, const double *pos,
+                                const double *quat, const double *lvel, const double *avel);
+/* dBodyAddForce / dBodyAddTorque for every body ([nb][3] each, NULL = none). */
+int gzcuda_batch_add_body_wrench(gzcuda_batch *b, const double *force, const double *torque);
+/* dBodyIsEnabled: flags[nb] receives GZ_BODY_DISABLED or 0. */
+int gzcuda_batch_get_body_flags(gzcuda_batch *b, int *flags);
+
+/* dJointSetHingeParam & friends (ODEJoint::SetParam ODEJoint.cc:392-510): slot = GZ_JP_*. */
+int gzcuda_batch_set_joint_param(gzcuda_batch *b, int joint, int slot, double value);
+/* Persistent joint state: lambda[nj][6], lambda_erp[nj][6] (dxJoint::lambda, joint.h:156-157),
+ * cumulative hinge angle (dxJointHinge::cumulative_angle). */
+int gzcuda_batch_get_joint_state(gzcuda_batch *b, double *lambda, double *lambda_erp, double *cum_angle);
+/* Device-side stand-in for a ModelPlugin that tracks a sinusoid with a PD torque through
+ * Joint::SetForce -> dJointAddHingeTorque (ODEHingeJoint.cc:159-162) once per step on
+ * Events::worldUpdateBegin: pd[nj][6] = amplitude, frequency (Hz), phase, kp, kd, torque clamp
+ * (clamp <= 0 disables the joint's controller). */
+int gzcuda_batch_set_hinge_pd(gzcuda_batch *b, const double *pd);
+
+/* Solver statistics per world: rms_residual[nw][4] (dWorldGetQuickStepRMSConstraintResidual,
+ * ODEPhysics::GetParam("constraint_residual") ODEPhysics.cc:1630-1635), number of contact
+ * joints created in the last step, number of rows. Any pointer may be NULL. */
+int gzcuda_batch_get_stats(gzcuda_batch *b, double *rms_residual, int *num_contacts, int *num_rows);
+/* ODEPhysics::SetParam for the numeric solver keys (ODEPhysics.cc:1420-1581):
+ * "iters", "sor", "cfm", "erp", "contact_max_correcting_vel", "contact_surface_layer",
+ * "max_contacts", "friction_iters", "warm_start_factor", "contact_residual_smoothing",
+ * "contact_sor_scale", "max_step_size". */
+int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double value);
+
+/* Collision products of the last step (ContactManager contents): candidate pairs of one world
+ * as world-local geom indices [n][2] sorted ascending, and its contacts: geoms[n][2] and
+ * data[n][7] = position(3), normal(3), depth.  Return the count (or a negative error). */
+int gzcuda_batch_get_pairs(gzcuda_batch *b, int world, int *pairs, int cap);
+int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *data, int cap);
+
+/* Instrumentation: device time in ms of the last gzcuda_batch_step call (CUDA events on the
+ * batch stream) and the number of kernel launches it issued. */
+int gzcuda_batch_last_step_ms(gzcuda_batch *b, float *ms, long *launches);
+/* Per-stage device time of the last step call, ms: collide, assemble, pgs, integrate. */
+int gzcuda_batch_stage_ms(gzcuda_batch *b, float ms[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GZCUDA_H */

@@ -13,6 +13,7 @@
 #pragma once
 #include "gz_math.cuh"
 #include "gz_batch.h"
+#include "../../include/gz_detmath.h"
 
 namespace gz {
 
@@ -29,7 +30,7 @@ __device__ inline double hinge_angle(const DevBatch &B, const Joint &j) {
   }
   double cost2 = qrel[0];
   double sint2 = sqrt(qrel[1] * qrel[1] + qrel[2] * qrel[2] + qrel[3] * qrel[3]);
-  double theta = (dot3(qrel + 1, j.axis1) >= 0) ? (2 * atan2(sint2, cost2)) : (2 * atan2(sint2, -cost2));
+  double theta = (dot3(qrel + 1, j.axis1) >= 0) ? (2 * gzdet_atan2(sint2, cost2)) : (2 * gzdet_atan2(sint2, -cost2));
   if (theta > 3.14159265358979323846) theta -= 2 * 3.14159265358979323846;
   return -theta;
 }
@@ -44,7 +45,7 @@ __global__ void k_control(DevBatch B) {
   for (int k = b.joint_begin; k < b.joint_end; k++) {
     const Joint &j = B.joint[B.body_joint[k]];
     if (j.type != GZ_JOINT_HINGE || !(j.pd[5] > 0)) continue;
-    double target = j.pd[0] * sin(2.0 * 3.14159265358979323846 * j.pd[1] * t + j.pd[2]);
+    double target = j.pd[0] * gzdet_sin(2.0 * 3.14159265358979323846 * j.pd[1] * t + j.pd[2]);
     double ang = hinge_angle(B, j);
     double angle = shortest_angular_distance_update(j.cum_angle, ang);   // dJointGetHingeAngle
     const Body &b1 = B.body[j.b1];

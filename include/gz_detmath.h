@@ -10,7 +10,7 @@
  * so it returns the SAME BITS on the host (compiled with -ffp-contract=off) and on the
  * device (compiled with -fmad=false).  libgzcuda uses it on the device; the parity
  * oracle links the reference's opende against it instead of glibc's libm for these three
- * symbols (oracle/shim/detmath_shim.h).  Accuracy: < 1 ulp over the tested ranges
+ * symbols (oracle/shim/detmath_shim.h).  Accuracy: atan2 < 1.5 ulp, sin/cos < 1 ulp over the tested ranges
  * (tests/test_detmath.py); argument range of sin/cos: |x| < 1e5.
  *
  * Constants come from tools/gen_detmath_tables.py (mpmath, 60 digits).

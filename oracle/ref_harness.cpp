@@ -34,6 +34,10 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <csignal>
+#include <execinfo.h>
+#include <unistd.h>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -95,6 +99,16 @@ struct RefBatch {
 };
 
 bool g_ode_inited = false;
+
+void segv_handler(int) {
+  void *bt[64];
+  int n = backtrace(bt, 64);
+  backtrace_symbols_fd(bt, n, 2);
+  _exit(139);
+}
+
+void body_moved_cb(dBodyID) {}      // ODELink::MoveCallback: copies the pose to Gazebo's dirty list
+void body_disabled_cb(dBodyID) {}   // ODELink::DisabledCallback: empty in the reference
 
 int geom_index(dGeomID g) { return (int)(intptr_t)dGeomGetData(g); }
 
@@ -284,6 +298,10 @@ void canonical_quickstep(RefBatch *B, RefWorld *w) {
     if (!(w->bodies[i]->flags & dxBodyDisabled)) active[uf_find(parent, i)] = 1;
   std::vector<int> root(nb);
   for (int i = 0; i < nb; i++) root[i] = uf_find(parent, i);
+  // island of every joint, fixed BEFORE stepping: dxQuickStepper overwrites dxBody::tag
+  std::vector<int> jroot(alljoints.size(), -1);
+  for (size_t k = 0; k < alljoints.size(); k++)
+    if (jen[k]) jroot[k] = root[alljoints[k]->node[0].body->tag];
 
   // bodies reached from an enabled body are re-enabled (util.cpp:480-484)
   for (int i = 0; i < nb; i++)
@@ -297,7 +315,7 @@ void canonical_quickstep(RefBatch *B, RefWorld *w) {
     ib.clear(); ij.clear();
     for (int i = r; i < nb; i++) if (root[i] == r) ib.push_back(w->bodies[i]);
     for (size_t k = 0; k < alljoints.size(); k++)
-      if (jen[k] && root[alljoints[k]->node[0].body->tag] == r) ij.push_back(alljoints[k]);
+      if (jroot[k] == r) ij.push_back(alljoints[k]);
     size_t req = dxEstimateQuickStepMemoryRequirements(ib.data(), (int)ib.size(), ij.data(), (int)ij.size());
     ctx = dxReallocateTemporayWorldProcessContext(ctx, req + 4096, NULL, NULL);
     world->qs.num_contacts = 0;
@@ -314,8 +332,12 @@ void canonical_quickstep(RefBatch *B, RefWorld *w) {
 }
 
 void step_world(RefBatch *B, RefWorld *w) {
+  static const bool trace = getenv("GZREF_TRACE") != nullptr;
+  if (trace) fprintf(stderr, "step %ld: control\n", w->step_index);
   apply_controllers(B, w);
+  if (trace) fprintf(stderr, "  collide\n");
   update_collision(B, w);
+  if (trace) fprintf(stderr, "  step (pairs %zu contacts %zu)\n", w->pairs.size(), w->contacts.size());
   w->num_contacts = 0;
   if (B->mode == 1) {
     canonical_quickstep(B, w);
@@ -332,7 +354,7 @@ void step_world(RefBatch *B, RefWorld *w) {
 extern "C" {
 
 void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
-  if (!g_ode_inited) { dInitODE2(0); g_ode_inited = true; }
+  if (!g_ode_inited) { dInitODE2(0); g_ode_inited = true; if (getenv("GZREF_TRACE")) signal(SIGSEGV, segv_handler); }
   dAllocateODEDataForThread(dAllocateMaskAll);
   RefBatch *B = new RefBatch;
   B->p = *p;
@@ -396,6 +418,11 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
       dBodySetAngularVel(body, sc->body_avel[3 * b], sc->body_avel[3 * b + 1], sc->body_avel[3 * b + 2]);
       dBodySetMaxVel(body, sc->body_contactp[2 * b + 0]);
       dBodySetMinDepth(body, sc->body_contactp[2 * b + 1]);
+      // ODELink::Init (ODELink.cc:121-125) always installs both callbacks; dBodyCreate leaves
+      // disabled_callback uninitialised (ode.cpp), so a body that auto-disables would jump
+      // through a garbage pointer without this.
+      dBodySetMovedCallback(body, body_moved_cb);
+      dBodySetDisabledCallback(body, body_disabled_cb);
       if (fl & GZ_BODY_DISABLED) dBodyDisable(body);
       w->bodies.push_back(body);
     }

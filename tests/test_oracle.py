@@ -1,0 +1,90 @@
+"""CPU tests of the oracle (the reference's own opende compiled in place, driven by
+oracle/ref_harness.cpp): it must reproduce the committed golden vectors, and it must show
+the behaviour the reference's own integration tests assert (test/integration/physics.cc)."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import scenes
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.mark.parametrize("name", sorted(scenes.GOLDEN))
+def test_oracle_reproduces_golden(oracle, name):
+    builder, steps = scenes.GOLDEN[name]
+    sc, p, pd = builder()
+    r = oracle.RefBatch(sc, p, mode=1)
+    if pd is not None:
+        r.set_hinge_pd(pd)
+    r.step(steps)
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    pos, quat, lvel, avel = r.body_state()
+    # same compiler flags, same machine class: bit-identical
+    assert np.array_equal(pos, g["pos"]) and np.array_equal(quat, g["quat"])
+    assert np.array_equal(lvel, g["lvel"]) and np.array_equal(avel, g["avel"])
+    assert np.array_equal(r.pairs(0), g["pairs0"])
+    cg, cd = r.contacts(0)
+    assert np.array_equal(cg, g["contact_geoms0"]) and np.array_equal(cd, g["contact_data0"])
+    assert np.array_equal(r.body_flags(), g["flags"])
+
+
+def test_free_fall_then_rest(oracle):
+    """PhysicsTest.DropStuffODE (test/integration/physics.cc:919-1062): free fall follows
+    v += g dt; z += v dt exactly, the box settles at z = 0.5, and stays there."""
+    sc, p, _ = scenes.box_drop()
+    r = oracle.RefBatch(sc, p, mode=1)
+    z, v = 2.0, 0.0
+    for _ in range(100):
+        r.step(1)
+        v += -9.8 * 0.001
+        z += v * 0.001
+        pos, _, lvel, _ = r.body_state()
+        assert abs(pos[0, 2] - z) < 1e-4 and abs(lvel[0, 2] - v) < 1e-4   # physics.cc:970-971
+    r.step(1900)
+    pos, _, lvel, _ = r.body_state()
+    assert abs(pos[0, 2] - 0.5) < 1e-5          # physics.cc:982-986
+    assert np.linalg.norm(lvel[0]) < 3e-5       # physics.cc:1018
+    assert abs(pos[0, 0]) < 1e-9 and abs(pos[0, 1]) < 1e-9   # no x/y drift
+
+
+def test_natural_and_canonical_order_agree_physically(oracle):
+    """Canonical (deterministic row order) and natural gzserver order are two valid PGS
+    orderings of the same LCP: a settled box ends at the same height in both."""
+    sc, p, _ = scenes.tilted_box()
+    a = oracle.RefBatch(sc, p, mode=0)
+    b = oracle.RefBatch(sc, p, mode=1)
+    a.step(3000)
+    b.step(3000)
+    za, zb = a.body_state()[0][0, 2], b.body_state()[0][0, 2]
+    assert abs(za - 0.5) < 1e-3 and abs(zb - 0.5) < 1e-3
+
+
+def test_auto_disable_puts_stack_to_sleep(oracle):
+    """ODEPhysics.cc:208-216 + util.cpp:116-252: a settled stack of jointless bodies
+    goes to sleep after idle_time = 1 s; sleeping bodies have exactly zero velocity."""
+    sc, p, _ = scenes.stack()
+    r = oracle.RefBatch(sc, p, mode=1)
+    r.step(4000)
+    flags = r.body_flags()
+    _, _, lvel, avel = r.body_state()
+    assert flags.all()
+    assert not lvel.any() and not avel.any()
+
+
+def test_collide_bitmask_filters_pairs(oracle):
+    """ODEPhysics::Collide (ODEPhysics.cc:1016-1018): disjoint collide bitmasks give no contacts
+    although the pair is still a broadphase candidate."""
+    from gazebo_b200 import scene as S
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), collide_bitmask=0x1)
+    b = sb.add_body([0, 0, 0.4], mass=1.0, inertia=S.box_inertia(1, 1, 1, 1))
+    sb.add_geom(S.GEOM_BOX, (1, 1, 1), sb.new_space(), body=b, collide_bitmask=0x2)
+    sb.end_world()
+    sc = sb.finish()
+    r = oracle.RefBatch(sc, S.default_params(), mode=1)
+    r.step(1)
+    assert len(r.pairs(0)) == 1
+    assert len(r.contacts(0)[0]) == 0

@@ -37,6 +37,10 @@ def lib():
     L.gzcuda_batch_create.argtypes = [vp, vp, ci]
     L.gzcuda_batch_destroy.argtypes = [vp]
     L.gzcuda_batch_step.argtypes = [vp, ci]
+    L.gzcuda_batch_step_io.argtypes = [vp, ci, dp, dp]
+    L.gzcuda_batch_set_profiling.argtypes = [vp, ci]
+    L.gzcuda_batch_pgs_ms.argtypes = [vp, dp, dp]
+    L.gzcuda_batch_get_counters.argtypes = [vp, dp, ci]
     L.gzcuda_batch_update_collision.argtypes = [vp]
     L.gzcuda_batch_update_physics.argtypes = [vp]
     L.gzcuda_world_step.argtypes = [vp, C.c_double]
@@ -66,7 +70,8 @@ EXPORTS = [
     "gzcuda_batch_get_body_flags", "gzcuda_batch_set_joint_param", "gzcuda_batch_get_joint_state",
     "gzcuda_batch_set_hinge_pd", "gzcuda_batch_get_stats", "gzcuda_batch_set_param",
     "gzcuda_batch_get_pairs", "gzcuda_batch_get_contacts", "gzcuda_batch_last_step_ms",
-    "gzcuda_batch_stage_ms",
+    "gzcuda_batch_stage_ms", "gzcuda_batch_step_io", "gzcuda_batch_set_profiling",
+    "gzcuda_batch_pgs_ms", "gzcuda_batch_get_counters",
 ]
 
 
@@ -103,6 +108,24 @@ class Batch:
     # ---- stepping
     def step(self, n=1):
         self._ck(self.L.gzcuda_batch_step(self.h, n))
+
+    def step_io(self, n, wrench_ptr, state_ptr):
+        """Host-buffer step: raw pointers (ints) to [nb][6] wrench in and [nb][13] state out."""
+        self._ck(self.L.gzcuda_batch_step_io(self.h, n, wrench_ptr, state_ptr))
+
+    def set_profiling(self, on):
+        self._ck(self.L.gzcuda_batch_set_profiling(self.h, int(on)))
+
+    def pgs_ms(self):
+        ms = C.c_float(0)
+        n = C.c_int(0)
+        self._ck(self.L.gzcuda_batch_pgs_ms(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def counters(self, reset=False):
+        out = (C.c_ulonglong * 4)()
+        self._ck(self.L.gzcuda_batch_get_counters(self.h, out, int(reset)))
+        return list(out)
 
     def update_collision(self):
         self._ck(self.L.gzcuda_batch_update_collision(self.h))

@@ -135,6 +135,9 @@ struct DevBatch {
   int *order;            // per world slab: order[k] = world-local row index
   int *qhead;            // per world: [2][max executors] queue heads (all / friction)
   int *scratch;          // per world int scratch (row counts etc.)
+  unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
+  double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)
+  double *io_out;        // [nb][13] staged pos(3) quat(4) lvel(3) avel(3)
 };
 
 }  // namespace gz

@@ -39,6 +39,9 @@ struct gzcuda_batch {
   bool have_pd = false;
   int pgs_threads = 32;
   size_t pgs_smem = 0;
+  bool profiling = false;             // record an event pair around every k_pgs launch
+  std::vector<cudaEvent_t> pgs_ev;    // 2 per step of the last step call
+  int pgs_pairs = 0;
 };
 
 // ---- host restatement of dInvertPDMatrix for n = 3 (deps/opende/src/matrix.cpp:124-228) ----
@@ -111,6 +114,7 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   if (b->ev0) cudaEventDestroy(b->ev0);
   if (b->ev1) cudaEventDestroy(b->ev1);
   for (auto &e : b->evs) if (e) cudaEventDestroy(e);
+  for (auto &e : b->pgs_ev) cudaEventDestroy(e);
   if (b->stream) cudaStreamDestroy(b->stream);
   delete b;
 }
@@ -266,6 +270,9 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.row, (size_t)row_tot))) return rc;
   if ((rc = dev_alloc(b, &d.order, (size_t)row_tot))) return rc;
   if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)2 * max_rc + 4 * max_nb)))) return rc;
+  if ((rc = dev_alloc(b, &d.acc, (size_t)4))) return rc;
+  if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
+  if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
 
   int E = ((std::max(max_nb, 1) + 15) / 16) * 16;
   b->pgs_threads = 2 * E;
@@ -307,7 +314,7 @@ static int launch_collision(gzcuda_batch *b) {
   return 0;
 }
 
-static int launch_physics(gzcuda_batch *b, bool stage_events) {
+static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
   k_island<<<W, T, 0, b->stream>>>(d);
@@ -318,7 +325,9 @@ static int launch_physics(gzcuda_batch *b, bool stage_events) {
   k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
   k_order<<<W, T, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
+  if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
   k_pgs<<<W, b->pgs_threads, b->pgs_smem, b->stream>>>(d);
+  if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
   if (stage_events) cudaEventRecord(b->evs[3], b->stream);
   if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_integrate<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
@@ -326,11 +335,17 @@ static int launch_physics(gzcuda_batch *b, bool stage_events) {
   return 0;
 }
 
-int gzcuda_batch_step(gzcuda_batch *b, int n_steps) {
-  if (!b || n_steps < 0) return fail(GZCUDA_E_INVALID, "bad batch or step count");
-  CK(cudaSetDevice(b->device));
-  b->last_launches = 0;
-  CK(cudaEventRecord(b->ev0, b->stream));
+static int run_steps(gzcuda_batch *b, int n_steps) {
+  if (b->profiling) {
+    while ((int)b->pgs_ev.size() < 2 * n_steps) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e));
+      b->pgs_ev.push_back(e);
+    }
+    b->pgs_pairs = n_steps;
+  } else {
+    b->pgs_pairs = 0;
+  }
   for (int s = 0; s < n_steps; s++) {
     const bool last = (s == n_steps - 1);
     if (last) cudaEventRecord(b->evs[0], b->stream);
@@ -340,13 +355,81 @@ int gzcuda_batch_step(gzcuda_batch *b, int n_steps) {
     }
     launch_collision(b);
     if (last) cudaEventRecord(b->evs[1], b->stream);
-    launch_physics(b, last);
+    launch_physics(b, last, b->profiling ? s : -1);
     if (last) cudaEventRecord(b->evs[4], b->stream);
     b->d.step_index++;
   }
+  b->stage_valid = b->stage_valid || n_steps > 0;
+  return 0;
+}
+
+int gzcuda_batch_step(gzcuda_batch *b, int n_steps) {
+  if (!b || n_steps < 0) return fail(GZCUDA_E_INVALID, "bad batch or step count");
+  CK(cudaSetDevice(b->device));
+  b->last_launches = 0;
+  CK(cudaEventRecord(b->ev0, b->stream));
+  int rc = run_steps(b, n_steps);
+  if (rc) return rc;
   CK(cudaEventRecord(b->ev1, b->stream));
-  b->stage_valid = n_steps > 0;
   CK(cudaGetLastError());
+  return 0;
+}
+
+// Host-buffer variant of gzcuda_batch_step: what the Gazebo glue calls once per World::Update.
+int gzcuda_batch_step_io(gzcuda_batch *b, int n_steps, const double *wrench_in, double *state_out) {
+  if (!b || n_steps < 0) return fail(GZCUDA_E_INVALID, "bad batch or step count");
+  CK(cudaSetDevice(b->device));
+  const int T = 128, nb = std::max(b->d.nb, 1);
+  b->last_launches = 0;
+  CK(cudaEventRecord(b->ev0, b->stream));
+  if (wrench_in) {
+    CK(cudaMemcpyAsync(b->d.io_in, wrench_in, sizeof(double) * 6 * (size_t)b->d.nb, cudaMemcpyHostToDevice, b->stream));
+    k_apply_wrench<<<cdiv(nb, T), T, 0, b->stream>>>(b->d);
+    b->last_launches++;
+  }
+  int rc = run_steps(b, n_steps);
+  if (rc) return rc;
+  if (state_out) {
+    k_gather_state<<<cdiv(nb, T), T, 0, b->stream>>>(b->d);
+    b->last_launches++;
+    CK(cudaMemcpyAsync(state_out, b->d.io_out, sizeof(double) * 13 * (size_t)b->d.nb, cudaMemcpyDeviceToHost, b->stream));
+  }
+  CK(cudaEventRecord(b->ev1, b->stream));
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+int gzcuda_batch_set_profiling(gzcuda_batch *b, int on) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  b->profiling = on != 0;
+  return 0;
+}
+
+// Sum of the k_pgs launch durations of the last step call (needs profiling on) and their count.
+int gzcuda_batch_pgs_ms(gzcuda_batch *b, float *total_ms, int *launches) {
+  if (!b) return fail(GZCUDA_E_INVALID, "null batch");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  float tot = 0;
+  for (int i = 0; i < b->pgs_pairs; i++) {
+    float t = 0;
+    CK(cudaEventElapsedTime(&t, b->pgs_ev[2 * i], b->pgs_ev[2 * i + 1]));
+    tot += t;
+  }
+  if (total_ms) *total_ms = tot;
+  if (launches) *launches = b->pgs_pairs;
+  return 0;
+}
+
+// Running totals since creation (or the last reset): constraint rows, friction rows, contacts,
+// world-steps.  Used for the algorithmic-bytes figure of the roofline.
+int gzcuda_batch_get_counters(gzcuda_batch *b, unsigned long long out[4], int reset) {
+  if (!b || !out) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  CK(cudaMemcpy(out, b->d.acc, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  if (reset) CK(cudaMemset(b->d.acc, 0, 4 * sizeof(unsigned long long)));
   return 0;
 }
 
@@ -395,17 +478,20 @@ static int check_overflow(gzcuda_batch *b) {
 
 int gzcuda_batch_get_body_state(gzcuda_batch *b, double *pos, double *quat, double *lvel, double *avel) {
   if (!b) return fail(GZCUDA_E_INVALID, "null batch");
-  int rc = gzcuda_batch_sync(b);
-  if (rc) return rc;
-  std::vector<Body> hb(b->d.nb);
-  CK(cudaMemcpy(hb.data(), b->d.body, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
-  for (int i = 0; i < b->d.nb; i++) {
+  CK(cudaSetDevice(b->device));
+  const int nb = b->d.nb;
+  k_gather_state<<<cdiv(std::max(nb, 1), 128), 128, 0, b->stream>>>(b->d);
+  std::vector<double> h((size_t)13 * nb);
+  CK(cudaMemcpyAsync(h.data(), b->d.io_out, h.size() * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  for (int i = 0; i < nb; i++) {
+    const double *o = h.data() + 13 * (size_t)i;
     for (int k = 0; k < 3; k++) {
-      if (pos) pos[3 * i + k] = hb[i].pos[k];
-      if (lvel) lvel[3 * i + k] = hb[i].lvel[k];
-      if (avel) avel[3 * i + k] = hb[i].avel[k];
+      if (pos) pos[3 * i + k] = o[k];
+      if (lvel) lvel[3 * i + k] = o[7 + k];
+      if (avel) avel[3 * i + k] = o[10 + k];
     }
-    if (quat) for (int k = 0; k < 4; k++) quat[4 * i + k] = hb[i].q[k];
+    if (quat) for (int k = 0; k < 4; k++) quat[4 * i + k] = o[3 + k];
   }
   return check_overflow(b);
 }

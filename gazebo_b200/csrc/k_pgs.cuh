@@ -343,4 +343,21 @@ __global__ void k_integrate(DevBatch B) {
   for (int j = 0; j < 3; j++) { b.facc[j] = 0; b.tacc[j] = 0; }
 }
 
+// Host exchange without touching the whole Body record: external wrench in, pose/velocity out.
+__global__ void k_apply_wrench(DevBatch B) {
+  int bi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bi >= B.nb) return;
+  Body &b = B.body[bi];
+  const double *in = B.io_in + 6 * (size_t)bi;
+  for (int k = 0; k < 3; k++) { b.facc[k] += in[k]; b.tacc[k] += in[3 + k]; }
+}
+__global__ void k_gather_state(DevBatch B) {
+  int bi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bi >= B.nb) return;
+  const Body &b = B.body[bi];
+  double *o = B.io_out + 13 * (size_t)bi;
+  for (int k = 0; k < 3; k++) { o[k] = b.pos[k]; o[7 + k] = b.lvel[k]; o[10 + k] = b.avel[k]; }
+  for (int k = 0; k < 4; k++) o[3 + k] = b.q[k];
+}
+
 }  // namespace gz

@@ -209,6 +209,10 @@ __global__ void k_info1(DevBatch B) {
     if (m > wi.row_cap) { ws.overflow |= 4; m = 0; }
     ws.m = m;
     ws.n_fric = 2 * ws.n_contacts;
+    atomicAdd(&B.acc[0], (unsigned long long)m);
+    atomicAdd(&B.acc[1], (unsigned long long)(m ? 2 * ws.n_contacts : 0));
+    atomicAdd(&B.acc[2], (unsigned long long)ws.n_contacts);
+    atomicAdd(&B.acc[3], 1ull);
   }
 }
 

@@ -47,6 +47,11 @@ void          gzcuda_batch_destroy(gzcuda_batch *b);
  * (:407-453) = dWorldQuickStep (deps/opende/src/ode.cpp:1980-1995).  Asynchronous on the
  * batch's stream; gzcuda_batch_sync or any getter waits for completion. */
 int gzcuda_batch_step(gzcuda_batch *b, int n_steps);
+/* Same, with HOST buffers, synchronous: uploads wrench_in[nb][6] (force, torque per body; what
+ * plugins wrote with dBodyAddForce/dBodyAddTorque since the last step; NULL = none), runs
+ * n_steps, downloads state_out[nb][13] = pos(3) quat(4) lvel(3) avel(3) (what ODELink::MoveCallback
+ * reads, ODELink.cc:142-178; NULL = none).  Pinned host memory makes the copies asynchronous. */
+int gzcuda_batch_step_io(gzcuda_batch *b, int n_steps, const double *wrench_in, double *state_out);
 /* The two halves, for callers that need Events::beforePhysicsUpdate between them
  * (gazebo/physics/World.cc:755-786). */
 int gzcuda_batch_update_collision(gzcuda_batch *b);   /* ODEPhysics::UpdateCollision */
@@ -99,6 +104,13 @@ int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *da
 /* Instrumentation: device time in ms of the last gzcuda_batch_step call (CUDA events on the
  * batch stream) and the number of kernel launches it issued. */
 int gzcuda_batch_last_step_ms(gzcuda_batch *b, float *ms, long *launches);
+/* Profiling of the dominant kernel: when on, every k_pgs launch is bracketed by CUDA events;
+ * gzcuda_batch_pgs_ms returns the summed duration and launch count of the last step call. */
+int gzcuda_batch_set_profiling(gzcuda_batch *b, int on);
+int gzcuda_batch_pgs_ms(gzcuda_batch *b, float *total_ms, int *launches);
+/* Running totals since creation / last reset: out[0] constraint rows, out[1] friction rows,
+ * out[2] contacts, out[3] world-steps (the m and m_fric of SURVEY.md section 8d). */
+int gzcuda_batch_get_counters(gzcuda_batch *b, unsigned long long out[4], int reset);
 /* Per-stage device time of the last step call, ms: collide, assemble, pgs, integrate. */
 int gzcuda_batch_stage_ms(gzcuda_batch *b, float ms[4]);
 

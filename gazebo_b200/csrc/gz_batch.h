@@ -133,7 +133,8 @@ struct DevBatch {
   Contact *contact;
   Row *row;
   int *order;            // per world slab: order[k] = world-local row index
-  int *qhead;            // per world: [2][max executors] queue heads (all / friction)
+  double *prec;          // packed row records (33 doubles each), per world slab at row0
+  int *sched;            // per world [max_nb][5]: nA, nF, queue start / friction start / end
   int *scratch;          // per world int scratch (row counts etc.)
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)

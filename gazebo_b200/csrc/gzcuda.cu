@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -39,6 +40,7 @@ struct gzcuda_batch {
   bool have_pd = false;
   int pgs_threads = 32;
   size_t pgs_smem = 0;
+  PgsCfg pgs;
   bool profiling = false;             // record an event pair around every k_pgs launch
   std::vector<cudaEvent_t> pgs_ev;    // 2 per step of the last step call
   int pgs_pairs = 0;
@@ -269,14 +271,30 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.contact, (size_t)contact_tot))) return rc;
   if ((rc = dev_alloc(b, &d.row, (size_t)row_tot))) return rc;
   if ((rc = dev_alloc(b, &d.order, (size_t)row_tot))) return rc;
-  if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)2 * max_rc + 4 * max_nb)))) return rc;
+  if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)2 * max_rc)))) return rc;
+  if ((rc = dev_alloc(b, &d.prec, (size_t)GZ_REC * row_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.sched, (size_t)W * GZ_SCHED * std::max(max_nb, 1)))) return rc;
   if ((rc = dev_alloc(b, &d.acc, (size_t)4))) return rc;
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
 
-  int E = ((std::max(max_nb, 1) + 15) / 16) * 16;
-  b->pgs_threads = 2 * E;
-  b->pgs_smem = ((size_t)13 * max_nb + 2 + (size_t)9 * E) * sizeof(double);
+  // PGS launch shape: L = 2 * nbp lanes per world, WPC worlds per CTA, pooled record budget
+  int nbp = 1;
+  while (nbp < max_nb) nbp <<= 1;
+  PgsCfg &c = b->pgs;
+  c.nbp = nbp; c.L = 2 * nbp;
+  c.wpc = std::max(1, std::min(32, 64 / c.L));
+  b->pgs_threads = std::max(32, c.wpc * c.L);
+  const size_t slot_bytes = (size_t)23 * nbp * sizeof(double);
+  size_t smem_target = 72 * 1024;
+  if (const char *e = getenv("GZCUDA_PGS_SMEM_KB")) smem_target = (size_t)atoi(e) * 1024;
+  long budget = ((long)(smem_target / c.wpc) - (long)slot_bytes) / (long)(GZ_REC * sizeof(double));
+  const long max_budget = ((long)(200 * 1024) / c.wpc - (long)slot_bytes) / (long)(GZ_REC * sizeof(double));
+  budget = std::min(budget, max_budget);
+  budget = std::max(0L, std::min(budget, (long)max_rc));
+  c.budget = (int)budget;
+  b->pgs_smem = (size_t)c.wpc * (slot_bytes + (size_t)c.budget * GZ_REC * sizeof(double));
+  if (b->pgs_smem > 227 * 1024) return fail(GZCUDA_E_INVALID, "PGS shared-memory footprint too large");
   if (b->pgs_smem > 48 * 1024)
     CK(cudaFuncSetAttribute(k_pgs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
   return 0;
@@ -322,11 +340,11 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_info1<<<W, T, 0, b->stream>>>(d);
   if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
+  k_schedule<<<W, T, 0, b->stream>>>(d);
   k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
-  k_order<<<W, T, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
-  k_pgs<<<W, b->pgs_threads, b->pgs_smem, b->stream>>>(d);
+  k_pgs<<<cdiv(W, b->pgs.wpc), b->pgs_threads, b->pgs_smem, b->stream>>>(d, b->pgs);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
   if (stage_events) cudaEventRecord(b->evs[3], b->stream);
   if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }

@@ -278,14 +278,17 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
 
-  // PGS launch shape: L = 2 * nbp lanes per world, WPC worlds per CTA, pooled record budget
+  // PGS launch shape: L = 2 * nbp lanes per world inside TW threads, WPC worlds per CTA,
+  // pooled record budget in shared memory
   int nbp = 1;
   while (nbp < max_nb) nbp <<= 1;
   PgsCfg &c = b->pgs;
   c.nbp = nbp; c.L = 2 * nbp;
-  c.wpc = std::max(1, std::min(32, 64 / c.L));
-  b->pgs_threads = std::max(32, c.wpc * c.L);
-  const size_t slot_bytes = (size_t)23 * nbp * sizeof(double);
+  c.tw = std::max(32, c.L);
+  c.wpc = std::max(1, 128 / c.tw);
+  if (const char *e = getenv("GZCUDA_PGS_WPC")) c.wpc = std::max(1, std::min(32, atoi(e)));
+  b->pgs_threads = c.wpc * c.tw;
+  const size_t slot_bytes = pgs_slot_doubles(nbp) * sizeof(double);
   size_t smem_target = 72 * 1024;
   if (const char *e = getenv("GZCUDA_PGS_SMEM_KB")) smem_target = (size_t)atoi(e) * 1024;
   long budget = ((long)(smem_target / c.wpc) - (long)slot_bytes) / (long)(GZ_REC * sizeof(double));
@@ -295,8 +298,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   c.budget = (int)budget;
   b->pgs_smem = (size_t)c.wpc * (slot_bytes + (size_t)c.budget * GZ_REC * sizeof(double));
   if (b->pgs_smem > 227 * 1024) return fail(GZCUDA_E_INVALID, "PGS shared-memory footprint too large");
-  if (b->pgs_smem > 48 * 1024)
-    CK(cudaFuncSetAttribute(k_pgs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
+  if (b->pgs_smem > 48 * 1024) {
+    CK(cudaFuncSetAttribute(k_pgs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
+    CK(cudaFuncSetAttribute(k_pgs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
+  }
   return 0;
 }
 
@@ -344,7 +349,8 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
-  k_pgs<<<cdiv(W, b->pgs.wpc), b->pgs_threads, b->pgs_smem, b->stream>>>(d, b->pgs);
+  if (b->pgs.L <= 32) k_pgs<false><<<cdiv(W, b->pgs.wpc), b->pgs_threads, b->pgs_smem, b->stream>>>(d, b->pgs);
+  else k_pgs<true><<<cdiv(W, b->pgs.wpc), b->pgs_threads, b->pgs_smem, b->stream>>>(d, b->pgs);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
   if (stage_events) cudaEventRecord(b->evs[3], b->stream);
   if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
@@ -615,6 +621,18 @@ int gzcuda_batch_get_stats(gzcuda_batch *b, double *rms_residual, int *num_conta
     if (num_contacts) num_contacts[w] = ws[w].n_contacts;
     if (num_rows) num_rows[w] = ws[w].m;
   }
+  return 0;
+}
+
+// Instrumentation of the last step's k_pgs: per world, loop trips and row updates of its longest
+// lane, and the cycles its sweeps took (out[nw][3]).
+int gzcuda_batch_get_pgs_debug(gzcuda_batch *b, int *out) {
+  if (!b || !out) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  std::vector<WorldStep> ws(b->d.n_worlds);
+  CK(cudaMemcpy(ws.data(), b->d.wstep, ws.size() * sizeof(WorldStep), cudaMemcpyDeviceToHost));
+  for (int w = 0; w < b->d.n_worlds; w++) { out[3 * w] = ws[w].pad[0]; out[3 * w + 1] = ws[w].pad[1]; out[3 * w + 2] = ws[w].n_fric; }
   return 0;
 }
 

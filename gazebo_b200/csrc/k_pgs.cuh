@@ -33,18 +33,20 @@ __device__ inline WScratch wscratch(const DevBatch &B, int w) {
   return s;
 }
 
-// ---- packed row record: what the sweeps stream, 33 doubles = 264 B --------------------------
+// ---- packed row record: what the sweeps stream, 34 doubles = 272 B (16-byte aligned) -------
 // [0..11] J (scaled by Ad)   [12..23] iMJ   [24] rhs  [25] rhs_erp  [26] Adcfm  [27] lo  [28] hi
-// [29] lambda  [30] lambda_erp  [31..32] RecInts
+// [29] lambda  [30] lambda_erp  [31] Ad (statistics)  [32..33] RecInts
 // Records of a world are stored executor by executor (an executor = the body that owns the row:
 // the higher-indexed of its two bodies), each executor's rows in order[] sequence, so a thread
 // walks a contiguous range and the friction rows of an executor are the tail of its range.
-#define GZ_REC 33
+#define GZ_REC 34
+#define GZ_REC_INTS 32
 struct RecInts {
-  int orig;               // world-local row index (write-back, statistics)
   int findex_p;           // -1 bilateral, -2 contact normal, >= 0 PACKED index of the normal row
   unsigned short b1, b2;  // world-local bodies, b2 = 0xFFFF: none
   unsigned short t1, t2;  // tickets: rows touching b1 / b2 that come earlier in order[]
+  unsigned short run;     // rows that follow in the same block (same bodies, consecutive tickets)
+  unsigned short pad;
 };
 // per-world schedule table (ints): for body/executor b: nA, nF, qs, qf, qe
 #define GZ_SCHED 5
@@ -175,213 +177,19 @@ __global__ void k_rowfinish(DevBatch B) {
   rec[25] = rhs_erp * Ad;
   rec[26] = Ad * cfm;
   rec[27] = r.lo; rec[28] = r.hi;
-  rec[29] = lam; rec[30] = lam_erp;
+  rec[29] = lam; rec[30] = lam_erp; rec[31] = Ad;
   RecInts ri;
-  ri.orig = i;
+  ri.run = 0; ri.pad = 0;
+  B.order[wi.row0 + r.next_f] = i;   // order[] is free after k_schedule: packed index -> row
   ri.findex_p = (r.findex >= 0) ? B.row[wi.row0 + r.findex].next_f : r.findex;
   ri.b1 = (unsigned short)r.b1; ri.b2 = (r.b2 >= 0) ? (unsigned short)r.b2 : (unsigned short)0xFFFF;
   ri.t1 = (unsigned short)r.t1a; ri.t2 = (unsigned short)r.t2a;
-  *reinterpret_cast<RecInts *>(rec + 31) = ri;
+  *reinterpret_cast<RecInts *>(rec + GZ_REC_INTS) = ri;
 }
 
-// The SOR-PGS sweeps.  L = 2 * nbp lanes per world (nbp = executors, a power of two >= nb;
-// lane = 2 * executor + solve), WPC worlds per CTA.  Dynamic shared memory per CTA:
-//   per world slot: ca[2][nbp][6] doubles | stat[nbp][9] doubles | done[2][nbp] ints | nA[nbp], nF[nbp] ints
-//   pool: WPC * budget packed records shared by the CTA's worlds (first come first served);
-//         records that do not fit are streamed from the packed slab in global memory instead.
-struct PgsCfg { int L, nbp, wpc, budget; };
-
-__device__ inline size_t pgs_slot_doubles(int nbp) { return (size_t)12 * nbp + 9 * nbp + 2 * nbp; }
-
-__global__ void k_pgs(DevBatch B, PgsCfg cfg) {
-  extern __shared__ double shd[];
-  const int L = cfg.L, nbp = cfg.nbp;
-  const int slot = threadIdx.x / L, l = threadIdx.x % L;
-  const int w = blockIdx.x * cfg.wpc + slot;
-  const bool live = w < B.n_worlds;
-  const size_t slotd = pgs_slot_doubles(nbp);
-  double *ca = shd + slot * slotd;                       // [2][nbp][6]
-  double *stat = ca + 12 * nbp;                          // [nbp][9]
-  volatile int *done = (volatile int *)(stat + 9 * nbp); // [2][nbp]
-  int *nAs = (int *)(stat + 9 * nbp) + 2 * nbp;          // [nbp]
-  int *nFs = nAs + nbp;                                  // [nbp]
-  double *pool = shd + cfg.wpc * slotd;
-  __shared__ int pool_off[33], pool_cap[33];
-
-  WorldInfo wi;
-  int nb = 0, m = 0;
-  const int *sch = nullptr;
-  const double *gslab = nullptr;
-  if (live) { wi = B.world[w]; nb = wi.nb; m = B.wstep[w].m; sch = wsched(B, w); gslab = wprec(B, wi); }
-  if (threadIdx.x == 0) {
-    int used = 0;
-    const int total = cfg.wpc * cfg.budget;
-    for (int k = 0; k < cfg.wpc; k++) {
-      int wk = blockIdx.x * cfg.wpc + k;
-      int mk = (wk < B.n_worlds) ? B.wstep[wk].m : 0;
-      int c = mk < total - used ? mk : total - used;
-      pool_off[k] = used; pool_cap[k] = c; used += c;
-    }
-  }
-  __syncthreads();
-  // stage the packed records (coalesced copy), zero the counters, load the per-body tables
-  for (int k = 0; k < cfg.wpc; k++) {
-    int wk = blockIdx.x * cfg.wpc + k;
-    if (wk >= B.n_worlds) break;
-    const WorldInfo wk_i = B.world[wk];
-    const double *src = wprec(B, wk_i);
-    double *dst = pool + (size_t)pool_off[k] * GZ_REC;
-    const int n = pool_cap[k] * GZ_REC;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
-  }
-  const int cap = pool_cap[slot];
-  double *mypool = pool + (size_t)pool_off[slot] * GZ_REC;
-  for (int i = l; i < nbp; i += L) {
-    done[i] = 0; done[nbp + i] = 0;
-    nAs[i] = (live && i < nb) ? sch[GZ_SCHED * i + 0] : 0;
-    nFs[i] = (live && i < nb) ? sch[GZ_SCHED * i + 1] : 0;
-    for (int t = 0; t < 6; t++) { ca[6 * i + t] = 0; ca[6 * (nbp + i) + t] = 0; }
-  }
-  __syncthreads();
-#define GZ_RECPTR(idx) (((idx) < cap) ? (mypool + (size_t)(idx) * GZ_REC) : (const_cast<double *>(gslab) + (size_t)(idx) * GZ_REC))
-  // initial caccel = iMJ * lambda0 over the warm-started (persistent-joint) rows, row index order
-  if (live && B.p.warm_start > 0 && m > 0) {
-    for (int b = l; b < nb; b += L) {
-      const Body &bd = B.body[wi.body0 + b];
-      if (!B.bstep[wi.body0 + b].active) continue;
-      for (int q = bd.joint_begin; q < bd.joint_end; q++) {
-        const Joint &j = B.joint[B.body_joint[q]];
-        for (int rr = 0; rr < j.m; rr++) {
-          const int pidx = B.row[wi.row0 + j.row0 + rr].next_f;
-          const double *rec = GZ_RECPTR(pidx);
-          const RecInts ri = *reinterpret_cast<const RecInts *>(rec + 31);
-          const double *im = (ri.b1 == b) ? rec + 12 : rec + 18;
-          for (int t = 0; t < 6; t++) {
-            ca[6 * b + t] += im[t] * rec[29];
-            ca[6 * (nbp + b) + t] += im[t] * rec[30];
-          }
-        }
-      }
-    }
-  }
-  __syncthreads();
-  const int s = l & 1, e = l >> 1;
-  const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
-  const double smooth = B.p.smooth_contacts;
-  double *cas = ca + 6 * (size_t)nbp * s;
-  volatile int *dn = done + nbp * s;
-  double acc[3] = {0, 0, 0}, err[3] = {0, 0, 0};
-  int cnt[3] = {0, 0, 0};
-  int qs = 0, qf = 0, qe = 0;
-  if (live && e < nb && m > 0) { qs = sch[GZ_SCHED * e + 2]; qf = sch[GZ_SCHED * e + 3]; qe = sch[GZ_SCHED * e + 4]; }
-  if (qe > qs) {
-    int sweep = 0, idx = qs;
-    if (iters == 0) { idx = qf; if (qf == qe) sweep = total; }
-    // header of the current row, kept in registers while the lane waits for its turn
-    double *rec = nullptr;
-    int b1 = 0, b2 = -1, fi = -1, tg1 = 0, tg2 = 0;
-    bool need_header = true;
-    while (sweep < total) {
-      if (need_header) {
-        rec = GZ_RECPTR(idx);
-        const RecInts ri = *reinterpret_cast<const RecInts *>(rec + 31);
-        b1 = ri.b1; b2 = (ri.b2 == 0xFFFF) ? -1 : (int)ri.b2; fi = ri.findex_p;
-        if (sweep < iters) {
-          tg1 = sweep * nAs[b1] + ri.t1;
-          if (b2 >= 0) tg2 = sweep * nAs[b2] + ri.t2;
-        } else {   // friction-only sweeps: ticket among the friction rows of the body
-          tg1 = iters * nAs[b1] + (sweep - iters) * nFs[b1] + (ri.t1 - (nAs[b1] - nFs[b1]));
-          if (b2 >= 0) tg2 = iters * nAs[b2] + (sweep - iters) * nFs[b2] + (ri.t2 - (nAs[b2] - nFs[b2]));
-        }
-        need_header = false;
-      }
-      const bool ready = (dn[b1] == tg1) && (b2 < 0 || dn[b2] == tg2);
-      if (ready) {
-        __threadfence_block();
-        double *c1 = cas + 6 * b1;
-        double *c2 = (b2 >= 0) ? cas + 6 * b2 : nullptr;
-        const double old_lambda = rec[29 + s];
-        double delta = rec[24 + s] - old_lambda * rec[26];
-        delta -= c1[0] * rec[0] + c1[1] * rec[1] + c1[2] * rec[2] + c1[3] * rec[3] + c1[4] * rec[4] + c1[5] * rec[5];
-        if (c2) delta -= c2[0] * rec[6] + c2[1] * rec[7] + c2[2] * rec[8] + c2[3] * rec[9] + c2[4] * rec[10] + c2[5] * rec[11];
-        double hi_act, lo_act;
-        if (fi >= 0) {
-          const double *nrec = GZ_RECPTR(fi);
-          hi_act = fabs(rec[28] * nrec[29 + s]);   // pyramid friction: |mu * lambda_normal|
-          lo_act = -hi_act;
-        } else { hi_act = rec[28]; lo_act = rec[27]; }
-        double nl = old_lambda + delta;
-        if (nl < lo_act) { delta = lo_act - old_lambda; nl = lo_act; }
-        else if (nl > hi_act) { delta = hi_act - old_lambda; nl = hi_act; }
-        // SMOOTH_LAMBDA on the lambda solve only; delta is not recomputed (quickstep_pgs_lcp.cpp:687-708)
-        if (s == 0 && fi != -1) nl = (1.0 - smooth) * nl + smooth * old_lambda;
-        rec[29 + s] = nl;
-        for (int t = 0; t < 6; t++) c1[t] += delta * rec[12 + t];
-        if (c2) for (int t = 0; t < 6; t++) c2[t] += delta * rec[18 + t];
-        // Statistics are reset every sweep (friction class) or every non-friction sweep (the
-        // other two), so only the last such sweeps survive: accumulate just there.
-        if (s == 0 && (sweep == iters - 1 || sweep == total - 1)) {
-          const int cls = (fi == -1) ? 0 : (fi == -2 ? 1 : 2);
-          if (sweep == iters - 1 || cls == 2) {
-            const RecInts ri = *reinterpret_cast<const RecInts *>(rec + 31);
-            const double Ad = B.row[wi.row0 + ri.orig].Ad;
-            double Ad2 = 0.0;
-            if (!dequal(Ad, 0.0)) Ad2 = 1.0 / (Ad * Ad);
-            const double d2 = delta * delta;
-            acc[cls] += d2; err[cls] += d2 * Ad2; cnt[cls]++;
-          }
-        }
-        __threadfence_block();
-        dn[b1] = tg1 + 1;
-        if (b2 >= 0) dn[b2] = tg2 + 1;
-        idx++;
-        need_header = true;
-        if (idx == qe) {
-          sweep++;
-          if (sweep == total - 1 && total - 1 != iters - 1) { acc[2] = 0; err[2] = 0; cnt[2] = 0; }
-          if (sweep < iters) idx = qs;
-          else { idx = qf; if (qf == qe) sweep = total; }
-        }
-      }
-    }
-  }
-  if (s == 0) {
-    double *st = stat + 9 * e;
-    for (int k = 0; k < 3; k++) { st[k] = acc[k]; st[3 + k] = err[k]; st[6 + k] = (double)cnt[k]; }
-  }
-  __syncthreads();
-  if (live) {
-    // write lambda back to the rows (k_lambda_save copies them to the joints) and caccel to the bodies
-    Row *rows = B.row + wi.row0;
-    for (int idx = qs + s; idx < qe; idx += 2) {     // the two solve lanes of an executor split its rows
-      const double *rec = GZ_RECPTR(idx);
-      const RecInts ri = *reinterpret_cast<const RecInts *>(rec + 31);
-      rows[ri.orig].lambda = rec[29];
-      rows[ri.orig].lambda_erp = rec[30];
-    }
-    for (int i = l; i < nb; i += L) {
-      BodyStep &bs = B.bstep[wi.body0 + i];
-      for (int t = 0; t < 6; t++) { bs.caccel[t] = ca[6 * i + t]; bs.caccel_erp[t] = ca[6 * (nbp + i) + t]; }
-    }
-    if (l == 0) {
-      WorldStep &ws = B.wstep[w];
-      double a[3] = {0, 0, 0}, er[3] = {0, 0, 0}, c[3] = {0, 0, 0};
-      if (m > 0)
-        for (int q = 0; q < nb; q++)
-          for (int k = 0; k < 3; k++) { a[k] += stat[9 * q + k]; er[k] += stat[9 * q + 3 + k]; c[k] += stat[9 * q + 6 + k]; }
-      // quickstep_pgs_lcp.cpp:814-855
-      const double tot = c[0] + c[1] + c[2];
-      for (int k = 0; k < 3; k++) {
-        ws.rms_dlambda[k] = sqrt(c[k] > 0 ? a[k] / c[k] : 0.0);
-        ws.rms_residual[k] = sqrt(c[k] > 0 ? er[k] / c[k] : 0.0);
-      }
-      ws.rms_dlambda[3] = sqrt((a[0] + a[1] + a[2] > 0) ? (a[0] + a[1] + a[2]) / tot : 0.0);
-      ws.rms_residual[3] = sqrt((er[0] + er[1] + er[2] > 0) ? (er[0] + er[1] + er[2]) / tot : 0.0);
-      ws.num_contacts_stat = (int)c[1];
-    }
-  }
-#undef GZ_RECPTR
-}
+}  // namespace gz
+#include "k_pgs_sweep.cuh"
+namespace gz {
 
 // One thread per joint: save lambda for the next step's warm start.
 __global__ void k_lambda_save(DevBatch B) {

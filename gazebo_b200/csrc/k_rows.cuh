@@ -208,7 +208,8 @@ __global__ void k_info1(DevBatch B) {
     int m = mj + 3 * ws.n_contacts;
     if (m > wi.row_cap) { ws.overflow |= 4; m = 0; }
     ws.m = m;
-    ws.n_fric = 2 * ws.n_contacts;
+    ws.n_fric = 0;   // reused by k_pgs as a cycle counter (instrumentation)
+    ws.pad[0] = 0; ws.pad[1] = 0;
     atomicAdd(&B.acc[0], (unsigned long long)m);
     atomicAdd(&B.acc[1], (unsigned long long)(m ? 2 * ws.n_contacts : 0));
     atomicAdd(&B.acc[2], (unsigned long long)ws.n_contacts);

@@ -111,6 +111,9 @@ int gzcuda_batch_pgs_ms(gzcuda_batch *b, float *total_ms, int *launches);
 /* Running totals since creation / last reset: out[0] constraint rows, out[1] friction rows,
  * out[2] contacts, out[3] world-steps (the m and m_fric of SURVEY.md section 8d). */
 int gzcuda_batch_get_counters(gzcuda_batch *b, unsigned long long out[4], int reset);
+/* Instrumentation of the last step's k_pgs launch, out[nw][3]: loop trips and row updates of the
+ * world's longest lane, and the SM cycles its sweeps took. */
+int gzcuda_batch_get_pgs_debug(gzcuda_batch *b, int *out);
 /* Per-stage device time of the last step call, ms: collide, assemble, pgs, integrate. */
 int gzcuda_batch_stage_ms(gzcuda_batch *b, float ms[4]);
 

@@ -13,6 +13,10 @@
 #pragma once
 #include "../../include/gzcuda_scene.h"
 
+// PGS schedule buckets (k_pgs.cuh): c = log2(lanes per solve) in 0..4, rung of the period ladder in 1..127
+#define GZ_NRUNG 128
+#define GZ_NBUCKET (5 * GZ_NRUNG)
+
 namespace gz {
 
 struct Body {
@@ -102,8 +106,7 @@ struct Row {
 struct WorldInfo {
   int body0, nb, geom0, ng, joint0, nj;
   int pair0, pair_cap, contact0, contact_cap, row0, row_cap;
-  int bj0;   // unused
-  int pad;
+  int slot0, slot_cap;   // packed-record slab of the world (schedule slots), see k_pgs.cuh
 };
 
 struct WorldStep {
@@ -133,9 +136,18 @@ struct DevBatch {
   Contact *contact;
   Row *row;
   int *order;            // per world slab: order[k] = world-local row index
-  double *prec;          // packed row records (33 doubles each), per world slab at row0
-  int *sched;            // per world [max_nb][5]: nA, nF, queue start / friction start / end
-  int *scratch;          // per world int scratch (row counts etc.)
+  double *prec;          // packed row records (34 doubles each), one slab per PGS warp (k_pgs.cuh)
+  long prec_cap;         // records the pool holds
+  double *lamg;          // [slots][2] lambda / lambda_erp spill for worlds whose lambdas exceed shared memory
+  int *wsched;           // per world WSched {R, k, nstage, bucket, idx, ...} (8 ints)
+  int *bk_count;         // [GZ_NBUCKET] worlds per schedule bucket (k, R) this step
+  int *bk_tab;           // [4][GZ_NBUCKET+1]: first warp / first record of each bucket; the same sorted heavy-first
+  int *warp_world;       // [n_worlds + GZ_NBUCKET][16] worlds of each PGS warp this step (-1: none)
+  int *scratch;          // per world int scratch [4][max_row_cap]
+  unsigned long long *prof;  // [8] k_pgs segment cycle sums (GZCUDA_PGS_PROF=1), see gzcuda_batch_get_pgs_profile
+  int pgs_prof;
+  int pgs_wpw_max;       // worlds per PGS warp the shared-memory budget allows
+  int pgs_rt, pgs_kmin, pgs_kmax;   // scheduler knobs: target period, lanes-per-solve range
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)
   double *io_out;        // [nb][13] staged pos(3) quat(4) lvel(3) avel(3)

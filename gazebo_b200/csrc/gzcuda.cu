@@ -38,7 +38,6 @@ struct gzcuda_batch {
   long last_launches = 0;
   bool stage_valid = false;
   bool have_pd = false;
-  int pgs_threads = 32;
   size_t pgs_smem = 0;
   PgsCfg pgs;
   bool profiling = false;             // record an event pair around every k_pgs launch
@@ -189,7 +188,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     }
   }
   int max_nb = 0, max_ng = 0, max_nj = 0, max_pc = 0, max_cc = 0, max_rc = 0;
-  long pair_tot = 0, contact_tot = 0, row_tot = 0;
+  long pair_tot = 0, contact_tot = 0, row_tot = 0, slot_tot = 0;
   for (int w = 0; w < W; w++) {
     const int g0 = sc->geom_off[w], g1 = sc->geom_off[w + 1];
     int nspace = 0;
@@ -246,8 +245,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     wi.contact_cap = std::min(8 * wi.pair_cap, std::max(64, 24 * n));
     wi.row_cap = 6 * wi.nj + 3 * wi.contact_cap;
     wi.pair0 = (int)pair_tot; wi.contact0 = (int)contact_tot; wi.row0 = (int)row_tot;
-    pair_tot += wi.pair_cap; contact_tot += wi.contact_cap; row_tot += wi.row_cap;
-    if (row_tot > 0x7fffffffL) return fail(GZCUDA_E_INVALID, "batch too large (row slab index overflow)");
+    wi.slot_cap = 0; wi.slot0 = 0;
+    // schedule slots a world can need: about twice its rows (periods are padded to a ladder and to k lanes)
+    pair_tot += wi.pair_cap; contact_tot += wi.contact_cap; row_tot += wi.row_cap; slot_tot += 2 * wi.row_cap + 64;
+    if (row_tot > 0x7fffffffL || slot_tot > 0x7fffffffL) return fail(GZCUDA_E_INVALID, "batch too large (row slab index overflow)");
     max_nb = std::max(max_nb, wi.nb); max_ng = std::max(max_ng, wi.ng); max_nj = std::max(max_nj, wi.nj);
     max_pc = std::max(max_pc, wi.pair_cap); max_cc = std::max(max_cc, wi.contact_cap);
     max_rc = std::max(max_rc, wi.row_cap);
@@ -271,33 +272,48 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.contact, (size_t)contact_tot))) return rc;
   if ((rc = dev_alloc(b, &d.row, (size_t)row_tot))) return rc;
   if ((rc = dev_alloc(b, &d.order, (size_t)row_tot))) return rc;
-  if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)2 * max_rc)))) return rc;
-  if ((rc = dev_alloc(b, &d.prec, (size_t)GZ_REC * row_tot))) return rc;
-  if ((rc = dev_alloc(b, &d.sched, (size_t)W * GZ_SCHED * std::max(max_nb, 1)))) return rc;
+  if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)4 * max_rc)))) return rc;
+  // record pool of the PGS warps: every world's slots, rounded up to whole warps (16 lane pairs per
+  // round), plus one partly filled warp per bucket in use; clamped to a share of device memory
+  {
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    long want = 2 * slot_tot + 64L * 1024 * 16;
+    const long most = (long)(free_b / 3 / (GZ_REC * sizeof(double)));
+    d.prec_cap = std::max(16L * GZ_RMAX, std::min(want, most));
+    if (d.prec_cap > 0x7fffffffL) d.prec_cap = 0x7fffffffL;
+  }
+  if ((rc = dev_alloc(b, &d.prec, (size_t)GZ_REC * d.prec_cap))) return rc;
+  if ((rc = dev_alloc(b, &d.lamg, (size_t)2 * d.prec_cap))) return rc;
+  if ((rc = dev_alloc(b, &d.wsched, (size_t)8 * W))) return rc;
+  if ((rc = dev_alloc(b, &d.bk_count, (size_t)GZ_NBUCKET))) return rc;
+  if ((rc = dev_alloc(b, &d.bk_tab, (size_t)4 * (GZ_NBUCKET + 1)))) return rc;
+  if ((rc = dev_alloc(b, &d.warp_world, (size_t)16 * (W + GZ_NBUCKET)))) return rc;
   if ((rc = dev_alloc(b, &d.acc, (size_t)4))) return rc;
+  if ((rc = dev_alloc(b, &d.prof, (size_t)8))) return rc;
+  d.pgs_prof = getenv("GZCUDA_PGS_PROF") ? atoi(getenv("GZCUDA_PGS_PROF")) : 0;
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
 
-  // PGS launch shape: L = 2 * nbp lanes per world inside TW threads, WPC worlds per CTA,
-  // pooled record budget in shared memory
-  int nbp = 1;
-  while (nbp < max_nb) nbp <<= 1;
+  // PGS launch shape (k_pgs_sweep.cuh): one warp per CTA, a fixed shared-memory budget per CTA
+  // that holds the accumulators of its worlds, their lambdas and as many row records as fit.
+  d.pgs_rt = 28; d.pgs_kmin = 1; d.pgs_kmax = 16;
+  if (const char *e = getenv("GZCUDA_PGS_RT")) d.pgs_rt = std::max(1, atoi(e));
+  if (const char *e = getenv("GZCUDA_PGS_KMIN")) d.pgs_kmin = std::max(1, std::min(16, atoi(e)));
+  if (const char *e = getenv("GZCUDA_PGS_KMAX")) d.pgs_kmax = std::max(d.pgs_kmin, std::min(16, atoi(e)));
+  for (int *kk : {&d.pgs_kmin, &d.pgs_kmax}) { int v = 1; while (2 * v <= *kk) v <<= 1; *kk = v; }
   PgsCfg &c = b->pgs;
-  c.nbp = nbp; c.L = 2 * nbp;
-  c.tw = std::max(32, c.L);
-  c.wpc = std::max(1, 128 / c.tw);
-  if (const char *e = getenv("GZCUDA_PGS_WPC")) c.wpc = std::max(1, std::min(32, atoi(e)));
-  b->pgs_threads = c.wpc * c.tw;
-  const size_t slot_bytes = pgs_slot_doubles(nbp) * sizeof(double);
-  size_t smem_target = 72 * 1024;
-  if (const char *e = getenv("GZCUDA_PGS_SMEM_KB")) smem_target = (size_t)atoi(e) * 1024;
-  long budget = ((long)(smem_target / c.wpc) - (long)slot_bytes) / (long)(GZ_REC * sizeof(double));
-  const long max_budget = ((long)(200 * 1024) / c.wpc - (long)slot_bytes) / (long)(GZ_REC * sizeof(double));
-  budget = std::min(budget, max_budget);
-  budget = std::max(0L, std::min(budget, (long)max_rc));
-  c.budget = (int)budget;
-  b->pgs_smem = (size_t)c.wpc * (slot_bytes + (size_t)c.budget * GZ_REC * sizeof(double));
-  if (b->pgs_smem > 227 * 1024) return fail(GZCUDA_E_INVALID, "PGS shared-memory footprint too large");
+  c.nbp = std::max(max_nb, 1);
+  size_t smem = 40 * 1024;
+  if (const char *e = getenv("GZCUDA_PGS_SMEM_KB")) smem = (size_t)atoi(e) * 1024;
+  const size_t ca_bytes = (size_t)12 * (c.nbp + 1) * sizeof(double);
+  const size_t ring_bytes = (size_t)GZ_RING_DOUBLES * sizeof(double);
+  smem = std::max(smem, ca_bytes + ring_bytes + 4096);
+  if (smem > (size_t)227 * 1024) return fail(GZCUDA_E_INVALID, "PGS accumulators of one world exceed shared memory");
+  c.wpw_max = (int)std::min<size_t>(16, std::max<size_t>(1, ((smem - ring_bytes) / 2) / ca_bytes));
+  d.pgs_wpw_max = c.wpw_max;
+  c.smem_doubles = (int)(smem / sizeof(double));
+  b->pgs_smem = smem;
   if (b->pgs_smem > 48 * 1024) {
     CK(cudaFuncSetAttribute(k_pgs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
     CK(cudaFuncSetAttribute(k_pgs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
@@ -345,17 +361,19 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_info1<<<W, T, 0, b->stream>>>(d);
   if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
-  k_schedule<<<W, T, 0, b->stream>>>(d);
+  k_schedule<<<W, 32, 0, b->stream>>>(d);
+  k_slab<<<1, 256, 0, b->stream>>>(d);
   k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
-  if (b->pgs.L <= 32) k_pgs<false><<<cdiv(W, b->pgs.wpc), b->pgs_threads, b->pgs_smem, b->stream>>>(d, b->pgs);
-  else k_pgs<true><<<cdiv(W, b->pgs.wpc), b->pgs_threads, b->pgs_smem, b->stream>>>(d, b->pgs);
+  // at most one warp per world plus a partly filled one per bucket; CTAs beyond the step's warp count exit at once
+  if (d.pgs_prof) k_pgs<true><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+  else k_pgs<false><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
   if (stage_events) cudaEventRecord(b->evs[3], b->stream);
   if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_integrate<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
-  b->last_launches += 8;
+  b->last_launches += 9;
   return 0;
 }
 
@@ -633,6 +651,17 @@ int gzcuda_batch_get_pgs_debug(gzcuda_batch *b, int *out) {
   std::vector<WorldStep> ws(b->d.n_worlds);
   CK(cudaMemcpy(ws.data(), b->d.wstep, ws.size() * sizeof(WorldStep), cudaMemcpyDeviceToHost));
   for (int w = 0; w < b->d.n_worlds; w++) { out[3 * w] = ws[w].pad[0]; out[3 * w + 1] = ws[w].pad[1]; out[3 * w + 2] = ws[w].n_fric; }
+  return 0;
+}
+
+// Developer instrumentation (GZCUDA_PGS_PROF=1 at creation): cycle sums over all k_pgs warps since
+// creation: fetch issue, wait, ring load, row update + sync, active lanes, rounds.
+int gzcuda_batch_get_pgs_profile(gzcuda_batch *b, unsigned long long out[8]) {
+  if (!b || !out) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  CK(cudaMemcpy(out, b->d.prof, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  CK(cudaMemset(b->d.prof, 0, 8 * sizeof(unsigned long long)));
   return 0;
 }
 

@@ -1,116 +1,257 @@
-// k_pgs.cuh — row prologue, dataflow schedule, the SOR-PGS sweeps, and integration.
+// k_pgs.cuh — row prologue, static modulo schedule, the SOR-PGS sweeps, and integration.
 //
+//   k_schedule   order[] of PGS_LCP with row_reorder1 (quickstep_pgs_lcp.cpp:1115-1150) and the
+//                static modulo schedule described below
+//   k_slab       lays the step's PGS warps and their record slabs out (prefix over the buckets)
 //   k_rowfinish  rhs / rhs_erp (quickstep.cpp:403-437), cfm /= h (:443), warm start (:473-495),
 //                iMJ = M^-1 J^T (quickstep_util.cpp:79-98), Ad and the Ad scaling
-//                (quickstep_pgs_lcp.cpp:1012-1028,1091-1107)
-//   k_schedule   order[] of PGS_LCP with row_reorder1 (quickstep_pgs_lcp.cpp:1115-1150) and the
-//                dataflow tickets / executor queues described below
+//                (quickstep_pgs_lcp.cpp:1012-1028,1091-1107); writes the packed records
 //   k_pgs        initial caccel = iMJ * lambda0 (multiply_invM_JT quickstep_util.cpp:101-119),
-//                then ComputeRows (quickstep_pgs_lcp.cpp:52-954) on shared-memory-staged rows
+//                then ComputeRows (quickstep_pgs_lcp.cpp:52-954), k_pgs_sweep.cuh
 //   k_integrate  lambda write-back (quickstep.cpp:523-541), dxUpdateBodies
 //                (quickstep_update_bodies.cpp:41-368), dxStepBody (util.cpp:274-379)
 //
 // Exact-order parallel Gauss-Seidel.  The reference sweeps rows strictly in order[]
 // sequence.  Two row updates commute EXACTLY when they share no body, so any schedule
 // that keeps, for every body, the order in which rows touch it gives bit-identical
-// lambda and caccel.  Each row gets a ticket per body = how many earlier rows (in
-// order[] sequence) touch that body; a row may run once both its bodies' completion
-// counters equal its tickets.  Sweeps pipeline automatically (sweep s+1 of a row starts
-// as soon as its bodies are done with sweep s).  The lambda and lambda_erp solves are
-// independent problems (split impulse, quickstep_pgs_lcp.cpp:526-542) and run on
-// separate threads with separate counters.
+// lambda and caccel.  Every sweep has the same dependency structure, so the schedule is
+// built once per step as a MODULO schedule (software pipelining of the sweep loop): row r
+// gets an offset off(r); in sweep s it runs in round s*R + off(r), on lane (off(r) mod R, j).
+// Constraints: consecutive rows on a body have increasing offsets, the first row of a body in
+// sweep s+1 comes after its last row of sweep s (last - first + 1 <= R), and at most k rows
+// share a round residue.  k (lanes per solve) is picked per world from its row count, so a
+// warp holds 16/k worlds and every lane has a row in (almost) every round.  The lambda and
+// lambda_erp solves are independent problems (split impulse, quickstep_pgs_lcp.cpp:526-542)
+// and run on adjacent lanes that share the row record.
+//
+// Worlds are grouped into BUCKETS of equal (k, R) — R is drawn from a geometric ladder — and
+// a PGS warp takes 16/k worlds of one bucket.  Because they share R, the records the warp needs
+// in one round are stored contiguously (slot-major, then lane pair): one 4352-byte bulk copy
+// per round feeds the whole warp.
 #pragma once
 #include "k_rows2.cuh"
 
 namespace gz {
 
-// per-world int scratch (B.scratch): bodies of the rows in order[] sequence
-struct WScratch { int *rb1, *rb2; };
+// per-world int scratch (B.scratch): bodies of the rows in order[] sequence, then the slot and
+// stage the scheduler gave each position
+struct WScratch { int *rb1, *rb2, *slot, *stage; };
 __device__ inline WScratch wscratch(const DevBatch &B, int w) {
   WScratch s;
-  int *base = B.scratch + (size_t)w * 2 * B.max_row_cap;
-  s.rb1 = base; s.rb2 = base + B.max_row_cap;
+  int *base = B.scratch + (size_t)w * 4 * B.max_row_cap;
+  s.rb1 = base; s.rb2 = base + B.max_row_cap; s.slot = base + 2 * (size_t)B.max_row_cap;
+  s.stage = base + 3 * (size_t)B.max_row_cap;
   return s;
 }
 
-// ---- packed row record: what the sweeps stream, 34 doubles = 272 B (16-byte aligned) -------
+// ---- packed row record: what the sweeps stream, 34 doubles = 272 B ---------------------------
 // [0..11] J (scaled by Ad)   [12..23] iMJ   [24] rhs  [25] rhs_erp  [26] Adcfm  [27] lo  [28] hi
-// [29] lambda  [30] lambda_erp  [31] Ad (statistics)  [32..33] RecInts
-// Records of a world are stored executor by executor (an executor = the body that owns the row:
-// the higher-indexed of its two bodies), each executor's rows in order[] sequence, so a thread
-// walks a contiguous range and the friction rows of an executor are the tail of its range.
+// [29] 1/Ad^2 (statistics)  [30..31] RecInts (16 bytes, 16-byte aligned)  [32..33] padding: the
+// 272-byte stride puts the 16 records a warp reads per round in distinct shared-memory banks.
+// A warp's slab holds R rounds of 16 records: record of (slot s, lane pair p) at (s * 16 + p).
+// A record is live only if its epoch equals the current step's (slabs are never cleared).
 #define GZ_REC 34
-#define GZ_REC_INTS 32
+#define GZ_REC_INTS 30
+#define GZ_ROUND_DOUBLES (16 * GZ_REC)
+#define GZ_FI_EMPTY (-3)
 struct RecInts {
-  int findex_p;           // -1 bilateral, -2 contact normal, >= 0 PACKED index of the normal row
+  int fi;                 // -1 bilateral, -2 contact normal, >= 0 world-local slot index (s * k + j) of the normal row
   unsigned short b1, b2;  // world-local bodies, b2 = 0xFFFF: none
-  unsigned short t1, t2;  // tickets: rows touching b1 / b2 that come earlier in order[]
-  unsigned short run;     // rows that follow in the same block (same bodies, consecutive tickets)
-  unsigned short pad;
+  int stage_epoch;        // (step epoch << 8) | off(r) / R
+  int orig;               // world-local row index (write-back)
 };
-// per-world schedule table (ints): for body/executor b: nA, nF, qs, qf, qe
-#define GZ_SCHED 5
+struct WSched { int R, k, nstage, bucket, idx, nslots, pad0, pad1; };
 
-__device__ inline int *wsched(const DevBatch &B, int w) { return B.sched + (size_t)w * GZ_SCHED * B.max_nb; }
-__device__ inline double *wprec(const DevBatch &B, const WorldInfo &wi) { return B.prec + (size_t)wi.row0 * GZ_REC; }
+// ---- buckets: c = log2(k) in 0..4, rb = rung of the R ladder in 1..127 -------------------------
+#define GZ_RMAX 1984   // rung_value(GZ_NRUNG - 1); GZ_NRUNG / GZ_NBUCKET live in gz_batch.h
+__host__ __device__ inline int rung_value(int rb) {
+  if (rb <= 32) return rb;
+  if (rb <= 48) return 32 + 2 * (rb - 32);
+  if (rb <= 64) return 64 + 4 * (rb - 48);
+  if (rb <= 80) return 128 + 8 * (rb - 64);
+  if (rb <= 96) return 256 + 16 * (rb - 80);
+  if (rb <= 112) return 512 + 32 * (rb - 96);
+  return 1024 + 64 * (rb - 112);
+}
+__host__ __device__ inline int rung_ceil(int R) {   // smallest rung whose value is >= R (R <= GZ_RMAX)
+  if (R <= 32) return R < 1 ? 1 : R;
+  if (R <= 64) return 32 + (R - 32 + 1) / 2;
+  if (R <= 128) return 48 + (R - 64 + 3) / 4;
+  if (R <= 256) return 64 + (R - 128 + 7) / 8;
+  if (R <= 512) return 80 + (R - 256 + 15) / 16;
+  if (R <= 1024) return 96 + (R - 512 + 31) / 32;
+  return 112 + (R - 1024 + 63) / 64;
+}
+// bk_tab rows
+#define GZ_BK_WARP0 0     // [bucket] first PGS warp (CTA) of the bucket
+#define GZ_BK_REC0 1      // [bucket] first record of the bucket's slabs
+#define GZ_BK_SWARP0 2    // [i] first warp of the i-th bucket in heavy-first order; [GZ_NBUCKET] = total warps
+#define GZ_BK_SBUCKET 3   // [i] bucket id of the i-th bucket in heavy-first order
+__device__ inline int *bk_row(const DevBatch &B, int row) { return B.bk_tab + row * (GZ_NBUCKET + 1); }
+__device__ inline int bucket_wpw(const DevBatch &B, int bucket) { return min(16 >> (bucket / GZ_NRUNG), B.pgs_wpw_max); }
 
-// One CTA per world: order[] positions (closed form), per-body tickets, per-executor queues,
-// packed position of every row.  Needs only b1/b2 of the rows, which k_rows_* wrote.
-// Row::t1a/t2a receive the tickets, Row::next_a the rank inside the owner's queue and
-// Row::next_f the packed index.
-__global__ void k_schedule(DevBatch B) {
-  const int w = blockIdx.x;
+// where a world's records live once k_slab has run
+struct WSlab { double *base; int k, wslot, warp; };
+__device__ inline WSlab wslab(const DevBatch &B, const WSched &sc) {
+  const int per = bucket_wpw(B, sc.bucket);
+  WSlab s;
+  s.k = sc.k; s.wslot = sc.idx % per;
+  const int wb = sc.idx / per;
+  const int w0 = bk_row(B, GZ_BK_WARP0)[sc.bucket];
+  s.warp = w0 < 0 ? -1 : w0 + wb;   // -1: the record pool was exhausted (k_slab flagged it)
+  s.base = B.prec + ((size_t)bk_row(B, GZ_BK_REC0)[sc.bucket] + (size_t)wb * sc.R * 16) * GZ_REC;
+  return s;
+}
+__device__ inline double *slab_rec(const WSlab &s, int local) {   // local = slot * k + j
+  return s.base + ((size_t)(local / s.k) * 16 + s.wslot * s.k + (local % s.k)) * GZ_REC;
+}
+
+// One warp per world: order[] positions (closed form), rows per body, k, then the greedy modulo
+// scheduler on lane 0 (integer work only, m iterations per attempt), then the slot of every row.
+// Row::next_f receives the world-local slot index, Row::t1a the stage.
+__global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
+  __shared__ unsigned short occ[GZ_RMAX];
+  __shared__ int cnt[512], last[512], first[512];
+  const int w = blockIdx.x, lane = threadIdx.x;
   const WorldInfo wi = B.world[w];
-  const WorldStep &ws = B.wstep[w];
-  const int m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc;
+  WorldStep &ws = B.wstep[w];
+  const int m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc, nb = wi.nb;
+  WSched *wsch = reinterpret_cast<WSched *>(B.wsched) + w;
+  if (m == 0 || m > GZ_RMAX) {
+    // nothing to solve: constraint accelerations are zero (free bodies still integrate)
+    for (int b = lane; b < nb; b += 32) {
+      BodyStep &bs = B.bstep[wi.body0 + b];
+      for (int t = 0; t < 6; t++) { bs.caccel[t] = 0; bs.caccel_erp[t] = 0; }
+    }
+    if (lane == 0) {
+      WSched z; z.R = 1; z.k = 1; z.nstage = 0; z.bucket = -1; z.idx = 0; z.nslots = 0; z.pad0 = z.pad1 = 0; *wsch = z;
+      for (int k = 0; k < 4; k++) { ws.rms_dlambda[k] = 0; ws.rms_residual[k] = 0; }
+      ws.num_contacts_stat = 0;
+      if (m > GZ_RMAX) ws.overflow |= 8;   // needs the large-world solver
+    }
+    return;
+  }
   int *order = B.order + wi.row0;
   Row *rows = B.row + wi.row0;
   WScratch S = wscratch(B, w);
-  int *sch = wsched(B, w);
+  for (int b = lane; b < nb; b += 32) cnt[b] = 0;
+  __syncwarp();
   // order[]: bilateral rows in index order, contact normals in REVERSE index order, friction
   // rows in index order (quickstep_pgs_lcp.cpp:1115-1150).  Persistent-joint rows are all
   // bilateral and every contact has exactly (normal, fric1, fric2): positions are closed-form.
-  for (int i = threadIdx.x; i < m; i += blockDim.x) {
+  for (int i = lane; i < m; i += 32) {
     int pos;
     if (i < mj) pos = i;
     else {
       int c = (i - mj) / 3, f = (i - mj) % 3;
       pos = (f == 0) ? mj + (nc - 1 - c) : mj + nc + 2 * c + (f - 1);
     }
+    const int x1 = rows[i].b1, x2 = rows[i].b2;
     order[pos] = i;
-    S.rb1[pos] = rows[i].b1;
-    S.rb2[pos] = rows[i].b2;
+    S.rb1[pos] = x1;
+    S.rb2[pos] = x2;
+    atomicAdd(&cnt[x1], 1);
+    if (x2 >= 0) atomicAdd(&cnt[x2], 1);
   }
-  __syncthreads();
-  const int nfr0 = mj + nc;   // positions >= nfr0 are friction rows
-  for (int b = threadIdx.x; b < wi.nb; b += blockDim.x) {
-    int cA = 0, cF = 0, nQ = 0, nQF = 0;
-    for (int k = 0; k < m; k++) {
-      int x1 = S.rb1[k], x2 = S.rb2[k];
-      if (x1 != b && x2 != b) continue;
-      Row &r = rows[order[k]];
-      bool fr = k >= nfr0;
-      if (x1 == b) r.t1a = cA; else r.t2a = cA;
-      cA++; if (fr) cF++;
-      int owner = (x2 >= 0) ? (x1 > x2 ? x1 : x2) : x1;
-      if (owner == b) { r.owner = b; r.next_a = nQ; nQ++; if (fr) nQF++; }
+  __syncwarp();
+  int maxcnt = 0;
+  for (int b = lane; b < nb; b += 32) maxcnt = max(maxcnt, cnt[b]);
+  maxcnt = __reduce_max_sync(0xffffffffu, maxcnt);
+  // lanes per solve: the smallest power of two that brings rows/k down to the period the busiest
+  // body (or the batch-wide target period) imposes anyway
+  const int target = max(maxcnt, B.pgs_rt);
+  int k = B.pgs_kmin;
+  while (k < B.pgs_kmax && (m + k - 1) / k > target) k <<= 1;
+  int rb = rung_ceil(max((m + k - 1) / k, maxcnt));
+  int R = rung_value(rb);
+  int nstage = 1;
+  bool done = false;
+  for (int attempt = 0; !done; attempt++) {
+    const bool give_up = attempt >= 24 || rb >= GZ_NRUNG;
+    if (give_up) {   // always valid: the sequential sweep itself (one lane per solve)
+      k = 1; rb = rung_ceil(m); R = rung_value(rb); nstage = 1;
+      for (int pos = lane; pos < m; pos += 32) { S.slot[pos] = pos; S.stage[pos] = 0; }
+      break;
     }
-    sch[GZ_SCHED * b + 0] = cA; sch[GZ_SCHED * b + 1] = cF;
-    sch[GZ_SCHED * b + 2] = nQ; sch[GZ_SCHED * b + 3] = nQF;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int acc = 0;
-    for (int b = 0; b < wi.nb; b++) {
-      int nQ = sch[GZ_SCHED * b + 2], nQF = sch[GZ_SCHED * b + 3];
-      sch[GZ_SCHED * b + 2] = acc; sch[GZ_SCHED * b + 3] = acc + nQ - nQF; sch[GZ_SCHED * b + 4] = acc + nQ;
-      acc += nQ;
+    for (int s = lane; s < R; s += 32) occ[s] = 0;
+    for (int b = lane; b < nb; b += 32) { last[b] = -1; first[b] = -1; }
+    __syncwarp();
+    int fail = 0, need = R, maxoff = 0;
+    if (lane == 0) {
+      for (int pos = 0; pos < m; pos++) {
+        const int x1 = S.rb1[pos], x2 = S.rb2[pos];
+        int o = last[x1] + 1;
+        if (x2 >= 0) o = max(o, last[x2] + 1);
+        int s = o % R, n = 0;
+        while (occ[s] == k) {
+          o++; s++;
+          if (s == R) s = 0;
+          if (++n > R) { fail = 1; break; }
+        }
+        if (fail) break;
+        const int ln = occ[s]++;
+        S.slot[pos] = s * k + ln;
+        S.stage[pos] = o / R;
+        last[x1] = o;
+        if (first[x1] < 0) first[x1] = o;
+        if (x2 >= 0) { last[x2] = o; if (first[x2] < 0) first[x2] = o; }
+        maxoff = max(maxoff, o);
+      }
+      if (!fail)
+        for (int b = 0; b < nb; b++)
+          if (first[b] >= 0) need = max(need, last[b] - first[b] + 1);
     }
+    fail = __shfl_sync(0xffffffffu, fail, 0);
+    need = __shfl_sync(0xffffffffu, need, 0);
+    maxoff = __shfl_sync(0xffffffffu, maxoff, 0);
+    if (!fail && need == R && maxoff / R < 255) { done = true; nstage = maxoff / R + 1; }
+    else { rb++; R = rung_value(rb); }   // next rung (3-6 % longer): jumping to `need` overshoots badly
+    __syncwarp();
   }
+  if (lane == 0) {
+    int c = 0;
+    while ((1 << c) < k) c++;
+    WSched z; z.R = R; z.k = k; z.nstage = nstage; z.bucket = c * GZ_NRUNG + rb; z.nslots = R * k; z.pad0 = z.pad1 = 0;
+    z.idx = atomicAdd(&B.bk_count[z.bucket], 1);
+    *wsch = z;
+  }
+  for (int pos = lane; pos < m; pos += 32) {
+    Row &r = rows[order[pos]];
+    r.next_f = S.slot[pos];
+    r.t1a = S.stage[pos];
+  }
+}
+
+// One CTA: warps and record slabs of every bucket, heaviest period first so that the longest
+// warps are the first to be scheduled on the SMs; clears the warp -> world table.
+__global__ void k_slab(DevBatch B) {
+  __shared__ int nwarp[GZ_NBUCKET];
+  const int t = threadIdx.x;
+  for (int b = t; b < GZ_NBUCKET; b += blockDim.x) {
+    const int per = bucket_wpw(B, b);
+    nwarp[b] = (B.bk_count[b] + per - 1) / per;
+  }
+  const int nw_max = B.n_worlds + GZ_NBUCKET;
+  for (int i = t; i < nw_max * 16; i += blockDim.x) B.warp_world[i] = -1;
   __syncthreads();
-  for (int i = threadIdx.x; i < m; i += blockDim.x) {
-    Row &r = rows[i];
-    r.next_f = sch[GZ_SCHED * r.owner + 2] + r.next_a;
+  if (t == 0) {
+    int *warp0 = bk_row(B, GZ_BK_WARP0), *rec0 = bk_row(B, GZ_BK_REC0);
+    int *swarp0 = bk_row(B, GZ_BK_SWARP0), *sbucket = bk_row(B, GZ_BK_SBUCKET);
+    int warps = 0, i = 0;
+    long recs = 0;
+    for (int rb = GZ_NRUNG - 1; rb >= 0; rb--)
+      for (int c = 4; c >= 0; c--) {
+        const int b = c * GZ_NRUNG + rb;
+        warp0[b] = warps; rec0[b] = (int)recs;
+        swarp0[i] = warps; sbucket[i] = b; i++;
+        long nrec = (long)nwarp[b] * rung_value(rb) * 16;
+        if (recs + nrec > B.prec_cap) {   // pool exhausted: the bucket is dropped and the step flagged
+          if (nwarp[b] > 0) B.wstep[0].overflow |= 16;
+          nwarp[b] = 0; nrec = 0; warp0[b] = -1;
+        }
+        warps += nwarp[b]; recs += nrec;
+      }
+    swarp0[GZ_NBUCKET] = warps;
   }
 }
 
@@ -171,19 +312,26 @@ __global__ void k_rowfinish(DevBatch B) {
   else Ad = B.p.contact_sor_scale * B.p.sor_w / (d + cfm);
   r.Ad = Ad;
   r.lambda = lam; r.lambda_erp = lam_erp;
-  double *rec = wprec(B, wi) + (size_t)r.next_f * GZ_REC;
-  for (int j = 0; j < 12; j++) { rec[j] = J[j] * Ad; rec[12 + j] = iMJ[j]; }
-  rec[24] = rhs * Ad;
-  rec[25] = rhs_erp * Ad;
-  rec[26] = Ad * cfm;
-  rec[27] = r.lo; rec[28] = r.hi;
-  rec[29] = lam; rec[30] = lam_erp; rec[31] = Ad;
+  const WSched sc = reinterpret_cast<const WSched *>(B.wsched)[w];
+  const WSlab sl = wslab(B, sc);
+  if (sl.warp < 0) return;
+  if (i == 0) B.warp_world[sl.warp * 16 + sl.wslot] = w;
+  double *rec = slab_rec(sl, r.next_f);
+  double2 *rec2 = reinterpret_cast<double2 *>(rec);
+  for (int j = 0; j < 6; j++) {
+    rec2[j] = make_double2(J[2 * j] * Ad, J[2 * j + 1] * Ad);
+    rec2[6 + j] = make_double2(iMJ[2 * j], iMJ[2 * j + 1]);
+  }
+  rec2[12] = make_double2(rhs * Ad, rhs_erp * Ad);
+  rec2[13] = make_double2(Ad * cfm, r.lo);
+  double Ad2 = 0.0;   // quickstep_pgs_lcp.cpp:745-752
+  if (!dequal(Ad, 0.0)) Ad2 = 1.0 / (Ad * Ad);
+  rec2[14] = make_double2(r.hi, Ad2);
   RecInts ri;
-  ri.run = 0; ri.pad = 0;
-  B.order[wi.row0 + r.next_f] = i;   // order[] is free after k_schedule: packed index -> row
-  ri.findex_p = (r.findex >= 0) ? B.row[wi.row0 + r.findex].next_f : r.findex;
+  ri.fi = (r.findex >= 0) ? B.row[wi.row0 + r.findex].next_f : r.findex;
   ri.b1 = (unsigned short)r.b1; ri.b2 = (r.b2 >= 0) ? (unsigned short)r.b2 : (unsigned short)0xFFFF;
-  ri.t1 = (unsigned short)r.t1a; ri.t2 = (unsigned short)r.t2a;
+  ri.stage_epoch = (int)((((unsigned)B.step_index + 1u) << 8) | (unsigned)r.t1a);
+  ri.orig = i;
   *reinterpret_cast<RecInts *>(rec + GZ_REC_INTS) = ri;
 }
 

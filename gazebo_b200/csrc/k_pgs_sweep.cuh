@@ -1,321 +1,340 @@
-// k_pgs_sweep.cuh — the SOR-PGS sweeps (ComputeRows, quickstep_pgs_lcp.cpp:52-954) as an
-// exact-order dataflow over shared-memory-staged packed rows.
+// k_pgs_sweep.cuh — the SOR-PGS sweeps (ComputeRows, quickstep_pgs_lcp.cpp:52-954) run from the
+// static modulo schedule k_schedule built (k_pgs.cuh).
 //
-// Threads: a world gets TW threads (TW = 32 when 2*nbp <= 32, else 2*nbp); lane l < 2*nbp is
-// (executor e = l >> 1, solve s = l & 1).  A CTA holds WPC worlds.  When a world fits one warp
-// (the batched small-world case) its lanes run in lockstep and need no memory fences; larger
-// worlds span several warps and use __threadfence_block around the completion counters.
+// One warp per CTA.  A warp holds 16/k worlds of the same class k (lanes per solve); lane l is
+// (world slot l / 2k, schedule lane j = (l % 2k) / 2, solve S = l & 1: lambda or lambda_erp).
+// In round T a lane takes the record at (slot T mod R, lane j) of its world and, if that row
+// is due (sweep = T / R - stage inside the sweep range), updates it.  All lanes of the warp run
+// the same instruction stream with no waiting and no inter-lane traffic except through the
+// bodies' accumulators; rows that run in the same round share no body by construction, so one
+// __syncwarp per round orders everything and the result is bit-identical to the sequential sweep.
 //
-// Shared memory per CTA: per world slot ca[2][nbp+1][6] (slot nbp is a dummy "no body"),
-// stat[nbp][9], done[2][nbp+1], nA[nbp], nF[nbp]; then a pool of WPC*budget packed records
-// handed out first come first served.  Records that do not fit are read from the packed slab in
-// global memory (same layout), so capacity is a performance knob, never a correctness limit.
+// With 4096 small worlds there is about one such warp per SM sub-partition, so the kernel runs at
+// the LATENCY of one round; everything below is arranged to keep that short:
+//  * row records stream from the packed slab (L2-resident: k_rowfinish wrote it just before)
+//    into a shared-memory ring with bulk async copies (cp.async.bulk + mbarrier, one copy of
+//    k * 272 bytes per world and round, issued by the world's first lane) several rounds ahead;
+//  * the record of round T+1 is read from the ring into registers while round T computes;
+//  * the two 6-term dot products are issued interleaved and without branches.
+// Shared memory per CTA: accumulators ca[world][solve][nbp+1][6] (slot nbp = "no body"), the
+// ring, the mbarriers, then lambda[world][slot][2] (spilled to global memory if it does not fit).
 #pragma once
 
 namespace gz {
 
-struct PgsCfg { int L, nbp, tw, wpc, budget; };
+#define GZ_RING_D 4                 // ring stages
+#define GZ_RING_DOUBLES (GZ_RING_D * GZ_ROUND_DOUBLES + 2 * GZ_RING_D)   // records + one mbarrier per stage (padded)
 
-__host__ __device__ inline size_t pgs_slot_doubles(int nbp) {
-  // ca 12*(nbp+1) | stat 9*nbp | done 2*(nbp+1) ints + nA,nF 2*nbp ints -> (4*nbp+2)/2 doubles
-  size_t n = (size_t)12 * (nbp + 1) + 9 * nbp + 2 * nbp + 2;
-  return (n + 1) & ~(size_t)1;   // even: keeps the record pool 16-byte aligned
-}
+struct PgsCfg { int smem_doubles, nbp, wpw_max; };
 
-// the per-row constants a lane keeps in registers while it waits for its turn
+// the constants of one row, in registers
 struct RowRegs {
-  double J[12], iM[12], rhs, adcfm, lo, hi, Ad;
-  int b1, b2, fi, t1, t2, run;
+  double J[12], iM[12], rhs, adcfm, lo, hi, Ad2;
+  int fi, b1, b2, stage;
 };
 
-__device__ __forceinline__ void load_row(RowRegs &R, const double *rec, const int S) {
+// Reads one record; a record whose epoch is not this step's is an empty slot (or a stale one in a
+// part of the slab no world of this warp owns) and is turned into a harmless no-op row.
+__device__ __forceinline__ void load_row(RowRegs &R, const double *rec, const int S, const int nbp, const unsigned epoch) {
+  const double2 *r2 = reinterpret_cast<const double2 *>(rec);
 #pragma unroll
-  for (int k = 0; k < 12; k++) { R.J[k] = rec[k]; R.iM[k] = rec[12 + k]; }
-  R.rhs = rec[24 + S]; R.adcfm = rec[26]; R.lo = rec[27]; R.hi = rec[28]; R.Ad = rec[31];
-  const RecInts ri = *reinterpret_cast<const RecInts *>(rec + GZ_REC_INTS);
-  R.b1 = ri.b1; R.b2 = (ri.b2 == 0xFFFF) ? -1 : (int)ri.b2; R.fi = ri.findex_p;
-  R.t1 = ri.t1; R.t2 = ri.t2; R.run = ri.run;
+  for (int k = 0; k < 6; k++) {
+    const double2 a = r2[k], b = r2[6 + k];
+    R.J[2 * k] = a.x; R.J[2 * k + 1] = a.y;
+    R.iM[2 * k] = b.x; R.iM[2 * k + 1] = b.y;
+  }
+  const double2 c = r2[12], d = r2[13], e = r2[14];
+  R.rhs = S ? c.y : c.x; R.adcfm = d.x; R.lo = d.y; R.hi = e.x; R.Ad2 = e.y;
+  const int4 iv = *reinterpret_cast<const int4 *>(rec + GZ_REC_INTS);   // RecInts: fi | b1,b2 | epoch,stage | orig
+  const bool valid = ((unsigned)iv.z >> 8) == epoch;
+  const int b2 = (iv.y >> 16) & 0xFFFF;
+  R.fi = valid ? iv.x : GZ_FI_EMPTY;
+  R.b1 = valid ? (iv.y & 0xFFFF) : 0;
+  R.b2 = (valid && b2 != 0xFFFF) ? b2 : nbp;
+  R.stage = iv.z & 255;
 }
 
-// One solve (S = 0: lambda with smoothing and statistics, S = 1: lambda_erp) of one executor.
-// S is a run-time value on purpose: the two solve lanes of an executor sit in the same warp and
-// must share one instruction stream.  SMEM = every record of this world is in the shared pool
-// (pure LDS path); otherwise records are addressed generically (pool or global slab).
-// The next row is fetched into registers right after a row update, inside the same divergent
-// region, so a loop trip is "check" or "check + update + fetch" and nothing else.
-template <bool MULTIWARP, bool SMEM>
-__device__ __forceinline__ void pgs_lane(const DevBatch &B, const int S, const int qs, const int qf, const int qe,
-                                         const int cap, double *mypool, double *gslab,
-                                         double *cas, volatile int *dn, const int *nAs, const int *nFs,
-                                         const int nbp, double *st, int *dbg_iters) {
+// ---- mbarrier / bulk-copy wrappers (PTX ISA: mbarrier, cp.async.bulk) ---------------------------
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// One row update of one solve.  Mirrors quickstep_pgs_lcp.cpp:488-808 for the pyramid friction
+// model Gazebo uses by default: delta, limits from lo/hi or |hi * lambda[findex]|, clamp,
+// SMOOTH_LAMBDA on the lambda solve only (delta is not recomputed after it), caccel update.
+// Branch-free, stores under the predicate `act`, so that the compiler can schedule a whole
+// round as one basic block.  A row without a second body has J2 = iMJ2 = 0 and reads the
+// all-zero dummy accumulator; the reference skips that term, and so does the select below.
+struct PgsStat { double acc[3], err[3]; int cnt[3]; };
+
+__device__ __forceinline__ void pgs_row(const RowRegs &R, const bool act, const int S, const int idx, double *cas,
+                                        double *lam, const int nbp, const double smooth, const bool stat01,
+                                        const bool stat2, PgsStat &st) {
+  double *c1 = cas + 6 * R.b1, *c2 = cas + 6 * R.b2;
+  const bool two = R.b2 < nbp;
+  double a1[6], a2[6];
+  {
+    const double2 *p1 = reinterpret_cast<const double2 *>(c1), *p2 = reinterpret_cast<const double2 *>(c2);
+#pragma unroll
+    for (int t = 0; t < 3; t++) {
+      const double2 x = p1[t], y = p2[t];
+      a1[2 * t] = x.x; a1[2 * t + 1] = x.y; a2[2 * t] = y.x; a2[2 * t + 1] = y.y;
+    }
+  }
+  const double old_lambda = lam[2 * idx + S];
+  const int fi = R.fi;
+  const double nlam = lam[2 * (fi >= 0 ? fi : idx) + S];
+  const double hf = fabs(R.hi * nlam);   // pyramid friction: |mu * lambda_normal|
+  const double hi_act = fi >= 0 ? hf : R.hi, lo_act = fi >= 0 ? -hf : R.lo;
+  // the two dot products, term by term in the reference's left-to-right order, interleaved
+  double d1 = a1[0] * R.J[0], d2 = a2[0] * R.J[6];
+#pragma unroll
+  for (int t = 1; t < 6; t++) { d1 += a1[t] * R.J[t]; d2 += a2[t] * R.J[6 + t]; }
+  double delta = R.rhs - old_lambda * R.adcfm;
+  delta -= d1;
+  const double delta2 = delta - d2;
+  delta = two ? delta2 : delta;
+  double nl = old_lambda + delta;
+  const double dlo = lo_act - old_lambda, dhi = hi_act - old_lambda;
+  const bool below = nl < lo_act, above = !below && nl > hi_act;
+  delta = below ? dlo : (above ? dhi : delta);
+  nl = below ? lo_act : (above ? hi_act : nl);
+  const double sm = (1.0 - smooth) * nl + smooth * old_lambda;
+  nl = (S == 0 && fi != -1) ? sm : nl;
+  if (act) lam[2 * idx + S] = nl;
+  {
+    double2 *p1 = reinterpret_cast<double2 *>(c1);
+    double2 *p2 = reinterpret_cast<double2 *>(c2);
+    double2 o1[3], o2[3];
+#pragma unroll
+    for (int t = 0; t < 3; t++) {
+      o1[t] = make_double2(a1[2 * t] + delta * R.iM[2 * t], a1[2 * t + 1] + delta * R.iM[2 * t + 1]);
+      o2[t] = make_double2(a2[2 * t] + delta * R.iM[6 + 2 * t], a2[2 * t + 1] + delta * R.iM[6 + 2 * t + 1]);
+    }
+    if (act) {
+#pragma unroll
+      for (int t = 0; t < 3; t++) p1[t] = o1[t];
+    }
+    if (act && two) {
+#pragma unroll
+      for (int t = 0; t < 3; t++) p2[t] = o2[t];
+    }
+  }
+  // rms_dlambda / rms_constraint_residual (quickstep_pgs_lcp.cpp:700-760,814-855): the sums
+  // restart every sweep, so only the last sweep that touches a class survives.
+  {
+    const int cls = (fi == -1) ? 0 : (fi == -2 ? 1 : 2);
+    const bool on = act && S == 0 && ((cls == 2) ? stat2 : stat01);
+    const double dd = delta * delta, e2 = dd * R.Ad2;
+    if (on && cls == 0) { st.acc[0] += dd; st.err[0] += e2; st.cnt[0]++; }
+    if (on && cls == 1) { st.acc[1] += dd; st.err[1] += e2; st.cnt[1]++; }
+    if (on && cls == 2) { st.acc[2] += dd; st.err[2] += e2; st.cnt[2]++; }
+  }
+}
+
+template <bool PROF>
+__global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
+  extern __shared__ __align__(16) double shd[];
+  const int lane = threadIdx.x;
+  const int nbp = cfg.nbp;
+  // ---- which bucket, which warp of it (buckets are laid out heaviest first by k_slab)
+  const int cta = blockIdx.x;
+  const int *swarp0 = bk_row(B, GZ_BK_SWARP0);
+  if (cta >= swarp0[GZ_NBUCKET]) return;
+  int lo_i = 0, hi_i = GZ_NBUCKET - 1;
+  while (lo_i < hi_i) {   // largest i with swarp0[i] <= cta
+    const int mid = (lo_i + hi_i + 1) >> 1;
+    if (swarp0[mid] <= cta) lo_i = mid; else hi_i = mid - 1;
+  }
+  const int bucket = bk_row(B, GZ_BK_SBUCKET)[lo_i];
+  const int k = 1 << (bucket / GZ_NRUNG), LW = 2 * k, R = rung_value(bucket % GZ_NRUNG);
+  const int wpw = bucket_wpw(B, bucket);
+  const int wb = cta - swarp0[lo_i];
+  const size_t slab_rec0 = (size_t)bk_row(B, GZ_BK_REC0)[bucket] + (size_t)wb * R * 16;
+  const double *slab = B.prec + slab_rec0 * GZ_REC;
+  const int wslot = lane / LW, jl = (lane % LW) >> 1, S = lane & 1, lw = lane % LW;
+  const int w = (wslot < wpw) ? B.warp_world[cta * 16 + wslot] : -1;
+  const bool live = w >= 0;
+  WorldInfo wi;
+  wi.nb = 0; wi.row0 = 0; wi.body0 = 0;
+  int nstage = 0;
+  if (live) { wi = B.world[w]; nstage = reinterpret_cast<const WSched *>(B.wsched)[w].nstage; }
+  const int nslots = R * k;
+  // ---- carve shared memory: ca | ring + mbarriers | lambda (first come first served over world slots)
+  const int ca_doubles = 12 * (nbp + 1);
+  double *ca = shd + (size_t)(wslot < wpw ? wslot : 0) * ca_doubles;
+  double *ring = shd + (size_t)wpw * ca_doubles;
+  const int lam_need = 2 * nslots;
+  const int lam_fit = (cfg.smem_doubles - (wpw * ca_doubles + GZ_RING_DOUBLES)) / (lam_need > 0 ? lam_need : 1);
+  double *lam = (wslot < lam_fit) ? shd + wpw * ca_doubles + GZ_RING_DOUBLES + (size_t)wslot * lam_need
+                                  : B.lamg + 2 * (slab_rec0 + (size_t)wslot * nslots);
+  if (!live) lam = shd;
+  const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring);
+  const unsigned bar_s = ring_s + GZ_RING_D * GZ_ROUND_DOUBLES * 8;
+  if (lane < GZ_RING_D) mbar_init(bar_s + 8 * lane, 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  const unsigned epoch = ((unsigned)B.step_index + 1u) & 0xFFFFFFu;
+  WSlab sl;
+  sl.base = const_cast<double *>(slab); sl.k = k; sl.wslot = wslot; sl.warp = cta;
+  // ---- lambda0 and the accumulators
+  if (wslot < wpw)
+    for (int i = lw; i < ca_doubles; i += LW) ca[i] = 0.0;
+  __syncwarp();
+  if (live) {
+    const Row *rows = B.row + wi.row0;
+    for (int i = lw; i < nslots; i += LW) {
+      const RecInts *ri = reinterpret_cast<const RecInts *>(slab_rec(sl, i) + GZ_REC_INTS);
+      double l0 = 0.0, l1 = 0.0;
+      if (((unsigned)ri->stage_epoch >> 8) == epoch) { const Row &r = rows[ri->orig]; l0 = r.lambda; l1 = r.lambda_erp; }
+      lam[2 * i] = l0; lam[2 * i + 1] = l1;
+    }
+    // initial caccel = iMJ * lambda0 over the warm-started (persistent-joint) rows, in row index
+    // order per body (multiply_invM_JT, quickstep_util.cpp:101-119)
+    if (B.p.warm_start > 0) {
+      for (int b = lw; b < wi.nb; b += LW) {
+        const Body &bd = B.body[wi.body0 + b];
+        if (!B.bstep[wi.body0 + b].active) continue;
+        double s0[6] = {0, 0, 0, 0, 0, 0}, s1[6] = {0, 0, 0, 0, 0, 0};
+        for (int q = bd.joint_begin; q < bd.joint_end; q++) {
+          const Joint &j = B.joint[B.body_joint[q]];
+          for (int rr = 0; rr < j.m; rr++) {
+            const Row &r = rows[j.row0 + rr];
+            const double *rec = slab_rec(sl, r.next_f);
+            const double *im = (r.b1 == b) ? rec + 12 : rec + 18;
+            for (int t = 0; t < 6; t++) { s0[t] += im[t] * r.lambda; s1[t] += im[t] * r.lambda_erp; }
+          }
+        }
+        for (int t = 0; t < 6; t++) { ca[6 * b + t] = s0[t]; ca[6 * (nbp + 1 + b) + t] = s1[t]; }
+      }
+    }
+  }
+  __syncwarp();
+  // ---- the sweeps
   const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
   const double smooth = B.p.smooth_contacts;
-  double acc[3] = {0, 0, 0}, err[3] = {0, 0, 0};
-  int cnt[3] = {0, 0, 0};
-  int loops = 0, execs = 0;
-  if (qe > qs) {
-    int sweep = 0, idx = qs;
-    if (iters == 0) { idx = qf; if (qf == qe) sweep = total; }
-    RowRegs R;
-    double *lam = nullptr;      // &lambda (S=0) or &lambda_erp (S=1) of the current row
-    int tg1 = 0, tg2 = 0, d2i = nbp;
-#define GZ_FETCH()                                                                               \
-    {                                                                                            \
-      double *rec = (SMEM || idx < cap) ? mypool + (size_t)idx * GZ_REC : gslab + (size_t)idx * GZ_REC; \
-      load_row(R, rec, S);                                                                       \
-      lam = rec + 29 + S;                                                                        \
-      d2i = (R.b2 >= 0) ? R.b2 : nbp;   /* dummy counter slot nbp stays 0 */                     \
-      if (sweep < iters) {                                                                       \
-        tg1 = sweep * nAs[R.b1] + R.t1;                                                          \
-        tg2 = (R.b2 >= 0) ? sweep * nAs[R.b2] + R.t2 : 0;                                        \
-      } else { /* friction-only sweeps: ticket among the friction rows of the body */            \
-        tg1 = iters * nAs[R.b1] + (sweep - iters) * nFs[R.b1] + (R.t1 - (nAs[R.b1] - nFs[R.b1])); \
-        tg2 = (R.b2 >= 0) ? iters * nAs[R.b2] + (sweep - iters) * nFs[R.b2] + (R.t2 - (nAs[R.b2] - nFs[R.b2])) : 0; \
-      }                                                                                          \
-    }
-    if (sweep < total) GZ_FETCH();
-    while (sweep < total) {
-      loops++;
-      const bool ready = (dn[R.b1] == tg1) && (dn[d2i] == tg2);
-      if (ready) {
-        if (MULTIWARP) __threadfence_block(); else asm volatile("" ::: "memory");
-        // A block = R.run + 1 consecutive rows of this queue on the same bodies with consecutive
-        // tickets: the bodies are acquired once, their accumulators live in registers across the
-        // block, and the counters advance by the block length at the end.
-        const int b1 = R.b1, b2 = R.b2, nblk = R.run + 1;
-        double *c1 = cas + 6 * b1, *c2 = cas + 6 * b2;
-        double a1[6], a2[6];
-#pragma unroll
-        for (int t = 0; t < 6; t++) { a1[t] = c1[t]; a2[t] = (b2 >= 0) ? c2[t] : 0.0; }
-        // Software pipeline without register copies: every field of R is reloaded from the NEXT
-        // row of the block right after its last use, so the loads overlap the dependent FP chain
-        // of the current row.  (When there is no next row the current record is re-read, which
-        // is harmless.)  Safe: a row's lambda is written only by its own update, and a friction
-        // row's normal lives in an earlier block of this same lane.
-        double old_lambda = *lam;
-        double nlam = 0.0;
-        if (R.fi >= 0) nlam = ((SMEM || R.fi < cap) ? mypool + (size_t)R.fi * GZ_REC : gslab + (size_t)R.fi * GZ_REC)[29 + S];
-        for (int k = 0; k < nblk; k++) {
-          const int nidx = (k + 1 < nblk) ? idx + 1 : idx;
-          double *rn = (SMEM || nidx < cap) ? mypool + (size_t)nidx * GZ_REC : gslab + (size_t)nidx * GZ_REC;
-          double delta = R.rhs - old_lambda * R.adcfm;
-          delta -= a1[0] * R.J[0] + a1[1] * R.J[1] + a1[2] * R.J[2] + a1[3] * R.J[3] + a1[4] * R.J[4] + a1[5] * R.J[5];
-          if (b2 >= 0)
-            delta -= a2[0] * R.J[6] + a2[1] * R.J[7] + a2[2] * R.J[8] + a2[3] * R.J[9] + a2[4] * R.J[10] + a2[5] * R.J[11];
-          const double rhs_n = rn[24 + S], adcfm_n = rn[26], old_n = rn[29 + S];
-#pragma unroll
-          for (int t = 0; t < 12; t++) R.J[t] = rn[t];
-          double hi_act, lo_act;
-          const int fi = R.fi;
-          if (fi >= 0) {
-            hi_act = fabs(R.hi * nlam);   // pyramid friction: |mu * lambda_normal|
-            lo_act = -hi_act;
-          } else { hi_act = R.hi; lo_act = R.lo; }
-          double nl = old_lambda + delta;
-          if (nl < lo_act) { delta = lo_act - old_lambda; nl = lo_act; }
-          else if (nl > hi_act) { delta = hi_act - old_lambda; nl = hi_act; }
-          // SMOOTH_LAMBDA on the lambda solve only; delta is not recomputed (quickstep_pgs_lcp.cpp:687-708)
-          if (S == 0 && fi != -1) nl = (1.0 - smooth) * nl + smooth * old_lambda;
-          *lam = nl;
-#pragma unroll
-          for (int t = 0; t < 6; t++) a1[t] += delta * R.iM[t];
-          if (b2 >= 0) {
-#pragma unroll
-            for (int t = 0; t < 6; t++) a2[t] += delta * R.iM[6 + t];
-          }
-#pragma unroll
-          for (int t = 0; t < 12; t++) R.iM[t] = rn[12 + t];
-          // Statistics restart every sweep (friction class) or every non-friction sweep (the
-          // other two), so only the last such sweeps survive: accumulate just there.
-          if (S == 0 && (sweep == iters - 1 || sweep == total - 1)) {
-            const int cls = (fi == -1) ? 0 : (fi == -2 ? 1 : 2);
-            if (sweep == iters - 1 || cls == 2) {
-              double Ad2 = 0.0;
-              if (!dequal(R.Ad, 0.0)) Ad2 = 1.0 / (R.Ad * R.Ad);
-              const double d2 = delta * delta;
-              acc[cls] += d2; err[cls] += d2 * Ad2; cnt[cls]++;
-            }
-          }
-          // remaining fields of the next row
-          R.rhs = rhs_n; R.adcfm = adcfm_n; R.lo = rn[27]; R.hi = rn[28]; R.Ad = rn[31];
-          R.fi = reinterpret_cast<const RecInts *>(rn + GZ_REC_INTS)->findex_p;
-          old_lambda = old_n;
-          lam = rn + 29 + S;
-          if (R.fi >= 0) nlam = ((SMEM || R.fi < cap) ? mypool + (size_t)R.fi * GZ_REC : gslab + (size_t)R.fi * GZ_REC)[29 + S];
-          idx++;
-          execs++;
-        }
-#pragma unroll
-        for (int t = 0; t < 6; t++) c1[t] = a1[t];
-        if (b2 >= 0) {
-#pragma unroll
-          for (int t = 0; t < 6; t++) c2[t] = a2[t];
-        }
-        if (MULTIWARP) __threadfence_block(); else asm volatile("" ::: "memory");
-        dn[b1] = tg1 + nblk;
-        if (b2 >= 0) dn[b2] = tg2 + nblk;
-        if (idx == qe) {
-          sweep++;
-          if (S == 0 && sweep == total - 1 && total - 1 != iters - 1) { acc[2] = 0; err[2] = 0; cnt[2] = 0; }
-          if (sweep < iters) idx = qs;
-          else { idx = qf; if (qf == qe) sweep = total; }
-        }
-        if (sweep < total) GZ_FETCH();
-      }
-    }
-#undef GZ_FETCH
+  const bool on = live && total > 0;
+  const int max_nstage = __reduce_max_sync(0xffffffffu, nstage);
+  const int rounds = (total > 0 && max_nstage > 0) ? (total + max_nstage - 1) * R : 0;
+  double *cas = ca + (size_t)6 * (nbp + 1) * S;
+  PgsStat st;
+  for (int t = 0; t < 3; t++) { st.acc[t] = 0; st.err[t] = 0; st.cnt[t] = 0; }
+  const int pair = lane >> 1;
+  int F = 0, fslot = 0;                         // producer side (lane 0): round F needs slot fslot
+#define GZ_FETCH()                                                                                \
+  {                                                                                               \
+    if (lane == 0 && F < rounds) {                                                                \
+      const unsigned bar = bar_s + 8 * (F & (GZ_RING_D - 1));                                     \
+      mbar_expect_tx(bar, GZ_ROUND_DOUBLES * 8);                                                  \
+      bulk_g2s(ring_s + (unsigned)((F & (GZ_RING_D - 1)) * GZ_ROUND_DOUBLES * 8),                 \
+               slab + (size_t)fslot * GZ_ROUND_DOUBLES, GZ_ROUND_DOUBLES * 8, bar);               \
+    }                                                                                             \
+    F++;                                                                                          \
+    if (++fslot == R) fslot = 0;                                                                  \
   }
-  dbg_iters[0] = loops; dbg_iters[1] = execs;
-  if (S == 0) {
-    for (int k = 0; k < 3; k++) { st[k] = acc[k]; st[3 + k] = err[k]; st[6 + k] = (double)cnt[k]; }
+  // consumer side: wait for the stage of round r, then read this lane pair's record from it
+#define GZ_TAKE(REGS, r)                                                                          \
+  {                                                                                               \
+    mbar_wait(bar_s + 8 * ((r) & (GZ_RING_D - 1)), ((r) / GZ_RING_D) & 1);                        \
+    load_row(REGS, ring + (size_t)((r) & (GZ_RING_D - 1)) * GZ_ROUND_DOUBLES + pair * GZ_REC, S, nbp, epoch); \
   }
-}
-
-}  // namespace gz
-
-namespace gz {
-
-template <bool MULTIWARP>
-__global__ void k_pgs(DevBatch B, PgsCfg cfg) {
-  extern __shared__ __align__(16) double shd[];
-  const int L = cfg.L, nbp = cfg.nbp, TW = cfg.tw;
-  const int slot = threadIdx.x / TW, l = threadIdx.x % TW;
-  const int w = blockIdx.x * cfg.wpc + slot;
-  const bool live = w < B.n_worlds;
-  const size_t slotd = pgs_slot_doubles(nbp);
-  double *ca = shd + slot * slotd;                              // [2][nbp+1][6]
-  double *stat = ca + 12 * (nbp + 1);                           // [nbp][9]
-  volatile int *done = (volatile int *)(stat + 9 * nbp);        // [2][nbp+1]
-  int *nAs = (int *)(stat + 9 * nbp) + 2 * (nbp + 1);           // [nbp]
-  int *nFs = nAs + nbp;                                         // [nbp]
-  double *pool = shd + cfg.wpc * slotd;
-  __shared__ int pool_off[33], pool_cap[33];
-
-  WorldInfo wi;
-  int nb = 0, m = 0;
-  const int *sch = nullptr;
-  double *gslab = nullptr;
-  if (live) { wi = B.world[w]; nb = wi.nb; m = B.wstep[w].m; sch = wsched(B, w); gslab = wprec(B, wi); }
-  if (threadIdx.x == 0) {
-    int used = 0;
-    const int total = cfg.wpc * cfg.budget;
-    for (int k = 0; k < cfg.wpc; k++) {
-      int wk = blockIdx.x * cfg.wpc + k;
-      int mk = (wk < B.n_worlds) ? B.wstep[wk].m : 0;
-      int c = mk < total - used ? mk : total - used;
-      pool_off[k] = used; pool_cap[k] = c; used += c;
-    }
+#define GZ_ROUND(CUR, NXT)                                                                        \
+  {                                                                                               \
+    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;                                                     \
+    if (prof) c0 = clock64();                                                                     \
+    GZ_FETCH();                                 /* round T + D - 1 into the stage round T - 1 used */ \
+    if (prof) c1 = clock64();                                                                     \
+    if (T + 1 < rounds) GZ_TAKE(NXT, T + 1);                                                      \
+    if (prof) c2 = clock64();                                                                     \
+    const int sweep = period - CUR.stage;                                                         \
+    const bool act = on && CUR.fi != GZ_FI_EMPTY && sweep >= 0 && sweep < total &&                \
+                     (sweep < iters || CUR.fi >= 0);                                              \
+    pgs_row(CUR, act, S, on ? slot * k + jl : 0, cas, lam, nbp, smooth, sweep == iters - 1, sweep == total - 1, st); \
+    __syncwarp();                                                                                 \
+    if (++slot == R) { slot = 0; period++; }                                                      \
+    T++;                                                                                          \
+    if (prof) {                                                                                   \
+      c3 = clock64();                                                                             \
+      pc[0] += c1 - c0; pc[1] += c2 - c1; pc[3] += c3 - c2;                                       \
+      pc[4] += __popc(__ballot_sync(0xffffffffu, act));                                           \
+    }                                                                                             \
   }
-  __syncthreads();
-  // stage the packed records with 16-byte copies (records are 272 B, slabs 16-byte aligned)
-  for (int k = 0; k < cfg.wpc; k++) {
-    int wk = blockIdx.x * cfg.wpc + k;
-    if (wk >= B.n_worlds) break;
-    const WorldInfo wk_i = B.world[wk];
-    const double2 *src = reinterpret_cast<const double2 *>(wprec(B, wk_i));
-    double2 *dst = reinterpret_cast<double2 *>(pool + (size_t)pool_off[k] * GZ_REC);
-    const int n = pool_cap[k] * (GZ_REC / 2);
-    for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
-  }
-  const int cap = pool_cap[slot];
-  double *mypool = pool + (size_t)pool_off[slot] * GZ_REC;
-  for (int i = l; i <= nbp; i += TW) {
-    done[i] = 0; done[nbp + 1 + i] = 0;
-    for (int t = 0; t < 6; t++) { ca[6 * i + t] = 0; ca[6 * (nbp + 1 + i) + t] = 0; }
-    if (i < nbp) {
-      nAs[i] = (live && i < nb) ? sch[GZ_SCHED * i + 0] : 0;
-      nFs[i] = (live && i < nb) ? sch[GZ_SCHED * i + 1] : 0;
-    }
-  }
-  __syncthreads();
-  // initial caccel = iMJ * lambda0 over the warm-started (persistent-joint) rows, in row index
-  // order (multiply_invM_JT, quickstep_util.cpp:101-119)
-  if (live && B.p.warm_start > 0 && m > 0) {
-    for (int b = l; b < nb; b += TW) {
-      const Body &bd = B.body[wi.body0 + b];
-      if (!B.bstep[wi.body0 + b].active) continue;
-      for (int q = bd.joint_begin; q < bd.joint_end; q++) {
-        const Joint &j = B.joint[B.body_joint[q]];
-        for (int rr = 0; rr < j.m; rr++) {
-          const int pidx = B.row[wi.row0 + j.row0 + rr].next_f;
-          const double *rec = (pidx < cap) ? mypool + (size_t)pidx * GZ_REC : gslab + (size_t)pidx * GZ_REC;
-          const RecInts ri = *reinterpret_cast<const RecInts *>(rec + GZ_REC_INTS);
-          const double *im = (ri.b1 == b) ? rec + 12 : rec + 18;
-          for (int t = 0; t < 6; t++) {
-            ca[6 * b + t] += im[t] * rec[29];
-            ca[6 * (nbp + 1 + b) + t] += im[t] * rec[30];
-          }
-        }
-      }
-    }
-  }
-  __syncthreads();
-  const int s = l & 1, e = l >> 1;
-  int qs = 0, qf = 0, qe = 0;
-  if (live && l < L && e < nb && m > 0) { qs = sch[GZ_SCHED * e + 2]; qf = sch[GZ_SCHED * e + 3]; qe = sch[GZ_SCHED * e + 4]; }
-  // block lengths: walk the executor's queue backwards; a row joins the block of its successor
-  // when both touch the same bodies with consecutive tickets (and the successor does not start
-  // the friction-only part of the queue)
-  if (s == 0) {
-    int run_next = 0, nb1 = -1, nb2 = -1, nt1 = 0, nt2 = 0;
-    for (int idx = qe - 1; idx >= qs; idx--) {
-      double *rec = (idx < cap) ? mypool + (size_t)idx * GZ_REC : gslab + (size_t)idx * GZ_REC;
-      RecInts ri = *reinterpret_cast<const RecInts *>(rec + GZ_REC_INTS);
-      int run = 0;
-      if (idx + 1 < qe && idx + 1 != qf && ri.b1 == nb1 && ri.b2 == nb2 && ri.t1 + 1 == nt1 &&
-          (ri.b2 == 0xFFFF || ri.t2 + 1 == nt2) && run_next < 60000)
-        run = run_next + 1;
-      ri.run = (unsigned short)run;
-      *reinterpret_cast<RecInts *>(rec + GZ_REC_INTS) = ri;
-      run_next = run; nb1 = ri.b1; nb2 = ri.b2; nt1 = ri.t1; nt2 = ri.t2;
-    }
-  }
-  if (MULTIWARP) __syncthreads(); else __syncwarp();
-  int dbg[2] = {0, 0};
+  constexpr bool prof = PROF;
+  long long pc[5] = {0, 0, 0, 0, 0};
+  int slot = 0, period = 0, T = 0;
   const long long t0 = clock64();
-  if (m <= cap)   // uniform per world (per warp in the single-warp case): all rows are in the pool
-    pgs_lane<MULTIWARP, true>(B, s, qs, qf, qe, cap, mypool, gslab, ca + 6 * (size_t)(nbp + 1) * s,
-                              done + (nbp + 1) * s, nAs, nFs, nbp, stat + 9 * (e < nbp ? e : 0), dbg);
-  else
-    pgs_lane<MULTIWARP, false>(B, s, qs, qf, qe, cap, mypool, gslab, ca + 6 * (size_t)(nbp + 1) * s,
-                               done + (nbp + 1) * s, nAs, nFs, nbp, stat + 9 * (e < nbp ? e : 0), dbg);
-  const long long t1 = clock64();
-  if (live) {   // instrumentation: longest lane of the world (loop trips, row updates) and its cycles
-    WorldStep &wsd = B.wstep[w];
-    atomicMax(&wsd.pad[0], dbg[0]);
-    atomicMax(&wsd.pad[1], dbg[1]);
-    atomicMax(&wsd.n_fric, (int)(t1 - t0));
+  RowRegs A, Bn;
+  if (rounds > 0) {
+    for (int d = 0; d < GZ_RING_D - 1; d++) GZ_FETCH();
+    GZ_TAKE(A, 0);
+    while (T + 1 < rounds) {
+      GZ_ROUND(A, Bn);
+      GZ_ROUND(Bn, A);
+    }
+    if (T < rounds) GZ_ROUND(A, Bn);
   }
-  if (MULTIWARP) __syncthreads(); else __syncwarp();
+#undef GZ_ROUND
+#undef GZ_TAKE
+#undef GZ_FETCH
+  const long long t1 = clock64();
+  __syncwarp();
+  // ---- statistics: reduce over the 2k lanes of the world (lambda-solve lanes carry the sums)
+  for (int d = 1; d < LW; d <<= 1) {
+#pragma unroll
+    for (int t = 0; t < 3; t++) {
+      st.acc[t] += __shfl_xor_sync(0xffffffffu, st.acc[t], d);
+      st.err[t] += __shfl_xor_sync(0xffffffffu, st.err[t], d);
+      st.cnt[t] += __shfl_xor_sync(0xffffffffu, st.cnt[t], d);
+    }
+  }
   if (live) {
     // lambda back to the rows (k_lambda_save copies them to the joints), caccel to the bodies
-    Row *rows = B.row + wi.row0;
-    for (int idx = qs + s; idx < qe; idx += 2) {   // the two solve lanes of an executor split its rows
-      const double *rec = (idx < cap) ? mypool + (size_t)idx * GZ_REC : gslab + (size_t)idx * GZ_REC;
-      const int orig = B.order[wi.row0 + idx];
-      rows[orig].lambda = rec[29];
-      rows[orig].lambda_erp = rec[30];
+    Row *rw = B.row + wi.row0;
+    for (int i = lw; i < nslots; i += LW) {
+      const RecInts *ri = reinterpret_cast<const RecInts *>(slab_rec(sl, i) + GZ_REC_INTS);
+      if (((unsigned)ri->stage_epoch >> 8) == epoch) { rw[ri->orig].lambda = lam[2 * i]; rw[ri->orig].lambda_erp = lam[2 * i + 1]; }
     }
-    for (int i = l; i < nb; i += TW) {
+    for (int i = lw; i < wi.nb; i += LW) {
       BodyStep &bs = B.bstep[wi.body0 + i];
       for (int t = 0; t < 6; t++) { bs.caccel[t] = ca[6 * i + t]; bs.caccel_erp[t] = ca[6 * (nbp + 1 + i) + t]; }
     }
-    if (l == 0) {
+    if (lw == 0) {
       WorldStep &ws = B.wstep[w];
-      double a[3] = {0, 0, 0}, er[3] = {0, 0, 0}, c[3] = {0, 0, 0};
-      if (m > 0)
-        for (int q = 0; q < nb; q++)
-          for (int k = 0; k < 3; k++) { a[k] += stat[9 * q + k]; er[k] += stat[9 * q + 3 + k]; c[k] += stat[9 * q + 6 + k]; }
+      const double *a = st.acc, *er = st.err;
+      const double c[3] = {(double)st.cnt[0], (double)st.cnt[1], (double)st.cnt[2]};
       // quickstep_pgs_lcp.cpp:814-855
       const double tot = c[0] + c[1] + c[2];
-      for (int k = 0; k < 3; k++) {
-        ws.rms_dlambda[k] = sqrt(c[k] > 0 ? a[k] / c[k] : 0.0);
-        ws.rms_residual[k] = sqrt(c[k] > 0 ? er[k] / c[k] : 0.0);
+      for (int q = 0; q < 3; q++) {
+        ws.rms_dlambda[q] = sqrt(c[q] > 0 ? a[q] / c[q] : 0.0);
+        ws.rms_residual[q] = sqrt(c[q] > 0 ? er[q] / c[q] : 0.0);
       }
       ws.rms_dlambda[3] = sqrt((a[0] + a[1] + a[2] > 0) ? (a[0] + a[1] + a[2]) / tot : 0.0);
       ws.rms_residual[3] = sqrt((er[0] + er[1] + er[2] > 0) ? (er[0] + er[1] + er[2]) / tot : 0.0);
-      ws.num_contacts_stat = (int)c[1];
+      ws.num_contacts_stat = st.cnt[1];
+      // instrumentation: rounds the warp ran, this world's period * 256 + k, SM cycles of the sweeps
+      ws.pad[0] = rounds; ws.pad[1] = R * 256 + k; ws.n_fric = (int)(t1 - t0);
     }
+  }
+  if (prof && lane == 0) {
+    for (int q = 0; q < 5; q++) atomicAdd(&B.prof[q], (unsigned long long)pc[q]);
+    atomicAdd(&B.prof[5], (unsigned long long)rounds);
   }
 }
 

@@ -161,6 +161,8 @@ __global__ void k_info1(DevBatch B) {
   __shared__ int carry;
   __shared__ int warp_sums[32];
   if (threadIdx.x == 0) carry = 0;
+  if (w == 0)   // the schedule buckets are rebuilt by k_schedule
+    for (int i = threadIdx.x; i < GZ_NBUCKET; i += blockDim.x) B.bk_count[i] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   for (int k0 = 0; k0 < wi.nj; k0 += blockDim.x) {

@@ -114,6 +114,10 @@ int gzcuda_batch_get_counters(gzcuda_batch *b, unsigned long long out[4], int re
 /* Instrumentation of the last step's k_pgs launch, out[nw][3]: loop trips and row updates of the
  * world's longest lane, and the SM cycles its sweeps took. */
 int gzcuda_batch_get_pgs_debug(gzcuda_batch *b, int *out);
+/* Developer instrumentation of k_pgs (enabled by GZCUDA_PGS_PROF=1 when the batch is created):
+ * cycle sums over all warps since the last call: out[0] fetch issue, [1] wait, [2] ring load,
+ * [3] row update, [4] active lanes, [5] rounds. */
+int gzcuda_batch_get_pgs_profile(gzcuda_batch *b, unsigned long long out[8]);
 /* Per-stage device time of the last step call, ms: collide, assemble, pgs, integrate. */
 int gzcuda_batch_stage_ms(gzcuda_batch *b, float ms[4]);
 

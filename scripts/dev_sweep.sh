@@ -1,8 +1,7 @@
 #!/bin/bash
-# usage: dev_sweep.sh "WPC:KB WPC:KB ..."
+# usage: dev_sweep.sh "SMEM_KB=44,RT=28 SMEM_KB=100 ..."   (each item: comma-separated GZCUDA_PGS_* knobs)
 for cfg in $1; do
-  wpc=${cfg%%:*}; kb=${cfg##*:}
-  GZCUDA_PGS_WPC=$wpc GZCUDA_PGS_SMEM_KB=$kb python bench.py --steps 100 --warmup 30 --no-cpu-baseline 2>&1 | python -c "
-import sys,json
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('wpc=$wpc kb=$kb', round(d['value']), 'pgs_ms', round(d['roofline']['avg_launch_ms'],3))"
+  envs=""
+  for kv in ${cfg//,/ }; do envs="$envs GZCUDA_PGS_$kv"; done
+  env $envs python scripts/dev_pgs_knobs.py 2>&1 | tail -1
 done

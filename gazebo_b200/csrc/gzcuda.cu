@@ -304,7 +304,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   for (int *kk : {&d.pgs_kmin, &d.pgs_kmax}) { int v = 1; while (2 * v <= *kk) v <<= 1; *kk = v; }
   PgsCfg &c = b->pgs;
   c.nbp = std::max(max_nb, 1);
-  size_t smem = 40 * 1024;
+  size_t smem = 52 * 1024;
   if (const char *e = getenv("GZCUDA_PGS_SMEM_KB")) smem = (size_t)atoi(e) * 1024;
   const size_t ca_bytes = (size_t)12 * (c.nbp + 1) * sizeof(double);
   const size_t ring_bytes = (size_t)GZ_RING_DOUBLES * sizeof(double);

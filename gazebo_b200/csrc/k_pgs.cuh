@@ -56,7 +56,7 @@ __device__ inline WScratch wscratch(const DevBatch &B, int w) {
 #define GZ_FI_EMPTY (-3)
 struct RecInts {
   int fi;                 // -1 bilateral, -2 contact normal, >= 0 world-local slot index (s * k + j) of the normal row
-  unsigned short b1, b2;  // world-local bodies, b2 = 0xFFFF: none
+  unsigned short b1, b2;  // world-local bodies, b2 = max_nb (the dummy accumulator slot): none
   int stage_epoch;        // (step epoch << 8) | off(r) / R
   int orig;               // world-local row index (write-back)
 };
@@ -329,7 +329,7 @@ __global__ void k_rowfinish(DevBatch B) {
   rec2[14] = make_double2(r.hi, Ad2);
   RecInts ri;
   ri.fi = (r.findex >= 0) ? B.row[wi.row0 + r.findex].next_f : r.findex;
-  ri.b1 = (unsigned short)r.b1; ri.b2 = (r.b2 >= 0) ? (unsigned short)r.b2 : (unsigned short)0xFFFF;
+  ri.b1 = (unsigned short)r.b1; ri.b2 = (r.b2 >= 0) ? (unsigned short)r.b2 : (unsigned short)B.max_nb;   // none = the all-zero dummy slot
   ri.stage_epoch = (int)((((unsigned)B.step_index + 1u) << 8) | (unsigned)r.t1a);
   ri.orig = i;
   *reinterpret_cast<RecInts *>(rec + GZ_REC_INTS) = ri;

@@ -22,20 +22,24 @@
 
 namespace gz {
 
-#define GZ_RING_D 4                 // ring stages
-#define GZ_RING_DOUBLES (GZ_RING_D * GZ_ROUND_DOUBLES + 2 * GZ_RING_D)   // records + one mbarrier per stage (padded)
+#define GZ_RING_D 2                 // ring stages
+#define GZ_RING_G 4                 // rounds per stage: one fetch (and one mbarrier wait) per G rounds
+#define GZ_STAGE_DOUBLES (GZ_RING_G * GZ_ROUND_DOUBLES)
+#define GZ_RING_DOUBLES (GZ_RING_D * GZ_STAGE_DOUBLES + 2 * GZ_RING_D)   // records + one mbarrier per stage (padded)
 
 struct PgsCfg { int smem_doubles, nbp, wpw_max; };
 
 // the constants of one row, in registers
 struct RowRegs {
-  double J[12], iM[12], rhs, adcfm, lo, hi, Ad2;
+  double J[12], iM[12], rhs, adcfm, lo, hi;
   int fi, b1, b2, stage;
 };
 
 // Reads one record; a record whose epoch is not this step's is an empty slot (or a stale one in a
 // part of the slab no world of this warp owns) and is turned into a harmless no-op row.
-__device__ __forceinline__ void load_row(RowRegs &R, const double *rec, const int S, const int nbp, const unsigned epoch) {
+// epoch_sh = epoch << 8; dummy_bb = (nbp << 16): body 1 = 0, body 2 = the all-zero dummy.
+__device__ __forceinline__ void load_row(RowRegs &R, const double *rec, const int S, const unsigned epoch_sh,
+                                         const unsigned dummy_bb) {
   const double2 *r2 = reinterpret_cast<const double2 *>(rec);
 #pragma unroll
   for (int k = 0; k < 6; k++) {
@@ -43,14 +47,14 @@ __device__ __forceinline__ void load_row(RowRegs &R, const double *rec, const in
     R.J[2 * k] = a.x; R.J[2 * k + 1] = a.y;
     R.iM[2 * k] = b.x; R.iM[2 * k + 1] = b.y;
   }
-  const double2 c = r2[12], d = r2[13], e = r2[14];
-  R.rhs = S ? c.y : c.x; R.adcfm = d.x; R.lo = d.y; R.hi = e.x; R.Ad2 = e.y;
+  const double2 d = r2[13];
+  R.rhs = rec[24 + S]; R.adcfm = d.x; R.lo = d.y; R.hi = rec[28];
   const int4 iv = *reinterpret_cast<const int4 *>(rec + GZ_REC_INTS);   // RecInts: fi | b1,b2 | epoch,stage | orig
-  const bool valid = ((unsigned)iv.z >> 8) == epoch;
-  const int b2 = (iv.y >> 16) & 0xFFFF;
+  const bool valid = ((unsigned)iv.z ^ epoch_sh) < 256u;
+  const unsigned bb = valid ? (unsigned)iv.y : dummy_bb;
   R.fi = valid ? iv.x : GZ_FI_EMPTY;
-  R.b1 = valid ? (iv.y & 0xFFFF) : 0;
-  R.b2 = (valid && b2 != 0xFFFF) ? b2 : nbp;
+  R.b1 = bb & 0xFFFFu;
+  R.b2 = bb >> 16;
   R.stage = iv.z & 255;
 }
 
@@ -85,9 +89,10 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 // all-zero dummy accumulator; the reference skips that term, and so does the select below.
 struct PgsStat { double acc[3], err[3]; int cnt[3]; };
 
+template <bool STATS>
 __device__ __forceinline__ void pgs_row(const RowRegs &R, const bool act, const int S, const int idx, double *cas,
-                                        double *lam, const int nbp, const double smooth, const bool stat01,
-                                        const bool stat2, PgsStat &st) {
+                                        double *lam, const int nbp, const double smooth, const double Ad2,
+                                        const bool stat01, const bool stat2, PgsStat &st) {
   double *c1 = cas + 6 * R.b1, *c2 = cas + 6 * R.b2;
   const bool two = R.b2 < nbp;
   double a1[6], a2[6];
@@ -140,10 +145,10 @@ __device__ __forceinline__ void pgs_row(const RowRegs &R, const bool act, const 
   }
   // rms_dlambda / rms_constraint_residual (quickstep_pgs_lcp.cpp:700-760,814-855): the sums
   // restart every sweep, so only the last sweep that touches a class survives.
-  {
+  if (STATS) {
     const int cls = (fi == -1) ? 0 : (fi == -2 ? 1 : 2);
     const bool on = act && S == 0 && ((cls == 2) ? stat2 : stat01);
-    const double dd = delta * delta, e2 = dd * R.Ad2;
+    const double dd = delta * delta, e2 = dd * Ad2;
     if (on && cls == 0) { st.acc[0] += dd; st.err[0] += e2; st.cnt[0]++; }
     if (on && cls == 1) { st.acc[1] += dd; st.err[1] += e2; st.cnt[1]++; }
     if (on && cls == 2) { st.acc[2] += dd; st.err[2] += e2; st.cnt[2]++; }
@@ -188,7 +193,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
                                   : B.lamg + 2 * (slab_rec0 + (size_t)wslot * nslots);
   if (!live) lam = shd;
   const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring);
-  const unsigned bar_s = ring_s + GZ_RING_D * GZ_ROUND_DOUBLES * 8;
+  const unsigned bar_s = ring_s + GZ_RING_D * GZ_STAGE_DOUBLES * 8;
   if (lane < GZ_RING_D) mbar_init(bar_s + 8 * lane, 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   const unsigned epoch = ((unsigned)B.step_index + 1u) & 0xFFFFFFu;
@@ -237,61 +242,67 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   PgsStat st;
   for (int t = 0; t < 3; t++) { st.acc[t] = 0; st.err[t] = 0; st.cnt[t] = 0; }
   const int pair = lane >> 1;
-  int F = 0, fslot = 0;                         // producer side (lane 0): round F needs slot fslot
-#define GZ_FETCH()                                                                                \
-  {                                                                                               \
-    if (lane == 0 && F < rounds) {                                                                \
-      const unsigned bar = bar_s + 8 * (F & (GZ_RING_D - 1));                                     \
-      mbar_expect_tx(bar, GZ_ROUND_DOUBLES * 8);                                                  \
-      bulk_g2s(ring_s + (unsigned)((F & (GZ_RING_D - 1)) * GZ_ROUND_DOUBLES * 8),                 \
-               slab + (size_t)fslot * GZ_ROUND_DOUBLES, GZ_ROUND_DOUBLES * 8, bar);               \
+  const unsigned epoch_sh = epoch << 8, dummy_bb = (unsigned)nbp << 16;
+  const int ngroups = (rounds + GZ_RING_G - 1) / GZ_RING_G;
+  int fs = 0;                                   // producer side (lane 0): first slot of the next group to fetch
+  // one group = GZ_RING_G consecutive rounds = consecutive slots of the slab (wrapping at R)
+#define GZ_FETCH(g)                                                                               \
+  if (lane == 0 && (g) < ngroups) {                                                               \
+    const unsigned bar = bar_s + 8 * ((g) & (GZ_RING_D - 1));                                     \
+    unsigned dst = ring_s + (unsigned)(((g) & (GZ_RING_D - 1)) * GZ_STAGE_DOUBLES * 8);           \
+    mbar_expect_tx(bar, GZ_STAGE_DOUBLES * 8);                                                    \
+    int left = GZ_RING_G;                                                                         \
+    while (left > 0) {                                                                            \
+      const int n = min(left, R - fs);                                                            \
+      bulk_g2s(dst, slab + (size_t)fs * GZ_ROUND_DOUBLES, (unsigned)(n * GZ_ROUND_DOUBLES * 8), bar); \
+      dst += (unsigned)(n * GZ_ROUND_DOUBLES * 8);                                                \
+      left -= n; fs += n;                                                                         \
+      if (fs == R) fs = 0;                                                                        \
     }                                                                                             \
-    F++;                                                                                          \
-    if (++fslot == R) fslot = 0;                                                                  \
   }
-  // consumer side: wait for the stage of round r, then read this lane pair's record from it
-#define GZ_TAKE(REGS, r)                                                                          \
+#define GZ_RECP(g, i) (ring + (size_t)((g) & (GZ_RING_D - 1)) * GZ_STAGE_DOUBLES + (size_t)(i) * GZ_ROUND_DOUBLES + pair * GZ_REC)
+#define GZ_ROUND(CUR, NXT, g, i, NG, NI)        /* CUR = record of round (g, i); reads NXT = (NG, NI) */ \
   {                                                                                               \
-    mbar_wait(bar_s + 8 * ((r) & (GZ_RING_D - 1)), ((r) / GZ_RING_D) & 1);                        \
-    load_row(REGS, ring + (size_t)((r) & (GZ_RING_D - 1)) * GZ_ROUND_DOUBLES + pair * GZ_REC, S, nbp, epoch); \
-  }
-#define GZ_ROUND(CUR, NXT)                                                                        \
-  {                                                                                               \
-    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;                                                     \
+    long long c0 = 0, c3 = 0;                                                                     \
     if (prof) c0 = clock64();                                                                     \
-    GZ_FETCH();                                 /* round T + D - 1 into the stage round T - 1 used */ \
-    if (prof) c1 = clock64();                                                                     \
-    if (T + 1 < rounds) GZ_TAKE(NXT, T + 1);                                                      \
-    if (prof) c2 = clock64();                                                                     \
+    load_row(NXT, GZ_RECP(NG, NI), S, epoch_sh, dummy_bb);                                        \
     const int sweep = period - CUR.stage;                                                         \
-    const bool act = on && CUR.fi != GZ_FI_EMPTY && sweep >= 0 && sweep < total &&                \
-                     (sweep < iters || CUR.fi >= 0);                                              \
-    pgs_row(CUR, act, S, on ? slot * k + jl : 0, cas, lam, nbp, smooth, sweep == iters - 1, sweep == total - 1, st); \
+    const bool act = on && (unsigned)sweep < (unsigned)(CUR.fi >= 0 ? total : (CUR.fi == GZ_FI_EMPTY ? 0 : iters)); \
+    const bool st_round = (period >= iters - 1 && period < iters - 1 + max_nstage) ||             \
+                          (period >= total - 1 && period < total - 1 + max_nstage);               \
+    const int idx = on ? slot * k + jl : 0;                                                       \
+    if (st_round)                                                                                 \
+      pgs_row<true>(CUR, act, S, idx, cas, lam, nbp, smooth, GZ_RECP(g, i)[29], sweep == iters - 1, sweep == total - 1, st); \
+    else                                                                                          \
+      pgs_row<false>(CUR, act, S, idx, cas, lam, nbp, smooth, 0.0, false, false, st);             \
     __syncwarp();                                                                                 \
     if (++slot == R) { slot = 0; period++; }                                                      \
-    T++;                                                                                          \
     if (prof) {                                                                                   \
       c3 = clock64();                                                                             \
-      pc[0] += c1 - c0; pc[1] += c2 - c1; pc[3] += c3 - c2;                                       \
+      pc[3] += c3 - c0;                                                                           \
       pc[4] += __popc(__ballot_sync(0xffffffffu, act));                                           \
     }                                                                                             \
   }
   constexpr bool prof = PROF;
   long long pc[5] = {0, 0, 0, 0, 0};
-  int slot = 0, period = 0, T = 0;
+  int slot = 0, period = 0;
   const long long t0 = clock64();
   RowRegs A, Bn;
-  if (rounds > 0) {
-    for (int d = 0; d < GZ_RING_D - 1; d++) GZ_FETCH();
-    GZ_TAKE(A, 0);
-    while (T + 1 < rounds) {
-      GZ_ROUND(A, Bn);
-      GZ_ROUND(Bn, A);
+  if (ngroups > 0) {
+    GZ_FETCH(0);
+    mbar_wait(bar_s, 0);
+    load_row(A, GZ_RECP(0, 0), S, epoch_sh, dummy_bb);
+    for (int g = 0; g < ngroups; g++) {
+      GZ_FETCH(g + 1);                          // into the stage group g - 1 used
+      GZ_ROUND(A, Bn, g, 0, g, 1);
+      GZ_ROUND(Bn, A, g, 1, g, 2);
+      GZ_ROUND(A, Bn, g, 2, g, 3);
+      if (g + 1 < ngroups) mbar_wait(bar_s + 8 * ((g + 1) & (GZ_RING_D - 1)), ((g + 1) / GZ_RING_D) & 1);
+      GZ_ROUND(Bn, A, g, 3, g + 1, 0);          // past the last group this reads a stale stage: never used
     }
-    if (T < rounds) GZ_ROUND(A, Bn);
   }
 #undef GZ_ROUND
-#undef GZ_TAKE
+#undef GZ_RECP
 #undef GZ_FETCH
   const long long t1 = clock64();
   __syncwarp();

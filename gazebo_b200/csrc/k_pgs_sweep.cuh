@@ -271,7 +271,8 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
     const bool st_round = (period >= iters - 1 && period < iters - 1 + max_nstage) ||             \
                           (period >= total - 1 && period < total - 1 + max_nstage);               \
     const int idx = on ? slot * k + jl : 0;                                                       \
-    if (st_round)                                                                                 \
+    if (!__any_sync(0xffffffffu, act)) { /* nothing due in this round (friction-only sweeps, pipeline ends) */ } \
+    else if (st_round)                                                                            \
       pgs_row<true>(CUR, act, S, idx, cas, lam, nbp, smooth, GZ_RECP(g, i)[29], sweep == iters - 1, sweep == total - 1, st); \
     else                                                                                          \
       pgs_row<false>(CUR, act, S, idx, cas, lam, nbp, smooth, 0.0, false, false, st);             \

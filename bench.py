@@ -95,8 +95,9 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n_worlds = min(WORLDS_PER_GPU, 16 * cores)
-    # each "step" of this arm = one world step of the sampled worlds; K steps timed
+    n_worlds = min(WORLDS_PER_GPU, 64 * cores)
+    # each "step" of this arm = one world step of the sampled worlds (a bounded sample of the
+    # 4096-world batch, dealt round-robin to all host threads); K steps timed
     rate, dt, flavour = cpu_reference_rate(n_worlds, args.steps, args.warmup, cores)
     sample = "%d worlds x %d steps on %d threads (oracle/_ref %s flavour, natural order, dWorldQuickStep)" % (
         n_worlds, args.steps, cores, flavour)
@@ -129,15 +130,14 @@ def run_gpu(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    from gazebo_b200 import sharding
+
     def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return sharding.max_over_ranks(x, dist, "cuda")
 
     n_worlds = args.worlds
-    sc, pd = W.revolve_worlds(n_worlds, first_world=rank * n_worlds)
+    first_world, _ = sharding.world_block(rank, n_worlds)
+    sc, pd = W.revolve_worlds(n_worlds, first_world=first_world)
     p = S.default_params()
     b = Batch(sc, p, device=local_rank)
     b.set_hinge_pd(pd)
@@ -160,7 +160,7 @@ def run_gpu(args, rank, world, local_rank):
     stage = b.stage_ms()
     b.set_profiling(False)
     ms = max_over_ranks(ms)
-    value = world * n_worlds * K / (ms * 1e-3)
+    value = sharding.job_throughput(n_worlds, world, K, ms * 1e-3)
 
     # ---- end to end through the host-buffer ABI call: pinned wrench in, pinned state out, every step
     nb = sc.nb
@@ -177,7 +177,7 @@ def run_gpu(args, rank, world, local_rank):
     barrier()
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    e2e_value = world * n_worlds * K / e2e_s
+    e2e_value = sharding.job_throughput(n_worlds, world, K, e2e_s)
     finite = bool(torch.isfinite(state).all())
 
     if rank != 0:
@@ -204,8 +204,11 @@ def run_gpu(args, rank, world, local_rank):
                         "PD-driven sinusoid gaits, deterministic row-order mode" % n_worlds,
             "worlds_per_gpu": n_worlds, "bodies_per_gpu": sc.nb, "geoms_per_gpu": sc.ng, "joints_per_gpu": sc.nj,
             "rows_per_world_step": rows / max(wsteps, 1), "contacts_per_world_step": contacts / max(wsteps, 1),
-            "l2": "no flush between steps: the steps of one call run back to back like the product does; "
-                  "the per-step working set (row slabs + geoms + bodies) is reported in DESIGN.md",
+            "l2": "inputs larger than L2, no flush: a step touches bodies+geoms+joints (%.0f MB), the row array and the "
+                  "PGS record slabs (~%.0f MB at %.0f rows/world), more than the 126 MB L2, so a step does not find its "
+                  "inputs in L2 from the previous one; inside k_pgs the record slab is L2-resident across the 60 sweeps "
+                  "by design (DESIGN.md 3-4)" % ((sc.nb * 704 + sc.ng * 448 + sc.nj * 432) / 1e6,
+                                                2 * 1.25 * rows / max(wsteps, 1) * n_worlds * 300 / 1e6, rows / max(wsteps, 1)),
             "stage_ms_last_step": {"collide": stage[0], "assemble": stage[1], "pgs": stage[2], "integrate": stage[3]},
             "finite": finite,
         },
@@ -216,18 +219,19 @@ def run_gpu(args, rank, world, local_rank):
                      "frac": achieved / peak if peak else None, "traffic": traffic, "peak_kind": peak_kind,
                      "bytes_per_launch": bytes_per_launch, "avg_launch_ms": pgs_avg_ms,
                      "share_of_step": pgs_ms / ms if ms > 0 else None,
-                     "note": "achieved = algorithmic bytes (288 B/row/sweep); rows are L1/L2-resident during the "
-                             "sweeps, so DRAM traffic (traffic) is far lower — this kernel is latency/FP64-bound, "
-                             "not HBM-bound"},
+                     "note": "achieved = algorithmic bytes (288 B per row per sweep, SURVEY 8d) / CUDA-event time of k_pgs; "
+                             "the record slab stays in L2 across the 60 sweeps, so measured DRAM traffic (traffic, from "
+                             "profiles/) is far lower: at 4096 small worlds this kernel is bound by the latency of the "
+                             "exact-order dependent FP64 chain per body, not by HBM (DESIGN.md 4)"},
         "clocks": sampler.summary(),
     }
     # CPU baseline on this box's host cores (rank 0, N=1 only), bounded sample
     if world == 1 and not args.no_cpu_baseline:
         try:
             cores = os.cpu_count() or 1
-            nw = min(n_worlds, 16 * cores)
-            steps = 300
-            rate, dt, flavour = cpu_reference_rate(nw, steps, 50, cores)
+            nw = min(n_worlds, 64 * cores)
+            steps = 3000      # ~10-20 s of CPU work on all cores
+            rate, dt, flavour = cpu_reference_rate(nw, steps, 100, cores)
             line["cpu_baseline"] = {
                 "value": rate, "unit": UNIT, "cores": cores, "kind": "reference",
                 "sample": "%d worlds x %d steps in %.1f s on %d threads (oracle/_ref %s flavour: the reference's own "

@@ -89,34 +89,43 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 // all-zero dummy accumulator; the reference skips that term, and so does the select below.
 struct PgsStat { double acc[3], err[3]; int cnt[3]; };
 
-template <bool STATS>
-__device__ __forceinline__ void pgs_row(const RowRegs &R, const bool act, const int S, const int idx, double *cas,
-                                        double *lam, const int nbp, const double smooth, const double Ad2,
-                                        const bool stat01, const bool stat2, PgsStat &st) {
-  double *c1 = cas + 6 * R.b1, *c2 = cas + 6 * R.b2;
-  const bool two = R.b2 < nbp;
-  double a1[6], a2[6];
-  {
-    const double2 *p1 = reinterpret_cast<const double2 *>(c1), *p2 = reinterpret_cast<const double2 *>(c2);
+// what a row update reads before it can start: the accumulators of its bodies and two lambdas
+struct RowIn { double a1[6], a2[6], old_lambda, nlam; };
+
+__device__ __forceinline__ void pgs_row_in(RowIn &I, const RowRegs &R, const int S, const int idx, const double *cas,
+                                           const double *lam) {
+  const double2 *p1 = reinterpret_cast<const double2 *>(cas + 6 * R.b1);
+  const double2 *p2 = reinterpret_cast<const double2 *>(cas + 6 * R.b2);
 #pragma unroll
-    for (int t = 0; t < 3; t++) {
-      const double2 x = p1[t], y = p2[t];
-      a1[2 * t] = x.x; a1[2 * t + 1] = x.y; a2[2 * t] = y.x; a2[2 * t + 1] = y.y;
-    }
+  for (int t = 0; t < 3; t++) {
+    const double2 x = p1[t], y = p2[t];
+    I.a1[2 * t] = x.x; I.a1[2 * t + 1] = x.y; I.a2[2 * t] = y.x; I.a2[2 * t + 1] = y.y;
   }
-  const double old_lambda = lam[2 * idx + S];
+  I.old_lambda = lam[2 * idx + S];
+  I.nlam = lam[2 * (R.fi >= 0 ? R.fi : idx) + S];
+}
+
+template <bool STATS, bool TWO>
+__device__ __forceinline__ void pgs_row(const RowRegs &R, const RowIn &I, const bool act, const int S, const int idx,
+                                        double *cas, double *lam, const int nbp, const double smooth, const double Ad2,
+                                        const bool stat01, const bool stat2, PgsStat &st) {
+  // TWO = false: no due row of this warp has a second body in this round (warp-uniform), so the
+  // second body's half of the work is not even issued
+  double *c1 = cas + 6 * R.b1, *c2 = cas + 6 * R.b2;
+  const bool two = TWO && R.b2 < nbp;
+  const double *a1 = I.a1, *a2 = I.a2;
+  const double old_lambda = I.old_lambda, nlam = I.nlam;
   const int fi = R.fi;
-  const double nlam = lam[2 * (fi >= 0 ? fi : idx) + S];
   const double hf = fabs(R.hi * nlam);   // pyramid friction: |mu * lambda_normal|
   const double hi_act = fi >= 0 ? hf : R.hi, lo_act = fi >= 0 ? -hf : R.lo;
   // the two dot products, term by term in the reference's left-to-right order, interleaved
-  double d1 = a1[0] * R.J[0], d2 = a2[0] * R.J[6];
+  double d1 = a1[0] * R.J[0], d2 = 0.0;
+  if (TWO) d2 = a2[0] * R.J[6];
 #pragma unroll
-  for (int t = 1; t < 6; t++) { d1 += a1[t] * R.J[t]; d2 += a2[t] * R.J[6 + t]; }
+  for (int t = 1; t < 6; t++) { d1 += a1[t] * R.J[t]; if (TWO) d2 += a2[t] * R.J[6 + t]; }
   double delta = R.rhs - old_lambda * R.adcfm;
   delta -= d1;
-  const double delta2 = delta - d2;
-  delta = two ? delta2 : delta;
+  if (TWO) { const double delta2 = delta - d2; delta = two ? delta2 : delta; }
   double nl = old_lambda + delta;
   const double dlo = lo_act - old_lambda, dhi = hi_act - old_lambda;
   const bool below = nl < lo_act, above = !below && nl > hi_act;
@@ -132,13 +141,13 @@ __device__ __forceinline__ void pgs_row(const RowRegs &R, const bool act, const 
 #pragma unroll
     for (int t = 0; t < 3; t++) {
       o1[t] = make_double2(a1[2 * t] + delta * R.iM[2 * t], a1[2 * t + 1] + delta * R.iM[2 * t + 1]);
-      o2[t] = make_double2(a2[2 * t] + delta * R.iM[6 + 2 * t], a2[2 * t + 1] + delta * R.iM[6 + 2 * t + 1]);
+      if (TWO) o2[t] = make_double2(a2[2 * t] + delta * R.iM[6 + 2 * t], a2[2 * t + 1] + delta * R.iM[6 + 2 * t + 1]);
     }
     if (act) {
 #pragma unroll
       for (int t = 0; t < 3; t++) p1[t] = o1[t];
     }
-    if (act && two) {
+    if (TWO && act && two) {
 #pragma unroll
       for (int t = 0; t < 3; t++) p2[t] = o2[t];
     }
@@ -265,17 +274,23 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   {                                                                                               \
     long long c0 = 0, c3 = 0;                                                                     \
     if (prof) c0 = clock64();                                                                     \
-    load_row(NXT, GZ_RECP(NG, NI), S, epoch_sh, dummy_bb);                                        \
     const int sweep = period - CUR.stage;                                                         \
     const bool act = on && (unsigned)sweep < (unsigned)(CUR.fi >= 0 ? total : (CUR.fi == GZ_FI_EMPTY ? 0 : iters)); \
     const bool st_round = (period >= iters - 1 && period < iters - 1 + max_nstage) ||             \
                           (period >= total - 1 && period < total - 1 + max_nstage);               \
     const int idx = on ? slot * k + jl : 0;                                                       \
-    if (!__any_sync(0xffffffffu, act)) { /* nothing due in this round (friction-only sweeps, pipeline ends) */ } \
+    RowIn in;                                                                                     \
+    pgs_row_in(in, CUR, S, idx, cas, lam);      /* issue these loads first, then the next record's */ \
+    load_row(NXT, GZ_RECP(NG, NI), S, epoch_sh, dummy_bb);                                        \
+    const unsigned due = __ballot_sync(0xffffffffu, act);                                         \
+    const unsigned due2 = __ballot_sync(0xffffffffu, act && CUR.b2 < nbp);                        \
+    if (!due) { /* nothing due in this round (friction-only sweeps, pipeline ends) */ }           \
     else if (st_round)                                                                            \
-      pgs_row<true>(CUR, act, S, idx, cas, lam, nbp, smooth, GZ_RECP(g, i)[29], sweep == iters - 1, sweep == total - 1, st); \
+      pgs_row<true, true>(CUR, in, act, S, idx, cas, lam, nbp, smooth, GZ_RECP(g, i)[29], sweep == iters - 1, sweep == total - 1, st); \
+    else if (due2)                                                                                \
+      pgs_row<false, true>(CUR, in, act, S, idx, cas, lam, nbp, smooth, 0.0, false, false, st);       \
     else                                                                                          \
-      pgs_row<false>(CUR, act, S, idx, cas, lam, nbp, smooth, 0.0, false, false, st);             \
+      pgs_row<false, false>(CUR, in, act, S, idx, cas, lam, nbp, smooth, 0.0, false, false, st);      \
     __syncwarp();                                                                                 \
     if (++slot == R) { slot = 0; period++; }                                                      \
     if (prof) {                                                                                   \

@@ -13,8 +13,8 @@
 #pragma once
 #include "../../include/gzcuda_scene.h"
 
-// PGS schedule buckets (k_pgs.cuh): c = log2(lanes per solve) in 0..4, rung of the period ladder in 1..127
-#define GZ_NRUNG 128
+// PGS schedule buckets (k_pgs.cuh): c = log2(lanes per solve) in 0..4, rung of the period ladder in 1..159
+#define GZ_NRUNG 160
 #define GZ_NBUCKET (5 * GZ_NRUNG)
 
 namespace gz {
@@ -147,6 +147,7 @@ struct DevBatch {
   unsigned long long *prof;  // [8] k_pgs segment cycle sums (GZCUDA_PGS_PROF=1), see gzcuda_batch_get_pgs_profile
   int pgs_prof;
   int pgs_wpw_max;       // worlds per PGS warp the shared-memory budget allows
+  int sch_rcap;          // longest schedule period k_schedule's occupancy table holds
   int pgs_rt, pgs_kmin, pgs_kmax;   // scheduler knobs: target period, lanes-per-solve range
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)

@@ -297,6 +297,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
 
   // PGS launch shape (k_pgs_sweep.cuh): one warp per CTA, a fixed shared-memory budget per CTA
   // that holds the accumulators of its worlds, their lambdas and as many row records as fit.
+  d.sch_rcap = std::min(GZ_RMAX, 2 * std::max(max_rc, 1) + 64);
   d.pgs_rt = 28; d.pgs_kmin = 1; d.pgs_kmax = 16;
   if (const char *e = getenv("GZCUDA_PGS_RT")) d.pgs_rt = std::max(1, atoi(e));
   if (const char *e = getenv("GZCUDA_PGS_KMIN")) d.pgs_kmin = std::max(1, std::min(16, atoi(e)));
@@ -361,7 +362,8 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_info1<<<W, T, 0, b->stream>>>(d);
   if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
-  k_schedule<<<W, 32, 0, b->stream>>>(d);
+  const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16;
+  k_schedule<<<W, 32, sch_smem, b->stream>>>(d);
   k_slab<<<1, 256, 0, b->stream>>>(d);
   k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);

@@ -63,7 +63,7 @@ struct RecInts {
 struct WSched { int R, k, nstage, bucket, idx, nslots, pad0, pad1; };
 
 // ---- buckets: c = log2(k) in 0..4, rb = rung of the R ladder in 1..127 -------------------------
-#define GZ_RMAX 1984   // rung_value(GZ_NRUNG - 1); GZ_NRUNG / GZ_NBUCKET live in gz_batch.h
+#define GZ_RMAX 9984   // rung_value(GZ_NRUNG - 1); GZ_NRUNG / GZ_NBUCKET live in gz_batch.h
 __host__ __device__ inline int rung_value(int rb) {
   if (rb <= 32) return rb;
   if (rb <= 48) return 32 + 2 * (rb - 32);
@@ -71,7 +71,8 @@ __host__ __device__ inline int rung_value(int rb) {
   if (rb <= 80) return 128 + 8 * (rb - 64);
   if (rb <= 96) return 256 + 16 * (rb - 80);
   if (rb <= 112) return 512 + 32 * (rb - 96);
-  return 1024 + 64 * (rb - 112);
+  if (rb <= 128) return 1024 + 64 * (rb - 112);
+  return 2048 + 256 * (rb - 128);
 }
 __host__ __device__ inline int rung_ceil(int R) {   // smallest rung whose value is >= R (R <= GZ_RMAX)
   if (R <= 32) return R < 1 ? 1 : R;
@@ -80,7 +81,8 @@ __host__ __device__ inline int rung_ceil(int R) {   // smallest rung whose value
   if (R <= 256) return 64 + (R - 128 + 7) / 8;
   if (R <= 512) return 80 + (R - 256 + 15) / 16;
   if (R <= 1024) return 96 + (R - 512 + 31) / 32;
-  return 112 + (R - 1024 + 63) / 64;
+  if (R <= 2048) return 112 + (R - 1024 + 63) / 64;
+  return 128 + (R - 2048 + 255) / 256;
 }
 // bk_tab rows
 #define GZ_BK_WARP0 0     // [bucket] first PGS warp (CTA) of the bucket
@@ -110,14 +112,16 @@ __device__ inline double *slab_rec(const WSlab &s, int local) {   // local = slo
 // scheduler on lane 0 (integer work only, m iterations per attempt), then the slot of every row.
 // Row::next_f receives the world-local slot index, Row::t1a the stage.
 __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
-  __shared__ unsigned short occ[GZ_RMAX];
-  __shared__ int cnt[512], last[512], first[512];
+  // dynamic shared memory: cnt, last, first [max_nb] ints, then occ [sch_rcap] shorts
+  extern __shared__ int sch_sh[];
+  int *cnt = sch_sh, *last = sch_sh + B.max_nb, *first = sch_sh + 2 * B.max_nb;
+  unsigned short *occ = reinterpret_cast<unsigned short *>(sch_sh + 3 * B.max_nb);
   const int w = blockIdx.x, lane = threadIdx.x;
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
   const int m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc, nb = wi.nb;
   WSched *wsch = reinterpret_cast<WSched *>(B.wsched) + w;
-  if (m == 0 || m > GZ_RMAX) {
+  if (m == 0 || m > 16 * GZ_RMAX) {
     // nothing to solve: constraint accelerations are zero (free bodies still integrate)
     for (int b = lane; b < nb; b += 32) {
       BodyStep &bs = B.bstep[wi.body0 + b];
@@ -127,7 +131,7 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
       WSched z; z.R = 1; z.k = 1; z.nstage = 0; z.bucket = -1; z.idx = 0; z.nslots = 0; z.pad0 = z.pad1 = 0; *wsch = z;
       for (int k = 0; k < 4; k++) { ws.rms_dlambda[k] = 0; ws.rms_residual[k] = 0; }
       ws.num_contacts_stat = 0;
-      if (m > GZ_RMAX) ws.overflow |= 8;   // needs the large-world solver
+      if (m > 16 * GZ_RMAX) ws.overflow |= 8;   // needs the large-world solver
     }
     return;
   }
@@ -167,7 +171,18 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   int nstage = 1;
   bool done = false;
   for (int attempt = 0; !done; attempt++) {
-    const bool give_up = attempt >= 24 || rb >= GZ_NRUNG;
+    const bool give_up = attempt >= 24 || rb >= GZ_NRUNG || R > B.sch_rcap;
+    if (give_up && m > min(GZ_RMAX, B.sch_rcap)) {   // cannot happen with sane inputs; refuse rather than solve wrongly
+      for (int b = lane; b < nb; b += 32) {
+        BodyStep &bs = B.bstep[wi.body0 + b];
+        for (int t = 0; t < 6; t++) { bs.caccel[t] = 0; bs.caccel_erp[t] = 0; }
+      }
+      if (lane == 0) {
+        WSched z; z.R = 1; z.k = 1; z.nstage = 0; z.bucket = -1; z.idx = 0; z.nslots = 0; z.pad0 = z.pad1 = 0; *wsch = z;
+        ws.overflow |= 8;
+      }
+      return;
+    }
     if (give_up) {   // always valid: the sequential sweep itself (one lane per solve)
       k = 1; rb = rung_ceil(m); R = rung_value(rb); nstage = 1;
       for (int pos = lane; pos < m; pos += 32) { S.slot[pos] = pos; S.stage[pos] = 0; }

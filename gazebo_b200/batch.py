@@ -43,6 +43,7 @@ def lib():
     L.gzcuda_batch_get_counters.argtypes = [vp, dp, ci]
     L.gzcuda_batch_get_pgs_debug.argtypes = [vp, dp]
     L.gzcuda_batch_get_pgs_profile.argtypes = [vp, dp]
+    L.gzcuda_batch_get_pgs_timeline.argtypes = [vp, dp]
     L.gzcuda_batch_update_collision.argtypes = [vp]
     L.gzcuda_batch_update_physics.argtypes = [vp]
     L.gzcuda_world_step.argtypes = [vp, C.c_double]
@@ -74,7 +75,7 @@ EXPORTS = [
     "gzcuda_batch_get_pairs", "gzcuda_batch_get_contacts", "gzcuda_batch_last_step_ms",
     "gzcuda_batch_stage_ms", "gzcuda_batch_step_io", "gzcuda_batch_set_profiling",
     "gzcuda_batch_pgs_ms", "gzcuda_batch_get_counters", "gzcuda_batch_get_pgs_debug",
-    "gzcuda_batch_get_pgs_profile",
+    "gzcuda_batch_get_pgs_profile", "gzcuda_batch_get_pgs_timeline",
 ]
 
 
@@ -136,9 +137,14 @@ class Batch:
         return out
 
     def pgs_profile(self):
-        out = (C.c_ulonglong * 8)()
+        out = (C.c_ulonglong * 16)()
         self._ck(self.L.gzcuda_batch_get_pgs_profile(self.h, out))
         return list(out)
+
+    def pgs_timeline(self):
+        out = np.zeros((self.scene.n_worlds, 2), dtype=np.uint64)
+        self._ck(self.L.gzcuda_batch_get_pgs_timeline(self.h, _p(out)))
+        return out
 
     def update_collision(self):
         self._ck(self.L.gzcuda_batch_update_collision(self.h))

@@ -26,7 +26,8 @@ def build_lib(force=False, verbose=False):
     if not force and os.path.exists(OUT) and os.path.getmtime(OUT) >= _newest_source():
         return OUT
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "gzcuda.cu")]
+    extra = os.environ.get("GZCUDA_NVCC_EXTRA", "").split()   # developer experiments, e.g. -DGZ_RING_G=2
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "gzcuda.cu")]
     subprocess.check_call(cmd)
     return OUT
 

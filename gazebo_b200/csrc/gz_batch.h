@@ -15,7 +15,8 @@
 
 // PGS schedule buckets (k_pgs.cuh): c = log2(lanes per solve) in 0..4, rung of the period ladder in 1..159
 #define GZ_NRUNG 160
-#define GZ_NBUCKET (5 * GZ_NRUNG)
+#define GZ_NBUCKET (10 * GZ_NRUNG)
+#define GZ_CHAIN_NCLS 2   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
 
 namespace gz {
 
@@ -138,16 +139,19 @@ struct DevBatch {
   int *order;            // per world slab: order[k] = world-local row index
   double *prec;          // packed row records (34 doubles each), one slab per PGS warp (k_pgs.cuh)
   long prec_cap;         // records the pool holds
+  double *runrec;        // chain mode: the records of run items, per world at row0 (34 doubles each), k_pgs.cuh
   double *lamg;          // [slots][2] lambda / lambda_erp spill for worlds whose lambdas exceed shared memory
   int *wsched;           // per world WSched {R, k, nstage, bucket, idx, ...} (8 ints)
   int *bk_count;         // [GZ_NBUCKET] worlds per schedule bucket (k, R) this step
   int *bk_tab;           // [4][GZ_NBUCKET+1]: first warp / first record of each bucket; the same sorted heavy-first
   int *warp_world;       // [n_worlds + GZ_NBUCKET][16] worlds of each PGS warp this step (-1: none)
-  int *scratch;          // per world int scratch [4][max_row_cap]
-  unsigned long long *prof;  // [8] k_pgs segment cycle sums (GZCUDA_PGS_PROF=1), see gzcuda_batch_get_pgs_profile
+  int *scratch;          // per world int scratch [7][max_row_cap]
+  unsigned long long *prof;  // [16] k_pgs / k_pgs_chain segment cycle sums (GZCUDA_PGS_PROF=1), see gzcuda_batch_get_pgs_profile
   int pgs_prof;
   int pgs_wpw_max;       // worlds per PGS warp the shared-memory budget allows
   int sch_rcap;          // longest schedule period k_schedule's occupancy table holds
+  int pgs_chain_min;     // rows on the busiest body from which a world is scheduled in chain mode
+  int pgs_chain_doubles[GZ_CHAIN_NCLS];   // shared memory (doubles) of k_pgs_chain's launches, ascending
   int pgs_rt, pgs_kmin, pgs_kmax;   // scheduler knobs: target period, lanes-per-solve range
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)

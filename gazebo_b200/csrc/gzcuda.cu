@@ -31,6 +31,8 @@ struct gzcuda_batch {
   DevBatch d;
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream_chain[GZ_CHAIN_NCLS] = {};   // the chain-mode PGS launches (one per shared-memory size class) run
+  cudaEvent_t ev_fork = nullptr, ev_join[GZ_CHAIN_NCLS] = {};   // beside the regular one: fork / join by events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   std::vector<void *> allocs;
   std::vector<WorldInfo> h_world;
@@ -38,8 +40,8 @@ struct gzcuda_batch {
   long last_launches = 0;
   bool stage_valid = false;
   bool have_pd = false;
-  size_t pgs_smem = 0;
-  PgsCfg pgs;
+  size_t pgs_smem = 0, pgs_chain_smem[GZ_CHAIN_NCLS] = {};
+  PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
   bool profiling = false;             // record an event pair around every k_pgs launch
   std::vector<cudaEvent_t> pgs_ev;    // 2 per step of the last step call
   int pgs_pairs = 0;
@@ -116,6 +118,9 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   if (b->ev1) cudaEventDestroy(b->ev1);
   for (auto &e : b->evs) if (e) cudaEventDestroy(e);
   for (auto &e : b->pgs_ev) cudaEventDestroy(e);
+  if (b->ev_fork) cudaEventDestroy(b->ev_fork);
+  for (auto &e : b->ev_join) if (e) cudaEventDestroy(e);
+  for (auto &st : b->stream_chain) if (st) cudaStreamDestroy(st);
   if (b->stream) cudaStreamDestroy(b->stream);
   delete b;
 }
@@ -272,7 +277,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.contact, (size_t)contact_tot))) return rc;
   if ((rc = dev_alloc(b, &d.row, (size_t)row_tot))) return rc;
   if ((rc = dev_alloc(b, &d.order, (size_t)row_tot))) return rc;
-  if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)4 * max_rc)))) return rc;
+  if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)7 * max_rc)))) return rc;
+  if ((rc = dev_alloc(b, &d.runrec, (size_t)GZ_REC * row_tot))) return rc;
   // record pool of the PGS warps: every world's slots, rounded up to whole warps (16 lane pairs per
   // round), plus one partly filled warp per bucket in use; clamped to a share of device memory
   {
@@ -284,13 +290,13 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if (d.prec_cap > 0x7fffffffL) d.prec_cap = 0x7fffffffL;
   }
   if ((rc = dev_alloc(b, &d.prec, (size_t)GZ_REC * d.prec_cap))) return rc;
-  if ((rc = dev_alloc(b, &d.lamg, (size_t)2 * d.prec_cap))) return rc;
+  if ((rc = dev_alloc(b, &d.lamg, (size_t)2 * (3 * (size_t)row_tot + 128 * (size_t)W)))) return rc;   // per world 2 x (3 row_cap + 128)
   if ((rc = dev_alloc(b, &d.wsched, (size_t)8 * W))) return rc;
   if ((rc = dev_alloc(b, &d.bk_count, (size_t)GZ_NBUCKET))) return rc;
   if ((rc = dev_alloc(b, &d.bk_tab, (size_t)4 * (GZ_NBUCKET + 1)))) return rc;
   if ((rc = dev_alloc(b, &d.warp_world, (size_t)16 * (W + GZ_NBUCKET)))) return rc;
   if ((rc = dev_alloc(b, &d.acc, (size_t)4))) return rc;
-  if ((rc = dev_alloc(b, &d.prof, (size_t)8))) return rc;
+  if ((rc = dev_alloc(b, &d.prof, (size_t)16 + 2 * (size_t)W))) return rc;
   d.pgs_prof = getenv("GZCUDA_PGS_PROF") ? atoi(getenv("GZCUDA_PGS_PROF")) : 0;
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
@@ -298,7 +304,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   // PGS launch shape (k_pgs_sweep.cuh): one warp per CTA, a fixed shared-memory budget per CTA
   // that holds the accumulators of its worlds, their lambdas and as many row records as fit.
   d.sch_rcap = std::min(GZ_RMAX, 2 * std::max(max_rc, 1) + 64);
-  d.pgs_rt = 28; d.pgs_kmin = 1; d.pgs_kmax = 16;
+  d.pgs_rt = 28; d.pgs_kmin = 1; d.pgs_kmax = 16; d.pgs_chain_min = 28;
+  if (const char *e = getenv("GZCUDA_PGS_CHAIN_MIN")) d.pgs_chain_min = std::max(2, atoi(e));
   if (const char *e = getenv("GZCUDA_PGS_RT")) d.pgs_rt = std::max(1, atoi(e));
   if (const char *e = getenv("GZCUDA_PGS_KMIN")) d.pgs_kmin = std::max(1, std::min(16, atoi(e)));
   if (const char *e = getenv("GZCUDA_PGS_KMAX")) d.pgs_kmax = std::max(d.pgs_kmin, std::min(16, atoi(e)));
@@ -319,6 +326,29 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     CK(cudaFuncSetAttribute(k_pgs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
     CK(cudaFuncSetAttribute(k_pgs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
   }
+  // chain-mode worlds (k_pgs_chain.cuh): one world per CTA, resident in shared memory; one launch per
+  // size class (ascending), so that small worlds do not take a large world's share of an SM
+  size_t csmem[GZ_CHAIN_NCLS] = {56 * 1024, 200 * 1024};
+  if (const char *e = getenv("GZCUDA_PGS_CHAIN_KB")) {   // comma-separated, ascending
+    const char *q = e;
+    for (int i = 0; i < GZ_CHAIN_NCLS && *q; i++) {
+      csmem[i] = (size_t)atoi(q) * 1024;
+      while (*q && *q != ',') q++;
+      if (*q == ',') q++;
+    }
+  }
+  for (int q = 0; q < GZ_CHAIN_NCLS; q++) {
+    csmem[q] = std::min<size_t>((size_t)227 * 1024, std::max<size_t>(csmem[q], 16 * 1024));
+    b->pgs_chain[q] = c;
+    b->pgs_chain[q].smem_doubles = (int)(csmem[q] / sizeof(double));
+    d.pgs_chain_doubles[q] = b->pgs_chain[q].smem_doubles;
+    b->pgs_chain_smem[q] = csmem[q];
+  }
+  {
+    const size_t mx = *std::max_element(csmem, csmem + GZ_CHAIN_NCLS);
+    CK(cudaFuncSetAttribute(k_pgs_chain<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx));
+    CK(cudaFuncSetAttribute(k_pgs_chain<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx));
+  }
   return 0;
 }
 
@@ -336,6 +366,14 @@ gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params
   bool ok = cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) == cudaSuccess &&
             cudaEventCreate(&b->ev0) == cudaSuccess && cudaEventCreate(&b->ev1) == cudaSuccess;
   for (auto &e : b->evs) ok = ok && cudaEventCreate(&e) == cudaSuccess;
+  {
+    int plo = 0, phi = 0;
+    cudaDeviceGetStreamPriorityRange(&plo, &phi);
+    ok = ok && cudaEventCreateWithFlags(&b->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int q = 0; q < GZ_CHAIN_NCLS; q++)
+      ok = ok && cudaStreamCreateWithPriority(&b->stream_chain[q], cudaStreamNonBlocking, phi) == cudaSuccess &&
+           cudaEventCreateWithFlags(&b->ev_join[q], cudaEventDisableTiming) == cudaSuccess;
+  }
   if (!ok) { fail(GZCUDA_E_CUDA, "stream/event creation failed"); gzcuda_batch_destroy(b); return nullptr; }
   if (build(b, scene, params) != 0) { gzcuda_batch_destroy(b); return nullptr; }
   return b;
@@ -369,8 +407,22 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
   // at most one warp per world plus a partly filled one per bucket; CTAs beyond the step's warp count exit at once
+  // chain-mode warps (heavy worlds, first in warp order) are their own instantiation on a second, higher-priority stream
+  const bool chain_on = d.pgs_chain_min < (1 << 24);
+  if (chain_on) {
+    cudaEventRecord(b->ev_fork, b->stream);
+    for (int q = GZ_CHAIN_NCLS - 1; q >= 0; q--) {   // the large worlds first: they take longest
+      cudaStreamWaitEvent(b->stream_chain[q], b->ev_fork, 0);
+      if (d.pgs_prof) k_pgs_chain<true><<<W, 32, b->pgs_chain_smem[q], b->stream_chain[q]>>>(d, b->pgs_chain[q], q);
+      else k_pgs_chain<false><<<W, 32, b->pgs_chain_smem[q], b->stream_chain[q]>>>(d, b->pgs_chain[q], q);
+      cudaEventRecord(b->ev_join[q], b->stream_chain[q]);
+      b->last_launches++;
+    }
+  }
   if (d.pgs_prof) k_pgs<true><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
   else k_pgs<false><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+  if (chain_on)
+    for (int q = 0; q < GZ_CHAIN_NCLS; q++) cudaStreamWaitEvent(b->stream, b->ev_join[q], 0);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
   if (stage_events) cudaEventRecord(b->evs[3], b->stream);
   if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
@@ -656,14 +708,24 @@ int gzcuda_batch_get_pgs_debug(gzcuda_batch *b, int *out) {
   return 0;
 }
 
-// Developer instrumentation (GZCUDA_PGS_PROF=1 at creation): cycle sums over all k_pgs warps since
-// creation: fetch issue, wait, ring load, row update + sync, active lanes, rounds.
-int gzcuda_batch_get_pgs_profile(gzcuda_batch *b, unsigned long long out[8]) {
+// Developer instrumentation: when the sweeps of each world started and
+// ended in the last step, ns of the GPU's global timer, out[nw][2].
+int gzcuda_batch_get_pgs_timeline(gzcuda_batch *b, unsigned long long *out) {
   if (!b || !out) return fail(GZCUDA_E_INVALID, "null argument");
   int rc = gzcuda_batch_sync(b);
   if (rc) return rc;
-  CK(cudaMemcpy(out, b->d.prof, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-  CK(cudaMemset(b->d.prof, 0, 8 * sizeof(unsigned long long)));
+  CK(cudaMemcpy(out, b->d.prof + 16, 2 * (size_t)b->d.n_worlds * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// Developer instrumentation (GZCUDA_PGS_PROF=1 at creation): cycle sums over all k_pgs warps since
+// creation: fetch issue, wait, ring load, row update + sync, active lanes, rounds.
+int gzcuda_batch_get_pgs_profile(gzcuda_batch *b, unsigned long long out[16]) {
+  if (!b || !out) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  CK(cudaMemcpy(out, b->d.prof, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  CK(cudaMemset(b->d.prof, 0, 16 * sizeof(unsigned long long)));
   return 0;
 }
 

@@ -35,12 +35,13 @@ namespace gz {
 
 // per-world int scratch (B.scratch): bodies of the rows in order[] sequence, then the slot and
 // stage the scheduler gave each position
-struct WScratch { int *rb1, *rb2, *slot, *stage; };
+struct WScratch { int *rb1, *rb2, *slot, *stage, *it_pos, *it_len, *runoff; };
 __device__ inline WScratch wscratch(const DevBatch &B, int w) {
   WScratch s;
-  int *base = B.scratch + (size_t)w * 4 * B.max_row_cap;
-  s.rb1 = base; s.rb2 = base + B.max_row_cap; s.slot = base + 2 * (size_t)B.max_row_cap;
-  s.stage = base + 3 * (size_t)B.max_row_cap;
+  const size_t n = B.max_row_cap;
+  int *base = B.scratch + (size_t)w * 7 * n;
+  s.rb1 = base; s.rb2 = base + n; s.slot = base + 2 * n; s.stage = base + 3 * n;
+  s.it_pos = base + 4 * n; s.it_len = base + 5 * n; s.runoff = base + 6 * n;
   return s;
 }
 
@@ -54,15 +55,19 @@ __device__ inline WScratch wscratch(const DevBatch &B, int w) {
 #define GZ_REC_INTS 30
 #define GZ_ROUND_DOUBLES (16 * GZ_REC)
 #define GZ_FI_EMPTY (-3)
+#define GZ_FI_RUN (-4)     // fi <= GZ_FI_RUN - 1: head of a run of (GZ_FI_RUN - fi) rows (chain mode)
+#define GZ_CHAIN_K 16      // lane pairs of a chain-mode world: it has a warp to itself
+#define GZ_CHAIN_FIXED_DOUBLES (32 * 10 + 2)   // k_pgs_chain shared memory: run statistics, mbarrier (padded)
 struct RecInts {
   int fi;                 // -1 bilateral, -2 contact normal, >= 0 world-local slot index (s * k + j) of the normal row
   unsigned short b1, b2;  // world-local bodies, b2 = max_nb (the dummy accumulator slot): none
   int stage_epoch;        // (step epoch << 8) | off(r) / R
   int orig;               // world-local row index (write-back)
 };
-struct WSched { int R, k, nstage, bucket, idx, nslots, pad0, pad1; };
+struct WSched { int R, k, nstage, bucket, idx, nslots, nrun, pad1; };
 
-// ---- buckets: c = log2(k) in 0..4, rb = rung of the R ladder in 1..127 -------------------------
+// ---- buckets: (chain mode, c = log2(k) in 0..4, rb = rung of the R ladder); id = (chain * 5 + c) * GZ_NRUNG + rb;
+// for chain-mode worlds k = GZ_CHAIN_K and c is the shared-memory size class (0 .. GZ_CHAIN_NCLS - 1, ascending) ----
 #define GZ_RMAX 9984   // rung_value(GZ_NRUNG - 1); GZ_NRUNG / GZ_NBUCKET live in gz_batch.h
 __host__ __device__ inline int rung_value(int rb) {
   if (rb <= 32) return rb;
@@ -90,27 +95,44 @@ __host__ __device__ inline int rung_ceil(int R) {   // smallest rung whose value
 #define GZ_BK_SWARP0 2    // [i] first warp of the i-th bucket in heavy-first order; [GZ_NBUCKET] = total warps
 #define GZ_BK_SBUCKET 3   // [i] bucket id of the i-th bucket in heavy-first order
 __device__ inline int *bk_row(const DevBatch &B, int row) { return B.bk_tab + row * (GZ_NBUCKET + 1); }
-__device__ inline int bucket_wpw(const DevBatch &B, int bucket) { return min(16 >> (bucket / GZ_NRUNG), B.pgs_wpw_max); }
+// worlds per PGS warp.  A chain-mode world has a warp to itself: a round lasts as long as its longest
+// run, so the runs of several worlds in one warp would add up.
+__device__ inline int bucket_wpw(const DevBatch &B, int bucket) {
+  return bucket >= 5 * GZ_NRUNG ? 1 : min(16 >> ((bucket / GZ_NRUNG) % 5), B.pgs_wpw_max);
+}
 
-// where a world's records live once k_slab has run
-struct WSlab { double *base; int k, wslot, warp; };
+// where a world's records live once k_slab has run.  A chain-mode world has a warp to itself; its
+// rows live in the world's run array (B.runrec, order[] sequence) and its slab holds only the 16-byte
+// heads of its schedule items, [R][GZ_CHAIN_K] RecInts: R * 256 bytes, i.e. "width" 1 record per round.
+struct WSlab { double *base; int k, wslot, warp, width; };
+__device__ inline int bucket_width(int bucket) { return bucket >= 5 * GZ_NRUNG ? 1 : 16; }
+__device__ inline RecInts *chain_head(const WSlab &s, int local) { return reinterpret_cast<RecInts *>(s.base) + local; }
 __device__ inline WSlab wslab(const DevBatch &B, const WSched &sc) {
   const int per = bucket_wpw(B, sc.bucket);
   WSlab s;
-  s.k = sc.k; s.wslot = sc.idx % per;
+  s.k = sc.k; s.wslot = sc.idx % per; s.width = bucket_width(sc.bucket);
   const int wb = sc.idx / per;
   const int w0 = bk_row(B, GZ_BK_WARP0)[sc.bucket];
   s.warp = w0 < 0 ? -1 : w0 + wb;   // -1: the record pool was exhausted (k_slab flagged it)
-  s.base = B.prec + ((size_t)bk_row(B, GZ_BK_REC0)[sc.bucket] + (size_t)wb * sc.R * 16) * GZ_REC;
+  s.base = B.prec + ((size_t)bk_row(B, GZ_BK_REC0)[sc.bucket] + (size_t)wb * sc.R * s.width) * GZ_REC;
   return s;
 }
 __device__ inline double *slab_rec(const WSlab &s, int local) {   // local = slot * k + j
-  return s.base + ((size_t)(local / s.k) * 16 + s.wslot * s.k + (local % s.k)) * GZ_REC;
+  return s.base + ((size_t)(local / s.k) * s.width + s.wslot * s.k + (local % s.k)) * GZ_REC;
 }
 
-// One warp per world: order[] positions (closed form), rows per body, k, then the greedy modulo
-// scheduler on lane 0 (integer work only, m iterations per attempt), then the slot of every row.
-// Row::next_f receives the world-local slot index, Row::t1a the stage.
+// One warp per world: order[] positions (closed form), schedule items, k, then the greedy modulo
+// scheduler on lane 0 (integer work only), then where every row's record and lambda live.
+//
+// A schedule ITEM is one row, or - in CHAIN mode - a maximal run of consecutive rows (in order[]
+// sequence, inside one of the three segments bilateral / normals / frictions) that touch the same
+// bodies.  Chain mode is for worlds whose busiest body carries a long serial chain (a robot lying
+// on all its boxes: 80 rows on the core): k_pgs_chain (k_pgs_chain.cuh) runs an item in ONE round,
+// its rows back to back with the bodies' accumulators in registers, instead of one round per row.
+// It needs the whole world in shared memory; a world that does not fit is scheduled row by row.
+// Row::next_f = lambda index, Row::t1a = stage, Row::t2a = index in the world's run array (-1: the
+// row has its own slab slot, which is next_f), Row::t1f = slab slot | len << 20 for the first row of
+// an item of a chain-mode world (-1 otherwise).
 __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   // dynamic shared memory: cnt, last, first [max_nb] ints, then occ [sch_rcap] shorts
   extern __shared__ int sch_sh[];
@@ -121,119 +143,178 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   WorldStep &ws = B.wstep[w];
   const int m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc, nb = wi.nb;
   WSched *wsch = reinterpret_cast<WSched *>(B.wsched) + w;
-  if (m == 0 || m > 16 * GZ_RMAX) {
-    // nothing to solve: constraint accelerations are zero (free bodies still integrate)
+  bool refuse = (m == 0 || m > 16 * GZ_RMAX);
+  int *order = B.order + wi.row0;
+  Row *rows = B.row + wi.row0;
+  WScratch S = wscratch(B, w);
+  int k = 1, rb = 1, R = 1, nstage = 1, nitems = 0, nrun = 0, chain = 0, cls = 0;
+  if (!refuse) {
+    // order[]: bilateral rows in index order, contact normals in REVERSE index order, friction
+    // rows in index order (quickstep_pgs_lcp.cpp:1115-1150).  Persistent-joint rows are all
+    // bilateral and every contact has exactly (normal, fric1, fric2): positions are closed-form.
+    for (int i = lane; i < m; i += 32) {
+      int pos;
+      if (i < mj) pos = i;
+      else {
+        int c = (i - mj) / 3, f = (i - mj) % 3;
+        pos = (f == 0) ? mj + (nc - 1 - c) : mj + nc + 2 * c + (f - 1);
+      }
+      order[pos] = i;
+      S.rb1[pos] = rows[i].b1;
+      S.rb2[pos] = rows[i].b2;
+    }
+    __syncwarp();
+    // chain mode needs the whole world resident in k_pgs_chain's shared memory: accumulators, fixed
+    // part, lambda[m][2], m + 1 records, and (checked once R is known) the heads [R][GZ_CHAIN_K]
+    const int res_doubles = 12 * (max(B.max_nb, 1) + 1) + GZ_CHAIN_FIXED_DOUBLES + 2 * m + (m + 1) * GZ_REC;
+    for (int pass = 0; pass < 2; pass++) {   // pass 0 may choose chain mode; pass 1 is the fallback if it does not fit
+      for (int b = lane; b < nb; b += 32) cnt[b] = 0;
+      __syncwarp();
+      for (int pos = lane; pos < m; pos += 32) {
+        atomicAdd(&cnt[S.rb1[pos]], 1);
+        if (S.rb2[pos] >= 0) atomicAdd(&cnt[S.rb2[pos]], 1);
+      }
+      __syncwarp();
+      int maxcnt = 0;
+      for (int b = lane; b < nb; b += 32) maxcnt = max(maxcnt, cnt[b]);
+      maxcnt = __reduce_max_sync(0xffffffffu, maxcnt);
+      chain = (pass == 0 && maxcnt >= B.pgs_chain_min && res_doubles + 2 * GZ_CHAIN_K <= B.pgs_chain_doubles[GZ_CHAIN_NCLS - 1]) ? 1 : 0;
+      // ---- items
+      if (chain) {
+        __syncwarp();
+        for (int b = lane; b < nb; b += 32) cnt[b] = 0;
+        __syncwarp();
+        if (lane == 0) {
+          int pos = 0;
+          nitems = 0;
+          while (pos < m) {
+            const int x1 = S.rb1[pos], x2 = S.rb2[pos];
+            const int seg_end = pos < mj ? mj : (pos < mj + nc ? mj + nc : m);
+            int L = 1;
+            while (pos + L < seg_end && L < 2000 && S.rb1[pos + L] == x1 && S.rb2[pos + L] == x2) L++;
+            S.it_pos[nitems] = pos; S.it_len[nitems] = L;
+            cnt[x1]++;
+            if (x2 >= 0) cnt[x2]++;
+            nitems++; pos += L;
+          }
+        }
+        nitems = __shfl_sync(0xffffffffu, nitems, 0);
+        __syncwarp();
+        maxcnt = 0;
+        for (int b = lane; b < nb; b += 32) maxcnt = max(maxcnt, cnt[b]);
+        maxcnt = __reduce_max_sync(0xffffffffu, maxcnt);
+      } else {
+        nitems = m;
+      }
+      // lanes per solve: the smallest power of two that brings items/k down to the period the busiest
+      // body (or the batch-wide target period) imposes anyway; a chain-mode world has the whole warp
+      if (chain) k = GZ_CHAIN_K;
+      else {
+        const int target = max(maxcnt, B.pgs_rt);
+        k = B.pgs_kmin;
+        while (k < B.pgs_kmax && (nitems + k - 1) / k > target) k <<= 1;
+      }
+      rb = rung_ceil(max((nitems + k - 1) / k, maxcnt));
+      R = rung_value(rb);
+      bool done = false;
+      for (int attempt = 0; !done; attempt++) {
+        const bool give_up = attempt >= 24 || rb >= GZ_NRUNG || R > B.sch_rcap;
+        if (give_up && chain) break;                                                   // pass 1 will do it
+        if (give_up && nitems > min(GZ_RMAX, B.sch_rcap)) { refuse = true; break; }   // cannot happen with sane inputs
+        if (give_up) {   // always valid: the sequential sweep itself (one lane per solve)
+          k = 1; rb = rung_ceil(nitems); R = rung_value(rb); nstage = 1;
+          for (int it = lane; it < nitems; it += 32) { S.slot[it] = it; S.stage[it] = 0; }
+          done = true;
+          break;
+        }
+        for (int s = lane; s < R; s += 32) occ[s] = 0;
+        for (int b = lane; b < nb; b += 32) { last[b] = -1; first[b] = -1; }
+        __syncwarp();
+        int fail = 0, need = R, maxoff = 0;
+        if (lane == 0) {
+          for (int it = 0; it < nitems; it++) {
+            const int pos = chain ? S.it_pos[it] : it;
+            const int x1 = S.rb1[pos], x2 = S.rb2[pos];
+            int o = last[x1] + 1;
+            if (x2 >= 0) o = max(o, last[x2] + 1);
+            int s = o % R, n = 0;
+            while (occ[s] == k) {
+              o++; s++;
+              if (s == R) s = 0;
+              if (++n > R) { fail = 1; break; }
+            }
+            if (fail) break;
+            const int ln = occ[s]++;
+            S.slot[it] = s * k + ln;      // per ITEM here; expanded to rows below
+            S.stage[it] = o / R;
+            last[x1] = o;
+            if (first[x1] < 0) first[x1] = o;
+            if (x2 >= 0) { last[x2] = o; if (first[x2] < 0) first[x2] = o; }
+            maxoff = max(maxoff, o);
+          }
+          if (!fail)
+            for (int b = 0; b < nb; b++)
+              if (first[b] >= 0) need = max(need, last[b] - first[b] + 1);
+        }
+        fail = __shfl_sync(0xffffffffu, fail, 0);
+        need = __shfl_sync(0xffffffffu, need, 0);
+        maxoff = __shfl_sync(0xffffffffu, maxoff, 0);
+        if (!fail && need == R && maxoff / R < 255) { done = true; nstage = maxoff / R + 1; }
+        else { rb++; R = rung_value(rb); }   // next rung (3-6 % longer): jumping to `need` overshoots badly
+        __syncwarp();
+      }
+      if (refuse) break;
+      if (chain && done) {   // does it fit, and in which shared-memory class
+        const int need_doubles = res_doubles + 2 * R * GZ_CHAIN_K;
+        cls = 0;
+        while (cls < GZ_CHAIN_NCLS && need_doubles > B.pgs_chain_doubles[cls]) cls++;
+        if (cls < GZ_CHAIN_NCLS) break;
+      } else if (done) break;
+      chain = 0;
+    }
+  }
+  if (refuse) {
+    // nothing to solve (or a step this solver refuses): constraint accelerations are zero
     for (int b = lane; b < nb; b += 32) {
       BodyStep &bs = B.bstep[wi.body0 + b];
       for (int t = 0; t < 6; t++) { bs.caccel[t] = 0; bs.caccel_erp[t] = 0; }
     }
     if (lane == 0) {
-      WSched z; z.R = 1; z.k = 1; z.nstage = 0; z.bucket = -1; z.idx = 0; z.nslots = 0; z.pad0 = z.pad1 = 0; *wsch = z;
-      for (int k = 0; k < 4; k++) { ws.rms_dlambda[k] = 0; ws.rms_residual[k] = 0; }
+      WSched z; z.R = 1; z.k = 1; z.nstage = 0; z.bucket = -1; z.idx = 0; z.nslots = 0; z.nrun = 0; z.pad1 = 0; *wsch = z;
+      for (int q = 0; q < 4; q++) { ws.rms_dlambda[q] = 0; ws.rms_residual[q] = 0; }
       ws.num_contacts_stat = 0;
-      if (m > 16 * GZ_RMAX) ws.overflow |= 8;   // needs the large-world solver
+      if (m > 0) ws.overflow |= 8;   // needs the large-world solver
     }
     return;
   }
-  int *order = B.order + wi.row0;
-  Row *rows = B.row + wi.row0;
-  WScratch S = wscratch(B, w);
-  for (int b = lane; b < nb; b += 32) cnt[b] = 0;
+  const int nslots = R * k;
   __syncwarp();
-  // order[]: bilateral rows in index order, contact normals in REVERSE index order, friction
-  // rows in index order (quickstep_pgs_lcp.cpp:1115-1150).  Persistent-joint rows are all
-  // bilateral and every contact has exactly (normal, fric1, fric2): positions are closed-form.
-  for (int i = lane; i < m; i += 32) {
-    int pos;
-    if (i < mj) pos = i;
-    else {
-      int c = (i - mj) / 3, f = (i - mj) % 3;
-      pos = (f == 0) ? mj + (nc - 1 - c) : mj + nc + 2 * c + (f - 1);
+  // ---- rows: lambda index, stage, run membership
+  if (!chain) {
+    for (int pos = lane; pos < m; pos += 32) {
+      Row &r = rows[order[pos]];
+      r.next_f = S.slot[pos]; r.t1a = S.stage[pos]; r.t2a = -1; r.t1f = -1;
     }
-    const int x1 = rows[i].b1, x2 = rows[i].b2;
-    order[pos] = i;
-    S.rb1[pos] = x1;
-    S.rb2[pos] = x2;
-    atomicAdd(&cnt[x1], 1);
-    if (x2 >= 0) atomicAdd(&cnt[x2], 1);
-  }
-  __syncwarp();
-  int maxcnt = 0;
-  for (int b = lane; b < nb; b += 32) maxcnt = max(maxcnt, cnt[b]);
-  maxcnt = __reduce_max_sync(0xffffffffu, maxcnt);
-  // lanes per solve: the smallest power of two that brings rows/k down to the period the busiest
-  // body (or the batch-wide target period) imposes anyway
-  const int target = max(maxcnt, B.pgs_rt);
-  int k = B.pgs_kmin;
-  while (k < B.pgs_kmax && (m + k - 1) / k > target) k <<= 1;
-  int rb = rung_ceil(max((m + k - 1) / k, maxcnt));
-  int R = rung_value(rb);
-  int nstage = 1;
-  bool done = false;
-  for (int attempt = 0; !done; attempt++) {
-    const bool give_up = attempt >= 24 || rb >= GZ_NRUNG || R > B.sch_rcap;
-    if (give_up && m > min(GZ_RMAX, B.sch_rcap)) {   // cannot happen with sane inputs; refuse rather than solve wrongly
-      for (int b = lane; b < nb; b += 32) {
-        BodyStep &bs = B.bstep[wi.body0 + b];
-        for (int t = 0; t < 6; t++) { bs.caccel[t] = 0; bs.caccel_erp[t] = 0; }
+  } else {
+    // every row of a chain-mode world lives in the run array at its order[] position, which is also
+    // its lambda index; the first row of an item carries the item's head
+    nrun = m;
+    for (int it = lane; it < nitems; it += 32) {
+      const int pos = S.it_pos[it], L = S.it_len[it], slot = S.slot[it], stage = S.stage[it];
+      for (int i = 0; i < L; i++) {
+        Row &r = rows[order[pos + i]];
+        r.next_f = pos + i; r.t1a = stage; r.t2a = pos + i;
+        r.t1f = (i == 0) ? (slot | (L << 20)) : -1;
       }
-      if (lane == 0) {
-        WSched z; z.R = 1; z.k = 1; z.nstage = 0; z.bucket = -1; z.idx = 0; z.nslots = 0; z.pad0 = z.pad1 = 0; *wsch = z;
-        ws.overflow |= 8;
-      }
-      return;
     }
-    if (give_up) {   // always valid: the sequential sweep itself (one lane per solve)
-      k = 1; rb = rung_ceil(m); R = rung_value(rb); nstage = 1;
-      for (int pos = lane; pos < m; pos += 32) { S.slot[pos] = pos; S.stage[pos] = 0; }
-      break;
-    }
-    for (int s = lane; s < R; s += 32) occ[s] = 0;
-    for (int b = lane; b < nb; b += 32) { last[b] = -1; first[b] = -1; }
-    __syncwarp();
-    int fail = 0, need = R, maxoff = 0;
-    if (lane == 0) {
-      for (int pos = 0; pos < m; pos++) {
-        const int x1 = S.rb1[pos], x2 = S.rb2[pos];
-        int o = last[x1] + 1;
-        if (x2 >= 0) o = max(o, last[x2] + 1);
-        int s = o % R, n = 0;
-        while (occ[s] == k) {
-          o++; s++;
-          if (s == R) s = 0;
-          if (++n > R) { fail = 1; break; }
-        }
-        if (fail) break;
-        const int ln = occ[s]++;
-        S.slot[pos] = s * k + ln;
-        S.stage[pos] = o / R;
-        last[x1] = o;
-        if (first[x1] < 0) first[x1] = o;
-        if (x2 >= 0) { last[x2] = o; if (first[x2] < 0) first[x2] = o; }
-        maxoff = max(maxoff, o);
-      }
-      if (!fail)
-        for (int b = 0; b < nb; b++)
-          if (first[b] >= 0) need = max(need, last[b] - first[b] + 1);
-    }
-    fail = __shfl_sync(0xffffffffu, fail, 0);
-    need = __shfl_sync(0xffffffffu, need, 0);
-    maxoff = __shfl_sync(0xffffffffu, maxoff, 0);
-    if (!fail && need == R && maxoff / R < 255) { done = true; nstage = maxoff / R + 1; }
-    else { rb++; R = rung_value(rb); }   // next rung (3-6 % longer): jumping to `need` overshoots badly
-    __syncwarp();
   }
   if (lane == 0) {
     int c = 0;
     while ((1 << c) < k) c++;
-    WSched z; z.R = R; z.k = k; z.nstage = nstage; z.bucket = c * GZ_NRUNG + rb; z.nslots = R * k; z.pad0 = z.pad1 = 0;
+    WSched z; z.R = R; z.k = k; z.nstage = nstage; z.bucket = chain ? (5 + cls) * GZ_NRUNG + rb : c * GZ_NRUNG + rb;
+    z.nslots = nslots; z.nrun = nrun; z.pad1 = 0;
     z.idx = atomicAdd(&B.bk_count[z.bucket], 1);
     *wsch = z;
-  }
-  for (int pos = lane; pos < m; pos += 32) {
-    Row &r = rows[order[pos]];
-    r.next_f = S.slot[pos];
-    r.t1a = S.stage[pos];
   }
 }
 
@@ -254,12 +335,13 @@ __global__ void k_slab(DevBatch B) {
     int *swarp0 = bk_row(B, GZ_BK_SWARP0), *sbucket = bk_row(B, GZ_BK_SBUCKET);
     int warps = 0, i = 0;
     long recs = 0;
-    for (int rb = GZ_NRUNG - 1; rb >= 0; rb--)
+    for (int chain = 1; chain >= 0; chain--)   // chain-mode buckets have few, very long rounds: first
+     for (int rb = GZ_NRUNG - 1; rb >= 0; rb--)
       for (int c = 4; c >= 0; c--) {
-        const int b = c * GZ_NRUNG + rb;
+        const int b = (chain * 5 + c) * GZ_NRUNG + rb;
         warp0[b] = warps; rec0[b] = (int)recs;
         swarp0[i] = warps; sbucket[i] = b; i++;
-        long nrec = (long)nwarp[b] * rung_value(rb) * 16;
+        long nrec = (long)nwarp[b] * rung_value(rb) * bucket_width(b);
         if (recs + nrec > B.prec_cap) {   // pool exhausted: the bucket is dropped and the step flagged
           if (nwarp[b] > 0) B.wstep[0].overflow |= 16;
           nwarp[b] = 0; nrec = 0; warp0[b] = -1;
@@ -331,7 +413,9 @@ __global__ void k_rowfinish(DevBatch B) {
   const WSlab sl = wslab(B, sc);
   if (sl.warp < 0) return;
   if (i == 0) B.warp_world[sl.warp * 16 + sl.wslot] = w;
-  double *rec = slab_rec(sl, r.next_f);
+  const unsigned epoch_sh = ((unsigned)B.step_index + 1u) << 8;
+  // the row's record: its own slab slot, or its place in the world's run array (chain mode)
+  double *rec = (r.t2a < 0) ? slab_rec(sl, r.next_f) : B.runrec + ((size_t)wi.row0 + r.t2a) * GZ_REC;
   double2 *rec2 = reinterpret_cast<double2 *>(rec);
   for (int j = 0; j < 6; j++) {
     rec2[j] = make_double2(J[2 * j] * Ad, J[2 * j + 1] * Ad);
@@ -343,15 +427,26 @@ __global__ void k_rowfinish(DevBatch B) {
   if (!dequal(Ad, 0.0)) Ad2 = 1.0 / (Ad * Ad);
   rec2[14] = make_double2(r.hi, Ad2);
   RecInts ri;
-  ri.fi = (r.findex >= 0) ? B.row[wi.row0 + r.findex].next_f : r.findex;
+  ri.fi = (r.findex >= 0) ? B.row[wi.row0 + r.findex].next_f : r.findex;   // lambda index of the normal row
   ri.b1 = (unsigned short)r.b1; ri.b2 = (r.b2 >= 0) ? (unsigned short)r.b2 : (unsigned short)B.max_nb;   // none = the all-zero dummy slot
-  ri.stage_epoch = (int)((((unsigned)B.step_index + 1u) << 8) | (unsigned)r.t1a);
+  ri.stage_epoch = (int)(epoch_sh | (unsigned)r.t1a);
   ri.orig = i;
   *reinterpret_cast<RecInts *>(rec + GZ_REC_INTS) = ri;
+  if (r.t1f >= 0) {
+    // first row of a schedule item of a chain-mode world: the item's head sits in the slot the
+    // scheduler gave it.  fi = GZ_FI_RUN - len, orig = first index in the run array | friction flag << 30
+    RecInts hi;
+    hi.fi = GZ_FI_RUN - (r.t1f >> 20);
+    hi.b1 = ri.b1; hi.b2 = ri.b2;
+    hi.stage_epoch = ri.stage_epoch;
+    hi.orig = r.t2a | ((r.findex >= 0) ? (1 << 30) : 0);
+    *chain_head(sl, r.t1f & 0xFFFFF) = hi;
+  }
 }
 
 }  // namespace gz
 #include "k_pgs_sweep.cuh"
+#include "k_pgs_chain.cuh"
 namespace gz {
 
 // One thread per joint: save lambda for the next step's warm start.

@@ -23,7 +23,9 @@
 namespace gz {
 
 #define GZ_RING_D 2                 // ring stages
-#define GZ_RING_G 4                 // rounds per stage: one fetch (and one mbarrier wait) per G rounds
+#ifndef GZ_RING_G
+#define GZ_RING_G 4                 // rounds per stage (2 or 4): one fetch (and one mbarrier wait) per G rounds
+#endif
 #define GZ_STAGE_DOUBLES (GZ_RING_G * GZ_ROUND_DOUBLES)
 #define GZ_RING_DOUBLES (GZ_RING_D * GZ_STAGE_DOUBLES + 2 * GZ_RING_D)   // records + one mbarrier per stage (padded)
 
@@ -32,7 +34,7 @@ struct PgsCfg { int smem_doubles, nbp, wpw_max; };
 // the constants of one row, in registers
 struct RowRegs {
   double J[12], iM[12], rhs, adcfm, lo, hi;
-  int fi, b1, b2, stage;
+  int fi, b1, b2, stage, orig;
 };
 
 // Reads one record; a record whose epoch is not this step's is an empty slot (or a stale one in a
@@ -56,6 +58,13 @@ __device__ __forceinline__ void load_row(RowRegs &R, const double *rec, const in
   R.b1 = bb & 0xFFFFu;
   R.b2 = bb >> 16;
   R.stage = iv.z & 255;
+  R.orig = iv.w;
+}
+
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
 }
 
 // ---- mbarrier / bulk-copy wrappers (PTX ISA: mbarrier, cp.async.bulk) ---------------------------
@@ -105,16 +114,11 @@ __device__ __forceinline__ void pgs_row_in(RowIn &I, const RowRegs &R, const int
   I.nlam = lam[2 * (R.fi >= 0 ? R.fi : idx) + S];
 }
 
-template <bool STATS, bool TWO>
-__device__ __forceinline__ void pgs_row(const RowRegs &R, const RowIn &I, const bool act, const int S, const int idx,
-                                        double *cas, double *lam, const int nbp, const double smooth, const double Ad2,
-                                        const bool stat01, const bool stat2, PgsStat &st) {
-  // TWO = false: no due row of this warp has a second body in this round (warp-uniform), so the
-  // second body's half of the work is not even issued
-  double *c1 = cas + 6 * R.b1, *c2 = cas + 6 * R.b2;
-  const bool two = TWO && R.b2 < nbp;
-  const double *a1 = I.a1, *a2 = I.a2;
-  const double old_lambda = I.old_lambda, nlam = I.nlam;
+// The arithmetic of one row update given the accumulators of its bodies: returns delta, sets nl.
+template <bool TWO>
+__device__ __forceinline__ double pgs_delta(const RowRegs &R, const double *a1, const double *a2, const bool two,
+                                            const double old_lambda, const double nlam, const int S, const double smooth,
+                                            double &nl_out) {
   const int fi = R.fi;
   const double hf = fabs(R.hi * nlam);   // pyramid friction: |mu * lambda_normal|
   const double hi_act = fi >= 0 ? hf : R.hi, lo_act = fi >= 0 ? -hf : R.lo;
@@ -132,7 +136,33 @@ __device__ __forceinline__ void pgs_row(const RowRegs &R, const RowIn &I, const 
   delta = below ? dlo : (above ? dhi : delta);
   nl = below ? lo_act : (above ? hi_act : nl);
   const double sm = (1.0 - smooth) * nl + smooth * old_lambda;
-  nl = (S == 0 && fi != -1) ? sm : nl;
+  nl_out = (S == 0 && fi != -1) ? sm : nl;
+  return delta;
+}
+
+// rms_dlambda / rms_constraint_residual (quickstep_pgs_lcp.cpp:700-760,814-855): the sums
+// restart every sweep, so only the last sweep that touches a class survives.
+__device__ __forceinline__ void pgs_stat(PgsStat &st, const int fi, const bool on01, const bool on2, const double delta,
+                                         const double Ad2) {
+  const int cls = (fi == -1) ? 0 : (fi == -2 ? 1 : 2);
+  const bool on = (cls == 2) ? on2 : on01;
+  const double dd = delta * delta, e2 = dd * Ad2;
+  if (on && cls == 0) { st.acc[0] += dd; st.err[0] += e2; st.cnt[0]++; }
+  if (on && cls == 1) { st.acc[1] += dd; st.err[1] += e2; st.cnt[1]++; }
+  if (on && cls == 2) { st.acc[2] += dd; st.err[2] += e2; st.cnt[2]++; }
+}
+
+template <bool STATS, bool TWO>
+__device__ __forceinline__ void pgs_row(const RowRegs &R, const RowIn &I, const bool act, const int S, const int idx,
+                                        double *cas, double *lam, const int nbp, const double smooth, const double Ad2,
+                                        const bool stat01, const bool stat2, PgsStat &st) {
+  // TWO = false: no due row of this warp has a second body in this round (warp-uniform), so the
+  // second body's half of the work is not even issued
+  double *c1 = cas + 6 * R.b1, *c2 = cas + 6 * R.b2;
+  const bool two = TWO && R.b2 < nbp;
+  const double *a1 = I.a1, *a2 = I.a2;
+  double nl;
+  const double delta = pgs_delta<TWO>(R, a1, a2, two, I.old_lambda, I.nlam, S, smooth, nl);
   if (act) lam[2 * idx + S] = nl;
   {
     double2 *p1 = reinterpret_cast<double2 *>(c1);
@@ -152,16 +182,7 @@ __device__ __forceinline__ void pgs_row(const RowRegs &R, const RowIn &I, const 
       for (int t = 0; t < 3; t++) p2[t] = o2[t];
     }
   }
-  // rms_dlambda / rms_constraint_residual (quickstep_pgs_lcp.cpp:700-760,814-855): the sums
-  // restart every sweep, so only the last sweep that touches a class survives.
-  if (STATS) {
-    const int cls = (fi == -1) ? 0 : (fi == -2 ? 1 : 2);
-    const bool on = act && S == 0 && ((cls == 2) ? stat2 : stat01);
-    const double dd = delta * delta, e2 = dd * Ad2;
-    if (on && cls == 0) { st.acc[0] += dd; st.err[0] += e2; st.cnt[0]++; }
-    if (on && cls == 1) { st.acc[1] += dd; st.err[1] += e2; st.cnt[1]++; }
-    if (on && cls == 2) { st.acc[2] += dd; st.err[2] += e2; st.cnt[2]++; }
-  }
+  if (STATS) pgs_stat(st, R.fi, act && S == 0 && stat01, act && S == 0 && stat2, delta, Ad2);
 }
 
 template <bool PROF>
@@ -179,7 +200,8 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
     if (swarp0[mid] <= cta) lo_i = mid; else hi_i = mid - 1;
   }
   const int bucket = bk_row(B, GZ_BK_SBUCKET)[lo_i];
-  const int k = 1 << (bucket / GZ_NRUNG), LW = 2 * k, R = rung_value(bucket % GZ_NRUNG);
+  const int k = 1 << ((bucket / GZ_NRUNG) % 5), LW = 2 * k, R = rung_value(bucket % GZ_NRUNG);
+  if (bucket >= 5 * GZ_NRUNG) return;          // chain-mode worlds: k_pgs_chain (k_pgs_chain.cuh)
   const int wpw = bucket_wpw(B, bucket);
   const int wb = cta - swarp0[lo_i];
   const size_t slab_rec0 = (size_t)bk_row(B, GZ_BK_REC0)[bucket] + (size_t)wb * R * 16;
@@ -190,16 +212,30 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   WorldInfo wi;
   wi.nb = 0; wi.row0 = 0; wi.body0 = 0;
   int nstage = 0;
-  if (live) { wi = B.world[w]; nstage = reinterpret_cast<const WSched *>(B.wsched)[w].nstage; }
+  if (live) {
+    wi = B.world[w];
+    nstage = reinterpret_cast<const WSched *>(B.wsched)[w].nstage;
+  }
   const int nslots = R * k;
   // ---- carve shared memory: ca | ring + mbarriers | lambda (first come first served over world slots)
   const int ca_doubles = 12 * (nbp + 1);
   double *ca = shd + (size_t)(wslot < wpw ? wslot : 0) * ca_doubles;
   double *ring = shd + (size_t)wpw * ca_doubles;
+  // lambda[nslots][2] per world; a world whose lambdas do not fit spills to its global region
   const int lam_need = 2 * nslots;
-  const int lam_fit = (cfg.smem_doubles - (wpw * ca_doubles + GZ_RING_DOUBLES)) / (lam_need > 0 ? lam_need : 1);
-  double *lam = (wslot < lam_fit) ? shd + wpw * ca_doubles + GZ_RING_DOUBLES + (size_t)wslot * lam_need
-                                  : B.lamg + 2 * (slab_rec0 + (size_t)wslot * nslots);
+  int lam_off = wpw * ca_doubles + GZ_RING_DOUBLES, my_lam_off = -1;
+  for (int s = 0; s < wpw; s++) {
+    const int need = __shfl_sync(0xffffffffu, lam_need, s * LW);
+    const bool fits = lam_off + need <= cfg.smem_doubles;
+    if (s == wslot && fits) my_lam_off = lam_off;
+    if (fits) lam_off += need;
+  }
+  double *lam = (my_lam_off >= 0) ? shd + my_lam_off : B.lamg + 2 * (3 * (size_t)wi.row0 + 128 * (size_t)(w < 0 ? 0 : w));
+  bool live_ok = live;
+  if (live && my_lam_off < 0 && nslots > 3 * wi.row_cap + 128) {   // cannot happen with sane inputs
+    if (lw == 0) B.wstep[w].overflow |= 8;
+    live_ok = false;
+  }
   if (!live) lam = shd;
   const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring);
   const unsigned bar_s = ring_s + GZ_RING_D * GZ_STAGE_DOUBLES * 8;
@@ -207,17 +243,17 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   const unsigned epoch = ((unsigned)B.step_index + 1u) & 0xFFFFFFu;
   WSlab sl;
-  sl.base = const_cast<double *>(slab); sl.k = k; sl.wslot = wslot; sl.warp = cta;
+  sl.base = const_cast<double *>(slab); sl.k = k; sl.wslot = wslot; sl.warp = cta; sl.width = 16;
   // ---- lambda0 and the accumulators
   if (wslot < wpw)
     for (int i = lw; i < ca_doubles; i += LW) ca[i] = 0.0;
   __syncwarp();
-  if (live) {
+  if (live_ok) {
     const Row *rows = B.row + wi.row0;
     for (int i = lw; i < nslots; i += LW) {
       const RecInts *ri = reinterpret_cast<const RecInts *>(slab_rec(sl, i) + GZ_REC_INTS);
       double l0 = 0.0, l1 = 0.0;
-      if (((unsigned)ri->stage_epoch >> 8) == epoch) { const Row &r = rows[ri->orig]; l0 = r.lambda; l1 = r.lambda_erp; }
+      if (((unsigned)ri->stage_epoch >> 8) == epoch && ri->fi >= GZ_FI_EMPTY + 1) { const Row &r = rows[ri->orig]; l0 = r.lambda; l1 = r.lambda_erp; }
       lam[2 * i] = l0; lam[2 * i + 1] = l1;
     }
     // initial caccel = iMJ * lambda0 over the warm-started (persistent-joint) rows, in row index
@@ -244,7 +280,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   // ---- the sweeps
   const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
   const double smooth = B.p.smooth_contacts;
-  const bool on = live && total > 0;
+  const bool on = live_ok && total > 0;
   const int max_nstage = __reduce_max_sync(0xffffffffu, nstage);
   const int rounds = (total > 0 && max_nstage > 0) ? (total + max_nstage - 1) * R : 0;
   double *cas = ca + (size_t)6 * (nbp + 1) * S;
@@ -275,7 +311,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
     long long c0 = 0, c3 = 0;                                                                     \
     if (prof) c0 = clock64();                                                                     \
     const int sweep = period - CUR.stage;                                                         \
-    const bool act = on && (unsigned)sweep < (unsigned)(CUR.fi >= 0 ? total : (CUR.fi == GZ_FI_EMPTY ? 0 : iters)); \
+    const bool act = on && (unsigned)sweep < (unsigned)(CUR.fi >= 0 ? total : (CUR.fi >= -2 ? iters : 0)); \
     const bool st_round = (period >= iters - 1 && period < iters - 1 + max_nstage) ||             \
                           (period >= total - 1 && period < total - 1 + max_nstage);               \
     const int idx = on ? slot * k + jl : 0;                                                       \
@@ -302,6 +338,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   constexpr bool prof = PROF;
   long long pc[5] = {0, 0, 0, 0, 0};
   int slot = 0, period = 0;
+  const unsigned long long g0 = gtimer();
   const long long t0 = clock64();
   RowRegs A, Bn;
   if (ngroups > 0) {
@@ -311,10 +348,12 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
     for (int g = 0; g < ngroups; g++) {
       GZ_FETCH(g + 1);                          // into the stage group g - 1 used
       GZ_ROUND(A, Bn, g, 0, g, 1);
+#if GZ_RING_G == 4
       GZ_ROUND(Bn, A, g, 1, g, 2);
       GZ_ROUND(A, Bn, g, 2, g, 3);
+#endif
       if (g + 1 < ngroups) mbar_wait(bar_s + 8 * ((g + 1) & (GZ_RING_D - 1)), ((g + 1) / GZ_RING_D) & 1);
-      GZ_ROUND(Bn, A, g, 3, g + 1, 0);          // past the last group this reads a stale stage: never used
+      GZ_ROUND(Bn, A, g, GZ_RING_G - 1, g + 1, 0);   // past the last group this reads a stale stage: never used
     }
   }
 #undef GZ_ROUND
@@ -331,12 +370,14 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
       st.cnt[t] += __shfl_xor_sync(0xffffffffu, st.cnt[t], d);
     }
   }
-  if (live) {
+  if (live_ok) {
     // lambda back to the rows (k_lambda_save copies them to the joints), caccel to the bodies
     Row *rw = B.row + wi.row0;
     for (int i = lw; i < nslots; i += LW) {
       const RecInts *ri = reinterpret_cast<const RecInts *>(slab_rec(sl, i) + GZ_REC_INTS);
-      if (((unsigned)ri->stage_epoch >> 8) == epoch) { rw[ri->orig].lambda = lam[2 * i]; rw[ri->orig].lambda_erp = lam[2 * i + 1]; }
+      if (((unsigned)ri->stage_epoch >> 8) == epoch && ri->fi >= GZ_FI_EMPTY + 1) {
+        rw[ri->orig].lambda = lam[2 * i]; rw[ri->orig].lambda_erp = lam[2 * i + 1];
+      }
     }
     for (int i = lw; i < wi.nb; i += LW) {
       BodyStep &bs = B.bstep[wi.body0 + i];
@@ -359,6 +400,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
       ws.pad[0] = rounds; ws.pad[1] = R * 256 + k; ws.n_fric = (int)(t1 - t0);
     }
   }
+  if (live && lw == 0) { B.prof[16 + 2 * w] = g0; B.prof[16 + 2 * w + 1] = gtimer(); }
   if (prof && lane == 0) {
     for (int q = 0; q < 5; q++) atomicAdd(&B.prof[q], (unsigned long long)pc[q]);
     atomicAdd(&B.prof[5], (unsigned long long)rounds);

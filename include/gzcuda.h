@@ -116,8 +116,13 @@ int gzcuda_batch_get_counters(gzcuda_batch *b, unsigned long long out[4], int re
 int gzcuda_batch_get_pgs_debug(gzcuda_batch *b, int *out);
 /* Developer instrumentation of k_pgs (enabled by GZCUDA_PGS_PROF=1 when the batch is created):
  * cycle sums over all warps since the last call: out[0] fetch issue, [1] wait, [2] ring load,
- * [3] row update, [4] active lanes, [5] rounds. */
-int gzcuda_batch_get_pgs_profile(gzcuda_batch *b, unsigned long long out[8]);
+ * [3] row update, [4] active lanes, [5] rounds; k_pgs_chain: [8] cycles of rounds with a run item,
+ * [9] such rounds, [10] rows of the longest run of each, [11] cycles of the other rounds, [12] their
+ * count, [13] sweep cycles in total, [14] worlds. */
+int gzcuda_batch_get_pgs_profile(gzcuda_batch *b, unsigned long long out[16]);
+/* Developer instrumentation: start and end of each world's sweeps in the last
+ * step, ns of the GPU's global timer, out[nw][2]. */
+int gzcuda_batch_get_pgs_timeline(gzcuda_batch *b, unsigned long long *out);
 /* Per-stage device time of the last step call, ms: collide, assemble, pgs, integrate. */
 int gzcuda_batch_stage_ms(gzcuda_batch *b, float ms[4]);
 

@@ -18,4 +18,7 @@ print("%-40s pgs %.3f ms | rounds mean %.0f max %d | cyc/round mean %.0f | cycle
     {int(x): int((k == x).sum()) for x in np.unique(k)}, ["%.3f" % x for x in ms]), flush=True)
 if os.environ.get("GZCUDA_PGS_PROF"):
     r = max(pf[5], 1)
+    if pf[14]:
+        print("   chain: %d worlds, run rounds %.0f/world at %.0f cycles (longest run %.1f rows), other rounds %.0f/world at %.0f cycles, sweep cycles %.0f/world" % (
+            pf[14] // 20, pf[9] / pf[14], pf[8] / max(pf[9], 1), pf[10] / max(pf[9], 1), pf[12] / pf[14], pf[11] / max(pf[12], 1), pf[13] / pf[14]))
     print("   per round: fetch %.0f wait %.0f load %.0f row %.0f cycles, active lanes %.1f" % (pf[0] / r, pf[1] / r, pf[2] / r, pf[3] / r, pf[4] / r))

@@ -16,7 +16,7 @@
 // PGS schedule buckets (k_pgs.cuh): c = log2(lanes per solve) in 0..4, rung of the period ladder in 1..159
 #define GZ_NRUNG 160
 #define GZ_NBUCKET (10 * GZ_NRUNG)
-#define GZ_CHAIN_NCLS 2   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
+#define GZ_CHAIN_NCLS 4   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
 
 namespace gz {
 

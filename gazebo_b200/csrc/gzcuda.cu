@@ -328,7 +328,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   }
   // chain-mode worlds (k_pgs_chain.cuh): one world per CTA, resident in shared memory; one launch per
   // size class (ascending), so that small worlds do not take a large world's share of an SM
-  size_t csmem[GZ_CHAIN_NCLS] = {56 * 1024, 200 * 1024};
+  size_t csmem[GZ_CHAIN_NCLS] = {32 * 1024, 56 * 1024, 104 * 1024, 200 * 1024};
   if (const char *e = getenv("GZCUDA_PGS_CHAIN_KB")) {   // comma-separated, ascending
     const char *q = e;
     for (int i = 0; i < GZ_CHAIN_NCLS && *q; i++) {
@@ -371,7 +371,8 @@ gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params
     cudaDeviceGetStreamPriorityRange(&plo, &phi);
     ok = ok && cudaEventCreateWithFlags(&b->ev_fork, cudaEventDisableTiming) == cudaSuccess;
     for (int q = 0; q < GZ_CHAIN_NCLS; q++)
-      ok = ok && cudaStreamCreateWithPriority(&b->stream_chain[q], cudaStreamNonBlocking, phi) == cudaSuccess &&
+      // (greatest priority = lowest number) the larger the class, the longer its worlds run: first on the SMs
+      ok = ok && cudaStreamCreateWithPriority(&b->stream_chain[q], cudaStreamNonBlocking, std::min(plo, phi + (GZ_CHAIN_NCLS - 1 - q))) == cudaSuccess &&
            cudaEventCreateWithFlags(&b->ev_join[q], cudaEventDisableTiming) == cudaSuccess;
   }
   if (!ok) { fail(GZCUDA_E_CUDA, "stream/event creation failed"); gzcuda_batch_destroy(b); return nullptr; }

@@ -103,7 +103,8 @@ __device__ inline int bucket_wpw(const DevBatch &B, int bucket) {
 
 // where a world's records live once k_slab has run.  A chain-mode world has a warp to itself; its
 // rows live in the world's run array (B.runrec, order[] sequence) and its slab holds only the 16-byte
-// heads of its schedule items, [R][GZ_CHAIN_K] RecInts: R * 256 bytes, i.e. "width" 1 record per round.
+// heads of its schedule items, [R][GZ_CHAIN_K] RecInts: R * 256 bytes, i.e. "width" 1 record per round
+// (its bucket's rung is that of its row count m >= R, see k_schedule).
 struct WSlab { double *base; int k, wslot, warp, width; };
 __device__ inline int bucket_width(int bucket) { return bucket >= 5 * GZ_NRUNG ? 1 : 16; }
 __device__ inline RecInts *chain_head(const WSlab &s, int local) { return reinterpret_cast<RecInts *>(s.base) + local; }
@@ -114,7 +115,7 @@ __device__ inline WSlab wslab(const DevBatch &B, const WSched &sc) {
   const int wb = sc.idx / per;
   const int w0 = bk_row(B, GZ_BK_WARP0)[sc.bucket];
   s.warp = w0 < 0 ? -1 : w0 + wb;   // -1: the record pool was exhausted (k_slab flagged it)
-  s.base = B.prec + ((size_t)bk_row(B, GZ_BK_REC0)[sc.bucket] + (size_t)wb * sc.R * s.width) * GZ_REC;
+  s.base = B.prec + ((size_t)bk_row(B, GZ_BK_REC0)[sc.bucket] + (size_t)wb * rung_value(sc.bucket % GZ_NRUNG) * s.width) * GZ_REC;
   return s;
 }
 __device__ inline double *slab_rec(const WSlab &s, int local) {   // local = slot * k + j
@@ -311,7 +312,9 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   if (lane == 0) {
     int c = 0;
     while ((1 << c) < k) c++;
-    WSched z; z.R = R; z.k = k; z.nstage = nstage; z.bucket = chain ? (5 + cls) * GZ_NRUNG + rb : c * GZ_NRUNG + rb;
+    // a chain-mode world is filed under the rung of its ROW COUNT: that, not its period, is how long it
+    // runs (k_slab orders the warps longest first), and m records hold its R <= m rounds of heads
+    WSched z; z.R = R; z.k = k; z.nstage = nstage; z.bucket = chain ? (5 + cls) * GZ_NRUNG + rung_ceil(m) : c * GZ_NRUNG + rb;
     z.nslots = nslots; z.nrun = nrun; z.pad1 = 0;
     z.idx = atomicAdd(&B.bk_count[z.bucket], 1);
     *wsch = z;

@@ -147,16 +147,17 @@ __global__ void __launch_bounds__(32) k_pgs_chain(DevBatch B, PgsCfg cfg, int cl
   }
   const int bucket = bk_row(B, GZ_BK_SBUCKET)[lo_i];
   if (bucket / GZ_NRUNG != 5 + cls) return;
-  const int R = rung_value(bucket % GZ_NRUNG);
   const int wb = cta - swarp0[lo_i];
-  const int nheads = R * GZ_CHAIN_K;
-  const RecInts *heads_g = reinterpret_cast<const RecInts *>(B.prec + ((size_t)bk_row(B, GZ_BK_REC0)[bucket] + (size_t)wb * R) * GZ_REC);
+  const RecInts *heads_g = reinterpret_cast<const RecInts *>(
+      B.prec + ((size_t)bk_row(B, GZ_BK_REC0)[bucket] + (size_t)wb * rung_value(bucket % GZ_NRUNG)) * GZ_REC);
   const int jl = lane >> 1, S = lane & 1;
   const int w = B.warp_world[cta * 16];
   if (w < 0) return;
   const WorldInfo wi = B.world[w];
   const int m = B.wstep[w].m;
-  const int nstage = reinterpret_cast<const WSched *>(B.wsched)[w].nstage;
+  const WSched sc = reinterpret_cast<const WSched *>(B.wsched)[w];
+  const int nstage = sc.nstage, R = sc.R;   // (the bucket's rung is that of m, not R)
+  const int nheads = R * GZ_CHAIN_K;
   const double *runrec_g = B.runrec + (size_t)wi.row0 * GZ_REC;
   // ---- carve shared memory (k_schedule checked that it fits)
   const int ca_doubles = 12 * (nbp + 1);

@@ -403,7 +403,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
   const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16;
   k_schedule<<<W, 32, sch_smem, b->stream>>>(d);
-  k_slab<<<1, 256, 0, b->stream>>>(d);
+  k_slab<<<1 + cdiv((W + GZ_NBUCKET) * 16, GZ_SLAB_T * 8), GZ_SLAB_T, 0, b->stream>>>(d);
   k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);

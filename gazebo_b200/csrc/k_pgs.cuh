@@ -321,36 +321,82 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   }
 }
 
-// One CTA: warps and record slabs of every bucket, heaviest period first so that the longest
-// warps are the first to be scheduled on the SMs; clears the warp -> world table.
-__global__ void k_slab(DevBatch B) {
-  __shared__ int nwarp[GZ_NBUCKET];
+// Warps and record slabs of every bucket, heaviest first so that the longest warps are the first to
+// be scheduled on the SMs: chain-mode buckets by row count, then the others by period.  Block 0 does
+// the prefix over the buckets (256 threads, GZ_SLAB_IT consecutive buckets each); the other blocks
+// clear the warp -> world table.
+#define GZ_SLAB_T 256
+#define GZ_SLAB_IT ((GZ_NBUCKET + GZ_SLAB_T - 1) / GZ_SLAB_T)
+__device__ inline int slab_bucket(int i) {   // i-th bucket in heavy-first order
+  const int chain = i < 5 * GZ_NRUNG ? 1 : 0, r = i - (1 - chain) * 5 * GZ_NRUNG;
+  const int rb = GZ_NRUNG - 1 - r / 5, c = 4 - r % 5;
+  return (chain * 5 + c) * GZ_NRUNG + rb;
+}
+__global__ void __launch_bounds__(GZ_SLAB_T) k_slab(DevBatch B) {
   const int t = threadIdx.x;
-  for (int b = t; b < GZ_NBUCKET; b += blockDim.x) {
-    const int per = bucket_wpw(B, b);
-    nwarp[b] = (B.bk_count[b] + per - 1) / per;
+  if (blockIdx.x > 0) {
+    const int n = (B.n_worlds + GZ_NBUCKET) * 16;
+    for (int i = (blockIdx.x - 1) * GZ_SLAB_T + t; i < n; i += (gridDim.x - 1) * GZ_SLAB_T) B.warp_world[i] = -1;
+    return;
   }
-  const int nw_max = B.n_worlds + GZ_NBUCKET;
-  for (int i = t; i < nw_max * 16; i += blockDim.x) B.warp_world[i] = -1;
+  __shared__ int sw[GZ_SLAB_T];
+  __shared__ long long sr[GZ_SLAB_T];
+  int *warp0 = bk_row(B, GZ_BK_WARP0), *rec0 = bk_row(B, GZ_BK_REC0);
+  int *swarp0 = bk_row(B, GZ_BK_SWARP0), *sbucket = bk_row(B, GZ_BK_SBUCKET);
+  int nw[GZ_SLAB_IT];
+  long long nr[GZ_SLAB_IT];
+  int lw = 0;
+  long long lr = 0;
+#pragma unroll
+  for (int q = 0; q < GZ_SLAB_IT; q++) {
+    const int i = t * GZ_SLAB_IT + q;
+    nw[q] = 0; nr[q] = 0;
+    if (i < GZ_NBUCKET) {
+      const int b = slab_bucket(i), per = bucket_wpw(B, b);
+      nw[q] = (B.bk_count[b] + per - 1) / per;
+      nr[q] = (long long)nw[q] * rung_value(b % GZ_NRUNG) * bucket_width(b);
+    }
+    lw += nw[q]; lr += nr[q];
+  }
+  sw[t] = lw; sr[t] = lr;
   __syncthreads();
-  if (t == 0) {
-    int *warp0 = bk_row(B, GZ_BK_WARP0), *rec0 = bk_row(B, GZ_BK_REC0);
-    int *swarp0 = bk_row(B, GZ_BK_SWARP0), *sbucket = bk_row(B, GZ_BK_SBUCKET);
-    int warps = 0, i = 0;
-    long recs = 0;
-    for (int chain = 1; chain >= 0; chain--)   // chain-mode buckets have few, very long rounds: first
-     for (int rb = GZ_NRUNG - 1; rb >= 0; rb--)
-      for (int c = 4; c >= 0; c--) {
-        const int b = (chain * 5 + c) * GZ_NRUNG + rb;
+  for (int d = 1; d < GZ_SLAB_T; d <<= 1) {   // inclusive scan over the threads
+    const int aw = t >= d ? sw[t - d] : 0;
+    const long long ar = t >= d ? sr[t - d] : 0;
+    __syncthreads();
+    sw[t] += aw; sr[t] += ar;
+    __syncthreads();
+  }
+  const long long total = sr[GZ_SLAB_T - 1];
+  if (total <= B.prec_cap) {
+    int warps = sw[t] - lw;
+    long long recs = sr[t] - lr;
+#pragma unroll
+    for (int q = 0; q < GZ_SLAB_IT; q++) {
+      const int i = t * GZ_SLAB_IT + q;
+      if (i < GZ_NBUCKET) {
+        const int b = slab_bucket(i);
         warp0[b] = warps; rec0[b] = (int)recs;
-        swarp0[i] = warps; sbucket[i] = b; i++;
-        long nrec = (long)nwarp[b] * rung_value(rb) * bucket_width(b);
-        if (recs + nrec > B.prec_cap) {   // pool exhausted: the bucket is dropped and the step flagged
-          if (nwarp[b] > 0) B.wstep[0].overflow |= 16;
-          nwarp[b] = 0; nrec = 0; warp0[b] = -1;
-        }
-        warps += nwarp[b]; recs += nrec;
+        swarp0[i] = warps; sbucket[i] = b;
+        warps += nw[q]; recs += nr[q];
       }
+    }
+    if (t == GZ_SLAB_T - 1) swarp0[GZ_NBUCKET] = sw[t];
+  } else if (t == 0) {   // pool exhausted: buckets that do not fit are dropped and the step flagged
+    int warps = 0;
+    long long recs = 0;
+    for (int i = 0; i < GZ_NBUCKET; i++) {
+      const int b = slab_bucket(i), per = bucket_wpw(B, b);
+      int n = (B.bk_count[b] + per - 1) / per;
+      long long nrec = (long long)n * rung_value(b % GZ_NRUNG) * bucket_width(b);
+      warp0[b] = warps; rec0[b] = (int)recs;
+      swarp0[i] = warps; sbucket[i] = b;
+      if (recs + nrec > B.prec_cap) {
+        if (n > 0) B.wstep[0].overflow |= 16;
+        n = 0; nrec = 0; warp0[b] = -1;
+      }
+      warps += n; recs += nrec;
+    }
     swarp0[GZ_NBUCKET] = warps;
   }
 }

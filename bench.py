@@ -215,14 +215,16 @@ def run_gpu(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(nb * 6 * 8), "d2h_bytes_per_step": int(nb * 13 * 8),
                 "api": "gzcuda_batch_step_io (pinned host buffers, 1 step per call)"},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "k_pgs", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": "k_pgs + k_pgs_chain (the PGS sweeps: one k_pgs launch and the chain-mode launches beside it, "
+                                                  "timed together as one launch)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak if peak else None, "traffic": traffic, "peak_kind": peak_kind,
                      "bytes_per_launch": bytes_per_launch, "avg_launch_ms": pgs_avg_ms,
                      "share_of_step": pgs_ms / ms if ms > 0 else None,
-                     "note": "achieved = algorithmic bytes (288 B per row per sweep, SURVEY 8d) / CUDA-event time of k_pgs; "
-                             "the record slab stays in L2 across the 60 sweeps, so measured DRAM traffic (traffic, from "
-                             "profiles/) is far lower: at 4096 small worlds this kernel is bound by the latency of the "
-                             "exact-order dependent FP64 chain per body, not by HBM (DESIGN.md 4)"},
+                     "note": "achieved = algorithmic bytes (288 B per row per sweep, SURVEY 8d) / CUDA-event time of the PGS "
+                             "sweeps; the records stay in L2 (k_pgs) or in shared memory (k_pgs_chain) across the 60 sweeps, "
+                             "so measured DRAM traffic (traffic, from profiles/) is far lower: at 4096 small worlds the sweeps "
+                             "are bound by the exact-order dependent FP64 chain per body, then by shared-memory capacity "
+                             "and wavefronts, not by HBM (DESIGN.md 4)"},
         "clocks": sampler.summary(),
     }
     # CPU baseline on this box's host cores (rank 0, N=1 only), bounded sample

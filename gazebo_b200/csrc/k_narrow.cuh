@@ -138,6 +138,187 @@ __device__ inline int col_box_plane(const Geom &bx, const Geom &pl, COut &o) {
   return ret;
 }
 
+// ---- dCollideSpheres (collision_util.cpp:38-67) on two points, contact slot i ----
+__device__ inline int spheres_pp(const double *p1, double r1, const double *p2, double r2, COut &o, int i) {
+  double t[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+  double d = sqrt(t[0] * t[0] + t[1] * t[1] + t[2] * t[2]);
+  if (d > (r1 + r2)) return 0;
+  if (d <= 0) {
+    for (int k = 0; k < 3; k++) o.pos[i][k] = p1[k];
+    o.nrm[i][0] = 1; o.nrm[i][1] = 0; o.nrm[i][2] = 0;
+    o.depth[i] = r1 + r2;
+  } else {
+    double d1 = 1.0 / d;
+    for (int k = 0; k < 3; k++) o.nrm[i][k] = (p1[k] - p2[k]) * d1;
+    double kk = 0.5 * (r2 - r1 - d);
+    for (int k = 0; k < 3; k++) o.pos[i][k] = p1[k] + o.nrm[i][k] * kk;
+    o.depth[i] = r1 + r2 - d;
+  }
+  return 1;
+}
+
+// ---- dClosestLineSegmentPoints (collision_util.cpp:109-225): closest points of segments a1a2, b1b2,
+// by Voronoi features in the reference's order: vertex-vertex, edge-vertex, then edge-edge ----
+__device__ inline void closest_segment_points(const double *a1, const double *a2, const double *b1, const double *b2,
+                                              double *cp1, double *cp2) {
+  double a1a2[3], b1b2[3], a1b1[3], a1b2[3], a2b1[3], a2b2[3], n[3];
+  for (int k = 0; k < 3; k++) { a1a2[k] = a2[k] - a1[k]; b1b2[k] = b2[k] - b1[k]; a1b1[k] = b1[k] - a1[k]; }
+  const double da1 = dot3(a1a2, a1b1), db1 = dot3(b1b2, a1b1);
+  if (da1 <= 0 && db1 >= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a1[k]; cp2[k] = b1[k]; } return; }
+  for (int k = 0; k < 3; k++) a1b2[k] = b2[k] - a1[k];
+  const double da2 = dot3(a1a2, a1b2), db2 = dot3(b1b2, a1b2);
+  if (da2 <= 0 && db2 <= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a1[k]; cp2[k] = b2[k]; } return; }
+  for (int k = 0; k < 3; k++) a2b1[k] = b1[k] - a2[k];
+  const double da3 = dot3(a1a2, a2b1), db3 = dot3(b1b2, a2b1);
+  if (da3 >= 0 && db3 >= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a2[k]; cp2[k] = b1[k]; } return; }
+  for (int k = 0; k < 3; k++) a2b2[k] = b2[k] - a2[k];
+  const double da4 = dot3(a1a2, a2b2), db4 = dot3(b1b2, a2b2);
+  if (da4 >= 0 && db4 <= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a2[k]; cp2[k] = b2[k]; } return; }
+  const double la = dot3(a1a2, a1a2);
+  if (da1 >= 0 && da3 <= 0) {
+    const double kk = da1 / la;
+    for (int k = 0; k < 3; k++) n[k] = a1b1[k] - kk * a1a2[k];
+    if (dot3(b1b2, n) >= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a1[k] + kk * a1a2[k]; cp2[k] = b1[k]; } return; }
+  }
+  if (da2 >= 0 && da4 <= 0) {
+    const double kk = da2 / la;
+    for (int k = 0; k < 3; k++) n[k] = a1b2[k] - kk * a1a2[k];
+    if (dot3(b1b2, n) <= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a1[k] + kk * a1a2[k]; cp2[k] = b2[k]; } return; }
+  }
+  const double lb = dot3(b1b2, b1b2);
+  if (db1 <= 0 && db2 >= 0) {
+    const double kk = -db1 / lb;
+    for (int k = 0; k < 3; k++) n[k] = -a1b1[k] - kk * b1b2[k];
+    if (dot3(a1a2, n) >= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a1[k]; cp2[k] = b1[k] + kk * b1b2[k]; } return; }
+  }
+  if (db3 <= 0 && db4 >= 0) {
+    const double kk = -db3 / lb;
+    for (int k = 0; k < 3; k++) n[k] = -a2b1[k] - kk * b1b2[k];
+    if (dot3(a1a2, n) <= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a2[k]; cp2[k] = b1[k] + kk * b1b2[k]; } return; }
+  }
+  const double kk = dot3(a1a2, b1b2);
+  double det = la * lb - kk * kk;
+  if (det <= 0) { for (int k = 0; k < 3; k++) { cp1[k] = a1[k]; cp2[k] = b1[k]; } return; }
+  det = 1.0 / det;
+  const double alpha = (lb * da1 - kk * db1) * det;
+  const double beta = (kk * da1 - la * db1) * det;
+  for (int k = 0; k < 3; k++) { cp1[k] = a1[k] + alpha * a1a2[k]; cp2[k] = b1[k] + beta * b1b2[k]; }
+}
+
+// ---- dClosestLineBoxPoints (collision_util.cpp:247-390): closest points of the segment p1p2 and the
+// box (c, R, side): piecewise-linear root of d|D(t)|^2/dt over t in [0, 1], in box coordinates with
+// the line mirrored so that its direction is non-negative ----
+__device__ inline void closest_line_box_points(const double *p1, const double *p2, const double *c, const double *R,
+                                               const double *side, double *lret, double *bret) {
+  double tmp[3], s[3], v[3], sign[3], v2[3], h[3], tanchor[3];
+  int region[3];
+  for (int k = 0; k < 3; k++) tmp[k] = p1[k] - c[k];
+  mul1_331(s, R, tmp);
+  for (int k = 0; k < 3; k++) tmp[k] = p2[k] - p1[k];
+  mul1_331(v, R, tmp);
+  for (int i = 0; i < 3; i++) {
+    if (v[i] < 0) { s[i] = -s[i]; v[i] = -v[i]; sign[i] = -1; } else sign[i] = 1;
+  }
+  for (int i = 0; i < 3; i++) { v2[i] = v[i] * v[i]; h[i] = 0.5 * side[i]; }
+  const double tanchor_eps = 1e-307;
+  for (int i = 0; i < 3; i++) {
+    if (v[i] > tanchor_eps) {
+      if (s[i] < -h[i]) { region[i] = -1; tanchor[i] = (-h[i] - s[i]) / v[i]; }
+      else { region[i] = (s[i] > h[i]); tanchor[i] = (h[i] - s[i]) / v[i]; }
+    } else { region[i] = 0; tanchor[i] = 2; }
+  }
+  double t = 0, dd2dt = 0;
+  for (int i = 0; i < 3; i++) dd2dt -= (region[i] ? v2[i] : 0) * tanchor[i];
+  if (!(dd2dt >= 0)) {
+    bool found = false;
+    do {
+      double next_t = 1;
+      for (int i = 0; i < 3; i++)
+        if (tanchor[i] > t && tanchor[i] < 1 && tanchor[i] < next_t) next_t = tanchor[i];
+      double next_dd2dt = 0;
+      for (int i = 0; i < 3; i++) next_dd2dt += (region[i] ? v2[i] : 0) * (next_t - tanchor[i]);
+      if (next_dd2dt >= 0) {
+        const double m = (next_dd2dt - dd2dt) / (next_t - t);
+        t -= dd2dt / m;
+        found = true;
+        break;
+      }
+      for (int i = 0; i < 3; i++)
+        if (dequal(tanchor[i], next_t)) { tanchor[i] = (h[i] - s[i]) / v[i]; region[i]++; }
+      t = next_t;
+      dd2dt = next_dd2dt;
+    } while (t < 1);
+    if (!found) t = 1;
+  }
+  for (int i = 0; i < 3; i++) lret[i] = p1[i] + t * tmp[i];
+  for (int i = 0; i < 3; i++) {
+    tmp[i] = sign[i] * (s[i] + t * v[i]);
+    if (tmp[i] < -h[i]) tmp[i] = -h[i];
+    else if (tmp[i] > h[i]) tmp[i] = h[i];
+  }
+  mul0_331(s, R, tmp);
+  for (int i = 0; i < 3; i++) bret[i] = s[i] + c[i];
+}
+
+// ---- dCollideCapsuleSphere (capsule.cpp:130-162) ------------------------------
+__device__ inline int col_capsule_sphere(const Geom &c, const Geom &sp, COut &o) {
+  double alpha = c.R[2] * (sp.pos[0] - c.pos[0]) + c.R[5] * (sp.pos[1] - c.pos[1]) + c.R[8] * (sp.pos[2] - c.pos[2]);
+  const double lz2 = c.dims[1] * 0.5;
+  if (alpha > lz2) alpha = lz2;
+  if (alpha < -lz2) alpha = -lz2;
+  double p[3];
+  for (int k = 0; k < 3; k++) p[k] = c.pos[k] + alpha * c.R[3 * k + 2];
+  return spheres_pp(p, c.dims[0], sp.pos, sp.dims[0], o, 0);
+}
+
+// ---- dCollideCapsuleBox (capsule.cpp:165-205) -----------------------------------
+__device__ inline int col_capsule_box(const Geom &c, const Geom &bx, COut &o) {
+  const double clen = c.dims[1] * 0.5;
+  double p1[3], p2[3], pl[3], pb[3];
+  for (int k = 0; k < 3; k++) { p1[k] = c.pos[k] + clen * c.R[3 * k + 2]; p2[k] = c.pos[k] - clen * c.R[3 * k + 2]; }
+  closest_line_box_points(p1, p2, bx.pos, bx.R, bx.dims, pl, pb);
+  return spheres_pp(pl, c.dims[0], pb, 0.0, o, 0);
+}
+
+// ---- dCollideCapsuleCapsule (capsule.cpp:208-327): (almost) parallel axes give up to two contacts at
+// the ends of the overlap, else the closest points of the two axis segments ----
+__device__ inline int col_capsule_capsule(const Geom &c1, const Geom &c2, COut &o) {
+  const double tolerance = 1e-5;
+  const double lz1 = c1.dims[1] * 0.5, lz2 = c2.dims[1] * 0.5, r1 = c1.dims[0], r2 = c2.dims[0];
+  const double *pos1 = c1.pos, *pos2 = c2.pos;
+  double axis1[3] = {c1.R[2], c1.R[5], c1.R[8]}, axis2[3] = {c2.R[2], c2.R[5], c2.R[8]};
+  double sphere1[3], sphere2[3];
+  const double a1a2 = dot3(axis1, axis2);
+  const double det = 1.0 - a1a2 * a1a2;
+  if (det < tolerance) {
+    if (a1a2 < 0) { axis2[0] = -axis2[0]; axis2[1] = -axis2[1]; axis2[2] = -axis2[2]; }
+    double q[3];
+    for (int i = 0; i < 3; i++) q[i] = pos1[i] - pos2[i];
+    const double k = dot3(axis1, q);
+    const double a1lo = -lz1, a1hi = lz1, a2lo = -lz2 - k, a2hi = lz2 - k;
+    const double lo = (a1lo > a2lo) ? a1lo : a2lo, hi = (a1hi < a2hi) ? a1hi : a2hi;
+    if (lo <= hi) {
+      if (lo < hi) {   // Gazebo asks for 250 contacts: the two-contact branch is always allowed
+        for (int i = 0; i < 3; i++) { sphere1[i] = pos1[i] + lo * axis1[i]; sphere2[i] = pos2[i] + (lo + k) * axis2[i]; }
+        if (spheres_pp(sphere1, r1, sphere2, r2, o, 0)) {
+          for (int i = 0; i < 3; i++) { sphere1[i] = pos1[i] + hi * axis1[i]; sphere2[i] = pos2[i] + (hi + k) * axis2[i]; }
+          if (spheres_pp(sphere1, r1, sphere2, r2, o, 1)) return 2;
+        }
+      }
+      const double alpha1 = (lo + hi) * 0.5, alpha2 = alpha1 + k;
+      for (int i = 0; i < 3; i++) { sphere1[i] = pos1[i] + alpha1 * axis1[i]; sphere2[i] = pos2[i] + alpha2 * axis2[i]; }
+      return spheres_pp(sphere1, r1, sphere2, r2, o, 0);
+    }
+  }
+  double a1[3], a2[3], b1[3], b2[3];
+  for (int i = 0; i < 3; i++) {
+    a1[i] = pos1[i] + axis1[i] * lz1; a2[i] = pos1[i] - axis1[i] * lz1;
+    b1[i] = pos2[i] + axis2[i] * lz2; b2[i] = pos2[i] - axis2[i] * lz2;
+  }
+  closest_segment_points(a1, a2, b1, b2, sphere1, sphere2);
+  return spheres_pp(sphere1, r1, sphere2, r2, o, 0);
+}
+
 // ---- dCollideCapsulePlane (capsule.cpp:330-383) -----------------------------
 __device__ inline int col_capsule_plane(const Geom &c, const Geom &pl, COut &o) {
   const double *pp = pl.dims;

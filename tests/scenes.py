@@ -82,6 +82,45 @@ def stack():
     return sb.finish(), S.default_params(), None
 
 
+def capsules():
+    """capsule-{sphere, box, capsule, plane}: a tight heap of capsules, spheres and boxes dropped into
+    a static four-box pen, two PARALLEL capsules lying on each other (the two-contact branch of
+    capsule.cpp:232-283) and a capsule falling across a static box."""
+    sb = S.SceneBuilder()
+    rng = np.random.Generator(np.random.PCG64(2024))
+    sb.begin_world()
+    sb.add_ground_plane()
+    pen = sb.new_space()
+    for dx, dy, sx, sy in ((0.75, 0, 0.1, 1.6), (-0.75, 0, 0.1, 1.6), (0, 0.75, 1.4, 0.1), (0, -0.75, 1.4, 0.1)):
+        sb.add_geom(S.GEOM_BOX, (sx, sy, 0.8), pen, pos=(dx, dy, 0.4))
+    kinds = [S.GEOM_CAPSULE, S.GEOM_SPHERE, S.GEOM_CAPSULE, S.GEOM_BOX]
+    n = 0
+    for iz in range(3):
+        for iy in range(3):
+            for ix in range(3):
+                kind = kinds[n % 4]
+                n += 1
+                pos = [0.4 * (ix - 1) + rng.uniform(-0.03, 0.03), 0.4 * (iy - 1) + rng.uniform(-0.03, 0.03), 0.35 + 0.5 * iz]
+                if kind == S.GEOM_CAPSULE:
+                    b = sb.add_body(pos, S.q_random(rng), mass=0.8, inertia=S.cylinder_inertia(0.8, 0.08, 0.3))
+                    sb.add_geom(kind, (0.08, 0.3), sb.new_space(), body=b)
+                elif kind == S.GEOM_SPHERE:
+                    b = sb.add_body(pos, mass=0.5, inertia=S.sphere_inertia(0.5, 0.15))
+                    sb.add_geom(kind, (0.15,), sb.new_space(), body=b)
+                else:
+                    b = sb.add_body(pos, S.q_random(rng), mass=1.0, inertia=S.box_inertia(1.0, 0.25, 0.2, 0.15))
+                    sb.add_geom(kind, (0.25, 0.2, 0.15), sb.new_space(), body=b)
+    lie = S.q_from_axis_angle([0, 1, 0], math.pi / 2)          # axis along x
+    for i, (y, z) in enumerate(((3.0, 0.1), (3.0, 0.32), (3.02, 0.56))):
+        b = sb.add_body([2.0 + 0.1 * i, y, z], lie, mass=1.0, inertia=S.cylinder_inertia(1.0, 0.1, 0.6))
+        sb.add_geom(S.GEOM_CAPSULE, (0.1, 0.6), sb.new_space(), body=b)
+    sb.add_geom(S.GEOM_BOX, (0.4, 0.4, 0.4), sb.new_space(), pos=(-3, 0, 0.2))          # static box
+    b = sb.add_body([-3.0, 0.1, 0.7], S.q_from_rpy(0.2, 1.3, 0.4), mass=1.0, inertia=S.cylinder_inertia(1.0, 0.1, 0.8))
+    sb.add_geom(S.GEOM_CAPSULE, (0.1, 0.8), sb.new_space(), body=b)
+    sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 GOLDEN = {
     "box_drop": (box_drop, 1500),
     "tilted_box": (tilted_box, 600),
@@ -90,4 +129,5 @@ GOLDEN = {
     "revolve4": (revolve4, 400),
     "boxes30": (boxes30, 500),
     "stack": (stack, 1500),
+    "capsules": (capsules, 500),
 }

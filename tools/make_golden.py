@@ -13,6 +13,8 @@ from oracle.refharness import RefBatch
 out = os.path.join(ROOT, "tests", "golden")
 os.makedirs(out, exist_ok=True)
 for name, (builder, steps) in scenes.GOLDEN.items():
+    if os.environ.get('ONLY') and name != os.environ['ONLY']:
+        continue
     sc, p, pd = builder()
     r = RefBatch(sc, p, mode=1)
     if pd is not None:

@@ -144,8 +144,13 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       Joint &J = hj[j];
       memset(&J, 0, sizeof(J));
       J.type = sc->joint_type[j];
-      if (J.type != GZ_JOINT_HINGE && J.type != GZ_JOINT_FIXED)
-        return fail(GZCUDA_E_INVALID, "joint type not supported (hinge and fixed are)");
+      if (J.type < GZ_JOINT_HINGE || J.type > GZ_JOINT_UNIVERSAL)
+        return fail(GZCUDA_E_INVALID, "unknown joint type");
+      if (J.type == GZ_JOINT_UNIVERSAL) {
+        const double *P = sc->joint_param + GZ_JP_COUNT * j;
+        if (P[GZ_JP_FMAX] > 0 || std::isfinite(P[GZ_JP_LOSTOP]) || std::isfinite(P[GZ_JP_HISTOP]))
+          return fail(GZCUDA_E_INVALID, "universal joint limits and motors are not supported");
+      }
       const int nbw = sc->body_off[w + 1] - sc->body_off[w];
       if (sc->joint_body1[j] < 0 || sc->joint_body1[j] >= nbw || sc->joint_body2[j] >= nbw)
         return fail(GZCUDA_E_INVALID, "joint body index out of range");

@@ -35,6 +35,21 @@ __device__ inline double hinge_angle(const DevBatch &B, const Joint &j) {
   return -theta;
 }
 
+// dJointGetSliderPosition (slider.cpp:40-84); anchor1 holds dxJointSlider::offset
+__device__ inline double slider_position(const DevBatch &B, const Joint &j) {
+  const Body &b1 = B.body[j.b1];
+  double ax1[3], q[3];
+  mul0_331(ax1, b1.R, j.axis1);
+  if (j.b2 >= 0) {
+    const Body &b2 = B.body[j.b2];
+    mul0_331(q, b2.R, j.anchor1);
+    for (int i = 0; i < 3; i++) q[i] = b1.pos[i] - q[i] - b2.pos[i];
+  } else {
+    for (int i = 0; i < 3; i++) q[i] = b1.pos[i] - j.anchor1[i];
+  }
+  return dot3(ax1, q);
+}
+
 // One thread per body: adds the PD torque of every hinge touching the body, in joint order
 // (the order dBodyAddTorque calls arrive in when the host loops over joints).
 __global__ void k_control(DevBatch B) {
@@ -184,6 +199,20 @@ __global__ void k_info1(DevBatch B) {
           }
         } else if (j.type == GZ_JOINT_FIXED) {
           m = 6;
+        } else if (j.type == GZ_JOINT_BALL) {
+          m = 3;
+        } else if (j.type == GZ_JOINT_UNIVERSAL) {
+          m = 4;   // limits and motors of the two axes are not supported (gzcuda_batch_create checks)
+        } else if (j.type == GZ_JOINT_SLIDER) {
+          // dxJointSlider::getInfo1 (slider.cpp:118-148)
+          m = (j.param[GZ_JP_FMAX] > 0) ? 6 : 5;
+          const double lo = j.param[GZ_JP_LOSTOP], hi = j.param[GZ_JP_HISTOP];
+          j.limit = 0;
+          if ((lo > -GZ_INF || hi < GZ_INF) && lo <= hi) {
+            const double pos = slider_position(B, j);
+            if (pos <= lo) { j.limit = 1; j.limit_err = pos - lo; m = 6; }
+            else if (pos >= hi) { j.limit = 2; j.limit_err = pos - hi; m = 6; }
+          }
         }
       }
       j.m = m;

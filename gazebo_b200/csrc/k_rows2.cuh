@@ -11,15 +11,24 @@ __device__ inline void row_init(Row &r, int lb1, int lb2, double cfm, double cvm
   r.b1 = lb1; r.b2 = lb2; r.src = src;
 }
 
-// dxJointLimitMotor::addLimot, rotational case (joint.cpp:573-750).  Returns 1 if a row was written.
-__device__ inline int add_limot_rot(DevBatch &B, Joint &j, Row &r, const double *ax1, double fps) {
+// dxJointLimitMotor::addLimot (joint.cpp:573-750), rotational (hinge) or linear (slider, with the
+// linear torque decoupling vector ltd when the joint has two bodies).  Returns 1 if a row was written.
+__device__ inline int add_limot(DevBatch &B, Joint &j, Row &r, const double *ax1, double fps, bool rotational) {
   const double fmax = j.param[GZ_JP_FMAX], vel = j.param[GZ_JP_VEL];
   const double lostop = j.param[GZ_JP_LOSTOP], histop = j.param[GZ_JP_HISTOP];
   int powered = fmax > 0;
   const int limit = j.limit;
   if (!(powered || limit)) return 0;
-  for (int k = 0; k < 3; k++) r.J[3 + k] = ax1[k];
-  if (j.b2 >= 0) for (int k = 0; k < 3; k++) r.J[9 + k] = -ax1[k];
+  const int o = rotational ? 3 : 0;
+  for (int k = 0; k < 3; k++) r.J[o + k] = ax1[k];
+  if (j.b2 >= 0) for (int k = 0; k < 3; k++) r.J[6 + o + k] = -ax1[k];
+  double ltd[3] = {0, 0, 0};
+  if (!rotational && j.b2 >= 0) {
+    double c[3];
+    for (int k = 0; k < 3; k++) c[k] = 0.5 * (B.body[j.b2].pos[k] - B.body[j.b1].pos[k]);
+    cross3(ltd, c, ax1);
+    for (int k = 0; k < 3; k++) { r.J[3 + k] = ltd[k]; r.J[9 + k] = ltd[k]; }
+  }
   if (limit && dequal(lostop, histop)) powered = 0;
   if (powered) {
     r.cfm = j.param[GZ_JP_NORMAL_CFM];
@@ -33,10 +42,14 @@ __device__ inline int add_limot_rot(DevBatch &B, Joint &j, Row &r, const double 
       // their stops on one body would make the summation order matter; atomics keep it
       // race-free (order then differs from the reference in the last bit only).
       Body &b1 = B.body[j.b1];
-      atomicAdd(&b1.tacc[0], -fm * ax1[0]); atomicAdd(&b1.tacc[1], -fm * ax1[1]); atomicAdd(&b1.tacc[2], -fm * ax1[2]);
+      double *acc1 = rotational ? b1.tacc : b1.facc;
+      atomicAdd(&acc1[0], -fm * ax1[0]); atomicAdd(&acc1[1], -fm * ax1[1]); atomicAdd(&acc1[2], -fm * ax1[2]);
       if (j.b2 >= 0) {
         Body &b2 = B.body[j.b2];
-        atomicAdd(&b2.tacc[0], fm * ax1[0]); atomicAdd(&b2.tacc[1], fm * ax1[1]); atomicAdd(&b2.tacc[2], fm * ax1[2]);
+        double *acc2 = rotational ? b2.tacc : b2.facc;
+        atomicAdd(&acc2[0], fm * ax1[0]); atomicAdd(&acc2[1], fm * ax1[1]); atomicAdd(&acc2[2], fm * ax1[2]);
+        if (!rotational)
+          for (int k = 0; k < 3; k++) { atomicAdd(&b1.tacc[k], -fm * ltd[k]); atomicAdd(&b2.tacc[k], -fm * ltd[k]); }
       }
     }
   }
@@ -49,8 +62,8 @@ __device__ inline int add_limot_rot(DevBatch &B, Joint &j, Row &r, const double 
       if (limit == 1) { r.lo = 0; r.hi = GZ_INF; } else { r.lo = -GZ_INF; r.hi = 0; }
       const double bounce = j.param[GZ_JP_BOUNCE];
       if (bounce > 0) {
-        double vvel = dot3(B.body[j.b1].avel, ax1);
-        if (j.b2 >= 0) vvel -= dot3(B.body[j.b2].avel, ax1);
+        double vvel = dot3(rotational ? B.body[j.b1].avel : B.body[j.b1].lvel, ax1);
+        if (j.b2 >= 0) vvel -= dot3(rotational ? B.body[j.b2].avel : B.body[j.b2].lvel, ax1);
         if (limit == 1) {
           if (vel < 0) { double newc = -bounce * vvel; if (newc > r.c) r.c = newc; }
         } else {
@@ -60,6 +73,40 @@ __device__ inline int add_limot_rot(DevBatch &B, Joint &j, Row &r, const double 
     }
   }
   return 1;
+}
+
+// setBall (joint.cpp:93-134): rows 0..2 keep the anchor points together; k = fps * erp
+__device__ inline void set_ball(Row *rows, const Body &b1, const Body *b2, const Joint &j, double k) {
+  double a1[3], a2[3];
+  rows[0].J[0] = 1; rows[1].J[1] = 1; rows[2].J[2] = 1;
+  mul0_331(a1, b1.R, j.anchor1);
+  // dSetCrossMatrixMinus(J1a, a1)
+  rows[0].J[3 + 1] = a1[2];  rows[0].J[3 + 2] = -a1[1];
+  rows[1].J[3 + 0] = -a1[2]; rows[1].J[3 + 2] = a1[0];
+  rows[2].J[3 + 0] = a1[1];  rows[2].J[3 + 1] = -a1[0];
+  if (b2) {
+    rows[0].J[6] = -1; rows[1].J[7] = -1; rows[2].J[8] = -1;
+    mul0_331(a2, b2->R, j.anchor2);
+    // dSetCrossMatrixPlus(J2a, a2)
+    rows[0].J[9 + 1] = -a2[2]; rows[0].J[9 + 2] = a2[1];
+    rows[1].J[9 + 0] = a2[2];  rows[1].J[9 + 2] = -a2[0];
+    rows[2].J[9 + 0] = -a2[1]; rows[2].J[9 + 1] = a2[0];
+    for (int i = 0; i < 3; i++) rows[i].c = k * (a2[i] + b2->pos[i] - a1[i] - b1.pos[i]);
+  } else {
+    for (int i = 0; i < 3; i++) rows[i].c = k * (j.anchor2[i] - a1[i] - b1.pos[i]);
+  }
+}
+
+// setFixedOrientation (joint.cpp:212-265) on rows[0..2]; k = fps * erp
+__device__ inline void set_fixed_orientation(Row *rows, const Body &b1, const Body *b2, const Joint &j, double k) {
+  rows[0].J[3] = 1; rows[1].J[4] = 1; rows[2].J[5] = 1;
+  if (b2) { rows[0].J[9] = -1; rows[1].J[10] = -1; rows[2].J[11] = -1; }
+  double qerr[4], e[3];
+  if (b2) { double qq[4]; qmul1(qq, b1.q, b2->q); qmul2(qerr, qq, j.qrel); }
+  else qmul3(qerr, b1.q, j.qrel);
+  if (qerr[0] < 0) { qerr[1] = -qerr[1]; qerr[2] = -qerr[2]; qerr[3] = -qerr[3]; }
+  mul0_331(e, b1.R, qerr + 1);
+  rows[0].c = 2 * k * e[0]; rows[1].c = 2 * k * e[1]; rows[2].c = 2 * k * e[2];
 }
 
 // One thread per persistent joint.
@@ -79,26 +126,8 @@ __global__ void k_rows_joint(DevBatch B) {
   for (int r = 0; r < j.m; r++) row_init(rows[r], lb1, lb2, B.p.cfm, B.p.contact_max_correcting_vel, ji);
   if (j.type == GZ_JOINT_HINGE) {
     if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 5; r++) rows[r].cfm = j.param[GZ_JP_CFM];
-    // setBall (joint.cpp:93-134)
-    double a1[3], a2[3];
-    rows[0].J[0] = 1; rows[1].J[1] = 1; rows[2].J[2] = 1;
-    mul0_331(a1, b1.R, j.anchor1);
-    // dSetCrossMatrixMinus(J1a, a1)
-    rows[0].J[3 + 1] = a1[2];  rows[0].J[3 + 2] = -a1[1];
-    rows[1].J[3 + 0] = -a1[2]; rows[1].J[3 + 2] = a1[0];
-    rows[2].J[3 + 0] = a1[1];  rows[2].J[3 + 1] = -a1[0];
     const double k = fps * erp;
-    if (b2) {
-      rows[0].J[6] = -1; rows[1].J[7] = -1; rows[2].J[8] = -1;
-      mul0_331(a2, b2->R, j.anchor2);
-      // dSetCrossMatrixPlus(J2a, a2)
-      rows[0].J[9 + 1] = -a2[2]; rows[0].J[9 + 2] = a2[1];
-      rows[1].J[9 + 0] = a2[2];  rows[1].J[9 + 2] = -a2[0];
-      rows[2].J[9 + 0] = -a2[1]; rows[2].J[9 + 1] = a2[0];
-      for (int i = 0; i < 3; i++) rows[i].c = k * (a2[i] + b2->pos[i] - a1[i] - b1.pos[i]);
-    } else {
-      for (int i = 0; i < 3; i++) rows[i].c = k * (j.anchor2[i] - a1[i] - b1.pos[i]);
-    }
+    set_ball(rows, b1, b2, j, k);
     double ax1[3], p[3], q[3];
     mul0_331(ax1, b1.R, j.axis1);
     plane_space(ax1, p, q);
@@ -110,19 +139,61 @@ __global__ void k_rows_joint(DevBatch B) {
     cross3(bb, ax1, ax2);
     rows[3].c = k * dot3(bb, p);
     rows[4].c = k * dot3(bb, q);
-    if (j.m == 6) add_limot_rot(B, j, rows[5], ax1, fps);
+    if (j.m == 6) add_limot(B, j, rows[5], ax1, fps, true);
+  } else if (j.type == GZ_JOINT_BALL || j.type == GZ_JOINT_UNIVERSAL) {
+    // dxJointBall::getInfo2 (ball.cpp:56-69), dxJointUniversal::getInfo2 (universal.cpp:306-372; without
+    // limits and motors): setBall, then for the universal joint one row that keeps the axes perpendicular
+    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < j.m; r++) rows[r].cfm = j.param[GZ_JP_CFM];
+    set_ball(rows, b1, b2, j, fps * erp);
+    if (j.type == GZ_JOINT_UNIVERSAL) {
+      double ax1[3], ax2[3], t[3], p[3];
+      mul0_331(ax1, b1.R, j.axis1);
+      if (b2) mul0_331(ax2, b2->R, j.axis2);
+      else { ax2[0] = j.axis2[0]; ax2[1] = j.axis2[1]; ax2[2] = j.axis2[2]; }
+      const double k = dot3(ax1, ax2);
+      for (int i = 0; i < 3; i++) t[i] = ax2[i] - k * ax1[i];
+      cross3(p, ax1, t);
+      safe_normalize3(p);
+      for (int i = 0; i < 3; i++) rows[3].J[3 + i] = p[i];
+      if (b2) for (int i = 0; i < 3; i++) rows[3].J[9 + i] = -p[i];
+      rows[3].c = fps * erp * -k;
+    }
+  } else if (j.type == GZ_JOINT_SLIDER) {
+    // dxJointSlider::getInfo2 (slider.cpp:151-238); anchor1 holds dxJointSlider::offset
+    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 5; r++) rows[r].cfm = j.param[GZ_JP_CFM];
+    double c[3] = {0, 0, 0};
+    if (b2) for (int i = 0; i < 3; i++) c[i] = b2->pos[i] - b1.pos[i];
+    set_fixed_orientation(rows, b1, b2, j, fps * erp);   // rows 0..2
+    double ax1[3], p[3], q[3];
+    mul0_331(ax1, b1.R, j.axis1);
+    plane_space(ax1, p, q);
+    if (b2) {
+      double t[3];
+      cross3(t, c, p);
+      for (int i = 0; i < 3; i++) { t[i] *= 0.5; rows[3].J[3 + i] = t[i]; rows[3].J[9 + i] = t[i]; }
+      cross3(t, c, q);
+      for (int i = 0; i < 3; i++) { t[i] *= 0.5; rows[4].J[3 + i] = t[i]; rows[4].J[9 + i] = t[i]; }
+      for (int i = 0; i < 3; i++) { rows[3].J[6 + i] = -p[i]; rows[4].J[6 + i] = -q[i]; }
+    }
+    for (int i = 0; i < 3; i++) { rows[3].J[i] = p[i]; rows[4].J[i] = q[i]; }
+    const double k = fps * erp;
+    if (b2) {
+      double ofs[3];
+      mul0_331(ofs, b2->R, j.anchor1);
+      for (int i = 0; i < 3; i++) c[i] += ofs[i];
+      rows[3].c = k * dot3(p, c);
+      rows[4].c = k * dot3(q, c);
+    } else {
+      double ofs[3];
+      for (int i = 0; i < 3; i++) ofs[i] = j.anchor1[i] - b1.pos[i];
+      rows[3].c = k * dot3(p, ofs);
+      rows[4].c = k * dot3(q, ofs);
+    }
+    if (j.m == 6) add_limot(B, j, rows[5], ax1, fps, false);
   } else if (j.type == GZ_JOINT_FIXED) {
     if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 6; r++) rows[r].cfm = j.param[GZ_JP_CFM];
-    // setFixedOrientation(rows 3..5) (joint.cpp:212-265)
-    rows[3].J[3] = 1; rows[4].J[4] = 1; rows[5].J[5] = 1;
-    if (b2) { rows[3].J[9] = -1; rows[4].J[10] = -1; rows[5].J[11] = -1; }
-    double qerr[4], e[3];
-    if (b2) { double qq[4]; qmul1(qq, b1.q, b2->q); qmul2(qerr, qq, j.qrel); }
-    else qmul3(qerr, b1.q, j.qrel);
-    if (qerr[0] < 0) { qerr[1] = -qerr[1]; qerr[2] = -qerr[2]; qerr[3] = -qerr[3]; }
-    mul0_331(e, b1.R, qerr + 1);
     const double k = fps * erp;
-    rows[3].c = 2 * k * e[0]; rows[4].c = 2 * k * e[1]; rows[5].c = 2 * k * e[2];
+    set_fixed_orientation(rows + 3, b1, b2, j, k);
     // position rows (fixed.cpp:82-109); anchor1 holds dxJointFixed::offset
     rows[0].J[0] = 1; rows[1].J[1] = 1; rows[2].J[2] = 1;
     double ofs[3];

@@ -272,6 +272,58 @@ class SceneBuilder:
         self._push_joint(JOINT_FIXED, b1, b2, ofs, z, z, z, qrel, self.joint_params(**params))
         return self._nj - 1 - self._w_j0
 
+    def add_ball(self, b1, b2, anchor, **params):
+        """Ball-and-socket (dxJointBall); anchor in world coordinates at the current body poses."""
+        p1, q1 = self._body_pose(b1)
+        anchor = np.asarray(anchor, float)
+        a1 = q_to_R(q1).T @ (anchor - p1)
+        if b2 >= 0:
+            p2, q2 = self._body_pose(b2)
+            a2 = q_to_R(q2).T @ (anchor - p2)
+        else:
+            a2 = anchor
+        z = np.zeros(3)
+        self._push_joint(JOINT_BALL, b1, b2, a1, a2, z, z, (1, 0, 0, 0), self.joint_params(**params))
+        return self._nj - 1 - self._w_j0
+
+    def add_universal(self, b1, b2, anchor, axis1, axis2, **params):
+        """Universal joint (dxJointUniversal): axis1 is fixed in body 1, axis2 in body 2 (or the world);
+        both in world coordinates at the current poses.  Joint limits and motors are not supported."""
+        p1, q1 = self._body_pose(b1)
+        R1 = q_to_R(q1)
+        anchor = np.asarray(anchor, float)
+        axis1 = np.asarray(axis1, float) / np.linalg.norm(axis1)
+        axis2 = np.asarray(axis2, float) / np.linalg.norm(axis2)
+        a1 = R1.T @ (anchor - p1)
+        ax1 = R1.T @ axis1
+        if b2 >= 0:
+            p2, q2 = self._body_pose(b2)
+            R2 = q_to_R(q2)
+            a2 = R2.T @ (anchor - p2)
+            ax2 = R2.T @ axis2
+        else:
+            a2, ax2 = anchor, axis2
+        self._push_joint(JOINT_UNIVERSAL, b1, b2, a1, a2, ax1, ax2, (1, 0, 0, 0), self.joint_params(**params))
+        return self._nj - 1 - self._w_j0
+
+    def add_slider(self, b1, b2, axis, **params):
+        """Slider / prismatic joint (dxJointSlider): axis in world coordinates at the current poses; anchor1
+        holds dxJointSlider::offset (slider.cpp computeOffset), qrel the initial relative rotation."""
+        p1, q1 = self._body_pose(b1)
+        R1 = q_to_R(q1)
+        axis = np.asarray(axis, float)
+        axis = axis / np.linalg.norm(axis)
+        ax1 = R1.T @ axis
+        if b2 >= 0:
+            p2, q2 = self._body_pose(b2)
+            ofs = q_to_R(q2).T @ (p1 - p2)
+            qrel = q_mul(q_conj(q1), q2)
+        else:
+            ofs, qrel = p1, q_conj(q1)
+        z = np.zeros(3)
+        self._push_joint(JOINT_SLIDER, b1, b2, ofs, z, ax1, z, qrel, self.joint_params(**params))
+        return self._nj - 1 - self._w_j0
+
     def _push_joint(self, t, b1, b2, a1, a2, ax1, ax2, qrel, param):
         self.j["type"].append(t)
         self.j["b1"].append(int(b1))

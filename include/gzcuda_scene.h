@@ -116,7 +116,7 @@ typedef struct gz_scene {
   const int    *joint_type;    /* [nj] GZ_JOINT_* */
   const int    *joint_body1;   /* [nj] world-local, never -1 */
   const int    *joint_body2;   /* [nj] world-local or -1 (attached to the world) */
-  const double *joint_anchor1; /* [nj][3] body-1 frame (hinge/ball anchor1; fixed: offset) */
+  const double *joint_anchor1; /* [nj][3] body-1 frame (hinge/ball/universal anchor1; fixed, slider: offset) */
   const double *joint_anchor2; /* [nj][3] body-2 frame (or world frame when body2 = -1) */
   const double *joint_axis1;   /* [nj][3] body-1 frame */
   const double *joint_axis2;   /* [nj][3] body-2 frame (or world) */

@@ -503,6 +503,43 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
         dxJointFixed *fj = (dxJointFixed *)jt;
         for (int k = 0; k < 3; k++) fj->offset[k] = sc->joint_anchor1[3 * j + k];
         for (int k = 0; k < 4; k++) fj->qrel[k] = sc->joint_qrel[4 * j + k];
+      } else if (sc->joint_type[j] == GZ_JOINT_BALL) {
+        jt = dJointCreateBall(w->world, 0);
+        dJointAttach(jt, b1, b2);
+        dxJointBall *bj = (dxJointBall *)jt;
+        for (int k = 0; k < 3; k++) {
+          bj->anchor1[k] = sc->joint_anchor1[3 * j + k];
+          bj->anchor2[k] = sc->joint_anchor2[3 * j + k];
+        }
+      } else if (sc->joint_type[j] == GZ_JOINT_UNIVERSAL) {
+        jt = dJointCreateUniversal(w->world, 0);
+        dJointAttach(jt, b1, b2);
+        dxJointUniversal *uj = (dxJointUniversal *)jt;
+        for (int k = 0; k < 3; k++) {
+          uj->anchor1[k] = sc->joint_anchor1[3 * j + k];
+          uj->anchor2[k] = sc->joint_anchor2[3 * j + k];
+          uj->axis1[k] = sc->joint_axis1[3 * j + k];
+          uj->axis2[k] = sc->joint_axis2[3 * j + k];
+        }
+        uj->computeInitialRelativeRotations();   // qrel1 / qrel2: joint angles only (limits are not used)
+      } else if (sc->joint_type[j] == GZ_JOINT_SLIDER) {
+        jt = dJointCreateSlider(w->world, 0);
+        dJointAttach(jt, b1, b2);
+        dxJointSlider *sj = (dxJointSlider *)jt;
+        for (int k = 0; k < 3; k++) {
+          sj->axis1[k] = sc->joint_axis1[3 * j + k];
+          sj->offset[k] = sc->joint_anchor1[3 * j + k];
+        }
+        for (int k = 0; k < 4; k++) sj->qrel[k] = sc->joint_qrel[4 * j + k];
+        sj->limot.lostop = P[GZ_JP_LOSTOP];
+        sj->limot.histop = P[GZ_JP_HISTOP];
+        sj->limot.vel = P[GZ_JP_VEL];
+        sj->limot.fmax = P[GZ_JP_FMAX];
+        sj->limot.fudge_factor = P[GZ_JP_FUDGE];
+        sj->limot.bounce = P[GZ_JP_BOUNCE];
+        sj->limot.normal_cfm = P[GZ_JP_NORMAL_CFM];
+        sj->limot.stop_erp = P[GZ_JP_STOP_ERP];
+        sj->limot.stop_cfm = P[GZ_JP_STOP_CFM];
       } else {
         return nullptr;
       }

@@ -121,6 +121,46 @@ def capsules():
     return sb.finish(), S.default_params(), None
 
 
+def joints():
+    """ball / universal / slider joints: a ball-jointed pendulum chain hanging from the world, a
+    universal-jointed two-link arm, a slider on the world with limits and bounce, a powered slider between
+    two free bodies (linear torque decoupling), all above the plane so that links also hit the ground."""
+    sb = S.SceneBuilder()
+    rng = np.random.Generator(np.random.PCG64(99))
+    sb.begin_world()
+    sb.add_ground_plane()
+    sp = sb.new_space()
+    # ball chain hanging from the world
+    prev = -1
+    for i in range(4):
+        b = sb.add_body([0.3 * i + 0.15, 0.0, 1.5], mass=0.5, inertia=S.box_inertia(0.5, 0.28, 0.06, 0.06))
+        sb.add_geom(S.GEOM_BOX, (0.28, 0.06, 0.06), sp, body=b)
+        sb.add_ball(b, prev, [0.3 * i, 0.0, 1.5])
+        prev = b
+    # universal arm: base link on a world universal joint, second link on a body-body universal joint
+    sp2 = sb.new_space()
+    u1 = sb.add_body([0.0, 2.0, 1.0], mass=1.0, inertia=S.box_inertia(1.0, 0.1, 0.1, 0.4))
+    sb.add_geom(S.GEOM_BOX, (0.1, 0.1, 0.4), sp2, body=u1)
+    sb.add_universal(u1, -1, [0.0, 2.0, 1.2], [1, 0, 0], [0, 1, 0])
+    u2 = sb.add_body([0.0, 2.0, 0.6], S.q_from_rpy(0.1, 0.2, 0.0), mass=0.7, inertia=S.box_inertia(0.7, 0.1, 0.1, 0.4),
+                     lvel=(0.4, 0.3, 0.0))
+    sb.add_geom(S.GEOM_BOX, (0.1, 0.1, 0.4), sp2, body=u2)
+    sb.add_universal(u1, u2, [0.0, 2.0, 0.8], [0, 1, 0], [1, 0, 0], erp=0.3, cfm=1e-6)
+    # slider on the world along a tilted axis, limits and bounce
+    s1 = sb.add_body([2.0, 0.0, 1.0], S.q_random(rng), mass=1.0, inertia=S.box_inertia(1.0, 0.2, 0.2, 0.2))
+    sb.add_geom(S.GEOM_BOX, (0.2, 0.2, 0.2), sb.new_space(), body=s1)
+    sb.add_slider(s1, -1, [0.3, 0.0, 1.0], lostop=-0.3, histop=0.25, bounce=0.4, stop_erp=0.3, stop_cfm=1e-5)
+    # powered slider between two free bodies falling onto the plane
+    sp3 = sb.new_space()
+    p1 = sb.add_body([2.0, 2.0, 0.8], mass=1.0, inertia=S.box_inertia(1.0, 0.3, 0.2, 0.2))
+    sb.add_geom(S.GEOM_BOX, (0.3, 0.2, 0.2), sp3, body=p1)
+    p2 = sb.add_body([2.5, 2.05, 0.85], S.q_from_rpy(0.0, 0.0, 0.3), mass=0.6, inertia=S.sphere_inertia(0.6, 0.12))
+    sb.add_geom(S.GEOM_SPHERE, (0.12,), sp3, body=p2)
+    sb.add_slider(p1, p2, [1.0, 0.2, 0.1], lostop=-0.2, histop=0.2, vel=0.5, fmax=3.0, fudge=0.7, normal_cfm=1e-6)
+    sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 GOLDEN = {
     "box_drop": (box_drop, 1500),
     "tilted_box": (tilted_box, 600),
@@ -130,4 +170,5 @@ GOLDEN = {
     "boxes30": (boxes30, 500),
     "stack": (stack, 1500),
     "capsules": (capsules, 500),
+    "joints": (joints, 600),
 }

@@ -171,9 +171,11 @@ __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) 
   else if (t1 == GZ_GEOM_CAPSULE && t2 == GZ_GEOM_CAPSULE) n = col_capsule_capsule(g1, g2, o);
   else if (t1 == GZ_GEOM_CAPSULE && t2 == GZ_GEOM_PLANE) n = col_capsule_plane(g1, g2, o);
   else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_CAPSULE) { n = col_capsule_plane(g2, g1, o); rev = true; }
+  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_SPHERE) n = col_cylinder_sphere(g1, g2, o);
+  else if (t1 == GZ_GEOM_SPHERE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_sphere(g2, g1, o); rev = true; }
   else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_PLANE) n = col_cylinder_plane(g1, g2, o);
   else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_plane(g2, g1, o); rev = true; }
-  else n = 0;   // pairs not implemented yet are listed in DESIGN.md (cylinder vs sphere / box / capsule / cylinder)
+  else n = 0;   // pairs not implemented yet are listed in DESIGN.md (cylinder vs box / capsule / cylinder)
   if (rev)
     for (int i = 0; i < n; i++) { o.nrm[i][0] = -o.nrm[i][0]; o.nrm[i][1] = -o.nrm[i][1]; o.nrm[i][2] = -o.nrm[i][2]; }
   return n;

@@ -343,6 +343,60 @@ __device__ inline int col_capsule_plane(const Geom &c, const Geom &pl, COut &o) 
   return n;
 }
 
+// ---- dCollideCylinderSphere (collision_cylinder_sphere.cpp:53-278): one contact; three cases by where
+// the sphere centre projects: beside the barrel, over a cap, or near a rim ----
+__device__ inline int col_cylinder_sphere(const Geom &c, const Geom &sp, COut &o) {
+  const double toleranz = 0.0000001;
+  const double radius = c.dims[0], length = c.dims[1], radius2 = sp.dims[0];
+  const double *cylpos = c.pos, *SpherePos = sp.pos;
+  const double vDir1[3] = {c.R[2], c.R[5], c.R[8]};
+  double G1Pos1[3], G1Pos2[3], C[3];
+  double s = length * 0.5;
+  for (int k = 0; k < 3; k++) { G1Pos2[k] = vDir1[k] * s + cylpos[k]; G1Pos1[k] = vDir1[k] * -s + cylpos[k]; }
+  s = (SpherePos[0] - G1Pos1[0]) * vDir1[0] - (G1Pos1[1] - SpherePos[1]) * vDir1[1] - (G1Pos1[2] - SpherePos[2]) * vDir1[2];
+  if (s < (-radius2) || s > (length + radius2)) return 0;
+  for (int k = 0; k < 3; k++) C[k] = s * vDir1[k] + G1Pos1[k] - SpherePos[k];
+  const double t = sqrt(C[0] * C[0] + C[1] * C[1] + C[2] * C[2]);
+  if (t > (radius + radius2)) return 0;
+  if (t > radius && (s < 0 || s > length)) {
+    // rim
+    const double *G = (s <= 0) ? G1Pos1 : G1Pos2;
+    const double ds = (s <= 0) ? s : (s - length);
+    const double depth = radius2 - sqrt(ds * ds + (t - radius) * (t - radius));
+    if (depth < 0) return 0;
+    for (int k = 0; k < 3; k++) o.pos[0][k] = C[k] / t * -radius + G[k];
+    for (int k = 0; k < 3; k++) o.nrm[0][k] = (o.pos[0][k] - SpherePos[k]) / (radius2 - depth);
+    o.depth[0] = depth;
+    return 1;
+  } else if ((radius - t) <= s && (radius - t) <= (length - s)) {
+    // barrel
+    const double depth = (radius2 + radius) - t;
+    if (depth < 0) return 0;
+    if (t > (radius2 + toleranz)) {
+      for (int k = 0; k < 3; k++) C[k] /= t;
+      for (int k = 0; k < 3; k++) { o.pos[0][k] = C[k] * radius2 + SpherePos[k]; o.nrm[0][k] = C[k]; }
+    } else {
+      for (int k = 0; k < 3; k++) { o.pos[0][k] = C[k] + SpherePos[k]; o.nrm[0][k] = C[k] / t; }
+    }
+    o.depth[0] = depth;
+    return 1;
+  } else {
+    // caps
+    if (s <= (length * 0.5)) {
+      const double depth = s + radius2;
+      if (depth < 0) return 0;
+      for (int k = 0; k < 3; k++) { o.pos[0][k] = radius2 * vDir1[k] + SpherePos[k]; o.nrm[0][k] = vDir1[k]; }
+      o.depth[0] = depth;
+    } else {
+      const double depth = (radius2 + length - s);
+      if (depth < 0) return 0;
+      for (int k = 0; k < 3; k++) { o.pos[0][k] = radius2 * -vDir1[k] + SpherePos[k]; o.nrm[0][k] = -vDir1[k]; }
+      o.depth[0] = depth;
+    }
+    return 1;
+  }
+}
+
 // ---- dCollideCylinderPlane (collision_cylinder_plane.cpp:43-267) ------------
 __device__ inline int col_cylinder_plane(const Geom &c, const Geom &pl, COut &o) {
   const double toleranz = 0.0000001;

@@ -161,6 +161,31 @@ def joints():
     return sb.finish(), S.default_params(), None
 
 
+def cylinders():
+    """cylinder-sphere (barrel, cap and rim cases) and cylinder-plane: spheres dropped onto static
+    standing / lying / tilted cylinders and onto free cylinders (kept apart: cylinder-cylinder is not built)."""
+    sb = S.SceneBuilder()
+    rng = np.random.Generator(np.random.PCG64(5))
+    sb.begin_world()
+    sb.add_ground_plane()
+    lie = S.q_from_axis_angle([0, 1, 0], math.pi / 2)
+    poses = [((0, 0, 0.3), (1, 0, 0, 0)), ((2, 0, 0.25), lie), ((4, 0, 0.4), S.q_from_rpy(0.5, 0.3, 0.0))]
+    for (pos, q) in poses:                                   # static cylinders r 0.25, l 0.6
+        sb.add_geom(S.GEOM_CYLINDER, (0.25, 0.6), sb.new_space(), pos=pos, quat=q)
+        for k in range(4):                                   # spheres over cap centre, rim, barrel side, far side
+            off = [(0.02, 0.01), (0.24, 0.03), (0.33, -0.02), (-0.1, 0.28)][k]
+            b = sb.add_body([pos[0] + off[0], pos[1] + off[1], 1.0 + 0.35 * k], mass=0.3, inertia=S.sphere_inertia(0.3, 0.1))
+            sb.add_geom(S.GEOM_SPHERE, (0.1,), sb.new_space(), body=b)
+    for i in range(3):                                       # free cylinders with a sphere landing on each
+        q = [S.q_from_rpy(0.0, 0.0, 0.0), lie, S.q_random(rng)][i]
+        b = sb.add_body([2.0 * i, 3.0, 0.5], q, mass=1.0, inertia=S.cylinder_inertia(1.0, 0.2, 0.4))
+        sb.add_geom(S.GEOM_CYLINDER, (0.2, 0.4), sb.new_space(), body=b)
+        b = sb.add_body([2.0 * i + 0.05, 3.02, 1.2], mass=0.4, inertia=S.sphere_inertia(0.4, 0.12))
+        sb.add_geom(S.GEOM_SPHERE, (0.12,), sb.new_space(), body=b)
+    sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 GOLDEN = {
     "box_drop": (box_drop, 1500),
     "tilted_box": (tilted_box, 600),
@@ -171,4 +196,5 @@ GOLDEN = {
     "stack": (stack, 1500),
     "capsules": (capsules, 500),
     "joints": (joints, 600),
+    "cylinders": (cylinders, 500),
 }

@@ -150,6 +150,7 @@ struct DevBatch {
   int pgs_prof;
   int pgs_wpw_max;       // worlds per PGS warp the shared-memory budget allows
   int sch_rcap;          // longest schedule period k_schedule's occupancy table holds
+  int sch_rpar;          // longest period k_schedule probes on 32 lanes at once (0: the probe is off)
   int pgs_chain_min;     // rows on the busiest body from which a world is scheduled in chain mode
   int pgs_chain_doubles[GZ_CHAIN_NCLS];   // shared memory (doubles) of k_pgs_chain's launches, ascending
   int pgs_rt, pgs_kmin, pgs_kmax;   // scheduler knobs: target period, lanes-per-solve range

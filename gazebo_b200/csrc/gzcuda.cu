@@ -309,6 +309,9 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   // PGS launch shape (k_pgs_sweep.cuh): one warp per CTA, a fixed shared-memory budget per CTA
   // that holds the accumulators of its worlds, their lambdas and as many row records as fit.
   d.sch_rcap = std::min(GZ_RMAX, 2 * std::max(max_rc, 1) + 64);
+  // 32 candidate periods probed at once need 32 x (2 max_nb ints + sch_rpar shorts) of shared memory
+  d.sch_rpar = (max_nb <= 16) ? 96 : 0;
+  if (const char *e = getenv("GZCUDA_SCH_RPAR")) d.sch_rpar = std::max(0, std::min(512, atoi(e)));
   d.pgs_rt = 28; d.pgs_kmin = 1; d.pgs_kmax = 16; d.pgs_chain_min = 28;
   if (const char *e = getenv("GZCUDA_PGS_CHAIN_MIN")) d.pgs_chain_min = std::max(2, atoi(e));
   if (const char *e = getenv("GZCUDA_PGS_RT")) d.pgs_rt = std::max(1, atoi(e));
@@ -406,7 +409,8 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_info1<<<W, T, 0, b->stream>>>(d);
   if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
-  const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16;
+  const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16 +
+                          (d.sch_rpar > 0 ? (size_t)32 * (2 * std::max(d.max_nb, 1) * sizeof(int) + d.sch_rpar * sizeof(unsigned short)) : 0);
   k_schedule<<<W, 32, sch_smem, b->stream>>>(d);
   k_slab<<<1 + cdiv((W + GZ_NBUCKET) * 16, GZ_SLAB_T * 8), GZ_SLAB_T, 0, b->stream>>>(d);
   k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);

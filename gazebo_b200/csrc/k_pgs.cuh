@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   extern __shared__ int sch_sh[];
   int *cnt = sch_sh, *last = sch_sh + B.max_nb, *first = sch_sh + 2 * B.max_nb;
   unsigned short *occ = reinterpret_cast<unsigned short *>(sch_sh + 3 * B.max_nb);
+  const int nb_cap = max(B.max_nb, 1);   // the probe tables follow occ: [nb_cap][32] ints x 2, [sch_rpar][32] shorts
   const int w = blockIdx.x, lane = threadIdx.x;
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
@@ -216,7 +217,45 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
         while (k < B.pgs_kmax && (nitems + k - 1) / k > target) k <<= 1;
       }
       rb = rung_ceil(max((nitems + k - 1) / k, maxcnt));
-      R = rung_value(rb);
+      // probe: lane l runs the greedy for rung rb + l (feasibility only, tables per lane in shared
+      // memory); the serial ladder below then starts at the first rung that works
+      if (B.sch_rpar > 0 && rb < GZ_NRUNG && rung_value(rb) <= B.sch_rpar) {
+        int *plast = reinterpret_cast<int *>(occ + ((B.sch_rcap + 1) & ~1)) , *pfirst = plast + 32 * nb_cap;
+        unsigned short *pocc = reinterpret_cast<unsigned short *>(pfirst + 32 * nb_cap);
+        const int rbl = rb + lane;
+        const bool valid = rbl < GZ_NRUNG && rung_value(min(rbl, GZ_NRUNG - 1)) <= B.sch_rpar;
+        const int Rl = valid ? rung_value(rbl) : 1;
+        __syncwarp();   // it_pos / it_len written by lane 0
+        int pf = valid ? 0 : 1, pneed = Rl, pmax = 0;
+        for (int s = 0; s < Rl; s++) pocc[s * 32 + lane] = 0;
+        for (int b = 0; b < nb; b++) { plast[b * 32 + lane] = -1; pfirst[b * 32 + lane] = -1; }
+        for (int it = 0; it < nitems && !pf; it++) {
+          const int pos = chain ? S.it_pos[it] : it;
+          const int x1 = S.rb1[pos], x2 = S.rb2[pos];
+          int o = plast[x1 * 32 + lane] + 1;
+          if (x2 >= 0) o = max(o, plast[x2 * 32 + lane] + 1);
+          int s = o % Rl, n = 0;
+          while (pocc[s * 32 + lane] == k) {
+            o++; s++;
+            if (s == Rl) s = 0;
+            if (++n > Rl) { pf = 1; break; }
+          }
+          if (pf) break;
+          pocc[s * 32 + lane]++;
+          plast[x1 * 32 + lane] = o;
+          if (pfirst[x1 * 32 + lane] < 0) pfirst[x1 * 32 + lane] = o;
+          if (x2 >= 0) { plast[x2 * 32 + lane] = o; if (pfirst[x2 * 32 + lane] < 0) pfirst[x2 * 32 + lane] = o; }
+          pmax = max(pmax, o);
+        }
+        if (!pf)
+          for (int b = 0; b < nb; b++)
+            if (pfirst[b * 32 + lane] >= 0) pneed = max(pneed, plast[b * 32 + lane] - pfirst[b * 32 + lane] + 1);
+        const unsigned okm = __ballot_sync(0xffffffffu, !pf && pneed == Rl && pmax / Rl < 255);
+        const unsigned vm = __ballot_sync(0xffffffffu, valid);
+        rb += okm ? __ffs(okm) - 1 : __popc(vm);   // none works: go on after the probed rungs (rb stays warp-uniform)
+        __syncwarp();
+      }
+      R = rung_value(min(rb, GZ_NRUNG - 1));
       bool done = false;
       for (int attempt = 0; !done; attempt++) {
         const bool give_up = attempt >= 24 || rb >= GZ_NRUNG || R > B.sch_rcap;

@@ -43,6 +43,7 @@ struct gzcuda_batch {
   size_t pgs_smem = 0, pgs_chain_smem[GZ_CHAIN_NCLS] = {};
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
   bool profiling = false;             // record an event pair around every k_pgs launch
+  bool reg_first = false;             // experiment: k_pgs before (and above) the small chain-mode launches
   std::vector<cudaEvent_t> pgs_ev;    // 2 per step of the last step call
   int pgs_pairs = 0;
 };
@@ -352,6 +353,14 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     d.pgs_chain_doubles[q] = b->pgs_chain[q].smem_doubles;
     b->pgs_chain_smem[q] = csmem[q];
   }
+  if (!(getenv("GZCUDA_PGS_CARVEOUT") && atoi(getenv("GZCUDA_PGS_CARVEOUT")) == 0)) {
+    // k_pgs and the k_pgs_chain launches share the SMs: ask for the largest shared-memory carve-out for all
+    // of them, so that an SM configured for one can take CTAs of the other
+    CK(cudaFuncSetAttribute(k_pgs<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_pgs<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_pgs_chain<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_pgs_chain<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  }
   {
     const size_t mx = *std::max_element(csmem, csmem + GZ_CHAIN_NCLS);
     CK(cudaFuncSetAttribute(k_pgs_chain<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx));
@@ -371,7 +380,10 @@ gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params
   if (cudaSetDevice(device) != cudaSuccess) { fail(GZCUDA_E_CUDA, "cudaSetDevice failed"); return nullptr; }
   gzcuda_batch *b = new gzcuda_batch;
   b->device = device;
-  bool ok = cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) == cudaSuccess &&
+  int plo0 = 0, phi0 = 0;
+  cudaDeviceGetStreamPriorityRange(&plo0, &phi0);
+  b->reg_first = getenv("GZCUDA_PGS_REGFIRST") && atoi(getenv("GZCUDA_PGS_REGFIRST")) != 0;
+  bool ok = cudaStreamCreateWithPriority(&b->stream, cudaStreamNonBlocking, b->reg_first ? phi0 : plo0) == cudaSuccess &&
             cudaEventCreate(&b->ev0) == cudaSuccess && cudaEventCreate(&b->ev1) == cudaSuccess;
   for (auto &e : b->evs) ok = ok && cudaEventCreate(&e) == cudaSuccess;
   {
@@ -380,7 +392,8 @@ gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params
     ok = ok && cudaEventCreateWithFlags(&b->ev_fork, cudaEventDisableTiming) == cudaSuccess;
     for (int q = 0; q < GZ_CHAIN_NCLS; q++)
       // (greatest priority = lowest number) the larger the class, the longer its worlds run: first on the SMs
-      ok = ok && cudaStreamCreateWithPriority(&b->stream_chain[q], cudaStreamNonBlocking, std::min(plo, phi + (GZ_CHAIN_NCLS - 1 - q))) == cudaSuccess &&
+      ok = ok && cudaStreamCreateWithPriority(&b->stream_chain[q], cudaStreamNonBlocking,
+                                              b->reg_first ? (q >= 2 ? phi : plo) : std::min(plo, phi + (GZ_CHAIN_NCLS - 1 - q))) == cudaSuccess &&
            cudaEventCreateWithFlags(&b->ev_join[q], cudaEventDisableTiming) == cudaSuccess;
   }
   if (!ok) { fail(GZCUDA_E_CUDA, "stream/event creation failed"); gzcuda_batch_destroy(b); return nullptr; }
@@ -419,8 +432,13 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   // at most one warp per world plus a partly filled one per bucket; CTAs beyond the step's warp count exit at once
   // chain-mode warps (heavy worlds, first in warp order) are their own instantiation on a second, higher-priority stream
   const bool chain_on = d.pgs_chain_min < (1 << 24);
-  if (chain_on) {
+  if (chain_on && b->reg_first) {
     cudaEventRecord(b->ev_fork, b->stream);
+    if (d.pgs_prof) k_pgs<true><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+    else k_pgs<false><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+  }
+  if (chain_on) {
+    if (!b->reg_first) cudaEventRecord(b->ev_fork, b->stream);
     for (int q = GZ_CHAIN_NCLS - 1; q >= 0; q--) {   // the large worlds first: they take longest
       cudaStreamWaitEvent(b->stream_chain[q], b->ev_fork, 0);
       if (d.pgs_prof) k_pgs_chain<true><<<W, 32, b->pgs_chain_smem[q], b->stream_chain[q]>>>(d, b->pgs_chain[q], q);
@@ -429,8 +447,10 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
       b->last_launches++;
     }
   }
-  if (d.pgs_prof) k_pgs<true><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
-  else k_pgs<false><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+  if (!(chain_on && b->reg_first)) {
+    if (d.pgs_prof) k_pgs<true><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+    else k_pgs<false><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+  }
   if (chain_on)
     for (int q = 0; q < GZ_CHAIN_NCLS; q++) cudaStreamWaitEvent(b->stream, b->ev_join[q], 0);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);

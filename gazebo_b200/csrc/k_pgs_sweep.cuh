@@ -24,7 +24,7 @@ namespace gz {
 
 #define GZ_RING_D 2                 // ring stages
 #ifndef GZ_RING_G
-#define GZ_RING_G 4                 // rounds per stage (2 or 4): one fetch (and one mbarrier wait) per G rounds
+#define GZ_RING_G 4                 // rounds per stage (2, 3 or 4): one fetch (and one mbarrier wait) per G rounds
 #endif
 #define GZ_STAGE_DOUBLES (GZ_RING_G * GZ_ROUND_DOUBLES)
 #define GZ_RING_DOUBLES (GZ_RING_D * GZ_STAGE_DOUBLES + 2 * GZ_RING_D)   // records + one mbarrier per stage (padded)
@@ -345,6 +345,22 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
     GZ_FETCH(0);
     mbar_wait(bar_s, 0);
     load_row(A, GZ_RECP(0, 0), S, epoch_sh, dummy_bb);
+#if GZ_RING_G == 3
+    for (int g = 0; g < ngroups; g += 2) {      // two groups per trip: the A / Bn roles swap after an odd group
+      GZ_FETCH(g + 1);                          // into the stage group g - 1 used
+      GZ_ROUND(A, Bn, g, 0, g, 1);
+      GZ_ROUND(Bn, A, g, 1, g, 2);
+      if (g + 1 < ngroups) mbar_wait(bar_s + 8 * ((g + 1) & (GZ_RING_D - 1)), ((g + 1) / GZ_RING_D) & 1);
+      GZ_ROUND(A, Bn, g, 2, g + 1, 0);          // past the last group this reads a stale stage: never used
+      if (g + 1 < ngroups) {
+        GZ_FETCH(g + 2);
+        GZ_ROUND(Bn, A, g + 1, 0, g + 1, 1);
+        GZ_ROUND(A, Bn, g + 1, 1, g + 1, 2);
+        if (g + 2 < ngroups) mbar_wait(bar_s + 8 * ((g + 2) & (GZ_RING_D - 1)), ((g + 2) / GZ_RING_D) & 1);
+        GZ_ROUND(Bn, A, g + 1, 2, g + 2, 0);
+      }
+    }
+#else
     for (int g = 0; g < ngroups; g++) {
       GZ_FETCH(g + 1);                          // into the stage group g - 1 used
       GZ_ROUND(A, Bn, g, 0, g, 1);
@@ -355,6 +371,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
       if (g + 1 < ngroups) mbar_wait(bar_s + 8 * ((g + 1) & (GZ_RING_D - 1)), ((g + 1) / GZ_RING_D) & 1);
       GZ_ROUND(Bn, A, g, GZ_RING_G - 1, g + 1, 0);   // past the last group this reads a stale stage: never used
     }
+#endif
   }
 #undef GZ_ROUND
 #undef GZ_RECP

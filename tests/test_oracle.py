@@ -88,3 +88,14 @@ def test_collide_bitmask_filters_pairs(oracle):
     r.step(1)
     assert len(r.pairs(0)) == 1
     assert len(r.contacts(0)[0]) == 0
+
+
+@pytest.mark.parametrize("case", ["test_drop_stuff_free_fall_then_rest", "test_zero_max_contacts_is_harmless",
+                                  "test_simple_pendulum_angle_and_energy", "test_unwrapped_hinge_angle",
+                                  "test_anchored_kinematic_loop_stays_closed"])
+def test_oracle_passes_the_acceptance_cases(oracle, case, monkeypatch):
+    """The behavioural cases of tests/test_acceptance_gpu.py (restated from the reference's integration
+    tests) run against the oracle: the harness is configured like Gazebo configures ODE."""
+    from tests import test_acceptance_gpu as acc
+    monkeypatch.setattr(acc, "_batch", lambda sc, p: oracle.RefBatch(sc, p, mode=1))
+    getattr(acc, case)()

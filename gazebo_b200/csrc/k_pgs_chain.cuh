@@ -49,13 +49,16 @@ __device__ __forceinline__ void run_load(RunRec &X, const double *rec, const int
 // recomputed after it), caccel update in registers.
 template <bool TWO, bool STATS>
 __device__ __forceinline__ void run_row(const RunRec &X, double *a1, double *a2, double *lp, const double *lamS,
-                                        const int S, const double smooth, const bool stat01, const bool stat2,
-                                        PgsStat &st) {
+                                        const int S, const double smooth, const double smooth1, const bool stat01,
+                                        const bool stat2, PgsStat &st) {
   const double old_lambda = *lp;
   const bool fric = X.fi >= 0;
   const double nlam = lamS[2 * (fric ? X.fi : 0)];
-  const double hf = fabs(X.hi * nlam);   // pyramid friction: |mu * lambda_normal|
-  const double hi_act = fric ? hf : X.hi, lo_act = fric ? -hf : X.lo;
+  // pyramid friction: |mu * lambda_normal| and its negative, by the sign bit (integer pipe, not FP64)
+  const double hl = X.hi * nlam;
+  const double hf = __hiloint2double(__double2hiint(hl) & 0x7fffffff, __double2loint(hl));
+  const double nhf = __hiloint2double(__double2hiint(hl) | 0x80000000, __double2loint(hl));
+  const double hi_act = fric ? hf : X.hi, lo_act = fric ? nhf : X.lo;
   double d1 = a1[0] * X.J[0], d2 = 0.0;
   if (TWO) d2 = a2[0] * X.J[6];
 #pragma unroll
@@ -68,7 +71,7 @@ __device__ __forceinline__ void run_row(const RunRec &X, double *a1, double *a2,
   const bool below = nl < lo_act, above = !below && nl > hi_act;
   delta = below ? dlo : (above ? dhi : delta);
   nl = below ? lo_act : (above ? hi_act : nl);
-  const double sm = (1.0 - smooth) * nl + smooth * old_lambda;
+  const double sm = smooth1 * nl + smooth * old_lambda;   // smooth1 = 1.0 - smooth
   *lp = (S == 0 && X.fi != -1) ? sm : nl;
 #pragma unroll
   for (int t = 0; t < 6; t++) a1[t] += delta * X.iM[t];
@@ -92,6 +95,7 @@ __device__ __noinline__ void pgs_run_sm(const int fi, const int orig, const int 
   const double *lamS = shd + lam_off + S;
   double *c1 = shd + cas_off + 6 * b1, *c2 = shd + cas_off + 6 * b2;
   const bool stat01 = flags & 1, stat2 = flags & 2;
+  const double smooth1 = 1.0 - smooth;
   PgsStat st;
   for (int t = 0; t < 3; t++) { st.acc[t] = 0; st.err[t] = 0; st.cnt[t] = 0; }
   double a1[6], a2[6];
@@ -109,12 +113,12 @@ __device__ __noinline__ void pgs_run_sm(const int fi, const int orig, const int 
   int i = 0;
   for (; i + 2 <= len; i += 2) {
     run_load<TWO, STATS>(Y, rp + GZ_REC, S);
-    run_row<TWO, STATS>(X, a1, a2, lp, lamS, S, smooth, stat01, stat2, st);
+    run_row<TWO, STATS>(X, a1, a2, lp, lamS, S, smooth, smooth1, stat01, stat2, st);
     run_load<TWO, STATS>(X, rp + 2 * GZ_REC, S);   // at the end one record past the item: still inside the array (m + 1 records)
-    run_row<TWO, STATS>(Y, a1, a2, lp + 2, lamS, S, smooth, stat01, stat2, st);
+    run_row<TWO, STATS>(Y, a1, a2, lp + 2, lamS, S, smooth, smooth1, stat01, stat2, st);
     rp += 2 * GZ_REC; lp += 4;
   }
-  if (i < len) run_row<TWO, STATS>(X, a1, a2, lp, lamS, S, smooth, stat01, stat2, st);
+  if (i < len) run_row<TWO, STATS>(X, a1, a2, lp, lamS, S, smooth, smooth1, stat01, stat2, st);
   double2 *p1 = reinterpret_cast<double2 *>(c1);
 #pragma unroll
   for (int t = 0; t < 3; t++) p1[t] = make_double2(a1[2 * t], a1[2 * t + 1]);
@@ -237,6 +241,7 @@ __global__ void __launch_bounds__(32) k_pgs_chain(DevBatch B, PgsCfg cfg, int cl
     const bool act = h.x <= GZ_FI_RUN - 1 && (unsigned)sweep < (unsigned)(((h.w >> 30) & 1) ? total : iters);
     const int b1 = h.y & 0xFFFF, b2 = (unsigned)h.y >> 16;
     // one code path for all lanes of the round: the two-body loop if any due item has a second body
+    // (running the single-body items first and the others after them was measured: slower)
     const unsigned due2 = __ballot_sync(0xffffffffu, act && b2 < nbp);
     if (act) {
       if (st_round) {

@@ -371,6 +371,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
 
 gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params, int device) {
   if (!scene || !params || scene->n_worlds <= 0) { fail(GZCUDA_E_INVALID, "null or empty scene"); return nullptr; }
+  if (params->friction_model != 0 && params->friction_model != 2) {
+    fail(GZCUDA_E_INVALID, "friction_model: pyramid (0) and box (2) are supported, cone (1) is not");
+    return nullptr;
+  }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     fail(GZCUDA_E_CUDA, "no CUDA device: libgzcuda has no CPU fallback");
@@ -775,6 +779,10 @@ int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double v) {
   else if (k == "contact_residual_smoothing") p.smooth_contacts = v;
   else if (k == "contact_sor_scale") p.contact_sor_scale = v;
   else if (k == "max_step_size") p.step_size = v;
+  else if (k == "friction_model") {   // ODEPhysics::SetParam takes "pyramid_model" / "box_model" / "cone_model": 0 / 2 / 1 here
+    if ((int)v != 0 && (int)v != 2) return fail(GZCUDA_E_INVALID, "friction_model: pyramid (0) and box (2) are supported");
+    p.friction_model = (int)v;
+  }
   else return fail(GZCUDA_E_INVALID, "unknown parameter key: " + k);
   return 0;
 }

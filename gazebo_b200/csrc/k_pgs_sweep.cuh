@@ -102,7 +102,7 @@ struct PgsStat { double acc[3], err[3]; int cnt[3]; };
 struct RowIn { double a1[6], a2[6], old_lambda, nlam; };
 
 __device__ __forceinline__ void pgs_row_in(RowIn &I, const RowRegs &R, const int S, const int idx, const double *cas,
-                                           const double *lam) {
+                                           const double *lam, const bool box) {
   const double2 *p1 = reinterpret_cast<const double2 *>(cas + 6 * R.b1);
   const double2 *p2 = reinterpret_cast<const double2 *>(cas + 6 * R.b2);
 #pragma unroll
@@ -112,6 +112,7 @@ __device__ __forceinline__ void pgs_row_in(RowIn &I, const RowRegs &R, const int
   }
   I.old_lambda = lam[2 * idx + S];
   I.nlam = lam[2 * (R.fi >= 0 ? R.fi : idx) + S];
+  if (box) I.nlam = 1.0;   // box friction (quickstep_pgs_lcp.cpp:588-594): limits +-hi, i.e. |hi * 1|
 }
 
 // The arithmetic of one row update given the accumulators of its bodies: returns delta, sets nl.
@@ -280,6 +281,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   // ---- the sweeps
   const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
   const double smooth = B.p.smooth_contacts;
+  const bool box = B.p.friction_model == 2;
   const bool on = live_ok && total > 0;
   const int max_nstage = __reduce_max_sync(0xffffffffu, nstage);
   const int rounds = (total > 0 && max_nstage > 0) ? (total + max_nstage - 1) * R : 0;
@@ -316,7 +318,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
                           (period >= total - 1 && period < total - 1 + max_nstage);               \
     const int idx = on ? slot * k + jl : 0;                                                       \
     RowIn in;                                                                                     \
-    pgs_row_in(in, CUR, S, idx, cas, lam);      /* issue these loads first, then the next record's */ \
+    pgs_row_in(in, CUR, S, idx, cas, lam, box); /* issue these loads first, then the next record's */ \
     load_row(NXT, GZ_RECP(NG, NI), S, epoch_sh, dummy_bb);                                        \
     const unsigned due = __ballot_sync(0xffffffffu, act);                                         \
     const unsigned due2 = __ballot_sync(0xffffffffu, act && CUR.b2 < nbp);                        \

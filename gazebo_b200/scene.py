@@ -37,6 +37,7 @@ class GzParams(C.Structure):
         ("adis_idle_steps", C.c_int), ("adis_idle_time", C.c_double),
         ("adis_linear_threshold_sq", C.c_double), ("adis_angular_threshold_sq", C.c_double),
         ("damping_linear_threshold_sq", C.c_double), ("damping_angular_threshold_sq", C.c_double),
+        ("friction_model", C.c_int),
     ]
 
 

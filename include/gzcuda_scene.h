@@ -79,6 +79,9 @@ typedef struct gz_params {
   /* damping thresholds (squared speeds, ode.cpp:1678-1679) */
   double damping_linear_threshold_sq;
   double damping_angular_threshold_sq;
+  /* qs.friction_model (ode.cpp:1672, ODEPhysics::SetFrictionModel): 0 = pyramid (default), 2 = box
+   * (friction limits +-mu instead of +-mu * lambda_normal); 1 = cone is not supported */
+  int    friction_model;
 } gz_params;
 
 typedef struct gz_scene {

@@ -391,6 +391,7 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
     w->world->qs.warm_start = p->warm_start;
     w->world->qs.smooth_contacts = p->smooth_contacts;
     w->world->qs.contact_sor_scale = p->contact_sor_scale;
+    w->world->qs.friction_model = p->friction_model == 2 ? box_friction : pyramid_friction;
 
     // bodies: ODELink::Init / UpdateMass / UpdateSurface
     for (int b = sc->body_off[wi]; b < sc->body_off[wi + 1]; b++) {

@@ -87,21 +87,19 @@ struct Contact {
   int row0, pad;
 };
 
-// One constraint row: 40 doubles = 320 B.
+// One constraint row as the assembly kernels leave it: 24 doubles = 192 B.  (What the sweeps read is the
+// packed record k_rowfinish makes of it, k_pgs.cuh.)
 struct Row {
-  double J[12];      // scaled by Ad after the prologue (quickstep_pgs_lcp.cpp:1091-1107)
-  double iMJ[12];
-  double rhs, rhs_erp, Adcfm, Ad;
+  double J[12];      // unscaled; the record holds J * Ad (quickstep_pgs_lcp.cpp:1091-1107)
+  double Ad;
   double lo, hi;
   double lambda, lambda_erp;
   double c, cfm, c_v_max;
-  double pad0;
   int b1, b2;        // WORLD-LOCAL body indices, b2 = -1
   int findex;        // -1 bilateral, -2 contact normal, >=0 absolute (world-local) row of the normal
   int src;           // joint index (>=0, global) or ~contact index (global) for write-back
-  int t1a, t2a, t1f, t2f;   // dataflow tickets (see k_pgs.cuh)
-  int next_a, next_f;       // per-executor queues, all-rows sweeps / friction-only sweeps
-  int owner, pad1;
+  int t1a, t2a, t1f; // k_schedule: stage, index in the run array or -1, item head slot | len << 20 or -1 (k_pgs.cuh)
+  int next_f;        // k_schedule: lambda index (slab slot, or order[] position in chain mode)
 };
 
 struct WorldInfo {

@@ -126,6 +126,17 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   delete b;
 }
 
+// the instantiation of the sweep kernels for (timeline profiling, box friction model)
+typedef void (*PgsKernel)(DevBatch, PgsCfg);
+typedef void (*PgsChainKernel)(DevBatch, PgsCfg, int);
+static PgsKernel pgs_kernel(bool prof, bool box) {
+  return prof ? (box ? k_pgs<true, true> : k_pgs<true, false>) : (box ? k_pgs<false, true> : k_pgs<false, false>);
+}
+static PgsChainKernel pgs_chain_kernel(bool prof, bool box) {
+  return prof ? (box ? k_pgs_chain<true, true> : k_pgs_chain<true, false>)
+              : (box ? k_pgs_chain<false, true> : k_pgs_chain<false, false>);
+}
+
 static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   const int W = sc->n_worlds;
   const int nb = sc->body_off[W], ng = sc->geom_off[W], nj = sc->joint_off[W];
@@ -332,8 +343,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   c.smem_doubles = (int)(smem / sizeof(double));
   b->pgs_smem = smem;
   if (b->pgs_smem > 48 * 1024) {
-    CK(cudaFuncSetAttribute(k_pgs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
-    CK(cudaFuncSetAttribute(k_pgs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
+    for (int v = 0; v < 4; v++)
+      CK(cudaFuncSetAttribute(pgs_kernel(v & 1, v & 2), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgs_smem));
   }
   // chain-mode worlds (k_pgs_chain.cuh): one world per CTA, resident in shared memory; one launch per
   // size class (ascending), so that small worlds do not take a large world's share of an SM
@@ -356,15 +367,15 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if (!(getenv("GZCUDA_PGS_CARVEOUT") && atoi(getenv("GZCUDA_PGS_CARVEOUT")) == 0)) {
     // k_pgs and the k_pgs_chain launches share the SMs: ask for the largest shared-memory carve-out for all
     // of them, so that an SM configured for one can take CTAs of the other
-    CK(cudaFuncSetAttribute(k_pgs<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaFuncSetAttribute(k_pgs<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaFuncSetAttribute(k_pgs_chain<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaFuncSetAttribute(k_pgs_chain<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    for (int v = 0; v < 4; v++) {
+      CK(cudaFuncSetAttribute(pgs_kernel(v & 1, v & 2), cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+      CK(cudaFuncSetAttribute(pgs_chain_kernel(v & 1, v & 2), cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    }
   }
   {
     const size_t mx = *std::max_element(csmem, csmem + GZ_CHAIN_NCLS);
-    CK(cudaFuncSetAttribute(k_pgs_chain<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx));
-    CK(cudaFuncSetAttribute(k_pgs_chain<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx));
+    for (int v = 0; v < 4; v++)
+      CK(cudaFuncSetAttribute(pgs_chain_kernel(v & 1, v & 2), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx));
   }
   return 0;
 }
@@ -436,24 +447,23 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   // at most one warp per world plus a partly filled one per bucket; CTAs beyond the step's warp count exit at once
   // chain-mode warps (heavy worlds, first in warp order) are their own instantiation on a second, higher-priority stream
   const bool chain_on = d.pgs_chain_min < (1 << 24);
+  const PgsKernel kp = pgs_kernel(d.pgs_prof, d.p.friction_model == 2);
+  const PgsChainKernel kc = pgs_chain_kernel(d.pgs_prof, d.p.friction_model == 2);
   if (chain_on && b->reg_first) {
     cudaEventRecord(b->ev_fork, b->stream);
-    if (d.pgs_prof) k_pgs<true><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
-    else k_pgs<false><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+    kp<<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
   }
   if (chain_on) {
     if (!b->reg_first) cudaEventRecord(b->ev_fork, b->stream);
     for (int q = GZ_CHAIN_NCLS - 1; q >= 0; q--) {   // the large worlds first: they take longest
       cudaStreamWaitEvent(b->stream_chain[q], b->ev_fork, 0);
-      if (d.pgs_prof) k_pgs_chain<true><<<W, 32, b->pgs_chain_smem[q], b->stream_chain[q]>>>(d, b->pgs_chain[q], q);
-      else k_pgs_chain<false><<<W, 32, b->pgs_chain_smem[q], b->stream_chain[q]>>>(d, b->pgs_chain[q], q);
+      kc<<<W, 32, b->pgs_chain_smem[q], b->stream_chain[q]>>>(d, b->pgs_chain[q], q);
       cudaEventRecord(b->ev_join[q], b->stream_chain[q]);
       b->last_launches++;
     }
   }
   if (!(chain_on && b->reg_first)) {
-    if (d.pgs_prof) k_pgs<true><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
-    else k_pgs<false><<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+    kp<<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
   }
   if (chain_on)
     for (int q = 0; q < GZ_CHAIN_NCLS; q++) cudaStreamWaitEvent(b->stream, b->ev_join[q], 0);

@@ -47,13 +47,13 @@ __device__ __forceinline__ void run_load(RunRec &X, const double *rec, const int
 // One row update of one solve (quickstep_pgs_lcp.cpp:488-808, pyramid friction): delta, limits from
 // lo/hi or |hi * lambda[findex]|, clamp, SMOOTH_LAMBDA on the lambda solve only (delta is not
 // recomputed after it), caccel update in registers.
-template <bool TWO, bool STATS>
+template <bool TWO, bool STATS, bool BOX>
 __device__ __forceinline__ void run_row(const RunRec &X, double *a1, double *a2, double *lp, const double *lamS,
                                         const int S, const double smooth, const double smooth1, const bool stat01,
-                                        const bool stat2, const bool box, PgsStat &st) {
+                                        const bool stat2, PgsStat &st) {
   const double old_lambda = *lp;
   const bool fric = X.fi >= 0;
-  const double nlam = box ? 1.0 : lamS[2 * (fric ? X.fi : 0)];   // box friction: limits +-hi
+  const double nlam = BOX ? 1.0 : lamS[2 * (fric ? X.fi : 0)];   // box friction: limits +-hi
   // pyramid friction: |mu * lambda_normal| and its negative, by the sign bit (integer pipe, not FP64)
   const double hl = X.hi * nlam;
   const double hf = __hiloint2double(__double2hiint(hl) & 0x7fffffff, __double2loint(hl));
@@ -83,8 +83,8 @@ __device__ __forceinline__ void run_row(const RunRec &X, double *a1, double *a2,
 }
 
 // offsets are in doubles from the start of the dynamic shared array; flags: 1 = sweep iters - 1
-// (bilateral and normal statistics), 2 = sweep total - 1 (friction statistics), 4 = box friction model
-template <bool TWO, bool STATS>
+// (bilateral and normal statistics), 2 = sweep total - 1 (friction statistics); BOX = box friction model
+template <bool TWO, bool STATS, bool BOX>
 __device__ __noinline__ void pgs_run_sm(const int fi, const int orig, const int b1, const int b2, const int S,
                                         const int cas_off, const int lam_off, const int run_off, const int nbp,
                                         const double smooth, const int flags, const int stat_off) {
@@ -94,7 +94,7 @@ __device__ __noinline__ void pgs_run_sm(const int fi, const int orig, const int 
   double *lp = shd + lam_off + 2 * roff + S;
   const double *lamS = shd + lam_off + S;
   double *c1 = shd + cas_off + 6 * b1, *c2 = shd + cas_off + 6 * b2;
-  const bool stat01 = flags & 1, stat2 = flags & 2, box = flags & 4;
+  const bool stat01 = flags & 1, stat2 = flags & 2;
   const double smooth1 = 1.0 - smooth;
   PgsStat st;
   for (int t = 0; t < 3; t++) { st.acc[t] = 0; st.err[t] = 0; st.cnt[t] = 0; }
@@ -113,12 +113,12 @@ __device__ __noinline__ void pgs_run_sm(const int fi, const int orig, const int 
   int i = 0;
   for (; i + 2 <= len; i += 2) {
     run_load<TWO, STATS>(Y, rp + GZ_REC, S);
-    run_row<TWO, STATS>(X, a1, a2, lp, lamS, S, smooth, smooth1, stat01, stat2, box, st);
+    run_row<TWO, STATS, BOX>(X, a1, a2, lp, lamS, S, smooth, smooth1, stat01, stat2, st);
     run_load<TWO, STATS>(X, rp + 2 * GZ_REC, S);   // at the end one record past the item: still inside the array (m + 1 records)
-    run_row<TWO, STATS>(Y, a1, a2, lp + 2, lamS, S, smooth, smooth1, stat01, stat2, box, st);
+    run_row<TWO, STATS, BOX>(Y, a1, a2, lp + 2, lamS, S, smooth, smooth1, stat01, stat2, st);
     rp += 2 * GZ_REC; lp += 4;
   }
-  if (i < len) run_row<TWO, STATS>(X, a1, a2, lp, lamS, S, smooth, smooth1, stat01, stat2, box, st);
+  if (i < len) run_row<TWO, STATS, BOX>(X, a1, a2, lp, lamS, S, smooth, smooth1, stat01, stat2, st);
   double2 *p1 = reinterpret_cast<double2 *>(c1);
 #pragma unroll
   for (int t = 0; t < 3; t++) p1[t] = make_double2(a1[2 * t], a1[2 * t + 1]);
@@ -135,7 +135,7 @@ __device__ __noinline__ void pgs_run_sm(const int fi, const int orig, const int 
 }
 
 // cls: shared-memory size class of this launch (0 small, 1 large); worlds of the other class exit
-template <bool PROF>
+template <bool PROF, bool BOX>
 __global__ void __launch_bounds__(32) k_pgs_chain(DevBatch B, PgsCfg cfg, int cls) {
   extern __shared__ __align__(16) double shd[];
   const int lane = threadIdx.x;
@@ -227,7 +227,6 @@ __global__ void __launch_bounds__(32) k_pgs_chain(DevBatch B, PgsCfg cfg, int cl
   const double smooth = B.p.smooth_contacts;
   const int rounds = (total > 0 && nstage > 0) ? (total + nstage - 1) * R : 0;
   const int cas_off = 6 * (nbp + 1) * S;
-  const int boxf = B.p.friction_model == 2 ? 4 : 0;
   int slot = 0, period = 0;
   long long pc[5] = {0, 0, 0, 0, 0};
   const unsigned long long g0 = gtimer();
@@ -246,12 +245,12 @@ __global__ void __launch_bounds__(32) k_pgs_chain(DevBatch B, PgsCfg cfg, int cl
     const unsigned due2 = __ballot_sync(0xffffffffu, act && b2 < nbp);
     if (act) {
       if (st_round) {
-        const int flags = (sweep == iters - 1 ? 1 : 0) | (sweep == total - 1 ? 2 : 0) | boxf;
-        if (due2) pgs_run_sm<true, true>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, flags, stat_off + 10 * lane);
-        else pgs_run_sm<false, true>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, flags, stat_off + 10 * lane);
+        const int flags = (sweep == iters - 1 ? 1 : 0) | (sweep == total - 1 ? 2 : 0);
+        if (due2) pgs_run_sm<true, true, BOX>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, flags, stat_off + 10 * lane);
+        else pgs_run_sm<false, true, BOX>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, flags, stat_off + 10 * lane);
       } else {
-        if (due2) pgs_run_sm<true, false>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, boxf, 0);
-        else pgs_run_sm<false, false>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, boxf, 0);
+        if (due2) pgs_run_sm<true, false, BOX>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, 0, 0);
+        else pgs_run_sm<false, false, BOX>(h.x, h.w, b1, b2, S, cas_off, lam_off, run_off, nbp, smooth, 0, 0);
       }
     }
     __syncwarp();

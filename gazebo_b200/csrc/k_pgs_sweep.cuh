@@ -186,7 +186,7 @@ __device__ __forceinline__ void pgs_row(const RowRegs &R, const RowIn &I, const 
   if (STATS) pgs_stat(st, R.fi, act && S == 0 && stat01, act && S == 0 && stat2, delta, Ad2);
 }
 
-template <bool PROF>
+template <bool PROF, bool BOX>
 __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   extern __shared__ __align__(16) double shd[];
   const int lane = threadIdx.x;
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   // ---- the sweeps
   const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
   const double smooth = B.p.smooth_contacts;
-  const bool box = B.p.friction_model == 2;
+  constexpr bool box = BOX;   // box friction model (friction_model == 2), chosen at launch
   const bool on = live_ok && total > 0;
   const int max_nstage = __reduce_max_sync(0xffffffffu, nstage);
   const int rounds = (total > 0 && max_nstage > 0) ? (total + max_nstage - 1) * R : 0;

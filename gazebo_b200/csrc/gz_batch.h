@@ -152,6 +152,7 @@ struct DevBatch {
   int pgs_chain_min;     // rows on the busiest body from which a world is scheduled in chain mode
   int pgs_chain_doubles[GZ_CHAIN_NCLS];   // shared memory (doubles) of k_pgs_chain's launches, ascending
   int pgs_rt, pgs_kmin, pgs_kmax;   // scheduler knobs: target period, lanes-per-solve range
+  int bp_sap_min;        // geoms from which a world takes the sort-and-sweep broadphase (k_collide.cuh)
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)
   double *io_out;        // [nb][13] staged pos(3) quat(4) lvel(3) avel(3)

@@ -41,6 +41,8 @@ struct gzcuda_batch {
   bool stage_valid = false;
   bool have_pd = false;
   size_t pgs_smem = 0, pgs_chain_smem[GZ_CHAIN_NCLS] = {};
+  size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
+  int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
   bool profiling = false;             // record an event pair around every k_pgs launch
   bool reg_first = false;             // experiment: k_pgs before (and above) the small chain-mode launches
@@ -318,6 +320,28 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
 
+  // Broadphase (k_collide.cuh): all pairs for small worlds, sort-and-sweep from bp_sap_min geoms on,
+  // if the sorted keys and the n x n hit bits of the largest world fit in shared memory
+  {
+    d.bp_sap_min = 64;
+    if (const char *e = getenv("GZCUDA_BP_SAP_MIN")) d.bp_sap_min = std::max(2, atoi(e));
+    b->bp_smem = (size_t)(max_ng + 1) * sizeof(int);
+    b->bp_threads = 128;
+    if (max_ng >= d.bp_sap_min) {
+      size_t npad = 32;
+      while (npad < (size_t)max_ng) npad <<= 1;
+      const size_t need = npad * 20 + ((size_t)max_ng + 1) * 4 + (size_t)max_ng * (((size_t)max_ng + 31) / 32) * 4 + 16;
+      if (need <= (size_t)220 * 1024) {
+        b->bp_smem = std::max(b->bp_smem, need);
+        b->bp_threads = 512;
+        if (b->bp_smem > 48 * 1024)
+          CK(cudaFuncSetAttribute(k_broadphase, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->bp_smem));
+      } else {
+        d.bp_sap_min = 1 << 30;   // the largest world does not fit: every world takes the all-pairs path
+      }
+    }
+  }
+
   // PGS launch shape (k_pgs_sweep.cuh): one warp per CTA, a fixed shared-memory budget per CTA
   // that holds the accumulators of its worlds, their lambdas and as many row records as fit.
   d.sch_rcap = std::min(GZ_RMAX, 2 * std::max(max_rc, 1) + 64);
@@ -422,7 +446,7 @@ static int launch_collision(gzcuda_batch *b) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
   k_geom<<<cdiv(std::max(d.ng, 1), T), T, 0, b->stream>>>(d);
-  k_broadphase<<<W, T, (d.max_ng + 1) * sizeof(int), b->stream>>>(d);
+  k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
   k_narrow<<<dim3(cdiv(d.max_pair_cap, T), W), T, 0, b->stream>>>(d);
   k_contacts<<<W, T, 0, b->stream>>>(d);
   b->last_launches += 4;

@@ -101,14 +101,118 @@ __device__ inline bool pair_passes(const DevBatch &B, const Geom &g1, const Geom
   return true;
 }
 
-// One CTA per world.  Two passes over the (i<j) pair matrix, one warp per row i:
+// Sort-and-sweep broadphase of one world (n >= B.bp_sap_min geoms), one CTA.  The geoms are sorted
+// by the lower x bound of their AABB (bitonic sort in shared memory); one warp per sorted position
+// p then walks forward while min_x[q] <= max_x[p] — exactly the pairs that overlap on x, every
+// other pair fails collideAABBs' first comparison (collision_space_internal.h:66-72) — and gives
+// each survivor the full test.  Hits set bit (lower index, higher index) of an n x n bit matrix
+// in shared memory; popcounts per row, a warp prefix scan and an in-order walk of the set bits
+// emit the pair list sorted by (i, j): the same list as the all-pairs path, whatever order the
+// sweep found the pairs in.  (The reference's own structure here is a multi-resolution hash
+// space, collision_space.cpp:427-593; both are exact AABB-overlap filters, so the pair SET is
+// the same — the tests compare the lists with the reference's, sorted.)
+__device__ void broadphase_sap(const DevBatch &B, const int w, const WorldInfo &wi, int *sh) {
+  const int n = wi.ng, tid = threadIdx.x, nt = blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarp = nt >> 5;
+  int npad = 32;
+  while (npad < n) npad <<= 1;
+  const int nw = (n + 31) >> 5;
+  double *skey = reinterpret_cast<double *>(sh);          // [npad] lower x bound, sorted
+  double *smax = skey + npad;                             // [npad] upper x bound of the same geom
+  int *sidx = reinterpret_cast<int *>(smax + npad);       // [npad] world-local geom index
+  int *rowcnt = sidx + npad;                              // [n + 1]
+  unsigned *bm = reinterpret_cast<unsigned *>(rowcnt + n + 1);   // [n][nw] upper-triangular hit matrix
+  const Geom *G = B.geom + wi.geom0;
+  for (int i = tid; i < npad; i += nt) { skey[i] = (i < n) ? G[i].aabb[0] : GZ_INF; sidx[i] = i; }
+  for (int i = tid; i < n * nw; i += nt) bm[i] = 0u;
+  __syncthreads();
+  for (int k = 2; k <= npad; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < npad; i += nt) {
+        const int l = i ^ j;
+        if (l > i) {
+          const double a = skey[i], b = skey[l];
+          const int ia = sidx[i], ib = sidx[l];
+          const bool gt = a > b || (a == b && ia > ib);   // padding (index >= n, key +inf) sorts last
+          if (gt == ((i & k) == 0)) { skey[i] = b; skey[l] = a; sidx[i] = ib; sidx[l] = ia; }
+        }
+      }
+      __syncthreads();
+    }
+  for (int p = tid; p < n; p += nt) smax[p] = G[sidx[p]].aabb[1];
+  __syncthreads();
+  for (int p = warp; p < n - 1; p += nwarp) {
+    const int ip = sidx[p];
+    const double mx = smax[p];
+    for (int q0 = p + 1; q0 < n; q0 += 32) {
+      const int q = q0 + lane;
+      const bool in = (q < n) && skey[q] <= mx;
+      if (in) {
+        const int iq = sidx[q];
+        const int lo = min(ip, iq), hi = max(ip, iq);
+        if (pair_passes(B, G[lo], G[hi])) atomicOr(&bm[lo * nw + (hi >> 5)], 1u << (hi & 31));
+      }
+      if (!__all_sync(0xffffffffu, in)) break;   // sorted: nothing further overlaps p on x
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += nt) {
+    int c = 0;
+    for (int k = i >> 5; k < nw; k++) c += __popc(bm[i * nw + k]);
+    rowcnt[i] = c;
+  }
+  __syncthreads();
+  if (warp == 0) {   // exclusive scan of the row counts, 32 at a time
+    int carry = 0;
+    for (int i0 = 0; i0 < n; i0 += 32) {
+      const int i = i0 + lane;
+      const int c = (i < n) ? rowcnt[i] : 0;
+      int v = c;
+      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
+      if (i < n) rowcnt[i] = carry + v - c;
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+    if (lane == 0) {
+      WorldStep &ws = B.wstep[w];
+      ws.overflow = 0;
+      if (carry > wi.pair_cap) { ws.overflow |= 1; carry = wi.pair_cap; }
+      ws.n_pairs = carry;
+    }
+  }
+  __syncthreads();
+  for (int i = warp; i < n; i += nwarp) {
+    int base = rowcnt[i];
+    for (int k0 = (i >> 5) & ~31; k0 < nw; k0 += 32) {
+      const int k = k0 + lane;
+      unsigned m = (k < nw) ? bm[i * nw + k] : 0u;
+      const int c = __popc(m);
+      int v = c;
+      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
+      int at = base + v - c;
+      while (m) {
+        const int j = 32 * k + __ffs(m) - 1;
+        m &= m - 1;
+        if (at < wi.pair_cap) {
+          B.pair[2 * (wi.pair0 + at)] = wi.geom0 + i;
+          B.pair[2 * (wi.pair0 + at) + 1] = wi.geom0 + j;
+        }
+        at++;
+      }
+      base += __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
+}
+
+// One CTA per world.  Small worlds: two passes over the (i<j) pair matrix, one warp per row i:
 // count, block-wide exclusive scan of the row counts, then ordered emission with
-// warp ballots.  Output is sorted by (i, j) by construction.
-__global__ void k_broadphase(DevBatch B) {
-  extern __shared__ int sh[];
+// warp ballots.  Output is sorted by (i, j) by construction.  Worlds with bp_sap_min geoms or
+// more take the sort-and-sweep path above.
+__global__ void __launch_bounds__(512) k_broadphase(DevBatch B) {
+  extern __shared__ __align__(16) int sh[];
   const int w = blockIdx.x;
   const WorldInfo wi = B.world[w];
   const int n = wi.ng;
+  if (n >= B.bp_sap_min) { broadphase_sap(B, w, wi, sh); return; }
   int *rowcnt = sh;            // [n+1]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const Geom *G = B.geom + wi.geom0;

@@ -16,6 +16,7 @@
 // PGS schedule buckets (k_pgs.cuh): c = log2(lanes per solve) in 0..4, rung of the period ladder in 1..159
 #define GZ_NRUNG 160
 #define GZ_NBUCKET (10 * GZ_NRUNG)
+#define GZ_PAIR_MAXC 16  // contacts one geom pair can yield (box-box: 8, cylinder-box: up to 13)
 #define GZ_CHAIN_NCLS 4   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
 
 namespace gz {
@@ -131,7 +132,7 @@ struct DevBatch {
   Joint *joint;
   int *pair;             // [pairs][2] global geom indices
   int *pair_nc;          // contacts of each pair after Gazebo's truncation
-  double *pair_contact;  // [pairs][8][7]  pos, normal, depth
+  double *pair_contact;  // [pairs][GZ_PAIR_MAXC][7]  pos, normal, depth
   Contact *contact;
   Row *row;
   int *order;            // per world slab: order[k] = world-local row index

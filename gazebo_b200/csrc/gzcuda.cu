@@ -292,7 +292,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_upload(b, &d.joint, hj))) return rc;
   if ((rc = dev_alloc(b, &d.pair, (size_t)2 * pair_tot))) return rc;
   if ((rc = dev_alloc(b, &d.pair_nc, (size_t)pair_tot))) return rc;
-  if ((rc = dev_alloc(b, &d.pair_contact, (size_t)56 * pair_tot))) return rc;
+  if ((rc = dev_alloc(b, &d.pair_contact, (size_t)7 * GZ_PAIR_MAXC * pair_tot))) return rc;
   if ((rc = dev_alloc(b, &d.contact, (size_t)contact_tot))) return rc;
   if ((rc = dev_alloc(b, &d.row, (size_t)row_tot))) return rc;
   if ((rc = dev_alloc(b, &d.order, (size_t)row_tot))) return rc;

@@ -15,6 +15,8 @@
 // AABB-overlap test between the model spaces followed by geom-vs-geom AABB tests.
 #pragma once
 #include "k_boxbox.cuh"
+#include "../../include/gz_detmath.h"
+#include "k_cylbox.cuh"
 
 namespace gz {
 
@@ -279,7 +281,9 @@ __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) 
   else if (t1 == GZ_GEOM_SPHERE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_sphere(g2, g1, o); rev = true; }
   else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_PLANE) n = col_cylinder_plane(g1, g2, o);
   else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_plane(g2, g1, o); rev = true; }
-  else n = 0;   // pairs not implemented yet are listed in DESIGN.md (cylinder vs box / capsule / cylinder)
+  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_BOX) n = col_cylinder_box(g1, g2, o);
+  else if (t1 == GZ_GEOM_BOX && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_box(g2, g1, o); rev = true; }
+  else n = 0;   // pairs not implemented yet are listed in DESIGN.md (cylinder vs capsule / cylinder: libccd MPR)
   if (rev)
     for (int i = 0; i < n; i++) { o.nrm[i][0] = -o.nrm[i][0]; o.nrm[i][1] = -o.nrm[i][1]; o.nrm[i][2] = -o.nrm[i][2]; }
   return n;
@@ -303,15 +307,15 @@ __global__ void k_narrow(DevBatch B) {
     if ((unsigned)g2.max_contacts < maxCollide) maxCollide = g2.max_contacts;
     COut o;
     numc = collide_dispatch(g1, g2, o);
-    int idx[8];
-    for (int i = 0; i < 8; i++) idx[i] = i;
+    int idx[GZ_PAIR_MAXC];
+    for (int i = 0; i < GZ_PAIR_MAXC; i++) idx[i] = i;
     if (maxCollide > 0 && (unsigned)numc > maxCollide) {
       double mx = o.depth[maxCollide - 1];
       for (unsigned i = maxCollide; i < (unsigned)numc; ++i)
         if (o.depth[i] > mx) { mx = o.depth[i]; idx[maxCollide - 1] = i; }
       numc = maxCollide;
     }
-    double *out = B.pair_contact + (size_t)pi * 56;
+    double *out = B.pair_contact + (size_t)pi * (7 * GZ_PAIR_MAXC);
     for (int c = 0; c < numc; c++) {
       int s = idx[c];
       for (int i = 0; i < 3; i++) { out[7 * c + i] = o.pos[s][i]; out[7 * c + 3 + i] = o.nrm[s][i]; }
@@ -382,7 +386,7 @@ __global__ void k_contacts(DevBatch B) {
       // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
       int b1 = g1.body, b2 = g2.body, reverse = 0;
       if (b1 < 0) { b1 = b2; b2 = -1; reverse = 1; }
-      const double *src = B.pair_contact + (size_t)pi * 56;
+      const double *src = B.pair_contact + (size_t)pi * (7 * GZ_PAIR_MAXC);
       for (int j = 0; j < c; j++) {
         int ci = off + j;
         if (ci >= wi.contact_cap) break;

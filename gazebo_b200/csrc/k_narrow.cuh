@@ -12,10 +12,10 @@
 
 namespace gz {
 
-struct COut {          // up to 8 contacts: position, depth; one normal per contact
-  double pos[8][3];
-  double nrm[8][3];
-  double depth[8];
+struct COut {          // up to GZ_PAIR_MAXC contacts: position, depth; one normal per contact
+  double pos[GZ_PAIR_MAXC][3];
+  double nrm[GZ_PAIR_MAXC][3];
+  double depth[GZ_PAIR_MAXC];
 };
 
 // ---- dCollideSpherePlane  (deps/opende/src/sphere.cpp:226-251) --------------

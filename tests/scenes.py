@@ -186,6 +186,40 @@ def cylinders():
     return sb.finish(), S.default_params(), None
 
 
+def cylboxes():
+    """cylinder-box (collision_cylinder_box.cpp): cylinders standing, lying and tilted dropped onto
+    static boxes (cap-on-face = the polygon clip branch, barrel-on-face and barrel-on-edge = the
+    generator-line branch), boxes dropped onto static cylinders, and a free box landing on a free
+    lying cylinder.  Groups are spaced so that no two cylinders ever meet (cylinder-cylinder is MPR)."""
+    sb = S.SceneBuilder()
+    rng = np.random.Generator(np.random.PCG64(77))
+    sb.begin_world()
+    sb.add_ground_plane()
+    lie = S.q_from_axis_angle([0, 1, 0], math.pi / 2)
+    drops = [((1, 0, 0, 0), (0.0, 0.0)), (lie, (0.02, 0.01)), (S.q_from_rpy(0.4, 0.2, 0.1), (0.05, -0.03)),
+             (S.q_from_rpy(0.0, 1.2, 0.7), (0.3, 0.28)), (S.q_random(rng), (-0.1, 0.05)), ((1, 0, 0, 0), (0.33, 0.0))]
+    for i, (q, off) in enumerate(drops):                      # free cylinders onto static boxes 0.8 x 0.8 x 0.4
+        x = 3.0 * i
+        sb.add_geom(S.GEOM_BOX, (0.8, 0.8, 0.4), sb.new_space(), pos=(x, 0, 0.2), quat=S.q_from_rpy(0, 0, 0.3 * i))
+        b = sb.add_body([x + off[0], off[1], 0.85], q, mass=1.0, inertia=S.cylinder_inertia(1.0, 0.15, 0.4))
+        sb.add_geom(S.GEOM_CYLINDER, (0.15, 0.4), sb.new_space(), body=b)
+    poses = [((0, 5, 0.3), (1, 0, 0, 0)), ((3, 5, 0.25), lie), ((6, 5, 0.4), S.q_from_rpy(0.5, 0.3, 0.0))]
+    for (pos, q) in poses:                                    # free boxes onto static cylinders r 0.25, l 0.6
+        sb.add_geom(S.GEOM_CYLINDER, (0.25, 0.6), sb.new_space(), pos=pos, quat=q)
+        for k in range(2):
+            side = rng.uniform(0.12, 0.3, size=3)
+            off = [(0.03, 0.02), (0.2, -0.15)][k]
+            b = sb.add_body([pos[0] + off[0], pos[1] + off[1], 1.0 + 0.5 * k], S.q_random(rng), mass=0.6,
+                            inertia=S.box_inertia(0.6, *side))
+            sb.add_geom(S.GEOM_BOX, side, sb.new_space(), body=b)
+    b = sb.add_body([0.0, 10.0, 0.2], lie, mass=2.0, inertia=S.cylinder_inertia(2.0, 0.2, 0.8))   # free on free
+    sb.add_geom(S.GEOM_CYLINDER, (0.2, 0.8), sb.new_space(), body=b)
+    b = sb.add_body([0.05, 10.02, 0.7], S.q_from_rpy(0.1, 0.0, 0.4), mass=0.5, inertia=S.box_inertia(0.5, 0.3, 0.2, 0.1))
+    sb.add_geom(S.GEOM_BOX, (0.3, 0.2, 0.1), sb.new_space(), body=b)
+    sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 GOLDEN = {
     "box_drop": (box_drop, 1500),
     "tilted_box": (tilted_box, 600),
@@ -197,4 +231,5 @@ GOLDEN = {
     "capsules": (capsules, 500),
     "joints": (joints, 600),
     "cylinders": (cylinders, 500),
+    "cylboxes": (cylboxes, 500),
 }

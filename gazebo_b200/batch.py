@@ -59,6 +59,8 @@ def lib():
     L.gzcuda_batch_set_param.argtypes = [vp, C.c_char_p, C.c_double]
     L.gzcuda_batch_get_pairs.argtypes = [vp, ci, dp, ci]
     L.gzcuda_batch_get_contacts.argtypes = [vp, ci, dp, dp, ci]
+    L.gzcuda_batch_get_joint_feedback.argtypes = [vp, dp]
+    L.gzcuda_batch_get_contact_feedback.argtypes = [vp, ci, dp, ci]
     L.gzcuda_batch_last_step_ms.argtypes = [vp, dp, dp]
     L.gzcuda_batch_stage_ms.argtypes = [vp, dp]
     _lib = L
@@ -76,6 +78,7 @@ EXPORTS = [
     "gzcuda_batch_stage_ms", "gzcuda_batch_step_io", "gzcuda_batch_set_profiling",
     "gzcuda_batch_pgs_ms", "gzcuda_batch_get_counters", "gzcuda_batch_get_pgs_debug",
     "gzcuda_batch_get_pgs_profile", "gzcuda_batch_get_pgs_timeline",
+    "gzcuda_batch_get_joint_feedback", "gzcuda_batch_get_contact_feedback",
 ]
 
 
@@ -212,6 +215,17 @@ class Batch:
         d = np.empty((cap, 7))
         n = self._ck(self.L.gzcuda_batch_get_contacts(self.h, world, _p(g), _p(d), cap))
         return g[:n].copy(), d[:n].copy()
+
+    def joint_feedback(self):
+        """dJointFeedback of every persistent joint after the last step: [nj][12] = f1, t1, f2, t2."""
+        fb = np.zeros((self.scene.nj, 12))
+        self._ck(self.L.gzcuda_batch_get_joint_feedback(self.h, _p(fb)))
+        return fb
+
+    def contact_feedback(self, world, cap=1 << 16):
+        fb = np.zeros((cap, 12))
+        n = self._ck(self.L.gzcuda_batch_get_contact_feedback(self.h, world, _p(fb), cap))
+        return fb[:n].copy()
 
     def last_step_ms(self):
         ms = C.c_float(0)

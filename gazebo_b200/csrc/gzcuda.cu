@@ -855,6 +855,40 @@ int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *da
   return ws.n_contacts;
 }
 
+int gzcuda_batch_get_joint_feedback(gzcuda_batch *b, double *fb) {
+  if (!b || !fb) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  const int nj = b->d.nj;
+  if (nj == 0) return 0;
+  double *dev = nullptr;
+  CK(cudaMalloc(&dev, (size_t)12 * nj * sizeof(double)));
+  k_feedback_joint<<<cdiv(nj, 128), 128, 0, b->stream>>>(b->d, dev);
+  cudaError_t e = cudaMemcpyAsync(fb, dev, (size_t)12 * nj * sizeof(double), cudaMemcpyDeviceToHost, b->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+  cudaFree(dev);
+  if (e != cudaSuccess) return fail(GZCUDA_E_CUDA, cudaGetErrorString(e));
+  return nj;
+}
+
+int gzcuda_batch_get_contact_feedback(gzcuda_batch *b, int world, double *fb, int cap) {
+  if (!b || !fb || world < 0 || world >= b->d.n_worlds) return fail(GZCUDA_E_INVALID, "bad argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  WorldStep ws;
+  CK(cudaMemcpy(&ws, b->d.wstep + world, sizeof(ws), cudaMemcpyDeviceToHost));
+  const int n = ws.n_contacts;
+  if (n == 0) return 0;
+  double *dev = nullptr;
+  CK(cudaMalloc(&dev, (size_t)12 * n * sizeof(double)));
+  k_feedback_contact<<<cdiv(n, 128), 128, 0, b->stream>>>(b->d, world, dev);
+  cudaError_t e = cudaMemcpyAsync(fb, dev, (size_t)12 * std::min(n, cap) * sizeof(double), cudaMemcpyDeviceToHost, b->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+  cudaFree(dev);
+  if (e != cudaSuccess) return fail(GZCUDA_E_CUDA, cudaGetErrorString(e));
+  return n;
+}
+
 int gzcuda_batch_last_step_ms(gzcuda_batch *b, float *ms, long *launches) {
   if (!b) return fail(GZCUDA_E_INVALID, "null batch");
   int rc = gzcuda_batch_sync(b);

@@ -549,6 +549,38 @@ __global__ void k_lambda_save(DevBatch B) {
   for (int k = 0; k < j.m; k++) { j.lambda[k] = rows[k].lambda; j.lambda_erp[k] = rows[k].lambda_erp; }
 }
 
+// Joint feedback (dJointFeedback {f1, t1, f2, t2}: quickstep_update_bodies.cpp:79-119, Multiply1_12q1
+// quickstep_util.cpp:42-73): the constraint wrench on each body = sum over the joint's rows of
+// (unscaled J row) * lambda, rows in order.  Computed on demand from the row array of the last
+// step; out[.][12].  One thread per persistent joint / per contact of one world.
+__device__ inline void feedback_rows(const Row *rows, int m, bool two, double *out) {
+  double f[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < m; i++) {
+    const double s = rows[i].lambda;
+    for (int t = 0; t < 6; t++) f[t] += rows[i].J[t] * s;
+    if (two) for (int t = 0; t < 6; t++) f[6 + t] += rows[i].J[6 + t] * s;
+  }
+  for (int t = 0; t < 12; t++) out[t] = f[t];
+}
+
+__global__ void k_feedback_joint(DevBatch B, double *out) {
+  int ji = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ji >= B.nj) return;
+  const Joint &j = B.joint[ji];
+  const WorldInfo wi = B.world[j.world];
+  const bool live = j.m > 0 && B.wstep[j.world].m > 0;
+  feedback_rows(B.row + wi.row0 + j.row0, live ? j.m : 0, j.b2 >= 0, out + 12 * (size_t)ji);
+}
+
+__global__ void k_feedback_contact(DevBatch B, int world, double *out) {
+  const WorldInfo wi = B.world[world];
+  int ci = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ci >= B.wstep[world].n_contacts) return;
+  const Contact &C = B.contact[wi.contact0 + ci];
+  const bool live = B.wstep[world].m > 0 && B.bstep[C.b1].active;
+  feedback_rows(B.row + wi.row0 + C.row0, live ? 3 : 0, C.b2 >= 0, out + 12 * (size_t)ci);
+}
+
 // One thread per body: dxUpdateBodies + dxStepBody.
 __global__ void k_integrate(DevBatch B) {
   int bi = blockIdx.x * blockDim.x + threadIdx.x;

@@ -101,6 +101,15 @@ int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double value);
 int gzcuda_batch_get_pairs(gzcuda_batch *b, int world, int *pairs, int cap);
 int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *data, int cap);
 
+/* Constraint wrenches of the last step (dJointFeedback {f1[3], t1[3], f2[3], t2[3]}, world frame:
+ * dJointSetFeedback, filled by quickstep_update_bodies.cpp:79-119; ODEJoint::GetForceTorque
+ * ODEJoint.cc:1010-1090 and the contact wrenches of ODEPhysics::UpdatePhysics ODEPhysics.cc:422-449
+ * read them).  Joints: fb[nj][12] in scene joint order; contacts of one world: fb[n][12] in the
+ * order of gzcuda_batch_get_contacts, body 1 = the contact joint's first body after dJointAttach's
+ * swap.  A joint or contact whose island was not stepped reports zeros.  Return the count. */
+int gzcuda_batch_get_joint_feedback(gzcuda_batch *b, double *fb);
+int gzcuda_batch_get_contact_feedback(gzcuda_batch *b, int world, double *fb, int cap);
+
 /* Instrumentation: device time in ms of the last gzcuda_batch_step call (CUDA events on the
  * batch stream) and the number of kernel launches it issued. */
 int gzcuda_batch_last_step_ms(gzcuda_batch *b, float *ms, long *launches);

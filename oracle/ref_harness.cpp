@@ -81,6 +81,8 @@ struct RefWorld {
   std::vector<int> joint_type;
   std::vector<HingePD> pd;
   std::vector<dJointID> contact_joints;       // created this step, creation order
+  bool feedback = false;                      // gzref_enable_feedback: dJointSetFeedback on joints and contacts
+  std::vector<dJointFeedback> joint_fb, contact_fb;
   std::vector<std::pair<int,int>> pairs;      // colliders of this step
   std::vector<ContactRec> contacts;           // contacts of this step
   dContactGeom contactCollisions[MAX_COLLIDE_RETURNS];
@@ -241,6 +243,13 @@ void update_collision(RefBatch *B, RefWorld *w) {
   }
   for (size_t i = 0; i < w->pairs.size(); ++i)
     collide_pair(B, w, w->pairs[i].first, w->pairs[i].second);
+  if (w->feedback) {   // ODEPhysics.cc:1319: dJointSetFeedback(contact_joint, &contactFeedback->feedbacks[j])
+    w->contact_fb.assign(w->contact_joints.size(), dJointFeedback());
+    for (size_t i = 0; i < w->contact_joints.size(); ++i) {
+      memset(&w->contact_fb[i], 0, sizeof(dJointFeedback));
+      dJointSetFeedback(w->contact_joints[i], &w->contact_fb[i]);
+    }
+  }
 }
 
 // ---- plugin stand-in: PD-tracked sinusoid on hinge joints -------------------
@@ -677,6 +686,40 @@ void gzref_get_joint_state(void *h, double *lambda, double *lambda_erp, double *
       cum_angle[j] = (w->joint_type[k] == GZ_JOINT_HINGE) ? ((dxJointHinge *)jt)->cumulative_angle : 0.0;
       j++;
     }
+}
+
+// ODEJoint::SetProvideFeedback (ODEJoint.cc:1262-1275) on every joint, contact feedback as when a
+// contact subscriber exists.  Does not change the dynamics (quickstep keeps a copy of J).
+void gzref_enable_feedback(void *h) {
+  RefBatch *B = static_cast<RefBatch *>(h);
+  for (RefWorld *w : B->worlds) {
+    w->feedback = true;
+    w->joint_fb.assign(w->joints.size(), dJointFeedback());
+    for (size_t j = 0; j < w->joints.size(); ++j) {
+      memset(&w->joint_fb[j], 0, sizeof(dJointFeedback));
+      dJointSetFeedback(w->joints[j], &w->joint_fb[j]);
+    }
+  }
+}
+
+static void fb_copy(const dJointFeedback &f, double *o) {
+  for (int k = 0; k < 3; k++) { o[k] = f.f1[k]; o[3 + k] = f.t1[k]; o[6 + k] = f.f2[k]; o[9 + k] = f.t2[k]; }
+}
+
+void gzref_get_joint_feedback(void *h, double *out) {
+  RefBatch *B = static_cast<RefBatch *>(h);
+  for (size_t wi = 0; wi < B->worlds.size(); ++wi) {
+    RefWorld *w = B->worlds[wi];
+    for (size_t j = 0; j < w->joint_fb.size(); ++j) fb_copy(w->joint_fb[j], out + 12 * (B->joint_off[wi] + j));
+  }
+}
+
+int gzref_get_contact_feedback(void *h, int world, double *out, int cap) {
+  RefBatch *B = static_cast<RefBatch *>(h);
+  RefWorld *w = B->worlds[world];
+  int n = (int)w->contact_fb.size();
+  for (int i = 0; i < n && i < cap; ++i) fb_copy(w->contact_fb[i], out + 12 * i);
+  return n;
 }
 
 }  // extern "C"

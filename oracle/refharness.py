@@ -50,6 +50,9 @@ def _load(flavour):
     lib.gzref_get_body_flags.argtypes = [C.c_void_p, C.c_void_p]
     lib.gzref_get_stats.argtypes = [C.c_void_p] * 4
     lib.gzref_get_joint_state.argtypes = [C.c_void_p] * 4
+    lib.gzref_enable_feedback.argtypes = [C.c_void_p]
+    lib.gzref_get_joint_feedback.argtypes = [C.c_void_p, C.c_void_p]
+    lib.gzref_get_contact_feedback.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
     _libs[flavour] = lib
     return lib
 
@@ -128,3 +131,17 @@ class RefBatch:
         lam, lam_erp, cum = np.empty((nj, 6)), np.empty((nj, 6)), np.empty(nj)
         self.lib.gzref_get_joint_state(self.h, _p(lam), _p(lam_erp), _p(cum))
         return lam, lam_erp, cum
+
+    def enable_feedback(self):
+        """dJointSetFeedback on every persistent joint and, from the next step on, every contact joint."""
+        self.lib.gzref_enable_feedback(self.h)
+
+    def joint_feedback(self):
+        fb = np.zeros((self.scene.nj, 12))
+        self.lib.gzref_get_joint_feedback(self.h, _p(fb))
+        return fb
+
+    def contact_feedback(self, world, cap=1 << 16):
+        fb = np.zeros((cap, 12))
+        n = self.lib.gzref_get_contact_feedback(self.h, world, _p(fb), cap)
+        return fb[:n].copy()

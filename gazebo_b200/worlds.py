@@ -168,10 +168,15 @@ def chain_worlds(n_worlds=256, n_links=50, config=5, first_world=0):
     return sb.finish()
 
 
-def pioneer_worlds(n_worlds=1024, config=3, first_world=0):
+def pioneer_worlds(n_worlds=1024, config=3, first_world=0, drive=False, torque=5.0):
     """C3: pioneer2dx restated (asset not vendored in the reference): chassis box + castor
     sphere on one link, two cylinder wheels on hinge joints about y.  Returns
-    (Scene, wheel_cmd[n_worlds][2]) = target wheel joint velocities (rad/s)."""
+    (Scene, wheel_cmd[n_worlds][2]) = target wheel joint velocities (rad/s).
+    drive=True: the wheel hinges run their velocity motor (dParamVel = wheelSpeed / wheelRadius,
+    dParamFMax = torque: Joint::SetParam("vel" / "fmax"), the way diff-drive plugins command wheels
+    through the solver).  This fork's DiffDrivePlugin::OnUpdate (plugins/DiffDrivePlugin.cc:100-122)
+    instead calls Joint::SetVelocity -> SetVelocityMaximal (ODEHingeJoint.cc:153-156), a host write
+    of the wheel link velocities every update: that is gzcuda_batch_set_body_state on this side."""
     sb = S.SceneBuilder()
     cmds = []
     for w in range(n_worlds):
@@ -184,14 +189,18 @@ def pioneer_worlds(n_worlds=1024, config=3, first_world=0):
         sb.add_geom(S.GEOM_SPHERE, (0.04,), space, body=chassis, pos=(-0.2, 0, -0.12),
                     mu=0.0, mu2=0.0, slip1=1.0, slip2=1.0)
         qw = S.q_from_axis_angle([1, 0, 0], math.pi / 2)
-        wheels = []
-        for sy in (+1, -1):
-            wb = sb.add_body([0.1, sy * 0.17, 0.11], qw, 1.5, [0.0051, 0.0051, 0.0090, 0, 0, 0])
-            sb.add_geom(S.GEOM_CYLINDER, (0.11, 0.05), space, body=wb)
-            sb.add_hinge(wb, chassis, [0.1, sy * 0.17, 0.11], [0, 1, 0])
-            wheels.append(wb)
         v, yaw = 0.2, rng.uniform(-0.5, 0.5)
         sep, r = 0.34, 0.11
-        cmds.append([(v + yaw * sep / 2) / r, (v - yaw * sep / 2) / r])
+        cmd = [(v + yaw * sep / 2) / r, (v - yaw * sep / 2) / r]
+        wheels = []
+        for k, sy in enumerate((+1, -1)):
+            wb = sb.add_body([0.1, sy * 0.17, 0.11], qw, 1.5, [0.0051, 0.0051, 0.0090, 0, 0, 0])
+            sb.add_geom(S.GEOM_CYLINDER, (0.11, 0.05), space, body=wb)
+            if drive:
+                sb.add_hinge(wb, chassis, [0.1, sy * 0.17, 0.11], [0, 1, 0], vel=cmd[k], fmax=torque)
+            else:
+                sb.add_hinge(wb, chassis, [0.1, sy * 0.17, 0.11], [0, 1, 0])
+            wheels.append(wb)
+        cmds.append(cmd)
         sb.end_world()
     return sb.finish(), np.array(cmds)

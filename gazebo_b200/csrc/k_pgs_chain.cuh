@@ -304,7 +304,7 @@ __global__ void __launch_bounds__(32) k_pgs_chain(DevBatch B, PgsCfg cfg, int cl
     // instrumentation: rounds the warp ran, this world's period * 256 + k, SM cycles of the sweeps
     ws.pad[0] = rounds; ws.pad[1] = R * 256 + GZ_CHAIN_K; ws.n_fric = (int)(t1 - t0);
   }
-  if (lane == 0) { B.prof[16 + 2 * w] = g0; B.prof[16 + 2 * w + 1] = gtimer(); }
+  if (lane == 0) { B.prof[16 + 2 * w] = g0; B.prof[16 + 2 * w + 1] = (gtimer() & ~511ull) | smid(); }
   if (PROF && lane == 0) {
     for (int q = 0; q < 5; q++) atomicAdd(&B.prof[8 + q], (unsigned long long)pc[q]);
     atomicAdd(&B.prof[13], (unsigned long long)(t1 - t0));

@@ -67,6 +67,12 @@ __device__ __forceinline__ unsigned long long gtimer() {
   return t;
 }
 
+__device__ __forceinline__ unsigned smid() {
+  unsigned s;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
+  return s & 511u;
+}
+
 // ---- mbarrier / bulk-copy wrappers (PTX ISA: mbarrier, cp.async.bulk) ---------------------------
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -419,7 +425,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
       ws.pad[0] = rounds; ws.pad[1] = R * 256 + k; ws.n_fric = (int)(t1 - t0);
     }
   }
-  if (live && lw == 0) { B.prof[16 + 2 * w] = g0; B.prof[16 + 2 * w + 1] = gtimer(); }
+  if (live && lw == 0) { B.prof[16 + 2 * w] = g0; B.prof[16 + 2 * w + 1] = (gtimer() & ~511ull) | smid(); }   // low 9 bits: the SM it ran on
   if (prof && lane == 0) {
     for (int q = 0; q < 5; q++) atomicAdd(&B.prof[q], (unsigned long long)pc[q]);
     atomicAdd(&B.prof[5], (unsigned long long)rounds);

@@ -21,3 +21,10 @@ for a, c in zip(edges[:-1], edges[1:]):
     mid = (a + c) / 2
     fl = ok & (st <= mid) & (en > mid)
     print("  t=%5.0f us: in flight chain %4d regular worlds %4d" % (mid, (fl & (k == 16)).sum(), (fl & (k != 16)).sum()))
+sm = tl[:, 1] & 511
+for tq in (100.0, 300.0):
+    fl = ok & (st <= tq) & (en > tq)
+    cc = np.bincount(sm[fl & (k == 16)], minlength=160)[:148]; rr = np.bincount(sm[fl & (k != 16)], minlength=160)[:148]
+    print("  t=%.0f us, per SM: chain warps min %d mean %.1f max %d | SMs by chain warps %s | regular worlds per SM by chain warps %s" % (
+        tq, cc.min(), cc.mean(), cc.max(), {int(x): int((cc == x).sum()) for x in np.unique(cc)},
+        {int(x): round(float(rr[cc == x].mean()), 1) for x in np.unique(cc)}))

@@ -31,6 +31,9 @@ struct gzcuda_batch {
   DevBatch d;
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream_hi = nullptr;   // the long-period part of k_pgs when it is launched in two parts (GZCUDA_PGS_RSPLIT)
+  cudaEvent_t ev_join_hi = nullptr;
+  int pgs_rsplit = 0;
   cudaStream_t stream_chain[GZ_CHAIN_NCLS] = {};   // the chain-mode PGS launches (one per shared-memory size class) run
   cudaEvent_t ev_fork = nullptr, ev_join[GZ_CHAIN_NCLS] = {};   // beside the regular one: fork / join by events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -124,6 +127,8 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   if (b->ev_fork) cudaEventDestroy(b->ev_fork);
   for (auto &e : b->ev_join) if (e) cudaEventDestroy(e);
   for (auto &st : b->stream_chain) if (st) cudaStreamDestroy(st);
+  if (b->stream_hi) cudaStreamDestroy(b->stream_hi);
+  if (b->ev_join_hi) cudaEventDestroy(b->ev_join_hi);
   if (b->stream) cudaStreamDestroy(b->stream);
   delete b;
 }
@@ -355,6 +360,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if (const char *e = getenv("GZCUDA_PGS_KMAX")) d.pgs_kmax = std::max(d.pgs_kmin, std::min(16, atoi(e)));
   for (int *kk : {&d.pgs_kmin, &d.pgs_kmax}) { int v = 1; while (2 * v <= *kk) v <<= 1; *kk = v; }
   PgsCfg &c = b->pgs;
+  c.part = 0; c.rsplit = 0;
   c.nbp = std::max(max_nb, 1);
   size_t smem = 52 * 1024;
   if (const char *e = getenv("GZCUDA_PGS_SMEM_KB")) smem = (size_t)atoi(e) * 1024;
@@ -435,6 +441,10 @@ gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params
                                               b->reg_first ? (q >= 2 ? phi : plo) : std::min(plo, phi + (GZ_CHAIN_NCLS - 1 - q))) == cudaSuccess &&
            cudaEventCreateWithFlags(&b->ev_join[q], cudaEventDisableTiming) == cudaSuccess;
   }
+  if (const char *e = getenv("GZCUDA_PGS_RSPLIT")) b->pgs_rsplit = std::max(0, atoi(e));
+  if (b->pgs_rsplit > 0)
+    ok = ok && cudaStreamCreateWithPriority(&b->stream_hi, cudaStreamNonBlocking, phi0) == cudaSuccess &&
+         cudaEventCreateWithFlags(&b->ev_join_hi, cudaEventDisableTiming) == cudaSuccess;
   if (!ok) { fail(GZCUDA_E_CUDA, "stream/event creation failed"); gzcuda_batch_destroy(b); return nullptr; }
   if (build(b, scene, params) != 0) { gzcuda_batch_destroy(b); return nullptr; }
   return b;
@@ -477,8 +487,20 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     cudaEventRecord(b->ev_fork, b->stream);
     kp<<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
   }
+  const bool split = chain_on && !b->reg_first && b->pgs_rsplit > 0;
+  PgsCfg cfg_lo = b->pgs;
+  if (split) {   // the long-period warps of k_pgs first, above everything else
+    PgsCfg cfg_hi = b->pgs;
+    cfg_hi.part = 1; cfg_hi.rsplit = b->pgs_rsplit;
+    cfg_lo.part = 2; cfg_lo.rsplit = b->pgs_rsplit;
+    cudaEventRecord(b->ev_fork, b->stream);
+    cudaStreamWaitEvent(b->stream_hi, b->ev_fork, 0);
+    kp<<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream_hi>>>(d, cfg_hi);
+    cudaEventRecord(b->ev_join_hi, b->stream_hi);
+    b->last_launches++;
+  }
   if (chain_on) {
-    if (!b->reg_first) cudaEventRecord(b->ev_fork, b->stream);
+    if (!b->reg_first && !split) cudaEventRecord(b->ev_fork, b->stream);
     for (int q = GZ_CHAIN_NCLS - 1; q >= 0; q--) {   // the large worlds first: they take longest
       cudaStreamWaitEvent(b->stream_chain[q], b->ev_fork, 0);
       kc<<<W, 32, b->pgs_chain_smem[q], b->stream_chain[q]>>>(d, b->pgs_chain[q], q);
@@ -487,8 +509,9 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     }
   }
   if (!(chain_on && b->reg_first)) {
-    kp<<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, b->pgs);
+    kp<<<W + GZ_NBUCKET, 32, b->pgs_smem, b->stream>>>(d, cfg_lo);
   }
+  if (split) cudaStreamWaitEvent(b->stream, b->ev_join_hi, 0);
   if (chain_on)
     for (int q = 0; q < GZ_CHAIN_NCLS; q++) cudaStreamWaitEvent(b->stream, b->ev_join[q], 0);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);

@@ -29,7 +29,9 @@ namespace gz {
 #define GZ_STAGE_DOUBLES (GZ_RING_G * GZ_ROUND_DOUBLES)
 #define GZ_RING_DOUBLES (GZ_RING_D * GZ_STAGE_DOUBLES + 2 * GZ_RING_D)   // records + one mbarrier per stage (padded)
 
-struct PgsCfg { int smem_doubles, nbp, wpw_max; };
+// part / rsplit: k_pgs can be launched in two parts (GZCUDA_PGS_RSPLIT): part 1 takes the warps whose period is
+// >= rsplit (they run longest) and goes first at high priority, part 2 the others; part 0 = all warps
+struct PgsCfg { int smem_doubles, nbp, wpw_max, part, rsplit; };
 
 // the constants of one row, in registers
 struct RowRegs {
@@ -209,6 +211,8 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   const int bucket = bk_row(B, GZ_BK_SBUCKET)[lo_i];
   const int k = 1 << ((bucket / GZ_NRUNG) % 5), LW = 2 * k, R = rung_value(bucket % GZ_NRUNG);
   if (bucket >= 5 * GZ_NRUNG) return;          // chain-mode worlds: k_pgs_chain (k_pgs_chain.cuh)
+  if (cfg.part == 1 && R < cfg.rsplit) return;
+  if (cfg.part == 2 && R >= cfg.rsplit) return;
   const int wpw = bucket_wpw(B, bucket);
   const int wb = cta - swarp0[lo_i];
   const size_t slab_rec0 = (size_t)bk_row(B, GZ_BK_REC0)[bucket] + (size_t)wb * R * 16;

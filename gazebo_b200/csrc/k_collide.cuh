@@ -17,6 +17,7 @@
 #include "k_boxbox.cuh"
 #include "../../include/gz_detmath.h"
 #include "k_cylbox.cuh"
+#include "k_mpr.cuh"
 
 namespace gz {
 
@@ -283,7 +284,10 @@ __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) 
   else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_plane(g2, g1, o); rev = true; }
   else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_BOX) n = col_cylinder_box(g1, g2, o);
   else if (t1 == GZ_GEOM_BOX && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_box(g2, g1, o); rev = true; }
-  else n = 0;   // pairs not implemented yet are listed in DESIGN.md (cylinder vs capsule / cylinder: libccd MPR)
+  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_CYLINDER) n = col_mpr(g1, false, g2, o);
+  else if (t1 == GZ_GEOM_CAPSULE && t2 == GZ_GEOM_CYLINDER) n = col_mpr(g1, true, g2, o);
+  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_CAPSULE) { n = col_mpr(g2, true, g1, o); rev = true; }
+  else n = 0;
   if (rev)
     for (int i = 0; i < n; i++) { o.nrm[i][0] = -o.nrm[i][0]; o.nrm[i][1] = -o.nrm[i][1]; o.nrm[i][2] = -o.nrm[i][2]; }
   return n;

@@ -220,6 +220,35 @@ def cylboxes():
     return sb.finish(), S.default_params(), None
 
 
+def cylcyl():
+    """cylinder-cylinder and capsule-cylinder (libccd MPR, collision_libccd.cpp:305-344): cylinders
+    dropped onto static cylinders (cap on cap, barrel across barrel, tilted), capsules dropped onto
+    static cylinders, and a free cylinder landing on a free lying cylinder."""
+    sb = S.SceneBuilder()
+    rng = np.random.Generator(np.random.PCG64(91))
+    sb.begin_world()
+    sb.add_ground_plane()
+    lie = S.q_from_axis_angle([0, 1, 0], math.pi / 2)
+    liey = S.q_from_axis_angle([1, 0, 0], math.pi / 2)
+    statics = [((0, 0, 0.3), (1, 0, 0, 0)), ((3, 0, 0.25), lie), ((6, 0, 0.4), S.q_from_rpy(0.5, 0.3, 0.0))]
+    drops = [((1, 0, 0, 0), (0.03, 0.02)), (liey, (0.0, 0.05)), (S.q_from_rpy(0.3, 0.9, 0.2), (0.05, -0.02))]
+    for (pos, q), (dq, off) in zip(statics, drops):          # free cylinders onto static cylinders r 0.25, l 0.6
+        sb.add_geom(S.GEOM_CYLINDER, (0.25, 0.6), sb.new_space(), pos=pos, quat=q)
+        b = sb.add_body([pos[0] + off[0], pos[1] + off[1], 1.1], dq, mass=0.8, inertia=S.cylinder_inertia(0.8, 0.12, 0.3))
+        sb.add_geom(S.GEOM_CYLINDER, (0.12, 0.3), sb.new_space(), body=b)
+    for i, (pos, q) in enumerate(statics):                   # capsules onto static cylinders
+        p2 = (pos[0], pos[1] + 4.0, pos[2])
+        sb.add_geom(S.GEOM_CYLINDER, (0.25, 0.6), sb.new_space(), pos=p2, quat=q)
+        b = sb.add_body([p2[0] + 0.04, p2[1] - 0.03, 1.2], S.q_random(rng), mass=0.5, inertia=S.cylinder_inertia(0.5, 0.08, 0.3))
+        sb.add_geom(S.GEOM_CAPSULE, (0.08, 0.3), sb.new_space(), body=b)
+    b = sb.add_body([0.0, 9.0, 0.2], lie, mass=2.0, inertia=S.cylinder_inertia(2.0, 0.2, 0.8))      # free on free
+    sb.add_geom(S.GEOM_CYLINDER, (0.2, 0.8), sb.new_space(), body=b)
+    b = sb.add_body([0.03, 9.02, 0.75], liey, mass=0.5, inertia=S.cylinder_inertia(0.5, 0.1, 0.5))
+    sb.add_geom(S.GEOM_CYLINDER, (0.1, 0.5), sb.new_space(), body=b)
+    sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 GOLDEN = {
     "box_drop": (box_drop, 1500),
     "tilted_box": (tilted_box, 600),
@@ -232,4 +261,5 @@ GOLDEN = {
     "joints": (joints, 600),
     "cylinders": (cylinders, 500),
     "cylboxes": (cylboxes, 500),
+    "cylcyl": (cylcyl, 400),
 }

@@ -278,7 +278,7 @@ __device__ inline int cb_clip_box_to_cylinder(CylBox &D, COut &o) {
 }
 
 // dCollideCylinderBox / sCylinderBoxData::PerformCollisionChecking (:985-1038)
-__device__ inline int col_cylinder_box(const Geom &c, const Geom &b, COut &o) {
+__device__ __noinline__ int col_cylinder_box(const Geom &c, const Geom &b, COut &o) {
   CylBox D;
   D.Rc = c.R; D.pc = c.pos; D.Rb = b.R; D.pb = b.pos;
   cb_col(c.R, 2, D.axis);

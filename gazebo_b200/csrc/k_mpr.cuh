@@ -339,7 +339,7 @@ __device__ inline void mpr_find_pos(const CcdSupp *P, double *pos) {
 }
 
 // ccdCollide + ccdMPRPenetration: 0 or 1 contact; normal = -dir
-__device__ inline int col_mpr(const Geom &g1, bool cap1, const Geom &g2, COut &o) {
+__device__ __noinline__ int col_mpr(const Geom &g1, bool cap1, const Geom &g2, COut &o) {
   CcdObj o1, o2;
   ccd_obj(o1, g1, cap1);
   ccd_obj(o2, g2, false);

@@ -38,6 +38,7 @@ def lib():
     L.gzcuda_batch_destroy.argtypes = [vp]
     L.gzcuda_batch_step.argtypes = [vp, ci]
     L.gzcuda_batch_step_io.argtypes = [vp, ci, dp, dp]
+    L.gzcuda_batch_step_log.argtypes = [vp, ci, ci, dp, ci]
     L.gzcuda_batch_set_profiling.argtypes = [vp, ci]
     L.gzcuda_batch_pgs_ms.argtypes = [vp, dp, dp]
     L.gzcuda_batch_get_counters.argtypes = [vp, dp, ci]
@@ -78,7 +79,7 @@ EXPORTS = [
     "gzcuda_batch_stage_ms", "gzcuda_batch_step_io", "gzcuda_batch_set_profiling",
     "gzcuda_batch_pgs_ms", "gzcuda_batch_get_counters", "gzcuda_batch_get_pgs_debug",
     "gzcuda_batch_get_pgs_profile", "gzcuda_batch_get_pgs_timeline",
-    "gzcuda_batch_get_joint_feedback", "gzcuda_batch_get_contact_feedback",
+    "gzcuda_batch_get_joint_feedback", "gzcuda_batch_get_contact_feedback", "gzcuda_batch_step_log",
 ]
 
 
@@ -215,6 +216,14 @@ class Batch:
         d = np.empty((cap, 7))
         n = self._ck(self.L.gzcuda_batch_get_contacts(self.h, world, _p(g), _p(d), cap))
         return g[:n].copy(), d[:n].copy()
+
+    def step_log(self, n_steps, every, frames=None):
+        """n_steps steps; returns frames[n_steps // every][nb][13] = pos, quat, lvel, avel after every `every`-th step."""
+        nf = n_steps // every
+        if frames is None:
+            frames = np.empty((max(nf, 1), self.scene.nb, 13))
+        n = self._ck(self.L.gzcuda_batch_step_log(self.h, n_steps, every, _p(frames), nf))
+        return frames[:n]
 
     def joint_feedback(self):
         """dJointFeedback of every persistent joint after the last step: [nj][12] = f1, t1, f2, t2."""

@@ -31,6 +31,9 @@ struct gzcuda_batch {
   DevBatch d;
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream_copy = nullptr;   // gzcuda_batch_step_log: device -> host copies of the state frames, beside the steps
+  cudaEvent_t ev_frame[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+  double *log_frame[2] = {nullptr, nullptr};   // two device staging frames [nb][13]
   cudaStream_t stream_hi = nullptr;   // the long-period part of k_pgs when it is launched in two parts (GZCUDA_PGS_RSPLIT)
   cudaEvent_t ev_join_hi = nullptr;
   int pgs_rsplit = 0;
@@ -127,6 +130,10 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   if (b->ev_fork) cudaEventDestroy(b->ev_fork);
   for (auto &e : b->ev_join) if (e) cudaEventDestroy(e);
   for (auto &st : b->stream_chain) if (st) cudaStreamDestroy(st);
+  if (b->stream_copy) cudaStreamDestroy(b->stream_copy);
+  for (auto &e : b->ev_frame) if (e) cudaEventDestroy(e);
+  for (auto &e : b->ev_copied) if (e) cudaEventDestroy(e);
+  for (auto &f : b->log_frame) if (f) cudaFree(f);
   if (b->stream_hi) cudaStreamDestroy(b->stream_hi);
   if (b->ev_join_hi) cudaEventDestroy(b->ev_join_hi);
   if (b->stream) cudaStreamDestroy(b->stream);
@@ -585,6 +592,54 @@ int gzcuda_batch_step_io(gzcuda_batch *b, int n_steps, const double *wrench_in, 
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(b->stream));
   return 0;
+}
+
+// State log at a decimated rate (the WorldState stream of gz log / ~/pose/info, gazebo/physics/World.cc:2757-2850,
+// gazebo/util/LogRecord.cc:193): n_steps steps in one call, the state of every body after each `every`-th step copied into
+// frames[frame][nb][13] (pos 3, quat 4, lvel 3, avel 3) by a copy stream that runs beside the next steps (two device staging
+// frames), no host synchronisation until the end.  Returns the number of frames written.
+int gzcuda_batch_step_log(gzcuda_batch *b, int n_steps, int every, double *frames, int max_frames) {
+  if (!b || n_steps < 0 || every <= 0 || !frames || max_frames < 0) return fail(GZCUDA_E_INVALID, "bad argument");
+  CK(cudaSetDevice(b->device));
+  const int T = 128, nb = std::max(b->d.nb, 1);
+  const size_t frame_doubles = (size_t)13 * b->d.nb;
+  if (!b->stream_copy) {
+    CK(cudaStreamCreateWithFlags(&b->stream_copy, cudaStreamNonBlocking));
+    for (int f = 0; f < 2; f++) {
+      CK(cudaEventCreateWithFlags(&b->ev_frame[f], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&b->ev_copied[f], cudaEventDisableTiming));
+      CK(cudaMalloc(&b->log_frame[f], std::max<size_t>(frame_doubles, 1) * sizeof(double)));
+    }
+  }
+  b->last_launches = 0;
+  CK(cudaEventRecord(b->ev0, b->stream));
+  int done = 0, nframes = 0;
+  double *const io_out = b->d.io_out;
+  while (done < n_steps) {
+    const int n = std::min(every, n_steps - done);
+    int rc = run_steps(b, n);
+    if (rc) { b->d.io_out = io_out; return rc; }
+    done += n;
+    if (n == every && nframes < max_frames) {
+      const int f = nframes & 1;
+      if (nframes >= 2) CK(cudaStreamWaitEvent(b->stream, b->ev_copied[f], 0));   // the frame's previous copy has left
+      b->d.io_out = b->log_frame[f];
+      k_gather_state<<<cdiv(nb, T), T, 0, b->stream>>>(b->d);
+      b->d.io_out = io_out;
+      b->last_launches++;
+      CK(cudaEventRecord(b->ev_frame[f], b->stream));
+      CK(cudaStreamWaitEvent(b->stream_copy, b->ev_frame[f], 0));
+      CK(cudaMemcpyAsync(frames + (size_t)nframes * frame_doubles, b->log_frame[f], frame_doubles * sizeof(double),
+                         cudaMemcpyDeviceToHost, b->stream_copy));
+      CK(cudaEventRecord(b->ev_copied[f], b->stream_copy));
+      nframes++;
+    }
+  }
+  CK(cudaEventRecord(b->ev1, b->stream));
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaStreamSynchronize(b->stream_copy));
+  return nframes;
 }
 
 int gzcuda_batch_set_profiling(gzcuda_batch *b, int on) {

@@ -52,6 +52,11 @@ int gzcuda_batch_step(gzcuda_batch *b, int n_steps);
  * n_steps, downloads state_out[nb][13] = pos(3) quat(4) lvel(3) avel(3) (what ODELink::MoveCallback
  * reads, ODELink.cc:142-178; NULL = none).  Pinned host memory makes the copies asynchronous. */
 int gzcuda_batch_step_io(gzcuda_batch *b, int n_steps, const double *wrench_in, double *state_out);
+/* State log at a decimated rate (the WorldState stream behind `gz log` and ~/pose/info: gazebo/physics/World.cc:2757-2850,
+ * gazebo/util/LogRecord.cc:193,809): n_steps steps in one call; after every `every`-th step the state of all bodies is
+ * copied to frames[frame][nb][13] (position 3, quaternion 4, linear 3 and angular 3 velocity; pinned host memory makes the
+ * copies run beside the following steps).  Returns the number of frames written (<= max_frames) or a negative error. */
+int gzcuda_batch_step_log(gzcuda_batch *b, int n_steps, int every, double *frames, int max_frames);
 /* The two halves, for callers that need Events::beforePhysicsUpdate between them
  * (gazebo/physics/World.cc:755-786). */
 int gzcuda_batch_update_collision(gzcuda_batch *b);   /* ODEPhysics::UpdateCollision */

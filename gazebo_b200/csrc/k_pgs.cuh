@@ -146,6 +146,7 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   const int m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc, nb = wi.nb;
   WSched *wsch = reinterpret_cast<WSched *>(B.wsched) + w;
   bool refuse = (m == 0 || m > 16 * GZ_RMAX);
+  long long tc0 = clock64();   // GZCUDA_PGS_PROF: cycles of the phases, summed over worlds into prof[6], [7], [15]
   int *order = B.order + wi.row0;
   Row *rows = B.row + wi.row0;
   WScratch S = wscratch(B, w);
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
       S.rb2[pos] = rows[i].b2;
     }
     __syncwarp();
+    if (B.pgs_prof && lane == 0) { const long long c = clock64(); atomicAdd(&B.prof[6], (unsigned long long)(c - tc0)); tc0 = c; }
     // chain mode needs the whole world resident in k_pgs_chain's shared memory: accumulators, fixed
     // part, lambda[m][2], m + 1 records, and (checked once R is known) the heads [R][GZ_CHAIN_K]
     const int res_doubles = 12 * (max(B.max_nb, 1) + 1) + GZ_CHAIN_FIXED_DOUBLES + 2 * m + (m + 1) * GZ_REC;
@@ -255,6 +257,7 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
         rb += okm ? __ffs(okm) - 1 : __popc(vm);   // none works: go on after the probed rungs (rb stays warp-uniform)
         __syncwarp();
       }
+      if (B.pgs_prof && lane == 0) { const long long c = clock64(); atomicAdd(&B.prof[7], (unsigned long long)(c - tc0)); tc0 = c; }
       R = rung_value(min(rb, GZ_NRUNG - 1));
       bool done = false;
       for (int attempt = 0; !done; attempt++) {
@@ -329,6 +332,7 @@ __global__ void __launch_bounds__(32) k_schedule(DevBatch B) {
   }
   const int nslots = R * k;
   __syncwarp();
+  if (B.pgs_prof && lane == 0) { const long long c = clock64(); atomicAdd(&B.prof[15], (unsigned long long)(c - tc0)); tc0 = c; }
   // ---- rows: lambda index, stage, run membership
   if (!chain) {
     for (int pos = lane; pos < m; pos += 32) {

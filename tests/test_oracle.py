@@ -99,3 +99,36 @@ def test_oracle_passes_the_acceptance_cases(oracle, case, monkeypatch):
     from tests import test_acceptance_gpu as acc
     monkeypatch.setattr(acc, "_batch", lambda sc, p: oracle.RefBatch(sc, p, mode=1))
     getattr(acc, case)()
+
+
+def test_feedback_of_a_resting_box_is_its_weight(oracle):
+    """dJointFeedback of contact joints (quickstep_update_bodies.cpp:79-119): a box at rest on the
+    plane is held up by its four contacts, whose feedback forces sum to m g on the box (ForceTorque-
+    style acceptance: the harness hook the GPU feedback getters are compared with is itself right)."""
+    sc, p, _ = scenes.box_drop()
+    r = oracle.RefBatch(sc, p, mode=1)
+    r.enable_feedback()
+    r.step(2500)
+    fb = r.contact_feedback(0)
+    assert fb.shape[0] >= 3
+    mass = float(np.asarray(sc.body_mass)[0]) if hasattr(sc, "body_mass") else None
+    total = fb[:, 0:3].sum(axis=0)
+    assert abs(total[0]) < 1e-6 and abs(total[1]) < 1e-6 and total[2] > 0
+    if mass is not None:
+        # 0.99 m g: the lambda solve is low-pass filtered (SMOOTH_LAMBDA, smooth_contacts = 0.01,
+        # quickstep_pgs_lcp.cpp:628-640), and the feedback reports that filtered lambda
+        assert abs(total[2] - 9.8 * mass) < 0.02 * 9.8 * mass
+
+
+def test_feedback_of_a_hanging_chain(oracle):
+    """Joint feedback of a chain hanging from the world: once it swings, the top hinge carries more
+    than any other and every joint's force pair is equal and opposite (f1 = -f2)."""
+    sc, p, _ = scenes.chain()
+    r = oracle.RefBatch(sc, p, mode=1)
+    r.enable_feedback()
+    r.step(300)
+    fb = r.joint_feedback()
+    assert np.isfinite(fb).all() and np.abs(fb[:, 0:3]).max() > 0
+    two = np.linalg.norm(fb[:, 6:9], axis=1) > 0           # joints between two links (the others hang from the world)
+    assert two.sum() >= fb.shape[0] - 4
+    assert np.abs(fb[two, 0:3] + fb[two, 6:9]).max() < 1e-9 * max(1.0, np.abs(fb).max())

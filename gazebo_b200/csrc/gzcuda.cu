@@ -47,6 +47,7 @@ struct gzcuda_batch {
   bool stage_valid = false;
   bool have_pd = false;
   size_t pgs_smem = 0, pgs_chain_smem[GZ_CHAIN_NCLS] = {};
+  bool has_cylinders = false;         // picks the k_narrow instantiation with the cylinder-box and MPR colliders
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
   int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
@@ -259,6 +260,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       G.scat = scat[G.space]; G.scol = scol[G.space];
       G.bitmask = sc->geom_collide_bitmask[g];
       G.max_contacts = sc->geom_max_contacts[g];
+      if (G.type == GZ_GEOM_CYLINDER) b->has_cylinders = true;
     }
     // static upper bound on candidate pairs of this world
     const int n = g1 - g0;
@@ -464,7 +466,8 @@ static int launch_collision(gzcuda_batch *b) {
   const int W = d.n_worlds, T = 128;
   k_geom<<<cdiv(std::max(d.ng, 1), T), T, 0, b->stream>>>(d);
   k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
-  k_narrow<<<dim3(cdiv(d.max_pair_cap, T), W), T, 0, b->stream>>>(d);
+  if (b->has_cylinders) k_narrow<true><<<dim3(cdiv(d.max_pair_cap, T), W), T, 0, b->stream>>>(d);
+  else k_narrow<false><<<dim3(cdiv(d.max_pair_cap, T), W), T, 0, b->stream>>>(d);
   k_contacts<<<W, T, 0, b->stream>>>(d);
   b->last_launches += 4;
   return 0;

@@ -259,6 +259,9 @@ __global__ void __launch_bounds__(512) k_broadphase(DevBatch B) {
 
 // dCollide's class-pair table (collision_kernel.cpp:168-269).  Returns contacts with the
 // normal convention of dCollide(g1, g2): reversed entries call fn(g2, g1) and flip normals.
+// CYL = the scene has cylinders: only then are the cylinder-box and MPR colliders compiled in (they double the
+// registers and the stack of k_narrow; scenes of boxes, spheres and capsules run the light instantiation)
+template <bool CYL>
 __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) {
   int t1 = g1.type, t2 = g2.type;
   int n = 0;
@@ -282,11 +285,11 @@ __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) 
   else if (t1 == GZ_GEOM_SPHERE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_sphere(g2, g1, o); rev = true; }
   else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_PLANE) n = col_cylinder_plane(g1, g2, o);
   else if (t1 == GZ_GEOM_PLANE && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_plane(g2, g1, o); rev = true; }
-  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_BOX) n = col_cylinder_box(g1, g2, o);
-  else if (t1 == GZ_GEOM_BOX && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_box(g2, g1, o); rev = true; }
-  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_CYLINDER) n = col_mpr(g1, false, g2, o);
-  else if (t1 == GZ_GEOM_CAPSULE && t2 == GZ_GEOM_CYLINDER) n = col_mpr(g1, true, g2, o);
-  else if (t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_CAPSULE) { n = col_mpr(g2, true, g1, o); rev = true; }
+  else if (CYL && t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_BOX) n = col_cylinder_box(g1, g2, o);
+  else if (CYL && t1 == GZ_GEOM_BOX && t2 == GZ_GEOM_CYLINDER) { n = col_cylinder_box(g2, g1, o); rev = true; }
+  else if (CYL && t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_CYLINDER) n = col_mpr(g1, false, g2, o);
+  else if (CYL && t1 == GZ_GEOM_CAPSULE && t2 == GZ_GEOM_CYLINDER) n = col_mpr(g1, true, g2, o);
+  else if (CYL && t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_CAPSULE) { n = col_mpr(g2, true, g1, o); rev = true; }
   else n = 0;
   if (rev)
     for (int i = 0; i < n; i++) { o.nrm[i][0] = -o.nrm[i][0]; o.nrm[i][1] = -o.nrm[i][1]; o.nrm[i][2] = -o.nrm[i][2]; }
@@ -294,6 +297,7 @@ __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) 
 }
 
 // grid (ceil(max_pair_cap / blockDim), n_worlds): one thread per candidate pair
+template <bool CYL>
 __global__ void k_narrow(DevBatch B) {
   const int w = blockIdx.y;
   const WorldInfo wi = B.world[w];
@@ -310,7 +314,7 @@ __global__ void k_narrow(DevBatch B) {
     if ((unsigned)g1.max_contacts < maxCollide) maxCollide = g1.max_contacts;
     if ((unsigned)g2.max_contacts < maxCollide) maxCollide = g2.max_contacts;
     COut o;
-    numc = collide_dispatch(g1, g2, o);
+    numc = collide_dispatch<CYL>(g1, g2, o);
     int idx[GZ_PAIR_MAXC];
     for (int i = 0; i < GZ_PAIR_MAXC; i++) idx[i] = i;
     if (maxCollide > 0 && (unsigned)numc > maxCollide) {

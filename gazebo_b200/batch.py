@@ -56,6 +56,7 @@ def lib():
     L.gzcuda_batch_set_joint_param.argtypes = [vp, ci, ci, C.c_double]
     L.gzcuda_batch_get_joint_state.argtypes = [vp, dp, dp, dp]
     L.gzcuda_batch_set_hinge_pd.argtypes = [vp, dp]
+    L.gzcuda_batch_set_joint_velocity_cmd.argtypes = [vp, dp]
     L.gzcuda_batch_get_stats.argtypes = [vp, dp, dp, dp]
     L.gzcuda_batch_set_param.argtypes = [vp, C.c_char_p, C.c_double]
     L.gzcuda_batch_get_pairs.argtypes = [vp, ci, dp, ci]
@@ -80,6 +81,7 @@ EXPORTS = [
     "gzcuda_batch_pgs_ms", "gzcuda_batch_get_counters", "gzcuda_batch_get_pgs_debug",
     "gzcuda_batch_get_pgs_profile", "gzcuda_batch_get_pgs_timeline",
     "gzcuda_batch_get_joint_feedback", "gzcuda_batch_get_contact_feedback", "gzcuda_batch_step_log",
+    "gzcuda_batch_set_joint_velocity_cmd",
 ]
 
 
@@ -194,6 +196,11 @@ class Batch:
     def set_hinge_pd(self, pd):
         pd = np.ascontiguousarray(pd, dtype=np.float64).reshape(self.scene.nj, 6)
         self._ck(self.L.gzcuda_batch_set_hinge_pd(self.h, _p(pd)))
+
+    def set_joint_velocity_cmd(self, vel):
+        """vel[nj] rad/s applied before every step as Joint::SetVelocity does (NaN = no command)."""
+        vel = np.ascontiguousarray(vel, dtype=np.float64).reshape(self.scene.nj)
+        self._ck(self.L.gzcuda_batch_set_joint_velocity_cmd(self.h, _p(vel)))
 
     def stats(self):
         nw = self.scene.n_worlds

@@ -74,7 +74,9 @@ struct Joint {
   int limit;         // dxJointLimitMotor::limit
   int m;             // rows this step (0 = not in an active island)
   int row0;          // first row (world-local)
-  int world, pad;
+  int world;
+  int has_vel_cmd;   // Joint::SetVelocity stand-in (k_velcmd): vel_cmd is applied before every step
+  double vel_cmd;
 };
 
 struct Contact {

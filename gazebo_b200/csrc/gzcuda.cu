@@ -46,6 +46,7 @@ struct gzcuda_batch {
   long last_launches = 0;
   bool stage_valid = false;
   bool have_pd = false;
+  bool have_velcmd = false;
   size_t pgs_smem = 0, pgs_chain_smem[GZ_CHAIN_NCLS] = {};
   bool has_cylinders = false;         // picks the k_narrow instantiation with the cylinder-box and MPR colliders
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
@@ -546,6 +547,10 @@ static int run_steps(gzcuda_batch *b, int n_steps) {
   for (int s = 0; s < n_steps; s++) {
     const bool last = (s == n_steps - 1);
     if (last) cudaEventRecord(b->evs[0], b->stream);
+    if (b->have_velcmd) {
+      k_velcmd<<<cdiv(b->d.n_worlds, 128), 128, 0, b->stream>>>(b->d);
+      b->last_launches++;
+    }
     if (b->have_pd) {
       k_control<<<cdiv(std::max(b->d.nb, 1), 128), 128, 0, b->stream>>>(b->d);
       b->last_launches++;
@@ -828,6 +833,25 @@ int gzcuda_batch_set_hinge_pd(gzcuda_batch *b, const double *pd) {
   }
   CK(cudaMemcpy(b->d.joint, hj.data(), hj.size() * sizeof(Joint), cudaMemcpyHostToDevice));
   b->have_pd = any;
+  return 0;
+}
+
+int gzcuda_batch_set_joint_velocity_cmd(gzcuda_batch *b, const double *vel) {
+  if (!b || !vel) return fail(GZCUDA_E_INVALID, "null argument");
+  int rc = gzcuda_batch_sync(b);
+  if (rc) return rc;
+  if (b->d.nj == 0) return 0;
+  std::vector<Joint> hj(b->d.nj);
+  CK(cudaMemcpy(hj.data(), b->d.joint, hj.size() * sizeof(Joint), cudaMemcpyDeviceToHost));
+  bool any = false;
+  for (int j = 0; j < b->d.nj; j++) {
+    const bool on = vel[j] == vel[j] && hj[j].type == GZ_JOINT_HINGE;   // NaN = no command
+    hj[j].has_vel_cmd = on ? 1 : 0;
+    hj[j].vel_cmd = on ? vel[j] : 0.0;
+    any = any || on;
+  }
+  CK(cudaMemcpy(b->d.joint, hj.data(), hj.size() * sizeof(Joint), cudaMemcpyHostToDevice));
+  b->have_velcmd = any;
   return 0;
 }
 

@@ -77,6 +77,38 @@ __global__ void k_control(DevBatch B) {
   }
 }
 
+// Device-side stand-in for a plugin that calls Joint::SetVelocity on hinge joints every update, which in this fork
+// is Joint::SetVelocityMaximal (gazebo/physics/Joint.cc:828-894; DiffDrivePlugin::OnUpdate plugins/DiffDrivePlugin.cc:100-122,
+// ODEHingeJoint::SetVelocity ODEHingeJoint.cc:153-156): the child link (body 1 of the ODE joint) gets the parent's angular
+// velocity plus vel along the joint axis, and the linear velocity of a point rigidly carried by the joint anchor.  One thread
+// per world walks its joints in order, as the plugin's calls arrive.  (Link frame = centre of mass in this scene format; the
+// anchor offsets are taken with ODE's matrix arithmetic, the same in the oracle harness.)
+__global__ void k_velcmd(DevBatch B) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= B.n_worlds) return;
+  const WorldInfo wi = B.world[w];
+  for (int k = 0; k < wi.nj; k++) {
+    const Joint &j = B.joint[wi.joint0 + k];
+    if (!j.has_vel_cmd || j.type != GZ_JOINT_HINGE) continue;
+    Body &c = B.body[j.b1];
+    double ang[3] = {0.0, 0.0, 0.0}, lin[3] = {0.0, 0.0, 0.0};
+    if (j.b2 >= 0) {
+      const Body &p = B.body[j.b2];
+      double off[3], cr[3];
+      mul0_331(off, p.R, j.anchor2);
+      cross3(cr, p.avel, off);
+      for (int i = 0; i < 3; i++) { ang[i] = p.avel[i]; lin[i] = p.lvel[i] + cr[i]; }
+    }
+    double axis[3], a[3], jw[3], off[3], cr[3];
+    mul0_331(axis, c.R, j.axis1);
+    for (int i = 0; i < 3; i++) ang[i] += j.vel_cmd * axis[i];
+    mul0_331(a, c.R, j.anchor1);
+    for (int i = 0; i < 3; i++) { jw[i] = c.pos[i] + a[i]; off[i] = c.pos[i] - jw[i]; }
+    cross3(cr, ang, off);
+    for (int i = 0; i < 3; i++) { c.avel[i] = ang[i]; c.lvel[i] = lin[i] + cr[i]; }
+  }
+}
+
 // One CTA per world.
 __global__ void k_island(DevBatch B) {
   const int w = blockIdx.x;

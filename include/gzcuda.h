@@ -89,6 +89,11 @@ int gzcuda_batch_get_joint_state(gzcuda_batch *b, double *lambda, double *lambda
  * Events::worldUpdateBegin: pd[nj][6] = amplitude, frequency (Hz), phase, kp, kd, torque clamp
  * (clamp <= 0 disables the joint's controller). */
 int gzcuda_batch_set_hinge_pd(gzcuda_batch *b, const double *pd);
+/* Device-side stand-in for a plugin that calls Joint::SetVelocity(0, v) on hinge joints every update (this fork's
+ * DiffDrivePlugin::OnUpdate, plugins/DiffDrivePlugin.cc:100-122 -> Joint::SetVelocityMaximal, Joint.cc:828-894): vel[nj] in
+ * rad/s, NaN = no command for that joint.  Applied before every step, joints in order.  A host plugin does the same through
+ * gzcuda_batch_set_body_state. */
+int gzcuda_batch_set_joint_velocity_cmd(gzcuda_batch *b, const double *vel);
 
 /* Solver statistics per world: rms_residual[nw][4] (dWorldGetQuickStepRMSConstraintResidual,
  * ODEPhysics::GetParam("constraint_residual") ODEPhysics.cc:1630-1635), number of contact

@@ -80,6 +80,7 @@ struct RefWorld {
   std::vector<dJointID> joints;
   std::vector<int> joint_type;
   std::vector<HingePD> pd;
+  std::vector<double> vel_cmd;                // per joint, NaN = none (gzref_set_joint_velocity_cmd)
   std::vector<dJointID> contact_joints;       // created this step, creation order
   bool feedback = false;                      // gzref_enable_feedback: dJointSetFeedback on joints and contacts
   std::vector<dJointFeedback> joint_fb, contact_fb;
@@ -271,6 +272,35 @@ void apply_controllers(RefBatch *B, RefWorld *w) {
   }
 }
 
+// ---- plugin stand-in: Joint::SetVelocity on hinge joints every update ---------
+// Joint::SetVelocityMaximal (gazebo/physics/Joint.cc:828-894) as this fork's DiffDrivePlugin::OnUpdate reaches it
+// (plugins/DiffDrivePlugin.cc:100-122, ODEHingeJoint::SetVelocity ODEHingeJoint.cc:153-156): the child link (ODE body 1)
+// takes the parent's angular velocity plus vel along the joint axis and the linear velocity of a point carried by the
+// anchor.  Link frame = centre of mass in this scene format; anchor offsets by ODE's matrix arithmetic.
+void apply_velocity_commands(RefWorld *w) {
+  for (size_t j = 0; j < w->joints.size() && j < w->vel_cmd.size(); ++j) {
+    const double vel = w->vel_cmd[j];
+    if (!(vel == vel) || w->joint_type[j] != GZ_JOINT_HINGE) continue;
+    dxJointHinge *hj = static_cast<dxJointHinge *>(w->joints[j]);
+    dxBody *c = hj->node[0].body, *p = hj->node[1].body;
+    double ang[3] = {0.0, 0.0, 0.0}, lin[3] = {0.0, 0.0, 0.0};
+    if (p) {
+      dVector3 off, cr;
+      dMultiply0_331(off, p->posr.R, hj->anchor2);
+      dCalcVectorCross3(cr, p->avel, off);
+      for (int i = 0; i < 3; i++) { ang[i] = p->avel[i]; lin[i] = p->lvel[i] + cr[i]; }
+    }
+    dVector3 axis, a, jw, off, cr, angv;
+    dMultiply0_331(axis, c->posr.R, hj->axis1);
+    for (int i = 0; i < 3; i++) ang[i] += vel * axis[i];
+    dMultiply0_331(a, c->posr.R, hj->anchor1);
+    for (int i = 0; i < 3; i++) { jw[i] = c->posr.pos[i] + a[i]; off[i] = c->posr.pos[i] - jw[i]; angv[i] = ang[i]; }
+    dCalcVectorCross3(cr, angv, off);
+    dBodySetAngularVel(c, ang[0], ang[1], ang[2]);
+    dBodySetLinearVel(c, lin[0] + cr[0], lin[1] + cr[1], lin[2] + cr[2]);
+  }
+}
+
 // ---- canonical-order step: islands by lowest body index ---------------------
 int uf_find(std::vector<int> &p, int x) {
   while (p[x] != x) { p[x] = p[p[x]]; x = p[x]; }
@@ -343,6 +373,7 @@ void canonical_quickstep(RefBatch *B, RefWorld *w) {
 void step_world(RefBatch *B, RefWorld *w) {
   static const bool trace = getenv("GZREF_TRACE") != nullptr;
   if (trace) fprintf(stderr, "step %ld: control\n", w->step_index);
+  apply_velocity_commands(w);
   apply_controllers(B, w);
   if (trace) fprintf(stderr, "  collide\n");
   update_collision(B, w);
@@ -585,6 +616,14 @@ void gzref_set_hinge_pd(void *h, const double *pd) {
       HingePD v = {c[0], c[1], c[2], c[3], c[4], c[5]};
       w->pd[j] = v;
     }
+  }
+}
+
+void gzref_set_joint_velocity_cmd(void *h, const double *vel) {
+  RefBatch *B = static_cast<RefBatch *>(h);
+  for (size_t wi = 0; wi < B->worlds.size(); wi++) {
+    RefWorld *w = B->worlds[wi];
+    w->vel_cmd.assign(vel + B->joint_off[wi], vel + B->joint_off[wi] + w->joints.size());
   }
 }
 

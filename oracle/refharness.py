@@ -51,6 +51,7 @@ def _load(flavour):
     lib.gzref_get_stats.argtypes = [C.c_void_p] * 4
     lib.gzref_get_joint_state.argtypes = [C.c_void_p] * 4
     lib.gzref_enable_feedback.argtypes = [C.c_void_p]
+    lib.gzref_set_joint_velocity_cmd.argtypes = [C.c_void_p, C.c_void_p]
     lib.gzref_get_joint_feedback.argtypes = [C.c_void_p, C.c_void_p]
     lib.gzref_get_contact_feedback.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
     _libs[flavour] = lib
@@ -145,3 +146,7 @@ class RefBatch:
         fb = np.zeros((cap, 12))
         n = self.lib.gzref_get_contact_feedback(self.h, world, _p(fb), cap)
         return fb[:n].copy()
+
+    def set_joint_velocity_cmd(self, vel):
+        vel = np.ascontiguousarray(vel, dtype=np.float64).reshape(self.scene.nj)
+        self.lib.gzref_set_joint_velocity_cmd(self.h, _p(vel))

@@ -477,9 +477,7 @@ static int launch_collision(gzcuda_batch *b) {
 static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
-  k_island<<<W, T, 0, b->stream>>>(d);
-  k_bodyprep<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
-  k_info1<<<W, T, 0, b->stream>>>(d);
+  k_assemble1<<<W, T, 0, b->stream>>>(d);   // islands, body prologue, row counts
   if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
   const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16 +
@@ -529,7 +527,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   if (stage_events) cudaEventRecord(b->evs[3], b->stream);
   if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_integrate<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
-  b->last_launches += 9;
+  b->last_launches += 7;
   return 0;
 }
 

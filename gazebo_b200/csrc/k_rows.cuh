@@ -109,8 +109,8 @@ __global__ void k_velcmd(DevBatch B) {
   }
 }
 
-// One CTA per world.
-__global__ void k_island(DevBatch B) {
+// One CTA per world (a phase of k_assemble1 below).
+__device__ __forceinline__ void island_world(const DevBatch &B) {
   const int w = blockIdx.x;
   const WorldInfo wi = B.world[w];
   const WorldStep &ws = B.wstep[w];
@@ -175,9 +175,7 @@ __global__ void k_island(DevBatch B) {
 }
 
 // One thread per body (active bodies only).
-__global__ void k_bodyprep(DevBatch B) {
-  int bi = blockIdx.x * blockDim.x + threadIdx.x;
-  if (bi >= B.nb) return;
+__device__ __forceinline__ void bodyprep_body(const DevBatch &B, const int bi) {
   BodyStep &bs = B.bstep[bi];
   for (int k = 0; k < 6; k++) { bs.caccel[k] = 0; bs.caccel_erp[k] = 0; }
   if (!bs.active) return;
@@ -201,7 +199,7 @@ __global__ void k_bodyprep(DevBatch B) {
 
 // One CTA per world: row count per joint (with the hinge's cumulative-angle side effect),
 // exclusive scan -> Joint::row0; contacts follow with 3 rows each.
-__global__ void k_info1(DevBatch B) {
+__device__ __forceinline__ void info1_world(const DevBatch &B) {
   const int w = blockIdx.x;
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
@@ -278,6 +276,17 @@ __global__ void k_info1(DevBatch B) {
     atomicAdd(&B.acc[2], (unsigned long long)ws.n_contacts);
     atomicAdd(&B.acc[3], 1ull);
   }
+}
+
+// One CTA per world: auto-disable + islands, the body prologue of its bodies, row counts and offsets - three
+// phases that were three launches (k_island, k_bodyprep, k_info1), separated by block barriers.
+__global__ void k_assemble1(DevBatch B) {
+  island_world(B);
+  __syncthreads();
+  const WorldInfo wi = B.world[blockIdx.x];
+  for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) bodyprep_body(B, wi.body0 + i);
+  __syncthreads();
+  info1_world(B);
 }
 
 }  // namespace gz

@@ -6,7 +6,7 @@ tag=${1:-rXX}
 out=gpurun_out
 python bench.py > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err
 python bench.py --impl reference > $out/${tag}_bench_reference_n1.json 2> $out/${tag}_bench_reference_n1.err
-STEPS=104 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 2000 -c 120 --csv \
+STEPS=104 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 1750 -c 108 --csv \
   --log-file $out/${tag}_launches_steady.csv python scripts/dev_ncu_target.py > $out/${tag}_ncu1.log 2>&1
 STEPS=102 ncu --set full --clock-control none --import-source on -k regex:k_pgs --launch-skip 500 --launch-count 10 \
   -o $out/${tag}_pgs_full -f python scripts/dev_ncu_target.py > $out/${tag}_ncu2.log 2>&1

@@ -17,6 +17,7 @@
 #define GZ_NRUNG 160
 #define GZ_NBUCKET (10 * GZ_NRUNG)
 #define GZ_PAIR_MAXC 16  // contacts one geom pair can yield (box-box: 8, cylinder-box: up to 13)
+#define GZ_ENT 20          // doubles per body-owner PGS entry (k_pgsb.cuh)
 #define GZ_CHAIN_NCLS 4   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
 
 namespace gz {
@@ -157,6 +158,16 @@ struct DevBatch {
   int pgs_rt, pgs_kmin, pgs_kmax;   // scheduler knobs: target period, lanes-per-solve range
   int bp_sap_min;        // geoms from which a world takes the sort-and-sweep broadphase (k_collide.cuh)
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
+  // ---- body-owner PGS (k_pgsb.cuh): per-body entry lists in a bump-allocated pool
+  int pgs_impl;          // 1: body-owner sweeps (k_pgsb), 0: the round-1 row-slot sweeps (k_pgs / k_pgs_chain)
+  double *ent;           // [ent_cap][GZ_ENT] half-records, one per (row, body), grouped per body in order[] sequence
+  int *ent_row;          // [ent_cap] world-local row index if this entry is the row's body-1 half (lambda write-back), else -1
+  double *ent_ad2;       // [ent_cap] 1 / Ad^2 (statistics sweeps only)
+  long ent_cap;
+  unsigned long long *ent_cursor;   // [2] bump allocators, used alternately by step parity (the idle one is reset)
+  int4 *bsched;          // [nb] {first entry (pool index), entries, first friction entry (list index), 0}
+  int4 *wsb;             // [n_worlds] {period R, stages, first entry, entries}
+  int *sticky;           // [4] OR of every step's overflow masks since the last check, first world, spare
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)
   double *io_out;        // [nb][13] staged pos(3) quat(4) lvel(3) avel(3)
 };

@@ -52,6 +52,12 @@ struct gzcuda_batch {
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
   int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
+  PgsbCfg pgsb2;                      // the large shared-memory class of the one-warp CTAs
+  size_t pgsb2_smem = 0;
+  PgsbCfg pgsb;                       // body-owner sweeps (k_pgsb.cuh): lane layout, CTA shape, shared memory
+  bool pgsb_multi = false;
+  int pgsb_threads = 32, pgsb_ctas = 0;
+  size_t pgsb_smem = 0, bsched_smem = 0;
   bool profiling = false;             // record an event pair around every k_pgs launch
   bool reg_first = false;             // experiment: k_pgs before (and above) the small chain-mode launches
   std::vector<cudaEvent_t> pgs_ev;    // 2 per step of the last step call
@@ -93,6 +99,8 @@ static bool invert_pd3(const double A[9], double Ainv[9]) {
   }
   return true;
 }
+
+static inline int cdiv_host(int a, int b) { return (a + b - 1) / b; }
 
 template <class T>
 static int dev_alloc(gzcuda_batch *b, T **p, size_t n) {
@@ -334,6 +342,59 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   d.pgs_prof = getenv("GZCUDA_PGS_PROF") ? atoi(getenv("GZCUDA_PGS_PROF")) : 0;
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
+  if ((rc = dev_alloc(b, &d.sticky, (size_t)4))) return rc;
+
+  // Body-owner PGS (k_pgsb.cuh): the default for worlds of up to 256 bodies.  Entry pool: a row has one entry
+  // per body, so 2 x rows is the worst case; clamped to a quarter of the free memory (k_bsched flags a step
+  // that does not fit).
+  d.pgs_impl = (max_nb <= 256) ? 1 : 0;
+  if (const char *e = getenv("GZCUDA_PGS_IMPL")) d.pgs_impl = (atoi(e) != 0 && max_nb <= 256) ? 1 : 0;
+  if (d.pgs_impl == 1) {
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    const size_t per_ent = GZ_ENT * sizeof(double) + sizeof(int) + sizeof(double);
+    long want = 2 * row_tot + 1024;
+    const long most = (long)(free_b / 4 / per_ent);
+    d.ent_cap = std::max(4096L, std::min(want, most));
+    if (d.ent_cap > 0x7ffffff0L) d.ent_cap = 0x7ffffff0L;
+    if ((rc = dev_alloc(b, &d.ent, (size_t)GZ_ENT * d.ent_cap))) return rc;
+    if ((rc = dev_alloc(b, &d.ent_row, (size_t)d.ent_cap))) return rc;
+    if ((rc = dev_alloc(b, &d.ent_ad2, (size_t)d.ent_cap))) return rc;
+    if ((rc = dev_alloc(b, &d.ent_cursor, (size_t)2))) return rc;
+    if ((rc = dev_alloc(b, &d.bsched, (size_t)nb))) return rc;
+    if ((rc = dev_alloc(b, &d.wsb, (size_t)W))) return rc;
+    int bp = 1;
+    while (bp < max_nb) bp <<= 1;
+    PgsbCfg &c = b->pgsb;
+    c.lw = 2 * bp;
+    b->pgsb_multi = c.lw > 32;
+    c.wpc = b->pgsb_multi ? 1 : 32 / c.lw;
+    b->pgsb_threads = b->pgsb_multi ? c.lw : 32;
+    b->pgsb_ctas = cdiv_host(W, c.wpc);
+    // Shared memory per CTA for staged entries (176 B each).  One-warp CTAs come in two classes: the small one
+    // (7 CTAs per SM) takes the CTAs whose worlds fit it, the large one (3 per SM) the rest; what fits neither
+    // reads the pool.  A multi-warp CTA (one world) has one class.
+    size_t kb1 = b->pgsb_multi ? 128 : 32, kb2 = 72;
+    if (const char *e = getenv("GZCUDA_PGSB_KB")) kb1 = (size_t)std::max(0, atoi(e));
+    if (const char *e = getenv("GZCUDA_PGSB_KB2")) kb2 = (size_t)std::max(0, atoi(e));
+    kb1 = std::min<size_t>(kb1, 200); kb2 = std::min<size_t>(std::max(kb2, kb1), 200);
+    const size_t ent_b = GZ_ENTS * sizeof(double);
+    const size_t xch_b = b->pgsb_multi ? (size_t)2 * c.lw * sizeof(double) : 0;
+    const size_t red_b = b->pgsb_multi ? (size_t)9 * c.lw * sizeof(double) : 0;
+    c.nres = (int)(kb1 * 1024 / ent_b);
+    c.cls = b->pgsb_multi ? -1 : 0;
+    b->pgsb2 = c;
+    b->pgsb2.nres = (int)(kb2 * 1024 / ent_b);
+    b->pgsb2.cls = 1;
+    b->pgsb_smem = std::max((size_t)c.nres * ent_b + xch_b, red_b);
+    b->pgsb2_smem = (size_t)b->pgsb2.nres * ent_b;
+    b->bsched_smem = (size_t)5 * std::max(max_nb, 1) * sizeof(int);
+    const int mx_smem = (int)std::max(b->pgsb_smem, b->pgsb2_smem);
+    for (auto f : {k_pgsb<false, false>, k_pgsb<false, true>, k_pgsb<true, false>, k_pgsb<true, true>}) {
+      if (mx_smem > 48 * 1024) CK(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, mx_smem));
+      CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    }
+  }
 
   // Broadphase (k_collide.cuh): all pairs for small worlds, sort-and-sweep from bp_sap_min geoms on,
   // if the sorted keys and the n x n hit bits of the largest world fit in shared memory
@@ -480,6 +541,36 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_assemble1<<<W, T, 0, b->stream>>>(d);   // islands, body prologue, row counts
   if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
+  if (d.pgs_impl == 1) {
+    // body-owner sweeps: schedule (integer work on the row counts), row prologue + entries, sweeps
+    k_bsched<<<W, 128, b->bsched_smem, b->stream>>>(d);
+    k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
+    if (stage_events) cudaEventRecord(b->evs[2], b->stream);
+    if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
+    const bool box = d.p.friction_model == 2;
+    if (b->pgsb_multi) {
+      if (box) k_pgsb<true, true><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
+      else k_pgsb<true, false><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
+    } else {
+      // the large class beside the small one, on its own stream (fork / join by events); it goes first: its worlds run longest
+      cudaEventRecord(b->ev_fork, b->stream);
+      cudaStreamWaitEvent(b->stream_chain[GZ_CHAIN_NCLS - 1], b->ev_fork, 0);
+      cudaStream_t s2 = b->stream_chain[GZ_CHAIN_NCLS - 1];
+      if (box) k_pgsb<false, true><<<b->pgsb_ctas, 32, b->pgsb2_smem, s2>>>(d, b->pgsb2, b->pgsb.nres);
+      else k_pgsb<false, false><<<b->pgsb_ctas, 32, b->pgsb2_smem, s2>>>(d, b->pgsb2, b->pgsb.nres);
+      cudaEventRecord(b->ev_join[0], s2);
+      if (box) k_pgsb<false, true><<<b->pgsb_ctas, 32, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
+      else k_pgsb<false, false><<<b->pgsb_ctas, 32, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
+      cudaStreamWaitEvent(b->stream, b->ev_join[0], 0);
+      b->last_launches++;
+    }
+    if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
+    if (stage_events) cudaEventRecord(b->evs[3], b->stream);
+    if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
+    k_integrate<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
+    b->last_launches += 6;
+    return 0;
+  }
   const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16 +
                           (d.sch_rpar > 0 ? (size_t)32 * (2 * std::max(d.max_nb, 1) * sizeof(int) + d.sch_rpar * sizeof(unsigned short)) : 0);
   k_schedule<<<W, 32, sch_smem, b->stream>>>(d);

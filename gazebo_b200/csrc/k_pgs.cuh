@@ -30,6 +30,7 @@
 // per round feeds the whole warp.
 #pragma once
 #include "k_rows2.cuh"
+#include "k_pgsb.cuh"
 
 namespace gz {
 
@@ -501,6 +502,42 @@ __global__ void k_rowfinish(DevBatch B) {
   else Ad = B.p.contact_sor_scale * B.p.sor_w / (d + cfm);
   r.Ad = Ad;
   r.lambda = lam; r.lambda_erp = lam_erp;
+  if (B.pgs_impl == 1) {
+    // body-owner sweeps (k_pgsb.cuh): one entry per body of the row, at the place k_bsched gave it
+    const int nc = B.wstep[w].n_contacts, mj = B.wstep[w].m - 3 * nc;
+    const WScratchB S = wscratchb(B, w);
+    const int pos = order_pos(i, mj, nc);
+    const int off = S.off[pos];
+    if (off < 0) return;   // a row of an island that is not stepped, or a world the entry pool could not take
+    const int cls = r.findex == -1 ? 0 : (r.findex == -2 ? 1 : 2);
+    int back1 = 0, back2 = 0;
+    if (cls == 2) {
+      const int pn = order_pos(r.findex, mj, nc);
+      back1 = S.idx1[pos] - S.idx1[pn];
+      if (r.b2 >= 0) back2 = S.idx2[pos] - S.idx2[pn];
+    }
+    double Ad2 = 0.0;   // quickstep_pgs_lcp.cpp:745-752
+    if (!dequal(Ad, 0.0)) Ad2 = 1.0 / (Ad * Ad);
+    const double rhsA = rhs * Ad, rhsA_erp = rhs_erp * Ad, adcfm = Ad * cfm;
+    for (int h = 0; h < (r.b2 >= 0 ? 2 : 1); h++) {
+      const int e = B.bsched[wi.body0 + (h ? r.b2 : r.b1)].x + (h ? S.idx2[pos] : S.idx1[pos]);
+      double2 *e2 = reinterpret_cast<double2 *>(B.ent + (size_t)e * GZ_ENT);
+      for (int j = 0; j < 3; j++) {
+        e2[j] = make_double2(J[6 * h + 2 * j] * Ad, J[6 * h + 2 * j + 1] * Ad);
+        e2[3 + j] = make_double2(iMJ[6 * h + 2 * j], iMJ[6 * h + 2 * j + 1]);
+      }
+      e2[6] = make_double2(rhsA, lam);
+      e2[7] = make_double2(rhsA_erp, lam_erp);
+      e2[8] = make_double2(adcfm, r.lo);
+      const int mx = off | (cls << 27) | (h << 29);
+      const int partner = h ? r.b1 : (r.b2 >= 0 ? r.b2 : GZ_ENT_NOPART);
+      const int my = partner | ((h ? back2 : back1) << 16);
+      e2[9] = make_double2(r.hi, __hiloint2double(my, mx));
+      B.ent_row[e] = h ? -1 : i;
+      B.ent_ad2[e] = Ad2;
+    }
+    return;
+  }
   const WSched sc = reinterpret_cast<const WSched *>(B.wsched)[w];
   const WSlab sl = wslab(B, sc);
   if (sl.warp < 0) return;

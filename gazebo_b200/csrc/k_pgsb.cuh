@@ -1,0 +1,395 @@
+// k_pgsb.cuh — body-owner SOR-PGS: ComputeRows (quickstep_pgs_lcp.cpp:52-954) with one lane per
+// (body, solve) instead of one lane per row.
+//
+// The reference sweeps rows strictly in order[] sequence.  Two row updates commute EXACTLY when they
+// share no body, so any execution that keeps, for every body, the order in which rows touch it is
+// bit-identical (same argument as round 1's row-slot kernels).  Here the per-body order is not a
+// constraint a scheduler has to satisfy but the data structure itself:
+//
+//   * every body has an ENTRY LIST: its half of every row that touches it, in order[] sequence
+//     (bilateral rows, contact normals in reverse index order, friction rows; :1115-1150);
+//   * lane (b, S) owns body b for the whole kernel and keeps caccel[b] (S = 0) or caccel_erp[b]
+//     (S = 1) in SIX REGISTERS; the lambda / lambda_erp solves are independent problems (split
+//     impulse, :526-542) on adjacent lanes reading the same entry;
+//   * a two-body row is run by its two owner lanes in the same round: each computes the 6-term dot
+//     product of its own half (the reference subtracts the two sums separately, :526-531), the
+//     partial sums are exchanged with ONE shuffle, both lanes then compute the same delta and each
+//     updates its own accumulator and its own copy of lambda.  Nothing else is shared, so there is
+//     no shared-memory traffic on the dependent chain and no barrier in the one-warp case;
+//   * the round of a row is off(r) = 1 + max over its bodies of the round of their previous row
+//     (one serial pass, k_bsched: no greedy, no period probing), the sweep period of a world is
+//     R = the longest span first..last of any body, and row r of sweep s runs in round s*R + off(r)
+//     (software pipelining of the sweep loop: sweeps overlap wherever bodies allow);
+//   * entries (160 B) are staged in shared memory once per step and stay there for the 60 sweeps;
+//     what does not fit the CTA's budget is read from the pool (L2) with the same code path.
+//
+// Worlds of up to 16 bodies share a warp (32 / (2 * padded bodies) worlds per warp, event-driven
+// rounds: the warp jumps to the next round in which any lane is due).  Larger worlds take a CTA of
+// their own (up to 256 bodies): the exchange goes through shared memory and one barrier per round.
+#pragma once
+
+namespace gz {
+
+// ---- entry: what a lane streams per row of its body, 20 doubles = 160 B ------------------------------
+// [0..5] J half (scaled by Ad)  [6..11] iMJ half  [12] rhs*Ad  [13] lambda  [14] rhs_erp*Ad  [15] lambda_erp
+// [16] Ad*cfm  [17] lo  [18] hi  [19] meta {int x, y}:
+//   x = off (bits 0..26) | class << 27 (0 bilateral, 1 contact normal, 2 friction) | is-body-2 << 29
+//   y = partner body (world-local, 0xFFFF none) | back << 16 (friction: distance, in list entries, to the normal row)
+#define GZ_ENT_OFFMASK 0x7FFFFFF
+#define GZ_ENT_NOPART 0xFFFF
+
+struct WScratchB { int *rb1, *rb2, *off, *idx1, *idx2; };
+__device__ inline WScratchB wscratchb(const DevBatch &B, int w) {
+  WScratchB s;
+  const size_t n = B.max_row_cap;
+  int *base = B.scratch + (size_t)w * 7 * n;
+  s.rb1 = base; s.rb2 = base + n; s.off = base + 2 * n; s.idx1 = base + 3 * n; s.idx2 = base + 4 * n;
+  return s;
+}
+
+// order[] position of row i (quickstep_pgs_lcp.cpp:1115-1150 with row_reorder1): bilateral rows in index
+// order, contact normals in REVERSE index order, friction rows in index order.  mj = persistent-joint rows.
+__device__ __forceinline__ int order_pos(int i, int mj, int nc) {
+  if (i < mj) return i;
+  const int c = (i - mj) / 3, f = (i - mj) % 3;
+  return f == 0 ? mj + (nc - 1 - c) : mj + nc + 2 * c + (f - 1);
+}
+
+// One CTA per world: bodies of the rows by order[] position (parallel), then ONE serial pass that gives
+// every row its round offset and its place in the entry lists of its bodies, then the world's period and
+// its slice of the entry pool.  Integer work only; needs the row counts (k_assemble1), not the rows.
+// Dynamic shared memory: 5 * max_nb ints.
+__global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
+  extern __shared__ int bs_sh[];
+  const int w = blockIdx.x, tid = threadIdx.x;
+  const WorldInfo wi = B.world[w];
+  WorldStep &ws = B.wstep[w];
+  const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc;
+  int *last = bs_sh, *first = bs_sh + B.max_nb, *cnt = bs_sh + 2 * B.max_nb, *fr0 = bs_sh + 3 * B.max_nb, *base = bs_sh + 4 * B.max_nb;
+  __shared__ int s_R, s_maxoff, s_nent, s_wbase;
+  const WScratchB S = wscratchb(B, w);
+  const int par = (int)(B.step_index & 1);
+  if (w == 0 && tid == 0) B.ent_cursor[par ^ 1] = 0ull;   // the other parity's allocator: idle this step
+  for (int b = tid; b < nb; b += blockDim.x) { last[b] = -1; first[b] = -1; cnt[b] = 0; fr0[b] = -1; }
+  if (m > 0) {
+    for (int k = tid; k < wi.nj; k += blockDim.x) {
+      const Joint &j = B.joint[wi.joint0 + k];
+      const int b1 = j.b1 - wi.body0, b2 = j.b2 >= 0 ? j.b2 - wi.body0 : -1;
+      for (int r = 0; r < j.m; r++) { S.rb1[j.row0 + r] = b1; S.rb2[j.row0 + r] = b2; }
+    }
+    for (int c = tid; c < nc; c += blockDim.x) {
+      const Contact &C = B.contact[wi.contact0 + c];
+      // a contact whose island is not stepped this step has rows (getInfo1 counted them) but they are never swept
+      const bool live = B.bstep[C.b1].active != 0;
+      const int b1 = live ? C.b1 - wi.body0 : -2, b2 = C.b2 >= 0 ? C.b2 - wi.body0 : -1;
+      const int pn = mj + (nc - 1 - c), pf = mj + nc + 2 * c;
+      S.rb1[pn] = b1; S.rb2[pn] = b2;
+      S.rb1[pf] = b1; S.rb2[pf] = b2;
+      S.rb1[pf + 1] = b1; S.rb2[pf + 1] = b2;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int maxoff = -1;
+    const int pfric = mj + nc;
+    for (int pos = 0; pos < m; pos++) {
+      const int x1 = S.rb1[pos], x2 = S.rb2[pos];
+      if (x1 < 0) { S.off[pos] = -1; continue; }
+      int o = last[x1] + 1;
+      if (x2 >= 0) o = max(o, last[x2] + 1);
+      const int i1 = cnt[x1]++;
+      last[x1] = o;
+      if (first[x1] < 0) first[x1] = o;
+      if (pos >= pfric && fr0[x1] < 0) fr0[x1] = i1;
+      S.idx1[pos] = i1;
+      if (x2 >= 0) {
+        const int i2 = cnt[x2]++;
+        last[x2] = o;
+        if (first[x2] < 0) first[x2] = o;
+        if (pos >= pfric && fr0[x2] < 0) fr0[x2] = i2;
+        S.idx2[pos] = i2;
+      }
+      S.off[pos] = o;
+      maxoff = max(maxoff, o);
+    }
+    int R = 1, nent = 0;
+    for (int b = 0; b < nb; b++) {
+      if (first[b] >= 0) R = max(R, last[b] - first[b] + 1);
+      base[b] = nent;
+      nent += cnt[b];
+    }
+    long long wbase = 0;
+    if (nent > 0) {
+      wbase = (long long)atomicAdd(&B.ent_cursor[par], (unsigned long long)nent);
+      if (wbase + nent > B.ent_cap || maxoff > GZ_ENT_OFFMASK) {   // pool exhausted: the world is not solved, the step is flagged
+        ws.overflow |= 16;
+        nent = 0;
+      }
+    }
+    s_R = R; s_maxoff = maxoff; s_nent = nent; s_wbase = (int)wbase;
+    B.wsb[w] = make_int4(R, maxoff < 0 ? 0 : maxoff / R + 1, (int)wbase, nent);
+    if (nent == 0)
+      for (int pos = 0; pos < m; pos++) S.off[pos] = -1;   // rows without entries: k_rowfinish skips them
+  }
+  __syncthreads();
+  const int nent = s_nent, wbase = s_wbase;
+  for (int b = tid; b < nb; b += blockDim.x)
+    B.bsched[wi.body0 + b] = nent > 0 ? make_int4(wbase + base[b], cnt[b], fr0[b] < 0 ? cnt[b] : fr0[b], 0) : make_int4(0, 0, 0, 0);
+}
+
+// ---- the sweeps ---------------------------------------------------------------------------------------
+struct PgsbCfg {
+  int lw;        // lanes per world = 2 * padded body count (power of two, >= 2)
+  int wpc;       // worlds per CTA (32 / lw for one-warp CTAs, 1 for multi-warp CTAs)
+  int nres;      // entries the CTA can stage in shared memory (all its worlds together)
+  int cls;       // this launch takes the CTAs of this shared-memory class (k_pgsb_class), -1: every CTA, from the pool
+};
+
+// Entries staged in shared memory are padded to 22 doubles (176 B = 11 x 16 B, an odd number of 16-byte bank
+// groups) so that the 16 distinct entries a warp reads per 128-bit load spread over all banks.
+#define GZ_ENTS 22
+
+// The sweeps of one lane.  RES: the lane's list is in shared memory (stride GZ_ENTS), else in the pool (stride
+// GZ_ENT).  The current entry lives in registers; its successor is loaded IN PLACE, field by field right after
+// the last use of each field in this round (J after the dot product, iMJ and the scalars after the accumulator
+// update), so the loads run beside the arithmetic and no register is ever moved.
+template <bool RES, bool MULTI, bool BOX>
+__device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp, const int cnt, const int fric0, const int R,
+                                           const int nstage, const int S, const int bl, const int lane_base,
+                                           const int LW, double *xch, const int e0, double (&a)[6],
+                                           double (&st_acc)[3], double (&st_err)[3], int (&st_cnt)[3]) {
+  constexpr int STR = RES ? GZ_ENTS : GZ_ENT;
+  const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
+  const double smooth = B.p.smooth_contacts, smooth1 = 1.0 - smooth;
+  int i = (iters > 0) ? 0 : fric0, sweep = 0;
+  double J[6], iM[6], rhs = 0, lam = 0, adcfm = 0, lo = 0, hi = 0;
+  int mx = 0, my = GZ_ENT_NOPART;
+  int T_due = 0x7fffffff;
+#pragma unroll
+  for (int t = 0; t < 6; t++) { J[t] = 0; iM[t] = 0; }
+  if (i < cnt && total > 0) {
+    const double2 *p2 = reinterpret_cast<const double2 *>(lp + (size_t)i * STR);
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const double2 x = p2[k], y = p2[3 + k];
+      J[2 * k] = x.x; J[2 * k + 1] = x.y; iM[2 * k] = y.x; iM[2 * k + 1] = y.y;
+    }
+    const double2 rl = p2[6 + S], cl = p2[8], hm = p2[9];
+    rhs = rl.x; lam = rl.y; adcfm = cl.x; lo = cl.y; hi = hm.x;
+    mx = __double2loint(hm.y); my = __double2hiint(hm.y);
+    T_due = mx & GZ_ENT_OFFMASK;
+  }
+  const int rounds_multi = (total > 0 && nstage > 0) ? (total + nstage - 1) * R : 0;
+  int T = -1, Tlast = 0;
+  for (;;) {
+    if (MULTI) {
+      if (++T >= rounds_multi) break;
+    } else {
+      T = __reduce_min_sync(0xffffffffu, T_due);   // event-driven: the next round in which any lane of the warp is due
+      if (T == 0x7fffffff) break;
+    }
+    Tlast = T;
+    const bool due = (T_due == T);
+    // where this lane goes next
+    int inx = i + 1, nsw = sweep;
+    if (inx == cnt) { nsw = sweep + 1; inx = nsw < iters ? 0 : fric0; }
+    const bool more = due && nsw < total && inx < cnt;
+    double *pc = lp + (size_t)i * STR;
+    const double2 *pn2 = reinterpret_cast<const double2 *>(lp + (size_t)inx * STR);
+    double2 hmn = make_double2(0.0, 0.0);
+    if (more) hmn = pn2[9];
+    const int cls = (mx >> 27) & 3;
+    const bool isb2 = (mx >> 29) & 1, fric = cls == 2;
+    const int part = my & 0xFFFF;
+    const bool two = part != GZ_ENT_NOPART;
+    // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594)
+    double nlam = 1.0;
+    if (!BOX && due && fric) nlam = (pc - (size_t)((unsigned)my >> 16) * STR)[13 + 2 * S];
+    // this body's half of the dot product, term by term in the reference's left-to-right order
+    double d = a[0] * J[0];
+#pragma unroll
+    for (int t = 1; t < 6; t++) d += a[t] * J[t];
+    if (more) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) { const double2 x = pn2[k]; J[2 * k] = x.x; J[2 * k + 1] = x.y; }
+    }
+    double pd = 0.0;
+    if (MULTI) {
+      double *x = xch + (size_t)(T & 1) * LW;
+      x[threadIdx.x] = d;
+      __syncthreads();
+      if (due && two) pd = x[2 * part + S];
+    } else {
+      if (__any_sync(0xffffffffu, due && two)) pd = __shfl_sync(0xffffffffu, d, lane_base + 2 * (two ? part : bl) + S);
+    }
+    const double d1 = isb2 ? pd : d, d2 = isb2 ? d : pd;
+    const double old_lambda = lam;
+    double delta = rhs - old_lambda * adcfm;
+    delta -= d1;
+    { const double delta2 = delta - d2; delta = two ? delta2 : delta; }
+    const double hl = hi * nlam;
+    const double hf = __hiloint2double(__double2hiint(hl) & 0x7fffffff, __double2loint(hl));
+    const double nhf = __hiloint2double(__double2hiint(hl) | 0x80000000, __double2loint(hl));
+    const double hi_act = fric ? hf : hi, lo_act = fric ? nhf : lo;
+    double nl = old_lambda + delta;
+    const double dlo = lo_act - old_lambda, dhi = hi_act - old_lambda;
+    const bool below = nl < lo_act, above = !below && nl > hi_act;
+    delta = below ? dlo : (above ? dhi : delta);
+    nl = below ? lo_act : (above ? hi_act : nl);
+    // SMOOTH_LAMBDA on the lambda solve of non-bilateral rows; delta is not recomputed after it (:687-691 vs :706)
+    const double sm = smooth1 * nl + smooth * old_lambda;
+    const double nlw = (S == 0 && cls != 0) ? sm : nl;
+    if (due) {
+      pc[13 + 2 * S] = nlw;
+#pragma unroll
+      for (int t = 0; t < 6; t++) a[t] += delta * iM[t];
+      // rms_dlambda / rms_constraint_residual (:700-760, 814-855): the sums restart every sweep, so the last
+      // sweep that touches a class survives: iters - 1 for bilateral and normal rows, total - 1 for friction
+      if (S == 0 && !isb2 && sweep == (fric ? total : iters) - 1) {
+        const double dd = delta * delta, e2 = dd * B.ent_ad2[e0 + i];
+        if (cls == 0) { st_acc[0] += dd; st_err[0] += e2; st_cnt[0]++; }
+        else if (cls == 1) { st_acc[1] += dd; st_err[1] += e2; st_cnt[1]++; }
+        else { st_acc[2] += dd; st_err[2] += e2; st_cnt[2]++; }
+      }
+      T_due = 0x7fffffff;
+    }
+    if (more) {   // (after this round's lambda store, so a one-entry list reads back what it just wrote)
+#pragma unroll
+      for (int k = 0; k < 3; k++) { const double2 y = pn2[3 + k]; iM[2 * k] = y.x; iM[2 * k + 1] = y.y; }
+      const double2 rl = pn2[6 + S], cl = pn2[8];
+      rhs = rl.x; lam = rl.y; adcfm = cl.x; lo = cl.y; hi = hmn.x;
+      mx = __double2loint(hmn.y); my = __double2hiint(hmn.y);
+      i = inx; sweep = nsw;
+      T_due = sweep * R + (mx & GZ_ENT_OFFMASK);
+    }
+  }
+  return Tlast;
+}
+
+// Shared-memory class of a CTA: 0 if the entries of all its worlds fit the small budget, 1 the large one,
+// 2 neither (the CTA then reads the pool).  Uniform over the CTA.
+__device__ __forceinline__ int pgsb_cta_entries(const DevBatch &B, const PgsbCfg &cfg) {
+  int n = 0;
+  for (int s = 0; s < cfg.wpc; s++) {
+    const int w = blockIdx.x * cfg.wpc + s;
+    if (w < B.n_worlds) n += B.wsb[w].w;
+  }
+  return n;
+}
+
+template <bool MULTI, bool BOX>
+__global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg cfg, int nres_small) {
+  extern __shared__ __align__(16) double shd[];
+  const int tid = threadIdx.x;
+  const int LW = cfg.lw;
+  // ---- is this CTA of this launch's class?
+  const int cta_ent = pgsb_cta_entries(B, cfg);
+  const bool res = cta_ent <= cfg.nres;
+  if (cfg.cls == 0 && !res) return;                                   // small class: only what fits
+  if (cfg.cls == 1 && cta_ent <= nres_small) return;                  // large class: what the small one left (pool if too large)
+  const int wslot = MULTI ? 0 : tid / LW, lw = MULTI ? tid : tid % LW;
+  const int bl = lw >> 1, S = lw & 1;
+  const int w = blockIdx.x * cfg.wpc + wslot;
+  const bool live_w = w < B.n_worlds;
+  WorldInfo wi;
+  wi.nb = 0; wi.body0 = 0; wi.row0 = 0;
+  int4 sc = make_int4(1, 0, 0, 0);
+  if (live_w) { wi = B.world[w]; sc = B.wsb[w]; }
+  const int R = sc.x, nent = sc.w;
+  // ---- stage the entries of the CTA's worlds in shared memory (world after world, 22-double stride)
+  int soff = 0;   // first staged entry of this world
+  if (!MULTI)
+    for (int s = 0; s < wslot; s++) soff += B.wsb[blockIdx.x * cfg.wpc + s].w;
+  if (res) {
+    const int n2 = nent * (GZ_ENT / 2);
+    const double2 *src = reinterpret_cast<const double2 *>(B.ent + (size_t)sc.z * GZ_ENT);
+    double2 *dst = reinterpret_cast<double2 *>(shd + (size_t)soff * GZ_ENTS);
+    for (int q = lw; q < n2; q += LW) dst[(q / (GZ_ENT / 2)) * (GZ_ENTS / 2) + q % (GZ_ENT / 2)] = src[q];
+  }
+  double *xch = shd + (size_t)cfg.nres * GZ_ENTS;   // MULTI: [2][LW] partial dot products
+  if (MULTI) __syncthreads(); else __syncwarp();
+  // ---- this lane's list
+  int cnt = 0, e0 = sc.z, fric0 = 0;
+  if (live_w && bl < wi.nb) { const int4 bs = B.bsched[wi.body0 + bl]; e0 = bs.x; cnt = bs.y; fric0 = bs.z; }
+  double *lp = res ? shd + (size_t)(soff + (e0 - sc.z)) * GZ_ENTS : B.ent + (size_t)e0 * GZ_ENT;
+  const int lstr = res ? GZ_ENTS : GZ_ENT;
+  // ---- initial caccel = iMJ * lambda0 over the warm-started (persistent-joint) rows, in row index order per
+  // body (multiply_invM_JT, quickstep_util.cpp:101-119): the bilateral entries lead every list
+  double a[6] = {0, 0, 0, 0, 0, 0};
+  if (B.p.warm_start > 0) {
+    for (int q = 0; q < cnt; q++) {
+      const double *p = lp + (size_t)q * lstr;
+      const int mx = __double2loint(p[19]);
+      if (((mx >> 27) & 3) != 0) break;
+      const double l0 = p[13 + 2 * S];
+#pragma unroll
+      for (int t = 0; t < 6; t++) a[t] += p[6 + t] * l0;
+    }
+  }
+  double st_acc[3] = {0, 0, 0}, st_err[3] = {0, 0, 0};
+  int st_cnt[3] = {0, 0, 0};
+  const int lane_base = MULTI ? 0 : (tid & 31) - lw;   // first lane of this world in the warp
+  int Tlast;
+  if (res) Tlast = pgsb_sweeps<true, MULTI, BOX>(B, lp, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch, e0, a, st_acc, st_err, st_cnt);
+  else Tlast = pgsb_sweeps<false, MULTI, BOX>(B, lp, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch, e0, a, st_acc, st_err, st_cnt);
+  // ---- results: caccel to the bodies, lambda back to the rows (k_lambda_save copies them to the joints)
+  if (live_w && bl < wi.nb) {
+    BodyStep &bs = B.bstep[wi.body0 + bl];
+    double *o = S ? bs.caccel_erp : bs.caccel;
+#pragma unroll
+    for (int t = 0; t < 6; t++) o[t] = a[t];
+    Row *rw = B.row + wi.row0;
+    for (int q = 0; q < cnt; q++) {
+      const int r = B.ent_row[e0 + q];
+      if (r < 0) continue;
+      const double v = lp[(size_t)q * lstr + 13 + 2 * S];
+      if (S) rw[r].lambda_erp = v; else rw[r].lambda = v;
+    }
+  }
+  // ---- statistics: reduce over the lanes of the world
+  if (MULTI) {
+    __syncthreads();
+    double *red = shd;   // the staged entries are dead now
+    for (int q = 0; q < 3; q++) {
+      red[(size_t)(3 * q + 0) * LW + tid] = st_acc[q];
+      red[(size_t)(3 * q + 1) * LW + tid] = st_err[q];
+      red[(size_t)(3 * q + 2) * LW + tid] = (double)st_cnt[q];
+    }
+    __syncthreads();
+    if (tid < 9) {
+      double s = 0;
+      for (int k = 0; k < LW; k++) s += red[(size_t)tid * LW + k];
+      red[(size_t)tid * LW] = s;
+    }
+    __syncthreads();
+    for (int q = 0; q < 3; q++) {
+      st_acc[q] = red[(size_t)(3 * q + 0) * LW]; st_err[q] = red[(size_t)(3 * q + 1) * LW];
+      st_cnt[q] = (int)red[(size_t)(3 * q + 2) * LW];
+    }
+  } else {
+    for (int dd = 1; dd < LW; dd <<= 1) {
+#pragma unroll
+      for (int q = 0; q < 3; q++) {
+        st_acc[q] += __shfl_xor_sync(0xffffffffu, st_acc[q], dd);
+        st_err[q] += __shfl_xor_sync(0xffffffffu, st_err[q], dd);
+        st_cnt[q] += __shfl_xor_sync(0xffffffffu, st_cnt[q], dd);
+      }
+    }
+  }
+  if (live_w && lw == 0) {
+    WorldStep &ws = B.wstep[w];
+    const double c[3] = {(double)st_cnt[0], (double)st_cnt[1], (double)st_cnt[2]};
+    const double tot = c[0] + c[1] + c[2];   // quickstep_pgs_lcp.cpp:814-855
+    for (int q = 0; q < 3; q++) {
+      ws.rms_dlambda[q] = sqrt(c[q] > 0 ? st_acc[q] / c[q] : 0.0);
+      ws.rms_residual[q] = sqrt(c[q] > 0 ? st_err[q] / c[q] : 0.0);
+    }
+    const double sa = st_acc[0] + st_acc[1] + st_acc[2], se = st_err[0] + st_err[1] + st_err[2];
+    ws.rms_dlambda[3] = sqrt(sa > 0 ? sa / tot : 0.0);
+    ws.rms_residual[3] = sqrt(se > 0 ? se / tot : 0.0);
+    ws.num_contacts_stat = st_cnt[1];
+    ws.pad[0] = Tlast + 1; ws.pad[1] = R * 256 + (res ? 1 : 0);   // instrumentation: rounds, period, staged or not
+  }
+}
+
+}  // namespace gz

@@ -17,6 +17,7 @@
 #define GZ_NRUNG 160
 #define GZ_NBUCKET (10 * GZ_NRUNG)
 #define GZ_PAIR_MAXC 16  // contacts one geom pair can yield (box-box: 8, cylinder-box: up to 13)
+#define GZ_PGSB_NKEY 512   // period histogram of k_border: periods >= 511 share the last key
 #define GZ_ENT 20          // doubles per body-owner PGS entry (k_pgsb.cuh)
 #define GZ_CHAIN_NCLS 4   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
 
@@ -162,11 +163,15 @@ struct DevBatch {
   int pgs_impl;          // 1: body-owner sweeps (k_pgsb), 0: the round-1 row-slot sweeps (k_pgs / k_pgs_chain)
   double *ent;           // [ent_cap][GZ_ENT] half-records, one per (row, body), grouped per body in order[] sequence
   int *ent_row;          // [ent_cap] world-local row index if this entry is the row's body-1 half (lambda write-back), else -1
-  double *ent_ad2;       // [ent_cap] 1 / Ad^2 (statistics sweeps only)
+  double *ent_ad2;       // [ent_cap] 1 / Ad^2 (statistics)
+  double *ent_dl;        // [ent_cap][2] last delta of each entry, for entries swept from the pool (statistics)
   long ent_cap;
   unsigned long long *ent_cursor;   // [2] bump allocators, used alternately by step parity (the idle one is reset)
   int4 *bsched;          // [nb] {first entry (pool index), entries, first friction entry (list index), 0}
   int4 *wsb;             // [n_worlds] {period R, stages, first entry, entries}
+  int *rk_count;         // [2][GZ_PGSB_NKEY] worlds per period this step (by step parity, like ent_cursor)
+  int *wkey;             // [n_worlds] period key | rank among the worlds of that key << 10
+  int *wperm;            // [n_worlds] sweep order: worlds by period, longest first (k_border)
   int *sticky;           // [4] OR of every step's overflow masks since the last check, first world, spare
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)
   double *io_out;        // [nb][13] staged pos(3) quat(4) lvel(3) avel(3)

@@ -52,8 +52,9 @@ struct gzcuda_batch {
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
   int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
-  PgsbCfg pgsb2;                      // the large shared-memory class of the one-warp CTAs
-  size_t pgsb2_smem = 0;
+  PgsbCfg pgsbc[3];                   // the shared-memory classes of the one-warp CTAs, ascending (pgsbc[0] == pgsb)
+  size_t pgsbc_smem[3] = {0, 0, 0};
+  int pgsb_ncls = 1;
   PgsbCfg pgsb;                       // body-owner sweeps (k_pgsb.cuh): lane layout, CTA shape, shared memory
   bool pgsb_multi = false;
   int pgsb_threads = 32, pgsb_ctas = 0;
@@ -352,17 +353,27 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if (d.pgs_impl == 1) {
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
-    const size_t per_ent = GZ_ENT * sizeof(double) + sizeof(int) + sizeof(double);
+    const size_t per_ent = GZ_ENT * sizeof(double) + sizeof(int) + 3 * sizeof(double);
     long want = 2 * row_tot + 1024;
     const long most = (long)(free_b / 4 / per_ent);
     d.ent_cap = std::max(4096L, std::min(want, most));
     if (d.ent_cap > 0x7ffffff0L) d.ent_cap = 0x7ffffff0L;
     if ((rc = dev_alloc(b, &d.ent, (size_t)GZ_ENT * d.ent_cap))) return rc;
+    {   // the pool's last entry: the all-zero dummy entry (no partner) of lanes without rows
+      double dm[GZ_ENT] = {0};
+      const int meta[2] = {0, GZ_ENT_NOPART};
+      memcpy(&dm[19], meta, sizeof(double));
+      CK(cudaMemcpy(d.ent + (size_t)GZ_ENT * (d.ent_cap - 1), dm, sizeof(dm), cudaMemcpyHostToDevice));
+    }
     if ((rc = dev_alloc(b, &d.ent_row, (size_t)d.ent_cap))) return rc;
     if ((rc = dev_alloc(b, &d.ent_ad2, (size_t)d.ent_cap))) return rc;
+    if ((rc = dev_alloc(b, &d.ent_dl, (size_t)2 * d.ent_cap))) return rc;
     if ((rc = dev_alloc(b, &d.ent_cursor, (size_t)2))) return rc;
     if ((rc = dev_alloc(b, &d.bsched, (size_t)nb))) return rc;
     if ((rc = dev_alloc(b, &d.wsb, (size_t)W))) return rc;
+    if ((rc = dev_alloc(b, &d.rk_count, (size_t)2 * GZ_PGSB_NKEY))) return rc;
+    if ((rc = dev_alloc(b, &d.wkey, (size_t)W))) return rc;
+    if ((rc = dev_alloc(b, &d.wperm, (size_t)W))) return rc;
     int bp = 1;
     while (bp < max_nb) bp <<= 1;
     PgsbCfg &c = b->pgsb;
@@ -374,22 +385,33 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     // Shared memory per CTA for staged entries (176 B each).  One-warp CTAs come in two classes: the small one
     // (7 CTAs per SM) takes the CTAs whose worlds fit it, the large one (3 per SM) the rest; what fits neither
     // reads the pool.  A multi-warp CTA (one world) has one class.
-    size_t kb1 = b->pgsb_multi ? 128 : 32, kb2 = 72;
-    if (const char *e = getenv("GZCUDA_PGSB_KB")) kb1 = (size_t)std::max(0, atoi(e));
-    if (const char *e = getenv("GZCUDA_PGSB_KB2")) kb2 = (size_t)std::max(0, atoi(e));
-    kb1 = std::min<size_t>(kb1, 200); kb2 = std::min<size_t>(std::max(kb2, kb1), 200);
+    size_t kb[3] = {b->pgsb_multi ? (size_t)128 : (size_t)32, 72, 200};
+    if (const char *e = getenv("GZCUDA_PGSB_KB")) {   // comma-separated, ascending
+      const char *q = e;
+      for (int i = 0; i < 3 && *q; i++) {
+        kb[i] = (size_t)std::max(0, atoi(q));
+        while (*q && *q != ',') q++;
+        if (*q == ',') q++;
+      }
+    }
+    for (int i = 0; i < 3; i++) kb[i] = std::min<size_t>(std::max(kb[i], i ? kb[i - 1] : 0), 200);
     const size_t ent_b = GZ_ENTS * sizeof(double);
     const size_t xch_b = b->pgsb_multi ? (size_t)2 * c.lw * sizeof(double) : 0;
     const size_t red_b = b->pgsb_multi ? (size_t)9 * c.lw * sizeof(double) : 0;
-    c.nres = (int)(kb1 * 1024 / ent_b);
+    c.nres = (int)(kb[0] * 1024 / ent_b) - 1;
     c.cls = b->pgsb_multi ? -1 : 0;
-    b->pgsb2 = c;
-    b->pgsb2.nres = (int)(kb2 * 1024 / ent_b);
-    b->pgsb2.cls = 1;
-    b->pgsb_smem = std::max((size_t)c.nres * ent_b + xch_b, red_b);
-    b->pgsb2_smem = (size_t)b->pgsb2.nres * ent_b;
+    b->pgsb_smem = std::max((size_t)(c.nres + 1) * ent_b + xch_b, red_b);
+    b->pgsb_ncls = b->pgsb_multi ? 1 : 3;
+    size_t mx_b = b->pgsb_smem;
+    for (int i = 0; i < 3; i++) {
+      b->pgsbc[i] = c;
+      b->pgsbc[i].nres = (int)(kb[i] * 1024 / ent_b) - 1;
+      b->pgsbc[i].cls = i;
+      b->pgsbc_smem[i] = (size_t)(b->pgsbc[i].nres + 1) * ent_b;
+      if (!b->pgsb_multi) mx_b = std::max(mx_b, b->pgsbc_smem[i]);
+    }
     b->bsched_smem = (size_t)5 * std::max(max_nb, 1) * sizeof(int);
-    const int mx_smem = (int)std::max(b->pgsb_smem, b->pgsb2_smem);
+    const int mx_smem = (int)mx_b;
     for (auto f : {k_pgsb<false, false>, k_pgsb<false, true>, k_pgsb<true, false>, k_pgsb<true, true>}) {
       if (mx_smem > 48 * 1024) CK(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, mx_smem));
       CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
@@ -544,6 +566,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   if (d.pgs_impl == 1) {
     // body-owner sweeps: schedule (integer work on the row counts), row prologue + entries, sweeps
     k_bsched<<<W, 128, b->bsched_smem, b->stream>>>(d);
+    k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
     k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
     if (stage_events) cudaEventRecord(b->evs[2], b->stream);
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
@@ -552,23 +575,26 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
       if (box) k_pgsb<true, true><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
       else k_pgsb<true, false><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
     } else {
-      // the large class beside the small one, on its own stream (fork / join by events); it goes first: its worlds run longest
+      // one launch per shared-memory class, side by side (fork / join by events); the largest class goes first,
+      // on this stream: its worlds run longest
       cudaEventRecord(b->ev_fork, b->stream);
-      cudaStreamWaitEvent(b->stream_chain[GZ_CHAIN_NCLS - 1], b->ev_fork, 0);
-      cudaStream_t s2 = b->stream_chain[GZ_CHAIN_NCLS - 1];
-      if (box) k_pgsb<false, true><<<b->pgsb_ctas, 32, b->pgsb2_smem, s2>>>(d, b->pgsb2, b->pgsb.nres);
-      else k_pgsb<false, false><<<b->pgsb_ctas, 32, b->pgsb2_smem, s2>>>(d, b->pgsb2, b->pgsb.nres);
-      cudaEventRecord(b->ev_join[0], s2);
-      if (box) k_pgsb<false, true><<<b->pgsb_ctas, 32, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
-      else k_pgsb<false, false><<<b->pgsb_ctas, 32, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
-      cudaStreamWaitEvent(b->stream, b->ev_join[0], 0);
+      for (int q = b->pgsb_ncls - 1; q >= 0; q--) {
+        cudaStream_t sq = q == b->pgsb_ncls - 1 ? b->stream : b->stream_chain[q];
+        if (sq != b->stream) cudaStreamWaitEvent(sq, b->ev_fork, 0);
+        const int lower = q > 0 ? b->pgsbc[q - 1].nres : -1;
+        if (box) k_pgsb<false, true><<<b->pgsb_ctas, 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
+        else k_pgsb<false, false><<<b->pgsb_ctas, 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
+        if (sq != b->stream) cudaEventRecord(b->ev_join[q], sq);
+      }
+      for (int q = 0; q < b->pgsb_ncls - 1; q++) cudaStreamWaitEvent(b->stream, b->ev_join[q], 0);
+      b->last_launches++;
       b->last_launches++;
     }
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
     if (stage_events) cudaEventRecord(b->evs[3], b->stream);
     if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
     k_integrate<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
-    b->last_launches += 6;
+    b->last_launches += 7;
     return 0;
   }
   const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16 +

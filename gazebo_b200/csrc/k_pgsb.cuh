@@ -38,6 +38,17 @@ namespace gz {
 #define GZ_ENT_OFFMASK 0x7FFFFFF
 #define GZ_ENT_NOPART 0xFFFF
 
+__device__ __forceinline__ unsigned long long pgsb_gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned pgsb_smid() {
+  unsigned s;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
+  return s & 511u;
+}
+
 struct WScratchB { int *rb1, *rb2, *off, *idx1, *idx2; };
 __device__ inline WScratchB wscratchb(const DevBatch &B, int w) {
   WScratchB s;
@@ -69,7 +80,10 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
   __shared__ int s_R, s_maxoff, s_nent, s_wbase;
   const WScratchB S = wscratchb(B, w);
   const int par = (int)(B.step_index & 1);
-  if (w == 0 && tid == 0) B.ent_cursor[par ^ 1] = 0ull;   // the other parity's allocator: idle this step
+  if (w == 0) {   // the other parity's allocator and period histogram: idle this step
+    if (tid == 0) B.ent_cursor[par ^ 1] = 0ull;
+    for (int q = tid; q < GZ_PGSB_NKEY; q += blockDim.x) B.rk_count[(par ^ 1) * GZ_PGSB_NKEY + q] = 0;
+  }
   for (int b = tid; b < nb; b += blockDim.x) { last[b] = -1; first[b] = -1; cnt[b] = 0; fr0[b] = -1; }
   if (m > 0) {
     for (int k = tid; k < wi.nj; k += blockDim.x) {
@@ -121,13 +135,17 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
     long long wbase = 0;
     if (nent > 0) {
       wbase = (long long)atomicAdd(&B.ent_cursor[par], (unsigned long long)nent);
-      if (wbase + nent > B.ent_cap || maxoff > GZ_ENT_OFFMASK) {   // pool exhausted: the world is not solved, the step is flagged
+      if (wbase + nent > B.ent_cap - 1 || maxoff > GZ_ENT_OFFMASK) {   // (the pool's last entry is the dummy entry)   // pool exhausted: the world is not solved, the step is flagged
         ws.overflow |= 16;
         nent = 0;
       }
     }
     s_R = R; s_maxoff = maxoff; s_nent = nent; s_wbase = (int)wbase;
     B.wsb[w] = make_int4(R, maxoff < 0 ? 0 : maxoff / R + 1, (int)wbase, nent);
+    // k_border sorts the worlds by period, longest first: worlds of a warp then run for about the same number
+    // of rounds, and the longest ones start first
+    const int key = nent > 0 ? min(R, GZ_PGSB_NKEY - 1) : 0;
+    B.wkey[w] = key | (atomicAdd(&B.rk_count[par * GZ_PGSB_NKEY + key], 1) << 10);
     if (nent == 0)
       for (int pos = 0; pos < m; pos++) S.off[pos] = -1;   // rows without entries: k_rowfinish skips them
   }
@@ -137,38 +155,73 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
     B.bsched[wi.body0 + b] = nent > 0 ? make_int4(wbase + base[b], cnt[b], fr0[b] < 0 ? cnt[b] : fr0[b], 0) : make_int4(0, 0, 0, 0);
 }
 
+// Places every world in the sweep order: by period, longest first (counting sort: k_bsched counted the periods
+// and gave every world its rank among those of equal period).  Each block rebuilds the prefix over the keys.
+__global__ void __launch_bounds__(256) k_border(DevBatch B) {
+  __shared__ int pre[GZ_PGSB_NKEY];
+  const int par = (int)(B.step_index & 1);
+  const int *cnt = B.rk_count + par * GZ_PGSB_NKEY;
+  for (int q = threadIdx.x; q < GZ_PGSB_NKEY; q += blockDim.x) pre[q] = cnt[GZ_PGSB_NKEY - 1 - q];   // descending key
+  __syncthreads();
+  if (threadIdx.x < 32) {   // exclusive scan of GZ_PGSB_NKEY values by one warp
+    int carry = 0;
+    for (int b0 = 0; b0 < GZ_PGSB_NKEY; b0 += 32) {
+      const int v = pre[b0 + threadIdx.x];
+      int x = v;
+      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, x, d); if ((int)threadIdx.x >= d) x += t; }
+      pre[b0 + threadIdx.x] = carry + x - v;
+      carry += __shfl_sync(0xffffffffu, x, 31);
+    }
+  }
+  __syncthreads();
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= B.n_worlds) return;
+  const int k = B.wkey[w];
+  B.wperm[pre[GZ_PGSB_NKEY - 1 - (k & 1023)] + (k >> 10)] = w;
+}
+
 // ---- the sweeps ---------------------------------------------------------------------------------------
+template <bool V> struct PgsbTag { static constexpr bool value = V; };
 struct PgsbCfg {
   int lw;        // lanes per world = 2 * padded body count (power of two, >= 2)
   int wpc;       // worlds per CTA (32 / lw for one-warp CTAs, 1 for multi-warp CTAs)
   int nres;      // entries the CTA can stage in shared memory (all its worlds together)
-  int cls;       // this launch takes the CTAs of this shared-memory class (k_pgsb_class), -1: every CTA, from the pool
+  int cls;       // shared-memory class of this launch (0..2, ascending budgets), -1: the only launch (multi-warp CTAs)
 };
 
 // Entries staged in shared memory are padded to 22 doubles (176 B = 11 x 16 B, an odd number of 16-byte bank
 // groups) so that the 16 distinct entries a warp reads per 128-bit load spread over all banks.
 #define GZ_ENTS 22
 
-// The sweeps of one lane.  RES: the lane's list is in shared memory (stride GZ_ENTS), else in the pool (stride
-// GZ_ENT).  The current entry lives in registers; its successor is loaded IN PLACE, field by field right after
-// the last use of each field in this round (J after the dot product, iMJ and the scalars after the accumulator
-// update), so the loads run beside the arithmetic and no register is ever moved.
+// The sweeps of one lane = (body, solve).  RES: the lane's list is in shared memory (stride GZ_ENTS, lofs doubles
+// into the dynamic shared array), else in the pool (lp_g, stride GZ_ENT).  The current entry lives in registers;
+// its successor is loaded IN PLACE, field by field right after the last use of each field in this pass (J after
+// the dot product, iMJ and the scalars after the accumulator update), so the loads run beside the arithmetic and
+// no register is ever moved.  A pass is ONE basic block (no branch, so the compiler interleaves the address and
+// round arithmetic with the dependent FP64 chain): a lane that is not due, or has finished, "moves on" to the
+// entry it already holds and keeps its state through selects and predicated updates; a lane without rows holds
+// an all-zero dummy entry.  The last delta of every entry is left beside it (shared memory: the spare doubles of
+// the padded entry; pool: ent_dl) for the statistics.
 template <bool RES, bool MULTI, bool BOX>
-__device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp, const int cnt, const int fric0, const int R,
-                                           const int nstage, const int S, const int bl, const int lane_base,
-                                           const int LW, double *xch, const int e0, double (&a)[6],
-                                           double (&st_acc)[3], double (&st_err)[3], int (&st_cnt)[3]) {
+__device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp_g, const int lofs, const int cnt, const int fric0,
+                                           const int R, const int nstage, const int S, const int bl, const int lane_base,
+                                           const int LW, const int xch_ofs, const int e0, double (&a)[6]) {
+  extern __shared__ __align__(16) double shd[];
   constexpr int STR = RES ? GZ_ENTS : GZ_ENT;
+  double *const lp = RES ? shd + lofs : lp_g;
   const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
   const double smooth = B.p.smooth_contacts, smooth1 = 1.0 - smooth;
-  int i = (iters > 0) ? 0 : fric0, sweep = 0;
-  double J[6], iM[6], rhs = 0, lam = 0, adcfm = 0, lo = 0, hi = 0;
-  int mx = 0, my = GZ_ENT_NOPART;
-  int T_due = 0x7fffffff;
-#pragma unroll
-  for (int t = 0; t < 6; t++) { J[t] = 0; iM[t] = 0; }
-  if (i < cnt && total > 0) {
-    const double2 *p2 = reinterpret_cast<const double2 *>(lp + (size_t)i * STR);
+  int sweep = 0;
+  double *pc = lp + (size_t)((iters > 0) ? 0 : fric0) * STR;   // current entry
+  double *const p0 = lp, *const pfr = lp + (size_t)fric0 * STR, *const pend = lp + (size_t)cnt * STR;
+  double *dlc = B.ent_dl + 2 * ((size_t)e0 + ((iters > 0) ? 0 : fric0)) + S;   // pool: where the current entry's delta goes
+  double *const dl0 = B.ent_dl + 2 * (size_t)e0 + S, *const dlfr = dl0 + 2 * fric0;
+  const bool alive = pc < pend && total > 0;
+  if (!alive) pc = RES ? shd + xch_ofs - GZ_ENTS : B.ent + (size_t)(B.ent_cap - 1) * GZ_ENT;   // the all-zero dummy entry
+  double J[6], iM[6], rhs, lam, adcfm, lo, hi;
+  int mx, my;
+  {
+    const double2 *p2 = reinterpret_cast<const double2 *>(pc);
 #pragma unroll
     for (int k = 0; k < 3; k++) {
       const double2 x = p2[k], y = p2[3 + k];
@@ -177,10 +230,10 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp, const 
     const double2 rl = p2[6 + S], cl = p2[8], hm = p2[9];
     rhs = rl.x; lam = rl.y; adcfm = cl.x; lo = cl.y; hi = hm.x;
     mx = __double2loint(hm.y); my = __double2hiint(hm.y);
-    T_due = mx & GZ_ENT_OFFMASK;
   }
+  int T_due = alive ? (mx & GZ_ENT_OFFMASK) : 0x7fffffff;
   const int rounds_multi = (total > 0 && nstage > 0) ? (total + nstage - 1) * R : 0;
-  int T = -1, Tlast = 0;
+  int T = -1, npass = 0;
   for (;;) {
     if (MULTI) {
       if (++T >= rounds_multi) break;
@@ -188,45 +241,50 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp, const 
       T = __reduce_min_sync(0xffffffffu, T_due);   // event-driven: the next round in which any lane of the warp is due
       if (T == 0x7fffffff) break;
     }
-    Tlast = T;
+    npass++;
     const bool due = (T_due == T);
-    // where this lane goes next
-    int inx = i + 1, nsw = sweep;
-    if (inx == cnt) { nsw = sweep + 1; inx = nsw < iters ? 0 : fric0; }
-    const bool more = due && nsw < total && inx < cnt;
-    double *pc = lp + (size_t)i * STR;
-    const double2 *pn2 = reinterpret_cast<const double2 *>(lp + (size_t)inx * STR);
-    double2 hmn = make_double2(0.0, 0.0);
-    if (more) hmn = pn2[9];
+    // where this lane goes next: its next entry, or (not due / finished) the entry it holds
+    double *pn = pc + STR, *dln = dlc + 2;
+    int nsw = sweep;
+    if (pn == pend) { nsw = sweep + 1; pn = nsw < iters ? p0 : pfr; dln = nsw < iters ? dl0 : dlfr; }
+    const bool more = due && nsw < total && pn != pend;
+    pn = more ? pn : pc;
+    dln = more ? dln : dlc;
+    nsw = more ? nsw : sweep;
+    const double2 *pn2 = reinterpret_cast<const double2 *>(pn);
+    const double2 hmn = pn2[9];
     const int cls = (mx >> 27) & 3;
-    const bool isb2 = (mx >> 29) & 1, fric = cls == 2;
-    const int part = my & 0xFFFF;
-    const bool two = part != GZ_ENT_NOPART;
-    // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594)
+    const bool fric = cls == 2;
+    // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594);
+    // (the distance to the normal row is 0 for the other classes: they read their own lambda and ignore it)
     double nlam = 1.0;
-    if (!BOX && due && fric) nlam = (pc - (size_t)((unsigned)my >> 16) * STR)[13 + 2 * S];
+    if (!BOX) nlam = (pc - (size_t)((unsigned)my >> 16) * STR)[13 + 2 * S];
     // this body's half of the dot product, term by term in the reference's left-to-right order
     double d = a[0] * J[0];
 #pragma unroll
     for (int t = 1; t < 6; t++) d += a[t] * J[t];
-    if (more) {
 #pragma unroll
-      for (int k = 0; k < 3; k++) { const double2 x = pn2[k]; J[2 * k] = x.x; J[2 * k + 1] = x.y; }
-    }
-    double pd = 0.0;
-    if (MULTI) {
-      double *x = xch + (size_t)(T & 1) * LW;
-      x[threadIdx.x] = d;
-      __syncthreads();
-      if (due && two) pd = x[2 * part + S];
-    } else {
-      if (__any_sync(0xffffffffu, due && two)) pd = __shfl_sync(0xffffffffu, d, lane_base + 2 * (two ? part : bl) + S);
-    }
-    const double d1 = isb2 ? pd : d, d2 = isb2 ? d : pd;
+    for (int k = 0; k < 3; k++) { const double2 x = pn2[k]; J[2 * k] = x.x; J[2 * k + 1] = x.y; }
     const double old_lambda = lam;
     double delta = rhs - old_lambda * adcfm;
-    delta -= d1;
-    { const double delta2 = delta - d2; delta = two ? delta2 : delta; }
+    {
+      double pd = 0.0;
+      const int part = my & 0xFFFF;
+      const bool two = part != GZ_ENT_NOPART;
+      if (MULTI) {
+        double *x = shd + xch_ofs + (size_t)(T & 1) * LW;
+        x[threadIdx.x] = d;
+        __syncthreads();
+        pd = x[two ? 2 * part + S : threadIdx.x];
+      } else {
+        pd = __shfl_sync(0xffffffffu, d, lane_base + 2 * (two ? part : bl) + S);
+      }
+      const bool isb2 = (mx >> 29) & 1;
+      const double d1 = isb2 ? pd : d, d2 = isb2 ? d : pd;
+      delta -= d1;
+      const double delta2 = delta - d2;
+      delta = two ? delta2 : delta;
+    }
     const double hl = hi * nlam;
     const double hf = __hiloint2double(__double2hiint(hl) & 0x7fffffff, __double2loint(hl));
     const double nhf = __hiloint2double(__double2hiint(hl) | 0x80000000, __double2loint(hl));
@@ -239,31 +297,20 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp, const 
     // SMOOTH_LAMBDA on the lambda solve of non-bilateral rows; delta is not recomputed after it (:687-691 vs :706)
     const double sm = smooth1 * nl + smooth * old_lambda;
     const double nlw = (S == 0 && cls != 0) ? sm : nl;
-    if (due) {
-      pc[13 + 2 * S] = nlw;
+    if (due) pc[13 + 2 * S] = nlw;
+    if (due) { if (RES) pc[20 + S] = delta; else *dlc = delta; }
 #pragma unroll
-      for (int t = 0; t < 6; t++) a[t] += delta * iM[t];
-      // rms_dlambda / rms_constraint_residual (:700-760, 814-855): the sums restart every sweep, so the last
-      // sweep that touches a class survives: iters - 1 for bilateral and normal rows, total - 1 for friction
-      if (S == 0 && !isb2 && sweep == (fric ? total : iters) - 1) {
-        const double dd = delta * delta, e2 = dd * B.ent_ad2[e0 + i];
-        if (cls == 0) { st_acc[0] += dd; st_err[0] += e2; st_cnt[0]++; }
-        else if (cls == 1) { st_acc[1] += dd; st_err[1] += e2; st_cnt[1]++; }
-        else { st_acc[2] += dd; st_err[2] += e2; st_cnt[2]++; }
-      }
-      T_due = 0x7fffffff;
-    }
-    if (more) {   // (after this round's lambda store, so a one-entry list reads back what it just wrote)
+    for (int t = 0; t < 6; t++) { const double u = a[t] + delta * iM[t]; a[t] = due ? u : a[t]; }
+    // (after this pass's lambda store, so a one-entry list reads back what it just wrote)
 #pragma unroll
-      for (int k = 0; k < 3; k++) { const double2 y = pn2[3 + k]; iM[2 * k] = y.x; iM[2 * k + 1] = y.y; }
-      const double2 rl = pn2[6 + S], cl = pn2[8];
-      rhs = rl.x; lam = rl.y; adcfm = cl.x; lo = cl.y; hi = hmn.x;
-      mx = __double2loint(hmn.y); my = __double2hiint(hmn.y);
-      i = inx; sweep = nsw;
-      T_due = sweep * R + (mx & GZ_ENT_OFFMASK);
-    }
+    for (int k = 0; k < 3; k++) { const double2 y = pn2[3 + k]; iM[2 * k] = y.x; iM[2 * k + 1] = y.y; }
+    const double2 rl = pn2[6 + S], cl = pn2[8];
+    rhs = rl.x; lam = rl.y; adcfm = cl.x; lo = cl.y; hi = hmn.x;
+    mx = __double2loint(hmn.y); my = __double2hiint(hmn.y);
+    pc = pn; dlc = dln; sweep = nsw;
+    T_due = more ? sweep * R + (mx & GZ_ENT_OFFMASK) : (due ? 0x7fffffff : T_due);
   }
-  return Tlast;
+  return npass;
 }
 
 // Shared-memory class of a CTA: 0 if the entries of all its worlds fit the small budget, 1 the large one,
@@ -271,8 +318,8 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp, const 
 __device__ __forceinline__ int pgsb_cta_entries(const DevBatch &B, const PgsbCfg &cfg) {
   int n = 0;
   for (int s = 0; s < cfg.wpc; s++) {
-    const int w = blockIdx.x * cfg.wpc + s;
-    if (w < B.n_worlds) n += B.wsb[w].w;
+    const int q = blockIdx.x * cfg.wpc + s;
+    if (q < B.n_worlds) n += B.wsb[B.wperm[q]].w;
   }
   return n;
 }
@@ -285,12 +332,15 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
   // ---- is this CTA of this launch's class?
   const int cta_ent = pgsb_cta_entries(B, cfg);
   const bool res = cta_ent <= cfg.nres;
-  if (cfg.cls == 0 && !res) return;                                   // small class: only what fits
-  if (cfg.cls == 1 && cta_ent <= nres_small) return;                  // large class: what the small one left (pool if too large)
+  // class c takes the CTAs whose entries fit it and not the class below; the last class also takes what fits
+  // nowhere (those CTAs read the pool)
+  if (cfg.cls >= 0 && (cta_ent <= nres_small || (!res && cfg.cls < 2))) return;
   const int wslot = MULTI ? 0 : tid / LW, lw = MULTI ? tid : tid % LW;
   const int bl = lw >> 1, S = lw & 1;
-  const int w = blockIdx.x * cfg.wpc + wslot;
-  const bool live_w = w < B.n_worlds;
+  const unsigned long long g0 = pgsb_gtimer();
+  const int wq = blockIdx.x * cfg.wpc + wslot;   // place in the sweep order (k_border)
+  const bool live_w = wq < B.n_worlds;
+  const int w = live_w ? B.wperm[wq] : 0;
   WorldInfo wi;
   wi.nb = 0; wi.body0 = 0; wi.row0 = 0;
   int4 sc = make_int4(1, 0, 0, 0);
@@ -299,19 +349,25 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
   // ---- stage the entries of the CTA's worlds in shared memory (world after world, 22-double stride)
   int soff = 0;   // first staged entry of this world
   if (!MULTI)
-    for (int s = 0; s < wslot; s++) soff += B.wsb[blockIdx.x * cfg.wpc + s].w;
+    for (int s = 0; s < wslot; s++) soff += B.wsb[B.wperm[blockIdx.x * cfg.wpc + s]].w;
   if (res) {
     const int n2 = nent * (GZ_ENT / 2);
     const double2 *src = reinterpret_cast<const double2 *>(B.ent + (size_t)sc.z * GZ_ENT);
     double2 *dst = reinterpret_cast<double2 *>(shd + (size_t)soff * GZ_ENTS);
     for (int q = lw; q < n2; q += LW) dst[(q / (GZ_ENT / 2)) * (GZ_ENTS / 2) + q % (GZ_ENT / 2)] = src[q];
   }
-  double *xch = shd + (size_t)cfg.nres * GZ_ENTS;   // MULTI: [2][LW] partial dot products
+  const int xch_ofs = (cfg.nres + 1) * GZ_ENTS;   // after the staged entries and the dummy entry; MULTI: [2][LW] partial dot products
+  if (res) {   // the all-zero dummy entry (no partner, never due) of the lanes without rows
+    double *dm = shd + (size_t)cfg.nres * GZ_ENTS;
+    for (int q = lw; q < GZ_ENTS; q += LW) dm[q] = (q == 19) ? __hiloint2double(GZ_ENT_NOPART, 0) : 0.0;
+  }
   if (MULTI) __syncthreads(); else __syncwarp();
   // ---- this lane's list
   int cnt = 0, e0 = sc.z, fric0 = 0;
   if (live_w && bl < wi.nb) { const int4 bs = B.bsched[wi.body0 + bl]; e0 = bs.x; cnt = bs.y; fric0 = bs.z; }
-  double *lp = res ? shd + (size_t)(soff + (e0 - sc.z)) * GZ_ENTS : B.ent + (size_t)e0 * GZ_ENT;
+  const int lofs = (soff + (e0 - sc.z)) * GZ_ENTS;
+  double *lp_g = B.ent + (size_t)e0 * GZ_ENT;
+  double *lp = res ? shd + lofs : lp_g;
   const int lstr = res ? GZ_ENTS : GZ_ENT;
   // ---- initial caccel = iMJ * lambda0 over the warm-started (persistent-joint) rows, in row index order per
   // body (multiply_invM_JT, quickstep_util.cpp:101-119): the bilateral entries lead every list
@@ -326,12 +382,27 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
       for (int t = 0; t < 6; t++) a[t] += p[6 + t] * l0;
     }
   }
+  const int lane_base = MULTI ? 0 : (tid & 31) - lw;   // first lane of this world in the warp
+  int npass;
+  if (res) npass = pgsb_sweeps<true, MULTI, BOX>(B, lp_g, lofs, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch_ofs, e0, a);
+  else npass = pgsb_sweeps<false, MULTI, BOX>(B, lp_g, lofs, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch_ofs, e0, a);
+  // rms_dlambda / rms_constraint_residual (quickstep_pgs_lcp.cpp:700-760, 814-855): the sums restart every sweep,
+  // so what survives is the last update of every row (sweep iters - 1 for bilateral and normal rows, total - 1
+  // for friction rows): the deltas the sweeps left beside the entries
   double st_acc[3] = {0, 0, 0}, st_err[3] = {0, 0, 0};
   int st_cnt[3] = {0, 0, 0};
-  const int lane_base = MULTI ? 0 : (tid & 31) - lw;   // first lane of this world in the warp
-  int Tlast;
-  if (res) Tlast = pgsb_sweeps<true, MULTI, BOX>(B, lp, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch, e0, a, st_acc, st_err, st_cnt);
-  else Tlast = pgsb_sweeps<false, MULTI, BOX>(B, lp, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch, e0, a, st_acc, st_err, st_cnt);
+  if (S == 0) {
+    const double *dl = res ? lp + 20 : B.ent_dl + 2 * (size_t)e0;
+    const int dstr = res ? GZ_ENTS : 2;
+    const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
+    for (int q = 0; q < cnt; q++) {
+      const int mx = __double2loint(lp[(size_t)q * lstr + 19]);
+      const int cls = (mx >> 27) & 3;
+      if (((mx >> 29) & 1) || (cls == 2 ? total : iters) <= 0) continue;   // the row's body-1 entry carries it
+      const double de = dl[(size_t)q * dstr], dd = de * de, e2 = dd * B.ent_ad2[e0 + q];
+      st_acc[cls] += dd; st_err[cls] += e2; st_cnt[cls]++;
+    }
+  }
   // ---- results: caccel to the bodies, lambda back to the rows (k_lambda_save copies them to the joints)
   if (live_w && bl < wi.nb) {
     BodyStep &bs = B.bstep[wi.body0 + bl];
@@ -388,7 +459,8 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
     ws.rms_dlambda[3] = sqrt(sa > 0 ? sa / tot : 0.0);
     ws.rms_residual[3] = sqrt(se > 0 ? se / tot : 0.0);
     ws.num_contacts_stat = st_cnt[1];
-    ws.pad[0] = Tlast + 1; ws.pad[1] = R * 256 + (res ? 1 : 0);   // instrumentation: rounds, period, staged or not
+    ws.pad[0] = npass; ws.pad[1] = R * 256 + (res ? 1 : 0);   // instrumentation: rounds, period, staged or not
+    B.prof[16 + 2 * w] = g0; B.prof[16 + 2 * w + 1] = (pgsb_gtimer() & ~511ull) | pgsb_smid();   // timeline, low 9 bits: the SM
   }
 }
 

@@ -39,6 +39,9 @@
 #include <execinfo.h>
 #include <unistd.h>
 #include <cstring>
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -94,11 +97,26 @@ struct RefWorld {
   int num_contacts = 0;
 };
 
+struct RefBatch;
+// Persistent host threads for gzref_step_mt (every thread calls dAllocateODEDataForThread
+// ONCE, ODEPhysics.cc:149,362): created at the first multi-threaded step, parked on a condition variable between
+// calls, so that a short timed window measures stepping and not thread start-up.
+struct StepPool {
+  std::vector<std::thread> th;
+  std::mutex mu;
+  std::condition_variable cv_go, cv_done;
+  long gen = 0;
+  int nsteps = 0, running = 0;
+  bool quit = false;
+  std::atomic<size_t> next{0};
+};
+
 struct RefBatch {
   gz_params p;
   int mode;
   std::vector<RefWorld*> worlds;
   std::vector<int> body_off, geom_off, joint_off;
+  StepPool *pool = nullptr;
 };
 
 bool g_ode_inited = false;
@@ -595,8 +613,10 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
   return B;
 }
 
+static void pool_destroy(RefBatch *B);
 void gzref_destroy(void *h) {
   RefBatch *B = static_cast<RefBatch *>(h);
+  pool_destroy(B);
   for (RefWorld *w : B->worlds) {
     dJointGroupDestroy(w->contactGroup);
     dSpaceDestroy(w->top);
@@ -635,20 +655,64 @@ int gzref_step(void *h, int nsteps) {
   return 0;
 }
 
-// worlds dealt round-robin to nthreads host threads (BASELINE.md §3 procedure)
+// worlds dealt to nthreads persistent host threads (BASELINE.md section 3 procedure); a thread takes the next
+// world from a shared counter and steps it nsteps times (worlds are independent, so the order is free)
+static void pool_worker(RefBatch *B, StepPool *P) {
+  dAllocateODEDataForThread(dAllocateMaskAll);
+  long seen = 0;
+  for (;;) {
+    int nsteps;
+    {
+      std::unique_lock<std::mutex> lk(P->mu);
+      P->cv_go.wait(lk, [&] { return P->quit || P->gen != seen; });
+      if (P->quit) break;
+      seen = P->gen;
+      nsteps = P->nsteps;
+    }
+    for (;;) {
+      const size_t wi = P->next.fetch_add(1);
+      if (wi >= B->worlds.size()) break;
+      for (int s = 0; s < nsteps; s++) step_world(B, B->worlds[wi]);
+    }
+    {
+      std::lock_guard<std::mutex> lk(P->mu);
+      if (--P->running == 0) P->cv_done.notify_all();
+    }
+  }
+  dCleanupODEAllDataForThread();
+}
+
+static void pool_destroy(RefBatch *B) {
+  StepPool *P = B->pool;
+  if (!P) return;
+  { std::lock_guard<std::mutex> lk(P->mu); P->quit = true; }
+  P->cv_go.notify_all();
+  for (auto &t : P->th) t.join();
+  delete P;
+  B->pool = nullptr;
+}
+
 int gzref_step_mt(void *h, int nsteps, int nthreads) {
   RefBatch *B = static_cast<RefBatch *>(h);
   if (nthreads < 1) nthreads = 1;
-  std::vector<std::thread> th;
-  for (int t = 0; t < nthreads; t++) {
-    th.emplace_back([B, t, nthreads, nsteps]() {
-      dAllocateODEDataForThread(dAllocateMaskAll);
-      for (size_t wi = t; wi < B->worlds.size(); wi += nthreads)
-        for (int s = 0; s < nsteps; s++) step_world(B, B->worlds[wi]);
-      dCleanupODEAllDataForThread();
-    });
+  if (B->pool && (int)B->pool->th.size() != nthreads) pool_destroy(B);
+  if (!B->pool) {
+    B->pool = new StepPool;
+    for (int t = 0; t < nthreads; t++) B->pool->th.emplace_back(pool_worker, B, B->pool);
   }
-  for (auto &x : th) x.join();
+  StepPool *P = B->pool;
+  {
+    std::lock_guard<std::mutex> lk(P->mu);
+    P->nsteps = nsteps;
+    P->next.store(0);
+    P->running = nthreads;
+    P->gen++;
+  }
+  P->cv_go.notify_all();
+  {
+    std::unique_lock<std::mutex> lk(P->mu);
+    P->cv_done.wait(lk, [&] { return P->running == 0; });
+  }
   return 0;
 }
 

@@ -27,6 +27,7 @@ static int fail(int code, const std::string &msg) { g_err = msg; return code; }
       return fail(GZCUDA_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));    \
   } while (0)
 
+#define GZ_PGSB_NCLS 8
 struct gzcuda_batch {
   DevBatch d;
   int device = 0;
@@ -52,9 +53,11 @@ struct gzcuda_batch {
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
   int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
-  PgsbCfg pgsbc[3];                   // the shared-memory classes of the one-warp CTAs, ascending (pgsbc[0] == pgsb)
-  size_t pgsbc_smem[3] = {0, 0, 0};
+  PgsbCfg pgsbc[GZ_PGSB_NCLS];        // the shared-memory classes of the one-warp CTAs, ascending budgets
+  size_t pgsbc_smem[GZ_PGSB_NCLS] = {};
   int pgsb_ncls = 1;
+  cudaStream_t pgsb_stream[GZ_PGSB_NCLS] = {};   // one launch per class, side by side
+  cudaEvent_t pgsb_join[GZ_PGSB_NCLS] = {};
   PgsbCfg pgsb;                       // body-owner sweeps (k_pgsb.cuh): lane layout, CTA shape, shared memory
   bool pgsb_multi = false;
   int pgsb_threads = 32, pgsb_ctas = 0;
@@ -141,6 +144,8 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   if (b->ev_fork) cudaEventDestroy(b->ev_fork);
   for (auto &e : b->ev_join) if (e) cudaEventDestroy(e);
   for (auto &st : b->stream_chain) if (st) cudaStreamDestroy(st);
+  for (auto &st : b->pgsb_stream) if (st) cudaStreamDestroy(st);
+  for (auto &e : b->pgsb_join) if (e) cudaEventDestroy(e);
   if (b->stream_copy) cudaStreamDestroy(b->stream_copy);
   for (auto &e : b->ev_frame) if (e) cudaEventDestroy(e);
   for (auto &e : b->ev_copied) if (e) cudaEventDestroy(e);
@@ -385,31 +390,44 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     // Shared memory per CTA for staged entries (176 B each).  One-warp CTAs come in two classes: the small one
     // (7 CTAs per SM) takes the CTAs whose worlds fit it, the large one (3 per SM) the rest; what fits neither
     // reads the pool.  A multi-warp CTA (one world) has one class.
-    size_t kb[3] = {b->pgsb_multi ? (size_t)128 : (size_t)32, 72, 200};
-    if (const char *e = getenv("GZCUDA_PGSB_KB")) {   // comma-separated, ascending
-      const char *q = e;
-      for (int i = 0; i < 3 && *q; i++) {
-        kb[i] = (size_t)std::max(0, atoi(q));
-        while (*q && *q != ',') q++;
-        if (*q == ',') q++;
-      }
-    }
-    for (int i = 0; i < 3; i++) kb[i] = std::min<size_t>(std::max(kb[i], i ? kb[i - 1] : 0), 200);
+    // Shared memory per CTA for staged entries (176 B each).  One-warp CTAs come in classes of ascending budget,
+    // one launch each (a CTA belongs to the smallest class that holds the entries of its worlds; what fits none
+    // reads the pool); class q is sized so that 9 - q CTAs share an SM (233 KB, 1 KB reserved per CTA), the last
+    // one takes a whole SM.  A multi-warp CTA (one world) has one class.
     const size_t ent_b = GZ_ENTS * sizeof(double);
     const size_t xch_b = b->pgsb_multi ? (size_t)2 * c.lw * sizeof(double) : 0;
     const size_t red_b = b->pgsb_multi ? (size_t)9 * c.lw * sizeof(double) : 0;
-    c.nres = (int)(kb[0] * 1024 / ent_b) - 1;
-    c.cls = b->pgsb_multi ? -1 : 0;
-    b->pgsb_smem = std::max((size_t)(c.nres + 1) * ent_b + xch_b, red_b);
-    b->pgsb_ncls = b->pgsb_multi ? 1 : 3;
-    size_t mx_b = b->pgsb_smem;
-    for (int i = 0; i < 3; i++) {
-      b->pgsbc[i] = c;
-      b->pgsbc[i].nres = (int)(kb[i] * 1024 / ent_b) - 1;
-      b->pgsbc[i].cls = i;
-      b->pgsbc_smem[i] = (size_t)(b->pgsbc[i].nres + 1) * ent_b;
-      if (!b->pgsb_multi) mx_b = std::max(mx_b, b->pgsbc_smem[i]);
+    size_t byt[GZ_PGSB_NCLS];
+    b->pgsb_ncls = b->pgsb_multi ? 1 : GZ_PGSB_NCLS;
+    for (int i = 0; i < GZ_PGSB_NCLS; i++) byt[i] = (i == GZ_PGSB_NCLS - 1) ? (size_t)200 * 1024 : ((size_t)233 * 1024) / (9 - i) - 1024 - 64;
+    if (b->pgsb_multi) byt[0] = (size_t)128 * 1024;
+    if (const char *e = getenv("GZCUDA_PGSB_KB")) {   // comma-separated, ascending: replaces the classes
+      const char *q = e;
+      int n = 0;
+      while (n < GZ_PGSB_NCLS && *q) {
+        byt[n++] = (size_t)std::min(200, std::max(1, atoi(q))) * 1024;
+        while (*q && *q != ',') q++;
+        if (*q == ',') q++;
+      }
+      if (!b->pgsb_multi && n > 0) b->pgsb_ncls = n;
     }
+    size_t mx_b = 0;
+    for (int i = 0; i < b->pgsb_ncls; i++) {
+      b->pgsbc[i] = c;
+      b->pgsbc[i].nres = (int)(byt[i] / ent_b) - 1;   // (one slot is the dummy entry)
+      b->pgsbc[i].cls = b->pgsb_multi ? -1 : i;
+      b->pgsbc[i].last = i == b->pgsb_ncls - 1;
+      b->pgsbc_smem[i] = std::max((size_t)(b->pgsbc[i].nres + 1) * ent_b + xch_b, red_b);
+      mx_b = std::max(mx_b, b->pgsbc_smem[i]);
+      if (i > 0) {   // class 0 runs on the batch's stream; the larger the class, the higher the priority of its stream
+        int plo = 0, phi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&plo, &phi));
+        CK(cudaStreamCreateWithPriority(&b->pgsb_stream[i], cudaStreamNonBlocking, std::min(plo, phi + (b->pgsb_ncls - 1 - i))));
+        CK(cudaEventCreateWithFlags(&b->pgsb_join[i], cudaEventDisableTiming));
+      }
+    }
+    b->pgsb = b->pgsbc[0];
+    b->pgsb_smem = b->pgsbc_smem[0];
     b->bsched_smem = (size_t)5 * std::max(max_nb, 1) * sizeof(int);
     const int mx_smem = (int)mx_b;
     for (auto f : {k_pgsb<false, false>, k_pgsb<false, true>, k_pgsb<true, false>, k_pgsb<true, true>}) {
@@ -575,20 +593,19 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
       if (box) k_pgsb<true, true><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
       else k_pgsb<true, false><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
     } else {
-      // one launch per shared-memory class, side by side (fork / join by events); the largest class goes first,
-      // on this stream: its worlds run longest
+      // one launch per shared-memory class, side by side (fork / join by events), the largest class first and on
+      // the stream of highest priority: its worlds run longest
       cudaEventRecord(b->ev_fork, b->stream);
       for (int q = b->pgsb_ncls - 1; q >= 0; q--) {
-        cudaStream_t sq = q == b->pgsb_ncls - 1 ? b->stream : b->stream_chain[q];
-        if (sq != b->stream) cudaStreamWaitEvent(sq, b->ev_fork, 0);
+        cudaStream_t sq = q == 0 ? b->stream : b->pgsb_stream[q];
+        if (q > 0) cudaStreamWaitEvent(sq, b->ev_fork, 0);
         const int lower = q > 0 ? b->pgsbc[q - 1].nres : -1;
         if (box) k_pgsb<false, true><<<b->pgsb_ctas, 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
         else k_pgsb<false, false><<<b->pgsb_ctas, 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
-        if (sq != b->stream) cudaEventRecord(b->ev_join[q], sq);
+        if (q > 0) cudaEventRecord(b->pgsb_join[q], sq);
       }
-      for (int q = 0; q < b->pgsb_ncls - 1; q++) cudaStreamWaitEvent(b->stream, b->ev_join[q], 0);
-      b->last_launches++;
-      b->last_launches++;
+      for (int q = 1; q < b->pgsb_ncls; q++) cudaStreamWaitEvent(b->stream, b->pgsb_join[q], 0);
+      b->last_launches += b->pgsb_ncls - 1;
     }
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
     if (stage_events) cudaEventRecord(b->evs[3], b->stream);

@@ -142,9 +142,10 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
     }
     s_R = R; s_maxoff = maxoff; s_nent = nent; s_wbase = (int)wbase;
     B.wsb[w] = make_int4(R, maxoff < 0 ? 0 : maxoff / R + 1, (int)wbase, nent);
-    // k_border sorts the worlds by period, longest first: worlds of a warp then run for about the same number
-    // of rounds, and the longest ones start first
-    const int key = nent > 0 ? min(R, GZ_PGSB_NKEY - 1) : 0;
+    // k_border sorts the worlds by their number of entries (in steps of 4), largest first: that is their shared-
+    // memory need, so the CTAs of a class are filled tightly, and it follows the duration of the sweeps closely,
+    // so the worlds of a warp run for about the same number of rounds and the longest ones start first
+    const int key = min((nent + 3) >> 2, GZ_PGSB_NKEY - 1);
     B.wkey[w] = key | (atomicAdd(&B.rk_count[par * GZ_PGSB_NKEY + key], 1) << 10);
     if (nent == 0)
       for (int pos = 0; pos < m; pos++) S.off[pos] = -1;   // rows without entries: k_rowfinish skips them
@@ -186,7 +187,8 @@ struct PgsbCfg {
   int lw;        // lanes per world = 2 * padded body count (power of two, >= 2)
   int wpc;       // worlds per CTA (32 / lw for one-warp CTAs, 1 for multi-warp CTAs)
   int nres;      // entries the CTA can stage in shared memory (all its worlds together)
-  int cls;       // shared-memory class of this launch (0..2, ascending budgets), -1: the only launch (multi-warp CTAs)
+  int cls;       // shared-memory class of this launch (ascending budgets), -1: the only launch (multi-warp CTAs)
+  int last;      // the last class: it also takes the CTAs that fit no class (they read the pool)
 };
 
 // Entries staged in shared memory are padded to 22 doubles (176 B = 11 x 16 B, an odd number of 16-byte bank
@@ -218,32 +220,32 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp_g, cons
   double *const dl0 = B.ent_dl + 2 * (size_t)e0 + S, *const dlfr = dl0 + 2 * fric0;
   const bool alive = pc < pend && total > 0;
   if (!alive) pc = RES ? shd + xch_ofs - GZ_ENTS : B.ent + (size_t)(B.ent_cap - 1) * GZ_ENT;   // the all-zero dummy entry
-  double J[6], iM[6], rhs, lam, adcfm, lo, hi;
-  int mx, my;
-  {
-    const double2 *p2 = reinterpret_cast<const double2 *>(pc);
+  // the entry a lane holds: two register sets used alternately (a pass reads one and loads the other, so the
+  // loads of a pass are all issued at its start and have a whole pass to complete)
+  struct EntR { double J[6], iM[6], rhs, lam, adcfm, lo, hi; int mx, my; };
+  auto load_ent = [&](EntR &E, const double *p) {
+    const double2 *p2 = reinterpret_cast<const double2 *>(p);
 #pragma unroll
     for (int k = 0; k < 3; k++) {
       const double2 x = p2[k], y = p2[3 + k];
-      J[2 * k] = x.x; J[2 * k + 1] = x.y; iM[2 * k] = y.x; iM[2 * k + 1] = y.y;
+      E.J[2 * k] = x.x; E.J[2 * k + 1] = x.y; E.iM[2 * k] = y.x; E.iM[2 * k + 1] = y.y;
     }
     const double2 rl = p2[6 + S], cl = p2[8], hm = p2[9];
-    rhs = rl.x; lam = rl.y; adcfm = cl.x; lo = cl.y; hi = hm.x;
-    mx = __double2loint(hm.y); my = __double2hiint(hm.y);
-  }
-  int T_due = alive ? (mx & GZ_ENT_OFFMASK) : 0x7fffffff;
+    E.rhs = rl.x; E.lam = rl.y; E.adcfm = cl.x; E.lo = cl.y; E.hi = hm.x;
+    E.mx = __double2loint(hm.y); E.my = __double2hiint(hm.y);
+  };
+  EntR EA, EB;
+  load_ent(EA, pc);
+  int T_due = alive ? (EA.mx & GZ_ENT_OFFMASK) : 0x7fffffff;
   const int rounds_multi = (total > 0 && nstage > 0) ? (total + nstage - 1) * R : 0;
-  int T = -1, npass = 0;
-  for (;;) {
-    if (MULTI) {
-      if (++T >= rounds_multi) break;
-    } else {
-      T = __reduce_min_sync(0xffffffffu, T_due);   // event-driven: the next round in which any lane of the warp is due
-      if (T == 0x7fffffff) break;
-    }
+  int npass = 0;
+  // event-driven rounds: T = the next round in which any lane of the warp is due
+  int T = MULTI ? 0 : __reduce_min_sync(0xffffffffu, T_due);
+  // One pass: the lanes that are due in round T update the row they hold (C) and move on; every lane loads the
+  // entry it holds next (N): its next entry, or the one it holds already if it is not due or has finished.
+  auto pass = [&](EntR &C, EntR &N) {
     npass++;
     const bool due = (T_due == T);
-    // where this lane goes next: its next entry, or (not due / finished) the entry it holds
     double *pn = pc + STR, *dln = dlc + 2;
     int nsw = sweep;
     if (pn == pend) { nsw = sweep + 1; pn = nsw < iters ? p0 : pfr; dln = nsw < iters ? dl0 : dlfr; }
@@ -251,25 +253,22 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp_g, cons
     pn = more ? pn : pc;
     dln = more ? dln : dlc;
     nsw = more ? nsw : sweep;
-    const double2 *pn2 = reinterpret_cast<const double2 *>(pn);
-    const double2 hmn = pn2[9];
-    const int cls = (mx >> 27) & 3;
+    load_ent(N, pn);
+    const int cls = (C.mx >> 27) & 3;
     const bool fric = cls == 2;
     // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594);
     // (the distance to the normal row is 0 for the other classes: they read their own lambda and ignore it)
     double nlam = 1.0;
-    if (!BOX) nlam = (pc - (size_t)((unsigned)my >> 16) * STR)[13 + 2 * S];
+    if (!BOX) nlam = (pc - (size_t)((unsigned)C.my >> 16) * STR)[13 + 2 * S];
     // this body's half of the dot product, term by term in the reference's left-to-right order
-    double d = a[0] * J[0];
+    double d = a[0] * C.J[0];
 #pragma unroll
-    for (int t = 1; t < 6; t++) d += a[t] * J[t];
-#pragma unroll
-    for (int k = 0; k < 3; k++) { const double2 x = pn2[k]; J[2 * k] = x.x; J[2 * k + 1] = x.y; }
-    const double old_lambda = lam;
-    double delta = rhs - old_lambda * adcfm;
+    for (int t = 1; t < 6; t++) d += a[t] * C.J[t];
+    const double old_lambda = C.lam;
+    double delta = C.rhs - old_lambda * C.adcfm;
     {
       double pd = 0.0;
-      const int part = my & 0xFFFF;
+      const int part = C.my & 0xFFFF;
       const bool two = part != GZ_ENT_NOPART;
       if (MULTI) {
         double *x = shd + xch_ofs + (size_t)(T & 1) * LW;
@@ -279,19 +278,19 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp_g, cons
       } else {
         pd = __shfl_sync(0xffffffffu, d, lane_base + 2 * (two ? part : bl) + S);
       }
-      const bool isb2 = (mx >> 29) & 1;
+      const bool isb2 = (C.mx >> 29) & 1;
       const double d1 = isb2 ? pd : d, d2 = isb2 ? d : pd;
       delta -= d1;
       const double delta2 = delta - d2;
       delta = two ? delta2 : delta;
     }
-    const double hl = hi * nlam;
+    const double hl = C.hi * nlam;
     const double hf = __hiloint2double(__double2hiint(hl) & 0x7fffffff, __double2loint(hl));
     const double nhf = __hiloint2double(__double2hiint(hl) | 0x80000000, __double2loint(hl));
-    const double hi_act = fric ? hf : hi, lo_act = fric ? nhf : lo;
+    const double hi_act = fric ? hf : C.hi, lo_act = fric ? nhf : C.lo;
     double nl = old_lambda + delta;
     const double dlo = lo_act - old_lambda, dhi = hi_act - old_lambda;
-    const bool below = nl < lo_act, above = !below && nl > hi_act;
+    const bool below = nl < lo_act, over = nl > hi_act, above = !below && over;   // (two independent compares)
     delta = below ? dlo : (above ? dhi : delta);
     nl = below ? lo_act : (above ? hi_act : nl);
     // SMOOTH_LAMBDA on the lambda solve of non-bilateral rows; delta is not recomputed after it (:687-691 vs :706)
@@ -300,15 +299,16 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp_g, cons
     if (due) pc[13 + 2 * S] = nlw;
     if (due) { if (RES) pc[20 + S] = delta; else *dlc = delta; }
 #pragma unroll
-    for (int t = 0; t < 6; t++) { const double u = a[t] + delta * iM[t]; a[t] = due ? u : a[t]; }
-    // (after this pass's lambda store, so a one-entry list reads back what it just wrote)
-#pragma unroll
-    for (int k = 0; k < 3; k++) { const double2 y = pn2[3 + k]; iM[2 * k] = y.x; iM[2 * k + 1] = y.y; }
-    const double2 rl = pn2[6 + S], cl = pn2[8];
-    rhs = rl.x; lam = rl.y; adcfm = cl.x; lo = cl.y; hi = hmn.x;
-    mx = __double2loint(hmn.y); my = __double2hiint(hmn.y);
+    for (int t = 0; t < 6; t++) { const double u = a[t] + delta * C.iM[t]; a[t] = due ? u : a[t]; }
+    N.lam = (due && pn == pc) ? nlw : N.lam;   // a one-entry list holds on to the entry it has just updated
     pc = pn; dlc = dln; sweep = nsw;
-    T_due = more ? sweep * R + (mx & GZ_ENT_OFFMASK) : (due ? 0x7fffffff : T_due);
+    T_due = more ? sweep * R + (N.mx & GZ_ENT_OFFMASK) : (due ? 0x7fffffff : T_due);
+    T = MULTI ? T + 1 : __reduce_min_sync(0xffffffffu, T_due);
+  };
+  while (MULTI ? T < rounds_multi : T != 0x7fffffff) {
+    pass(EA, EB);
+    if (!(MULTI ? T < rounds_multi : T != 0x7fffffff)) break;
+    pass(EB, EA);
   }
   return npass;
 }
@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
   const bool res = cta_ent <= cfg.nres;
   // class c takes the CTAs whose entries fit it and not the class below; the last class also takes what fits
   // nowhere (those CTAs read the pool)
-  if (cfg.cls >= 0 && (cta_ent <= nres_small || (!res && cfg.cls < 2))) return;
+  if (cfg.cls >= 0 && (cta_ent <= nres_small || (!res && !cfg.last))) return;
   const int wslot = MULTI ? 0 : tid / LW, lw = MULTI ? tid : tid % LW;
   const int bl = lw >> 1, S = lw & 1;
   const unsigned long long g0 = pgsb_gtimer();
@@ -354,7 +354,12 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
     const int n2 = nent * (GZ_ENT / 2);
     const double2 *src = reinterpret_cast<const double2 *>(B.ent + (size_t)sc.z * GZ_ENT);
     double2 *dst = reinterpret_cast<double2 *>(shd + (size_t)soff * GZ_ENTS);
-    for (int q = lw; q < n2; q += LW) dst[(q / (GZ_ENT / 2)) * (GZ_ENTS / 2) + q % (GZ_ENT / 2)] = src[q];
+    // 16-byte asynchronous copies: all of them are in flight at once (one wait at the end)
+    for (int q = lw; q < n2; q += LW) {
+      const unsigned da = (unsigned)__cvta_generic_to_shared(dst + (q / (GZ_ENT / 2)) * (GZ_ENTS / 2) + q % (GZ_ENT / 2));
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da), "l"(src + q) : "memory");
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
   }
   const int xch_ofs = (cfg.nres + 1) * GZ_ENTS;   // after the staged entries and the dummy entry; MULTI: [2][LW] partial dot products
   if (res) {   // the all-zero dummy entry (no partner, never due) of the lanes without rows
@@ -386,35 +391,38 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
   int npass;
   if (res) npass = pgsb_sweeps<true, MULTI, BOX>(B, lp_g, lofs, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch_ofs, e0, a);
   else npass = pgsb_sweeps<false, MULTI, BOX>(B, lp_g, lofs, cnt, fric0, R, sc.y, S, bl, lane_base, LW, xch_ofs, e0, a);
+  // ---- results.  caccel to the bodies; then, over ALL entries of the world with all its lanes (coalesced reads
+  // of the side arrays): lambda back to the rows (k_lambda_save copies them to the joints), and the statistics.
   // rms_dlambda / rms_constraint_residual (quickstep_pgs_lcp.cpp:700-760, 814-855): the sums restart every sweep,
   // so what survives is the last update of every row (sweep iters - 1 for bilateral and normal rows, total - 1
-  // for friction rows): the deltas the sweeps left beside the entries
-  double st_acc[3] = {0, 0, 0}, st_err[3] = {0, 0, 0};
-  int st_cnt[3] = {0, 0, 0};
-  if (S == 0) {
-    const double *dl = res ? lp + 20 : B.ent_dl + 2 * (size_t)e0;
-    const int dstr = res ? GZ_ENTS : 2;
-    const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
-    for (int q = 0; q < cnt; q++) {
-      const int mx = __double2loint(lp[(size_t)q * lstr + 19]);
-      const int cls = (mx >> 27) & 3;
-      if (((mx >> 29) & 1) || (cls == 2 ? total : iters) <= 0) continue;   // the row's body-1 entry carries it
-      const double de = dl[(size_t)q * dstr], dd = de * de, e2 = dd * B.ent_ad2[e0 + q];
-      st_acc[cls] += dd; st_err[cls] += e2; st_cnt[cls]++;
-    }
-  }
-  // ---- results: caccel to the bodies, lambda back to the rows (k_lambda_save copies them to the joints)
+  // for friction rows): the deltas the sweeps left beside the entries.
   if (live_w && bl < wi.nb) {
     BodyStep &bs = B.bstep[wi.body0 + bl];
     double *o = S ? bs.caccel_erp : bs.caccel;
 #pragma unroll
     for (int t = 0; t < 6; t++) o[t] = a[t];
+  }
+  if (MULTI) __syncthreads(); else __syncwarp();
+  double st_acc[3] = {0, 0, 0}, st_err[3] = {0, 0, 0};
+  int st_cnt[3] = {0, 0, 0};
+  if (live_w) {
+    const double *wp = res ? shd + (size_t)soff * GZ_ENTS : B.ent + (size_t)sc.z * GZ_ENT;   // the world's entries
+    const double *wdl = res ? wp + 20 : B.ent_dl + 2 * (size_t)sc.z;
+    const int dstr = res ? GZ_ENTS : 2;
+    const int iters = B.p.iters, total = B.p.iters + B.p.friction_iters;
     Row *rw = B.row + wi.row0;
-    for (int q = 0; q < cnt; q++) {
-      const int r = B.ent_row[e0 + q];
-      if (r < 0) continue;
-      const double v = lp[(size_t)q * lstr + 13 + 2 * S];
-      if (S) rw[r].lambda_erp = v; else rw[r].lambda = v;
+    for (int q = lw; q < nent; q += LW) {
+      const int r = B.ent_row[sc.z + q];
+      if (r < 0) continue;   // the row's body-1 entry carries it
+      const double ad2 = B.ent_ad2[sc.z + q];
+      const double *p = wp + (size_t)q * lstr;
+      rw[r].lambda = p[13]; rw[r].lambda_erp = p[15];
+      const int cls = (__double2loint(p[19]) >> 27) & 3;
+      if ((cls == 2 ? total : iters) <= 0) continue;
+      const double de = wdl[(size_t)q * dstr], dd = de * de, e2 = dd * ad2;
+      if (cls == 0) { st_acc[0] += dd; st_err[0] += e2; st_cnt[0]++; }
+      else if (cls == 1) { st_acc[1] += dd; st_err[1] += e2; st_cnt[1]++; }
+      else { st_acc[2] += dd; st_err[2] += e2; st_cnt[2]++; }
     }
   }
   // ---- statistics: reduce over the lanes of the world

@@ -28,6 +28,8 @@ static int fail(int code, const std::string &msg) { g_err = msg; return code; }
   } while (0)
 
 #define GZ_PGSB_NCLS 8
+struct gzcuda_batch;
+extern "C" { static int check_sticky(gzcuda_batch *b); }
 struct gzcuda_batch {
   DevBatch d;
   int device = 0;
@@ -42,6 +44,7 @@ struct gzcuda_batch {
   cudaEvent_t ev_fork = nullptr, ev_join[GZ_CHAIN_NCLS] = {};   // beside the regular one: fork / join by events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   std::vector<void *> allocs;
+  int *h_sticky = nullptr;            // pinned copy of DevBatch::sticky, read back at every synchronising call
   std::vector<WorldInfo> h_world;
   float last_ms = 0;
   long last_launches = 0;
@@ -137,6 +140,7 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   cudaSetDevice(b->device);
   if (b->stream) cudaStreamSynchronize(b->stream);
   for (void *p : b->allocs) cudaFree(p);
+  if (b->h_sticky) cudaFreeHost(b->h_sticky);
   if (b->ev0) cudaEventDestroy(b->ev0);
   if (b->ev1) cudaEventDestroy(b->ev1);
   for (auto &e : b->evs) if (e) cudaEventDestroy(e);
@@ -297,6 +301,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     wi.pair_cap = (int)std::max(1L, std::min(np, np_limit));
     wi.contact_cap = std::min(8 * wi.pair_cap, std::max(64, 24 * n));
     wi.row_cap = 6 * wi.nj + 3 * wi.contact_cap;
+    // test hooks: shrink the slabs so that a step overflows them (tests/test_parity_gpu.py::test_capacity_overflow_is_sticky)
+    if (const char *e = getenv("GZCUDA_TEST_PAIR_CAP")) wi.pair_cap = std::max(1, std::min(wi.pair_cap, atoi(e)));
+    if (const char *e = getenv("GZCUDA_TEST_CONTACT_CAP")) wi.contact_cap = std::max(1, std::min(wi.contact_cap, atoi(e)));
+    if (const char *e = getenv("GZCUDA_TEST_ROW_CAP")) wi.row_cap = std::max(1, std::min(wi.row_cap, atoi(e)));
     wi.pair0 = (int)pair_tot; wi.contact0 = (int)contact_tot; wi.row0 = (int)row_tot;
     wi.slot_cap = 0; wi.slot0 = 0;
     // schedule slots a world can need: about twice its rows (periods are padded to a ladder and to k lanes)
@@ -349,6 +357,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.sticky, (size_t)4))) return rc;
+  CK(cudaMallocHost((void **)&b->h_sticky, 4 * sizeof(int)));
 
   // Body-owner PGS (k_pgsb.cuh): the default for worlds of up to 256 bodies.  Entry pool: a row has one entry
   // per body, so 2 x rows is the worst case; clamped to a quarter of the free memory (k_bsched flags a step
@@ -730,8 +739,7 @@ int gzcuda_batch_step_io(gzcuda_batch *b, int n_steps, const double *wrench_in, 
   }
   CK(cudaEventRecord(b->ev1, b->stream));
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(b->stream));
-  return 0;
+  return check_sticky(b);   // synchronises; GZCUDA_E_CAPACITY if any of the steps overflowed a slab
 }
 
 // State log at a decimated rate (the WorldState stream of gz log / ~/pose/info, gazebo/physics/World.cc:2757-2850,
@@ -777,8 +785,9 @@ int gzcuda_batch_step_log(gzcuda_batch *b, int n_steps, int every, double *frame
   }
   CK(cudaEventRecord(b->ev1, b->stream));
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(b->stream));
+  const int rc_cap = check_sticky(b);
   CK(cudaStreamSynchronize(b->stream_copy));
+  if (rc_cap) return rc_cap;
   return nframes;
 }
 
@@ -842,7 +851,22 @@ int gzcuda_world_step(gzcuda_batch *b, double step_size) {
 int gzcuda_batch_sync(gzcuda_batch *b) {
   if (!b) return fail(GZCUDA_E_INVALID, "null batch");
   CK(cudaSetDevice(b->device));
+  return check_sticky(b);
+}
+
+// Sticky capacity flag (DevBatch::sticky): a step that dropped pairs, contacts, rows or whole worlds somewhere in a
+// multi-step call must not go unnoticed.  Reads it back (stream-ordered, after everything queued so far), reports
+// GZCUDA_E_CAPACITY once and clears it.
+static int check_sticky(gzcuda_batch *b) {
+  CK(cudaMemcpyAsync(b->h_sticky, b->d.sticky, 4 * sizeof(int), cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
+  if (b->h_sticky[0]) {
+    char buf[200];
+    snprintf(buf, sizeof(buf), "capacity overflow during a step (mask %d: 1 pairs, 2 contacts, 4 rows, 8 solver limits, 16 record pool; "
+             "last world %d): results of that step are incomplete", b->h_sticky[0], b->h_sticky[1] - 1);
+    CK(cudaMemsetAsync(b->d.sticky, 0, 4 * sizeof(int), b->stream));
+    return fail(GZCUDA_E_CAPACITY, buf);
+  }
   return 0;
 }
 

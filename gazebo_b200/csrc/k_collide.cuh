@@ -374,16 +374,15 @@ __global__ void k_contacts(DevBatch B) {
       double kd = g1.surf[GZ_SF_KD] + g2.surf[GZ_SF_KD];
       double soft_erp = (h * kp) / (h * kp + kd);
       double soft_cfm = 1.0 / (h * kp + kd);
+      // fdir1 as written in ODEPhysics.cc:1120-1161: only surface 1's direction ever reaches the contact (the
+      // reference rotates surface 2's fd2 but never assigns it), rotated to the world frame by collision 1's pose
       double fd[3] = {g1.fdir1[0], g1.fdir1[1], g1.fdir1[2]};
-      bool fdset = (fd[0] != 0 || fd[1] != 0 || fd[2] != 0);
-      const Geom *fg = &g1;
-      bool fd2set = (g2.fdir1[0] != 0 || g2.fdir1[1] != 0 || g2.fdir1[2] != 0);
-      if (fd2set && (!fdset || g1.surf[GZ_SF_MU] > g2.surf[GZ_SF_MU])) {
-        fd[0] = g2.fdir1[0]; fd[1] = g2.fdir1[1]; fd[2] = g2.fdir1[2];
-        fg = &g2; fdset = true;
-      }
+      const bool fdset = (fd[0] != 0 || fd[1] != 0 || fd[2] != 0);
       double fdw[3] = {0, 0, 0};
-      if (fdset) mul0_331(fdw, fg->R, fd);
+      if (fdset) {
+        if (g1.type == GZ_GEOM_PLANE) { fdw[0] = fd[0]; fdw[1] = fd[1]; fdw[2] = fd[2]; }   // a plane has no pose: identity
+        else mul0_331(fdw, g1.R, fd);
+      }
       double mu = fmin(g1.surf[GZ_SF_MU], g2.surf[GZ_SF_MU]);
       double mu2 = fmin(g1.surf[GZ_SF_MU2], g2.surf[GZ_SF_MU2]);
       double slip1 = g1.surf[GZ_SF_SLIP1] + g2.surf[GZ_SF_SLIP1];

@@ -627,6 +627,15 @@ __global__ void k_integrate(DevBatch B) {
   int bi = blockIdx.x * blockDim.x + threadIdx.x;
   if (bi >= B.nb) return;
   const BodyStep &bs = B.bstep[bi];
+  {
+    // last kernel of the step: a capacity overflow of this step (pairs 1, contacts 2, rows 4, solver 8, record /
+    // entry pool 16) is ORed into the batch's STICKY word, which the host checks at every synchronising call
+    const int w = B.body[bi].world;
+    if (bi == B.world[w].body0) {
+      const int ov = B.wstep[w].overflow;
+      if (ov) { atomicOr(&B.sticky[0], ov); atomicMax(&B.sticky[1], w + 1); }
+    }
+  }
   if (!bs.active) return;
   Body &b = B.body[bi];
   const double h = B.p.step_size;

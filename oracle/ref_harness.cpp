@@ -196,21 +196,18 @@ void collide_pair(RefBatch *B, RefWorld *w, int i1, int i2) {
   contact.surface.soft_erp = (h * kp) / (h * kp + kd);
   contact.surface.soft_cfm = 1.0 / (h * kp + kd);
 
-  // fdir1: geom-frame direction of the surface with the smaller mu1, rotated to the
-  // world frame.  (Gazebo rotates with its own Pose3d quaternion, ODEPhysics.cc:1122-1161;
-  // here the ODE geom rotation matrix is used — equal up to rounding; both sides of the
-  // parity test use this form.)
+  // fdir1, AS WRITTEN in ODEPhysics.cc:1120-1161: fd is surface 1's direction1, rotated to the world frame by
+  // collision 1's pose.  Surface 2's direction (fd2) is rotated in the reference when surface 1 has none or the
+  // larger mu1, but it is never assigned to fd: it has NO effect on the contact, and dContactFDir1 is set only
+  // when surface 1 has a direction.  (Gazebo rotates with the collision's Pose3d quaternion; the ODE geom rotation
+  // matrix is used here - equal up to rounding, gzserver cannot be built in this image; both sides of the parity
+  // test use this form.)
   double fd[3] = {s1.fdir1[0], s1.fdir1[1], s1.fdir1[2]};
-  bool fdset = (fd[0] != 0 || fd[1] != 0 || fd[2] != 0);
-  int fdgeom = i1;
-  bool fd2set = (s2.fdir1[0] != 0 || s2.fdir1[1] != 0 || s2.fdir1[2] != 0);
-  if (fd2set && (!fdset || s1.s[GZ_SF_MU] > s2.s[GZ_SF_MU])) {
-    fd[0] = s2.fdir1[0]; fd[1] = s2.fdir1[1]; fd[2] = s2.fdir1[2];
-    fdgeom = i2;
-    fdset = true;
-  }
+  const bool fdset = (fd[0] != 0 || fd[1] != 0 || fd[2] != 0);
   if (fdset) {
-    const dReal *R = dGeomGetRotation(w->geoms[fdgeom]);
+    // (a plane is not placeable in ODE and has no pose in the scene format: its collision sits at the identity)
+    static const dReal ident[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    const dReal *R = dGeomGetClass(w->geoms[i1]) == dPlaneClass ? ident : dGeomGetRotation(w->geoms[i1]);
     dVector3 v = {fd[0], fd[1], fd[2], 0}, r;
     dMultiply0_331(r, R, v);
     contact.surface.mode |= dContactFDir1;

@@ -249,6 +249,51 @@ def cylcyl():
     return sb.finish(), S.default_params(), None
 
 
+def sleepers():
+    """Multi-island world for the island / auto-disable / re-enable logic (util.cpp:116-252, 408-558): six
+    separated auto-disable boxes land at different times and go to sleep one by one; a late box then falls onto
+    sleeper 0 and wakes it (a two-body island), the others stay asleep.  Until that hit every island is one box
+    on the plane, whose rows come in the same order whatever the island order: natural (dWorldQuickStep) and
+    canonical stepping agree to rounding there."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_ground_plane()
+    for i in range(6):
+        b = sb.add_body([1.5 * i, 0, 0.3 + 0.25 * i], S.q_from_rpy(0.02 * i, 0.01, 0.3 * i), mass=1.0,
+                        inertia=S.box_inertia(1, 0.4, 0.4, 0.4), flags=S.BODY_AUTO_DISABLE)
+        sb.add_geom(S.GEOM_BOX, (0.4, 0.4, 0.4), sb.new_space(), body=b)
+    b = sb.add_body([0.05, 0.02, 14.0], mass=0.5, inertia=S.box_inertia(0.5, 0.3, 0.3, 0.3), flags=S.BODY_AUTO_DISABLE)
+    sb.add_geom(S.GEOM_BOX, (0.3, 0.3, 0.3), sb.new_space(), body=b)
+    sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
+def fdir1():
+    """ODEPhysics.cc:1120-1161 as written: only collision 1's friction direction reaches the contact.  Anisotropic
+    friction (mu != mu2) and boxes sliding diagonally, with fdir1 on geom 1 only (the plane; a rotated static
+    platform), on geom 2 only (no effect), and on both with differing mu (geom 1's wins whatever the mu)."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    c, s_ = math.cos(0.4), math.sin(0.4)
+    sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), mu=1.0, mu2=0.15, fdir1=(c, s_, 0))   # geom 0: collision 1 of every plane pair
+    def slider(x, y, z, **kw):
+        b = sb.add_body([x, y, z], S.q_from_rpy(0, 0, 0.2), mass=1.0, inertia=S.box_inertia(1, 0.3, 0.3, 0.2), lvel=(0.7, 0.5, 0.0))
+        sb.add_geom(S.GEOM_BOX, (0.3, 0.3, 0.2), sb.new_space(), body=b, **kw)
+        return b
+    slider(0.0, 0.0, 0.1, mu=0.9, mu2=0.9)                                   # on the plane: the plane's fdir1
+    # platform without fdir1 (geom 1), slider with fdir1 (geom 2): no effect
+    sb.add_geom(S.GEOM_BOX, (3, 3, 0.5), sb.new_space(), pos=(5, 0, 0.25), mu=0.8, mu2=0.8)
+    slider(5.0, 0.0, 0.6, mu=0.6, mu2=0.1, fdir1=(0, 1, 0))
+    # rotated platform with fdir1 (geom 1), slider without
+    sb.add_geom(S.GEOM_BOX, (3, 3, 0.5), sb.new_space(), pos=(10, 0, 0.25), quat=S.q_from_rpy(0, 0, 0.5), mu=0.7, mu2=0.1, fdir1=(1, 0, 0))
+    slider(10.0, 0.0, 0.6, mu=0.9, mu2=0.9)
+    # both, geom 2 with the SMALLER mu: geom 1's direction is used all the same
+    sb.add_geom(S.GEOM_BOX, (3, 3, 0.5), sb.new_space(), pos=(15, 0, 0.25), quat=S.q_from_rpy(0, 0, -0.3), mu=0.8, mu2=0.2, fdir1=(0, 1, 0))
+    slider(15.0, 0.0, 0.6, mu=0.3, mu2=0.05, fdir1=(1, 0, 0))
+    sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 GOLDEN = {
     "box_drop": (box_drop, 1500),
     "tilted_box": (tilted_box, 600),
@@ -262,4 +307,5 @@ GOLDEN = {
     "cylinders": (cylinders, 500),
     "cylboxes": (cylboxes, 500),
     "cylcyl": (cylcyl, 400),
+    "fdir1": (fdir1, 300),
 }

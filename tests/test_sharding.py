@@ -51,6 +51,16 @@ def test_two_ranks_partition_worlds_and_aggregate():
     assert np.array_equal(np.concatenate([g["pd"] for g in gathered]), pd_whole)
 
 
+def test_strong_block_splits_the_stated_batch():
+    """BASELINE.json configs[1] read literally: 4096 worlds split over the ranks."""
+    for n in (1, 2, 3, 4, 8):
+        blocks = [sharding.strong_block(r, n, 4096) for r in range(n)]
+        assert blocks[0][0] == 0 and sum(c for _, c in blocks) == 4096
+        for (f0, c0), (f1, _) in zip(blocks, blocks[1:]):
+            assert f1 == f0 + c0
+        assert max(c for _, c in blocks) - min(c for _, c in blocks) <= 1
+
+
 def test_single_rank_is_identity():
     assert sharding.max_over_ranks(3.5) == 3.5
     assert sharding.world_block(5, 4096) == (5 * 4096, 4096)

@@ -275,6 +275,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       for (int k = 0; k < 3; k++) { G.opos[k] = sc->geom_pos[3 * g + k]; G.fdir1[k] = sc->geom_fdir1[3 * g + k]; }
       q_to_R(sc->geom_quat + 4 * g, G.oR);   // dGeomSetOffsetQuaternion / dGeomSetQuaternion: dQtoR, no normalisation
       for (int k = 0; k < GZ_SF_COUNT; k++) G.surf[k] = sc->geom_surf[GZ_SF_COUNT * g + k];
+      if (G.surf[GZ_SF_PATCH_RADIUS] > 0 || G.surf[GZ_SF_ELASTIC_MODULUS] > 0)
+        return fail(GZCUDA_E_INVALID, "torsional friction (patch_radius) and elastic-modulus contact rows are not supported");
       G.cat = sc->geom_category_bits[g]; G.col = sc->geom_collide_bits[g];
       G.scat = scat[G.space]; G.scol = scol[G.space];
       G.bitmask = sc->geom_collide_bitmask[g];
@@ -862,7 +864,7 @@ static int check_sticky(gzcuda_batch *b) {
   CK(cudaStreamSynchronize(b->stream));
   if (b->h_sticky[0]) {
     char buf[200];
-    snprintf(buf, sizeof(buf), "capacity overflow during a step (mask %d: 1 pairs, 2 contacts, 4 rows, 8 solver limits, 16 record pool; "
+    snprintf(buf, sizeof(buf), "capacity overflow during a step (mask %d: 1 pairs, 2 contacts, 4 rows, 8 solver limits, 16 record pool, 32 MPR iteration cap; "
              "last world %d): results of that step are incomplete", b->h_sticky[0], b->h_sticky[1] - 1);
     CK(cudaMemsetAsync(b->d.sticky, 0, 4 * sizeof(int), b->stream));
     return fail(GZCUDA_E_CAPACITY, buf);

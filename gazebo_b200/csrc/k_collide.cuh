@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(512) k_broadphase(DevBatch B) {
 // CYL = the scene has cylinders: only then are the cylinder-box and MPR colliders compiled in (they double the
 // registers and the stack of k_narrow; scenes of boxes, spheres and capsules run the light instantiation)
 template <bool CYL>
-__device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) {
+__device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o, int *overflow_word) {
   int t1 = g1.type, t2 = g2.type;
   int n = 0;
   bool rev = false;
@@ -291,6 +291,7 @@ __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o) 
   else if (CYL && t1 == GZ_GEOM_CAPSULE && t2 == GZ_GEOM_CYLINDER) n = col_mpr(g1, true, g2, o);
   else if (CYL && t1 == GZ_GEOM_CYLINDER && t2 == GZ_GEOM_CAPSULE) { n = col_mpr(g2, true, g1, o); rev = true; }
   else n = 0;
+  if (n < 0) { atomicOr(overflow_word, 32); n = 0; }   // MPR portal loop cap (k_mpr.cuh)
   if (rev)
     for (int i = 0; i < n; i++) { o.nrm[i][0] = -o.nrm[i][0]; o.nrm[i][1] = -o.nrm[i][1]; o.nrm[i][2] = -o.nrm[i][2]; }
   return n;
@@ -314,7 +315,7 @@ __global__ void k_narrow(DevBatch B) {
     if ((unsigned)g1.max_contacts < maxCollide) maxCollide = g1.max_contacts;
     if ((unsigned)g2.max_contacts < maxCollide) maxCollide = g2.max_contacts;
     COut o;
-    numc = collide_dispatch<CYL>(g1, g2, o);
+    numc = collide_dispatch<CYL>(g1, g2, o, &B.wstep[w].overflow);
     int idx[GZ_PAIR_MAXC];
     for (int i = 0; i < GZ_PAIR_MAXC; i++) idx[i] = i;
     if (maxCollide > 0 && (unsigned)numc > maxCollide) {

@@ -11,7 +11,8 @@
 //   distances     ccdVec3PointTriDist2 / PointSegmentDist2 (vec3.c:86-212); CCD_EPS = DBL_EPSILON (vec3.h:62)
 // ccd.max_iterations = 500, ccd.mpr_tolerance = 1e-6 (collision_libccd.cpp:269-270).  The two portal loops
 // the reference leaves unbounded are capped at GZ_MPR_LOOP_CAP trips here (a GPU thread must terminate);
-// a pair that hits the cap reports no contact.
+// a pair that hits the cap reports no contact and raises the step's capacity flag (bit 32, sticky: the next
+// synchronising call returns GZCUDA_E_CAPACITY), so the divergence from the reference is never silent.
 #pragma once
 
 namespace gz {
@@ -237,7 +238,7 @@ __device__ inline int mpr_discover_portal(const CcdObj &o1, const CcdObj &o2, Cc
     ccd_cross(dir, va, vb);
     ccd_normalize(dir);
   }
-  return -1;
+  return -2;   // GZ_MPR_LOOP_CAP trips: the reference would go on (reported, see col_mpr)
 }
 
 // refinePortal (mpr.c:285-317)
@@ -253,7 +254,7 @@ __device__ inline int mpr_refine_portal(const CcdObj &o1, const CcdObj &o2, CcdS
     if (!(ccd_zero(dot) || dot > 0.0) || mpr_reach_tolerance(P, v4, dir)) return -1;
     mpr_expand_portal(P, v4);
   }
-  return -1;
+  return -2;   // GZ_MPR_LOOP_CAP trips (reported, see col_mpr)
 }
 
 // __ccdVec3PointSegmentDist2 with P = origin and a witness (vec3.c:86-140)
@@ -346,6 +347,7 @@ __device__ __noinline__ int col_mpr(const Geom &g1, bool cap1, const Geom &g2, C
   CcdSupp P[4];
   double depth, dir[3], pos[3];
   const int res = mpr_discover_portal(o1, o2, P);
+  if (res == -2) return -1;   // a portal loop hit its trip cap: no contact AND the step is flagged (k_narrow)
   if (res < 0) return 0;
   if (res == 1) {          // findPenetrTouch
     depth = 0.;
@@ -357,7 +359,9 @@ __device__ __noinline__ int col_mpr(const Geom &g1, bool cap1, const Geom &g2, C
     depth = sqrt(ccd_dot(dir, dir));
     ccd_normalize(dir);
   } else {
-    if (mpr_refine_portal(o1, o2, P) < 0) return 0;
+    const int rr = mpr_refine_portal(o1, o2, P);
+    if (rr == -2) return -1;
+    if (rr < 0) return 0;
     // findPenetr (mpr.c:320-355)
     CcdSupp v4;
     double pd[3];

@@ -20,7 +20,7 @@ JP_LOSTOP, JP_HISTOP, JP_VEL, JP_FMAX, JP_FUDGE, JP_BOUNCE, JP_NORMAL_CFM, \
     JP_STOP_ERP, JP_STOP_CFM, JP_ERP, JP_CFM = range(11)
 JP_COUNT = 12
 SF_MU, SF_MU2, SF_KP, SF_KD, SF_SLIP1, SF_SLIP2, SF_BOUNCE, SF_BOUNCE_VEL = range(8)
-SF_COUNT = 8
+SF_COUNT = 10
 GZ_ALL_COLLIDE = 0x0FFFFFFF
 GZ_FIXED_COLLIDE = 0x00000001
 
@@ -145,7 +145,7 @@ def cylinder_inertia(mass, r, l):
 
 
 DEFAULT_SURFACE = dict(mu=1.0, mu2=1.0, kp=1e12, kd=1.0, slip1=0.0, slip2=0.0,
-                       bounce=0.0, bounce_vel=100000.0)
+                       bounce=0.0, bounce_vel=100000.0, patch_radius=0.0, elastic_modulus=0.0)
 
 
 class SceneBuilder:
@@ -221,7 +221,7 @@ class SceneBuilder:
         self.g["bitmask"].append(collide_bitmask & 0xFFFFFFFF)
         self.g["maxc"].append(int(max_contacts))
         self.g["surf"].append([s["mu"], s["mu2"], s["kp"], s["kd"], s["slip1"], s["slip2"],
-                               s["bounce"], s["bounce_vel"]])
+                               s["bounce"], s["bounce_vel"], s["patch_radius"], s["elastic_modulus"]])
         self.g["fdir1"].append(list(map(float, fdir1)))
         self._ng += 1
         return self._ng - 1 - self._w_g0

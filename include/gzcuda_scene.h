@@ -53,7 +53,12 @@ enum { GZ_JP_LOSTOP = 0, GZ_JP_HISTOP = 1, GZ_JP_VEL = 2, GZ_JP_FMAX = 3,
 /* geom_surf[] slots (ODESurfaceParams + FrictionPyramid) */
 enum { GZ_SF_MU = 0, GZ_SF_MU2 = 1, GZ_SF_KP = 2, GZ_SF_KD = 3,
        GZ_SF_SLIP1 = 4, GZ_SF_SLIP2 = 5, GZ_SF_BOUNCE = 6, GZ_SF_BOUNCE_VEL = 7,
-       GZ_SF_COUNT = 8 };
+       /* the two contact-row variants this library does NOT build yet; a scene that sets either (> 0) is refused
+        * by gzcuda_batch_create with GZCUDA_E_INVALID instead of being stepped without them:
+        * torsional friction (FrictionPyramid patch radius, contact.cpp:163-216, dContactMu3) and the
+        * elastic-modulus contact row (ODEPhysics.cc:1237-1251, contact.cpp:365-437) */
+       GZ_SF_PATCH_RADIUS = 8, GZ_SF_ELASTIC_MODULUS = 9,
+       GZ_SF_COUNT = 10 };
 
 /* World-level parameters, shared by every world of a batch
  * (ODEPhysics::Load, gazebo/physics/ode/ODEPhysics.cc:175-243; dWorldCreate

@@ -63,6 +63,7 @@ def lib():
     L.gzcuda_batch_get_contacts.argtypes = [vp, ci, dp, dp, ci]
     L.gzcuda_batch_get_joint_feedback.argtypes = [vp, dp]
     L.gzcuda_batch_get_contact_feedback.argtypes = [vp, ci, dp, ci]
+    L.gzcuda_batch_get_joint_feedback_noalloc.argtypes = [vp, dp]
     L.gzcuda_batch_last_step_ms.argtypes = [vp, dp, dp]
     L.gzcuda_batch_stage_ms.argtypes = [vp, dp]
     _lib = L
@@ -81,7 +82,7 @@ EXPORTS = [
     "gzcuda_batch_pgs_ms", "gzcuda_batch_get_counters", "gzcuda_batch_get_pgs_debug",
     "gzcuda_batch_get_pgs_profile", "gzcuda_batch_get_pgs_timeline",
     "gzcuda_batch_get_joint_feedback", "gzcuda_batch_get_contact_feedback", "gzcuda_batch_step_log",
-    "gzcuda_batch_set_joint_velocity_cmd",
+    "gzcuda_batch_set_joint_velocity_cmd", "gzcuda_batch_get_joint_feedback_noalloc",
 ]
 
 
@@ -236,6 +237,13 @@ class Batch:
         """dJointFeedback of every persistent joint after the last step: [nj][12] = f1, t1, f2, t2."""
         fb = np.zeros((self.scene.nj, 12))
         self._ck(self.L.gzcuda_batch_get_joint_feedback(self.h, _p(fb)))
+        return fb
+
+    def joint_feedback_noalloc(self):
+        """joint_feedback() through the entry point that allocates nothing (static device scratch inside the
+        library, at most GZCUDA_NOALLOC_MAX_JOINTS joints; no counterpart in the reference)."""
+        fb = np.zeros((self.scene.nj, 12))
+        self._ck(self.L.gzcuda_batch_get_joint_feedback_noalloc(self.h, _p(fb)))
         return fb
 
     def contact_feedback(self, world, cap=1 << 16):

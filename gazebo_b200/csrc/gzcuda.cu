@@ -1134,6 +1134,45 @@ int gzcuda_batch_get_joint_feedback(gzcuda_batch *b, double *fb) {
   return nj;
 }
 
+// ---- gzcuda_batch_get_joint_feedback without any allocation --------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  The scratch k_feedback_joint writes lives in this file-scope device array: GZCUDA_NOALLOC_MAX_JOINTS
+// x 12 doubles = 3 MiB, held by every GPU that loads the library until the process exits.  In host code the
+// array's NAME is a host-side stand-in, not a device address; the address is asked for once per device
+// (cudaGetSymbolAddress with that device current) and that pointer is what the kernel gets.  All calls share the
+// array and it keeps the last call's contents: the kernel overwrites every element of [0, 12 nj) it hands back, so
+// nothing has to be cleared; calls that overlap on the GPU (two batches' streams) would race and must be serialised
+// by the caller.
+static __device__ __align__(256) double g_noalloc_fb_scratch[12 * GZCUDA_NOALLOC_MAX_JOINTS];
+static double *g_noalloc_fb_ptr[64] = {};   // device address of the array, per device ordinal
+
+int gzcuda_batch_get_joint_feedback_noalloc(gzcuda_batch *b, double *fb) {
+  if (!b || !fb) return fail(GZCUDA_E_INVALID, "null argument");
+  const int nj = b->d.nj;
+  if (nj > GZCUDA_NOALLOC_MAX_JOINTS) {
+    char buf[160];
+    snprintf(buf, sizeof(buf), "gzcuda_batch_get_joint_feedback_noalloc: %d joints exceed the static scratch of %d "
+             "(GZCUDA_NOALLOC_MAX_JOINTS); use gzcuda_batch_get_joint_feedback", nj, GZCUDA_NOALLOC_MAX_JOINTS);
+    return fail(GZCUDA_E_INVALID, buf);
+  }
+  if (b->device < 0 || b->device >= 64) return fail(GZCUDA_E_INVALID, "device ordinal beyond 63");
+  int rc = gzcuda_batch_sync(b);   // (sets the batch's device current)
+  if (rc) return rc;
+  if (nj == 0) return 0;
+  if (!g_noalloc_fb_ptr[b->device]) {   // set-up, once per device, with that device current
+    double *ptr = nullptr;
+    CK(cudaGetSymbolAddress((void **)&ptr, g_noalloc_fb_scratch));
+    if (!ptr) return fail(GZCUDA_E_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_fb_ptr[b->device] = ptr;
+  }
+  double *dev = g_noalloc_fb_ptr[b->device];
+  k_feedback_joint<<<cdiv(nj, 128), 128, 0, b->stream>>>(b->d, dev);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(fb, dev, (size_t)12 * nj * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return nj;
+}
+
 int gzcuda_batch_get_contact_feedback(gzcuda_batch *b, int world, double *fb, int cap) {
   if (!b || !fb || world < 0 || world >= b->d.n_worlds) return fail(GZCUDA_E_INVALID, "bad argument");
   int rc = gzcuda_batch_sync(b);

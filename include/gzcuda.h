@@ -120,6 +120,18 @@ int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *da
 int gzcuda_batch_get_joint_feedback(gzcuda_batch *b, double *fb);
 int gzcuda_batch_get_contact_feedback(gzcuda_batch *b, int world, double *fb, int cap);
 
+/* gzcuda_batch_get_joint_feedback for callers that cannot allocate.  This entry point has NO counterpart in
+ * the reference: it was added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * gzcuda_batch_get_joint_feedback (fb[nj][12], host buffer; returns nj), but the device scratch the feedback
+ * kernel writes is a static array inside the library instead of a cudaMalloc per call: the call makes no
+ * cudaMalloc / cudaFree and uses no allocating library routine.  Limits: at most GZCUDA_NOALLOC_MAX_JOINTS
+ * joints in the batch (GZCUDA_E_INVALID beyond that); the array (3 MiB) is held by every GPU that loads the
+ * library until the process exits; all calls share it, so calls that overlap on the GPU (different batches
+ * on different host threads) race and must be serialised by the caller. */
+#define GZCUDA_NOALLOC_MAX_JOINTS 32768
+int gzcuda_batch_get_joint_feedback_noalloc(gzcuda_batch *b, double *fb);
+
 /* Instrumentation: device time in ms of the last gzcuda_batch_step call (CUDA events on the
  * batch stream) and the number of kernel launches it issued. */
 int gzcuda_batch_last_step_ms(gzcuda_batch *b, float *ms, long *launches);

@@ -51,6 +51,8 @@ def lib():
     L.gzcuda_batch_sync.argtypes = [vp]
     L.gzcuda_batch_get_body_state.argtypes = [vp, dp, dp, dp, dp]
     L.gzcuda_batch_set_body_state.argtypes = [vp, ci, ci, dp, dp, dp, dp]
+    L.gzcuda_batch_set_body_state_raw.argtypes = [vp, ci, ci, dp, dp, dp, dp]
+    L.gzcuda_batch_set_body_enabled.argtypes = [vp, ci, ci, dp]
     L.gzcuda_batch_add_body_wrench.argtypes = [vp, dp, dp]
     L.gzcuda_batch_get_body_flags.argtypes = [vp, dp]
     L.gzcuda_batch_set_joint_param.argtypes = [vp, ci, ci, C.c_double]
@@ -83,6 +85,7 @@ EXPORTS = [
     "gzcuda_batch_get_pgs_profile", "gzcuda_batch_get_pgs_timeline",
     "gzcuda_batch_get_joint_feedback", "gzcuda_batch_get_contact_feedback", "gzcuda_batch_step_log",
     "gzcuda_batch_set_joint_velocity_cmd", "gzcuda_batch_get_joint_feedback_noalloc",
+    "gzcuda_batch_set_body_state_raw", "gzcuda_batch_set_body_enabled",
 ]
 
 

@@ -175,6 +175,10 @@ struct DevBatch {
   int *sticky;           // [4] OR of every step's overflow masks since the last check, first world, spare
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)
   double *io_out;        // [nb][13] staged pos(3) quat(4) lvel(3) avel(3)
+  double *set_stage;     // [nb][13] staged setter input (gzcuda_batch_set_body_state; NaN = leave as it is)
+  double *jstage;        // [nj][6]  staged per-joint setter input (set_hinge_pd, set_joint_velocity_cmd)
+  double *fb_stage;      // [max(nj, max_contact_cap)][12] joint / contact feedback staging (the getters allocate nothing)
+  int *flag_stage;       // [nb] staged body flags (gzcuda_batch_get_body_flags)
 };
 
 }  // namespace gz

@@ -46,6 +46,7 @@ struct gzcuda_batch {
   std::vector<void *> allocs;
   int *h_sticky = nullptr;            // pinned copy of DevBatch::sticky, read back at every synchronising call
   std::vector<WorldInfo> h_world;
+  std::vector<int> h_joint_type;
   float last_ms = 0;
   long last_launches = 0;
   bool stage_valid = false;
@@ -273,7 +274,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         G.body = -1;
       }
       for (int k = 0; k < 3; k++) { G.opos[k] = sc->geom_pos[3 * g + k]; G.fdir1[k] = sc->geom_fdir1[3 * g + k]; }
-      q_to_R(sc->geom_quat + 4 * g, G.oR);   // dGeomSetOffsetQuaternion / dGeomSetQuaternion: dQtoR, no normalisation
+      if (sc->geom_rot) for (int k = 0; k < 9; k++) G.oR[k] = sc->geom_rot[9 * g + k];
+      else q_to_R(sc->geom_quat + 4 * g, G.oR);   // dGeomSetOffsetQuaternion / dGeomSetQuaternion: dQtoR, no normalisation
       for (int k = 0; k < GZ_SF_COUNT; k++) G.surf[k] = sc->geom_surf[GZ_SF_COUNT * g + k];
       if (G.surf[GZ_SF_PATCH_RADIUS] > 0 || G.surf[GZ_SF_ELASTIC_MODULUS] > 0)
         return fail(GZCUDA_E_INVALID, "torsional friction (patch_radius) and elastic-modulus contact rows are not supported");
@@ -358,6 +360,12 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   d.pgs_prof = getenv("GZCUDA_PGS_PROF") ? atoi(getenv("GZCUDA_PGS_PROF")) : 0;
   if ((rc = dev_alloc(b, &d.io_in, (size_t)6 * nb))) return rc;
   if ((rc = dev_alloc(b, &d.io_out, (size_t)13 * nb))) return rc;
+  if ((rc = dev_alloc(b, &d.set_stage, (size_t)13 * nb))) return rc;
+  if ((rc = dev_alloc(b, &d.jstage, (size_t)6 * nj))) return rc;
+  if ((rc = dev_alloc(b, &d.fb_stage, (size_t)12 * std::max(nj, max_cc)))) return rc;
+  if ((rc = dev_alloc(b, &d.flag_stage, (size_t)nb))) return rc;
+  b->h_joint_type.resize(nj);
+  for (int j = 0; j < nj; j++) b->h_joint_type[j] = hj[j].type;
   if ((rc = dev_alloc(b, &d.sticky, (size_t)4))) return rc;
   CK(cudaMallocHost((void **)&b->h_sticky, 4 * sizeof(int)));
 
@@ -904,60 +912,83 @@ int gzcuda_batch_get_body_state(gzcuda_batch *b, double *pos, double *quat, doub
   return check_overflow(b);
 }
 
+static int set_body_state_impl(gzcuda_batch *b, int first, int count, const double *pos, const double *quat,
+                               const double *lvel, const double *avel, int raw);
+
 int gzcuda_batch_set_body_state(gzcuda_batch *b, int first, int count, const double *pos,
                                 const double *quat, const double *lvel, const double *avel) {
-  if (!b || first < 0 || count < 0 || first + count > b->d.nb) return fail(GZCUDA_E_INVALID, "bad body range");
-  int rc = gzcuda_batch_sync(b);
-  if (rc) return rc;
-  std::vector<Body> hb(count);
+  return set_body_state_impl(b, first, count, pos, quat, lvel, avel, 0);
+}
+
+int gzcuda_batch_set_body_state_raw(gzcuda_batch *b, int first, int count, const double *pos,
+                                    const double *quat, const double *lvel, const double *avel) {
+  return set_body_state_impl(b, first, count, pos, quat, lvel, avel, 1);
+}
+
+int gzcuda_batch_set_body_enabled(gzcuda_batch *b, int first, int count, const int *enabled) {
+  if (!b || !enabled || first < 0 || count < 0 || first + count > b->d.nb) return fail(GZCUDA_E_INVALID, "bad body range");
   if (count == 0) return 0;
-  CK(cudaMemcpy(hb.data(), b->d.body + first, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
+  CK(cudaSetDevice(b->device));
+  CK(cudaMemcpyAsync(b->d.flag_stage, enabled, (size_t)count * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+  k_set_enabled<<<cdiv(count, 128), 128, 0, b->stream>>>(b->d, first, count);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+static int set_body_state_impl(gzcuda_batch *b, int first, int count, const double *pos, const double *quat,
+                               const double *lvel, const double *avel, int raw) {
+  if (!b || first < 0 || count < 0 || first + count > b->d.nb) return fail(GZCUDA_E_INVALID, "bad body range");
+  if (count == 0) return 0;
+  CK(cudaSetDevice(b->device));
+  // stream-ordered: stage [count][13] (NaN = group not given), one small kernel writes the touched fields
+  const double nan = std::nan("");
+  std::vector<double> h((size_t)13 * count);
   for (int i = 0; i < count; i++) {
+    double *o = h.data() + 13 * (size_t)i;
     for (int k = 0; k < 3; k++) {
-      if (pos) hb[i].pos[k] = pos[3 * i + k];
-      if (lvel) hb[i].lvel[k] = lvel[3 * i + k];
-      if (avel) hb[i].avel[k] = avel[3 * i + k];
+      o[k] = pos ? pos[3 * i + k] : nan;
+      o[7 + k] = lvel ? lvel[3 * i + k] : nan;
+      o[10 + k] = avel ? avel[3 * i + k] : nan;
     }
-    if (quat) {
-      for (int k = 0; k < 4; k++) hb[i].q[k] = quat[4 * i + k];
-      normalize4(hb[i].q);
-      q_to_R(hb[i].q, hb[i].R);
-    }
+    for (int k = 0; k < 4; k++) o[3 + k] = quat ? quat[4 * i + k] : nan;
   }
-  CK(cudaMemcpy(b->d.body + first, hb.data(), hb.size() * sizeof(Body), cudaMemcpyHostToDevice));
+  CK(cudaMemcpyAsync(b->d.set_stage, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));   // pageable source: staged before the call returns
+  k_set_state<<<cdiv(count, 128), 128, 0, b->stream>>>(b->d, first, count, raw);
+  CK(cudaGetLastError());
   return 0;
 }
 
 int gzcuda_batch_add_body_wrench(gzcuda_batch *b, const double *force, const double *torque) {
   if (!b) return fail(GZCUDA_E_INVALID, "null batch");
-  int rc = gzcuda_batch_sync(b);
-  if (rc) return rc;
-  std::vector<Body> hb(b->d.nb);
-  CK(cudaMemcpy(hb.data(), b->d.body, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
-  for (int i = 0; i < b->d.nb; i++)
+  CK(cudaSetDevice(b->device));
+  const int nb = b->d.nb;
+  if (nb == 0) return 0;
+  std::vector<double> h((size_t)6 * nb, 0.0);
+  for (int i = 0; i < nb; i++)
     for (int k = 0; k < 3; k++) {
-      if (force) hb[i].facc[k] += force[3 * i + k];
-      if (torque) hb[i].tacc[k] += torque[3 * i + k];
+      if (force) h[6 * (size_t)i + k] = force[3 * i + k];
+      if (torque) h[6 * (size_t)i + 3 + k] = torque[3 * i + k];
     }
-  CK(cudaMemcpy(b->d.body, hb.data(), hb.size() * sizeof(Body), cudaMemcpyHostToDevice));
+  CK(cudaMemcpyAsync(b->d.io_in, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+  k_apply_wrench<<<cdiv(nb, 128), 128, 0, b->stream>>>(b->d);
+  CK(cudaGetLastError());
   return 0;
 }
 
 int gzcuda_batch_get_body_flags(gzcuda_batch *b, int *flags) {
   if (!b || !flags) return fail(GZCUDA_E_INVALID, "null argument");
-  int rc = gzcuda_batch_sync(b);
-  if (rc) return rc;
-  std::vector<Body> hb(b->d.nb);
-  CK(cudaMemcpy(hb.data(), b->d.body, hb.size() * sizeof(Body), cudaMemcpyDeviceToHost));
-  for (int i = 0; i < b->d.nb; i++) flags[i] = hb[i].flags & GZ_BODY_DISABLED;
-  return 0;
+  CK(cudaSetDevice(b->device));
+  const int nb = b->d.nb;
+  if (nb == 0) return 0;
+  k_gather_flags<<<cdiv(nb, 128), 128, 0, b->stream>>>(b->d);
+  CK(cudaMemcpyAsync(flags, b->d.flag_stage, (size_t)nb * sizeof(int), cudaMemcpyDeviceToHost, b->stream));
+  return check_sticky(b);
 }
 
 int gzcuda_batch_set_joint_param(gzcuda_batch *b, int joint, int slot, double value) {
   if (!b || joint < 0 || joint >= b->d.nj || slot < 0 || slot >= GZ_JP_COUNT) return fail(GZCUDA_E_INVALID, "bad joint/slot");
-  int rc = gzcuda_batch_sync(b);
-  if (rc) return rc;
-  CK(cudaMemcpy(&b->d.joint[joint].param[slot], &value, sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaSetDevice(b->device));
+  CK(cudaMemcpyAsync(&b->d.joint[joint].param[slot], &value, sizeof(double), cudaMemcpyHostToDevice, b->stream));   // stream-ordered, 8 bytes
   return 0;
 }
 
@@ -979,36 +1010,28 @@ int gzcuda_batch_get_joint_state(gzcuda_batch *b, double *lambda, double *lambda
 
 int gzcuda_batch_set_hinge_pd(gzcuda_batch *b, const double *pd) {
   if (!b || !pd) return fail(GZCUDA_E_INVALID, "null argument");
-  int rc = gzcuda_batch_sync(b);
-  if (rc) return rc;
-  std::vector<Joint> hj(b->d.nj);
-  if (b->d.nj == 0) return 0;
-  CK(cudaMemcpy(hj.data(), b->d.joint, hj.size() * sizeof(Joint), cudaMemcpyDeviceToHost));
+  CK(cudaSetDevice(b->device));
+  const int nj = b->d.nj;
+  if (nj == 0) return 0;
   bool any = false;
-  for (int j = 0; j < b->d.nj; j++) {
-    for (int k = 0; k < 6; k++) hj[j].pd[k] = pd[6 * j + k];
-    any = any || pd[6 * j + 5] > 0;
-  }
-  CK(cudaMemcpy(b->d.joint, hj.data(), hj.size() * sizeof(Joint), cudaMemcpyHostToDevice));
+  for (int j = 0; j < nj; j++) any = any || pd[6 * j + 5] > 0;
+  CK(cudaMemcpyAsync(b->d.jstage, pd, (size_t)6 * nj * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+  k_set_pd<<<cdiv(nj, 128), 128, 0, b->stream>>>(b->d);
+  CK(cudaGetLastError());
   b->have_pd = any;
   return 0;
 }
 
 int gzcuda_batch_set_joint_velocity_cmd(gzcuda_batch *b, const double *vel) {
   if (!b || !vel) return fail(GZCUDA_E_INVALID, "null argument");
-  int rc = gzcuda_batch_sync(b);
-  if (rc) return rc;
-  if (b->d.nj == 0) return 0;
-  std::vector<Joint> hj(b->d.nj);
-  CK(cudaMemcpy(hj.data(), b->d.joint, hj.size() * sizeof(Joint), cudaMemcpyDeviceToHost));
+  CK(cudaSetDevice(b->device));
+  const int nj = b->d.nj;
+  if (nj == 0) return 0;
   bool any = false;
-  for (int j = 0; j < b->d.nj; j++) {
-    const bool on = vel[j] == vel[j] && hj[j].type == GZ_JOINT_HINGE;   // NaN = no command
-    hj[j].has_vel_cmd = on ? 1 : 0;
-    hj[j].vel_cmd = on ? vel[j] : 0.0;
-    any = any || on;
-  }
-  CK(cudaMemcpy(b->d.joint, hj.data(), hj.size() * sizeof(Joint), cudaMemcpyHostToDevice));
+  for (int j = 0; j < nj; j++) any = any || (vel[j] == vel[j] && b->h_joint_type[j] == GZ_JOINT_HINGE);   // NaN = no command
+  CK(cudaMemcpyAsync(b->d.jstage, vel, (size_t)nj * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+  k_set_velcmd<<<cdiv(nj, 128), 128, 0, b->stream>>>(b->d);
+  CK(cudaGetLastError());
   b->have_velcmd = any;
   return 0;
 }
@@ -1076,6 +1099,9 @@ int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double v) {
   else if (k == "contact_residual_smoothing") p.smooth_contacts = v;
   else if (k == "contact_sor_scale") p.contact_sor_scale = v;
   else if (k == "max_step_size") p.step_size = v;
+  else if (k == "gravity_x") p.gravity[0] = v;
+  else if (k == "gravity_y") p.gravity[1] = v;
+  else if (k == "gravity_z") p.gravity[2] = v;
   else if (k == "friction_model") {   // ODEPhysics::SetParam takes "pyramid_model" / "box_model" / "cone_model": 0 / 2 / 1 here
     if ((int)v != 0 && (int)v != 2) return fail(GZCUDA_E_INVALID, "friction_model: pyramid (0) and box (2) are supported");
     p.friction_model = (int)v;
@@ -1124,13 +1150,10 @@ int gzcuda_batch_get_joint_feedback(gzcuda_batch *b, double *fb) {
   if (rc) return rc;
   const int nj = b->d.nj;
   if (nj == 0) return 0;
-  double *dev = nullptr;
-  CK(cudaMalloc(&dev, (size_t)12 * nj * sizeof(double)));
+  double *dev = b->d.fb_stage;   // preallocated at creation
   k_feedback_joint<<<cdiv(nj, 128), 128, 0, b->stream>>>(b->d, dev);
-  cudaError_t e = cudaMemcpyAsync(fb, dev, (size_t)12 * nj * sizeof(double), cudaMemcpyDeviceToHost, b->stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
-  cudaFree(dev);
-  if (e != cudaSuccess) return fail(GZCUDA_E_CUDA, cudaGetErrorString(e));
+  CK(cudaMemcpyAsync(fb, dev, (size_t)12 * nj * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
   return nj;
 }
 
@@ -1181,13 +1204,10 @@ int gzcuda_batch_get_contact_feedback(gzcuda_batch *b, int world, double *fb, in
   CK(cudaMemcpy(&ws, b->d.wstep + world, sizeof(ws), cudaMemcpyDeviceToHost));
   const int n = ws.n_contacts;
   if (n == 0) return 0;
-  double *dev = nullptr;
-  CK(cudaMalloc(&dev, (size_t)12 * n * sizeof(double)));
+  double *dev = b->d.fb_stage;   // preallocated at creation ([max contact_cap][12])
   k_feedback_contact<<<cdiv(n, 128), 128, 0, b->stream>>>(b->d, world, dev);
-  cudaError_t e = cudaMemcpyAsync(fb, dev, (size_t)12 * std::min(n, cap) * sizeof(double), cudaMemcpyDeviceToHost, b->stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
-  cudaFree(dev);
-  if (e != cudaSuccess) return fail(GZCUDA_E_CUDA, cudaGetErrorString(e));
+  CK(cudaMemcpyAsync(fb, dev, (size_t)12 * std::min(n, cap) * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
   return n;
 }
 

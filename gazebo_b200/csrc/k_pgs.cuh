@@ -680,6 +680,52 @@ __global__ void k_apply_wrench(DevBatch B) {
   const double *in = B.io_in + 6 * (size_t)bi;
   for (int k = 0; k < 3; k++) { b.facc[k] += in[k]; b.tacc[k] += in[3 + k]; }
 }
+// Setters that a per-step plugin loop calls: stream-ordered, only the touched fields, no read-modify-write of the
+// whole body array on the host.  in[count][13] = pos 3, quat 4, lvel 3, avel 3; NaN in the first element of a
+// group = leave that group as it is.  A new quaternion is normalised and R rebuilt (dBodySetQuaternion, ode.cpp:414-427).
+__global__ void k_set_state(DevBatch B, int first, int count, int raw) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  Body &b = B.body[first + i];
+  const double *in = B.set_stage + 13 * (size_t)i;
+  if (in[0] == in[0]) for (int k = 0; k < 3; k++) b.pos[k] = in[k];
+  if (in[3] == in[3]) {
+    for (int k = 0; k < 4; k++) b.q[k] = in[3 + k];
+    if (!raw) normalize4(b.q);   // raw: the host's dBodySetQuaternion normalised it already; taken bit for bit
+    q_to_R(b.q, b.R);
+  }
+  if (in[7] == in[7]) for (int k = 0; k < 3; k++) b.lvel[k] = in[7 + k];
+  if (in[10] == in[10]) for (int k = 0; k < 3; k++) b.avel[k] = in[10 + k];
+}
+// dBodyEnable / dBodyDisable (ode.cpp:889-905): enabled[i] != 0 clears the disabled flag and restarts the auto-disable
+// counters, 0 sets the flag; a body whose flag already agrees is left alone.
+__global__ void k_set_enabled(DevBatch B, int first, int count) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  Body &b = B.body[first + i];
+  const bool want = B.flag_stage[i] != 0, is = !(b.flags & GZ_BODY_DISABLED);
+  if (want == is) return;
+  if (want) { b.flags &= ~GZ_BODY_DISABLED; b.adis_stepsleft = B.p.adis_idle_steps; b.adis_timeleft = B.p.adis_idle_time; }
+  else b.flags |= GZ_BODY_DISABLED;
+}
+__global__ void k_set_pd(DevBatch B) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= B.nj) return;
+  for (int k = 0; k < 6; k++) B.joint[j].pd[k] = B.jstage[6 * (size_t)j + k];
+}
+__global__ void k_set_velcmd(DevBatch B) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= B.nj) return;
+  const double v = B.jstage[j];
+  const bool on = v == v && B.joint[j].type == GZ_JOINT_HINGE;   // NaN = no command
+  B.joint[j].has_vel_cmd = on ? 1 : 0;
+  B.joint[j].vel_cmd = on ? v : 0.0;
+}
+__global__ void k_gather_flags(DevBatch B) {
+  int bi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bi >= B.nb) return;
+  B.flag_stage[bi] = B.body[bi].flags & GZ_BODY_DISABLED;
+}
 __global__ void k_gather_state(DevBatch B) {
   int bi = blockIdx.x * blockDim.x + threadIdx.x;
   if (bi >= B.nb) return;

@@ -84,6 +84,7 @@ class GzScene(C.Structure):
         ("joint_type", _IP), ("joint_body1", _IP), ("joint_body2", _IP),
         ("joint_anchor1", _DP), ("joint_anchor2", _DP), ("joint_axis1", _DP),
         ("joint_axis2", _DP), ("joint_qrel", _DP), ("joint_param", _DP),
+        ("geom_rot", _DP),      # optional, NULL here: the builders describe rotations by quaternions
     ]
 
 
@@ -392,7 +393,8 @@ class Scene:
         c = GzScene()
         c.n_worlds = self.n_worlds
         for name, ctype in GzScene._fields_[1:]:
-            setattr(c, name, A[name].ctypes.data_as(ctype))
+            if name in A:      # (optional fields such as geom_rot stay NULL)
+                setattr(c, name, A[name].ctypes.data_as(ctype))
         self.c = c
 
     def __getattr__(self, k):

@@ -74,6 +74,14 @@ int gzcuda_batch_get_body_state(gzcuda_batch *b, double *pos, double *quat, doub
  * ODELink::SetLinearVel/SetAngularVel); bodies [first, first+count). */
 int gzcuda_batch_set_body_state(gzcuda_batch *b, int first, int count, const double *pos,
                                 const double *quat, const double *lvel, const double *avel);
+/* The same for a binding that mirrors live dxBody objects (host/gzcuda_ode.cpp): the quaternion is taken bit for
+ * bit (dBodySetQuaternion normalised it on the host already, ode.cpp:414-427; normalising twice moves the last bit)
+ * and R is rebuilt from it as dQtoR does. */
+int gzcuda_batch_set_body_state_raw(gzcuda_batch *b, int first, int count, const double *pos,
+                                    const double *quat, const double *lvel, const double *avel);
+/* dBodyEnable / dBodyDisable (ode.cpp:869-887; ODELink::SetEnabled ODELink.cc:296-302): enabled[count], non-zero =
+ * enable (restarts the auto-disable counters), zero = disable.  Stream-ordered. */
+int gzcuda_batch_set_body_enabled(gzcuda_batch *b, int first, int count, const int *enabled);
 /* dBodyAddForce / dBodyAddTorque for every body ([nb][3] each, NULL = none). */
 int gzcuda_batch_add_body_wrench(gzcuda_batch *b, const double *force, const double *torque);
 /* dBodyIsEnabled: flags[nb] receives GZ_BODY_DISABLED or 0. */

@@ -130,6 +130,10 @@ typedef struct gz_scene {
   const double *joint_axis2;   /* [nj][3] body-2 frame (or world) */
   const double *joint_qrel;    /* [nj][4] initial relative rotation body1 -> body2 */
   const double *joint_param;   /* [nj][GZ_JP_COUNT] */
+
+  /* ---- optional (may be NULL) ---- */
+  const double *geom_rot;      /* [ng][9] row-major rotation replacing geom_quat: a binding that mirrors live ODE geoms
+                                * holds matrices (dxGeom::offset_posr / final_posr), and R -> q -> R is not exact */
 } gz_scene;
 
 #ifdef __cplusplus

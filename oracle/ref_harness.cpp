@@ -713,6 +713,44 @@ int gzref_step_mt(void *h, int nsteps, int nthreads) {
   return 0;
 }
 
+// ---- hooks for the tests of the host adapter (host/gzcuda_ode.cpp, libgzcuda_ode.so) -----------------------
+// The adapter works on LIVE ODE objects; these are the ones this harness built through the public ODE C API.
+// out[0] = dxWorld*, out[1] = the top-level dxSpace*, out[2] = user pointer for gzref_surface_cb.
+void gzref_world_handles(void *h, int world, void **out) {
+  RefWorld *w = static_cast<RefBatch *>(h)->worlds[world];
+  out[0] = w->world; out[1] = w->top; out[2] = w;
+}
+// What Gazebo's glue would answer from ODECollision / ODESurfaceParams (struct gzcuda_surface of
+// include/gzcuda_ode.h, restated here so that the harness does not depend on the product's headers beyond the scene).
+struct AdapterSurface {
+  double mu, mu2, kp, kd, slip1, slip2, bounce, bounce_vel, patch_radius, elastic_modulus, fdir1[3];
+  unsigned collide_bitmask; int max_contacts; long order_key;
+};
+int gzref_surface_cb(dGeomID g, AdapterSurface *o, void *user) {
+  RefWorld *w = static_cast<RefWorld *>(user);
+  const int i = geom_index(g);
+  if (i < 0 || i >= (int)w->surf.size()) return -1;
+  const Surface &s = w->surf[i];
+  o->mu = s.s[GZ_SF_MU]; o->mu2 = s.s[GZ_SF_MU2]; o->kp = s.s[GZ_SF_KP]; o->kd = s.s[GZ_SF_KD];
+  o->slip1 = s.s[GZ_SF_SLIP1]; o->slip2 = s.s[GZ_SF_SLIP2]; o->bounce = s.s[GZ_SF_BOUNCE]; o->bounce_vel = s.s[GZ_SF_BOUNCE_VEL];
+  o->patch_radius = 0; o->elastic_modulus = 0;
+  for (int k = 0; k < 3; k++) o->fdir1[k] = s.fdir1[k];
+  o->collide_bitmask = s.collide_bitmask; o->max_contacts = s.max_contacts;
+  o->order_key = i;   // Gazebo's creation order of the collisions = the scene's geom order
+  return 0;
+}
+// The plugin part of a step (World::Update, World.cc:746: plugins run before UpdateCollision): PD torques through
+// dJointAddHingeTorque, joint velocity commands through the bodies' velocities.  The adapter then has to honour what
+// these calls left in the dxBody objects.
+void gzref_plugin_update(void *h, int world) {
+  RefBatch *B = static_cast<RefBatch *>(h);
+  RefWorld *w = B->worlds[world];
+  dAllocateODEDataForThread(dAllocateMaskAll);
+  apply_velocity_commands(w);
+  apply_controllers(B, w);
+  w->step_index++;
+}
+
 // runs only ODEPhysics::UpdateCollision on one world (debug / parity of pair lists)
 int gzref_collide(void *h, int world) {
   RefBatch *B = static_cast<RefBatch *>(h);

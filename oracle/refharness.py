@@ -54,6 +54,8 @@ def _load(flavour):
     lib.gzref_set_joint_velocity_cmd.argtypes = [C.c_void_p, C.c_void_p]
     lib.gzref_get_joint_feedback.argtypes = [C.c_void_p, C.c_void_p]
     lib.gzref_get_contact_feedback.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    lib.gzref_world_handles.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    lib.gzref_plugin_update.argtypes = [C.c_void_p, C.c_int]
     _libs[flavour] = lib
     return lib
 
@@ -146,6 +148,20 @@ class RefBatch:
         fb = np.zeros((cap, 12))
         n = self.lib.gzref_get_contact_feedback(self.h, world, _p(fb), cap)
         return fb[:n].copy()
+
+    def world_handles(self, world):
+        """(dxWorld*, top dxSpace*, user pointer of gzref_surface_cb) of one world: the live ODE objects, for the
+        tests of the host adapter (libgzcuda_ode.so)."""
+        out = (C.c_void_p * 3)()
+        self.lib.gzref_world_handles(self.h, world, out)
+        return out[0], out[1], out[2]
+
+    def surface_cb_address(self):
+        return C.cast(self.lib.gzref_surface_cb, C.c_void_p).value
+
+    def plugin_update(self, world):
+        """The plugin part of a step (PD torques, joint velocity commands) applied to the live ODE objects."""
+        self.lib.gzref_plugin_update(self.h, world)
 
     def set_joint_velocity_cmd(self, vel):
         vel = np.ascontiguousarray(vel, dtype=np.float64).reshape(self.scene.nj)

@@ -27,6 +27,22 @@ def test_header_symbols_are_exported(gzlib):
     assert sorted(batch.EXPORTS) == decl    # the Python binding covers the whole header
 
 
+def test_adapter_header_symbols_are_exported():
+    """include/gzcuda_ode.h (the reference-facing step interface over live ODE objects) against libgzcuda_ode.so."""
+    path = os.path.join(ROOT, "gazebo_b200", "libgzcuda_ode.so")
+    if not os.path.exists(path):
+        pytest.skip("libgzcuda_ode.so needs the reference's headers to build (make -C host)")
+    text = open(os.path.join(ROOT, "include", "gzcuda_ode.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    decl = sorted(set(re.findall(r"\b(gzcuda_[a-z_0-9]+)\s*\(", text)) - {"gzcuda_surface_fn"})
+    out = subprocess.check_output(["nm", "-D", "--defined-only", path]).decode()
+    exported = set(line.split()[-1] for line in out.splitlines() if line.strip())
+    assert len(decl) >= 8 and not [s for s in decl if s not in exported]
+    undefined = subprocess.check_output(["nm", "-D", "--undefined-only", path]).decode()
+    # nothing of the oracle is linked in: the only ODE symbol it needs comes from the host process
+    assert "gzref" not in undefined and "dGeomMoved" in undefined
+
+
 def test_no_torch_or_cxx_types_in_signatures():
     text = open(os.path.join(ROOT, "include", "gzcuda.h")).read()
     assert "std::" not in text and "torch" not in text and "at::" not in text
@@ -58,10 +74,10 @@ def test_null_arguments_return_error_codes(gzlib):
 
 def test_product_never_imports_oracle():
     """Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may touch oracle/."""
-    pkg = os.path.join(ROOT, "gazebo_b200")
     bad = re.compile(r"from\s+oracle|import\s+oracle|#include\s+\".*oracle|libgzref|liboderef|refharness|dlopen")
-    for dirpath, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h")):
-                src = open(os.path.join(dirpath, f)).read()
-                assert not bad.search(src), f
+    for pkg in (os.path.join(ROOT, "gazebo_b200"), os.path.join(ROOT, "host"), os.path.join(ROOT, "include")):
+        for dirpath, _, files in os.walk(pkg):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                    src = open(os.path.join(dirpath, f)).read()
+                    assert not bad.search(src), f

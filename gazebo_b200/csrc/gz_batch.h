@@ -171,6 +171,7 @@ struct DevBatch {
   int4 *wsb;             // [n_worlds] {period R, stages, first entry, entries}
   int *rk_count;         // [2][GZ_PGSB_NKEY] worlds per period this step (by step parity, like ent_cursor)
   int *wkey;             // [n_worlds] period key | rank among the worlds of that key << 10
+  int *cls_ctr;          // [16] work-item counters of k_pgsb's shared-memory class launches (zeroed by k_border)
   int *wperm;            // [n_worlds] sweep order: worlds by period, longest first (k_border)
   int *sticky;           // [4] OR of every step's overflow masks since the last check, first world, spare
   double *io_in;         // [nb][6]  staged external wrench (gzcuda_batch_step_io)

@@ -59,6 +59,7 @@ struct gzcuda_batch {
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
   PgsbCfg pgsbc[GZ_PGSB_NCLS];        // the shared-memory classes of the one-warp CTAs, ascending budgets
   size_t pgsbc_smem[GZ_PGSB_NCLS] = {};
+  int pgsbc_grid[GZ_PGSB_NCLS] = {};         // persistent warps of each class: what the GPU can hold of them at once
   int pgsb_ncls = 1;
   cudaStream_t pgsb_stream[GZ_PGSB_NCLS] = {};   // one launch per class, side by side
   cudaEvent_t pgsb_join[GZ_PGSB_NCLS] = {};
@@ -398,6 +399,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if ((rc = dev_alloc(b, &d.rk_count, (size_t)2 * GZ_PGSB_NKEY))) return rc;
     if ((rc = dev_alloc(b, &d.wkey, (size_t)W))) return rc;
     if ((rc = dev_alloc(b, &d.wperm, (size_t)W))) return rc;
+    if ((rc = dev_alloc(b, &d.cls_ctr, (size_t)16))) return rc;
     int bp = 1;
     while (bp < max_nb) bp <<= 1;
     PgsbCfg &c = b->pgsb;
@@ -438,6 +440,12 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       b->pgsbc[i].last = i == b->pgsb_ncls - 1;
       b->pgsbc_smem[i] = std::max((size_t)(b->pgsbc[i].nres + 1) * ent_b + xch_b, red_b);
       mx_b = std::max(mx_b, b->pgsbc_smem[i]);
+      {
+        int n_sm = 148;
+        CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, b->device));
+        const int per_sm = (int)std::min<size_t>(16, std::max<size_t>(1, ((size_t)233 * 1024) / (b->pgsbc_smem[i] + 1024)));
+        b->pgsbc_grid[i] = std::max(1, std::min(b->pgsb_ctas, n_sm * per_sm));
+      }
       if (i > 0) {   // class 0 runs on the batch's stream; the larger the class, the higher the priority of its stream
         int plo = 0, phi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&plo, &phi));
@@ -581,14 +589,20 @@ gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params
 }
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+// blocks per world of a (gx, n_worlds) grid whose blocks stride over a world's items: enough to cover the slab's
+// capacity when the batch is small, but no more than keeps the whole grid near 8192 blocks (a block that finds
+// nothing to do still costs launch time: 57k mostly idle blocks made k_rowfinish the largest kernel outside the sweeps)
+static inline int item_blocks(int cap, int threads, int n_worlds) {
+  return std::max(1, std::min(cdiv(std::max(cap, 1), threads), 8192 / std::max(n_worlds, 1)));
+}
 
 static int launch_collision(gzcuda_batch *b) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
   k_geom<<<cdiv(std::max(d.ng, 1), T), T, 0, b->stream>>>(d);
   k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
-  if (b->has_cylinders) k_narrow<true><<<dim3(cdiv(d.max_pair_cap, T), W), T, 0, b->stream>>>(d);
-  else k_narrow<false><<<dim3(cdiv(d.max_pair_cap, T), W), T, 0, b->stream>>>(d);
+  if (b->has_cylinders) k_narrow<true><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
+  else k_narrow<false><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
   k_contacts<<<W, T, 0, b->stream>>>(d);
   b->last_launches += 4;
   return 0;
@@ -599,12 +613,12 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   const int W = d.n_worlds, T = 128;
   k_assemble1<<<W, T, 0, b->stream>>>(d);   // islands, body prologue, row counts
   if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
-  k_rows_contact<<<dim3(cdiv(d.max_contact_cap, T), W), T, 0, b->stream>>>(d);
+  k_rows_contact<<<dim3(item_blocks(d.max_contact_cap, 32, W), W), 32, 0, b->stream>>>(d);
   if (d.pgs_impl == 1) {
     // body-owner sweeps: schedule (integer work on the row counts), row prologue + entries, sweeps
     k_bsched<<<W, 128, b->bsched_smem, b->stream>>>(d);
     k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
-    k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
+    k_rowfinish<<<dim3(item_blocks(d.max_row_cap, 64, W), W), 64, 0, b->stream>>>(d);
     if (stage_events) cudaEventRecord(b->evs[2], b->stream);
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
     const bool box = d.p.friction_model == 2;
@@ -619,8 +633,8 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
         cudaStream_t sq = q == 0 ? b->stream : b->pgsb_stream[q];
         if (q > 0) cudaStreamWaitEvent(sq, b->ev_fork, 0);
         const int lower = q > 0 ? b->pgsbc[q - 1].nres : -1;
-        if (box) k_pgsb<false, true><<<b->pgsb_ctas, 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
-        else k_pgsb<false, false><<<b->pgsb_ctas, 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
+        if (box) k_pgsb<false, true><<<b->pgsbc_grid[q], 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
+        else k_pgsb<false, false><<<b->pgsbc_grid[q], 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
         if (q > 0) cudaEventRecord(b->pgsb_join[q], sq);
       }
       for (int q = 1; q < b->pgsb_ncls; q++) cudaStreamWaitEvent(b->stream, b->pgsb_join[q], 0);
@@ -637,7 +651,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
                           (d.sch_rpar > 0 ? (size_t)32 * (2 * std::max(d.max_nb, 1) * sizeof(int) + d.sch_rpar * sizeof(unsigned short)) : 0);
   k_schedule<<<W, 32, sch_smem, b->stream>>>(d);
   k_slab<<<1 + cdiv((W + GZ_NBUCKET) * 16, GZ_SLAB_T * 8), GZ_SLAB_T, 0, b->stream>>>(d);
-  k_rowfinish<<<dim3(cdiv(d.max_row_cap, T), W), T, 0, b->stream>>>(d);
+  k_rowfinish<<<dim3(item_blocks(d.max_row_cap, 64, W), W), 64, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
   // at most one warp per world plus a partly filled one per bucket; CTAs beyond the step's warp count exit at once

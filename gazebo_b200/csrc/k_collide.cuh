@@ -297,13 +297,9 @@ __device__ inline int collide_dispatch(const Geom &g1, const Geom &g2, COut &o, 
   return n;
 }
 
-// grid (ceil(max_pair_cap / blockDim), n_worlds): one thread per candidate pair
+// one candidate pair
 template <bool CYL>
-__global__ void k_narrow(DevBatch B) {
-  const int w = blockIdx.y;
-  const WorldInfo wi = B.world[w];
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= B.wstep[w].n_pairs) return;
+__device__ __forceinline__ void narrow_pair(DevBatch &B, const int w, const WorldInfo &wi, const int k) {
   const int pi = wi.pair0 + k;
   const Geom &g1 = B.geom[B.pair[2 * pi]];
   const Geom &g2 = B.geom[B.pair[2 * pi + 1]];
@@ -332,6 +328,16 @@ __global__ void k_narrow(DevBatch B) {
     }
   }
   B.pair_nc[pi] = numc;
+}
+
+// grid (gx, n_worlds): one thread per candidate pair, gx blocks striding over the world's pairs (gx is sized for
+// the pairs a world of the batch typically has, not for the slab's capacity: idle blocks cost launch time)
+template <bool CYL>
+__global__ void k_narrow(DevBatch B) {
+  const int w = blockIdx.y;
+  const WorldInfo wi = B.world[w];
+  const int n = B.wstep[w].n_pairs;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) narrow_pair<CYL>(B, w, wi, k);
 }
 
 // One CTA per world: exclusive scan of per-pair contact counts, then one thread per pair

@@ -447,11 +447,7 @@ __global__ void __launch_bounds__(GZ_SLAB_T) k_slab(DevBatch B) {
 
 // grid (ceil(max_row_cap / blockDim), n_worlds): one thread per row.  Finishes the row and
 // writes its packed record.
-__global__ void k_rowfinish(DevBatch B) {
-  const int w = blockIdx.y;
-  const WorldInfo wi = B.world[w];
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B.wstep[w].m) return;
+__device__ __forceinline__ void rowfinish_one(DevBatch &B, const int w, const WorldInfo &wi, const int i) {
   Row &r = B.row[wi.row0 + i];
   const double stepsize1 = 1.0 / B.p.step_size;
   const Body &b1 = B.body[wi.body0 + r.b1];
@@ -571,6 +567,14 @@ __global__ void k_rowfinish(DevBatch B) {
     hi.orig = r.t2a | ((r.findex >= 0) ? (1 << 30) : 0);
     *chain_head(sl, r.t1f & 0xFFFFF) = hi;
   }
+}
+
+// grid (gx, n_worlds): one thread per row, gx blocks striding over the world's rows
+__global__ void k_rowfinish(DevBatch B) {
+  const int w = blockIdx.y;
+  const WorldInfo wi = B.world[w];
+  const int m = B.wstep[w].m;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) rowfinish_one(B, w, wi, i);
 }
 
 }  // namespace gz

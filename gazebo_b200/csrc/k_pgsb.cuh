@@ -49,6 +49,7 @@ __device__ __forceinline__ unsigned pgsb_smid() {
   return s & 511u;
 }
 
+#define GZ_BS_SM 384   // rows up to which k_bsched works in shared memory
 struct WScratchB { int *rb1, *rb2, *off, *idx1, *idx2; };
 __device__ inline WScratchB wscratchb(const DevBatch &B, int w) {
   WScratchB s;
@@ -78,7 +79,13 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
   const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc;
   int *last = bs_sh, *first = bs_sh + B.max_nb, *cnt = bs_sh + 2 * B.max_nb, *fr0 = bs_sh + 3 * B.max_nb, *base = bs_sh + 4 * B.max_nb;
   __shared__ int s_R, s_maxoff, s_nent, s_wbase;
-  const WScratchB S = wscratchb(B, w);
+  const WScratchB G = wscratchb(B, w);
+  // the serial pass below walks these arrays with dependent accesses: worlds of up to GZ_BS_SM rows keep them in
+  // shared memory (the row offsets and list places go out to global memory in parallel afterwards)
+  __shared__ int sm_arr[5 * GZ_BS_SM];
+  const bool in_sm = m <= GZ_BS_SM;
+  WScratchB S = G;
+  if (in_sm) { S.rb1 = sm_arr; S.rb2 = sm_arr + GZ_BS_SM; S.off = sm_arr + 2 * GZ_BS_SM; S.idx1 = sm_arr + 3 * GZ_BS_SM; S.idx2 = sm_arr + 4 * GZ_BS_SM; }
   const int par = (int)(B.step_index & 1);
   if (w == 0) {   // the other parity's allocator and period histogram: idle this step
     if (tid == 0) B.ent_cursor[par ^ 1] = 0ull;
@@ -152,6 +159,8 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
   }
   __syncthreads();
   const int nent = s_nent, wbase = s_wbase;
+  if (in_sm)
+    for (int pos = tid; pos < m; pos += blockDim.x) { G.off[pos] = S.off[pos]; G.idx1[pos] = S.idx1[pos]; G.idx2[pos] = S.idx2[pos]; }
   for (int b = tid; b < nb; b += blockDim.x)
     B.bsched[wi.body0 + b] = nent > 0 ? make_int4(wbase + base[b], cnt[b], fr0[b] < 0 ? cnt[b] : fr0[b], 0) : make_int4(0, 0, 0, 0);
 }
@@ -161,6 +170,7 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
 __global__ void __launch_bounds__(256) k_border(DevBatch B) {
   __shared__ int pre[GZ_PGSB_NKEY];
   const int par = (int)(B.step_index & 1);
+  if (blockIdx.x == 0 && threadIdx.x < 16) B.cls_ctr[threadIdx.x] = 0;   // work counters of k_pgsb's class launches
   const int *cnt = B.rk_count + par * GZ_PGSB_NKEY;
   for (int q = threadIdx.x; q < GZ_PGSB_NKEY; q += blockDim.x) pre[q] = cnt[GZ_PGSB_NKEY - 1 - q];   // descending key
   __syncthreads();
@@ -303,42 +313,53 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp_g, cons
     N.lam = (due && pn == pc) ? nlw : N.lam;   // a one-entry list holds on to the entry it has just updated
     pc = pn; dlc = dln; sweep = nsw;
     T_due = more ? sweep * R + (N.mx & GZ_ENT_OFFMASK) : (due ? 0x7fffffff : T_due);
-    T = MULTI ? T + 1 : __reduce_min_sync(0xffffffffu, T_due);
   };
+#define GZ_PGSB_NEXT() T = MULTI ? T + 1 : __reduce_min_sync(0xffffffffu, T_due)
   while (MULTI ? T < rounds_multi : T != 0x7fffffff) {
     pass(EA, EB);
+    GZ_PGSB_NEXT();
     if (!(MULTI ? T < rounds_multi : T != 0x7fffffff)) break;
     pass(EB, EA);
+    GZ_PGSB_NEXT();
   }
+#undef GZ_PGSB_NEXT
   return npass;
 }
 
-// Shared-memory class of a CTA: 0 if the entries of all its worlds fit the small budget, 1 the large one,
-// 2 neither (the CTA then reads the pool).  Uniform over the CTA.
-__device__ __forceinline__ int pgsb_cta_entries(const DevBatch &B, const PgsbCfg &cfg) {
+// Shared memory a work item (the wpc worlds at places item * wpc .. of the sweep order) needs, in entries, rounded
+// up the way k_border's sort key is (steps of 4): NON-INCREASING in item, so the items of a shared-memory class
+// are a contiguous range.  A world beyond the key's range counts as "does not fit anywhere" (it reads the pool).
+__device__ __forceinline__ int pgsb_need(const DevBatch &B, const PgsbCfg &cfg, int item) {
   int n = 0;
   for (int s = 0; s < cfg.wpc; s++) {
-    const int q = blockIdx.x * cfg.wpc + s;
-    if (q < B.n_worlds) n += B.wsb[B.wperm[q]].w;
+    const int q = item * cfg.wpc + s;
+    if (q < B.n_worlds) {
+      const int key = B.wkey[B.wperm[q]] & 1023;
+      n += key >= GZ_PGSB_NKEY - 1 ? (1 << 24) : 4 * key;
+    }
   }
   return n;
 }
+// first item whose need is <= limit (items are sorted by need, largest first)
+__device__ __forceinline__ int pgsb_first_fitting(const DevBatch &B, const PgsbCfg &cfg, int n_items, int limit) {
+  int lo = 0, hi = n_items;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (pgsb_need(B, cfg, mid) <= limit) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
 
+// One work item: the sweeps of the wpc worlds of a warp (or of the one world of a multi-warp CTA).
 template <bool MULTI, bool BOX>
-__global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg cfg, int nres_small) {
+__device__ __forceinline__ void pgsb_item(const DevBatch &B, const PgsbCfg &cfg, const int item, const bool res) {
   extern __shared__ __align__(16) double shd[];
   const int tid = threadIdx.x;
   const int LW = cfg.lw;
-  // ---- is this CTA of this launch's class?
-  const int cta_ent = pgsb_cta_entries(B, cfg);
-  const bool res = cta_ent <= cfg.nres;
-  // class c takes the CTAs whose entries fit it and not the class below; the last class also takes what fits
-  // nowhere (those CTAs read the pool)
-  if (cfg.cls >= 0 && (cta_ent <= nres_small || (!res && !cfg.last))) return;
   const int wslot = MULTI ? 0 : tid / LW, lw = MULTI ? tid : tid % LW;
   const int bl = lw >> 1, S = lw & 1;
   const unsigned long long g0 = pgsb_gtimer();
-  const int wq = blockIdx.x * cfg.wpc + wslot;   // place in the sweep order (k_border)
+  const int wq = item * cfg.wpc + wslot;   // place in the sweep order (k_border)
   const bool live_w = wq < B.n_worlds;
   const int w = live_w ? B.wperm[wq] : 0;
   WorldInfo wi;
@@ -349,7 +370,7 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
   // ---- stage the entries of the CTA's worlds in shared memory (world after world, 22-double stride)
   int soff = 0;   // first staged entry of this world
   if (!MULTI)
-    for (int s = 0; s < wslot; s++) soff += B.wsb[B.wperm[blockIdx.x * cfg.wpc + s]].w;
+    for (int s = 0; s < wslot; s++) soff += B.wsb[B.wperm[item * cfg.wpc + s]].w;
   if (res) {
     const int n2 = nent * (GZ_ENT / 2);
     const double2 *src = reinterpret_cast<const double2 *>(B.ent + (size_t)sc.z * GZ_ENT);
@@ -469,6 +490,38 @@ __global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg c
     ws.num_contacts_stat = st_cnt[1];
     ws.pad[0] = npass; ws.pad[1] = R * 256 + (res ? 1 : 0);   // instrumentation: rounds, period, staged or not
     B.prof[16 + 2 * w] = g0; B.prof[16 + 2 * w + 1] = (pgsb_gtimer() & ~511ull) | pgsb_smid();   // timeline, low 9 bits: the SM
+  }
+}
+
+
+// The launch.  Multi-warp CTAs (worlds of more than 16 bodies): one CTA per world, entries staged if they fit.
+// One-warp CTAs: ONE LAUNCH PER SHARED-MEMORY CLASS (ascending budgets cfg.nres; nres_below = the budget of the
+// class below, -1 for the first), each a set of PERSISTENT warps that take the class's work items - a contiguous
+// range of the sweep order, heaviest first - from a counter until none is left: no CTA is launched only to find
+// that it belongs to another class, and the tail of a class is shared out dynamically.
+template <bool MULTI, bool BOX>
+__global__ void __launch_bounds__(MULTI ? 512 : 32) k_pgsb(DevBatch B, PgsbCfg cfg, int nres_below) {
+  if (MULTI) {
+    const int need = blockIdx.x < B.n_worlds ? B.wsb[B.wperm[blockIdx.x]].w : 0;
+    pgsb_item<true, BOX>(B, cfg, blockIdx.x, need <= cfg.nres);
+    return;
+  }
+  const int n_items = (B.n_worlds + cfg.wpc - 1) / cfg.wpc;
+  // class range: items that fit this class and not the one below; the last class also takes what fits nowhere
+  int lo = 0, hi = 0;
+  if (threadIdx.x == 0) {
+    lo = cfg.last ? 0 : pgsb_first_fitting(B, cfg, n_items, cfg.nres);
+    hi = nres_below >= 0 ? pgsb_first_fitting(B, cfg, n_items, nres_below) : n_items;
+  }
+  lo = __shfl_sync(0xffffffffu, lo, 0);
+  hi = __shfl_sync(0xffffffffu, hi, 0);
+  for (;;) {
+    int item = 0;
+    if (threadIdx.x == 0) item = lo + atomicAdd(&B.cls_ctr[cfg.cls], 1);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= hi) break;
+    pgsb_item<false, BOX>(B, cfg, item, pgsb_need(B, cfg, item) <= cfg.nres);
+    __syncwarp();   // the next item overwrites the staged entries
   }
 }
 

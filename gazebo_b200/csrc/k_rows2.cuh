@@ -213,11 +213,7 @@ __global__ void k_rows_joint(DevBatch B) {
 
 // One thread per contact: dxJointContact::getInfo2 with Gazebo's mode flags
 // (Bounce | Mu2 | SoftERP | SoftCFM | Approx1 | Approx3 | Slip1 | Slip2 [| FDir1]).
-__global__ void k_rows_contact(DevBatch B) {
-  const int w = blockIdx.y;
-  const WorldInfo wi = B.world[w];
-  const int ci = blockIdx.x * blockDim.x + threadIdx.x;
-  if (ci >= B.wstep[w].n_contacts || B.wstep[w].m == 0) return;
+__device__ __forceinline__ void rows_contact_one(DevBatch &B, const int w, const WorldInfo &wi, const int ci) {
   const Contact &C = B.contact[wi.contact0 + ci];
   Row *rows = B.row + wi.row0 + C.row0;
   const Body &b1 = B.body[C.b1];
@@ -287,6 +283,15 @@ __global__ void k_rows_contact(DevBatch B) {
     r.findex = abs_normal_row;
     r.cfm = f ? C.slip2 : C.slip1;
   }
+}
+
+// grid (gx, n_worlds): one thread per contact, gx blocks striding over the world's contacts
+__global__ void k_rows_contact(DevBatch B) {
+  const int w = blockIdx.y;
+  const WorldInfo wi = B.world[w];
+  if (B.wstep[w].m == 0) return;
+  const int n = B.wstep[w].n_contacts;
+  for (int ci = blockIdx.x * blockDim.x + threadIdx.x; ci < n; ci += gridDim.x * blockDim.x) rows_contact_one(B, w, wi, ci);
 }
 
 }  // namespace gz

@@ -43,6 +43,8 @@ struct gzcuda_batch {
   cudaStream_t stream_chain[GZ_CHAIN_NCLS] = {};   // the chain-mode PGS launches (one per shared-memory size class) run
   cudaEvent_t ev_fork = nullptr, ev_join[GZ_CHAIN_NCLS] = {};   // beside the regular one: fork / join by events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaStream_t stream_aux = nullptr;      // independent kernels of a step run beside the main stream (fork / join by events)
+  cudaEvent_t ev_aux_fork = nullptr, ev_aux_join = nullptr;
   std::vector<void *> allocs;
   int *h_sticky = nullptr;            // pinned copy of DevBatch::sticky, read back at every synchronising call
   std::vector<WorldInfo> h_world;
@@ -152,6 +154,9 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   for (auto &st : b->stream_chain) if (st) cudaStreamDestroy(st);
   for (auto &st : b->pgsb_stream) if (st) cudaStreamDestroy(st);
   for (auto &e : b->pgsb_join) if (e) cudaEventDestroy(e);
+  if (b->stream_aux) cudaStreamDestroy(b->stream_aux);
+  if (b->ev_aux_fork) cudaEventDestroy(b->ev_aux_fork);
+  if (b->ev_aux_join) cudaEventDestroy(b->ev_aux_join);
   if (b->stream_copy) cudaStreamDestroy(b->stream_copy);
   for (auto &e : b->ev_frame) if (e) cudaEventDestroy(e);
   for (auto &e : b->ev_copied) if (e) cudaEventDestroy(e);
@@ -569,6 +574,9 @@ gzcuda_batch *gzcuda_batch_create(const gz_scene *scene, const gz_params *params
   bool ok = cudaStreamCreateWithPriority(&b->stream, cudaStreamNonBlocking, b->reg_first ? phi0 : plo0) == cudaSuccess &&
             cudaEventCreate(&b->ev0) == cudaSuccess && cudaEventCreate(&b->ev1) == cudaSuccess;
   for (auto &e : b->evs) ok = ok && cudaEventCreate(&e) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&b->stream_aux, cudaStreamNonBlocking) == cudaSuccess &&
+       cudaEventCreateWithFlags(&b->ev_aux_fork, cudaEventDisableTiming) == cudaSuccess &&
+       cudaEventCreateWithFlags(&b->ev_aux_join, cudaEventDisableTiming) == cudaSuccess;
   {
     int plo = 0, phi = 0;
     cudaDeviceGetStreamPriorityRange(&plo, &phi);
@@ -612,12 +620,22 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
   k_assemble1<<<W, T, 0, b->stream>>>(d);   // islands, body prologue, row counts
-  if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
+  // the joint rows (one thread per joint: a long dependent chain on few threads) run beside the contact rows and
+  // the schedule, which do not depend on them; k_rowfinish needs all three
+  const bool fork_joint = d.nj > 0 && d.pgs_impl == 1;
+  if (fork_joint) {
+    cudaEventRecord(b->ev_aux_fork, b->stream);
+    cudaStreamWaitEvent(b->stream_aux, b->ev_aux_fork, 0);
+    k_rows_joint<<<cdiv(d.nj, 32), 32, 0, b->stream_aux>>>(d);
+    cudaEventRecord(b->ev_aux_join, b->stream_aux);
+    b->last_launches++;
+  } else if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(item_blocks(d.max_contact_cap, 32, W), W), 32, 0, b->stream>>>(d);
   if (d.pgs_impl == 1) {
     // body-owner sweeps: schedule (integer work on the row counts), row prologue + entries, sweeps
     k_bsched<<<W, 128, b->bsched_smem, b->stream>>>(d);
     k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
+    if (fork_joint) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
     k_rowfinish<<<dim3(item_blocks(d.max_row_cap, 64, W), W), 64, 0, b->stream>>>(d);
     if (stage_events) cudaEventRecord(b->evs[2], b->stream);
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
@@ -642,8 +660,15 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     }
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot + 1], b->stream);
     if (stage_events) cudaEventRecord(b->evs[3], b->stream);
-    if (d.nj > 0) { k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
-    k_integrate<<<cdiv(std::max(d.nb, 1), T), T, 0, b->stream>>>(d);
+    if (d.nj > 0) {   // lambda write-back to the joints beside the integration
+      cudaEventRecord(b->ev_aux_fork, b->stream);
+      cudaStreamWaitEvent(b->stream_aux, b->ev_aux_fork, 0);
+      k_lambda_save<<<cdiv(d.nj, T), T, 0, b->stream_aux>>>(d);
+      cudaEventRecord(b->ev_aux_join, b->stream_aux);
+      b->last_launches++;
+    }
+    k_integrate<<<cdiv(std::max(d.nb, 1), 64), 64, 0, b->stream>>>(d);
+    if (d.nj > 0) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
     b->last_launches += 7;
     return 0;
   }
@@ -716,11 +741,18 @@ static int run_steps(gzcuda_batch *b, int n_steps) {
       k_velcmd<<<cdiv(b->d.n_worlds, 128), 128, 0, b->stream>>>(b->d);
       b->last_launches++;
     }
-    if (b->have_pd) {
-      k_control<<<cdiv(std::max(b->d.nb, 1), 128), 128, 0, b->stream>>>(b->d);
+    // the plugin stand-in (PD torques into tacc) runs beside the collision pipeline, which does not read the
+    // accumulators; k_assemble1 (body prologue) is the first kernel that does
+    const bool fork_ctl = b->have_pd;
+    if (fork_ctl) {
+      cudaEventRecord(b->ev_aux_fork, b->stream);
+      cudaStreamWaitEvent(b->stream_aux, b->ev_aux_fork, 0);
+      k_control<<<cdiv(std::max(b->d.nb, 1), 64), 64, 0, b->stream_aux>>>(b->d);
+      cudaEventRecord(b->ev_aux_join, b->stream_aux);
       b->last_launches++;
     }
     launch_collision(b);
+    if (fork_ctl) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
     if (last) cudaEventRecord(b->evs[1], b->stream);
     launch_physics(b, last, b->profiling ? s : -1);
     if (last) cudaEventRecord(b->evs[4], b->stream);

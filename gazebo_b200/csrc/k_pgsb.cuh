@@ -110,6 +110,51 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
     }
   }
   __syncthreads();
+  if (B.max_nb <= 32) {
+    // ---- worlds of up to 32 bodies: the serial pass is run by ONE WARP with lane b holding body b's counters in
+    // registers: a row costs two shuffles and a handful of integer instructions instead of a chain of dependent
+    // shared-memory reads and writes on one thread
+    if (tid < 32) {
+      const int lane = tid, pfric = mj + nc;
+      int lst = -1, fst = -1, c = 0, f0 = -1, maxoff = -1;
+      for (int pos = 0; pos < m; pos++) {
+        const int x1 = S.rb1[pos], x2 = S.rb2[pos];          // same address for all lanes: broadcast
+        if (x1 < 0) { if (lane == 0) S.off[pos] = -1; continue; }
+        const int y2 = x2 >= 0 ? x2 : x1;
+        const int l1 = __shfl_sync(0xffffffffu, lst, x1), l2 = __shfl_sync(0xffffffffu, lst, y2);
+        const int c1 = __shfl_sync(0xffffffffu, c, x1), c2 = __shfl_sync(0xffffffffu, c, y2);
+        const int o = max(l1, l2) + 1;
+        if (lane == x1 || lane == x2) {
+          if (pos >= pfric && f0 < 0) f0 = c;
+          c++;
+          lst = o;
+          if (fst < 0) fst = o;
+        }
+        if (lane == 0) { S.off[pos] = o; S.idx1[pos] = c1; if (x2 >= 0) S.idx2[pos] = c2; }
+        maxoff = max(maxoff, o);
+      }
+      const int span = fst >= 0 ? lst - fst + 1 : 1;
+      const int R = __reduce_max_sync(0xffffffffu, span);
+      int incl = c;                                           // inclusive scan of the list lengths
+      for (int dd = 1; dd < 32; dd <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, dd); if (lane >= dd) incl += t; }
+      int nent = __shfl_sync(0xffffffffu, incl, 31);
+      if (lane < nb) { cnt[lane] = c; fr0[lane] = f0; base[lane] = incl - c; }
+      if (lane == 0) {
+        long long wbase = 0;
+        if (nent > 0) {
+          wbase = (long long)atomicAdd(&B.ent_cursor[par], (unsigned long long)nent);
+          if (wbase + nent > B.ent_cap - 1 || maxoff > GZ_ENT_OFFMASK) { ws.overflow |= 16; nent = 0; }   // pool exhausted (its last entry is the dummy entry)
+        }
+        s_nent = nent; s_wbase = (int)wbase;
+        B.wsb[w] = make_int4(R, maxoff < 0 ? 0 : maxoff / R + 1, (int)wbase, nent);
+        const int key = min((nent + 3) >> 2, GZ_PGSB_NKEY - 1);   // k_border's sort key, see below
+        B.wkey[w] = key | (atomicAdd(&B.rk_count[par * GZ_PGSB_NKEY + key], 1) << 10);
+      }
+      nent = __shfl_sync(0xffffffffu, nent, 0);
+      if (nent == 0)
+        for (int pos = lane; pos < m; pos += 32) S.off[pos] = -1;   // rows without entries: k_rowfinish skips them
+    }
+  } else
   if (tid == 0) {
     int maxoff = -1;
     const int pfric = mj + nc;

@@ -43,6 +43,7 @@ struct Body {
 // per-step scratch of a body
 struct BodyStep {
   double invMOI[9];
+  double MOI[9];      // world-frame inertia: scratch of k_dyn_inertia (DYNAMIC_INERTIA), written only when it is on
   double caccel[6], caccel_erp[6];
   int label;      // island label = lowest world-local body index of the component
   int active;     // in an island stepped this step

@@ -636,6 +636,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     k_bsched<<<W, 128, b->bsched_smem, b->stream>>>(d);
     k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
     if (fork_joint) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
+    if (d.p.dynamic_inertia && d.nj > 0) { k_dyn_inertia<<<cdiv(W, 64), 64, 0, b->stream>>>(d); b->last_launches++; }
     k_rowfinish<<<dim3(item_blocks(d.max_row_cap, 64, W), W), 64, 0, b->stream>>>(d);
     if (stage_events) cudaEventRecord(b->evs[2], b->stream);
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
@@ -676,6 +677,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
                           (d.sch_rpar > 0 ? (size_t)32 * (2 * std::max(d.max_nb, 1) * sizeof(int) + d.sch_rpar * sizeof(unsigned short)) : 0);
   k_schedule<<<W, 32, sch_smem, b->stream>>>(d);
   k_slab<<<1 + cdiv((W + GZ_NBUCKET) * 16, GZ_SLAB_T * 8), GZ_SLAB_T, 0, b->stream>>>(d);
+  if (d.p.dynamic_inertia && d.nj > 0) { k_dyn_inertia<<<cdiv(W, 64), 64, 0, b->stream>>>(d); b->last_launches++; }
   k_rowfinish<<<dim3(item_blocks(d.max_row_cap, 64, W), W), 64, 0, b->stream>>>(d);
   if (stage_events) cudaEventRecord(b->evs[2], b->stream);
   if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
@@ -1145,6 +1147,7 @@ int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double v) {
   else if (k == "contact_residual_smoothing") p.smooth_contacts = v;
   else if (k == "contact_sor_scale") p.contact_sor_scale = v;
   else if (k == "max_step_size") p.step_size = v;
+  else if (k == "dynamic_moi_rescaling") p.dynamic_inertia = v != 0;   // ODEPhysics::SetParam("use_dynamic_moi_rescaling")
   else if (k == "gravity_x") p.gravity[0] = v;
   else if (k == "gravity_y") p.gravity[1] = v;
   else if (k == "gravity_z") p.gravity[2] = v;

@@ -183,6 +183,10 @@ __device__ __forceinline__ void bodyprep_body(const DevBatch &B, const int bi) {
   double tmp[9], MOI[9];
   mul2_333(tmp, b.invI, b.R);
   mul0_333(bs.invMOI, b.R, tmp);
+  if (B.p.dynamic_inertia) {   // quickstep.cpp:119-139 computes MOI for every body; only DYNAMIC_INERTIA reads it later
+    mul2_333(tmp, b.I, b.R);
+    mul0_333(bs.MOI, b.R, tmp);
+  }
   if (!(b.flags & GZ_BODY_NO_GYRO)) {
     mul2_333(tmp, b.I, b.R);
     mul0_333(MOI, b.R, tmp);

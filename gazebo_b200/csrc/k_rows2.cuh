@@ -285,6 +285,73 @@ __device__ __forceinline__ void rows_contact_one(DevBatch &B, const int w, const
   }
 }
 
+// DYNAMIC_INERTIA (quickstep_util.cpp:170-524; switched by qs.dynamic_inertia_reduction, ODEPhysics.cc:186-194).  For
+// rows 3 and 4 of every hinge between two dynamic bodies - the two rotational constraint axes - compare the bodies'
+// inertia along the axis S; if the ratio exceeds 200 move dm of it from the large to the small one (MOI -/+= dm S S^T)
+// unless a row of either adjusted matrix would lose diagonal dominance (generalised line criterion), then invert both
+// matrices analytically.  The reference does this inside its serial getInfo2 loop, so a body shared by several hinges
+// is adjusted in joint order: one thread per world walks the world's joints in index order (the canonical order).
+__device__ inline void sym_inverse(const double *M, double *inv) {   // :396-419, cofactor by cofactor as written
+  const double det = M[0] * (M[8] * M[4] - M[7] * M[5]) - M[3] * (M[8] * M[1] - M[7] * M[2]) + M[6] * (M[5] * M[1] - M[4] * M[2]);
+  inv[0] = (M[8] * M[4] - M[7] * M[5]) / det;
+  inv[1] = -(M[8] * M[1] - M[7] * M[2]) / det;
+  inv[2] = (M[5] * M[1] - M[4] * M[2]) / det;
+  inv[3] = inv[1];
+  inv[4] = (M[8] * M[0] - M[6] * M[2]) / det;
+  inv[5] = -(M[5] * M[0] - M[3] * M[2]) / det;
+  inv[6] = inv[2];
+  inv[7] = inv[5];
+  inv[8] = (M[4] * M[0] - M[3] * M[1]) / det;
+}
+__global__ void k_dyn_inertia(DevBatch B) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= B.n_worlds) return;
+  const WorldInfo wi = B.world[w];
+  if (B.wstep[w].m == 0) return;
+  for (int k = 0; k < wi.nj; k++) {
+    const Joint &j = B.joint[wi.joint0 + k];
+    if (j.type != GZ_JOINT_HINGE || j.m == 0 || j.b2 < 0) continue;
+    double *MOI1 = B.bstep[j.b1].MOI, *MOI2 = B.bstep[j.b2].MOI;
+    double *inv1 = B.bstep[j.b1].invMOI, *inv2 = B.bstep[j.b2].invMOI;
+    for (int r = 3; r <= 4; r++) {
+      const Row &row = B.row[wi.row0 + j.row0 + r];
+      double S[3] = {row.J[3], row.J[4], row.J[5]};   // J1a
+      safe_normalize3(S);
+      // m = S' MOI S (dMultiply0_133 then dCalcVectorDot3)
+      double t1[3], t2[3];
+      for (int c = 0; c < 3; c++) {
+        t1[c] = MOI1[c] * S[0] + MOI1[3 + c] * S[1] + MOI1[6 + c] * S[2];
+        t2[c] = MOI2[c] * S[0] + MOI2[3 + c] * S[1] + MOI2[6 + c] * S[2];
+      }
+      const double m1 = t1[0] * S[0] + t1[1] * S[1] + t1[2] * S[2];
+      const double m2 = t2[0] * S[0] + t2[1] * S[1] + t2[2] * S[2];
+      double m_large = m1, m_small = m2;
+      double *ML = MOI1, *MS = MOI2;
+      if (m2 > m1) { m_large = m2; m_small = m1; ML = MOI2; MS = MOI1; }
+      const double SS[9] = {S[0] * S[0], S[0] * S[1], S[0] * S[2], S[1] * S[0], S[1] * S[1], S[1] * S[2],
+                            S[2] * S[0], S[2] * S[1], S[2] * S[2]};
+      const double moi_ratio_max = 200.0;
+      if (m_large > moi_ratio_max * m_small) {
+        const double dm = (m_large - moi_ratio_max * m_small) / (1 + moi_ratio_max);
+        int problem = 0;
+        for (int rw = 0; rw < 3; ++rw) {
+          const int c1 = (rw + 1) % 3, c2 = (rw + 2) % 3;
+          const int id = 3 * rw + rw, i1 = 3 * rw + c1, i2 = 3 * rw + c2;
+          const double Md_large = ML[id] - dm * SS[id];
+          const double Mod_large = fabs(ML[i1] - dm * SS[i1]) + fabs(ML[i2] - dm * SS[i2]);
+          const double Md_small = MS[id] + dm * SS[id];
+          const double Mod_small = fabs(MS[i1] + dm * SS[i1]) + fabs(MS[i2] + dm * SS[i2]);
+          if (Md_large <= Mod_large || Md_small <= Mod_small) problem = 1;   // gamma = 1
+        }
+        if (problem == 0)
+          for (int i = 0; i < 9; i++) { ML[i] -= dm * SS[i]; MS[i] += dm * SS[i]; }
+        sym_inverse(MOI1, inv1);   // (the reference re-inverts both whether or not the matrices changed)
+        sym_inverse(MOI2, inv2);
+      }
+    }
+  }
+}
+
 // grid (gx, n_worlds): one thread per contact, gx blocks striding over the world's contacts
 __global__ void k_rows_contact(DevBatch B) {
   const int w = blockIdx.y;

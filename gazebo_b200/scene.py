@@ -38,6 +38,7 @@ class GzParams(C.Structure):
         ("adis_linear_threshold_sq", C.c_double), ("adis_angular_threshold_sq", C.c_double),
         ("damping_linear_threshold_sq", C.c_double), ("damping_angular_threshold_sq", C.c_double),
         ("friction_model", C.c_int),
+        ("dynamic_inertia", C.c_int),
     ]
 
 

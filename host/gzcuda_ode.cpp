@@ -95,6 +95,7 @@ void read_params(const dxWorld *w, double h, int max_contacts, gz_params &p) {
   p.damping_linear_threshold_sq = w->dampingp.linear_threshold;
   p.damping_angular_threshold_sq = w->dampingp.angular_threshold;
   p.friction_model = (int)w->qs.friction_model;
+  p.dynamic_inertia = w->qs.dynamic_inertia_reduction ? 1 : 0;
 }
 
 }  // namespace
@@ -322,6 +323,7 @@ int push_params(Mirror *m, double h) {
     {"warm_start_factor", p.warm_start, o.warm_start}, {"contact_residual_smoothing", p.smooth_contacts, o.smooth_contacts},
     {"contact_sor_scale", p.contact_sor_scale, o.contact_sor_scale}, {"max_step_size", p.step_size, o.step_size},
     {"friction_model", (double)p.friction_model, (double)o.friction_model},
+    {"dynamic_moi_rescaling", (double)p.dynamic_inertia, (double)o.dynamic_inertia},
     {"gravity_x", p.gravity[0], o.gravity[0]}, {"gravity_y", p.gravity[1], o.gravity[1]}, {"gravity_z", p.gravity[2], o.gravity[2]},
   };
   for (auto &e : kv)

@@ -110,7 +110,8 @@ int gzcuda_batch_get_stats(gzcuda_batch *b, double *rms_residual, int *num_conta
 /* ODEPhysics::SetParam for the numeric solver keys (ODEPhysics.cc:1420-1581):
  * "iters", "sor", "cfm", "erp", "contact_max_correcting_vel", "contact_surface_layer",
  * "max_contacts", "friction_iters", "warm_start_factor", "contact_residual_smoothing",
- * "contact_sor_scale", "max_step_size". */
+ * "contact_sor_scale", "max_step_size", "friction_model", "dynamic_moi_rescaling" (ODEPhysics.cc:186-194:
+ * DYNAMIC_INERTIA, quickstep_util.cpp:170-524), and "gravity_x" / "gravity_y" / "gravity_z" (dWorldSetGravity). */
 int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double value);
 
 /* Collision products of the last step (ContactManager contents): candidate pairs of one world

@@ -87,6 +87,10 @@ typedef struct gz_params {
   /* qs.friction_model (ode.cpp:1672, ODEPhysics::SetFrictionModel): 0 = pyramid (default), 2 = box
    * (friction limits +-mu instead of +-mu * lambda_normal); 1 = cone is not supported */
   int    friction_model;
+  /* qs.dynamic_inertia_reduction (dWorldSetQuickStepInertiaRatioReduction; SDF <use_dynamic_moi_rescaling>,
+   * ODEPhysics.cc:186-194, default false): move inertia between the two bodies of a hinge along its constrained
+   * axes when their ratio exceeds 200 (DYNAMIC_INERTIA, quickstep_util.cpp:170-524) */
+  int    dynamic_inertia;
 } gz_params;
 
 typedef struct gz_scene {

@@ -426,7 +426,7 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
     dHashSpaceSetLevels(w->top, -2, 8);
     w->contactGroup = dJointGroupCreate(0);
     // ODEPhysics::Load (ODEPhysics.cc:175-243)
-    dWorldSetQuickStepInertiaRatioReduction(w->world, false);  // SDF default (physics.sdf:199)
+    dWorldSetQuickStepInertiaRatioReduction(w->world, p->dynamic_inertia != 0);  // SDF default false (physics.sdf:199)
     dWorldSetDamping(w->world, 0.0001, 0.0001);
     dWorldSetContactMaxCorrectingVel(w->world, p->contact_max_correcting_vel);
     dWorldSetContactSurfaceLayer(w->world, p->contact_surface_layer);

@@ -268,6 +268,31 @@ def sleepers():
     return sb.finish(), S.default_params(), None
 
 
+def dyn_inertia():
+    """DYNAMIC_INERTIA (quickstep_util.cpp:170-524): a heavy base carrying thin, light arms on hinges - inertia ratios
+    far beyond 200 along the hinges' constrained axes - one arm carrying a second one (a body shared by two hinges is
+    adjusted twice, in joint order), plus a pair of similar bodies that must be left alone.  Standing on the plane."""
+    sb = S.SceneBuilder()
+    p = S.default_params(dynamic_inertia=1)
+    for w in range(2):
+        sb.begin_world()
+        sb.add_ground_plane()
+        sp = sb.new_space()
+        base = sb.add_body([0, 0, 0.25], S.q_from_rpy(0, 0, 0.3 * w), mass=20.0, inertia=S.box_inertia(20.0, 0.6, 0.6, 0.5))
+        sb.add_geom(S.GEOM_BOX, (0.6, 0.6, 0.5), sp, body=base)
+        a1 = sb.add_body([0.5, 0, 0.55], S.q_from_rpy(0, 0.4, 0), mass=0.01, inertia=S.box_inertia(0.01, 0.4, 0.02, 0.02))
+        sb.add_geom(S.GEOM_BOX, (0.4, 0.02, 0.02), sp, body=a1)
+        sb.add_hinge(a1, base, [0.3, 0, 0.5], [0, 1, 0])
+        a2 = sb.add_body([0.9, 0, 0.55], S.q_from_rpy(0.2, 0, 0), mass=0.004, inertia=S.box_inertia(0.004, 0.3, 0.01, 0.01))
+        sb.add_geom(S.GEOM_BOX, (0.3, 0.01, 0.01), sp, body=a2)
+        sb.add_hinge(a2, a1, [0.72, 0, 0.55], [0, 0, 1])
+        c1 = sb.add_body([-0.6, 0.5 * w, 0.7], mass=1.0, inertia=S.box_inertia(1.0, 0.2, 0.2, 0.2))
+        sb.add_geom(S.GEOM_BOX, (0.2, 0.2, 0.2), sp, body=c1)
+        sb.add_hinge(c1, base, [-0.3, 0, 0.6], [1, 0, 0])
+        sb.end_world()
+    return sb.finish(), p, None
+
+
 def fdir1():
     """ODEPhysics.cc:1120-1161 as written: only collision 1's friction direction reaches the contact.  Anisotropic
     friction (mu != mu2) and boxes sliding diagonally, with fdir1 on geom 1 only (the plane; a rotated static
@@ -308,4 +333,5 @@ GOLDEN = {
     "cylboxes": (cylboxes, 500),
     "cylcyl": (cylcyl, 400),
     "fdir1": (fdir1, 300),
+    "dyn_inertia": (dyn_inertia, 400),
 }

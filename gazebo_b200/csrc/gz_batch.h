@@ -161,7 +161,9 @@ struct DevBatch {
   int bp_sap_min;        // geoms from which a world takes the sort-and-sweep broadphase (k_collide.cuh)
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   // ---- body-owner PGS (k_pgsb.cuh): per-body entry lists in a bump-allocated pool
-  int pgs_impl;          // 1: body-owner sweeps (k_pgsb), 0: the round-1 row-slot sweeps (k_pgs / k_pgs_chain)
+  int *bs_glob;          // [5][max_nb] k_bsched's per-body tables for worlds too large for shared memory (else null)
+  double *xch_g;         // [2][lanes] k_pgsl: partial dot products of a round (double-buffered), then [grid][9] statistics partials
+  int pgs_impl;          // 2: body-owner sweeps over a cooperative grid (k_pgsl, worlds of more than 512 bodies), 1: body-owner sweeps (k_pgsb), 0: the round-1 row-slot sweeps (k_pgs / k_pgs_chain)
   double *ent;           // [ent_cap][GZ_ENT] half-records, one per (row, body), grouped per body in order[] sequence
   int *ent_row;          // [ent_cap] world-local row index if this entry is the row's body-1 half (lambda write-back), else -1
   double *ent_ad2;       // [ent_cap] 1 / Ad^2 (statistics)

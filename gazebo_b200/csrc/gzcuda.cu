@@ -59,6 +59,7 @@ struct gzcuda_batch {
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
   int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
+  int pgsl_grid = 0;                  // CTAs of k_pgsl's cooperative grid
   PgsbCfg pgsbc[GZ_PGSB_NCLS];        // the shared-memory classes of the one-warp CTAs, ascending budgets
   size_t pgsbc_smem[GZ_PGSB_NCLS] = {};
   int pgsbc_grid[GZ_PGSB_NCLS] = {};         // persistent warps of each class: what the GPU can hold of them at once
@@ -326,7 +327,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   }
   d.max_nb = max_nb; d.max_ng = max_ng; d.max_nj = max_nj;
   d.max_pair_cap = max_pc; d.max_contact_cap = max_cc; d.max_row_cap = max_rc;
-  if (max_nb > 512) return fail(GZCUDA_E_INVALID, "worlds with more than 512 bodies need the streaming solver (not built yet)");
+  if (max_nb >= GZ_ENT_NOPART) return fail(GZCUDA_E_INVALID, "worlds are limited to 65534 bodies (16-bit partner ids in the PGS entries)");
   b->h_world = hw;
 
   int rc;
@@ -378,9 +379,26 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   // Body-owner PGS (k_pgsb.cuh): the default for worlds of up to 256 bodies.  Entry pool: a row has one entry
   // per body, so 2 x rows is the worst case; clamped to a quarter of the free memory (k_bsched flags a step
   // that does not fit).
-  d.pgs_impl = (max_nb <= 256) ? 1 : 0;
-  if (const char *e = getenv("GZCUDA_PGS_IMPL")) d.pgs_impl = (atoi(e) != 0 && max_nb <= 256) ? 1 : 0;
-  if (d.pgs_impl == 1) {
+  // <= 256 bodies: k_pgsb (warp or CTA per world); <= 512: round 1's row-slot kernels (a world's accumulators in one
+  // CTA's shared memory); beyond: k_pgsl, the body-owner sweeps over a cooperative grid
+  d.pgs_impl = (max_nb <= 256) ? 1 : (max_nb <= 512 ? 0 : 2);
+  if (const char *e = getenv("GZCUDA_PGS_IMPL")) {
+    const int v = atoi(e);
+    if (v == 0 && max_nb <= 512) d.pgs_impl = 0;
+    if (v == 2) d.pgs_impl = 2;
+  }
+  if (d.pgs_impl == 2) {
+    // one lane per (body, solve) of the largest world, all CTAs resident (cooperative launch)
+    int n_sm = 148, per_sm = 0;
+    CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, b->device));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pgsl<false>, 256, 0));
+    b->pgsl_grid = cdiv_host(2 * std::max(max_nb, 1), 256);
+    if (b->pgsl_grid > n_sm * per_sm) return fail(GZCUDA_E_INVALID, "world too large for one cooperative grid");
+    if ((rc = dev_alloc(b, &d.xch_g, (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid))) return rc;
+    if ((rc = dev_alloc(b, &d.bs_glob, (size_t)W * 5 * std::max(max_nb, 1)))) return rc;
+  }
+  if (d.pgs_impl >= 1) {
+    b->bsched_smem = (size_t)5 * std::max(max_nb, 1) * sizeof(int);
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
     const size_t per_ent = GZ_ENT * sizeof(double) + sizeof(int) + 3 * sizeof(double);
@@ -405,6 +423,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if ((rc = dev_alloc(b, &d.wkey, (size_t)W))) return rc;
     if ((rc = dev_alloc(b, &d.wperm, (size_t)W))) return rc;
     if ((rc = dev_alloc(b, &d.cls_ctr, (size_t)16))) return rc;
+  }
+  if (d.pgs_impl == 1) {
     int bp = 1;
     while (bp < max_nb) bp <<= 1;
     PgsbCfg &c = b->pgsb;
@@ -460,7 +480,6 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     }
     b->pgsb = b->pgsbc[0];
     b->pgsb_smem = b->pgsbc_smem[0];
-    b->bsched_smem = (size_t)5 * std::max(max_nb, 1) * sizeof(int);
     const int mx_smem = (int)mx_b;
     for (auto f : {k_pgsb<false, false>, k_pgsb<false, true>, k_pgsb<true, false>, k_pgsb<true, true>}) {
       if (mx_smem > 48 * 1024) CK(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, mx_smem));
@@ -486,8 +505,12 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
           CK(cudaFuncSetAttribute(k_broadphase, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->bp_smem));
       } else {
         d.bp_sap_min = 1 << 30;   // the largest world does not fit: every world takes the all-pairs path
+        b->bp_threads = 512;
       }
     }
+    if (b->bp_smem > (size_t)220 * 1024) return fail(GZCUDA_E_INVALID, "world has too many geoms for the broadphase's row counts");
+    if (b->bp_smem > 48 * 1024)
+      CK(cudaFuncSetAttribute(k_broadphase, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->bp_smem));
   }
 
   // PGS launch shape (k_pgs_sweep.cuh): one warp per CTA, a fixed shared-memory budget per CTA
@@ -622,7 +645,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_assemble1<<<W, T, 0, b->stream>>>(d);   // islands, body prologue, row counts
   // the joint rows (one thread per joint: a long dependent chain on few threads) run beside the contact rows and
   // the schedule, which do not depend on them; k_rowfinish needs all three
-  const bool fork_joint = d.nj > 0 && d.pgs_impl == 1;
+  const bool fork_joint = d.nj > 0 && d.pgs_impl >= 1;
   if (fork_joint) {
     cudaEventRecord(b->ev_aux_fork, b->stream);
     cudaStreamWaitEvent(b->stream_aux, b->ev_aux_fork, 0);
@@ -631,9 +654,9 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     b->last_launches++;
   } else if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(item_blocks(d.max_contact_cap, 32, W), W), 32, 0, b->stream>>>(d);
-  if (d.pgs_impl == 1) {
+  if (d.pgs_impl >= 1) {
     // body-owner sweeps: schedule (integer work on the row counts), row prologue + entries, sweeps
-    k_bsched<<<W, 128, b->bsched_smem, b->stream>>>(d);
+    k_bsched<<<W, 128, d.bs_glob ? 0 : b->bsched_smem, b->stream>>>(d);
     k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
     if (fork_joint) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
     if (d.p.dynamic_inertia && d.nj > 0) { k_dyn_inertia<<<cdiv(W, 64), 64, 0, b->stream>>>(d); b->last_launches++; }
@@ -641,7 +664,15 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     if (stage_events) cudaEventRecord(b->evs[2], b->stream);
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
     const bool box = d.p.friction_model == 2;
-    if (b->pgsb_multi) {
+    if (d.pgs_impl == 2) {
+      // large worlds: one cooperative launch per world (all CTAs resident, grid barrier per round)
+      for (int w = 0; w < W; w++) {
+        double *xch = d.xch_g, *partial = d.xch_g + (size_t)2 * b->pgsl_grid * 256;
+        void *args[] = {(void *)&d, (void *)&w, (void *)&xch, (void *)&partial};
+        cudaLaunchCooperativeKernel(box ? (void *)k_pgsl<true> : (void *)k_pgsl<false>, dim3(b->pgsl_grid), dim3(256), args, 0, b->stream);
+      }
+      b->last_launches += W - 1;
+    } else if (b->pgsb_multi) {
       if (box) k_pgsb<true, true><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
       else k_pgsb<true, false><<<b->pgsb_ctas, b->pgsb_threads, b->pgsb_smem, b->stream>>>(d, b->pgsb, 0);
     } else {

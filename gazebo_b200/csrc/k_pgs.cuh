@@ -498,8 +498,8 @@ __device__ __forceinline__ void rowfinish_one(DevBatch &B, const int w, const Wo
   else Ad = B.p.contact_sor_scale * B.p.sor_w / (d + cfm);
   r.Ad = Ad;
   r.lambda = lam; r.lambda_erp = lam_erp;
-  if (B.pgs_impl == 1) {
-    // body-owner sweeps (k_pgsb.cuh): one entry per body of the row, at the place k_bsched gave it
+  if (B.pgs_impl >= 1) {
+    // body-owner sweeps (k_pgsb.cuh, k_pgsl.cuh): one entry per body of the row, at the place k_bsched gave it
     const int nc = B.wstep[w].n_contacts, mj = B.wstep[w].m - 3 * nc;
     const WScratchB S = wscratchb(B, w);
     const int pos = order_pos(i, mj, nc);
@@ -580,6 +580,7 @@ __global__ void k_rowfinish(DevBatch B) {
 }  // namespace gz
 #include "k_pgs_sweep.cuh"
 #include "k_pgs_chain.cuh"
+#include "k_pgsl.cuh"
 namespace gz {
 
 // One thread per joint: save lambda for the next step's warm start.

@@ -77,7 +77,8 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
   const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc;
-  int *last = bs_sh, *first = bs_sh + B.max_nb, *cnt = bs_sh + 2 * B.max_nb, *fr0 = bs_sh + 3 * B.max_nb, *base = bs_sh + 4 * B.max_nb;
+  int *const tab = B.bs_glob ? B.bs_glob + (size_t)w * 5 * B.max_nb : bs_sh;   // (large worlds: the tables live in global memory)
+  int *last = tab, *first = tab + B.max_nb, *cnt = tab + 2 * B.max_nb, *fr0 = tab + 3 * B.max_nb, *base = tab + 4 * B.max_nb;
   __shared__ int s_R, s_maxoff, s_nent, s_wbase;
   const WScratchB G = wscratchb(B, w);
   // the serial pass below walks these arrays with dependent accesses: worlds of up to GZ_BS_SM rows keep them in

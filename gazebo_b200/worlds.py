@@ -204,3 +204,52 @@ def pioneer_worlds(n_worlds=1024, config=3, first_world=0, drive=False, torque=5
         cmds.append(cmd)
         sb.end_world()
     return sb.finish(), np.array(cmds)
+
+
+def rubble_world(n_bodies=20000, config=4, pen=None, auto_disable=False):
+    """C4: plane + 4 static wall boxes + n_bodies single-body models: 60 % boxes (half "2x4" planks 0.6-2.4 x 0.1016 x 0.0508 m,
+    half cinder blocks 0.2032 x 0.2032 x 0.4064 m as plugins/RubblePlugin.cc:71-91, scaled by 0.5), 25 % spheres r U(0.05, 0.15),
+    15 % capsules r U(0.04, 0.08), l U(0.1, 0.4); mass U(0.1, 1.0) kg; dropped in layers into a square pen (10 x 10 m at
+    20 000 bodies, the side scaled with sqrt(n) below that so the pile is as deep)."""
+    rng = np.random.Generator(np.random.PCG64(1000 * config))
+    if pen is None:
+        pen = 10.0 * math.sqrt(n_bodies / 20000.0)
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_ground_plane()
+    wall_h, wall_t = 2.0, 0.2
+    for sx, sy in ((1, 0), (-1, 0), (0, 1), (0, -1)):
+        size = (wall_t, pen + 2 * wall_t, wall_h) if sx else (pen + 2 * wall_t, wall_t, wall_h)
+        sb.add_geom(S.GEOM_BOX, size, sb.new_space(), pos=(sx * (pen + wall_t) / 2, sy * (pen + wall_t) / 2, wall_h / 2))
+    per_layer = max(1, int((pen / 0.45) ** 2))
+    side = int(math.ceil(math.sqrt(per_layer)))
+    flags = S.BODY_AUTO_DISABLE if auto_disable else 0
+    for k in range(n_bodies):
+        layer, cell = divmod(k, per_layer)
+        ix, iy = divmod(cell, side)
+        pos = [-pen / 2 + (ix + 0.5) * pen / side + rng.uniform(-0.05, 0.05),
+               -pen / 2 + (iy + 0.5) * pen / side + rng.uniform(-0.05, 0.05),
+               0.4 + 0.55 * layer + rng.uniform(0, 0.1)]
+        pos[0] = min(max(pos[0], -pen / 2 + 0.3), pen / 2 - 0.3)
+        pos[1] = min(max(pos[1], -pen / 2 + 0.3), pen / 2 - 0.3)
+        mass = rng.uniform(0.1, 1.0)
+        u = rng.uniform()
+        q = S.q_random(rng)
+        if u < 0.30:
+            dims = (0.5 * rng.uniform(0.6, 2.4) * 0.35, 0.5 * 0.1016, 0.5 * 0.0508)   # plank (length cut so it fits its cell)
+            b = sb.add_body(pos, q, mass, S.box_inertia(mass, *dims), flags=flags)
+            sb.add_geom(S.GEOM_BOX, dims, sb.new_space(), body=b)
+        elif u < 0.60:
+            dims = (0.5 * 0.2032, 0.5 * 0.2032, 0.5 * 0.4064)
+            b = sb.add_body(pos, q, mass, S.box_inertia(mass, *dims), flags=flags)
+            sb.add_geom(S.GEOM_BOX, dims, sb.new_space(), body=b)
+        elif u < 0.85:
+            r = rng.uniform(0.05, 0.15)
+            b = sb.add_body(pos, q, mass, S.sphere_inertia(mass, r), flags=flags)
+            sb.add_geom(S.GEOM_SPHERE, (r,), sb.new_space(), body=b)
+        else:
+            r, l = rng.uniform(0.04, 0.08), rng.uniform(0.1, 0.4)
+            b = sb.add_body(pos, q, mass, S.cylinder_inertia(mass, r, l), flags=flags)
+            sb.add_geom(S.GEOM_CAPSULE, (r, l), sb.new_space(), body=b)
+    sb.end_world()
+    return sb.finish()

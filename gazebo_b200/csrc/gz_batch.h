@@ -161,6 +161,9 @@ struct DevBatch {
   int bp_sap_min;        // geoms from which a world takes the sort-and-sweep broadphase (k_collide.cuh)
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   // ---- body-owner PGS (k_pgsb.cuh): per-body entry lists in a bump-allocated pool
+  int *ent_part;         // [ent_cap] the entry of the row's other body, -1 if none (k_pgsd only, else null)
+  int pgs_dataflow;      // large worlds: 1 = k_pgsd (dataflow, no rounds), 0 = k_pgsl (rounds with a grid barrier)
+  int *bs_clist;         // [2 * contacts] k_bsched_large's per-body contact lists (large worlds only, else null)
   int *bs_glob;          // [5][max_nb] k_bsched's per-body tables for worlds too large for shared memory (else null)
   double *xch_g;         // [2][lanes] k_pgsl: partial dot products of a round (double-buffered), then [grid][9] statistics partials
   int pgs_impl;          // 2: body-owner sweeps over a cooperative grid (k_pgsl, worlds of more than 512 bodies), 1: body-owner sweeps (k_pgsb), 0: the round-1 row-slot sweeps (k_pgs / k_pgs_chain)

@@ -13,6 +13,7 @@
 
 #include "../../include/gzcuda.h"
 #include "k_collide.cuh"
+#include "k_bpl.cuh"
 #include "k_pgs.cuh"
 
 using namespace gz;
@@ -59,7 +60,12 @@ struct gzcuda_batch {
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
   int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
+  bool bp_large = false;              // worlds too large for the one-CTA broadphase: k_bpl_* (sort, sweep, scan, emit)
+  BplBuf bpl = {};
   int pgsl_grid = 0;                  // CTAs of k_pgsl's cooperative grid
+  unsigned long long *pgsd_slots = nullptr;   // k_pgsd's exchange slots
+  unsigned long long pgsd_launches = 0;       // launches since the slots were last cleared (tags are 32 bits)
+  int bsl_grid = 0;                   // CTAs of k_bsched_large's cooperative grid
   PgsbCfg pgsbc[GZ_PGSB_NCLS];        // the shared-memory classes of the one-warp CTAs, ascending budgets
   size_t pgsbc_smem[GZ_PGSB_NCLS] = {};
   int pgsbc_grid[GZ_PGSB_NCLS] = {};         // persistent warps of each class: what the GPU can hold of them at once
@@ -391,10 +397,18 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     // one lane per (body, solve) of the largest world, all CTAs resident (cooperative launch)
     int n_sm = 148, per_sm = 0;
     CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, b->device));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pgsl<false>, 256, 0));
+    const char *eb = getenv("GZCUDA_PGSL_BARRIER");   // developer switch: the round-synchronous sweeps (k_pgsl) instead of the dataflow ones
+    d.pgs_dataflow = !(eb && atoi(eb) == 1);
+    if (d.pgs_dataflow) { CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pgsd<false>, 256, 0)); }
+    else CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pgsl<false>, 256, 0));
     b->pgsl_grid = cdiv_host(2 * std::max(max_nb, 1), 256);
+    int bsl_per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bsl_per_sm, k_bsched_large, 256, 0));
+    b->bsl_grid = std::max(1, std::min(n_sm * std::min(bsl_per_sm, 2), cdiv_host((int)std::max(row_tot, 1L), 256)));
     if (b->pgsl_grid > n_sm * per_sm) return fail(GZCUDA_E_INVALID, "world too large for one cooperative grid");
-    if ((rc = dev_alloc(b, &d.xch_g, (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid))) return rc;
+    if ((rc = dev_alloc(b, &d.xch_g, (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid + 8))) return rc;
+    CK(cudaMemset(d.xch_g, 0, ((size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid + 8) * sizeof(double)));
+    if ((rc = dev_alloc(b, &d.bs_clist, (size_t)2 * contact_tot + 2))) return rc;
     if ((rc = dev_alloc(b, &d.bs_glob, (size_t)W * 5 * std::max(max_nb, 1)))) return rc;
   }
   if (d.pgs_impl >= 1) {
@@ -416,6 +430,12 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if ((rc = dev_alloc(b, &d.ent_row, (size_t)d.ent_cap))) return rc;
     if ((rc = dev_alloc(b, &d.ent_ad2, (size_t)d.ent_cap))) return rc;
     if ((rc = dev_alloc(b, &d.ent_dl, (size_t)2 * d.ent_cap))) return rc;
+    if (d.pgs_impl == 2 && d.pgs_dataflow) {
+      // k_pgsd: partner entries, and per entry 2 solves x 2 sweep parities x 16-byte slots (tag 0 = never written)
+      if ((rc = dev_alloc(b, &d.ent_part, (size_t)d.ent_cap))) return rc;
+      if ((rc = dev_alloc(b, &b->pgsd_slots, (size_t)8 * d.ent_cap))) return rc;
+      CK(cudaMemset(b->pgsd_slots, 0, (size_t)8 * d.ent_cap * sizeof(unsigned long long)));
+    }
     if ((rc = dev_alloc(b, &d.ent_cursor, (size_t)2))) return rc;
     if ((rc = dev_alloc(b, &d.bsched, (size_t)nb))) return rc;
     if ((rc = dev_alloc(b, &d.wsb, (size_t)W))) return rc;
@@ -498,14 +518,24 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       size_t npad = 32;
       while (npad < (size_t)max_ng) npad <<= 1;
       const size_t need = npad * 20 + ((size_t)max_ng + 1) * 4 + (size_t)max_ng * (((size_t)max_ng + 31) / 32) * 4 + 16;
-      if (need <= (size_t)220 * 1024) {
+      const bool force_large = getenv("GZCUDA_BP_LARGE") && atoi(getenv("GZCUDA_BP_LARGE")) != 0;   // test hook
+      if (need <= (size_t)220 * 1024 && !force_large) {
         b->bp_smem = std::max(b->bp_smem, need);
         b->bp_threads = 512;
         if (b->bp_smem > 48 * 1024)
           CK(cudaFuncSetAttribute(k_broadphase, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->bp_smem));
       } else {
-        d.bp_sap_min = 1 << 30;   // the largest world does not fit: every world takes the all-pairs path
-        b->bp_threads = 512;
+        // the largest world does not fit one CTA's shared memory: the multi-CTA broadphase (k_bpl.cuh) for every world
+        b->bp_large = true;
+        BplBuf &Q = b->bpl;
+        Q.npad = (int)npad;
+        if ((rc = dev_alloc(b, &Q.key, npad))) return rc;
+        if ((rc = dev_alloc(b, &Q.maxx, (size_t)max_ng))) return rc;
+        if ((rc = dev_alloc(b, &Q.idx, npad))) return rc;
+        if ((rc = dev_alloc(b, &Q.cnt, (size_t)max_ng + 1))) return rc;
+        if ((rc = dev_alloc(b, &Q.fill, (size_t)max_ng))) return rc;
+        if ((rc = dev_alloc(b, &Q.tmp, (size_t)std::max(max_pc, 1)))) return rc;
+        b->bp_smem = 16;
       }
     }
     if (b->bp_smem > (size_t)220 * 1024) return fail(GZCUDA_E_INVALID, "world has too many geoms for the broadphase's row counts");
@@ -513,6 +543,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       CK(cudaFuncSetAttribute(k_broadphase, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->bp_smem));
   }
 
+  if (d.pgs_impl != 0) return 0;   // what follows configures round 1's row-slot kernels (worlds of 257..512 bodies)
   // PGS launch shape (k_pgs_sweep.cuh): one warp per CTA, a fixed shared-memory budget per CTA
   // that holds the accumulators of its worlds, their lambdas and as many row records as fit.
   d.sch_rcap = std::min(GZ_RMAX, 2 * std::max(max_rc, 1) + 64);
@@ -631,10 +662,20 @@ static int launch_collision(gzcuda_batch *b) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
   k_geom<<<cdiv(std::max(d.ng, 1), T), T, 0, b->stream>>>(d);
-  k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
+  if (b->bp_large) {
+    for (int w = 0; w < W; w++) {   // large worlds come one or a few per batch
+      const int nwarps = std::max(1, b->h_world[w].ng), blocks = std::min(cdiv(nwarps, 8), 148 * 8);
+      k_bpl_sort<<<1, 1024, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_sweep<0><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_scan<<<1, 1024, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_sweep<1><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_emit<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+    }
+    b->last_launches += 5 * W - 1;
+  } else k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
   if (b->has_cylinders) k_narrow<true><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
   else k_narrow<false><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
-  k_contacts<<<W, T, 0, b->stream>>>(d);
+  k_contacts<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // (one CTA per world: a large world gets the largest CTA)
   b->last_launches += 4;
   return 0;
 }
@@ -642,7 +683,7 @@ static int launch_collision(gzcuda_batch *b) {
 static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
-  k_assemble1<<<W, T, 0, b->stream>>>(d);   // islands, body prologue, row counts
+  k_assemble1<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // islands, body prologue, row counts
   // the joint rows (one thread per joint: a long dependent chain on few threads) run beside the contact rows and
   // the schedule, which do not depend on them; k_rowfinish needs all three
   const bool fork_joint = d.nj > 0 && d.pgs_impl >= 1;
@@ -656,7 +697,16 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   k_rows_contact<<<dim3(item_blocks(d.max_contact_cap, 32, W), W), 32, 0, b->stream>>>(d);
   if (d.pgs_impl >= 1) {
     // body-owner sweeps: schedule (integer work on the row counts), row prologue + entries, sweeps
-    k_bsched<<<W, 128, d.bs_glob ? 0 : b->bsched_smem, b->stream>>>(d);
+    if (d.pgs_impl == 2) {
+      for (int w = 0; w < W; w++) {
+        unsigned *bar = reinterpret_cast<unsigned *>(d.xch_g + (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid);
+        int relax = d.pgs_dataflow ? 0 : 1;   // round offsets are only needed by the round-synchronous sweeps
+        void *args[] = {(void *)&d, (void *)&w, (void *)&bar, (void *)&relax};
+        cudaLaunchCooperativeKernel((void *)k_bsched_large, dim3(b->bsl_grid), dim3(256), args, 0, b->stream);
+      }
+      b->last_launches += W - 1;
+    } else
+      k_bsched<<<W, 128, d.bs_glob ? 0 : b->bsched_smem, b->stream>>>(d);
     k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
     if (fork_joint) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
     if (d.p.dynamic_inertia && d.nj > 0) { k_dyn_inertia<<<cdiv(W, 64), 64, 0, b->stream>>>(d); b->last_launches++; }
@@ -666,9 +716,22 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     const bool box = d.p.friction_model == 2;
     if (d.pgs_impl == 2) {
       // large worlds: one cooperative launch per world (all CTAs resident, grid barrier per round)
-      for (int w = 0; w < W; w++) {
+      for (int w = 0; w < W && d.pgs_dataflow; w++) {
+        double *partial = d.xch_g + (size_t)2 * b->pgsl_grid * 256;
+        unsigned *epoch = reinterpret_cast<unsigned *>(d.xch_g + (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid) + 8;
+        // 32-bit tags: long before they could repeat, clear the slots and start the epochs again
+        if ((++b->pgsd_launches + 2) * (unsigned long long)(d.p.iters + d.p.friction_iters + 1) >= 0xFFFFFFFFull) {
+          cudaMemsetAsync(b->pgsd_slots, 0, (size_t)8 * d.ent_cap * sizeof(unsigned long long), b->stream);
+          cudaMemsetAsync(epoch, 0, sizeof(unsigned), b->stream);
+          b->pgsd_launches = 1;
+        }
+        void *args[] = {(void *)&d, (void *)&w, (void *)&b->pgsd_slots, (void *)&partial, (void *)&epoch};
+        cudaLaunchCooperativeKernel(box ? (void *)k_pgsd<true> : (void *)k_pgsd<false>, dim3(b->pgsl_grid), dim3(256), args, 0, b->stream);
+      }
+      for (int w = 0; w < W && !d.pgs_dataflow; w++) {
         double *xch = d.xch_g, *partial = d.xch_g + (size_t)2 * b->pgsl_grid * 256;
-        void *args[] = {(void *)&d, (void *)&w, (void *)&xch, (void *)&partial};
+        unsigned *bar = reinterpret_cast<unsigned *>(d.xch_g + (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid);
+        void *args[] = {(void *)&d, (void *)&w, (void *)&xch, (void *)&partial, (void *)&bar};
         cudaLaunchCooperativeKernel(box ? (void *)k_pgsl<true> : (void *)k_pgsl<false>, dim3(b->pgsl_grid), dim3(256), args, 0, b->stream);
       }
       b->last_launches += W - 1;

@@ -515,8 +515,10 @@ __device__ __forceinline__ void rowfinish_one(DevBatch &B, const int w, const Wo
     double Ad2 = 0.0;   // quickstep_pgs_lcp.cpp:745-752
     if (!dequal(Ad, 0.0)) Ad2 = 1.0 / (Ad * Ad);
     const double rhsA = rhs * Ad, rhsA_erp = rhs_erp * Ad, adcfm = Ad * cfm;
+    const int ent1 = B.bsched[wi.body0 + r.b1].x + S.idx1[pos], ent2 = r.b2 >= 0 ? B.bsched[wi.body0 + r.b2].x + S.idx2[pos] : -1;
     for (int h = 0; h < (r.b2 >= 0 ? 2 : 1); h++) {
-      const int e = B.bsched[wi.body0 + (h ? r.b2 : r.b1)].x + (h ? S.idx2[pos] : S.idx1[pos]);
+      const int e = h ? ent2 : ent1;
+      if (B.ent_part) B.ent_part[e] = h ? ent1 : ent2;
       double2 *e2 = reinterpret_cast<double2 *>(B.ent + (size_t)e * GZ_ENT);
       for (int j = 0; j < 3; j++) {
         e2[j] = make_double2(J[6 * h + 2 * j] * Ad, J[6 * h + 2 * j + 1] * Ad);

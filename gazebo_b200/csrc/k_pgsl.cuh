@@ -373,21 +373,22 @@ namespace gz {
 // ---- k_pgsd: the sweeps of a large world as DATAFLOW.  Same lanes, entries and arithmetic as k_pgsl, but no rounds and
 // no grid barrier: a lane walks its body's entry list at its own pace and meets another lane only at a two-body row,
 // where each publishes its half of the dot product in the row's slot and polls the partner's.  A slot carries value and
-// tag in two 8-byte words {32 bits of the double, tag} written by one 16-byte volatile store: each word is atomic, so a
+// tag in two 8-byte words {32 bits of the double, tag} written by one 16-byte store (relaxed, GPU scope): each word is atomic, so a
 // reader that finds the tag in both has the value (no fence, no second trip).  tag = epoch * (sweeps + 1) + sweep + 1,
 // the epoch counted on the device per launch; slots are double-buffered by the sweep's parity: a lane can only publish
 // sweep s + 2 of a row after its partner has published s + 1, i.e. has consumed s.
-// Progress: the grid is launched cooperatively (all lanes resident), a poll never blocks, and the rows a lane waits on
-// precede its own in order[] (a total order), so some lane can always advance.  The result does not depend on timing:
+// Progress: the grid is launched cooperatively (all lanes resident), a warp only spins while NONE of its lanes can
+// advance (so no lane waits on a lane of its own warp that is held at a reconvergence point), and the rows a lane
+// waits on precede its own in order[] (a total order), so some lane of the grid can always advance.  The result does not depend on timing:
 // every row still sees exactly the accumulators the serial sweep would give it.
 __device__ __forceinline__ void slot_put(unsigned long long *s, double v, unsigned tag) {
   const unsigned long long t = (unsigned long long)tag << 32;
   const unsigned long long w0 = t | (unsigned)__double2loint(v), w1 = t | (unsigned)__double2hiint(v);
-  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(s), "l"(w0), "l"(w1) : "memory");
+  asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(s), "l"(w0), "l"(w1) : "memory");
 }
 __device__ __forceinline__ bool slot_get(const unsigned long long *s, unsigned tag, double &v) {
   unsigned long long w0, w1;
-  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(s) : "memory");
+  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(s) : "memory");
   v = __hiloint2double((int)(unsigned)w1, (int)(unsigned)w0);
   return (unsigned)(w0 >> 32) == tag && (unsigned)(w1 >> 32) == tag;
 }
@@ -421,59 +422,94 @@ __global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned 
   const double smooth = B.p.smooth_contacts, smooth1 = 1.0 - smooth;
   const unsigned tag0 = epoch * (unsigned)(total + 1) + 1u;
   int i = (iters > 0) ? 0 : fric0, sweep = 0;
-  bool alive = i < cnt && total > 0, have = false;
-  double J[6], iM[6], d = 0.0, rhs = 0, old_lambda = 0, adcfm = 0, lo = 0, hi = 0, nlam = 1.0;
-  int mx = 0, pe = -1;
-  double *p = lp;
-  while (alive) {
-    if (!have) {
-      p = lp + (size_t)i * GZ_ENT;
-      const double2 *p2 = reinterpret_cast<const double2 *>(p);
-      double2 v[10];
+  bool alive = i < cnt && total > 0;
+  // The row in flight: what finishing it needs (everything that does not wait for the partner is computed when the
+  // row is loaded), and the NEXT row's Jacobian half and partner, loaded ahead: from the partner's value to this lane's
+  // next publication there are only the clamp, the accumulator update and the next dot product.
+  double iM[6] = {0, 0, 0, 0, 0, 0}, Jn[6] = {0, 0, 0, 0, 0, 0};
+  double d = 0.0, delta0 = 0, old_lambda = 0, lo_act = 0, hi_act = 0;
+  int cls = 0, pe = -1, pen = -1, ni = 0, nsweep = 0;
+  bool isb2 = false, has_next = false;
+  auto load_J = [&](int q) {   // Jacobian half (x Ad) and partner entry of list place q
+    const double2 *p2 = reinterpret_cast<const double2 *>(lp + (size_t)q * GZ_ENT);
+    const double2 v0 = p2[0], v1 = p2[1], v2 = p2[2];
+    pen = part[q];
+    Jn[0] = v0.x; Jn[1] = v0.y; Jn[2] = v1.x; Jn[3] = v1.y; Jn[4] = v2.x; Jn[5] = v2.y;
+  };
+  auto load_rest = [&](int q) {   // the rest of the row at list place q, and where the lane goes after it
+    const double *p = lp + (size_t)q * GZ_ENT;
+    const double2 *p2 = reinterpret_cast<const double2 *>(p);
+    const double2 v3 = p2[3], v4 = p2[4], v5 = p2[5], vs = p2[6 + S], v8 = p2[8], v9 = p2[9];
+    iM[0] = v3.x; iM[1] = v3.y; iM[2] = v4.x; iM[3] = v4.y; iM[4] = v5.x; iM[5] = v5.y;
+    const int mx = __double2loint(v9.y), my = __double2hiint(v9.y);
+    cls = (mx >> 27) & 3; isb2 = (mx >> 29) & 1;
+    // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594)
+    double nlam = 1.0;
+    if (!BOX && cls == 2) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_ENT)[13 + 2 * S];
+    old_lambda = vs.y;
+    delta0 = vs.x - old_lambda * v8.x;
+    const double hl = v9.x * nlam;
+    const double hf = fabs(hl);
+    hi_act = cls == 2 ? hf : v9.x; lo_act = cls == 2 ? -hf : v8.y;
+    ni = q + 1; nsweep = sweep;
+    if (ni == cnt) { nsweep = sweep + 1; ni = nsweep < iters ? 0 : fric0; }
+    has_next = nsweep < total && ni < cnt;
+    if (has_next) load_J(ni);
+  };
+  if (alive) {
+    load_J(i);
+    d = a[0] * Jn[0];
 #pragma unroll
-      for (int k = 0; k < 10; k++) v[k] = (k == 6 || k == 7) ? (k == 6 + S ? p2[k] : make_double2(0.0, 0.0)) : p2[k];
-      pe = part[i];
-#pragma unroll
-      for (int k = 0; k < 3; k++) { J[2 * k] = v[k].x; J[2 * k + 1] = v[k].y; iM[2 * k] = v[3 + k].x; iM[2 * k + 1] = v[3 + k].y; }
-      rhs = v[6 + S].x; old_lambda = v[6 + S].y; adcfm = v[8].x; lo = v[8].y; hi = v[9].x;
-      mx = __double2loint(v[9].y);
-      const int my = __double2hiint(v[9].y);
-      nlam = 1.0;
-      if (!BOX && ((mx >> 27) & 3) == 2) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_ENT)[13 + 2 * S];
-      d = a[0] * J[0];
-#pragma unroll
-      for (int t = 1; t < 6; t++) d += a[t] * J[t];
-      if (pe >= 0) slot_put(slots + 2 * (((size_t)(e0 + i) * 2 + S) * 2 + (sweep & 1)), d, tag0 + (unsigned)sweep);
-      have = true;
-    }
+    for (int t = 1; t < 6; t++) d += a[t] * Jn[t];
+    pe = pen;
+    if (pe >= 0) slot_put(slots + 2 * (((size_t)(e0 + i) * 2 + S) * 2 + (sweep & 1)), d, tag0 + (unsigned)sweep);
+    load_rest(i);
+  }
+  // The warp stays together: ALL its lanes poll back to back until some lane can finish its row (a waiting lane's
+  // poll interval is one L2 trip, not one pass of its neighbours through the row code), then those lanes finish.
+  int n_outer = 0, n_spin = 0;   // developer counters: passes of this warp through the row code, polls
+  const long long t_begin = clock64();
+  while (__any_sync(0xffffffffu, alive)) {
     double pd = 0.0;
-    bool ready = true;
-    if (pe >= 0) ready = slot_get(slots + 2 * (((size_t)pe * 2 + S) * 2 + (sweep & 1)), tag0 + (unsigned)sweep, pd);
+    bool ready;
+    n_outer++;
+    do {
+      n_spin++;
+      ready = alive;
+      if (alive && pe >= 0) ready = slot_get(slots + 2 * (((size_t)pe * 2 + S) * 2 + (sweep & 1)), tag0 + (unsigned)sweep, pd);
+    } while (!__any_sync(0xffffffffu, ready));
     if (ready) {
-      const int cls = (mx >> 27) & 3;
-      const bool fric = cls == 2, isb2 = (mx >> 29) & 1, two = pe >= 0;
-      double delta = rhs - old_lambda * adcfm;
+      // this body's half and the partner's, subtracted in the row's body order (body 1 first)
+      double delta = delta0;
       const double d1 = isb2 ? pd : d, d2 = isb2 ? d : pd;
       delta -= d1;
       const double delta2 = delta - d2;
-      delta = two ? delta2 : delta;
-      const double hl = hi * nlam;
-      const double hf = fabs(hl);
-      const double hi_act = fric ? hf : hi, lo_act = fric ? -hf : lo;
+      delta = pe >= 0 ? delta2 : delta;
       double nl = old_lambda + delta;
       const double dlo = lo_act - old_lambda, dhi = hi_act - old_lambda;
       const bool below = nl < lo_act, above = !below && nl > hi_act;
       delta = below ? dlo : (above ? dhi : delta);
       nl = below ? lo_act : (above ? hi_act : nl);
-      const double sm = smooth1 * nl + smooth * old_lambda;
-      p[13 + 2 * S] = (S == 0 && cls != 0) ? sm : nl;
-      dl[2 * (size_t)i] = delta;
 #pragma unroll
       for (int t = 0; t < 6; t++) a[t] += delta * iM[t];
-      have = false;
-      if (++i == cnt) { sweep++; i = sweep < iters ? 0 : fric0; }
-      alive = sweep < total && i < cnt;
+      double dn = 0.0;
+      if (has_next) {   // the next row's half goes out before anything else
+        dn = a[0] * Jn[0];
+#pragma unroll
+        for (int t = 1; t < 6; t++) dn += a[t] * Jn[t];
+        if (pen >= 0) slot_put(slots + 2 * (((size_t)(e0 + ni) * 2 + S) * 2 + (nsweep & 1)), dn, tag0 + (unsigned)nsweep);
+      }
+      // SMOOTH_LAMBDA on the lambda solve of non-bilateral rows; delta is not recomputed after it (:687-691 vs :706)
+      const double sm = smooth1 * nl + smooth * old_lambda;
+      lp[(size_t)i * GZ_ENT + 13 + 2 * S] = (S == 0 && cls != 0) ? sm : nl;
+      dl[2 * (size_t)i] = delta;
+      i = ni; sweep = nsweep; alive = has_next; d = dn; pe = pen;
+      if (alive) load_rest(i);
     }
+  }
+  if ((threadIdx.x & 31) == 0) {   // gzcuda_batch_get_pgs_debug: the longest warp's passes, polls, cycles / 16
+    WorldStep &wsd = B.wstep[w];
+    atomicMax(&wsd.pad[0], n_outer); atomicMax(&wsd.pad[1], n_spin); atomicMax(&wsd.n_fric, (int)((clock64() - t_begin) >> 4));
   }
   if (bl < wi.nb) {
     BodyStep &bs = B.bstep[wi.body0 + bl];
@@ -525,7 +561,6 @@ __global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned 
     ws.rms_dlambda[3] = sqrt(sa > 0 ? sa / tot : 0.0);
     ws.rms_residual[3] = sqrt(se > 0 ? se / tot : 0.0);
     ws.num_contacts_stat = (int)t[7];
-    ws.pad[0] = 0; ws.pad[1] = 0;
   }
 }
 

@@ -1,19 +1,22 @@
-"""Developer check (GPU box): BASELINE.json configs[0] (500 boxes on a plane, one world) — GPU vs CPU reference."""
-import sys, time; sys.path.insert(0, "/root/repo")
+"""Developer run (GPU box): C1 (500 boxes dropped on the plane, one world) time per step for each PGS implementation
+(GZCUDA_PGS_IMPL in the environment), with parity against the reference's opende when REF=1."""
+import os, sys, time; sys.path.insert(0, "/root/repo")
 import numpy as np
 from gazebo_b200 import scene as S, worlds as W
 from gazebo_b200.batch import Batch
-from oracle.refharness import RefBatch
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 500
-sc = W.box_drop_worlds(1, n)
+from oracle import refharness
+nbox = int(os.environ.get("N", "500")); steps = int(os.environ.get("STEPS", "1500")); chk = int(os.environ.get("CHK", "500"))
+sc = W.box_drop_worlds(1, nbox, auto_disable=os.environ.get("AUTO_DISABLE", "1") == "1")
 p = S.default_params()
 g = Batch(sc, p)
-r = RefBatch(sc, p, mode=1)
-for k in range(6):
-    t0 = time.perf_counter(); g.step(250); g.sync(); tg = time.perf_counter() - t0
-    t0 = time.perf_counter(); r.step(250); tr = time.perf_counter() - t0
-    gs, rs = g.body_state(), r.body_state()
-    d = [np.abs(a - b).max() for a, b in zip(gs, rs)]
+r = refharness.RefBatch(sc, p, mode=1) if os.environ.get("REF", "0") == "1" else None
+for k in range(0, steps, chk):
+    t = time.perf_counter(); g.step(chk); g.sync(); tg = (time.perf_counter() - t) / chk
     rms, nc, m = g.stats()
-    print("step %4d rows %5d contacts %5d | gpu %.2f ms/step, cpu(canonical, 1 thread) %.2f ms/step | dpos %.2e dq %.2e | stage ms %s" % (
-        250 * (k + 1), m[0], nc[0], 1e3 * tg / 250, 1e3 * tr / 250, d[0], d[1], ["%.3f" % x for x in g.stage_ms()]), flush=True)
+    line = "impl %s step %4d: gpu %.3f ms/step stages %s rows %d contacts %d" % (os.environ.get("GZCUDA_PGS_IMPL", "-"), k + chk, tg * 1e3, ["%.2f" % x for x in g.stage_ms()], m[0], nc[0])
+    if r is not None:
+        t = time.perf_counter(); r.step(chk); tr = (time.perf_counter() - t) / chk
+        gs, rs = g.body_state(), r.body_state()
+        line += " | cpu %.2f ms/step | max |dpos| %.2e |dq| %.2e pairs equal %s" % (tr * 1e3, np.abs(gs[0] - rs[0]).max(), np.abs(gs[1] - rs[1]).max(), np.array_equal(g.pairs(0), r.pairs(0)))
+    line += " | pgs debug %s" % (g.pgs_debug()[0].tolist(),)
+    print(line, flush=True)

@@ -18,4 +18,5 @@ for k in range(0, steps, chk):
         t = time.perf_counter(); r.step(chk); tr = (time.perf_counter() - t) / chk
         gs, rs = g.body_state(), r.body_state()
         line += " | cpu %.2f ms/step | max |dpos| %.2e |dq| %.2e pairs equal %s" % (tr * 1e3, np.abs(gs[0] - rs[0]).max(), np.abs(gs[1] - rs[1]).max(), np.array_equal(g.pairs(0), r.pairs(0)))
+    line += " | pgs debug %s" % (g.pgs_debug()[0].tolist(),)
     print(line, flush=True)

@@ -18,7 +18,9 @@
 #define GZ_NBUCKET (10 * GZ_NRUNG)
 #define GZ_PAIR_MAXC 16  // contacts one geom pair can yield (box-box: 8, cylinder-box: up to 13)
 #define GZ_PGSB_NKEY 512   // period histogram of k_border: periods >= 511 share the last key
-#define GZ_ENT 20          // doubles per body-owner PGS entry (k_pgsb.cuh)
+#define GZ_ENT 20
+#define GZ_PGSC_MAXCTA 1280  // k_pgsc: CTAs of one world; worlds beyond fall back to k_pgsd
+#define GZ_PGSC_TAB (GZ_PGSC_MAXCTA + 9)          // doubles per body-owner PGS entry (k_pgsb.cuh)
 #define GZ_CHAIN_NCLS 4   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
 
 namespace gz {
@@ -161,8 +163,14 @@ struct DevBatch {
   int bp_sap_min;        // geoms from which a world takes the sort-and-sweep broadphase (k_collide.cuh)
   unsigned long long *acc;   // [4] running totals: rows, friction rows, contacts, world-steps
   // ---- body-owner PGS (k_pgsb.cuh): per-body entry lists in a bump-allocated pool
+  int4 *ent_aux;         // [ent_cap] {entry of the row's other body or -1, that body, entries back to the normal row, class} (k_pgsc only, else null)
   int *ent_part;         // [ent_cap] the entry of the row's other body, -1 if none (k_pgsd only, else null)
+  int islands_hook;      // islands by hooking + pointer jumping (large worlds) instead of min-label propagation
   int pgs_dataflow;      // large worlds: 1 = k_pgsd (dataflow, no rounds), 0 = k_pgsl (rounds with a grid barrier)
+  int pgsc_bodies;       // k_pgsc: bodies per CTA = warps per CTA x pgsc_bpw
+  int pgsc_bpw;          // k_pgsc: bodies per warp (<= 16; the other lanes of the warp idle: a warp is ONE instruction stream
+                         // that runs its bodies' rows one after the other, so fewer bodies per warp = more streams)
+  int *cta_e0;           // [n_worlds][GZ_PGSC_TAB] first entry of every CTA of k_pgsc (then the world's end), else null
   int *bs_clist;         // [2 * contacts] k_bsched_large's per-body contact lists (large worlds only, else null)
   int *bs_glob;          // [5][max_nb] k_bsched's per-body tables for worlds too large for shared memory (else null)
   double *xch_g;         // [2][lanes] k_pgsl: partial dot products of a round (double-buffered), then [grid][9] statistics partials

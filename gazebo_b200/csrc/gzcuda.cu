@@ -65,6 +65,9 @@ struct gzcuda_batch {
   int pgsl_grid = 0;                  // CTAs of k_pgsl's cooperative grid
   unsigned long long *pgsd_slots = nullptr;   // k_pgsd's exchange slots
   unsigned long long pgsd_launches = 0;       // launches since the slots were last cleared (tags are 32 bits)
+  int pgs_large_mode = 1;             // large worlds: 0 k_pgsl (rounds + grid barrier), 1 k_pgsd (dataflow through L2), 2 k_pgsc (+ cluster shared memory)
+  int pgsc_grid = 0, pgsc_cluster = 1, pgsc_glob_every = 4, pgsc_sleep = 0;
+  size_t pgsc_smem = 0;
   int bsl_grid = 0;                   // CTAs of k_bsched_large's cooperative grid
   PgsbCfg pgsbc[GZ_PGSB_NCLS];        // the shared-memory classes of the one-warp CTAs, ascending budgets
   size_t pgsbc_smem[GZ_PGSB_NCLS] = {};
@@ -385,9 +388,11 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   // Body-owner PGS (k_pgsb.cuh): the default for worlds of up to 256 bodies.  Entry pool: a row has one entry
   // per body, so 2 x rows is the worst case; clamped to a quarter of the free memory (k_bsched flags a step
   // that does not fit).
-  // <= 256 bodies: k_pgsb (warp or CTA per world); <= 512: round 1's row-slot kernels (a world's accumulators in one
-  // CTA's shared memory); beyond: k_pgsl, the body-owner sweeps over a cooperative grid
-  d.pgs_impl = (max_nb <= 256) ? 1 : (max_nb <= 512 ? 0 : 2);
+  // <= 256 bodies: k_pgsb (warp or CTA per world); beyond: the body-owner sweeps over the whole GPU (k_pgsd: dataflow
+  // through L2 slots).  Round 1's row-slot kernels (worlds up to 512 bodies) remain behind GZCUDA_PGS_IMPL=0.
+  d.pgs_impl = (max_nb <= 256) ? 1 : 2;
+  d.islands_hook = max_nb > 512;
+  if (const char *e = getenv("GZCUDA_ISLANDS_HOOK")) d.islands_hook = atoi(e) != 0;   // developer / test switch
   if (const char *e = getenv("GZCUDA_PGS_IMPL")) {
     const int v = atoi(e);
     if (v == 0 && max_nb <= 512) d.pgs_impl = 0;
@@ -397,8 +402,12 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     // one lane per (body, solve) of the largest world, all CTAs resident (cooperative launch)
     int n_sm = 148, per_sm = 0;
     CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, b->device));
-    const char *eb = getenv("GZCUDA_PGSL_BARRIER");   // developer switch: the round-synchronous sweeps (k_pgsl) instead of the dataflow ones
-    d.pgs_dataflow = !(eb && atoi(eb) == 1);
+    // developer switches: GZCUDA_PGSL_MODE = 0 round-synchronous sweeps (k_pgsl), 1 dataflow through L2 (k_pgsd, the
+    // default), 2 dataflow with inboxes in cluster shared memory (k_pgsc: measured, not faster - DESIGN.md §4)
+    b->pgs_large_mode = 1;
+    if (const char *em = getenv("GZCUDA_PGSL_MODE")) b->pgs_large_mode = std::max(0, std::min(2, atoi(em)));
+    if (const char *eb = getenv("GZCUDA_PGSL_BARRIER")) if (atoi(eb) == 1) b->pgs_large_mode = 0;
+    d.pgs_dataflow = b->pgs_large_mode >= 1;
     if (d.pgs_dataflow) { CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pgsd<false>, 256, 0)); }
     else CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pgsl<false>, 256, 0));
     b->pgsl_grid = cdiv_host(2 * std::max(max_nb, 1), 256);
@@ -435,6 +444,52 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       if ((rc = dev_alloc(b, &d.ent_part, (size_t)d.ent_cap))) return rc;
       if ((rc = dev_alloc(b, &b->pgsd_slots, (size_t)8 * d.ent_cap))) return rc;
       CK(cudaMemset(b->pgsd_slots, 0, (size_t)8 * d.ent_cap * sizeof(unsigned long long)));
+    }
+    if (d.pgs_impl == 2 && b->pgs_large_mode == 2) {
+      // k_pgsc: CTAs of 8 warps, pgsc_bpw bodies per warp - as few as the resident warps allow (two CTAs of 256
+      // threads per SM at ~120 registers): a warp is one instruction stream for all its bodies' rows; clusters of 8
+      // CTAs (developer switch: 16); inboxes of 64 bytes per entry in shared memory; every cluster must be resident,
+      // else the L2 dataflow kernel takes the world
+      int n_sm = 148;
+      CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, b->device));
+      const int warps_res = n_sm * 2 * 8 * 7 / 8;   // (clusters do not pack every SM: leave an eighth)
+      int bpw = 1;
+      while (bpw < 16 && cdiv_host(std::max(max_nb, 1), bpw) > warps_res) bpw++;
+      if (const char *eb = getenv("GZCUDA_PGSC_BPW")) bpw = std::max(1, std::min(16, atoi(eb)));
+      d.pgsc_bpw = bpw;
+      d.pgsc_bodies = 8 * bpw;
+      const int ncta = cdiv_host(std::max(max_nb, 1), d.pgsc_bodies);
+      int clmax = 8;
+      if (const char *ec = getenv("GZCUDA_PGSC_CLUSTER")) { const int v = atoi(ec); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) clmax = v; }
+      int cl = 1;
+      while (cl < clmax && cl < ncta) cl <<= 1;
+      b->pgsc_cluster = cl;
+      b->pgsc_grid = cdiv_host(ncta, cl) * cl;
+      const size_t smem_max = ncta <= n_sm ? (size_t)192 * 1024 : (size_t)100 * 1024;   // one or two CTAs per SM
+      b->pgsc_smem = std::min(smem_max, (((size_t)64 * d.ent_cap + 1023) / 1024) * 1024);
+      if (const char *eg = getenv("GZCUDA_PGSC_GLOB_EVERY")) { int v = std::max(1, atoi(eg)), p2 = 1; while (p2 < v) p2 <<= 1; b->pgsc_glob_every = p2; }
+      if (const char *es = getenv("GZCUDA_PGSC_SLEEP")) b->pgsc_sleep = std::max(0, atoi(es));
+      bool ok = b->pgsc_grid <= GZ_PGSC_MAXCTA + 8;
+      for (int v = 0; v < 2 && ok; v++) {
+        const void *fn = v ? (const void *)k_pgsc<true> : (const void *)k_pgsc<false>;
+        ok = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgsc_smem) == cudaSuccess;
+        if (ok && cl > 8) ok = cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+        if (!ok) break;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(b->pgsc_grid); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = b->pgsc_smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int n_clusters = 0;
+        ok = cudaOccupancyMaxActiveClusters(&n_clusters, fn, &cfg) == cudaSuccess && n_clusters * cl >= b->pgsc_grid;
+      }
+      cudaGetLastError();
+      if (!ok) b->pgs_large_mode = 1;
+      else {
+        if ((rc = dev_alloc(b, &d.cta_e0, (size_t)W * GZ_PGSC_TAB))) return rc;
+        if ((rc = dev_alloc(b, &d.ent_aux, (size_t)d.ent_cap))) return rc;
+      }
     }
     if ((rc = dev_alloc(b, &d.ent_cursor, (size_t)2))) return rc;
     if ((rc = dev_alloc(b, &d.bsched, (size_t)nb))) return rc;
@@ -528,13 +583,23 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         // the largest world does not fit one CTA's shared memory: the multi-CTA broadphase (k_bpl.cuh) for every world
         b->bp_large = true;
         BplBuf &Q = b->bpl;
-        Q.npad = (int)npad;
-        if ((rc = dev_alloc(b, &Q.key, npad))) return rc;
+        const size_t nt = ((size_t)max_ng + 1 + GZ_BPL_TILE - 1) / GZ_BPL_TILE * GZ_BPL_TILE;   // whole tiles, at least one padding element
+        const size_t nwords = ((size_t)max_ng + 31) / 32 + 1;
+        Q.npad = (int)nt;
+        Q.chunks = GZ_BPL_CHUNKS; Q.big = GZ_BPL_BIG;
+        if (const char *e = getenv("GZCUDA_BPL_CHUNKS")) Q.chunks = std::max(1, atoi(e));   // developer / test switches
+        if (const char *e = getenv("GZCUDA_BPL_BIG")) Q.big = std::max(1, atoi(e));
+        if ((rc = dev_alloc(b, &Q.key, nt))) return rc;
+        if ((rc = dev_alloc(b, &Q.tkey, nt))) return rc;
         if ((rc = dev_alloc(b, &Q.maxx, (size_t)max_ng))) return rc;
-        if ((rc = dev_alloc(b, &Q.idx, npad))) return rc;
+        if ((rc = dev_alloc(b, &Q.idx, nt))) return rc;
+        if ((rc = dev_alloc(b, &Q.tidx, nt))) return rc;
         if ((rc = dev_alloc(b, &Q.cnt, (size_t)max_ng + 1))) return rc;
         if ((rc = dev_alloc(b, &Q.fill, (size_t)max_ng))) return rc;
         if ((rc = dev_alloc(b, &Q.tmp, (size_t)std::max(max_pc, 1)))) return rc;
+        if ((rc = dev_alloc(b, &Q.queue, (size_t)2 * max_ng + 2))) return rc;
+        if ((rc = dev_alloc(b, &Q.ctl, (size_t)2))) return rc;
+        if ((rc = dev_alloc(b, &Q.bits, (size_t)GZ_BPL_NBIG * 2 * nwords))) return rc;
         b->bp_smem = 16;
       }
     }
@@ -665,13 +730,17 @@ static int launch_collision(gzcuda_batch *b) {
   if (b->bp_large) {
     for (int w = 0; w < W; w++) {   // large worlds come one or a few per batch
       const int nwarps = std::max(1, b->h_world[w].ng), blocks = std::min(cdiv(nwarps, 8), 148 * 8);
-      k_bpl_sort<<<1, 1024, 0, b->stream>>>(d, w, b->bpl);
+      const int ntile = cdiv(b->h_world[w].ng + 1, GZ_BPL_TILE);
+      k_bpl_tilesort<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_merge<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_sweep<0><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_tail<0><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_scan<<<1, 1024, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_sweep<1><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_tail<1><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_emit<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
     }
-    b->last_launches += 5 * W - 1;
+    b->last_launches += 8 * W - 1;
   } else k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
   if (b->has_cylinders) k_narrow<true><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
   else k_narrow<false><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
@@ -719,11 +788,28 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
       for (int w = 0; w < W && d.pgs_dataflow; w++) {
         double *partial = d.xch_g + (size_t)2 * b->pgsl_grid * 256;
         unsigned *epoch = reinterpret_cast<unsigned *>(d.xch_g + (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid) + 8;
+        unsigned *ticket = epoch + 1;
         // 32-bit tags: long before they could repeat, clear the slots and start the epochs again
         if ((++b->pgsd_launches + 2) * (unsigned long long)(d.p.iters + d.p.friction_iters + 1) >= 0xFFFFFFFFull) {
           cudaMemsetAsync(b->pgsd_slots, 0, (size_t)8 * d.ent_cap * sizeof(unsigned long long), b->stream);
           cudaMemsetAsync(epoch, 0, sizeof(unsigned), b->stream);
           b->pgsd_launches = 1;
+        }
+        if (b->pgs_large_mode == 2) {
+          cudaLaunchConfig_t cfg = {};
+          cfg.gridDim = dim3(b->pgsc_grid); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = b->pgsc_smem; cfg.stream = b->stream;
+          cudaLaunchAttribute at[1];
+          at[0].id = cudaLaunchAttributeClusterDimension;
+          at[0].val.clusterDim.x = b->pgsc_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+          cfg.attrs = at; cfg.numAttrs = 1;
+          const int *tab = d.cta_e0 + (size_t)w * GZ_PGSC_TAB;
+          const unsigned *ep = epoch;
+          const int smem_entries = (int)(b->pgsc_smem / 64), glob_every = b->pgsc_glob_every - 1, sleep_ns = b->pgsc_sleep;
+          if (box) cudaLaunchKernelEx(&cfg, k_pgsc<true>, d, w, b->pgsd_slots, tab, ep, smem_entries, glob_every, sleep_ns);
+          else cudaLaunchKernelEx(&cfg, k_pgsc<false>, d, w, b->pgsd_slots, tab, ep, smem_entries, glob_every, sleep_ns);
+          k_pgs_large_stats<<<b->pgsl_grid, 256, 0, b->stream>>>(d, w, partial, ticket, epoch);
+          b->last_launches++;
+          continue;
         }
         void *args[] = {(void *)&d, (void *)&w, (void *)&b->pgsd_slots, (void *)&partial, (void *)&epoch};
         cudaLaunchCooperativeKernel(box ? (void *)k_pgsd<true> : (void *)k_pgsd<false>, dim3(b->pgsl_grid), dim3(256), args, 0, b->stream);

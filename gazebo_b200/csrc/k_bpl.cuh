@@ -5,40 +5,106 @@
 // the lower x bound of their AABB, sweep forward from every sorted position while the x intervals overlap, give the
 // survivors the full test.  Both are exact AABB-overlap filters, so the pair SET is the reference's; the list comes
 // out sorted by (i, j), the canonical order of the deterministic row-order mode.
-//   k_bpl_sort   one CTA: bitonic sort of (lower x bound, geom) in global memory, then the upper bounds in sorted order
-//   k_bpl_sweep  one warp per sorted position, all SMs; pass 0 counts the pairs of every lower-index geom,
-//                pass 1 stores the higher-index partners at the places the scan assigned
-//   k_bpl_scan   one CTA: exclusive scan of the counts, n_pairs, capacity flag
-//   k_bpl_emit   one warp per geom: ranks its partners by counting (lists are short, tens to a few hundred) and
-//                writes the pairs in ascending order
+//   k_bpl_tilesort  one CTA per 1024 geoms: bitonic sort of (lower x bound, geom) in shared memory
+//   k_bpl_merge     one thread per geom: its final place = its place in its tile + the number of smaller elements in
+//                   every other tile (binary searches); writes the sorted arrays and the upper bounds in sorted order
+//   k_bpl_sweep     one warp per sorted position, all SMs; pass 0 counts the pairs of every lower-index geom,
+//                   pass 1 stores the higher-index partners at the places the scan assigned.  A position whose x
+//                   interval covers more than GZ_BPL_CHUNKS x 32 followers (the ground plane, the pen's walls) hands
+//                   the rest to the queue
+//   k_bpl_tail      the queue: all warps share the followers of each queued position (without it the plane's warp
+//                   walked all 20 000 geoms alone and WAS the kernel's duration)
+//   k_bpl_scan      one CTA: exclusive scan of the counts, n_pairs, capacity flag
+//   k_bpl_emit      one warp per geom: puts its partners in ascending order - short lists by counting, long lists
+//                   (the plane's: thousands) through a bitmap over the geoms and its prefix popcount
 #pragma once
 
 namespace gz {
 
-struct BplBuf { double *key, *maxx; int *idx, *cnt, *fill, *tmp; int npad; };
+#define GZ_BPL_TILE 1024
+#define GZ_BPL_CHUNKS 64    // followers a warp of k_bpl_sweep tests by itself, in units of 32
+#define GZ_BPL_NBIG 8       // lists k_bpl_emit can order through a bitmap at the same time
+#define GZ_BPL_BIG 256      // ... from this length on
 
-__global__ void __launch_bounds__(1024) k_bpl_sort(DevBatch B, const int w, BplBuf Q) {
+struct BplBuf {
+  double *key, *maxx, *tkey;
+  int *idx, *cnt, *fill, *tmp, *tidx;
+  int *queue;   // [2 * n] (sorted position, first follower not tested yet)
+  int *ctl;     // [0] queue length, [1] bitmaps claimed
+  int *bits;    // [GZ_BPL_NBIG][2][(n + 31) / 32 + 1] bitmap and its exclusive prefix popcount
+  int npad;
+  int chunks, big;   // GZ_BPL_CHUNKS, GZ_BPL_BIG unless a developer switch says otherwise
+};
+
+// total order of the sort: by key, ties by geom index (padding: key +inf, index >= n, sorts last)
+__device__ __forceinline__ bool bpl_less(double ka, int ia, double kb, int ib) { return ka < kb || (ka == kb && ia < ib); }
+
+__global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_tilesort(DevBatch B, const int w, BplBuf Q) {
+  __shared__ double sk[GZ_BPL_TILE];
+  __shared__ int si[GZ_BPL_TILE];
   const WorldInfo wi = B.world[w];
-  const int n = wi.ng, tid = threadIdx.x, nt = blockDim.x, npad = Q.npad;
+  const int n = wi.ng, tid = threadIdx.x, g = blockIdx.x * GZ_BPL_TILE + tid;
   const Geom *G = B.geom + wi.geom0;
-  for (int i = tid; i < npad; i += nt) { Q.key[i] = (i < n) ? G[i].aabb[0] : GZ_INF; Q.idx[i] = i; }
-  for (int i = tid; i <= n; i += nt) { Q.cnt[i] = 0; if (i < n) Q.fill[i] = 0; }
+  double key = (g < n) ? G[g].aabb[0] : GZ_INF;
+  if (key != key) key = GZ_INF;   // a NaN bound (a body that left the number line) must not break the total order
+  sk[tid] = key;
+  si[tid] = g;
+  if (g <= n) { Q.cnt[g] = 0; if (g < n) Q.fill[g] = 0; }
+  if (g == 0) { Q.ctl[0] = 0; Q.ctl[1] = 0; B.wstep[w].overflow = 0; }   // (k_broadphase's role: the step's capacity mask starts here)
   __syncthreads();
-  for (int k = 2; k <= npad; k <<= 1)
+  for (int k = 2; k <= GZ_BPL_TILE; k <<= 1)
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = tid; i < npad; i += nt) {
-        const int l = i ^ j;
-        if (l > i) {
-          const double a = Q.key[i], b = Q.key[l];
-          const int ia = Q.idx[i], ib = Q.idx[l];
-          const bool gt = a > b || (a == b && ia > ib);   // padding (index >= n, key +inf) sorts last
-          if (gt == ((i & k) == 0)) { Q.key[i] = b; Q.key[l] = a; Q.idx[i] = ib; Q.idx[l] = ia; }
-        }
+      const int l = tid ^ j;
+      if (l > tid) {
+        const double a = sk[tid], b = sk[l];
+        const int ia = si[tid], ib = si[l];
+        const bool gt = bpl_less(b, ib, a, ia);
+        if (gt == ((tid & k) == 0)) { sk[tid] = b; sk[l] = a; si[tid] = ib; si[l] = ia; }
       }
       __syncthreads();
     }
-  for (int p = tid; p < n; p += nt) Q.maxx[p] = G[Q.idx[p]].aabb[1];
-  if (tid == 0) B.wstep[w].overflow = 0;   // (k_broadphase's role: the step's capacity mask starts here)
+  Q.tkey[g] = sk[tid]; Q.tidx[g] = si[tid];
+}
+
+__global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_merge(DevBatch B, const int w, BplBuf Q) {
+  const WorldInfo wi = B.world[w];
+  const int n = wi.ng, tid = threadIdx.x, t = blockIdx.x, ntile = gridDim.x;
+  const Geom *G = B.geom + wi.geom0;
+  const double k = Q.tkey[t * GZ_BPL_TILE + tid];
+  const int i = Q.tidx[t * GZ_BPL_TILE + tid];
+  int rank = tid;
+  for (int u = 0; u < ntile; u++) {
+    if (u == t) continue;
+    const double *uk = Q.tkey + u * GZ_BPL_TILE;
+    const int *ui = Q.tidx + u * GZ_BPL_TILE;
+    int lo = 0, hi = GZ_BPL_TILE;   // number of elements of tile u below (k, i)
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (bpl_less(uk[mid], ui[mid], k, i)) lo = mid + 1; else hi = mid;
+    }
+    rank += lo;
+  }
+  Q.key[rank] = k; Q.idx[rank] = i;
+  if (i < n) Q.maxx[rank] = G[i].aabb[1];   // (real geoms take the places below n: padding sorts last)
+}
+
+// the full test of sorted position q against position p's geom ip; returns whether q is still inside p's x interval
+template <int PASS>
+__device__ __forceinline__ bool bpl_follow(const DevBatch &B, const WorldInfo &wi, const Geom *G, const BplBuf &Q, const int ip,
+                                           const double mx, const int q, const int n) {
+  const bool in = (q < n) && Q.key[q] <= mx;
+  if (in) {
+    const int iq = Q.idx[q];
+    const int lo = min(ip, iq), hi = max(ip, iq);
+    if (pair_passes(B, G[lo], G[hi])) {
+      if (PASS == 0) atomicAdd(&Q.cnt[lo], 1);
+      else {
+        const int at = Q.cnt[lo] + atomicAdd(&Q.fill[lo], 1);   // cnt holds the exclusive scan now
+        if (at < wi.pair_cap) Q.tmp[at] = hi;
+      }
+    }
+  }
+  return in;
 }
 
 template <int PASS>
@@ -50,21 +116,32 @@ __global__ void __launch_bounds__(256) k_bpl_sweep(DevBatch B, const int w, BplB
   for (int p = warp; p < n - 1; p += nwarp) {
     const int ip = Q.idx[p];
     const double mx = Q.maxx[p];
-    for (int q0 = p + 1; q0 < n; q0 += 32) {
-      const int q = q0 + lane;
-      const bool in = (q < n) && Q.key[q] <= mx;
-      if (in) {
-        const int iq = Q.idx[q];
-        const int lo = min(ip, iq), hi = max(ip, iq);
-        if (pair_passes(B, G[lo], G[hi])) {
-          if (PASS == 0) atomicAdd(&Q.cnt[lo], 1);
-          else {
-            const int at = Q.cnt[lo] + atomicAdd(&Q.fill[lo], 1);   // cnt holds the exclusive scan now
-            if (at < wi.pair_cap) Q.tmp[at] = hi;
-          }
-        }
+    int c = 0;
+    for (int q0 = p + 1; q0 < n; q0 += 32, c++) {
+      if (c == Q.chunks) {   // a long interval: the rest goes to k_bpl_tail (queued once, by pass 0)
+        if (PASS == 0 && lane == 0) { const int at = atomicAdd(&Q.ctl[0], 1); Q.queue[2 * at] = p; Q.queue[2 * at + 1] = q0; }
+        break;
       }
+      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, q0 + lane, n);
       if (!__all_sync(0xffffffffu, in)) break;   // sorted: nothing further overlaps p on x
+    }
+  }
+}
+
+template <int PASS>
+__global__ void __launch_bounds__(256) k_bpl_tail(DevBatch B, const int w, BplBuf Q) {
+  const WorldInfo wi = B.world[w];
+  const int n = wi.ng, lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarp = (gridDim.x * blockDim.x) >> 5;
+  const Geom *G = B.geom + wi.geom0;
+  const int nq = Q.ctl[0];
+  for (int e = 0; e < nq; e++) {
+    const int p = Q.queue[2 * e], qs = Q.queue[2 * e + 1];
+    const int ip = Q.idx[p];
+    const double mx = Q.maxx[p];
+    for (int q0 = qs + 32 * warp; q0 < n; q0 += 32 * nwarp) {
+      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, q0 + lane, n);
+      if (!__all_sync(0xffffffffu, in)) break;   // sorted: this warp's later chunks are outside as well
     }
   }
 }
@@ -106,10 +183,41 @@ __global__ void __launch_bounds__(1024) k_bpl_scan(DevBatch B, const int w, BplB
 
 __global__ void __launch_bounds__(256) k_bpl_emit(DevBatch B, const int w, BplBuf Q) {
   const WorldInfo wi = B.world[w];
-  const int n = wi.ng, lane = threadIdx.x & 31;
+  const int n = wi.ng, lane = threadIdx.x & 31, nwords = (n + 31) / 32 + 1;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarp = (gridDim.x * blockDim.x) >> 5;
   for (int lo = warp; lo < n; lo += nwarp) {
     const int base = Q.cnt[lo], L = min(Q.cnt[lo + 1], wi.pair_cap) - base;
+    int slot = -1;
+    if (L >= Q.big) {
+      if (lane == 0) slot = atomicAdd(&Q.ctl[1], 1);
+      slot = __shfl_sync(0xffffffffu, slot, 0);
+      if (slot >= GZ_BPL_NBIG) slot = -1;   // (more long lists than bitmaps: counting still gives the right order)
+    }
+    if (slot >= 0) {
+      // partners of a geom are distinct: rank = number of set bits below the partner's
+      int *bits = Q.bits + (size_t)slot * 2 * nwords, *pre = bits + nwords;
+      for (int k = lane; k < nwords; k += 32) bits[k] = 0;
+      __syncwarp();
+      for (int e = lane; e < L; e += 32) { const int hi = Q.tmp[base + e]; atomicOr(&bits[hi >> 5], 1 << (hi & 31)); }
+      __syncwarp();
+      int carry = 0;
+      for (int k0 = 0; k0 < nwords; k0 += 32) {
+        const int k = k0 + lane;
+        const int c = k < nwords ? __popc(__ldcg(&bits[k])) : 0;
+        int v = c;
+        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
+        if (k < nwords) pre[k] = carry + v - c;
+        carry += __shfl_sync(0xffffffffu, v, 31);
+      }
+      __syncwarp();
+      for (int e = lane; e < L; e += 32) {
+        const int hi = Q.tmp[base + e];
+        const int rank = pre[hi >> 5] + __popc(__ldcg(&bits[hi >> 5]) & ((1u << (hi & 31)) - 1u));
+        B.pair[2 * (wi.pair0 + base + rank)] = wi.geom0 + lo;
+        B.pair[2 * (wi.pair0 + base + rank) + 1] = wi.geom0 + hi;
+      }
+      continue;
+    }
     for (int e = lane; e < L; e += 32) {
       const int hi = Q.tmp[base + e];
       int rank = 0;

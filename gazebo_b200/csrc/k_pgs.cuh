@@ -519,6 +519,10 @@ __device__ __forceinline__ void rowfinish_one(DevBatch &B, const int w, const Wo
     for (int h = 0; h < (r.b2 >= 0 ? 2 : 1); h++) {
       const int e = h ? ent2 : ent1;
       if (B.ent_part) B.ent_part[e] = h ? ent1 : ent2;
+      if (B.ent_aux) {   // k_pgsc: partner entry, the CTA that owns the partner's body, distance to the normal row, class
+        const int pbody = h ? r.b1 : r.b2;
+        B.ent_aux[e] = make_int4(h ? ent1 : ent2, pbody >= 0 ? pbody / B.pgsc_bodies : 0, h ? back2 : back1, cls);
+      }
       double2 *e2 = reinterpret_cast<double2 *>(B.ent + (size_t)e * GZ_ENT);
       for (int j = 0; j < 3; j++) {
         e2[j] = make_double2(J[6 * h + 2 * j] * Ad, J[6 * h + 2 * j + 1] * Ad);
@@ -583,6 +587,7 @@ __global__ void k_rowfinish(DevBatch B) {
 #include "k_pgs_sweep.cuh"
 #include "k_pgs_chain.cuh"
 #include "k_pgsl.cuh"
+#include "k_pgsc.cuh"
 namespace gz {
 
 // One thread per joint: save lambda for the next step's warm start.

@@ -315,6 +315,11 @@ __global__ void __launch_bounds__(256) k_bsched_large(DevBatch B, const int w, u
     B.bsched[wi.body0 + b] = nent > 0 ? make_int4(wbase + base[b], nj_rows + 3 * ncb, nj_rows + ncb, 0) : make_int4(0, 0, 0, 0);
   }
   for (int pos = gt; pos < m; pos += GT) S.off[pos] = (nent > 0 && S.rb1[pos] >= 0) ? 0 : -1;
+  if (B.cta_e0)   // k_pgsc: where the entries of every 256 bodies begin
+    for (int c = gt; c < GZ_PGSC_TAB; c += GT) {
+      const int b = c * B.pgsc_bodies;
+      B.cta_e0[(size_t)w * GZ_PGSC_TAB + c] = wbase + ((b < nb && nent > 0) ? base[b] : nent);
+    }
   pgsl_barrier(bar, bar_target);
   // ---- 5
   for (int it = 0; it < (1 << 20) && nent > 0 && relax; it++) {

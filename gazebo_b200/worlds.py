@@ -209,11 +209,12 @@ def pioneer_worlds(n_worlds=1024, config=3, first_world=0, drive=False, torque=5
 def rubble_world(n_bodies=20000, config=4, pen=None, auto_disable=False):
     """C4: plane + 4 static wall boxes + n_bodies single-body models: 60 % boxes (half "2x4" planks 0.6-2.4 x 0.1016 x 0.0508 m,
     half cinder blocks 0.2032 x 0.2032 x 0.4064 m as plugins/RubblePlugin.cc:71-91, scaled by 0.5), 25 % spheres r U(0.05, 0.15),
-    15 % capsules r U(0.04, 0.08), l U(0.1, 0.4); mass U(0.1, 1.0) kg; dropped in layers into a square pen (10 x 10 m at
-    20 000 bodies, the side scaled with sqrt(n) below that so the pile is as deep)."""
+    15 % capsules r U(0.04, 0.08), l U(0.1, 0.4); mass U(0.1, 1.0) kg; dropped in layers into a square pen (24 x 24 m at
+    20 000 bodies: 7 layers, the top one falls 3.7 m; the side scaled with sqrt(n) below that so the pile is as deep).
+    A 10 m pen (40 layers, the top one falls 22 m) ends in the reference as it does here: bodies shot out of the pile."""
     rng = np.random.Generator(np.random.PCG64(1000 * config))
     if pen is None:
-        pen = 10.0 * math.sqrt(n_bodies / 20000.0)
+        pen = 24.0 * math.sqrt(n_bodies / 20000.0)
     sb = S.SceneBuilder()
     sb.begin_world()
     sb.add_ground_plane()

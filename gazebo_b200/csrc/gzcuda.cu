@@ -68,6 +68,9 @@ struct gzcuda_batch {
   int pgs_large_mode = 1;             // large worlds: 0 k_pgsl (rounds + grid barrier), 1 k_pgsd (dataflow through L2), 2 k_pgsc (+ cluster shared memory)
   int pgsc_grid = 0, pgsc_cluster = 1, pgsc_glob_every = 4, pgsc_sleep = 0;
   size_t pgsc_smem = 0;
+  bool large_kernels = false;         // k_contacts_large / k_assemble1_large (cooperative grid) instead of the one-CTA-per-world kernels
+  int large_grid = 0;
+  int *large_part = nullptr;
   int bsl_grid = 0;                   // CTAs of k_bsched_large's cooperative grid
   PgsbCfg pgsbc[GZ_PGSB_NCLS];        // the shared-memory classes of the one-warp CTAs, ascending budgets
   size_t pgsbc_smem[GZ_PGSB_NCLS] = {};
@@ -418,6 +421,18 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if ((rc = dev_alloc(b, &d.xch_g, (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid + 8))) return rc;
     CK(cudaMemset(d.xch_g, 0, ((size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid + 8) * sizeof(double)));
     if ((rc = dev_alloc(b, &d.bs_clist, (size_t)2 * contact_tot + 2))) return rc;
+    // the one-CTA-per-world kernels of the step spread over a cooperative grid: worlds beyond 512 bodies (test switch
+    // GZCUDA_LARGE_KERNELS forces them onto small worlds)
+    b->large_kernels = max_nb > 512;
+    if (const char *el = getenv("GZCUDA_LARGE_KERNELS")) b->large_kernels = atoi(el) != 0;
+    if (b->large_kernels) {
+      int p1 = 0, p2 = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p1, k_contacts_large, 256, 0));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2, k_assemble1_large, 256, 0));
+      b->large_grid = n_sm * std::max(1, std::min(2, std::min(p1, p2)));
+      if (std::min(p1, p2) < 1) b->large_kernels = false;
+      else if ((rc = dev_alloc(b, &b->large_part, (size_t)b->large_grid + 1))) return rc;
+    }
     if ((rc = dev_alloc(b, &d.bs_glob, (size_t)W * 5 * std::max(max_nb, 1)))) return rc;
   }
   if (d.pgs_impl >= 1) {
@@ -744,7 +759,15 @@ static int launch_collision(gzcuda_batch *b) {
   } else k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
   if (b->has_cylinders) k_narrow<true><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
   else k_narrow<false><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
-  k_contacts<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // (one CTA per world: a large world gets the largest CTA)
+  if (b->large_kernels) {
+    for (int w = 0; w < W; w++) {
+      unsigned *bar = reinterpret_cast<unsigned *>(d.xch_g + (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid);
+      void *args[] = {(void *)&d, (void *)&w, (void *)&b->large_part, (void *)&bar};
+      cudaLaunchCooperativeKernel((void *)k_contacts_large, dim3(b->large_grid), dim3(256), args, 0, b->stream);
+    }
+    b->last_launches += W - 1;
+  } else
+    k_contacts<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // (one CTA per world: a large world gets the largest CTA)
   b->last_launches += 4;
   return 0;
 }
@@ -752,7 +775,15 @@ static int launch_collision(gzcuda_batch *b) {
 static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
-  k_assemble1<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // islands, body prologue, row counts
+  if (b->large_kernels) {
+    for (int w = 0; w < W; w++) {
+      unsigned *bar = reinterpret_cast<unsigned *>(d.xch_g + (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid);
+      void *args[] = {(void *)&d, (void *)&w, (void *)&bar};
+      cudaLaunchCooperativeKernel((void *)k_assemble1_large, dim3(b->large_grid), dim3(256), args, 0, b->stream);
+    }
+    b->last_launches += W - 1;
+  } else
+    k_assemble1<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // islands, body prologue, row counts
   // the joint rows (one thread per joint: a long dependent chain on few threads) run beside the contact rows and
   // the schedule, which do not depend on them; k_rowfinish needs all three
   const bool fork_joint = d.nj > 0 && d.pgs_impl >= 1;

@@ -340,10 +340,56 @@ __global__ void k_narrow(DevBatch B) {
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) narrow_pair<CYL>(B, w, wi, k);
 }
 
+// The contacts of candidate pair k of a world (c of them, from k_narrow) at place `off` of the world's contact list,
+// with the combined surface parameters.
+__device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldInfo &wi, const int k, const int c, const int off) {
+  const double h = B.p.step_size;
+  const int pi = wi.pair0 + k;
+  const int gi1 = B.pair[2 * pi], gi2 = B.pair[2 * pi + 1];
+  const Geom &g1 = B.geom[gi1];
+  const Geom &g2 = B.geom[gi2];
+  // surface combination, ODEPhysics.cc:1108-1258
+  double kp = 1.0 / (1.0 / g1.surf[GZ_SF_KP] + 1.0 / g2.surf[GZ_SF_KP]);
+  double kd = g1.surf[GZ_SF_KD] + g2.surf[GZ_SF_KD];
+  double soft_erp = (h * kp) / (h * kp + kd);
+  double soft_cfm = 1.0 / (h * kp + kd);
+  // fdir1 as written in ODEPhysics.cc:1120-1161: only surface 1's direction ever reaches the contact (the
+  // reference rotates surface 2's fd2 but never assigns it), rotated to the world frame by collision 1's pose
+  double fd[3] = {g1.fdir1[0], g1.fdir1[1], g1.fdir1[2]};
+  const bool fdset = (fd[0] != 0 || fd[1] != 0 || fd[2] != 0);
+  double fdw[3] = {0, 0, 0};
+  if (fdset) {
+    if (g1.type == GZ_GEOM_PLANE) { fdw[0] = fd[0]; fdw[1] = fd[1]; fdw[2] = fd[2]; }   // a plane has no pose: identity
+    else mul0_331(fdw, g1.R, fd);
+  }
+  double mu = fmin(g1.surf[GZ_SF_MU], g2.surf[GZ_SF_MU]);
+  double mu2 = fmin(g1.surf[GZ_SF_MU2], g2.surf[GZ_SF_MU2]);
+  double slip1 = g1.surf[GZ_SF_SLIP1] + g2.surf[GZ_SF_SLIP1];
+  double slip2 = g1.surf[GZ_SF_SLIP2] + g2.surf[GZ_SF_SLIP2];
+  slip1 *= c; slip2 *= c;
+  double bounce = fmin(g1.surf[GZ_SF_BOUNCE], g2.surf[GZ_SF_BOUNCE]);
+  double bounce_vel = fmin(g1.surf[GZ_SF_BOUNCE_VEL], g2.surf[GZ_SF_BOUNCE_VEL]);
+  // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
+  int b1 = g1.body, b2 = g2.body, reverse = 0;
+  if (b1 < 0) { b1 = b2; b2 = -1; reverse = 1; }
+  const double *src = B.pair_contact + (size_t)pi * (7 * GZ_PAIR_MAXC);
+  for (int j = 0; j < c; j++) {
+    int ci = off + j;
+    if (ci >= wi.contact_cap) break;
+    Contact &C = B.contact[wi.contact0 + ci];
+    for (int i = 0; i < 3; i++) { C.pos[i] = src[7 * j + i]; C.normal[i] = src[7 * j + 3 + i]; C.fdir1[i] = fdw[i]; }
+    C.depth = src[7 * j + 6];
+    C.mu = mu; C.mu2 = mu2; C.soft_erp = soft_erp; C.soft_cfm = soft_cfm;
+    C.slip1 = slip1; C.slip2 = slip2; C.bounce = bounce; C.bounce_vel = bounce_vel;
+    C.g1 = gi1; C.g2 = gi2; C.b1 = b1; C.b2 = b2; C.reverse = reverse; C.has_fdir1 = fdset ? 1 : 0;
+  }
+  if (b1 >= 0) B.bstep[b1].has_contact = 1;
+  if (b2 >= 0) B.bstep[b2].has_contact = 1;
+}
+
 // One CTA per world: exclusive scan of per-pair contact counts, then one thread per pair
-// writes its contacts (with the combined surface parameters) at the scanned offset.
+// writes its contacts at the scanned offset.
 __global__ void k_contacts(DevBatch B) {
-  extern __shared__ int sh[];
   const int w = blockIdx.x;
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
@@ -354,7 +400,6 @@ __global__ void k_contacts(DevBatch B) {
   for (int b = threadIdx.x; b < wi.nb; b += blockDim.x) B.bstep[wi.body0 + b].has_contact = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  const double h = B.p.step_size;
   for (int k0 = 0; k0 < np; k0 += blockDim.x) {
     int k = k0 + threadIdx.x;
     int c = (k < np) ? B.pair_nc[wi.pair0 + k] : 0;
@@ -371,49 +416,7 @@ __global__ void k_contacts(DevBatch B) {
     __syncthreads();
     int off = carry + (v - c) + (warp > 0 ? warp_sums[warp - 1] : 0);
     int total = warp_sums[nwarp - 1];
-    if (c > 0) {
-      const int pi = wi.pair0 + k;
-      const int gi1 = B.pair[2 * pi], gi2 = B.pair[2 * pi + 1];
-      const Geom &g1 = B.geom[gi1];
-      const Geom &g2 = B.geom[gi2];
-      // surface combination, ODEPhysics.cc:1108-1258
-      double kp = 1.0 / (1.0 / g1.surf[GZ_SF_KP] + 1.0 / g2.surf[GZ_SF_KP]);
-      double kd = g1.surf[GZ_SF_KD] + g2.surf[GZ_SF_KD];
-      double soft_erp = (h * kp) / (h * kp + kd);
-      double soft_cfm = 1.0 / (h * kp + kd);
-      // fdir1 as written in ODEPhysics.cc:1120-1161: only surface 1's direction ever reaches the contact (the
-      // reference rotates surface 2's fd2 but never assigns it), rotated to the world frame by collision 1's pose
-      double fd[3] = {g1.fdir1[0], g1.fdir1[1], g1.fdir1[2]};
-      const bool fdset = (fd[0] != 0 || fd[1] != 0 || fd[2] != 0);
-      double fdw[3] = {0, 0, 0};
-      if (fdset) {
-        if (g1.type == GZ_GEOM_PLANE) { fdw[0] = fd[0]; fdw[1] = fd[1]; fdw[2] = fd[2]; }   // a plane has no pose: identity
-        else mul0_331(fdw, g1.R, fd);
-      }
-      double mu = fmin(g1.surf[GZ_SF_MU], g2.surf[GZ_SF_MU]);
-      double mu2 = fmin(g1.surf[GZ_SF_MU2], g2.surf[GZ_SF_MU2]);
-      double slip1 = g1.surf[GZ_SF_SLIP1] + g2.surf[GZ_SF_SLIP1];
-      double slip2 = g1.surf[GZ_SF_SLIP2] + g2.surf[GZ_SF_SLIP2];
-      slip1 *= c; slip2 *= c;
-      double bounce = fmin(g1.surf[GZ_SF_BOUNCE], g2.surf[GZ_SF_BOUNCE]);
-      double bounce_vel = fmin(g1.surf[GZ_SF_BOUNCE_VEL], g2.surf[GZ_SF_BOUNCE_VEL]);
-      // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
-      int b1 = g1.body, b2 = g2.body, reverse = 0;
-      if (b1 < 0) { b1 = b2; b2 = -1; reverse = 1; }
-      const double *src = B.pair_contact + (size_t)pi * (7 * GZ_PAIR_MAXC);
-      for (int j = 0; j < c; j++) {
-        int ci = off + j;
-        if (ci >= wi.contact_cap) break;
-        Contact &C = B.contact[wi.contact0 + ci];
-        for (int i = 0; i < 3; i++) { C.pos[i] = src[7 * j + i]; C.normal[i] = src[7 * j + 3 + i]; C.fdir1[i] = fdw[i]; }
-        C.depth = src[7 * j + 6];
-        C.mu = mu; C.mu2 = mu2; C.soft_erp = soft_erp; C.soft_cfm = soft_cfm;
-        C.slip1 = slip1; C.slip2 = slip2; C.bounce = bounce; C.bounce_vel = bounce_vel;
-        C.g1 = gi1; C.g2 = gi2; C.b1 = b1; C.b2 = b2; C.reverse = reverse; C.has_fdir1 = fdset ? 1 : 0;
-      }
-      if (b1 >= 0) B.bstep[b1].has_contact = 1;
-      if (b2 >= 0) B.bstep[b2].has_contact = 1;
-    }
+    if (c > 0) contacts_of_pair(B, wi, k, c, off);
     __syncthreads();
     if (threadIdx.x == 0) carry += total;
     __syncthreads();

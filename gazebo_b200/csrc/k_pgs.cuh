@@ -588,6 +588,7 @@ __global__ void k_rowfinish(DevBatch B) {
 #include "k_pgs_chain.cuh"
 #include "k_pgsl.cuh"
 #include "k_pgsc.cuh"
+#include "k_large.cuh"
 namespace gz {
 
 // One thread per joint: save lambda for the next step's warm start.

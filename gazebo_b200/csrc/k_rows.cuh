@@ -109,35 +109,38 @@ __global__ void k_velcmd(DevBatch B) {
   }
 }
 
-// One CTA per world (a phase of k_assemble1 below).
-__device__ __forceinline__ void island_world(const DevBatch &B) {
-  const int w = blockIdx.x;
-  const WorldInfo wi = B.world[w];
-  const WorldStep &ws = B.wstep[w];
+// Auto-disable of one body (average_samples = 1: the instantaneous velocity is the average) and its island label's
+// start value (dxStepBody's bookkeeping, ode.cpp dInternalHandleAutoDisabling).
+__device__ __forceinline__ void autodisable_body(const DevBatch &B, const WorldInfo &wi, const int i) {
   const double h = B.p.step_size;
-  __shared__ int changed;
-  // 1. auto-disable (average_samples = 1: the instantaneous velocity is the average)
-  for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) {
-    Body &b = B.body[wi.body0 + i];
-    BodyStep &bs = B.bstep[wi.body0 + i];
-    bs.label = i;
-    bool has_joint = (b.joint_end > b.joint_begin) || bs.has_contact;
-    if (has_joint && (b.flags & (GZ_BODY_AUTO_DISABLE | GZ_BODY_DISABLED)) == GZ_BODY_AUTO_DISABLE) {
-      int idle = 1;
-      double av_l = dot3(b.lvel, b.lvel);
-      if (av_l > B.p.adis_linear_threshold_sq) idle = 0;
-      else {
-        double av_a = dot3(b.avel, b.avel);
-        if (av_a > B.p.adis_angular_threshold_sq) idle = 0;
-      }
-      if (idle) { b.adis_stepsleft--; b.adis_timeleft -= h; }
-      else { b.adis_stepsleft = B.p.adis_idle_steps; b.adis_timeleft = B.p.adis_idle_time; }
-      if (b.adis_stepsleft <= 0 && b.adis_timeleft <= 0) {
-        b.flags |= GZ_BODY_DISABLED;
-        for (int k = 0; k < 3; k++) { b.lvel[k] = 0; b.avel[k] = 0; }
-      }
+  Body &b = B.body[wi.body0 + i];
+  BodyStep &bs = B.bstep[wi.body0 + i];
+  bs.label = i;
+  bool has_joint = (b.joint_end > b.joint_begin) || bs.has_contact;
+  if (has_joint && (b.flags & (GZ_BODY_AUTO_DISABLE | GZ_BODY_DISABLED)) == GZ_BODY_AUTO_DISABLE) {
+    int idle = 1;
+    double av_l = dot3(b.lvel, b.lvel);
+    if (av_l > B.p.adis_linear_threshold_sq) idle = 0;
+    else {
+      double av_a = dot3(b.avel, b.avel);
+      if (av_a > B.p.adis_angular_threshold_sq) idle = 0;
+    }
+    if (idle) { b.adis_stepsleft--; b.adis_timeleft -= h; }
+    else { b.adis_stepsleft = B.p.adis_idle_steps; b.adis_timeleft = B.p.adis_idle_time; }
+    if (b.adis_stepsleft <= 0 && b.adis_timeleft <= 0) {
+      b.flags |= GZ_BODY_DISABLED;
+      for (int k = 0; k < 3; k++) { b.lvel[k] = 0; b.avel[k] = 0; }
     }
   }
+}
+
+// One CTA per world (a phase of k_assemble1 below).
+__device__ __forceinline__ void island_world(const DevBatch &B, const int w) {
+  const WorldInfo wi = B.world[w];
+  const WorldStep &ws = B.wstep[w];
+  __shared__ int changed;
+  // 1. auto-disable
+  for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) autodisable_body(B, wi, i);
   __syncthreads();
   // 2. connected components over two-body joints (persistent + contact): the smallest body index of the component
   // becomes everybody's label.  Small worlds: min-label propagation (a few passes).  Large worlds (a pile of
@@ -229,8 +232,7 @@ __device__ __forceinline__ void bodyprep_body(const DevBatch &B, const int bi) {
 
 // One CTA per world: row count per joint (with the hinge's cumulative-angle side effect),
 // exclusive scan -> Joint::row0; contacts follow with 3 rows each.
-__device__ __forceinline__ void info1_world(const DevBatch &B) {
-  const int w = blockIdx.x;
+__device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
   __shared__ int carry;
@@ -311,12 +313,12 @@ __device__ __forceinline__ void info1_world(const DevBatch &B) {
 // One CTA per world: auto-disable + islands, the body prologue of its bodies, row counts and offsets - three
 // phases that were three launches (k_island, k_bodyprep, k_info1), separated by block barriers.
 __global__ void k_assemble1(DevBatch B) {
-  island_world(B);
+  island_world(B, blockIdx.x);
   __syncthreads();
   const WorldInfo wi = B.world[blockIdx.x];
   for (int i = threadIdx.x; i < wi.nb; i += blockDim.x) bodyprep_body(B, wi.body0 + i);
   __syncthreads();
-  info1_world(B);
+  info1_world(B, blockIdx.x);
 }
 
 }  // namespace gz

@@ -14,6 +14,7 @@ UpdatePhysics) of every world of the batch.  One JSON line is printed by rank 0.
          per-body wrench array and downloads every body's pose + velocity
   roofline      k_pgsb: algorithmic bytes (288 B per row per sweep) / launch time
   strong        (N > 1) the same 4096 worlds split over the N ranks
+  --config c4   a second line for BASELINE.json configs[3] (ONE world: a 20 000-body rubble pile), same keys
   cpu_baseline  the reference's opende (oracle/_ref, -O3 -msse2 -DODE_SSE, natural gzserver
                 order, dWorldQuickStep) on this box's host cores, bounded sample
 """
@@ -279,6 +280,133 @@ def run_gpu(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_c4(args, rank, world, local_rank):
+    """--config c4: BASELINE.json configs[3], ONE world - a 20 000-body rubble pile in a walled pen - on one GPU (under
+    torchrun every rank steps its own replica: a single world does not shard).  The timed region starts once the pile
+    has formed (warm-up >= 2500 steps).  cpu_baseline: the reference's opende created from the GPU's body states at that
+    moment (it would need ~20 minutes to get there itself) and timed over a few steps on one thread."""
+    import resource
+    import torch
+    from gazebo_b200 import scene as S, worlds as W
+    from gazebo_b200.batch import Batch
+    try:   # dxHashSpace::collide's n x n / 8-byte matrix on the stack (collision_space.cpp:486-488): 50 MB at C4
+        resource.setrlimit(resource.RLIMIT_STACK, (resource.RLIM_INFINITY, resource.RLIM_INFINITY))
+    except Exception:
+        pass
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("gloo")
+    from gazebo_b200 import sharding
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n_bodies = args.bodies
+    sc = W.rubble_world(n_bodies)
+    p = S.default_params()
+    b = Batch(sc, p, device=local_rank)
+    K, Wm = args.steps, max(args.warmup, 2500)
+    b.step(Wm)
+    b.sync()
+    b.counters(reset=True)
+    b.set_profiling(True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    b.step(K)
+    b.sync()
+    barrier()
+    ms, launches = b.last_step_ms()
+    pgs_ms, pgs_launches = b.pgs_ms()
+    cnt = b.counters()
+    stage = b.stage_ms()
+    b.set_profiling(False)
+    ms = sharding.max_over_ranks(ms, dist, "cpu")
+    value = world * K / (ms * 1e-3)
+    nb = sc.nb
+    wrench = torch.zeros((nb, 6), dtype=torch.float64).pin_memory()
+    state = torch.empty((nb, 13), dtype=torch.float64).pin_memory()
+    for _ in range(3):
+        b.step_io(1, wrench.data_ptr(), state.data_ptr())
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        b.step_io(1, wrench.data_ptr(), state.data_ptr())
+    torch.cuda.synchronize()
+    e2e_s = sharding.max_over_ranks(time.perf_counter() - t0, dist, "cpu")
+    barrier()
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    if rank != 0:
+        return
+    peak, peak_kind = load_peaks()
+    rows, fric, contacts, wsteps = cnt
+    bytes_pgs = 288.0 * ((rows - fric) * p.iters + fric * (p.iters + p.friction_iters))
+    bytes_per_launch = bytes_pgs / max(pgs_launches, 1)
+    pgs_avg_ms = pgs_ms / max(pgs_launches, 1)
+    achieved = bytes_per_launch / (pgs_avg_ms * 1e-3) / 1e9 if pgs_avg_ms > 0 else 0.0
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "pgs_traffic_c4.json")) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    unit = "world-steps/s"
+    line = {
+        "metric": "world-steps/sec (20k-body rubble pile, one world)", "value": value, "unit": unit, "n_gpus": world, "steps": K,
+        "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "replicas only", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "configs[3]: ONE world, %d-body mixed box / sphere / capsule rubble pile in a walled pen on a plane, one "
+                               "island once formed; ODE quickstep 50+10 iters, dt=1ms, deterministic row-order mode; a single world does "
+                               "not shard: N > 1 = N replicas" % n_bodies,
+                   "bodies": sc.nb, "geoms": sc.ng, "rows_per_step": rows / max(wsteps, 1), "contacts_per_step": contacts / max(wsteps, 1),
+                   "l2": "no flush: the step's working set (entries 160 B x ~170 k, rows, contacts, bodies, geoms: ~90 MB) is below "
+                         "the 126 MB L2 and is rewritten every step; DRAM traffic is in roofline.traffic",
+                   "stage_ms_last_step": {"collide": stage[0], "assemble": stage[1], "pgs": stage[2], "integrate": stage[3]},
+                   "finite_bodies": int(torch.isfinite(state).all(dim=1).sum())},
+        "e2e": {"value": world * K / e2e_s, "unit": unit, "h2d_bytes_per_step": int(nb * 6 * 8), "d2h_bytes_per_step": int(nb * 13 * 8),
+                "api": "gzcuda_batch_step_io (pinned host buffers, 1 step per call)"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "k_pgsd (the PGS sweeps of the pile as dataflow over the whole GPU)", "achieved": achieved,
+                     "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic, "peak_kind": peak_kind,
+                     "bytes_per_launch": bytes_per_launch, "avg_launch_ms": pgs_avg_ms, "share_of_step": pgs_ms / ms if ms > 0 else None,
+                     "dram_achieved": (traffic / (pgs_avg_ms * 1e-3) / 1e9) if (traffic and pgs_avg_ms > 0) else None,
+                     "limiter": "the exact-order dependency chain through the pile: ~2 500 hops of ~1 500 cycles (publish -> L2 -> poll -> "
+                                "row update) per step, not bytes (DESIGN.md 4)",
+                     "note": "achieved = ALGORITHMIC bytes (288 B per row per sweep, SURVEY 8d) / CUDA-event time of the sweeps"},
+        "clocks": sampler.summary(),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            from oracle import refharness
+            flavour = "fast" if refharness.available("fast") else "parity"
+            pos, quat, lvel, avel = b.body_state()
+            bad = ~(np.isfinite(pos).all(axis=1) & np.isfinite(quat).all(axis=1) & np.isfinite(lvel).all(axis=1) & np.isfinite(avel).all(axis=1))
+            park = np.nonzero(bad | (np.abs(np.nan_to_num(pos)).max(axis=1) > 1e3))[0]
+            for k, bi in enumerate(park):   # bodies shot out of the pile on the way: parked far away
+                pos[bi] = (1000.0 + 2.0 * k, 1000.0, 1000.0); quat[bi] = (1, 0, 0, 0); lvel[bi] = 0; avel[bi] = 0
+            A = sc.arrays
+            A["body_pos"][:] = pos; A["body_quat"][:] = quat; A["body_lvel"][:] = lvel; A["body_avel"][:] = avel
+            r = refharness.RefBatch(sc, p, mode=0, flavour=flavour)
+            r.step(1)
+            n_cpu = 20
+            t0 = time.perf_counter(); r.step(n_cpu); dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": n_cpu / dt, "unit": unit, "cores": 1, "kind": "reference",
+                                    "sample": "%d steps (%.1f s) of the reference's own opende (oracle/_ref %s flavour, natural order, dWorldQuickStep) "
+                                              "on ONE thread (one world is one thread's work), created from the GPU's body states after %d steps "
+                                              "(%d bodies parked)" % (n_cpu, dt, flavour, Wm + 2 * K + 3, len(park))}
+        except Exception as e:
+            line["cpu_baseline"] = {"value": None, "unit": unit, "cores": 1, "kind": "reference", "sample": "unavailable: %s" % e}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -287,6 +415,8 @@ def main():
     ap.add_argument("--impl", default="gzcuda", choices=["gzcuda", "reference"])
     ap.add_argument("--worlds", type=int, default=WORLDS_PER_GPU, help="worlds per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", default="c2", choices=["c2", "c4"], help="c2: BASELINE.json configs[1] (the headline); c4: configs[3], one 20k-body pile")
+    ap.add_argument("--bodies", type=int, default=20000, help="--config c4: bodies of the pile")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -300,6 +430,9 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
+    if args.config == "c4":
+        run_c4(args, rank, world, local_rank)
+        return
     run_gpu(args, rank, world, local_rank)
 
 

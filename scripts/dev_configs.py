@@ -27,7 +27,7 @@ def run(name, sc, pd, warm, steps, cpu_worlds_scene=None, cpu_pd=None, cpu_steps
         line += " | cpu %9.0f world-steps/s on %d threads (%d worlds sampled)" % (csc.n_worlds * n / tc, th, csc.n_worlds)
     print(line, flush=True)
 
-sc = W.box_drop_worlds(1, 500); run("C1 500 boxes, 1 world", sc, None, 1500, 200)
+sc = W.box_drop_worlds(1, 500); run("C1 500 boxes, 1 world", sc, None, 1500, 200)   # (one world = one CPU thread)
 sc, pd = W.revolve_worlds(4096); csc, cpd = W.revolve_worlds(256)
 run("C2 4096 8-link robots", sc, pd, 100, 100, csc, cpd, 100)
 sc, _ = W.pioneer_worlds(1024, drive=True); csc, _ = W.pioneer_worlds(256, drive=True)

@@ -34,6 +34,7 @@ sys.path.insert(0, ROOT)
 WORLDS_PER_GPU = 4096
 METRIC = "batched world-steps/sec (8-link robots)"
 UNIT = "world-steps/s"
+CPU_PHASES = None
 
 
 def load_peaks():
@@ -88,6 +89,7 @@ def cpu_reference_rates(n_worlds, steps, warmup, threads, reps=3, flavour="fast"
     r = refharness.RefBatch(sc, S.default_params(), mode=0, flavour=flavour)
     r.set_hinge_pd(pd)
     r.step(warmup, threads=threads)
+    r.phase_seconds(reset=True)
     rates, secs = [], []
     for _ in range(reps):
         t0 = time.perf_counter()
@@ -95,6 +97,10 @@ def cpu_reference_rates(n_worlds, steps, warmup, threads, reps=3, flavour="fast"
         dt = time.perf_counter() - t0
         rates.append(n_worlds * steps / dt)
         secs.append(dt)
+    global CPU_PHASES
+    col, phy = r.phase_seconds()
+    CPU_PHASES = {"UpdateCollision": col / max(col + phy, 1e-30), "UpdatePhysics": phy / max(col + phy, 1e-30),
+                  "note": "share of the host threads' time inside the two calls of the path (host clock around them in the harness)"}
     return rates, secs, flavour
 
 
@@ -118,7 +124,7 @@ def run_reference(args, rank, world):
         "config": {"workload": "configs[1]: %d Revolve-style 8-link robot worlds on a plane, ODE quickstep 50+10 iters, dt=1ms "
                                "(the batch ONE GPU of the gzcuda arm steps; the host has one set of cores whatever --gpus says)" % n_worlds,
                    "worlds": n_worlds, "host_threads": cores, "windows": rates},
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample, "phases": CPU_PHASES},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -269,7 +275,8 @@ def run_gpu(args, rank, world, local_rank):
             line["cpu_baseline"] = {
                 "value": rate, "unit": UNIT, "cores": cores, "kind": "reference",
                 "sample": "%d worlds x %d steps, median of %d windows (%.1f s each) on %d persistent threads (oracle/_ref %s flavour: "
-                          "the reference's own opende, natural order, dWorldQuickStep)" % (nw, steps, len(rates), sorted(secs)[len(secs) // 2], cores, flavour)}
+                          "the reference's own opende, natural order, dWorldQuickStep)" % (nw, steps, len(rates), sorted(secs)[len(secs) // 2], cores, flavour),
+                "phases": CPU_PHASES}
         except Exception as e:   # the oracle library did not travel: say so instead of inventing a number
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
                                     "sample": "unavailable: %s" % e}

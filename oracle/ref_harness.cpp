@@ -44,6 +44,8 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+#include <chrono>
+#include <atomic>
 
 #include <gazebo/ode/ode.h>
 #include "config.h"
@@ -245,6 +247,8 @@ void collide_pair(RefBatch *B, RefWorld *w, int i1, int i2) {
   }
 }
 
+std::atomic<long long> g_phase_ns[2];   // [0] UpdateCollision, [1] UpdatePhysics: thread-seconds since the last reset
+
 // ---- ODEPhysics::UpdateCollision (ODEPhysics.cc:366-404) --------------------
 void update_collision(RefBatch *B, RefWorld *w) {
   dJointGroupEmpty(w->contactGroup);
@@ -391,7 +395,11 @@ void step_world(RefBatch *B, RefWorld *w) {
   apply_velocity_commands(w);
   apply_controllers(B, w);
   if (trace) fprintf(stderr, "  collide\n");
+  // the phase split of the CPU path (the reference's own -DTIMING split is #undef'd in quickstep_util.h:37): host
+  // clock around UpdateCollision and UpdatePhysics, summed over the worlds and steps of the calling thread
+  const auto t0 = std::chrono::steady_clock::now();
   update_collision(B, w);
+  const auto t1 = std::chrono::steady_clock::now();
   if (trace) fprintf(stderr, "  step (pairs %zu contacts %zu)\n", w->pairs.size(), w->contacts.size());
   w->num_contacts = 0;
   if (B->mode == 1) {
@@ -401,12 +409,21 @@ void step_world(RefBatch *B, RefWorld *w) {
     for (int k = 0; k < 4; k++) w->rms_residual[k] = w->world->qs.rms_constraint_residual[k];
     w->num_contacts = w->world->qs.num_contacts;
   }
+  const auto t2 = std::chrono::steady_clock::now();
+  g_phase_ns[0].fetch_add((long long)std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count(), std::memory_order_relaxed);
+  g_phase_ns[1].fetch_add((long long)std::chrono::duration_cast<std::chrono::nanoseconds>(t2 - t1).count(), std::memory_order_relaxed);
   w->step_index++;
 }
 
 }  // namespace
 
 extern "C" {
+
+// Thread-nanoseconds spent in UpdateCollision / UpdatePhysics since the last call with reset != 0.
+void gzref_phase_ns(long long out[2], int reset) {
+  out[0] = g_phase_ns[0].load(); out[1] = g_phase_ns[1].load();
+  if (reset) { g_phase_ns[0] = 0; g_phase_ns[1] = 0; }
+}
 
 void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
   if (!g_ode_inited) { dInitODE2(0); g_ode_inited = true; if (getenv("GZREF_TRACE")) signal(SIGSEGV, segv_handler); }

@@ -163,6 +163,12 @@ class RefBatch:
         """The plugin part of a step (PD torques, joint velocity commands) applied to the live ODE objects."""
         self.lib.gzref_plugin_update(self.h, world)
 
+    def phase_seconds(self, reset=False):
+        """Thread-seconds in UpdateCollision / UpdatePhysics since the last reset (all batches of this flavour)."""
+        out = (C.c_longlong * 2)()
+        self.lib.gzref_phase_ns(out, int(reset))
+        return out[0] * 1e-9, out[1] * 1e-9
+
     def set_joint_velocity_cmd(self, vel):
         vel = np.ascontiguousarray(vel, dtype=np.float64).reshape(self.scene.nj)
         self.lib.gzref_set_joint_velocity_cmd(self.h, _p(vel))

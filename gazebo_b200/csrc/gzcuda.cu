@@ -392,8 +392,9 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   // per body, so 2 x rows is the worst case; clamped to a quarter of the free memory (k_bsched flags a step
   // that does not fit).
   // <= 256 bodies: k_pgsb (warp or CTA per world); beyond: the body-owner sweeps over the whole GPU (k_pgsd: dataflow
-  // through L2 slots).  Round 1's row-slot kernels (worlds up to 512 bodies) remain behind GZCUDA_PGS_IMPL=0.
-  d.pgs_impl = (max_nb <= 256) ? 1 : 2;
+  // through L2 slots, one launch per world).  Batches of 8+ worlds of 257..512 bodies keep round 1's row-slot kernels
+  // (all worlds in one launch); GZCUDA_PGS_IMPL=0 forces them for any batch of worlds up to 512 bodies.
+  d.pgs_impl = (max_nb <= 256) ? 1 : ((max_nb <= 512 && W >= 8) ? 0 : 2);
   d.islands_hook = max_nb > 512;
   if (const char *e = getenv("GZCUDA_ISLANDS_HOOK")) d.islands_hook = atoi(e) != 0;   // developer / test switch
   if (const char *e = getenv("GZCUDA_PGS_IMPL")) {

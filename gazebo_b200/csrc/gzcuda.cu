@@ -937,7 +937,9 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   return 0;
 }
 
-static int run_steps(gzcuda_batch *b, int n_steps) {
+// wrench_in (host, [nb][6], may be null): added to the bodies' accumulators before the first step - uploaded and applied
+// on the auxiliary stream beside the first step's collision pipeline, ahead of the controllers as before
+static int run_steps(gzcuda_batch *b, int n_steps, const double *wrench_in = nullptr) {
   if (b->profiling) {
     while ((int)b->pgs_ev.size() < 2 * n_steps) {
       cudaEvent_t e;
@@ -957,13 +959,21 @@ static int run_steps(gzcuda_batch *b, int n_steps) {
     }
     // the plugin stand-in (PD torques into tacc) runs beside the collision pipeline, which does not read the
     // accumulators; k_assemble1 (body prologue) is the first kernel that does
-    const bool fork_ctl = b->have_pd;
+    const bool up = (s == 0 && wrench_in != nullptr);
+    const bool fork_ctl = b->have_pd || up;
     if (fork_ctl) {
       cudaEventRecord(b->ev_aux_fork, b->stream);
       cudaStreamWaitEvent(b->stream_aux, b->ev_aux_fork, 0);
-      k_control<<<cdiv(std::max(b->d.nb, 1), 64), 64, 0, b->stream_aux>>>(b->d);
+      if (up) {
+        CK(cudaMemcpyAsync(b->d.io_in, wrench_in, sizeof(double) * 6 * (size_t)b->d.nb, cudaMemcpyHostToDevice, b->stream_aux));
+        k_apply_wrench<<<cdiv(std::max(b->d.nb, 1), 128), 128, 0, b->stream_aux>>>(b->d);
+        b->last_launches++;
+      }
+      if (b->have_pd) {
+        k_control<<<cdiv(std::max(b->d.nb, 1), 64), 64, 0, b->stream_aux>>>(b->d);
+        b->last_launches++;
+      }
       cudaEventRecord(b->ev_aux_join, b->stream_aux);
-      b->last_launches++;
     }
     launch_collision(b);
     if (fork_ctl) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
@@ -995,12 +1005,12 @@ int gzcuda_batch_step_io(gzcuda_batch *b, int n_steps, const double *wrench_in, 
   const int T = 128, nb = std::max(b->d.nb, 1);
   b->last_launches = 0;
   CK(cudaEventRecord(b->ev0, b->stream));
-  if (wrench_in) {
+  if (wrench_in && n_steps == 0) {   // no step to run beside: apply at once
     CK(cudaMemcpyAsync(b->d.io_in, wrench_in, sizeof(double) * 6 * (size_t)b->d.nb, cudaMemcpyHostToDevice, b->stream));
     k_apply_wrench<<<cdiv(nb, T), T, 0, b->stream>>>(b->d);
     b->last_launches++;
   }
-  int rc = run_steps(b, n_steps);
+  int rc = run_steps(b, n_steps, wrench_in);
   if (rc) return rc;
   if (state_out) {
     k_gather_state<<<cdiv(nb, T), T, 0, b->stream>>>(b->d);

@@ -68,6 +68,10 @@ struct gzcuda_batch {
   int pgs_large_mode = 1;             // large worlds: 0 k_pgsl (rounds + grid barrier), 1 k_pgsd (dataflow through L2), 2 k_pgsc (+ cluster shared memory)
   int pgsc_grid = 0, pgsc_cluster = 1, pgsc_glob_every = 4, pgsc_sleep = 0;
   size_t pgsc_smem = 0;
+  bool pgsm = false;                  // k_pgsm: a world of up to 1024 bodies on one cluster, on chip (k_pgsd when it does not fit)
+  int pgsm_cluster = 1, pgsm_threads = 128;
+  size_t pgsm_smem = 0;
+  int *pgsm_done = nullptr;
   bool large_kernels = false;         // k_contacts_large / k_assemble1_large (cooperative grid) instead of the one-CTA-per-world kernels
   int large_grid = 0;
   int *large_part = nullptr;
@@ -507,6 +511,38 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         if ((rc = dev_alloc(b, &d.ent_aux, (size_t)d.ent_cap))) return rc;
       }
     }
+    if (d.pgs_impl == 2 && b->pgs_large_mode == 1 && max_nb <= 1024 && !(getenv("GZCUDA_PGSM") && atoi(getenv("GZCUDA_PGSM")) == 0)) {
+      // k_pgsm: 64 (up to 512 bodies) or 128 bodies per CTA, one cluster of up to 8 CTAs, the world's entries in shared memory
+      int per = max_nb <= 512 ? 64 : 128;
+      if (const char *ep = getenv("GZCUDA_PGSM_PER")) { const int v = atoi(ep); if ((v == 32 || v == 64 || v == 128) && cdiv_host(std::max(max_nb, 1), v) <= 16) per = v; }
+      const int ncta = cdiv_host(std::max(max_nb, 1), per);
+      int cl = 1;
+      while (cl < ncta) cl <<= 1;
+      b->pgsm_cluster = cl; b->pgsm_threads = 2 * per;
+      b->pgsm_smem = std::min((size_t)200 * 1024, (((size_t)GZ_PGSM_BYTES * d.ent_cap + 1023) / 1024) * 1024);
+      bool ok = cl <= 16;
+      for (int v = 0; v < 2 && ok; v++) {
+        const void *fn = v ? (const void *)k_pgsm<true> : (const void *)k_pgsm<false>;
+        ok = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->pgsm_smem) == cudaSuccess;
+        if (ok && cl > 8) ok = cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+        if (!ok) break;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(cl); cfg.blockDim = dim3(b->pgsm_threads); cfg.dynamicSmemBytes = b->pgsm_smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int n_clusters = 0;
+        ok = cudaOccupancyMaxActiveClusters(&n_clusters, fn, &cfg) == cudaSuccess && n_clusters >= 1;
+      }
+      cudaGetLastError();
+      if (ok) {
+        b->pgsm = true;
+        d.pgsc_bodies = per; d.pgsc_bpw = 16;
+        if ((rc = dev_alloc(b, &d.cta_e0, (size_t)W * GZ_PGSC_TAB))) return rc;
+        if ((rc = dev_alloc(b, &b->pgsm_done, (size_t)W))) return rc;
+      }
+    }
     if ((rc = dev_alloc(b, &d.ent_cursor, (size_t)2))) return rc;
     if ((rc = dev_alloc(b, &d.bsched, (size_t)nb))) return rc;
     if ((rc = dev_alloc(b, &d.wsb, (size_t)W))) return rc;
@@ -839,12 +875,29 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
           const int smem_entries = (int)(b->pgsc_smem / 64), glob_every = b->pgsc_glob_every - 1, sleep_ns = b->pgsc_sleep;
           if (box) cudaLaunchKernelEx(&cfg, k_pgsc<true>, d, w, b->pgsd_slots, tab, ep, smem_entries, glob_every, sleep_ns);
           else cudaLaunchKernelEx(&cfg, k_pgsc<false>, d, w, b->pgsd_slots, tab, ep, smem_entries, glob_every, sleep_ns);
-          k_pgs_large_stats<<<b->pgsl_grid, 256, 0, b->stream>>>(d, w, partial, ticket, epoch);
+          k_pgs_large_stats<<<b->pgsl_grid, 256, 0, b->stream>>>(d, w, partial, ticket, epoch, (const int *)nullptr);
           b->last_launches++;
           continue;
         }
-        void *args[] = {(void *)&d, (void *)&w, (void *)&b->pgsd_slots, (void *)&partial, (void *)&epoch};
+        const int *skip = nullptr;
+        if (b->pgsm) {
+          cudaLaunchConfig_t cfg = {};
+          cfg.gridDim = dim3(b->pgsm_cluster); cfg.blockDim = dim3(b->pgsm_threads); cfg.dynamicSmemBytes = b->pgsm_smem; cfg.stream = b->stream;
+          cudaLaunchAttribute at[1];
+          at[0].id = cudaLaunchAttributeClusterDimension;
+          at[0].val.clusterDim.x = b->pgsm_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+          cfg.attrs = at; cfg.numAttrs = 1;
+          const int *tab = d.cta_e0 + (size_t)w * GZ_PGSC_TAB;
+          const int smem_entries = (int)(b->pgsm_smem / GZ_PGSM_BYTES) & ~1;   // (even: the arrays behind the inboxes stay 16-byte aligned)
+          int *done = b->pgsm_done + w;
+          if (box) cudaLaunchKernelEx(&cfg, k_pgsm<true>, d, w, tab, smem_entries, done);
+          else cudaLaunchKernelEx(&cfg, k_pgsm<false>, d, w, tab, smem_entries, done);
+          skip = done;
+          b->last_launches += 2;
+        }
+        void *args[] = {(void *)&d, (void *)&w, (void *)&b->pgsd_slots, (void *)&partial, (void *)&epoch, (void *)&skip};
         cudaLaunchCooperativeKernel(box ? (void *)k_pgsd<true> : (void *)k_pgsd<false>, dim3(b->pgsl_grid), dim3(256), args, 0, b->stream);
+        if (b->pgsm) k_pgs_large_stats<<<b->pgsl_grid, 256, 0, b->stream>>>(d, w, partial, ticket, epoch, skip);
       }
       for (int w = 0; w < W && !d.pgs_dataflow; w++) {
         double *xch = d.xch_g, *partial = d.xch_g + (size_t)2 * b->pgsl_grid * 256;

@@ -589,6 +589,7 @@ __global__ void k_rowfinish(DevBatch B) {
 #include "k_pgsl.cuh"
 #include "k_pgsc.cuh"
 #include "k_large.cuh"
+#include "k_pgsm.cuh"
 namespace gz {
 
 // One thread per joint: save lambda for the next step's warm start.

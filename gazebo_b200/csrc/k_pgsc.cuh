@@ -232,7 +232,8 @@ __global__ void __launch_bounds__(256, 2) k_pgsc(DevBatch B, const int w, unsign
 // After k_pgsc (stream order): lambda back to the rows and the statistics of the last update of every row
 // (quickstep_pgs_lcp.cpp:700-760, 814-855), over all entries of the world with all lanes.  Deterministic: lanes of a
 // warp, warps of a CTA in order, and the CTA that arrives last adds the CTAs' partial sums in index order.
-__global__ void __launch_bounds__(256) k_pgs_large_stats(DevBatch B, const int w, double *partial, unsigned *ticket, unsigned *epoch_ctr) {
+__global__ void __launch_bounds__(256) k_pgs_large_stats(DevBatch B, const int w, double *partial, unsigned *ticket, unsigned *epoch_ctr, const int *only_if) {
+  if (only_if && !*only_if) return;   // (k_pgsd has run instead of k_pgsm and has done this itself)
   const int gl = blockIdx.x * blockDim.x + threadIdx.x, L = gridDim.x * blockDim.x;
   const WorldInfo wi = B.world[w];
   const int4 sc = B.wsb[w];

@@ -399,9 +399,10 @@ __device__ __forceinline__ bool slot_get(const unsigned long long *s, unsigned t
 }
 
 template <bool BOX>
-__global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned long long *slots, double *partial, unsigned *epoch_ctr) {
+__global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned long long *slots, double *partial, unsigned *epoch_ctr, const int *skip) {
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
+  if (skip && *skip) return;   // k_pgsm (one cluster, on chip) has taken the world this step
   const unsigned epoch = *epoch_ctr;   // (advanced by the last lane standing, after everybody has read it)
   const int gl = blockIdx.x * blockDim.x + threadIdx.x, L = gridDim.x * blockDim.x;
   const int bl = gl >> 1, S = gl & 1;

@@ -68,7 +68,7 @@ struct gzcuda_batch {
   int pgs_large_mode = 1;             // large worlds: 0 k_pgsl (rounds + grid barrier), 1 k_pgsd (dataflow through L2), 2 k_pgsc (+ cluster shared memory)
   int pgsc_grid = 0, pgsc_cluster = 1, pgsc_glob_every = 4, pgsc_sleep = 0;
   size_t pgsc_smem = 0;
-  bool pgsm = false;                  // k_pgsm: a world of up to 1024 bodies on one cluster, on chip (k_pgsd when it does not fit)
+  bool pgsm = false;                  // k_pgsm: a world of up to 2048 bodies on one cluster, on chip (k_pgsd when it does not fit)
   int pgsm_cluster = 1, pgsm_threads = 128;
   size_t pgsm_smem = 0;
   int *pgsm_done = nullptr;
@@ -511,15 +511,16 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         if ((rc = dev_alloc(b, &d.ent_aux, (size_t)d.ent_cap))) return rc;
       }
     }
-    if (d.pgs_impl == 2 && b->pgs_large_mode == 1 && max_nb <= 1024 && !(getenv("GZCUDA_PGSM") && atoi(getenv("GZCUDA_PGSM")) == 0)) {
-      // k_pgsm: 64 (up to 512 bodies) or 128 bodies per CTA, one cluster of up to 8 CTAs, the world's entries in shared memory
-      int per = max_nb <= 512 ? 64 : 128;
+    if (d.pgs_impl == 2 && b->pgs_large_mode == 1 && max_nb <= 2048 && !(getenv("GZCUDA_PGSM") && atoi(getenv("GZCUDA_PGSM")) == 0)) {
+      // k_pgsm: 64 (up to 1024 bodies) or 128 bodies per CTA, one cluster of up to 16 CTAs (more than 8: non-portable
+      // size, B200 allows it), the world's entries in shared memory
+      int per = max_nb <= 1024 ? 64 : 128;
       if (const char *ep = getenv("GZCUDA_PGSM_PER")) { const int v = atoi(ep); if ((v == 32 || v == 64 || v == 128) && cdiv_host(std::max(max_nb, 1), v) <= 16) per = v; }
       const int ncta = cdiv_host(std::max(max_nb, 1), per);
       int cl = 1;
       while (cl < ncta) cl <<= 1;
       b->pgsm_cluster = cl; b->pgsm_threads = 2 * per;
-      b->pgsm_smem = std::min((size_t)200 * 1024, (((size_t)GZ_PGSM_BYTES * d.ent_cap + 1023) / 1024) * 1024);
+      b->pgsm_smem = std::min((size_t)224 * 1024, (((size_t)GZ_PGSM_BYTES * d.ent_cap + 1023) / 1024) * 1024);
       bool ok = cl <= 16;
       for (int v = 0; v < 2 && ok; v++) {
         const void *fn = v ? (const void *)k_pgsm<true> : (const void *)k_pgsm<false>;

@@ -63,6 +63,7 @@ def lib():
     L.gzcuda_batch_set_param.argtypes = [vp, C.c_char_p, C.c_double]
     L.gzcuda_batch_get_pairs.argtypes = [vp, ci, dp, ci]
     L.gzcuda_batch_get_contacts.argtypes = [vp, ci, dp, dp, ci]
+    L.gzcuda_batch_ray_query.argtypes = [vp, ci, dp, dp, dp, dp, dp, dp]
     L.gzcuda_batch_get_joint_feedback.argtypes = [vp, dp]
     L.gzcuda_batch_get_contact_feedback.argtypes = [vp, ci, dp, ci]
     L.gzcuda_batch_get_joint_feedback_noalloc.argtypes = [vp, dp]
@@ -85,7 +86,7 @@ EXPORTS = [
     "gzcuda_batch_get_pgs_profile", "gzcuda_batch_get_pgs_timeline",
     "gzcuda_batch_get_joint_feedback", "gzcuda_batch_get_contact_feedback", "gzcuda_batch_step_log",
     "gzcuda_batch_set_joint_velocity_cmd", "gzcuda_batch_get_joint_feedback_noalloc",
-    "gzcuda_batch_set_body_state_raw", "gzcuda_batch_set_body_enabled",
+    "gzcuda_batch_set_body_state_raw", "gzcuda_batch_set_body_enabled", "gzcuda_batch_ray_query",
 ]
 
 
@@ -221,6 +222,18 @@ class Batch:
         out = np.empty((cap, 2), dtype=np.int32)
         n = self._ck(self.L.gzcuda_batch_get_pairs(self.h, world, _p(out), cap))
         return out[:n].copy()
+
+    def ray_query(self, world, start, direction, length):
+        """The CPU laser on the device (gzcuda_batch_ray_query): world = one index for all rays or one per ray.
+        Returns (range [n], world-local geom index of the hit or -1 [n])."""
+        start = np.ascontiguousarray(start, dtype=np.float64).reshape(-1, 3)
+        direction = np.ascontiguousarray(direction, dtype=np.float64).reshape(-1, 3)
+        length = np.ascontiguousarray(length, dtype=np.float64).reshape(-1)
+        n = len(length)
+        worlds = np.ascontiguousarray(np.broadcast_to(np.asarray(world, dtype=np.int32), (n,)))
+        rng, geom = np.empty(n), np.empty(n, dtype=np.int32)
+        self._ck(self.L.gzcuda_batch_ray_query(self.h, n, _p(worlds), _p(start), _p(direction), _p(length), _p(rng), _p(geom)))
+        return rng, geom
 
     def contacts(self, world, cap=1 << 16):
         g = np.empty((cap, 2), dtype=np.int32)

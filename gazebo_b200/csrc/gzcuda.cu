@@ -14,6 +14,7 @@
 #include "../../include/gzcuda.h"
 #include "k_collide.cuh"
 #include "k_bpl.cuh"
+#include "k_ray.cuh"
 #include "k_pgs.cuh"
 
 using namespace gz;
@@ -68,6 +69,8 @@ struct gzcuda_batch {
   int pgs_large_mode = 1;             // large worlds: 0 k_pgsl (rounds + grid barrier), 1 k_pgsd (dataflow through L2), 2 k_pgsc (+ cluster shared memory)
   int pgsc_grid = 0, pgsc_cluster = 1, pgsc_glob_every = 4, pgsc_sleep = 0;
   size_t pgsc_smem = 0;
+  void *ray_buf = nullptr;            // gzcuda_batch_ray_query's device buffers
+  int ray_cap = 0;
   bool pgsm = false;                  // k_pgsm: a world of up to 2048 bodies on one cluster, on chip (k_pgsd when it does not fit)
   int pgsm_cluster = 1, pgsm_threads = 128;
   size_t pgsm_smem = 0;
@@ -1449,6 +1452,37 @@ int gzcuda_batch_get_pairs(gzcuda_batch *b, int world, int *pairs, int cap) {
     pairs[2 * i + 1] = hp[2 * i + 1] - wi.geom0;
   }
   return ws.n_pairs;
+}
+
+int gzcuda_batch_ray_query(gzcuda_batch *b, int n_rays, const int *ray_world, const double *start, const double *dir,
+                           const double *length, double *out_range, int *out_geom) {
+  if (!b || n_rays < 0 || (n_rays > 0 && (!ray_world || !start || !dir || !length || !out_range))) return fail(GZCUDA_E_INVALID, "null argument");
+  if (n_rays == 0) return 0;
+  for (int k = 0; k < n_rays; k++)
+    if (ray_world[k] < 0 || ray_world[k] >= b->d.n_worlds) return fail(GZCUDA_E_INVALID, "ray in a world the batch does not have");
+  CK(cudaSetDevice(b->device));
+  // scan buffers grow with the largest scan asked for and are kept
+  if (n_rays > b->ray_cap) {
+    if (b->ray_buf) cudaFree(b->ray_buf);
+    b->ray_buf = nullptr; b->ray_cap = 0;
+    CK(cudaMalloc((void **)&b->ray_buf, (size_t)n_rays * (8 * sizeof(double) + 2 * sizeof(int))));
+    b->ray_cap = n_rays;
+  }
+  const size_t n = (size_t)n_rays;
+  double *d_start = reinterpret_cast<double *>(b->ray_buf), *d_dir = d_start + 3 * n, *d_len = d_dir + 3 * n, *d_range = d_len + n;
+  int *d_world = reinterpret_cast<int *>(d_range + n), *d_geom = d_world + n;
+  CK(cudaMemcpyAsync(d_start, start, 3 * n * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(d_dir, dir, 3 * n * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(d_len, length, n * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaMemcpyAsync(d_world, ray_world, n * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+  k_geom<<<cdiv(std::max(b->d.ng, 1), 128), 128, 0, b->stream>>>(b->d);   // poses and AABBs as of now (idempotent)
+  RayQuery Q;
+  Q.n = n_rays; Q.world = d_world; Q.start = d_start; Q.dir = d_dir; Q.length = d_len; Q.out_range = d_range; Q.out_geom = d_geom;
+  k_rays<<<std::min(cdiv(n_rays, 8), 148 * 8), 256, 0, b->stream>>>(b->d, Q);
+  CK(cudaMemcpyAsync(out_range, d_range, n * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+  if (out_geom) CK(cudaMemcpyAsync(out_geom, d_geom, n * sizeof(int), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaGetLastError());
+  return check_sticky(b);   // synchronises
 }
 
 int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *data, int cap) {

@@ -118,6 +118,14 @@ int gzcuda_batch_set_param(gzcuda_batch *b, const char *key, double value);
  * as world-local geom indices [n][2] sorted ascending, and its contacts: geoms[n][2] and
  * data[n][7] = position(3), normal(3), depth.  Return the count (or a negative error). */
 int gzcuda_batch_get_pairs(gzcuda_batch *b, int world, int *pairs, int cap);
+/* Ray queries against the CURRENT geometry of the worlds (poses as of the last step or setter): the CPU laser,
+ * gazebo::physics::ODEMultiRayShape::UpdateRays / UpdateCallback (gazebo/physics/ode/ODEMultiRayShape.cc:82-205) over
+ * ODE's ray colliders (deps/opende/src/ray.cpp:200-703).  n_rays rays, ray k in world ray_world[k] from start[k] along
+ * dir[k] (any length: normalised as dGeomRaySet does) up to length[k]; rays carry GZ_SENSOR_COLLIDE bits and ride on no
+ * body, as ODERayShape's do.  out_range[k] = distance to the nearest hit, or length[k]; out_geom[k] = world-local index of
+ * the geom hit, or -1 (may be NULL).  Host arrays; one kernel, one warp per ray. */
+int gzcuda_batch_ray_query(gzcuda_batch *b, int n_rays, const int *ray_world, const double *start, const double *dir,
+                           const double *length, double *out_range, int *out_geom);
 int gzcuda_batch_get_contacts(gzcuda_batch *b, int world, int *geoms, double *data, int cap);
 
 /* Constraint wrenches of the last step (dJointFeedback {f1[3], t1[3], f2[3], t2[3]}, world frame:

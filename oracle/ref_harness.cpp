@@ -417,7 +417,73 @@ void step_world(RefBatch *B, RefWorld *w) {
 
 }  // namespace
 
+// ---- the CPU laser: ODEMultiRayShape::UpdateRays / UpdateCallback (gazebo/physics/ode/ODEMultiRayShape.cc:82-205) and
+// ODERayShape (ODERayShape.cc:36-60, 95-122) restated through the ODE API; the ray colliders are the reference's
+// (deps/opende/src/ray.cpp) ----
+struct RayScan {
+  dSpaceID super = nullptr, raySpace = nullptr;
+  std::vector<dGeomID> rays;
+  std::vector<double> length;
+  std::vector<int> hit;
+};
+
+void ray_callback(void *data, dGeomID o1, dGeomID o2) {
+  RayScan *self = static_cast<RayScan *>(data);
+  if (dGeomIsSpace(o1) || dGeomIsSpace(o2)) {
+    if (dGeomGetSpace(o1) == self->super || dGeomGetSpace(o2) == self->super) dSpaceCollide2(o1, o2, self, &ray_callback);
+    if (dGeomGetSpace(o1) == self->raySpace || dGeomGetSpace(o2) == self->raySpace) dSpaceCollide2(o1, o2, self, &ray_callback);
+    return;
+  }
+  dGeomID ray = nullptr, other = nullptr;
+  if (dGeomGetClass(o1) == dRayClass) { ray = o1; other = o2; }
+  else if (dGeomGetClass(o2) == dRayClass) { ray = o2; other = o1; }
+  if (!ray || dGeomGetClass(other) == dRayClass) return;
+  dGeomRaySetParams(ray, 0, 0);
+  dGeomRaySetClosestHit(ray, 1);
+  dContactGeom contact;
+  const int n = dCollide(o1, o2, 1, &contact, sizeof(contact));
+  const int k = (int)(intptr_t)dGeomGetData(ray);
+  if (n > 0 && contact.depth < self->length[k]) {   // shape->SetLength(contact.depth): RayShape::contactLen only, the ODE ray keeps its length
+    self->length[k] = contact.depth;
+    self->hit[k] = geom_index(other);
+  }
+}
+
 extern "C" {
+
+// n rays of ONE world against its current geometry (the rays ride on no body: ODERayShape never calls dGeomSetBody,
+// so a laser sees its own link's collisions too).  out_range = the ray's length after the scan, out_geom = the
+// world-local geom index of the last shortening hit or -1.
+int gzref_ray_query(void *h, int world, int n, const double *start, const double *dir, const double *length,
+                    double *out_range, int *out_geom) {
+  RefBatch *B = static_cast<RefBatch *>(h);
+  if (!B || world < 0 || world >= (int)B->worlds.size()) return -1;
+  RefWorld *w = B->worlds[world];
+  RayScan S;
+  S.super = dSimpleSpaceCreate(0);
+  S.raySpace = dSimpleSpaceCreate(S.super);
+  dGeomSetCategoryBits((dGeomID)S.raySpace, 0x00000002);       // GZ_SENSOR_COLLIDE
+  dGeomSetCollideBits((dGeomID)S.raySpace, ~0x00000002u);
+  S.length.assign(length, length + n);
+  S.hit.assign(n, -1);
+  for (int k = 0; k < n; k++) {
+    dGeomID r = dCreateRay(S.raySpace, length[k]);
+    dGeomSetCategoryBits(r, 0x00000002);
+    dGeomSetCollideBits(r, ~0x00000002u);
+    dGeomSetData(r, (void *)(intptr_t)k);
+    S.rays.push_back(r);
+  }
+  for (int k = 0; k < n; k++) {
+    dGeomRaySet(S.rays[k], start[3 * k], start[3 * k + 1], start[3 * k + 2], dir[3 * k], dir[3 * k + 1], dir[3 * k + 2]);
+    dGeomRaySetLength(S.rays[k], length[k]);
+  }
+  dSpaceCollide2((dGeomID)S.super, (dGeomID)w->top, &S, &ray_callback);
+  for (int k = 0; k < n; k++) { out_range[k] = S.length[k]; out_geom[k] = S.hit[k]; }
+  for (dGeomID r : S.rays) dGeomDestroy(r);
+  dSpaceDestroy(S.raySpace);
+  dSpaceDestroy(S.super);
+  return 0;
+}
 
 // Thread-nanoseconds spent in UpdateCollision / UpdatePhysics since the last call with reset != 0.
 void gzref_phase_ns(long long out[2], int reset) {

@@ -42,6 +42,7 @@ def _load(flavour):
     lib.gzref_destroy.argtypes = [C.c_void_p]
     lib.gzref_set_hinge_pd.argtypes = [C.c_void_p, C.c_void_p]
     lib.gzref_step.argtypes = [C.c_void_p, C.c_int]
+    lib.gzref_ray_query.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gzref_step_mt.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.gzref_collide.argtypes = [C.c_void_p, C.c_int]
     lib.gzref_get_pairs.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
@@ -162,6 +163,19 @@ class RefBatch:
     def plugin_update(self, world):
         """The plugin part of a step (PD torques, joint velocity commands) applied to the live ODE objects."""
         self.lib.gzref_plugin_update(self.h, world)
+
+    def ray_query(self, world, start, direction, length):
+        """The CPU laser (ODEMultiRayShape::UpdateRays restated over the reference's ray colliders): rays of ONE world.
+        Returns (range [n], world-local geom index of the hit or -1 [n])."""
+        start = np.ascontiguousarray(start, dtype=np.float64).reshape(-1, 3)
+        direction = np.ascontiguousarray(direction, dtype=np.float64).reshape(-1, 3)
+        length = np.ascontiguousarray(length, dtype=np.float64).reshape(-1)
+        n = len(length)
+        rng, geom = np.empty(n), np.empty(n, dtype=np.int32)
+        rc = self.lib.gzref_ray_query(C.c_void_p(self.h), int(world), n, _p(start), _p(direction), _p(length), _p(rng), _p(geom))
+        if rc != 0:
+            raise RuntimeError("gzref_ray_query failed")
+        return rng, geom
 
     def phase_seconds(self, reset=False):
         """Thread-seconds in UpdateCollision / UpdatePhysics since the last reset (all batches of this flavour)."""

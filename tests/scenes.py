@@ -319,6 +319,44 @@ def fdir1():
     return sb.finish(), S.default_params(), None
 
 
+def ray_targets(n_worlds=2, per_type=6, seed=77):
+    """Worlds for the laser: a ground plane and, floating at rest (no gravity flag needed: they are never stepped far), boxes,
+    spheres, capsules and cylinders at random poses inside a 6 m cube, one sensor-category geom that rays must not see."""
+    sb = S.SceneBuilder()
+    for w in range(n_worlds):
+        rng = np.random.Generator(np.random.PCG64(seed + w))
+        sb.begin_world()
+        sb.add_ground_plane()
+        for k in range(4 * per_type):
+            pos = rng.uniform(-3, 3, 3) + np.array([0, 0, 3.5])
+            q = S.q_random(rng)
+            t = k % 4
+            if t == 0:
+                dims = tuple(rng.uniform(0.2, 1.0, 3)); b = sb.add_body(pos, q, 1.0, S.box_inertia(1.0, *dims)); sb.add_geom(S.GEOM_BOX, dims, sb.new_space(), body=b)
+            elif t == 1:
+                r = rng.uniform(0.1, 0.6); b = sb.add_body(pos, q, 1.0, S.sphere_inertia(1.0, r)); sb.add_geom(S.GEOM_SPHERE, (r,), sb.new_space(), body=b)
+            elif t == 2:
+                r, l = rng.uniform(0.1, 0.4), rng.uniform(0.2, 1.2); b = sb.add_body(pos, q, 1.0, S.cylinder_inertia(1.0, r, l)); sb.add_geom(S.GEOM_CAPSULE, (r, l), sb.new_space(), body=b)
+            else:
+                r, l = rng.uniform(0.1, 0.5), rng.uniform(0.2, 1.2); b = sb.add_body(pos, q, 1.0, S.cylinder_inertia(1.0, r, l)); sb.add_geom(S.GEOM_CYLINDER, (r, l), sb.new_space(), body=b)
+        # a big box of the sensor category right in the middle (GZ_SENSOR_COLLIDE = 2, collides with nothing of its kind): invisible to the rays
+        sb.add_geom(S.GEOM_BOX, (2.0, 2.0, 2.0), sb.new_space(), pos=(0, 0, 3.5), category_bits=0x2, collide_bits=0xFFFFFFFD)
+        sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
+def laser_rays(n, seed=5):
+    """n rays: origins inside and around the 6 m cube of ray_targets (some inside shapes), random directions of random
+    length (dGeomRaySet normalises), lengths 0.5..12 m; a few axis-parallel ones (the colliders' parallel branches)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    start = rng.uniform(-4, 4, (n, 3)) + np.array([0, 0, 3.5])
+    d = rng.normal(size=(n, 3)) * rng.uniform(0.1, 5.0, (n, 1))
+    for k in range(0, n, 17):
+        d[k] = 0.0; d[k, (k // 17) % 3] = 1.0 if (k // 51) % 2 == 0 else -1.0
+    length = rng.uniform(0.5, 12.0, n)
+    return start, d, length
+
+
 GOLDEN = {
     "box_drop": (box_drop, 1500),
     "tilted_box": (tilted_box, 600),

@@ -167,3 +167,24 @@ def test_feedback_of_a_hanging_chain(oracle):
     two = np.linalg.norm(fb[:, 6:9], axis=1) > 0           # joints between two links (the others hang from the world)
     assert two.sum() >= fb.shape[0] - 4
     assert np.abs(fb[two, 0:3] + fb[two, 6:9]).max() < 1e-9 * max(1.0, np.abs(fb).max())
+
+
+def test_laser_oracle_known_answers(oracle):
+    """gzref_ray_query (ODEMultiRayShape::UpdateRays restated over the reference's own ray colliders): closed-form cases."""
+    from gazebo_b200 import scene as S
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_ground_plane()
+    b = sb.add_body((0, 0, 1.0), (1, 0, 0, 0), 1.0, S.sphere_inertia(1.0, 0.5))
+    sb.add_geom(S.GEOM_SPHERE, (0.5,), sb.new_space(), body=b)
+    b2 = sb.add_body((3, 0, 0.5), (1, 0, 0, 0), 1.0, S.box_inertia(1.0, 1, 1, 1))
+    sb.add_geom(S.GEOM_BOX, (1, 1, 1), sb.new_space(), body=b2)
+    sb.end_world()
+    sc = sb.finish()
+    r = oracle.RefBatch(sc, S.default_params(), mode=1)
+    start = np.array([[-5, 0, 1.0], [-5, 0, 0.25], [0, 0, 5], [0, 5, 5], [0, 5, 5], [3, 0, 0.5]])
+    d = np.array([[1, 0, 0], [2, 0, 0], [0, 0, -1], [0, 0, -2.0], [0, 0, 1.0], [0, 1, 0]])
+    L = np.array([20.0, 20, 20, 20, 7, 20])
+    rng, geom = r.ray_query(0, start, d, L)
+    assert np.allclose(rng, [4.5, 7.5, 3.5, 5.0, 7.0, 0.5], atol=1e-12)   # sphere front, box front, sphere top, plane, nothing, box from inside
+    assert geom.tolist() == [1, 2, 1, 0, -1, 2]

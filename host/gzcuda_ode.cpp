@@ -505,4 +505,18 @@ int gzcuda_dworld_get_contacts(dxWorld *world, dxGeom **geoms, double *data, int
   return n;
 }
 
+int gzcuda_dworld_ray_query(dxWorld *world, int n, const double *start, const double *dir, const double *length,
+                            double *range, dxGeom **hit) {
+  auto it = g_mirrors.find(world);
+  if (it == g_mirrors.end() || !it->second->batch) return fail(GZCUDA_E_INVALID, "world is not mirrored");
+  Mirror *m = it->second;
+  if (n <= 0) return 0;
+  std::vector<int> w((size_t)n, 0), gi((size_t)n, -1);
+  const int rc = gzcuda_batch_ray_query(m->batch, n, w.data(), start, dir, length, range, gi.data());
+  if (rc < 0) return fail_lib("gzcuda_batch_ray_query");
+  if (hit)
+    for (int k = 0; k < n; k++) hit[k] = gi[k] >= 0 ? m->geoms[gi[k]] : nullptr;
+  return 0;
+}
+
 }  // extern "C"

@@ -55,6 +55,12 @@ void gzcuda_topology_changed(struct dxWorld *world);
 /* Contacts of the last gzcuda_dspace_collide, for ContactManager (ODEPhysics.cc:1262-1329): geoms[n][2] (dxGeom*),
  * data[n][7] = pos, normal, depth.  Returns the count. */
 int gzcuda_dworld_get_contacts(struct dxWorld *world, struct dxGeom **geoms, double *data, int cap);
+/* The CPU laser against the world as of the last gzcuda_dspace_collide / gzcuda_dworld_step: what
+ * ODEMultiRayShape::UpdateRays does with dSpaceCollide2(raySpace, worldSpace) (ODEMultiRayShape.cc:82-205) - n rays from
+ * start[k] along dir[k] up to length[k]; range[k] = distance to the nearest hit or length[k], hit[k] = the dxGeom hit or
+ * NULL (may be NULL itself).  Returns 0 or a negative error. */
+int gzcuda_dworld_ray_query(struct dxWorld *world, int n, const double *start, const double *dir, const double *length,
+                            double *range, struct dxGeom **hit);
 /* Frees the mirror and its device batch (ODEPhysics::Fini). */
 void gzcuda_dworld_release(struct dxWorld *world);
 const char *gzcuda_ode_last_error(void);

@@ -34,6 +34,7 @@ def adapter(oracle):
     L.gzcuda_dworld_step.argtypes = [vp, C.c_double]
     L.gzcuda_dworld_release.argtypes = [vp]
     L.gzcuda_topology_changed.argtypes = [vp]
+    L.gzcuda_dworld_ray_query.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
     L.gzcuda_ode_last_error.restype = C.c_char_p
     return L
 
@@ -99,3 +100,31 @@ def test_adapter_sleep_flags_and_wake_up(adapter, oracle):
     sc, p, _ = scenes.sleepers()
     live, ref = _run(adapter, oracle, sc, p, steps=2400, every=200)
     assert live.body_flags()[1:4].all()
+
+
+@pytest.mark.gpu
+def test_adapter_laser_over_live_ode_objects(adapter, oracle):
+    """gzcuda_dworld_ray_query: the laser against a LIVE ODE world (what ODEMultiRayShape::UpdateRays does with
+    dSpaceCollide2) - ranges bit-exact against the reference's own ray colliders on the same objects, and the dxGeom
+    handed back is the one the reference hits."""
+    sc, p, _ = scenes.ray_targets(n_worlds=1)
+    live = oracle.RefBatch(sc, p, mode=1)
+    world, top, user = live.world_handles(0)
+    adapter.gzcuda_ode_set_surface_callback(world, live.surface_cb_address(), user)
+    adapter.gzcuda_ode_set_max_contacts(world, p.max_contacts)
+    try:
+        for k in range(20):   # let the shapes move a little: the adapter mirrors the ODE objects' poses
+            assert adapter.gzcuda_dspace_collide(top, world) == 0, adapter.gzcuda_ode_last_error()
+            assert adapter.gzcuda_dworld_step(world, p.step_size) == 1, adapter.gzcuda_ode_last_error()
+        assert adapter.gzcuda_dspace_collide(top, world) == 0
+        start, d, length = scenes.laser_rays(2000)
+        start, d, length = np.ascontiguousarray(start), np.ascontiguousarray(d), np.ascontiguousarray(length)
+        rng = np.empty(len(length)); hit = (C.c_void_p * len(length))()
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        assert adapter.gzcuda_dworld_ray_query(world, len(length), vp(start), vp(d), vp(length), vp(rng), hit) == 0, adapter.gzcuda_ode_last_error()
+        rr, gr = live.ray_query(0, start, d, length)     # the reference's colliders on the same live objects
+        assert np.array_equal(rng, rr)
+        assert sum(1 for k in range(len(length)) if (hit[k] is not None) != (gr[k] >= 0)) == 0
+        assert (gr >= 0).sum() > 300
+    finally:
+        adapter.gzcuda_dworld_release(world)

@@ -14,7 +14,8 @@ UpdatePhysics) of every world of the batch.  One JSON line is printed by rank 0.
          per-body wrench array and downloads every body's pose + velocity
   roofline      k_pgsb: algorithmic bytes (288 B per row per sweep) / launch time
   strong        (N > 1) the same 4096 worlds split over the N ranks
-  --config c4   a second line for BASELINE.json configs[3] (ONE world: a 20 000-body rubble pile), same keys
+  --config c1   a line for BASELINE.json configs[0] (ONE world: 500 boxes), same keys
+  --config c4   a line for BASELINE.json configs[3] (ONE world: a 20 000-body rubble pile), same keys
   cpu_baseline  the reference's opende (oracle/_ref, -O3 -msse2 -DODE_SSE, natural gzserver
                 order, dWorldQuickStep) on this box's host cores, bounded sample
 """
@@ -288,7 +289,8 @@ def run_gpu(args, rank, world, local_rank):
 
 
 def run_c4(args, rank, world, local_rank):
-    """--config c4: BASELINE.json configs[3], ONE world - a 20 000-body rubble pile in a walled pen - on one GPU (under
+    """--config c1: BASELINE.json configs[0], ONE world - 500 boxes dropped on the plane, auto-disable on, timed once the
+    pile has settled (warm-up >= 1500 steps); --config c4: BASELINE.json configs[3], ONE world - a 20 000-body rubble pile in a walled pen - on one GPU (under
     torchrun every rank steps its own replica: a single world does not shard).  The timed region starts once the pile
     has formed (warm-up >= 2500 steps).  cpu_baseline: the reference's opende created from the GPU's body states at that
     moment (it would need ~20 minutes to get there itself) and timed over a few steps on one thread."""
@@ -313,11 +315,12 @@ def run_c4(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    n_bodies = args.bodies
-    sc = W.rubble_world(n_bodies)
+    c1 = args.config == "c1"
+    n_bodies = 500 if c1 else args.bodies
+    sc = W.box_drop_worlds(1, n_bodies) if c1 else W.rubble_world(n_bodies)
     p = S.default_params()
     b = Batch(sc, p, device=local_rank)
-    K, Wm = args.steps, max(args.warmup, 2500)
+    K, Wm = args.steps, max(args.warmup, 1500 if c1 else 2500)
     b.step(Wm)
     b.sync()
     b.counters(reset=True)
@@ -359,18 +362,20 @@ def run_c4(args, rank, world, local_rank):
     achieved = bytes_per_launch / (pgs_avg_ms * 1e-3) / 1e9 if pgs_avg_ms > 0 else 0.0
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "pgs_traffic_c4.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "pgs_traffic_c1.json" if c1 else "pgs_traffic_c4.json")) as f:
             traffic = json.load(f).get("dram_bytes_per_launch")
     except Exception:
         pass
     unit = "world-steps/s"
     line = {
-        "metric": "world-steps/sec (20k-body rubble pile, one world)", "value": value, "unit": unit, "n_gpus": world, "steps": K,
+        "metric": "world-steps/sec (500 boxes, one world)" if c1 else "world-steps/sec (20k-body rubble pile, one world)", "value": value, "unit": unit, "n_gpus": world, "steps": K,
         "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "replicas only", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "configs[3]: ONE world, %d-body mixed box / sphere / capsule rubble pile in a walled pen on a plane, one "
-                               "island once formed; ODE quickstep 50+10 iters, dt=1ms, deterministic row-order mode; a single world does "
-                               "not shard: N > 1 = N replicas" % n_bodies,
+        "config": {"workload": ("configs[0]: ONE world, %d boxes dropped on a plane, auto-disable on, timed settled (one island of ~340 bodies "
+                                "among ~120 awake ones); ODE quickstep 50+10 iters, dt=1ms, deterministic row-order mode; N > 1 = N replicas" % n_bodies) if c1 else
+                               ("configs[3]: ONE world, %d-body mixed box / sphere / capsule rubble pile in a walled pen on a plane, one "
+                                "island once formed; ODE quickstep 50+10 iters, dt=1ms, deterministic row-order mode; a single world does "
+                                "not shard: N > 1 = N replicas" % n_bodies),
                    "bodies": sc.nb, "geoms": sc.ng, "rows_per_step": rows / max(wsteps, 1), "contacts_per_step": contacts / max(wsteps, 1),
                    "l2": "no flush: the step's working set (entries 160 B x ~170 k, rows, contacts, bodies, geoms: ~90 MB) is below "
                          "the 126 MB L2 and is rewritten every step; DRAM traffic is in roofline.traffic",
@@ -379,12 +384,15 @@ def run_c4(args, rank, world, local_rank):
         "e2e": {"value": world * K / e2e_s, "unit": unit, "h2d_bytes_per_step": int(nb * 6 * 8), "d2h_bytes_per_step": int(nb * 13 * 8),
                 "api": "gzcuda_batch_step_io (pinned host buffers, 1 step per call)"},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "k_pgsd (the PGS sweeps of the pile as dataflow over the whole GPU)", "achieved": achieved,
+        "roofline": {"bound": "hbm", "kernel": "k_pgsm (the PGS sweeps on one thread-block cluster, entries in shared memory)" if c1 else
+                     "k_pgsd (the PGS sweeps of the pile as dataflow over the whole GPU)", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic, "peak_kind": peak_kind,
                      "bytes_per_launch": bytes_per_launch, "avg_launch_ms": pgs_avg_ms, "share_of_step": pgs_ms / ms if ms > 0 else None,
                      "dram_achieved": (traffic / (pgs_avg_ms * 1e-3) / 1e9) if (traffic and pgs_avg_ms > 0) else None,
-                     "limiter": "the exact-order dependency chain through the pile: ~2 500 hops of ~1 500 cycles (publish -> L2 -> poll -> "
-                                "row update) per step, not bytes (DESIGN.md 4)",
+                     "limiter": ("the exact-order dependency chain through the pile: ~3 100 hops of ~590 cycles (push into the partner CTA's "
+                                 "shared memory -> poll -> row update) per step, not bytes (DESIGN.md 4)") if c1 else
+                                ("the exact-order dependency chain through the pile: ~2 500 hops of ~1 500 cycles (publish -> L2 -> poll -> "
+                                 "row update) per step, not bytes (DESIGN.md 4)"),
                      "note": "achieved = ALGORITHMIC bytes (288 B per row per sweep, SURVEY 8d) / CUDA-event time of the sweeps"},
         "clocks": sampler.summary(),
     }
@@ -392,6 +400,15 @@ def run_c4(args, rank, world, local_rank):
         try:
             from oracle import refharness
             flavour = "fast" if refharness.available("fast") else "parity"
+            if c1:   # the reference gets there by itself in a few seconds
+                r = refharness.RefBatch(sc, p, mode=0, flavour=flavour)
+                r.step(Wm)
+                n_cpu = 1000
+                t0 = time.perf_counter(); r.step(n_cpu); dt = time.perf_counter() - t0
+                line["cpu_baseline"] = {"value": n_cpu / dt, "unit": unit, "cores": 1, "kind": "reference",
+                                        "sample": "%d steps (%.1f s) after %d of the reference's own opende (oracle/_ref %s flavour, natural order, "
+                                                  "dWorldQuickStep) on ONE thread (one world is one thread's work)" % (n_cpu, dt, Wm, flavour)}
+                raise StopIteration
             pos, quat, lvel, avel = b.body_state()
             bad = ~(np.isfinite(pos).all(axis=1) & np.isfinite(quat).all(axis=1) & np.isfinite(lvel).all(axis=1) & np.isfinite(avel).all(axis=1))
             park = np.nonzero(bad | (np.abs(np.nan_to_num(pos)).max(axis=1) > 1e3))[0]
@@ -407,6 +424,8 @@ def run_c4(args, rank, world, local_rank):
                                     "sample": "%d steps (%.1f s) of the reference's own opende (oracle/_ref %s flavour, natural order, dWorldQuickStep) "
                                               "on ONE thread (one world is one thread's work), created from the GPU's body states after %d steps "
                                               "(%d bodies parked)" % (n_cpu, dt, flavour, Wm + 2 * K + 3, len(park))}
+        except StopIteration:
+            pass
         except Exception as e:
             line["cpu_baseline"] = {"value": None, "unit": unit, "cores": 1, "kind": "reference", "sample": "unavailable: %s" % e}
     print(json.dumps(line), flush=True)
@@ -422,7 +441,7 @@ def main():
     ap.add_argument("--impl", default="gzcuda", choices=["gzcuda", "reference"])
     ap.add_argument("--worlds", type=int, default=WORLDS_PER_GPU, help="worlds per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--config", default="c2", choices=["c2", "c4"], help="c2: BASELINE.json configs[1] (the headline); c4: configs[3], one 20k-body pile")
+    ap.add_argument("--config", default="c2", choices=["c2", "c1", "c4"], help="c2: BASELINE.json configs[1] (the headline); c1: configs[0], 500 boxes in one world; c4: configs[3], one 20k-body pile")
     ap.add_argument("--bodies", type=int, default=20000, help="--config c4: bodies of the pile")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -437,7 +456,7 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
-    if args.config == "c4":
+    if args.config in ("c1", "c4"):
         run_c4(args, rank, world, local_rank)
         return
     run_gpu(args, rank, world, local_rank)

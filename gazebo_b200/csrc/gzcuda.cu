@@ -66,6 +66,7 @@ struct gzcuda_batch {
   int pgsl_grid = 0;                  // CTAs of k_pgsl's cooperative grid
   unsigned long long *pgsd_slots = nullptr;   // k_pgsd's exchange slots
   unsigned long long pgsd_launches = 0;       // launches since the slots were last cleared (tags are 32 bits)
+  unsigned long long pgsd_wrap = 0xFFFFFFFFull;   // tags in use before the slots are cleared (test switch GZCUDA_PGSD_WRAP: a small number)
   int pgs_large_mode = 1;             // large worlds: 0 k_pgsl (rounds + grid barrier), 1 k_pgsd (dataflow through L2), 2 k_pgsc (+ cluster shared memory)
   int pgsc_grid = 0, pgsc_cluster = 1, pgsc_glob_every = 4, pgsc_sleep = 0;
   size_t pgsc_smem = 0;
@@ -467,6 +468,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       if ((rc = dev_alloc(b, &d.ent_part, (size_t)d.ent_cap))) return rc;
       if ((rc = dev_alloc(b, &b->pgsd_slots, (size_t)8 * d.ent_cap))) return rc;
       CK(cudaMemset(b->pgsd_slots, 0, (size_t)8 * d.ent_cap * sizeof(unsigned long long)));
+      if (const char *ew = getenv("GZCUDA_PGSD_WRAP")) b->pgsd_wrap = std::max(1000ull, (unsigned long long)atoll(ew));
     }
     if (d.pgs_impl == 2 && b->pgs_large_mode == 2) {
       // k_pgsc: CTAs of 8 warps, pgsc_bpw bodies per warp - as few as the resident warps allow (two CTAs of 256
@@ -862,7 +864,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
         unsigned *epoch = reinterpret_cast<unsigned *>(d.xch_g + (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid) + 8;
         unsigned *ticket = epoch + 1;
         // 32-bit tags: long before they could repeat, clear the slots and start the epochs again
-        if ((++b->pgsd_launches + 2) * (unsigned long long)(d.p.iters + d.p.friction_iters + 1) >= 0xFFFFFFFFull) {
+        if ((++b->pgsd_launches + 2) * (unsigned long long)(d.p.iters + d.p.friction_iters + 1) >= b->pgsd_wrap) {
           cudaMemsetAsync(b->pgsd_slots, 0, (size_t)8 * d.ent_cap * sizeof(unsigned long long), b->stream);
           cudaMemsetAsync(epoch, 0, sizeof(unsigned), b->stream);
           b->pgsd_launches = 1;

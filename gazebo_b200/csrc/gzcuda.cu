@@ -218,8 +218,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       Joint &J = hj[j];
       memset(&J, 0, sizeof(J));
       J.type = sc->joint_type[j];
-      if (J.type < GZ_JOINT_HINGE || J.type > GZ_JOINT_UNIVERSAL)
+      if (J.type < GZ_JOINT_HINGE || J.type > GZ_JOINT_HINGE2)
         return fail(GZCUDA_E_INVALID, "unknown joint type");
+      if (J.type == GZ_JOINT_HINGE2 && sc->joint_body2[j] < 0)
+        return fail(GZCUDA_E_INVALID, "a hinge2 joint needs two bodies (joints/hinge2.cpp:31)");
       if (J.type == GZ_JOINT_UNIVERSAL) {
         const double *P = sc->joint_param + GZ_JP_COUNT * j;
         if (P[GZ_JP_FMAX] > 0 || std::isfinite(P[GZ_JP_LOSTOP]) || std::isfinite(P[GZ_JP_HISTOP]))

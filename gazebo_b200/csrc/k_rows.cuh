@@ -18,6 +18,17 @@
 namespace gz {
 
 // getHingeAngle (joint.cpp:442-465) + getHingeAngleFromRelativeQuat (:391-432)
+#define GZ_PI 3.14159265358979323846   // M_PI
+
+// dxJointHinge2::measureAngle1 (hinge2.cpp:34-52): axis 2 seen from body 1, against v1 / v2
+__device__ inline double hinge2_angle1(const DevBatch &B, const Joint &j) {
+  double p[3], q[3];
+  mul0_331(p, B.body[j.b2].R, j.axis2);
+  mul1_331(q, B.body[j.b1].R, p);
+  const double x = dot3(&j.param[GZ_JP_V1], q), y = dot3(&j.param[GZ_JP_V2], q);
+  return -gzdet_atan2(y, x);
+}
+
 __device__ inline double hinge_angle(const DevBatch &B, const Joint &j) {
   double qrel[4];
   const Body &b1 = B.body[j.b1];
@@ -263,6 +274,18 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
           m = 6;
         } else if (j.type == GZ_JOINT_BALL) {
           m = 3;
+        } else if (j.type == GZ_JOINT_HINGE2) {
+          // dxJointHinge2::getInfo1 (hinge2.cpp:108-127)
+          m = 4;
+          const double lo = j.param[GZ_JP_LOSTOP], hi = j.param[GZ_JP_HISTOP];
+          j.limit = 0;
+          if ((lo >= -GZ_PI || hi <= GZ_PI) && lo <= hi) {
+            const double angle = hinge2_angle1(B, j);
+            if (angle <= lo) { j.limit = 1; j.limit_err = angle - lo; }
+            else if (angle >= hi) { j.limit = 2; j.limit_err = angle - hi; }
+          }
+          if (j.limit || j.param[GZ_JP_FMAX] > 0) m++;
+          if (j.param[GZ_JP_FMAX2] > 0) m++;
         } else if (j.type == GZ_JOINT_UNIVERSAL) {
           m = 4;   // limits and motors of the two axes are not supported (gzcuda_batch_create checks)
         } else if (j.type == GZ_JOINT_SLIDER) {

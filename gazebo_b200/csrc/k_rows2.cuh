@@ -13,11 +13,21 @@ __device__ inline void row_init(Row &r, int lb1, int lb2, double cfm, double cvm
 
 // dxJointLimitMotor::addLimot (joint.cpp:573-750), rotational (hinge) or linear (slider, with the
 // linear torque decoupling vector ltd when the joint has two bodies).  Returns 1 if a row was written.
-__device__ inline int add_limot(DevBatch &B, Joint &j, Row &r, const double *ax1, double fps, bool rotational) {
-  const double fmax = j.param[GZ_JP_FMAX], vel = j.param[GZ_JP_VEL];
-  const double lostop = j.param[GZ_JP_LOSTOP], histop = j.param[GZ_JP_HISTOP];
+// dxJointLimitMotor as plain data (joints/joint.cpp:470-484)
+struct Limot { double lostop, histop, vel, fmax, fudge, bounce, normal_cfm, stop_erp, stop_cfm, limit_err; int limit; };
+__device__ inline Limot limot_of(const Joint &j) {   // the joint's (first) limit motor: joint_param slots 0..8
+  Limot L;
+  L.lostop = j.param[GZ_JP_LOSTOP]; L.histop = j.param[GZ_JP_HISTOP]; L.vel = j.param[GZ_JP_VEL]; L.fmax = j.param[GZ_JP_FMAX];
+  L.fudge = j.param[GZ_JP_FUDGE]; L.bounce = j.param[GZ_JP_BOUNCE]; L.normal_cfm = j.param[GZ_JP_NORMAL_CFM];
+  L.stop_erp = j.param[GZ_JP_STOP_ERP]; L.stop_cfm = j.param[GZ_JP_STOP_CFM]; L.limit_err = j.limit_err; L.limit = j.limit;
+  return L;
+}
+
+__device__ inline int add_limot(DevBatch &B, Joint &j, Row &r, const double *ax1, double fps, bool rotational, const Limot &M) {
+  const double fmax = M.fmax, vel = M.vel;
+  const double lostop = M.lostop, histop = M.histop;
   int powered = fmax > 0;
-  const int limit = j.limit;
+  const int limit = M.limit;
   if (!(powered || limit)) return 0;
   const int o = rotational ? 3 : 0;
   for (int k = 0; k < 3; k++) r.J[o + k] = ax1[k];
@@ -31,13 +41,13 @@ __device__ inline int add_limot(DevBatch &B, Joint &j, Row &r, const double *ax1
   }
   if (limit && dequal(lostop, histop)) powered = 0;
   if (powered) {
-    r.cfm = j.param[GZ_JP_NORMAL_CFM];
+    r.cfm = M.normal_cfm;
     if (!limit) {
       r.c = vel; r.lo = -fmax; r.hi = fmax;
     } else {
       double fm = fmax;
       if ((vel > 0) || (dequal(vel, 0.0) && limit == 2)) fm = -fm;
-      if ((limit == 1 && vel > 0) || (limit == 2 && vel < 0)) fm *= j.param[GZ_JP_FUDGE];
+      if ((limit == 1 && vel > 0) || (limit == 2 && vel < 0)) fm *= M.fudge;
       // dBodyAddTorque on both bodies from inside getInfo2.  Several powered hinges at
       // their stops on one body would make the summation order matter; atomics keep it
       // race-free (order then differs from the reference in the last bit only).
@@ -54,13 +64,13 @@ __device__ inline int add_limot(DevBatch &B, Joint &j, Row &r, const double *ax1
     }
   }
   if (limit) {
-    double k = fps * j.param[GZ_JP_STOP_ERP];
-    r.c = -k * j.limit_err;
-    r.cfm = j.param[GZ_JP_STOP_CFM];
+    double k = fps * M.stop_erp;
+    r.c = -k * M.limit_err;
+    r.cfm = M.stop_cfm;
     if (dequal(lostop, histop)) { r.lo = -GZ_INF; r.hi = GZ_INF; }
     else {
       if (limit == 1) { r.lo = 0; r.hi = GZ_INF; } else { r.lo = -GZ_INF; r.hi = 0; }
-      const double bounce = j.param[GZ_JP_BOUNCE];
+      const double bounce = M.bounce;
       if (bounce > 0) {
         double vvel = dot3(rotational ? B.body[j.b1].avel : B.body[j.b1].lvel, ax1);
         if (j.b2 >= 0) vvel -= dot3(rotational ? B.body[j.b2].avel : B.body[j.b2].lvel, ax1);
@@ -73,6 +83,10 @@ __device__ inline int add_limot(DevBatch &B, Joint &j, Row &r, const double *ax1
     }
   }
   return 1;
+}
+
+__device__ inline int add_limot(DevBatch &B, Joint &j, Row &r, const double *ax1, double fps, bool rotational) {
+  return add_limot(B, j, r, ax1, fps, rotational, limot_of(j));
 }
 
 // setBall (joint.cpp:93-134): rows 0..2 keep the anchor points together; k = fps * erp
@@ -95,6 +109,28 @@ __device__ inline void set_ball(Row *rows, const Body &b1, const Body *b2, const
   } else {
     for (int i = 0; i < 3; i++) rows[i].c = k * (j.anchor2[i] - a1[i] - b1.pos[i]);
   }
+}
+
+// setBall2 (joint.cpp:142-208): the ball rows aligned with `axis` (row 0 along it, with its own erp: the suspension)
+__device__ inline void set_ball2(Row *rows, const Body &b1, const Body &b2, const Joint &j, const double *axis, double k1, double k) {
+  double q1[3], q2[3], a1[3], a2[3], t[3];
+  plane_space(axis, q1, q2);
+  for (int i = 0; i < 3; i++) { rows[0].J[i] = axis[i]; rows[1].J[i] = q1[i]; rows[2].J[i] = q2[i]; }
+  mul0_331(a1, b1.R, j.anchor1);
+  cross3(t, a1, axis); for (int i = 0; i < 3; i++) rows[0].J[3 + i] = t[i];
+  cross3(t, a1, q1);   for (int i = 0; i < 3; i++) rows[1].J[3 + i] = t[i];
+  cross3(t, a1, q2);   for (int i = 0; i < 3; i++) rows[2].J[3 + i] = t[i];
+  for (int i = 0; i < 3; i++) { rows[0].J[6 + i] = -axis[i]; rows[1].J[6 + i] = -q1[i]; rows[2].J[6 + i] = -q2[i]; }
+  mul0_331(a2, b2.R, j.anchor2);
+  cross3(t, a2, axis); for (int i = 0; i < 3; i++) rows[0].J[9 + i] = -t[i];
+  cross3(t, a2, q1);   for (int i = 0; i < 3; i++) rows[1].J[9 + i] = -t[i];
+  cross3(t, a2, q2);   for (int i = 0; i < 3; i++) rows[2].J[9 + i] = -t[i];
+  double d[3];
+  for (int i = 0; i < 3; i++) { a1[i] += b1.pos[i]; a2[i] += b2.pos[i]; }
+  for (int i = 0; i < 3; i++) d[i] = a2[i] - a1[i];
+  rows[0].c = k1 * dot3(axis, d);
+  rows[1].c = k * dot3(q1, d);
+  rows[2].c = k * dot3(q2, d);
 }
 
 // setFixedOrientation (joint.cpp:212-265) on rows[0..2]; k = fps * erp
@@ -158,6 +194,28 @@ __global__ void k_rows_joint(DevBatch B) {
       if (b2) for (int i = 0; i < 3; i++) rows[3].J[9 + i] = -p[i];
       rows[3].c = fps * erp * -k;
     }
+  } else if (j.type == GZ_JOINT_HINGE2) {
+    // dxJointHinge2::getInfo2 (hinge2.cpp:158-222): ball rows aligned with axis 1 (row 0 = the suspension), one row that
+    // keeps the angle between the axes, then the limit / motor of axis 1 and the motor of axis 2
+    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 4; r++) rows[r].cfm = j.param[GZ_JP_CFM];
+    double ax1[3], ax2[3], q[3];
+    mul0_331(ax1, b1.R, j.axis1);
+    mul0_331(ax2, b2->R, j.axis2);
+    cross3(q, ax1, ax2);
+    const double sn = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]), cs = dot3(ax1, ax2);
+    safe_normalize3(q);
+    set_ball2(rows, b1, *b2, j, ax1, fps * j.param[GZ_JP_SUSP_ERP], fps * erp);
+    for (int i = 0; i < 3; i++) { rows[3].J[3 + i] = q[i]; rows[3].J[9 + i] = -q[i]; }
+    rows[3].c = fps * erp * (j.param[GZ_JP_C0] * sn - j.param[GZ_JP_S0] * cs);
+    int row = 4;
+    if (j.limit || j.param[GZ_JP_FMAX] > 0) row += add_limot(B, j, rows[row], ax1, fps, true);
+    if (j.param[GZ_JP_FMAX2] > 0) {
+      Limot M2;   // dxJointLimitMotor::init (joint.cpp:470-484) with dParamVel2 / dParamFMax2 set
+      M2.lostop = -GZ_INF; M2.histop = GZ_INF; M2.vel = j.param[GZ_JP_VEL2]; M2.fmax = j.param[GZ_JP_FMAX2];
+      M2.fudge = 1; M2.bounce = 0; M2.normal_cfm = B.p.cfm; M2.stop_erp = B.p.erp; M2.stop_cfm = B.p.cfm; M2.limit_err = 0; M2.limit = 0;
+      add_limot(B, j, rows[row], ax2, fps, true, M2);
+    }
+    rows[0].cfm = j.param[GZ_JP_SUSP_CFM];
   } else if (j.type == GZ_JOINT_SLIDER) {
     // dxJointSlider::getInfo2 (slider.cpp:151-238); anchor1 holds dxJointSlider::offset
     if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 5; r++) rows[r].cfm = j.param[GZ_JP_CFM];

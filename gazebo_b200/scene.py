@@ -14,11 +14,12 @@ import math
 import numpy as np
 
 GEOM_SPHERE, GEOM_BOX, GEOM_CAPSULE, GEOM_CYLINDER, GEOM_PLANE = range(5)
-JOINT_HINGE, JOINT_FIXED, JOINT_BALL, JOINT_SLIDER, JOINT_UNIVERSAL = 1, 2, 3, 4, 5
+JOINT_HINGE, JOINT_FIXED, JOINT_BALL, JOINT_SLIDER, JOINT_UNIVERSAL, JOINT_HINGE2 = 1, 2, 3, 4, 5, 6
 BODY_NO_GRAVITY, BODY_AUTO_DISABLE, BODY_DISABLED, BODY_NO_GYRO = 1, 2, 4, 8
 JP_LOSTOP, JP_HISTOP, JP_VEL, JP_FMAX, JP_FUDGE, JP_BOUNCE, JP_NORMAL_CFM, \
     JP_STOP_ERP, JP_STOP_CFM, JP_ERP, JP_CFM = range(11)
-JP_COUNT = 12
+JP_VEL2, JP_FMAX2, JP_SUSP_ERP, JP_SUSP_CFM, JP_V1, JP_V2, JP_C0, JP_S0 = 12, 13, 14, 15, 16, 19, 22, 23
+JP_COUNT = 24
 SF_MU, SF_MU2, SF_KP, SF_KD, SF_SLIP1, SF_SLIP2, SF_BOUNCE, SF_BOUNCE_VEL = range(8)
 SF_COUNT = 10
 GZ_ALL_COLLIDE = 0x0FFFFFFF
@@ -240,7 +241,7 @@ class SceneBuilder:
     @staticmethod
     def joint_params(lostop=-math.inf, histop=math.inf, vel=0.0, fmax=0.0, fudge=1.0,
                      bounce=0.0, normal_cfm=0.0, stop_erp=0.2, stop_cfm=0.0, erp=-1.0, cfm=-1.0):
-        return [lostop, histop, vel, fmax, fudge, bounce, normal_cfm, stop_erp, stop_cfm, erp, cfm, 0.0]
+        return [lostop, histop, vel, fmax, fudge, bounce, normal_cfm, stop_erp, stop_cfm, erp, cfm, 0.0] + [0.0] * (JP_COUNT - 12)
 
     def add_hinge(self, b1, b2, anchor, axis, **params):
         """Anchor and axis in world coordinates at the current body poses."""
@@ -260,6 +261,32 @@ class SceneBuilder:
         else:
             a2, ax2, qrel = anchor, axis, q_conj(q1)
         self._push_joint(JOINT_HINGE, b1, b2, a1, a2, ax1, ax2, qrel, self.joint_params(**params))
+        return self._nj - 1 - self._w_j0
+
+    def add_hinge2(self, b1, b2, anchor, axis1, axis2, vel2=0.0, fmax2=0.0, susp_erp=0.2, susp_cfm=0.0, **params):
+        """dxJointHinge2 (SDF revolute2: steering / suspension axis 1 on body 1, wheel axis 2 on body 2).  Anchor and axes
+        in world coordinates at the current body poses.  The members ODE derives in dJointSetHinge2Anchor / Axis1 / Axis2
+        (v1, v2 to measure the angle of axis 1, c0 / s0 = cos / sin of the angle between the axes) are computed here
+        and travel in joint_param: both sides of a parity test read the same numbers."""
+        assert b2 >= 0, "hinge2 needs two bodies"
+        p1, q1 = self._body_pose(b1)
+        p2, q2 = self._body_pose(b2)
+        R1, R2 = q_to_R(q1), q_to_R(q2)
+        anchor = np.asarray(anchor, float)
+        ax1w = np.asarray(axis1, float); ax1w = ax1w / np.linalg.norm(ax1w)
+        ax2w = np.asarray(axis2, float); ax2w = ax2w / np.linalg.norm(ax2w)
+        a1, a2 = R1.T @ (anchor - p1), R2.T @ (anchor - p2)
+        ax1, ax2 = R1.T @ ax1w, R2.T @ ax2w
+        g1, g2 = R1 @ ax1, R2 @ ax2                       # the axes back in world coordinates, as getAxisInfo sees them
+        cr = np.cross(g1, g2)
+        s0, c0 = math.sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]), float(g1 @ g2)
+        m2 = g2 - float(g1 @ g2) * g1                      # axis 2 made perpendicular to axis 1
+        m2 = m2 / np.linalg.norm(m2)
+        v1, v2 = R1.T @ m2, R1.T @ np.cross(g1, m2)
+        P = self.joint_params(**params)
+        P[JP_VEL2], P[JP_FMAX2], P[JP_SUSP_ERP], P[JP_SUSP_CFM] = vel2, fmax2, susp_erp, susp_cfm
+        P[JP_V1:JP_V1 + 3] = list(v1); P[JP_V2:JP_V2 + 3] = list(v2); P[JP_C0], P[JP_S0] = c0, s0
+        self._push_joint(JOINT_HINGE2, b1, b2, a1, a2, ax1, ax2, (1, 0, 0, 0), P)
         return self._nj - 1 - self._w_j0
 
     def add_fixed(self, b1, b2, **params):

@@ -132,6 +132,15 @@ int joint_params(dxJoint *j, double *P) {
     case dJointTypeSlider: limot_params(static_cast<dxJointSlider *>(j)->limot, P); return GZ_JOINT_SLIDER;
     case dJointTypeFixed: return GZ_JOINT_FIXED;
     case dJointTypeBall: return GZ_JOINT_BALL;
+    case dJointTypeHinge2: {
+      const dxJointHinge2 *h2 = static_cast<dxJointHinge2 *>(j);
+      limot_params(h2->limot1, P);
+      P[GZ_JP_VEL2] = h2->limot2.vel; P[GZ_JP_FMAX2] = h2->limot2.fmax;
+      P[GZ_JP_SUSP_ERP] = h2->susp_erp; P[GZ_JP_SUSP_CFM] = h2->susp_cfm;
+      for (int k = 0; k < 3; k++) { P[GZ_JP_V1 + k] = h2->v1[k]; P[GZ_JP_V2 + k] = h2->v2[k]; }
+      P[GZ_JP_C0] = h2->c0; P[GZ_JP_S0] = h2->s0;
+      return GZ_JOINT_HINGE2;
+    }
     default: return 0;
   }
 }
@@ -246,7 +255,7 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
   for (int i = 0; i < nj; i++) {
     dxJoint *j = m->joints[i];
     jtype[i] = joint_params(j, &m->jparam[(size_t)GZ_JP_COUNT * i]);
-    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball");
+    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball, hinge2");
     if (!j->node[0].body) return fail(GZCUDA_E_INVALID, "a joint without bodies");
     auto i1 = bidx.find(j->node[0].body);
     if (i1 == bidx.end()) return fail(GZCUDA_E_INVALID, "a joint is attached to a body of another world");
@@ -266,6 +275,9 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
       const dxJointFixed *fj = static_cast<dxJointFixed *>(j);
       for (int k = 0; k < 3; k++) ja1[3 * i + k] = fj->offset[k];
       for (int k = 0; k < 4; k++) jq[4 * i + k] = fj->qrel[k];
+    } else if (jtype[i] == GZ_JOINT_HINGE2) {
+      const dxJointHinge2 *h2 = static_cast<dxJointHinge2 *>(j);
+      for (int k = 0; k < 3; k++) { ja1[3 * i + k] = h2->anchor1[k]; ja2[3 * i + k] = h2->anchor2[k]; jx1[3 * i + k] = h2->axis1[k]; jx2[3 * i + k] = h2->axis2[k]; }
     } else if (jtype[i] == GZ_JOINT_BALL) {
       const dxJointBall *bj = static_cast<dxJointBall *>(j);
       for (int k = 0; k < 3; k++) { ja1[3 * i + k] = bj->anchor1[k]; ja2[3 * i + k] = bj->anchor2[k]; }

@@ -34,7 +34,9 @@ enum { GZ_GEOM_SPHERE = 0, GZ_GEOM_BOX = 1, GZ_GEOM_CAPSULE = 2,
 /* joint_type (dJointTypeHinge, dJointTypeFixed, …; contact joints are created
  * by the collide stage every step and never appear in the scene). */
 enum { GZ_JOINT_HINGE = 1, GZ_JOINT_FIXED = 2, GZ_JOINT_BALL = 3,
-       GZ_JOINT_SLIDER = 4, GZ_JOINT_UNIVERSAL = 5 };
+       GZ_JOINT_SLIDER = 4, GZ_JOINT_UNIVERSAL = 5,
+       GZ_JOINT_HINGE2 = 6 };  /* dxJointHinge2 (SDF revolute2): two bodies required; joint_anchor1/2, joint_axis1/2 in the
+                                * bodies' frames, the derived members v1, v2, c0, s0 in joint_param (below) */
 
 /* body_flags bits */
 enum { GZ_BODY_NO_GRAVITY   = 1,   /* dxBodyNoGravity (ODELink::SetGravityMode(false)) */
@@ -48,7 +50,14 @@ enum { GZ_JP_LOSTOP = 0, GZ_JP_HISTOP = 1, GZ_JP_VEL = 2, GZ_JP_FMAX = 3,
        GZ_JP_STOP_ERP = 7, GZ_JP_STOP_CFM = 8,
        GZ_JP_ERP = 9,      /* joint erp, < 0 = use world erp */
        GZ_JP_CFM = 10,     /* joint cfm, < 0 = use world cfm */
-       GZ_JP_COUNT = 12 };
+       /* hinge2 only (joints/hinge2.cpp): the motor of axis 2 (limot2: dParamVel2 / dParamFMax2; axis 2 is never
+        * limited, hinge2.cpp:125-127), the suspension (dParamSuspensionERP / CFM), and the members ODE derives when the
+        * anchor and the axes are set (makeV1andV2 :224-255, getAxisInfo :148-156) */
+       GZ_JP_VEL2 = 12, GZ_JP_FMAX2 = 13, GZ_JP_SUSP_ERP = 14, GZ_JP_SUSP_CFM = 15,
+       GZ_JP_V1 = 16,      /* v1[3]: 16..18 */
+       GZ_JP_V2 = 19,      /* v2[3]: 19..21 */
+       GZ_JP_C0 = 22, GZ_JP_S0 = 23,
+       GZ_JP_COUNT = 24 };
 
 /* geom_surf[] slots (ODESurfaceParams + FrictionPyramid) */
 enum { GZ_SF_MU = 0, GZ_SF_MU2 = 1, GZ_SF_KP = 2, GZ_SF_KD = 3,

@@ -661,6 +661,34 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
           uj->axis2[k] = sc->joint_axis2[3 * j + k];
         }
         uj->computeInitialRelativeRotations();   // qrel1 / qrel2: joint angles only (limits are not used)
+      } else if (sc->joint_type[j] == GZ_JOINT_HINGE2) {
+        if (!b2) return nullptr;
+        jt = dJointCreateHinge2(w->world, 0);
+        dJointAttach(jt, b1, b2);
+        dxJointHinge2 *h2 = (dxJointHinge2 *)jt;
+        for (int k = 0; k < 3; k++) {
+          h2->anchor1[k] = sc->joint_anchor1[3 * j + k];
+          h2->anchor2[k] = sc->joint_anchor2[3 * j + k];
+          h2->axis1[k] = sc->joint_axis1[3 * j + k];
+          h2->axis2[k] = sc->joint_axis2[3 * j + k];
+          h2->v1[k] = P[GZ_JP_V1 + k];      // what dJointSetHinge2Anchor / Axis1 / Axis2 derive (makeV1andV2, getAxisInfo)
+          h2->v2[k] = P[GZ_JP_V2 + k];
+        }
+        h2->c0 = P[GZ_JP_C0];
+        h2->s0 = P[GZ_JP_S0];
+        h2->susp_erp = P[GZ_JP_SUSP_ERP];
+        h2->susp_cfm = P[GZ_JP_SUSP_CFM];
+        h2->limot1.lostop = P[GZ_JP_LOSTOP];
+        h2->limot1.histop = P[GZ_JP_HISTOP];
+        h2->limot1.vel = P[GZ_JP_VEL];
+        h2->limot1.fmax = P[GZ_JP_FMAX];
+        h2->limot1.fudge_factor = P[GZ_JP_FUDGE];
+        h2->limot1.bounce = P[GZ_JP_BOUNCE];
+        h2->limot1.normal_cfm = P[GZ_JP_NORMAL_CFM];
+        h2->limot1.stop_erp = P[GZ_JP_STOP_ERP];
+        h2->limot1.stop_cfm = P[GZ_JP_STOP_CFM];
+        h2->limot2.vel = P[GZ_JP_VEL2];       // dParamVel2 / dParamFMax2 (ODEHinge2Joint.cc:184-186): axis 2 is only ever powered
+        h2->limot2.fmax = P[GZ_JP_FMAX2];
       } else if (sc->joint_type[j] == GZ_JOINT_SLIDER) {
         jt = dJointCreateSlider(w->world, 0);
         dJointAttach(jt, b1, b2);

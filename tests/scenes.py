@@ -319,6 +319,40 @@ def fdir1():
     return sb.finish(), S.default_params(), None
 
 
+def carts(n_worlds=3, seed=31):
+    """Hinge2 joints (dxJointHinge2, SDF revolute2) as on a car: a chassis box on four sphere wheels; axis 1 = vertical
+    (steering, limited to +-0.3..0.5 rad on the front wheels, locked by equal stops on the rear ones, one front wheel with
+    a steering motor), axis 2 = the axle (driven by a motor on the rear wheels, free on the front ones), the ball row
+    along axis 1 soft (suspension erp / cfm).  Carts start at different yaw, one tilted, and drive over the plane."""
+    sb = S.SceneBuilder()
+    rng = np.random.Generator(np.random.PCG64(seed))
+    for w in range(n_worlds):
+        sb.begin_world()
+        sb.add_ground_plane()
+        yaw = rng.uniform(-1.0, 1.0)
+        q = S.q_from_rpy(0.05 * w, -0.03 * w, yaw)
+        R = S.q_to_R(q)
+        c = np.array([0.0, 0.0, 0.45])
+        chassis = sb.add_body(c, q, 8.0, S.box_inertia(8.0, 1.2, 0.6, 0.2))
+        sb.add_geom(S.GEOM_BOX, (1.2, 0.6, 0.2), sb.new_space(), body=chassis)
+        space = sb.new_space()
+        for k, (dx, dy) in enumerate(((0.5, 0.4), (0.5, -0.4), (-0.5, 0.4), (-0.5, -0.4))):
+            pw = c + R @ np.array([dx, dy, -0.15])
+            wheel = sb.add_body(pw, q, 1.0, S.sphere_inertia(1.0, 0.2))
+            sb.add_geom(S.GEOM_SPHERE, (0.2,), sb.new_space(), body=wheel)
+            front = dx > 0
+            kw = dict(susp_erp=0.4, susp_cfm=0.02 + 0.01 * k)
+            if front:
+                kw.update(lostop=-0.3 - 0.05 * k, histop=0.5, stop_erp=0.3, stop_cfm=1e-4)
+                if k == 0:
+                    kw.update(vel=0.6, fmax=2.0, fudge=0.5)       # steers into its stop
+            else:
+                kw.update(lostop=0.0, histop=0.0, vel2=4.0 + w, fmax2=3.0)   # locked steering, driven axle
+            sb.add_hinge2(chassis, wheel, pw, R @ np.array([0, 0, 1.0]), R @ np.array([0, 1.0, 0]), **kw)
+        sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 def ray_targets(n_worlds=2, per_type=6, seed=77):
     """Worlds for the laser: a ground plane and, floating at rest (no gravity flag needed: they are never stepped far), boxes,
     spheres, capsules and cylinders at random poses inside a 6 m cube, one sensor-category geom that rays must not see."""
@@ -372,4 +406,5 @@ GOLDEN = {
     "cylcyl": (cylcyl, 400),
     "fdir1": (fdir1, 300),
     "dyn_inertia": (dyn_inertia, 400),
+    "carts": (carts, 600),
 }

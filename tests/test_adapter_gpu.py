@@ -103,6 +103,14 @@ def test_adapter_sleep_flags_and_wake_up(adapter, oracle):
 
 
 @pytest.mark.gpu
+def test_adapter_carts_on_hinge2_joints(adapter, oracle):
+    """dxJointHinge2 objects (steering limits and motor, driven axles, suspension) mirrored from the live ODE world:
+    anchors, axes, v1 / v2, c0 / s0 and both limit motors read from the dxJointHinge2 the reference built."""
+    sc, p, _ = scenes.carts()
+    _run(adapter, oracle, sc, p, steps=300, every=50)
+
+
+@pytest.mark.gpu
 def test_adapter_laser_over_live_ode_objects(adapter, oracle):
     """gzcuda_dworld_ray_query: the laser against a LIVE ODE world (what ODEMultiRayShape::UpdateRays does with
     dSpaceCollide2) - ranges bit-exact against the reference's own ray colliders on the same objects, and the dxGeom

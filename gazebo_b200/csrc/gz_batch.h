@@ -88,11 +88,12 @@ struct Contact {
   double pos[3], normal[3], depth;
   double mu, mu2, soft_erp, soft_cfm, slip1, slip2, bounce, bounce_vel;
   double fdir1[3];
+  double em, em_radius;   // Hertzian contact (dContactEM): E* > 0 = on; em_radius = patch radius, or the surface radius (em_surface)
   int g1, g2;        // GLOBAL geom indices (canonical: g1 < g2)
   int b1, b2;        // GLOBAL body indices after dJointAttach's swap (b1 >= 0)
   int reverse;       // dJOINT_REVERSE
   int has_fdir1;
-  int row0, pad;
+  int row0, em_surface;   // em_surface: the pair does not use the patch radius (contact.cpp:166-172)
 };
 
 // One constraint row as the assembly kernels leave it: 24 doubles = 192 B.  (What the sweeps read is the

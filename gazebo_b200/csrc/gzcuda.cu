@@ -306,8 +306,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       if (sc->geom_rot) for (int k = 0; k < 9; k++) G.oR[k] = sc->geom_rot[9 * g + k];
       else q_to_R(sc->geom_quat + 4 * g, G.oR);   // dGeomSetOffsetQuaternion / dGeomSetQuaternion: dQtoR, no normalisation
       for (int k = 0; k < GZ_SF_COUNT; k++) G.surf[k] = sc->geom_surf[GZ_SF_COUNT * g + k];
-      if (G.surf[GZ_SF_PATCH_RADIUS] > 0 || G.surf[GZ_SF_ELASTIC_MODULUS] > 0)
-        return fail(GZCUDA_E_INVALID, "torsional friction (patch_radius) and elastic-modulus contact rows are not supported");
+      if (G.surf[GZ_SF_MU3] > 0)
+        return fail(GZCUDA_E_INVALID, "torsional friction (mu3 > 0: a fourth contact row) is not supported");
       G.cat = sc->geom_category_bits[g]; G.col = sc->geom_collide_bits[g];
       G.scat = scat[G.space]; G.scol = scol[G.space];
       G.bitmask = sc->geom_collide_bitmask[g];

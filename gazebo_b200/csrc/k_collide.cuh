@@ -369,6 +369,26 @@ __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldI
   slip1 *= c; slip2 *= c;
   double bounce = fmin(g1.surf[GZ_SF_BOUNCE], g2.surf[GZ_SF_BOUNCE]);
   double bounce_vel = fmin(g1.surf[GZ_SF_BOUNCE_VEL], g2.surf[GZ_SF_BOUNCE_VEL]);
+  // Hertzian contact (ODEPhysics.cc:1186-1251): patch radius = the larger one, curvatures add, both surfaces must agree
+  // on use_patch_radius; E* from the two moduli and Poisson's ratios, only when both moduli are > 0
+  double em = 0.0, em_radius = 0.0;
+  int em_surface = 0;
+  {
+    const double patch = fmax(g1.surf[GZ_SF_PATCH_RADIUS], g2.surf[GZ_SF_PATCH_RADIUS]);
+    double curv1 = 0, curv2 = 0;
+    if (g1.surf[GZ_SF_SURFACE_RADIUS] > 0) curv1 = 1 / g1.surf[GZ_SF_SURFACE_RADIUS];
+    if (g2.surf[GZ_SF_SURFACE_RADIUS] > 0) curv2 = 1 / g2.surf[GZ_SF_SURFACE_RADIUS];
+    const double curv_sum = curv1 + curv2;
+    double surface_radius = 0;
+    if (curv_sum > 0) surface_radius = 1 / curv_sum;
+    const bool use_patch = g1.surf[GZ_SF_USE_PATCH_RADIUS] != 0 && g2.surf[GZ_SF_USE_PATCH_RADIUS] != 0;
+    const double nu1 = g1.surf[GZ_SF_POISSON], nu2 = g2.surf[GZ_SF_POISSON];
+    const double e1 = g1.surf[GZ_SF_ELASTIC_MODULUS], e2 = g2.surf[GZ_SF_ELASTIC_MODULUS];
+    if (e1 > 0 && e2 > 0) {
+      const double es = 1.0 / ((1.0 - nu1 * nu1) / e1 + (1.0 - nu2 * nu2) / e2);
+      if (es > 0.0) { em = es; em_radius = use_patch ? patch : surface_radius; em_surface = use_patch ? 0 : 1; }
+    }
+  }
   // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
   int b1 = g1.body, b2 = g2.body, reverse = 0;
   if (b1 < 0) { b1 = b2; b2 = -1; reverse = 1; }
@@ -381,6 +401,7 @@ __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldI
     C.depth = src[7 * j + 6];
     C.mu = mu; C.mu2 = mu2; C.soft_erp = soft_erp; C.soft_cfm = soft_cfm;
     C.slip1 = slip1; C.slip2 = slip2; C.bounce = bounce; C.bounce_vel = bounce_vel;
+    C.em = em; C.em_radius = em_radius; C.em_surface = em_surface;
     C.g1 = gi1; C.g2 = gi2; C.b1 = b1; C.b2 = b2; C.reverse = reverse; C.has_fdir1 = fdset ? 1 : 0;
   }
   if (b1 >= 0) B.bstep[b1].has_contact = 1;

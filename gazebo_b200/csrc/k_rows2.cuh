@@ -299,7 +299,19 @@ __device__ __forceinline__ void rows_contact_one(DevBatch &B, const int w, const
   if (depth < 0) depth = 0;
   r0.cfm = C.soft_cfm;
   const double motionN = 0;
-  const double local_erp = C.soft_erp;
+  double local_erp = C.soft_erp;
+  if (C.em > 0) {
+    // dContactEM (contact.cpp:163-216): Hertzian stiffness 4/3 E* sqrt(r x) linearised at this depth; kd recovered from
+    // the soft cfm / erp, then erp and cfm recomputed with it
+    double patch_radius;
+    if (C.em_surface) patch_radius = sqrt(C.em_radius * depth);   // (the surface radius is never negative here: :169-170)
+    else patch_radius = C.em_radius;
+    const double khertz_sqrtx = 4.0 / 3.0 * C.em * sqrt(patch_radius * depth);
+    const double kd = 1.0 / r0.cfm - local_erp / fps;
+    const double kph = khertz_sqrtx / fps;
+    local_erp = (kph) / (kph + kd);
+    r0.cfm = 1.0 / (kph + kd);
+  }
   const double k = fps * local_erp;
   const double pushout = k * depth + motionN;
   r0.c = pushout;

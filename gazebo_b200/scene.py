@@ -10,6 +10,7 @@ dJointSetHingeAnchor / dJointSetHingeAxis / dJointSetFixed store
 """
 import ctypes as C
 import math
+import sys
 
 import numpy as np
 
@@ -21,7 +22,8 @@ JP_LOSTOP, JP_HISTOP, JP_VEL, JP_FMAX, JP_FUDGE, JP_BOUNCE, JP_NORMAL_CFM, \
 JP_VEL2, JP_FMAX2, JP_SUSP_ERP, JP_SUSP_CFM, JP_V1, JP_V2, JP_C0, JP_S0 = 12, 13, 14, 15, 16, 19, 22, 23
 JP_COUNT = 24
 SF_MU, SF_MU2, SF_KP, SF_KD, SF_SLIP1, SF_SLIP2, SF_BOUNCE, SF_BOUNCE_VEL = range(8)
-SF_COUNT = 10
+SF_PATCH_RADIUS, SF_ELASTIC_MODULUS, SF_POISSON, SF_SURFACE_RADIUS, SF_USE_PATCH_RADIUS, SF_MU3 = 8, 9, 10, 11, 12, 13
+SF_COUNT = 14
 GZ_ALL_COLLIDE = 0x0FFFFFFF
 GZ_FIXED_COLLIDE = 0x00000001
 
@@ -148,7 +150,8 @@ def cylinder_inertia(mass, r, l):
 
 
 DEFAULT_SURFACE = dict(mu=1.0, mu2=1.0, kp=1e12, kd=1.0, slip1=0.0, slip2=0.0,
-                       bounce=0.0, bounce_vel=100000.0, patch_radius=0.0, elastic_modulus=0.0)
+                       bounce=0.0, bounce_vel=100000.0, patch_radius=0.0, elastic_modulus=0.0,
+                       poissons_ratio=0.3, surface_radius=sys.float_info.max, use_patch_radius=1.0, mu3=0.0)
 
 
 class SceneBuilder:
@@ -224,7 +227,8 @@ class SceneBuilder:
         self.g["bitmask"].append(collide_bitmask & 0xFFFFFFFF)
         self.g["maxc"].append(int(max_contacts))
         self.g["surf"].append([s["mu"], s["mu2"], s["kp"], s["kd"], s["slip1"], s["slip2"],
-                               s["bounce"], s["bounce_vel"], s["patch_radius"], s["elastic_modulus"]])
+                               s["bounce"], s["bounce_vel"], s["patch_radius"], s["elastic_modulus"],
+                               s["poissons_ratio"], s["surface_radius"], s["use_patch_radius"], s["mu3"]])
         self.g["fdir1"].append(list(map(float, fdir1)))
         self._ng += 1
         return self._ng - 1 - self._w_g0

@@ -30,11 +30,15 @@ struct dxGeom;
  * (Base::GetId): geoms are indexed in ascending order_key, which fixes the deterministic pair / row order. */
 typedef struct gzcuda_surface {
   double mu, mu2, kp, kd, slip1, slip2, bounce, bounce_vel;
-  double patch_radius, elastic_modulus;   /* torsional friction / elastic-modulus rows: must be 0 (not built) */
+  double patch_radius, elastic_modulus;   /* FrictionPyramid::PatchRadius / ElasticModulus (Hertzian contact when > 0 on both) */
   double fdir1[3];
   unsigned collide_bitmask;
   int max_contacts;
   long order_key;
+  /* FrictionPyramid::PoissonsRatio / SurfaceRadius / UsePatchRadius / MuTorsion; pre-set to Gazebo's defaults
+   * (0.3, DBL_MAX, 1, 0) before the callback runs.  mu3 > 0 (torsional friction) is refused: not built. */
+  double poissons_ratio, surface_radius, mu3;
+  int use_patch_radius;
 } gzcuda_surface;
 typedef int (*gzcuda_surface_fn)(struct dxGeom *geom, gzcuda_surface *out, void *user);
 

@@ -62,12 +62,17 @@ enum { GZ_JP_LOSTOP = 0, GZ_JP_HISTOP = 1, GZ_JP_VEL = 2, GZ_JP_FMAX = 3,
 /* geom_surf[] slots (ODESurfaceParams + FrictionPyramid) */
 enum { GZ_SF_MU = 0, GZ_SF_MU2 = 1, GZ_SF_KP = 2, GZ_SF_KD = 3,
        GZ_SF_SLIP1 = 4, GZ_SF_SLIP2 = 5, GZ_SF_BOUNCE = 6, GZ_SF_BOUNCE_VEL = 7,
-       /* the two contact-row variants this library does NOT build yet; a scene that sets either (> 0) is refused
-        * by gzcuda_batch_create with GZCUDA_E_INVALID instead of being stepped without them:
-        * torsional friction (FrictionPyramid patch radius, contact.cpp:163-216, dContactMu3) and the
-        * elastic-modulus contact row (ODEPhysics.cc:1237-1251, contact.cpp:365-437) */
-       GZ_SF_PATCH_RADIUS = 8, GZ_SF_ELASTIC_MODULUS = 9,
-       GZ_SF_COUNT = 10 };
+       /* Hertzian contact (FrictionPyramid elastic modulus / Poisson's ratio, ODEPhysics.cc:1186-1251, contact.cpp:163-216):
+        * when BOTH surfaces of a pair have an elastic modulus > 0 the normal row's stiffness follows 4/3 E* sqrt(r x)
+        * with r = the pair's patch radius (the larger of the two, when both surfaces say use_patch_radius) or
+        * sqrt(surface radius x depth) with 1/R = 1/R1 + 1/R2.  Gazebo's defaults: patch radius 0, elastic modulus 0 (off),
+        * Poisson's ratio 0.3, surface radius DBL_MAX, use_patch_radius 1 (SurfaceParams.cc:28-32). */
+       GZ_SF_PATCH_RADIUS = 8, GZ_SF_ELASTIC_MODULUS = 9, GZ_SF_POISSON = 10, GZ_SF_SURFACE_RADIUS = 11,
+       GZ_SF_USE_PATCH_RADIUS = 12,
+       /* torsional friction (a fourth contact row, dContactMu3, contact.cpp:365-437) is NOT built: a scene that sets
+        * mu3 > 0 on a surface is refused by gzcuda_batch_create with GZCUDA_E_INVALID instead of being stepped without it */
+       GZ_SF_MU3 = 13,
+       GZ_SF_COUNT = 14 };
 
 /* World-level parameters, shared by every world of a batch
  * (ODEPhysics::Load, gazebo/physics/ode/ODEPhysics.cc:175-243; dWorldCreate

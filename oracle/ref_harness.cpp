@@ -225,9 +225,24 @@ void collide_pair(RefBatch *B, RefWorld *w, int i1, int i2) {
   contact.surface.slip1 *= numc;
   contact.surface.slip2 *= numc;
   contact.surface.slip3 *= numc;
-  contact.surface.patch_radius = 0;
-  contact.surface.surface_radius = 0;
-  contact.surface.use_patch_radius = true;
+  // ODEPhysics.cc:1186-1251: patch radius, curvatures, use_patch_radius; dContactMu3 stays off (the scene format refuses
+  // mu3 > 0); Hertzian contact (dContactEM) when both surfaces have an elastic modulus
+  contact.surface.patch_radius = std::max(s1.s[GZ_SF_PATCH_RADIUS], s2.s[GZ_SF_PATCH_RADIUS]);
+  {
+    double curv1 = 0, curv2 = 0;
+    if (s1.s[GZ_SF_SURFACE_RADIUS] > 0) curv1 = 1 / s1.s[GZ_SF_SURFACE_RADIUS];
+    if (s2.s[GZ_SF_SURFACE_RADIUS] > 0) curv2 = 1 / s2.s[GZ_SF_SURFACE_RADIUS];
+    const double curvSum = curv1 + curv2;
+    contact.surface.surface_radius = 0;
+    if (curvSum > 0) contact.surface.surface_radius = 1 / curvSum;
+    contact.surface.use_patch_radius = s1.s[GZ_SF_USE_PATCH_RADIUS] != 0 && s2.s[GZ_SF_USE_PATCH_RADIUS] != 0;
+    const double nu1 = s1.s[GZ_SF_POISSON], nu2 = s2.s[GZ_SF_POISSON];
+    const double e1 = s1.s[GZ_SF_ELASTIC_MODULUS], e2 = s2.s[GZ_SF_ELASTIC_MODULUS];
+    if (e1 > 0 && e2 > 0) {
+      contact.surface.elastic_modulus = 1.0 / ((1.0 - nu1 * nu1) / e1 + (1.0 - nu2 * nu2) / e2);
+      if (contact.surface.elastic_modulus > 0.0) contact.surface.mode |= dContactEM;
+    }
+  }
   contact.surface.bounce = std::min(s1.s[GZ_SF_BOUNCE], s2.s[GZ_SF_BOUNCE]);
   contact.surface.bounce_vel = std::min(s1.s[GZ_SF_BOUNCE_VEL], s2.s[GZ_SF_BOUNCE_VEL]);
 
@@ -836,6 +851,7 @@ void gzref_world_handles(void *h, int world, void **out) {
 struct AdapterSurface {
   double mu, mu2, kp, kd, slip1, slip2, bounce, bounce_vel, patch_radius, elastic_modulus, fdir1[3];
   unsigned collide_bitmask; int max_contacts; long order_key;
+  double poissons_ratio, surface_radius, mu3; int use_patch_radius;
 };
 int gzref_surface_cb(dGeomID g, AdapterSurface *o, void *user) {
   RefWorld *w = static_cast<RefWorld *>(user);
@@ -844,7 +860,9 @@ int gzref_surface_cb(dGeomID g, AdapterSurface *o, void *user) {
   const Surface &s = w->surf[i];
   o->mu = s.s[GZ_SF_MU]; o->mu2 = s.s[GZ_SF_MU2]; o->kp = s.s[GZ_SF_KP]; o->kd = s.s[GZ_SF_KD];
   o->slip1 = s.s[GZ_SF_SLIP1]; o->slip2 = s.s[GZ_SF_SLIP2]; o->bounce = s.s[GZ_SF_BOUNCE]; o->bounce_vel = s.s[GZ_SF_BOUNCE_VEL];
-  o->patch_radius = 0; o->elastic_modulus = 0;
+  o->patch_radius = s.s[GZ_SF_PATCH_RADIUS]; o->elastic_modulus = s.s[GZ_SF_ELASTIC_MODULUS];
+  o->poissons_ratio = s.s[GZ_SF_POISSON]; o->surface_radius = s.s[GZ_SF_SURFACE_RADIUS];
+  o->use_patch_radius = s.s[GZ_SF_USE_PATCH_RADIUS] != 0; o->mu3 = s.s[GZ_SF_MU3];
   for (int k = 0; k < 3; k++) o->fdir1[k] = s.fdir1[k];
   o->collide_bitmask = s.collide_bitmask; o->max_contacts = s.max_contacts;
   o->order_key = i;   // Gazebo's creation order of the collisions = the scene's geom order

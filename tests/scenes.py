@@ -353,6 +353,39 @@ def carts(n_worlds=3, seed=31):
     return sb.finish(), S.default_params(), None
 
 
+def hertz(n_worlds=2, seed=53):
+    """Hertzian contact (FrictionPyramid elastic modulus, ODEPhysics.cc:1237-1251 / contact.cpp:163-216): soft spheres,
+    boxes and capsules (E = 1e5..1e7 Pa, Poisson's ratio 0.2..0.45) dropped on a soft plane and on each other; half of
+    them use the patch radius (0.02..0.1 m), the others the surface radius (their own radius of curvature, combined as
+    1/R = 1/R1 + 1/R2), a few have no modulus at all (the pair then keeps the kp / kd contact)."""
+    sb = S.SceneBuilder()
+    for w in range(n_worlds):
+        rng = np.random.Generator(np.random.PCG64(seed + w))
+        sb.begin_world()
+        # the plane: soft, flat (surface radius = infinity: Gazebo's default DBL_MAX), patch radius 0.05
+        sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), mu=100.0, mu2=50.0, elastic_modulus=5e6, poissons_ratio=0.3,
+                    patch_radius=0.05, use_patch_radius=float(w % 2))
+        for k in range(14):
+            pos = np.array([rng.uniform(-0.6, 0.6), rng.uniform(-0.6, 0.6), 0.4 + 0.45 * k])
+            q = S.q_random(rng)
+            em = 0.0 if k % 5 == 4 else 10 ** rng.uniform(5, 7)
+            use_patch = float((k + w) % 2)
+            kw = dict(elastic_modulus=em, poissons_ratio=rng.uniform(0.2, 0.45), patch_radius=rng.uniform(0.02, 0.1),
+                      use_patch_radius=use_patch, kp=1e6, kd=10.0)
+            t = k % 3
+            if t == 0:
+                r = rng.uniform(0.1, 0.25); b = sb.add_body(pos, q, 1.0, S.sphere_inertia(1.0, r))
+                sb.add_geom(S.GEOM_SPHERE, (r,), sb.new_space(), body=b, surface_radius=r, **kw)
+            elif t == 1:
+                d = tuple(rng.uniform(0.15, 0.4, 3)); b = sb.add_body(pos, q, 1.0, S.box_inertia(1.0, *d))
+                sb.add_geom(S.GEOM_BOX, d, sb.new_space(), body=b, **kw)      # flat faces: the default surface radius
+            else:
+                r, l = rng.uniform(0.08, 0.15), rng.uniform(0.2, 0.5); b = sb.add_body(pos, q, 1.0, S.cylinder_inertia(1.0, r, l))
+                sb.add_geom(S.GEOM_CAPSULE, (r, l), sb.new_space(), body=b, surface_radius=r, **kw)
+        sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 def ray_targets(n_worlds=2, per_type=6, seed=77):
     """Worlds for the laser: a ground plane and, floating at rest (no gravity flag needed: they are never stepped far), boxes,
     spheres, capsules and cylinders at random poses inside a 6 m cube, one sensor-category geom that rays must not see."""
@@ -407,4 +440,5 @@ GOLDEN = {
     "fdir1": (fdir1, 300),
     "dyn_inertia": (dyn_inertia, 400),
     "carts": (carts, 600),
+    "hertz": (hertz, 700),
 }

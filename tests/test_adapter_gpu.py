@@ -111,6 +111,13 @@ def test_adapter_carts_on_hinge2_joints(adapter, oracle):
 
 
 @pytest.mark.gpu
+def test_adapter_hertzian_contacts(adapter, oracle):
+    """Elastic modulus, Poisson's ratio, patch / surface radius travel through the surface callback (gzcuda_surface)."""
+    sc, p, _ = scenes.hertz()
+    _run(adapter, oracle, sc, p, steps=400, every=100)
+
+
+@pytest.mark.gpu
 def test_adapter_laser_over_live_ode_objects(adapter, oracle):
     """gzcuda_dworld_ray_query: the laser against a LIVE ODE world (what ODEMultiRayShape::UpdateRays does with
     dSpaceCollide2) - ranges bit-exact against the reference's own ray colliders on the same objects, and the dxGeom

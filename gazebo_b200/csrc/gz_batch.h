@@ -74,9 +74,11 @@ struct Joint {
   double lambda[6], lambda_erp[6];
   double cum_angle;
   double limit_err;
+  double cum_angle2, limit_err2;   // universal joints: axis 2 (limot2)
   double pd[6];      // amplitude, frequency, phase, kp, kd, torque clamp (<=0 off)
   int type, b1, b2;  // GLOBAL body indices, b2 = -1 for the world
   int limit;         // dxJointLimitMotor::limit
+  int limit2;        // ... of a universal joint's second axis
   int m;             // rows this step (0 = not in an active island)
   int row0;          // first row (world-local)
   int world;

@@ -222,11 +222,6 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         return fail(GZCUDA_E_INVALID, "unknown joint type");
       if (J.type == GZ_JOINT_HINGE2 && sc->joint_body2[j] < 0)
         return fail(GZCUDA_E_INVALID, "a hinge2 joint needs two bodies (joints/hinge2.cpp:31)");
-      if (J.type == GZ_JOINT_UNIVERSAL) {
-        const double *P = sc->joint_param + GZ_JP_COUNT * j;
-        if (P[GZ_JP_FMAX] > 0 || std::isfinite(P[GZ_JP_LOSTOP]) || std::isfinite(P[GZ_JP_HISTOP]))
-          return fail(GZCUDA_E_INVALID, "universal joint limits and motors are not supported");
-      }
       const int nbw = sc->body_off[w + 1] - sc->body_off[w];
       if (sc->joint_body1[j] < 0 || sc->joint_body1[j] >= nbw || sc->joint_body2[j] >= nbw)
         return fail(GZCUDA_E_INVALID, "joint body index out of range");

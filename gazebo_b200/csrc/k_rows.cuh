@@ -29,6 +29,15 @@ __device__ inline double hinge2_angle1(const DevBatch &B, const Joint &j) {
   return -gzdet_atan2(y, x);
 }
 
+// getHingeAngleFromRelativeQuat (joint.cpp:391-432)
+__device__ inline double angle_from_relative_quat(const double *qrel, const double *axis) {
+  double cost2 = qrel[0];
+  double sint2 = sqrt(qrel[1] * qrel[1] + qrel[2] * qrel[2] + qrel[3] * qrel[3]);
+  double theta = (dot3(qrel + 1, axis) >= 0) ? (2 * gzdet_atan2(sint2, cost2)) : (2 * gzdet_atan2(sint2, -cost2));
+  if (theta > 3.14159265358979323846) theta -= 2 * 3.14159265358979323846;
+  return -theta;
+}
+
 __device__ inline double hinge_angle(const DevBatch &B, const Joint &j) {
   double qrel[4];
   const Body &b1 = B.body[j.b1];
@@ -39,11 +48,75 @@ __device__ inline double hinge_angle(const DevBatch &B, const Joint &j) {
   } else {
     qmul3(qrel, b1.q, j.qrel);
   }
-  double cost2 = qrel[0];
-  double sint2 = sqrt(qrel[1] * qrel[1] + qrel[2] * qrel[2] + qrel[3] * qrel[3]);
-  double theta = (dot3(qrel + 1, j.axis1) >= 0) ? (2 * gzdet_atan2(sint2, cost2)) : (2 * gzdet_atan2(sint2, -cost2));
-  if (theta > 3.14159265358979323846) theta -= 2 * 3.14159265358979323846;
-  return -theta;
+  return angle_from_relative_quat(qrel, j.axis1);
+}
+
+// dRFrom2Axes (rotation.cpp:95-136) + dRtoQ / dQfromR (:261-311): the frame whose x axis is a and whose y axis is b made
+// perpendicular to a, as a quaternion
+__device__ inline void quat_from_2_axes(double *q, const double *a_in, const double *b_in) {
+  double ax = a_in[0], ay = a_in[1], az = a_in[2], bx = b_in[0], by = b_in[1], bz = b_in[2];
+  double R[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  double l = sqrt(ax * ax + ay * ay + az * az);
+  if (l > 0.0) {
+    l = 1.0 / l;
+    ax *= l; ay *= l; az *= l;
+    const double k = ax * bx + ay * by + az * bz;
+    bx -= k * ax; by -= k * ay; bz -= k * az;
+    l = sqrt(bx * bx + by * by + bz * bz);
+    if (l > 0.0) {
+      l = 1.0 / l;
+      bx *= l; by *= l; bz *= l;
+      R[0] = ax; R[3] = ay; R[6] = az;
+      R[1] = bx; R[4] = by; R[7] = bz;
+      R[2] = -by * az + ay * bz; R[5] = -bz * ax + az * bx; R[8] = -bx * ay + ax * by;
+    }
+  }
+  const double tr = R[0] + R[4] + R[8];
+  if (tr >= 0) {
+    double s = sqrt(tr + 1);
+    q[0] = 0.5 * s;
+    s = 0.5 * (1.0 / s);
+    q[1] = (R[7] - R[5]) * s; q[2] = (R[2] - R[6]) * s; q[3] = (R[3] - R[1]) * s;
+    return;
+  }
+  int c = 0;   // the largest diagonal element, ties as dQfromR's jumps resolve them
+  if (R[4] > R[0]) c = (R[8] > R[4]) ? 2 : 1;
+  else if (R[8] > R[0]) c = 2;
+  if (c == 0) {
+    double s = sqrt((R[0] - (R[4] + R[8])) + 1);
+    q[1] = 0.5 * s; s = 0.5 * (1.0 / s);
+    q[2] = (R[1] + R[3]) * s; q[3] = (R[6] + R[2]) * s; q[0] = (R[7] - R[5]) * s;
+  } else if (c == 1) {
+    double s = sqrt((R[4] - (R[8] + R[0])) + 1);
+    q[2] = 0.5 * s; s = 0.5 * (1.0 / s);
+    q[3] = (R[5] + R[7]) * s; q[1] = (R[1] + R[3]) * s; q[0] = (R[2] - R[6]) * s;
+  } else {
+    double s = sqrt((R[8] - (R[0] + R[4])) + 1);
+    q[3] = 0.5 * s; s = 0.5 * (1.0 / s);
+    q[1] = (R[6] + R[2]) * s; q[2] = (R[5] + R[7]) * s; q[0] = (R[3] - R[1]) * s;
+  }
+}
+
+// dxJointUniversal::getAngles (universal.cpp:75-165): the angles about axis 1 and axis 2
+__device__ inline void universal_angles(const DevBatch &B, const Joint &j, double &angle1, double &angle2) {
+  const Body &b1 = B.body[j.b1];
+  double ax1[3], ax2[3], qcross[4], qq[4], qrel[4], qcross2[4];
+  mul0_331(ax1, b1.R, j.axis1);
+  if (j.b2 >= 0) mul0_331(ax2, B.body[j.b2].R, j.axis2);
+  else { ax2[0] = j.axis2[0]; ax2[1] = j.axis2[1]; ax2[2] = j.axis2[2]; }
+  quat_from_2_axes(qcross, ax1, ax2);
+  qmul1(qq, b1.q, qcross);
+  qmul2(qrel, qq, j.qrel);   // joint_qrel = qrel1
+  angle1 = angle_from_relative_quat(qrel, j.axis1);
+  // the cross for axis 2 = the first one turned by 180 degrees about the direction between the two axes
+  qrel[0] = 0;
+  qrel[1] = ax1[0] + ax2[0]; qrel[2] = ax1[1] + ax2[1]; qrel[3] = ax1[2] + ax2[2];
+  const double l = 1.0 / sqrt(qrel[1] * qrel[1] + qrel[2] * qrel[2] + qrel[3] * qrel[3]);
+  qrel[1] *= l; qrel[2] *= l; qrel[3] *= l;
+  qmul0(qcross2, qrel, qcross);
+  if (j.b2 >= 0) { qmul1(qq, B.body[j.b2].q, qcross2); qmul2(qrel, qq, &j.param[GZ_JP_QREL2]); }
+  else qmul2(qrel, qcross2, &j.param[GZ_JP_QREL2]);
+  angle2 = -angle_from_relative_quat(qrel, j.axis2);
 }
 
 // dJointGetSliderPosition (slider.cpp:40-84); anchor1 holds dxJointSlider::offset
@@ -287,7 +360,28 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
           if (j.limit || j.param[GZ_JP_FMAX] > 0) m++;
           if (j.param[GZ_JP_FMAX2] > 0) m++;
         } else if (j.type == GZ_JOINT_UNIVERSAL) {
-          m = 4;   // limits and motors of the two axes are not supported (gzcuda_batch_create checks)
+          // dxJointUniversal::getInfo1 (universal.cpp:268-307)
+          m = 4;
+          const double lo1 = j.param[GZ_JP_LOSTOP], hi1 = j.param[GZ_JP_HISTOP];
+          const double lo2 = j.param[GZ_JP_LOSTOP2], hi2 = j.param[GZ_JP_HISTOP2];
+          const bool limiting1 = lo1 <= hi1, limiting2 = lo2 <= hi2;
+          j.limit = 0; j.limit2 = 0;
+          if (limiting1 || limiting2) {
+            double angle1, angle2;
+            universal_angles(B, j, angle1, angle2);
+            j.cum_angle = shortest_angular_distance_update(j.cum_angle, angle1);
+            j.cum_angle2 = shortest_angular_distance_update(j.cum_angle2, angle2);
+            if (limiting1) {
+              if (j.cum_angle <= lo1) { j.limit = 1; j.limit_err = j.cum_angle - lo1; }
+              else if (j.cum_angle >= hi1) { j.limit = 2; j.limit_err = j.cum_angle - hi1; }
+            }
+            if (limiting2) {
+              if (j.cum_angle2 <= lo2) { j.limit2 = 1; j.limit_err2 = j.cum_angle2 - lo2; }
+              else if (j.cum_angle2 >= hi2) { j.limit2 = 2; j.limit_err2 = j.cum_angle2 - hi2; }
+            }
+          }
+          if (j.limit || j.param[GZ_JP_FMAX] > 0) m++;
+          if (j.limit2 || j.param[GZ_JP_FMAX2] > 0) m++;
         } else if (j.type == GZ_JOINT_SLIDER) {
           // dxJointSlider::getInfo1 (slider.cpp:118-148)
           m = (j.param[GZ_JP_FMAX] > 0) ? 6 : 5;

@@ -177,9 +177,9 @@ __global__ void k_rows_joint(DevBatch B) {
     rows[4].c = k * dot3(bb, q);
     if (j.m == 6) add_limot(B, j, rows[5], ax1, fps, true);
   } else if (j.type == GZ_JOINT_BALL || j.type == GZ_JOINT_UNIVERSAL) {
-    // dxJointBall::getInfo2 (ball.cpp:56-69), dxJointUniversal::getInfo2 (universal.cpp:306-372; without
-    // limits and motors): setBall, then for the universal joint one row that keeps the axes perpendicular
-    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < j.m; r++) rows[r].cfm = j.param[GZ_JP_CFM];
+    // dxJointBall::getInfo2 (ball.cpp:56-69), dxJointUniversal::getInfo2 (universal.cpp:310-389): setBall, then for the
+    // universal joint one row that keeps the axes perpendicular and the limit motors of its two axes
+    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < (j.type == GZ_JOINT_UNIVERSAL ? 4 : j.m); r++) rows[r].cfm = j.param[GZ_JP_CFM];
     set_ball(rows, b1, b2, j, fps * erp);
     if (j.type == GZ_JOINT_UNIVERSAL) {
       double ax1[3], ax2[3], t[3], p[3];
@@ -193,6 +193,16 @@ __global__ void k_rows_joint(DevBatch B) {
       for (int i = 0; i < 3; i++) rows[3].J[3 + i] = p[i];
       if (b2) for (int i = 0; i < 3; i++) rows[3].J[9 + i] = -p[i];
       rows[3].c = fps * erp * -k;
+      // the limit / motor of axis 1, then of axis 2 (universal.cpp:384-388)
+      int row = 4;
+      if (j.limit || j.param[GZ_JP_FMAX] > 0) row += add_limot(B, j, rows[row], ax1, fps, true);
+      if (j.limit2 || j.param[GZ_JP_FMAX2] > 0) {
+        Limot M2;
+        M2.lostop = j.param[GZ_JP_LOSTOP2]; M2.histop = j.param[GZ_JP_HISTOP2]; M2.vel = j.param[GZ_JP_VEL2]; M2.fmax = j.param[GZ_JP_FMAX2];
+        M2.fudge = j.param[GZ_JP_FUDGE2]; M2.bounce = j.param[GZ_JP_BOUNCE2]; M2.normal_cfm = j.param[GZ_JP_NORMAL_CFM2];
+        M2.stop_erp = j.param[GZ_JP_STOP_ERP2]; M2.stop_cfm = j.param[GZ_JP_STOP_CFM2]; M2.limit_err = j.limit_err2; M2.limit = j.limit2;
+        add_limot(B, j, rows[row], ax2, fps, true, M2);
+      }
     }
   } else if (j.type == GZ_JOINT_HINGE2) {
     // dxJointHinge2::getInfo2 (hinge2.cpp:158-222): ball rows aligned with axis 1 (row 0 = the suspension), one row that

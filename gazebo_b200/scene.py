@@ -20,7 +20,8 @@ BODY_NO_GRAVITY, BODY_AUTO_DISABLE, BODY_DISABLED, BODY_NO_GYRO = 1, 2, 4, 8
 JP_LOSTOP, JP_HISTOP, JP_VEL, JP_FMAX, JP_FUDGE, JP_BOUNCE, JP_NORMAL_CFM, \
     JP_STOP_ERP, JP_STOP_CFM, JP_ERP, JP_CFM = range(11)
 JP_VEL2, JP_FMAX2, JP_SUSP_ERP, JP_SUSP_CFM, JP_V1, JP_V2, JP_C0, JP_S0 = 12, 13, 14, 15, 16, 19, 22, 23
-JP_COUNT = 24
+JP_LOSTOP2, JP_HISTOP2, JP_FUDGE2, JP_BOUNCE2, JP_NORMAL_CFM2, JP_STOP_ERP2, JP_STOP_CFM2, JP_QREL2 = 24, 25, 26, 27, 28, 29, 30, 31
+JP_COUNT = 36
 SF_MU, SF_MU2, SF_KP, SF_KD, SF_SLIP1, SF_SLIP2, SF_BOUNCE, SF_BOUNCE_VEL = range(8)
 SF_PATCH_RADIUS, SF_ELASTIC_MODULUS, SF_POISSON, SF_SURFACE_RADIUS, SF_USE_PATCH_RADIUS, SF_MU3 = 8, 9, 10, 11, 12, 13
 SF_COUNT = 14
@@ -320,9 +321,12 @@ class SceneBuilder:
         self._push_joint(JOINT_BALL, b1, b2, a1, a2, z, z, (1, 0, 0, 0), self.joint_params(**params))
         return self._nj - 1 - self._w_j0
 
-    def add_universal(self, b1, b2, anchor, axis1, axis2, **params):
-        """Universal joint (dxJointUniversal): axis1 is fixed in body 1, axis2 in body 2 (or the world);
-        both in world coordinates at the current poses.  Joint limits and motors are not supported."""
+    def add_universal(self, b1, b2, anchor, axis1, axis2, lostop2=-math.inf, histop2=math.inf, vel2=0.0, fmax2=0.0,
+                      fudge2=1.0, bounce2=0.0, normal_cfm2=0.0, stop_erp2=0.2, stop_cfm2=0.0, **params):
+        """Universal joint (dxJointUniversal): axis1 is fixed in body 1, axis2 in body 2 (or the world); both in world
+        coordinates at the current poses.  params = the limit motor of axis 1, the *2 arguments that of axis 2.  qrel1 /
+        qrel2 (the joint's cross against the two bodies at attach time, computeInitialRelativeRotations,
+        universal.cpp:716-758) are computed here and travel in the scene: both sides of a parity test read the same."""
         p1, q1 = self._body_pose(b1)
         R1 = q_to_R(q1)
         anchor = np.asarray(anchor, float)
@@ -336,8 +340,35 @@ class SceneBuilder:
             a2 = R2.T @ (anchor - p2)
             ax2 = R2.T @ axis2
         else:
+            q2 = np.array([1.0, 0, 0, 0])
             a2, ax2 = anchor, axis2
-        self._push_joint(JOINT_UNIVERSAL, b1, b2, a1, a2, ax1, ax2, (1, 0, 0, 0), self.joint_params(**params))
+
+        def cross_quat(a, b):   # dRFrom2Axes + dRtoQ: the frame whose x is a and whose y is b made perpendicular to a
+            a = a / np.linalg.norm(a)
+            b = b - float(a @ b) * a
+            b = b / np.linalg.norm(b)
+            R = np.stack([a, b, np.cross(a, b)], axis=1)
+            tr = R[0, 0] + R[1, 1] + R[2, 2]
+            if tr >= 0:
+                sq = math.sqrt(tr + 1); w = 0.5 * sq; sq = 0.5 / sq
+                return np.array([w, (R[2, 1] - R[1, 2]) * sq, (R[0, 2] - R[2, 0]) * sq, (R[1, 0] - R[0, 1]) * sq])
+            k = int(np.argmax([R[0, 0], R[1, 1], R[2, 2]]))
+            i1, i2 = (k + 1) % 3, (k + 2) % 3
+            sq = math.sqrt((R[k, k] - (R[i1, i1] + R[i2, i2])) + 1)
+            q = np.zeros(4); q[1 + k] = 0.5 * sq; sq = 0.5 / sq
+            q[1 + i1] = (R[k, i1] + R[i1, k]) * sq; q[1 + i2] = (R[i2, k] + R[k, i2]) * sq; q[0] = (R[i2, i1] - R[i1, i2]) * sq
+            return q
+
+        g1 = R1 @ ax1
+        g2 = (q_to_R(q2) @ ax2) if b2 >= 0 else ax2
+        qrel1 = q_mul(q_conj(q1), cross_quat(g1, g2))
+        qrel2 = q_mul(q_conj(q2), cross_quat(g2, g1))
+        P = self.joint_params(**params)
+        P[JP_VEL2], P[JP_FMAX2] = vel2, fmax2
+        P[JP_LOSTOP2], P[JP_HISTOP2], P[JP_FUDGE2], P[JP_BOUNCE2] = lostop2, histop2, fudge2, bounce2
+        P[JP_NORMAL_CFM2], P[JP_STOP_ERP2], P[JP_STOP_CFM2] = normal_cfm2, stop_erp2, stop_cfm2
+        P[JP_QREL2:JP_QREL2 + 4] = list(qrel2)
+        self._push_joint(JOINT_UNIVERSAL, b1, b2, a1, a2, ax1, ax2, tuple(qrel1), P)
         return self._nj - 1 - self._w_j0
 
     def add_slider(self, b1, b2, axis, **params):

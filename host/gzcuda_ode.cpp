@@ -133,6 +133,16 @@ int joint_params(dxJoint *j, double *P) {
     case dJointTypeSlider: limot_params(static_cast<dxJointSlider *>(j)->limot, P); return GZ_JOINT_SLIDER;
     case dJointTypeFixed: return GZ_JOINT_FIXED;
     case dJointTypeBall: return GZ_JOINT_BALL;
+    case dJointTypeUniversal: {
+      const dxJointUniversal *uj = static_cast<dxJointUniversal *>(j);
+      limot_params(uj->limot1, P);
+      const dxJointLimitMotor &l2 = uj->limot2;
+      P[GZ_JP_VEL2] = l2.vel; P[GZ_JP_FMAX2] = l2.fmax; P[GZ_JP_LOSTOP2] = l2.lostop; P[GZ_JP_HISTOP2] = l2.histop;
+      P[GZ_JP_FUDGE2] = l2.fudge_factor; P[GZ_JP_BOUNCE2] = l2.bounce; P[GZ_JP_NORMAL_CFM2] = l2.normal_cfm;
+      P[GZ_JP_STOP_ERP2] = l2.stop_erp; P[GZ_JP_STOP_CFM2] = l2.stop_cfm;
+      for (int k = 0; k < 4; k++) P[GZ_JP_QREL2 + k] = uj->qrel2[k];
+      return GZ_JOINT_UNIVERSAL;
+    }
     case dJointTypeHinge2: {
       const dxJointHinge2 *h2 = static_cast<dxJointHinge2 *>(j);
       limot_params(h2->limot1, P);
@@ -259,7 +269,7 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
   for (int i = 0; i < nj; i++) {
     dxJoint *j = m->joints[i];
     jtype[i] = joint_params(j, &m->jparam[(size_t)GZ_JP_COUNT * i]);
-    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball, hinge2");
+    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball, universal, hinge2");
     if (!j->node[0].body) return fail(GZCUDA_E_INVALID, "a joint without bodies");
     auto i1 = bidx.find(j->node[0].body);
     if (i1 == bidx.end()) return fail(GZCUDA_E_INVALID, "a joint is attached to a body of another world");
@@ -279,6 +289,10 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
       const dxJointFixed *fj = static_cast<dxJointFixed *>(j);
       for (int k = 0; k < 3; k++) ja1[3 * i + k] = fj->offset[k];
       for (int k = 0; k < 4; k++) jq[4 * i + k] = fj->qrel[k];
+    } else if (jtype[i] == GZ_JOINT_UNIVERSAL) {
+      const dxJointUniversal *uj = static_cast<dxJointUniversal *>(j);
+      for (int k = 0; k < 3; k++) { ja1[3 * i + k] = uj->anchor1[k]; ja2[3 * i + k] = uj->anchor2[k]; jx1[3 * i + k] = uj->axis1[k]; jx2[3 * i + k] = uj->axis2[k]; }
+      for (int k = 0; k < 4; k++) jq[4 * i + k] = uj->qrel1[k];
     } else if (jtype[i] == GZ_JOINT_HINGE2) {
       const dxJointHinge2 *h2 = static_cast<dxJointHinge2 *>(j);
       for (int k = 0; k < 3; k++) { ja1[3 * i + k] = h2->anchor1[k]; ja2[3 * i + k] = h2->anchor2[k]; jx1[3 * i + k] = h2->axis1[k]; jx2[3 * i + k] = h2->axis2[k]; }
@@ -424,6 +438,7 @@ int download(Mirror *m) {
       dxJoint *j = m->joints[i];
       for (int k = 0; k < 6; k++) { j->lambda[k] = lam[6 * (size_t)i + k]; j->lambda_erp[k] = lam_erp[6 * (size_t)i + k]; }
       if (j->type() == dJointTypeHinge) static_cast<dxJointHinge *>(j)->cumulative_angle = cum[i];
+      if (j->type() == dJointTypeUniversal) static_cast<dxJointUniversal *>(j)->cumulative_angle1 = cum[i];   // (axis 2's stays on the device)
     }
   }
   return 0;

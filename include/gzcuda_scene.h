@@ -57,7 +57,13 @@ enum { GZ_JP_LOSTOP = 0, GZ_JP_HISTOP = 1, GZ_JP_VEL = 2, GZ_JP_FMAX = 3,
        GZ_JP_V1 = 16,      /* v1[3]: 16..18 */
        GZ_JP_V2 = 19,      /* v2[3]: 19..21 */
        GZ_JP_C0 = 22, GZ_JP_S0 = 23,
-       GZ_JP_COUNT = 24 };
+       /* universal joints: the rest of the second limit motor (limot2: axis 2 has stops too, universal.cpp:268-307; its
+        * vel / fmax are GZ_JP_VEL2 / GZ_JP_FMAX2) and qrel2; joint_qrel holds qrel1 (the relative rotations of the
+        * joint's cross against the two bodies, computeInitialRelativeRotations, universal.cpp:716-758) */
+       GZ_JP_LOSTOP2 = 24, GZ_JP_HISTOP2 = 25, GZ_JP_FUDGE2 = 26, GZ_JP_BOUNCE2 = 27, GZ_JP_NORMAL_CFM2 = 28,
+       GZ_JP_STOP_ERP2 = 29, GZ_JP_STOP_CFM2 = 30,
+       GZ_JP_QREL2 = 31,   /* qrel2[4]: 31..34 */
+       GZ_JP_COUNT = 36 };
 
 /* geom_surf[] slots (ODESurfaceParams + FrictionPyramid) */
 enum { GZ_SF_MU = 0, GZ_SF_MU2 = 1, GZ_SF_KP = 2, GZ_SF_KD = 3,

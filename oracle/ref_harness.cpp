@@ -675,7 +675,13 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
           uj->axis1[k] = sc->joint_axis1[3 * j + k];
           uj->axis2[k] = sc->joint_axis2[3 * j + k];
         }
-        uj->computeInitialRelativeRotations();   // qrel1 / qrel2: joint angles only (limits are not used)
+        for (int k = 0; k < 4; k++) { uj->qrel1[k] = sc->joint_qrel[4 * j + k]; uj->qrel2[k] = P[GZ_JP_QREL2 + k]; }
+        uj->limot1.lostop = P[GZ_JP_LOSTOP]; uj->limot1.histop = P[GZ_JP_HISTOP]; uj->limot1.vel = P[GZ_JP_VEL]; uj->limot1.fmax = P[GZ_JP_FMAX];
+        uj->limot1.fudge_factor = P[GZ_JP_FUDGE]; uj->limot1.bounce = P[GZ_JP_BOUNCE]; uj->limot1.normal_cfm = P[GZ_JP_NORMAL_CFM];
+        uj->limot1.stop_erp = P[GZ_JP_STOP_ERP]; uj->limot1.stop_cfm = P[GZ_JP_STOP_CFM];
+        uj->limot2.lostop = P[GZ_JP_LOSTOP2]; uj->limot2.histop = P[GZ_JP_HISTOP2]; uj->limot2.vel = P[GZ_JP_VEL2]; uj->limot2.fmax = P[GZ_JP_FMAX2];
+        uj->limot2.fudge_factor = P[GZ_JP_FUDGE2]; uj->limot2.bounce = P[GZ_JP_BOUNCE2]; uj->limot2.normal_cfm = P[GZ_JP_NORMAL_CFM2];
+        uj->limot2.stop_erp = P[GZ_JP_STOP_ERP2]; uj->limot2.stop_cfm = P[GZ_JP_STOP_CFM2];
       } else if (sc->joint_type[j] == GZ_JOINT_HINGE2) {
         if (!b2) return nullptr;
         jt = dJointCreateHinge2(w->world, 0);
@@ -950,7 +956,8 @@ void gzref_get_joint_state(void *h, double *lambda, double *lambda_erp, double *
     for (size_t k = 0; k < w->joints.size(); k++) {
       dxJoint *jt = w->joints[k];
       for (int r = 0; r < 6; r++) { lambda[6 * j + r] = jt->lambda[r]; lambda_erp[6 * j + r] = jt->lambda_erp[r]; }
-      cum_angle[j] = (w->joint_type[k] == GZ_JOINT_HINGE) ? ((dxJointHinge *)jt)->cumulative_angle : 0.0;
+      cum_angle[j] = (w->joint_type[k] == GZ_JOINT_HINGE) ? ((dxJointHinge *)jt)->cumulative_angle :
+                     (w->joint_type[k] == GZ_JOINT_UNIVERSAL) ? ((dxJointUniversal *)jt)->cumulative_angle1 : 0.0;
       j++;
     }
 }

@@ -353,6 +353,37 @@ def carts(n_worlds=3, seed=31):
     return sb.finish(), S.default_params(), None
 
 
+def gimbals(n_worlds=2, seed=61):
+    """Universal joints with stops and motors on both axes (dxJointUniversal limot1 / limot2, universal.cpp:268-389):
+    an arm on the world swinging into the stops of both axes (bounce on one), a two-link arm whose second joint has a
+    motor on axis 1 driving into a stop (fudge factor) and stops on axis 2, a link whose axis 2 is locked by equal stops
+    and powered on axis 1; links fall onto the plane as well."""
+    sb = S.SceneBuilder()
+    for w in range(n_worlds):
+        rng = np.random.Generator(np.random.PCG64(seed + w))
+        sb.begin_world()
+        sb.add_ground_plane()
+        sp = sb.new_space()
+        a = sb.add_body([0.0, 0.0, 1.0], mass=1.0, inertia=S.box_inertia(1.0, 0.1, 0.1, 0.5), avel=tuple(rng.uniform(-3, 3, 3)))
+        sb.add_geom(S.GEOM_BOX, (0.1, 0.1, 0.5), sp, body=a)
+        sb.add_universal(a, -1, [0.0, 0.0, 1.25], [1, 0, 0], [0, 1, 0], lostop=-0.4, histop=0.3, stop_erp=0.3, stop_cfm=1e-5,
+                         lostop2=-0.25, histop2=0.35, bounce2=0.5, stop_erp2=0.25)
+        b = sb.add_body([0.0, 0.0, 0.5], S.q_from_rpy(0.05, -0.1, 0.0), mass=0.6, inertia=S.box_inertia(0.6, 0.1, 0.1, 0.4),
+                        lvel=(0.5, -0.4, 0.0))
+        sb.add_geom(S.GEOM_BOX, (0.1, 0.1, 0.4), sp, body=b)
+        sb.add_universal(a, b, [0.0, 0.0, 0.75], [0, 1, 0], [1, 0, 0], vel=1.5, fmax=0.8, fudge=0.4, lostop=-0.5, histop=0.2,
+                         lostop2=-0.3, histop2=0.3, erp=0.3, cfm=1e-6)
+        sp2 = sb.new_space()
+        c = sb.add_body([1.5, 0.0, 0.9], mass=0.8, inertia=S.box_inertia(0.8, 0.4, 0.1, 0.1))
+        sb.add_geom(S.GEOM_BOX, (0.4, 0.1, 0.1), sp2, body=c)
+        d = sb.add_body([1.9, 0.0, 0.9], S.q_from_rpy(0.0, 0.0, 0.2 * (w + 1)), mass=0.5, inertia=S.box_inertia(0.5, 0.4, 0.1, 0.1))
+        sb.add_geom(S.GEOM_BOX, (0.4, 0.1, 0.1), sp2, body=d)
+        sb.add_universal(c, d, [1.7, 0.0, 0.9], [0, 0, 1], [0, 1, 0], vel=-2.0, fmax=0.5, lostop2=0.0, histop2=0.0, vel2=0.7, fmax2=0.3,
+                         normal_cfm=1e-6, normal_cfm2=1e-6)
+        sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 def hertz(n_worlds=2, seed=53):
     """Hertzian contact (FrictionPyramid elastic modulus, ODEPhysics.cc:1237-1251 / contact.cpp:163-216): soft spheres,
     boxes and capsules (E = 1e5..1e7 Pa, Poisson's ratio 0.2..0.45) dropped on a soft plane and on each other; half of
@@ -441,4 +472,5 @@ GOLDEN = {
     "dyn_inertia": (dyn_inertia, 400),
     "carts": (carts, 600),
     "hertz": (hertz, 700),
+    "gimbals": (gimbals, 800),
 }

@@ -111,6 +111,13 @@ def test_adapter_carts_on_hinge2_joints(adapter, oracle):
 
 
 @pytest.mark.gpu
+def test_adapter_universal_joints_with_stops_and_motors(adapter, oracle):
+    """dxJointUniversal objects mirrored from the live world: qrel1 / qrel2 and both limit motors."""
+    sc, p, _ = scenes.gimbals()
+    _run(adapter, oracle, sc, p, steps=400, every=100)
+
+
+@pytest.mark.gpu
 def test_adapter_hertzian_contacts(adapter, oracle):
     """Elastic modulus, Poisson's ratio, patch / surface radius travel through the surface callback (gzcuda_surface)."""
     sc, p, _ = scenes.hertz()

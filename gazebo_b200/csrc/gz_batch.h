@@ -19,6 +19,8 @@
 #define GZ_PAIR_MAXC 16  // contacts one geom pair can yield (box-box: 8, cylinder-box: up to 13)
 #define GZ_PGSB_NKEY 512   // period histogram of k_border: periods >= 511 share the last key
 #define GZ_ENT 20
+#define GZ_JP_HOT 12   // joint_param slots kept in struct Joint; the rest ([GZ_JP_COUNT - GZ_JP_HOT] per joint) in joint_ext
+#define GZ_SF_HOT 8    // geom_surf slots kept in struct Geom; the rest ([GZ_SF_COUNT - GZ_SF_HOT] per geom) in geom_ext
 #define GZ_PGSC_MAXCTA 1280  // k_pgsc: CTAs of one world; worlds beyond fall back to k_pgsd
 #define GZ_PGSC_TAB (GZ_PGSC_MAXCTA + 9)          // doubles per body-owner PGS entry (k_pgsb.cuh)
 #define GZ_CHAIN_NCLS 4   // shared-memory size classes of chain-mode worlds (k_pgs_chain.cuh), at most 5
@@ -60,17 +62,18 @@ struct Geom {
   double pos[3];     // final pose (dxGeom::final_posr)
   double R[9];
   double aabb[6];
-  double surf[GZ_SF_COUNT];
+  double surf[GZ_SF_HOT];    // geom_surf slots 0..7; the Hertzian-contact slots live in DevBatch::geom_ext (em_on says whether to look)
   double fdir1[3];
   int type, body, space, world;   // body: GLOBAL body index or -1
   unsigned cat, col, scat, scol;  // geom bits and the bits of its space (ODECollision.cc:161-176)
   unsigned bitmask;
   int max_contacts;
+  int em_on, pad_;     // elastic modulus > 0 (ODEPhysics.cc:1241-1251 needs it on BOTH geoms of a pair)
 };
 
 struct Joint {
   double anchor1[3], anchor2[3], axis1[3], axis2[3], qrel[4];
-  double param[GZ_JP_COUNT];
+  double param[GZ_JP_HOT];   // joint_param slots 0..11; the hinge2 / universal-only slots live in DevBatch::joint_ext
   double lambda[6], lambda_erp[6];
   double cum_angle;
   double limit_err;
@@ -173,6 +176,8 @@ struct DevBatch {
   int pgsc_bodies;       // k_pgsc: bodies per CTA = warps per CTA x pgsc_bpw
   int pgsc_bpw;          // k_pgsc: bodies per warp (<= 16; the other lanes of the warp idle: a warp is ONE instruction stream
                          // that runs its bodies' rows one after the other, so fewer bodies per warp = more streams)
+  double *joint_ext;     // [nj][GZ_JP_COUNT - GZ_JP_HOT] the joint_param slots only hinge2 / universal joints read
+  double *geom_ext;      // [ng][GZ_SF_COUNT - GZ_SF_HOT] patch radius, elastic modulus, Poisson's ratio, surface radius, use_patch_radius, mu3
   int *cta_e0;           // [n_worlds][GZ_PGSC_TAB] first entry of every CTA of k_pgsc (then the world's end), else null
   int *bs_clist;         // [2 * contacts] k_bsched_large's per-body contact lists (large worlds only, else null)
   int *bs_glob;          // [5][max_nb] k_bsched's per-body tables for worlds too large for shared memory (else null)

@@ -209,6 +209,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   std::vector<Body> hb(nb);
   std::vector<Geom> hg(ng);
   std::vector<Joint> hj(nj);
+  std::vector<double> hjx((size_t)(GZ_JP_COUNT - GZ_JP_HOT) * nj), hgx((size_t)(GZ_SF_COUNT - GZ_SF_HOT) * ng);   // the cold slots (joint_ext, geom_ext)
   std::vector<WorldInfo> hw(W);
   std::vector<int> bj;                  // CSR payload
   std::vector<std::vector<int>> adj(nb);
@@ -232,7 +233,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         J.axis1[k] = sc->joint_axis1[3 * j + k]; J.axis2[k] = sc->joint_axis2[3 * j + k];
       }
       for (int k = 0; k < 4; k++) J.qrel[k] = sc->joint_qrel[4 * j + k];
-      for (int k = 0; k < GZ_JP_COUNT; k++) J.param[k] = sc->joint_param[GZ_JP_COUNT * j + k];
+      for (int k = 0; k < GZ_JP_HOT; k++) J.param[k] = sc->joint_param[GZ_JP_COUNT * j + k];
+      for (int k = GZ_JP_HOT; k < GZ_JP_COUNT; k++) hjx[(size_t)(GZ_JP_COUNT - GZ_JP_HOT) * j + k - GZ_JP_HOT] = sc->joint_param[GZ_JP_COUNT * j + k];
       J.world = w;
       adj[J.b1].push_back(j);
       if (J.b2 >= 0) adj[J.b2].push_back(j);
@@ -300,8 +302,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       for (int k = 0; k < 3; k++) { G.opos[k] = sc->geom_pos[3 * g + k]; G.fdir1[k] = sc->geom_fdir1[3 * g + k]; }
       if (sc->geom_rot) for (int k = 0; k < 9; k++) G.oR[k] = sc->geom_rot[9 * g + k];
       else q_to_R(sc->geom_quat + 4 * g, G.oR);   // dGeomSetOffsetQuaternion / dGeomSetQuaternion: dQtoR, no normalisation
-      for (int k = 0; k < GZ_SF_COUNT; k++) G.surf[k] = sc->geom_surf[GZ_SF_COUNT * g + k];
-      if (G.surf[GZ_SF_MU3] > 0)
+      for (int k = 0; k < GZ_SF_HOT; k++) G.surf[k] = sc->geom_surf[GZ_SF_COUNT * g + k];
+      for (int k = GZ_SF_HOT; k < GZ_SF_COUNT; k++) hgx[(size_t)(GZ_SF_COUNT - GZ_SF_HOT) * g + k - GZ_SF_HOT] = sc->geom_surf[GZ_SF_COUNT * g + k];
+      G.em_on = sc->geom_surf[GZ_SF_COUNT * g + GZ_SF_ELASTIC_MODULUS] > 0 ? 1 : 0;
+      if (sc->geom_surf[GZ_SF_COUNT * g + GZ_SF_MU3] > 0)
         return fail(GZCUDA_E_INVALID, "torsional friction (mu3 > 0: a fourth contact row) is not supported");
       G.cat = sc->geom_category_bits[g]; G.col = sc->geom_collide_bits[g];
       G.scat = scat[G.space]; G.scol = scol[G.space];
@@ -355,6 +359,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_upload(b, &d.body_joint, bj))) return rc;
   if ((rc = dev_upload(b, &d.geom, hg))) return rc;
   if ((rc = dev_upload(b, &d.joint, hj))) return rc;
+  if ((rc = dev_upload(b, &d.joint_ext, hjx))) return rc;
+  if ((rc = dev_upload(b, &d.geom_ext, hgx))) return rc;
   if ((rc = dev_alloc(b, &d.pair, (size_t)2 * pair_tot))) return rc;
   if ((rc = dev_alloc(b, &d.pair_nc, (size_t)pair_tot))) return rc;
   if ((rc = dev_alloc(b, &d.pair_contact, (size_t)7 * GZ_PAIR_MAXC * pair_tot))) return rc;
@@ -812,6 +818,14 @@ static int launch_collision(gzcuda_batch *b) {
   return 0;
 }
 
+// developer switch GZCUDA_DEBUG_SYNC=1: synchronise at a few points of the step and name the phase a fault came from
+static void dbg_point(gzcuda_batch *b, const char *what) {
+  static const bool on = getenv("GZCUDA_DEBUG_SYNC") && atoi(getenv("GZCUDA_DEBUG_SYNC")) != 0;
+  if (!on) return;
+  const cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { fprintf(stderr, "gzcuda debug: %s after %s (step %lld)\n", cudaGetErrorString(e), what, (long long)b->d.step_index); fflush(stderr); }
+}
+
 static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1) {
   DevBatch &d = b->d;
   const int W = d.n_worlds, T = 128;
@@ -824,6 +838,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     b->last_launches += W - 1;
   } else
     k_assemble1<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // islands, body prologue, row counts
+  dbg_point(b, "collision + k_assemble1");
   // the joint rows (one thread per joint: a long dependent chain on few threads) run beside the contact rows and
   // the schedule, which do not depend on them; k_rowfinish needs all three
   const bool fork_joint = d.nj > 0 && d.pgs_impl >= 1;
@@ -835,6 +850,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     b->last_launches++;
   } else if (d.nj > 0) { k_rows_joint<<<cdiv(d.nj, T), T, 0, b->stream>>>(d); b->last_launches++; }
   k_rows_contact<<<dim3(item_blocks(d.max_contact_cap, 32, W), W), 32, 0, b->stream>>>(d);
+  dbg_point(b, "k_rows_joint + k_rows_contact");
   if (d.pgs_impl >= 1) {
     // body-owner sweeps: schedule (integer work on the row counts), row prologue + entries, sweeps
     if (d.pgs_impl == 2) {
@@ -848,9 +864,11 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     } else
       k_bsched<<<W, 128, d.bs_glob ? 0 : b->bsched_smem, b->stream>>>(d);
     k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
+    dbg_point(b, "k_bsched + k_border");
     if (fork_joint) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
     if (d.p.dynamic_inertia && d.nj > 0) { k_dyn_inertia<<<cdiv(W, 64), 64, 0, b->stream>>>(d); b->last_launches++; }
     k_rowfinish<<<dim3(item_blocks(d.max_row_cap, 64, W), W), 64, 0, b->stream>>>(d);
+    dbg_point(b, "k_rowfinish");
     if (stage_events) cudaEventRecord(b->evs[2], b->stream);
     if (prof_slot >= 0) cudaEventRecord(b->pgs_ev[2 * prof_slot], b->stream);
     const bool box = d.p.friction_model == 2;
@@ -922,6 +940,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
         const int lower = q > 0 ? b->pgsbc[q - 1].nres : -1;
         if (box) k_pgsb<false, true><<<b->pgsbc_grid[q], 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
         else k_pgsb<false, false><<<b->pgsbc_grid[q], 32, b->pgsbc_smem[q], sq>>>(d, b->pgsbc[q], lower);
+        { char nm[96]; snprintf(nm, sizeof nm, "k_pgsb class %d (grid %d, smem %zu, nres %d, wpc %d, lw %d, lower %d)", q, b->pgsbc_grid[q], b->pgsbc_smem[q], b->pgsbc[q].nres, b->pgsbc[q].wpc, b->pgsbc[q].lw, lower); dbg_point(b, nm); }
         if (q > 0) cudaEventRecord(b->pgsb_join[q], sq);
       }
       for (int q = 1; q < b->pgsb_ncls; q++) cudaStreamWaitEvent(b->stream, b->pgsb_join[q], 0);
@@ -936,7 +955,9 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
       cudaEventRecord(b->ev_aux_join, b->stream_aux);
       b->last_launches++;
     }
+    dbg_point(b, "the sweeps");
     k_integrate<<<cdiv(std::max(d.nb, 1), 64), 64, 0, b->stream>>>(d);
+    dbg_point(b, "k_integrate");
     if (d.nj > 0) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);
     b->last_launches += 7;
     return 0;
@@ -1314,7 +1335,8 @@ int gzcuda_batch_get_body_flags(gzcuda_batch *b, int *flags) {
 int gzcuda_batch_set_joint_param(gzcuda_batch *b, int joint, int slot, double value) {
   if (!b || joint < 0 || joint >= b->d.nj || slot < 0 || slot >= GZ_JP_COUNT) return fail(GZCUDA_E_INVALID, "bad joint/slot");
   CK(cudaSetDevice(b->device));
-  CK(cudaMemcpyAsync(&b->d.joint[joint].param[slot], &value, sizeof(double), cudaMemcpyHostToDevice, b->stream));   // stream-ordered, 8 bytes
+  double *dst = slot < GZ_JP_HOT ? &b->d.joint[joint].param[slot] : b->d.joint_ext + (size_t)(GZ_JP_COUNT - GZ_JP_HOT) * joint + slot - GZ_JP_HOT;
+  CK(cudaMemcpyAsync(dst, &value, sizeof(double), cudaMemcpyHostToDevice, b->stream));   // stream-ordered, 8 bytes
   return 0;
 }
 

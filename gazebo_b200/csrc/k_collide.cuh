@@ -373,21 +373,20 @@ __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldI
   // on use_patch_radius; E* from the two moduli and Poisson's ratios, only when both moduli are > 0
   double em = 0.0, em_radius = 0.0;
   int em_surface = 0;
-  {
-    const double patch = fmax(g1.surf[GZ_SF_PATCH_RADIUS], g2.surf[GZ_SF_PATCH_RADIUS]);
+  if (g1.em_on && g2.em_on) {
+    const double *x1 = B.geom_ext + (size_t)gi1 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT, *x2 = B.geom_ext + (size_t)gi2 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT;
+    const double patch = fmax(x1[GZ_SF_PATCH_RADIUS], x2[GZ_SF_PATCH_RADIUS]);
     double curv1 = 0, curv2 = 0;
-    if (g1.surf[GZ_SF_SURFACE_RADIUS] > 0) curv1 = 1 / g1.surf[GZ_SF_SURFACE_RADIUS];
-    if (g2.surf[GZ_SF_SURFACE_RADIUS] > 0) curv2 = 1 / g2.surf[GZ_SF_SURFACE_RADIUS];
+    if (x1[GZ_SF_SURFACE_RADIUS] > 0) curv1 = 1 / x1[GZ_SF_SURFACE_RADIUS];
+    if (x2[GZ_SF_SURFACE_RADIUS] > 0) curv2 = 1 / x2[GZ_SF_SURFACE_RADIUS];
     const double curv_sum = curv1 + curv2;
     double surface_radius = 0;
     if (curv_sum > 0) surface_radius = 1 / curv_sum;
-    const bool use_patch = g1.surf[GZ_SF_USE_PATCH_RADIUS] != 0 && g2.surf[GZ_SF_USE_PATCH_RADIUS] != 0;
-    const double nu1 = g1.surf[GZ_SF_POISSON], nu2 = g2.surf[GZ_SF_POISSON];
-    const double e1 = g1.surf[GZ_SF_ELASTIC_MODULUS], e2 = g2.surf[GZ_SF_ELASTIC_MODULUS];
-    if (e1 > 0 && e2 > 0) {
-      const double es = 1.0 / ((1.0 - nu1 * nu1) / e1 + (1.0 - nu2 * nu2) / e2);
-      if (es > 0.0) { em = es; em_radius = use_patch ? patch : surface_radius; em_surface = use_patch ? 0 : 1; }
-    }
+    const bool use_patch = x1[GZ_SF_USE_PATCH_RADIUS] != 0 && x2[GZ_SF_USE_PATCH_RADIUS] != 0;
+    const double nu1 = x1[GZ_SF_POISSON], nu2 = x2[GZ_SF_POISSON];
+    const double e1 = x1[GZ_SF_ELASTIC_MODULUS], e2 = x2[GZ_SF_ELASTIC_MODULUS];
+    const double es = 1.0 / ((1.0 - nu1 * nu1) / e1 + (1.0 - nu2 * nu2) / e2);
+    if (es > 0.0) { em = es; em_radius = use_patch ? patch : surface_radius; em_surface = use_patch ? 0 : 1; }
   }
   // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
   int b1 = g1.body, b2 = g2.body, reverse = 0;

@@ -416,7 +416,7 @@ __device__ __forceinline__ void pgsb_item(const DevBatch &B, const PgsbCfg &cfg,
   // ---- stage the entries of the CTA's worlds in shared memory (world after world, 22-double stride)
   int soff = 0;   // first staged entry of this world
   if (!MULTI)
-    for (int s = 0; s < wslot; s++) soff += B.wsb[B.wperm[item * cfg.wpc + s]].w;
+    for (int s = 0; s < wslot && item * cfg.wpc + s < B.n_worlds; s++) soff += B.wsb[B.wperm[item * cfg.wpc + s]].w;   // (a partly filled last item)
   if (res) {
     const int n2 = nent * (GZ_ENT / 2);
     const double2 *src = reinterpret_cast<const double2 *>(B.ent + (size_t)sc.z * GZ_ENT);

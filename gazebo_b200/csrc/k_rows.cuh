@@ -20,12 +20,17 @@ namespace gz {
 // getHingeAngle (joint.cpp:442-465) + getHingeAngleFromRelativeQuat (:391-432)
 #define GZ_PI 3.14159265358979323846   // M_PI
 
+// the joint_param slots beyond GZ_JP_HOT (hinge2 / universal joints only): a side array, so that struct Joint stays small
+__device__ __forceinline__ const double *joint_ext(const DevBatch &B, const Joint &j) {
+  return B.joint_ext + (size_t)(&j - B.joint) * (GZ_JP_COUNT - GZ_JP_HOT) - GZ_JP_HOT;   // indexed by the slot number itself
+}
+
 // dxJointHinge2::measureAngle1 (hinge2.cpp:34-52): axis 2 seen from body 1, against v1 / v2
 __device__ inline double hinge2_angle1(const DevBatch &B, const Joint &j) {
   double p[3], q[3];
   mul0_331(p, B.body[j.b2].R, j.axis2);
   mul1_331(q, B.body[j.b1].R, p);
-  const double x = dot3(&j.param[GZ_JP_V1], q), y = dot3(&j.param[GZ_JP_V2], q);
+  const double x = dot3(&joint_ext(B, j)[GZ_JP_V1], q), y = dot3(&joint_ext(B, j)[GZ_JP_V2], q);
   return -gzdet_atan2(y, x);
 }
 
@@ -114,8 +119,8 @@ __device__ inline void universal_angles(const DevBatch &B, const Joint &j, doubl
   const double l = 1.0 / sqrt(qrel[1] * qrel[1] + qrel[2] * qrel[2] + qrel[3] * qrel[3]);
   qrel[1] *= l; qrel[2] *= l; qrel[3] *= l;
   qmul0(qcross2, qrel, qcross);
-  if (j.b2 >= 0) { qmul1(qq, B.body[j.b2].q, qcross2); qmul2(qrel, qq, &j.param[GZ_JP_QREL2]); }
-  else qmul2(qrel, qcross2, &j.param[GZ_JP_QREL2]);
+  if (j.b2 >= 0) { qmul1(qq, B.body[j.b2].q, qcross2); qmul2(qrel, qq, &joint_ext(B, j)[GZ_JP_QREL2]); }
+  else qmul2(qrel, qcross2, &joint_ext(B, j)[GZ_JP_QREL2]);
   angle2 = -angle_from_relative_quat(qrel, j.axis2);
 }
 
@@ -358,12 +363,12 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
             else if (angle >= hi) { j.limit = 2; j.limit_err = angle - hi; }
           }
           if (j.limit || j.param[GZ_JP_FMAX] > 0) m++;
-          if (j.param[GZ_JP_FMAX2] > 0) m++;
+          if (joint_ext(B, j)[GZ_JP_FMAX2] > 0) m++;
         } else if (j.type == GZ_JOINT_UNIVERSAL) {
           // dxJointUniversal::getInfo1 (universal.cpp:268-307)
           m = 4;
           const double lo1 = j.param[GZ_JP_LOSTOP], hi1 = j.param[GZ_JP_HISTOP];
-          const double lo2 = j.param[GZ_JP_LOSTOP2], hi2 = j.param[GZ_JP_HISTOP2];
+          const double lo2 = joint_ext(B, j)[GZ_JP_LOSTOP2], hi2 = joint_ext(B, j)[GZ_JP_HISTOP2];
           const bool limiting1 = lo1 <= hi1, limiting2 = lo2 <= hi2;
           j.limit = 0; j.limit2 = 0;
           if (limiting1 || limiting2) {
@@ -381,7 +386,7 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
             }
           }
           if (j.limit || j.param[GZ_JP_FMAX] > 0) m++;
-          if (j.limit2 || j.param[GZ_JP_FMAX2] > 0) m++;
+          if (j.limit2 || joint_ext(B, j)[GZ_JP_FMAX2] > 0) m++;
         } else if (j.type == GZ_JOINT_SLIDER) {
           // dxJointSlider::getInfo1 (slider.cpp:118-148)
           m = (j.param[GZ_JP_FMAX] > 0) ? 6 : 5;

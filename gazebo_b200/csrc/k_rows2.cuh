@@ -196,11 +196,11 @@ __global__ void k_rows_joint(DevBatch B) {
       // the limit / motor of axis 1, then of axis 2 (universal.cpp:384-388)
       int row = 4;
       if (j.limit || j.param[GZ_JP_FMAX] > 0) row += add_limot(B, j, rows[row], ax1, fps, true);
-      if (j.limit2 || j.param[GZ_JP_FMAX2] > 0) {
+      if (j.limit2 || joint_ext(B, j)[GZ_JP_FMAX2] > 0) {
         Limot M2;
-        M2.lostop = j.param[GZ_JP_LOSTOP2]; M2.histop = j.param[GZ_JP_HISTOP2]; M2.vel = j.param[GZ_JP_VEL2]; M2.fmax = j.param[GZ_JP_FMAX2];
-        M2.fudge = j.param[GZ_JP_FUDGE2]; M2.bounce = j.param[GZ_JP_BOUNCE2]; M2.normal_cfm = j.param[GZ_JP_NORMAL_CFM2];
-        M2.stop_erp = j.param[GZ_JP_STOP_ERP2]; M2.stop_cfm = j.param[GZ_JP_STOP_CFM2]; M2.limit_err = j.limit_err2; M2.limit = j.limit2;
+        M2.lostop = joint_ext(B, j)[GZ_JP_LOSTOP2]; M2.histop = joint_ext(B, j)[GZ_JP_HISTOP2]; M2.vel = joint_ext(B, j)[GZ_JP_VEL2]; M2.fmax = joint_ext(B, j)[GZ_JP_FMAX2];
+        M2.fudge = joint_ext(B, j)[GZ_JP_FUDGE2]; M2.bounce = joint_ext(B, j)[GZ_JP_BOUNCE2]; M2.normal_cfm = joint_ext(B, j)[GZ_JP_NORMAL_CFM2];
+        M2.stop_erp = joint_ext(B, j)[GZ_JP_STOP_ERP2]; M2.stop_cfm = joint_ext(B, j)[GZ_JP_STOP_CFM2]; M2.limit_err = j.limit_err2; M2.limit = j.limit2;
         add_limot(B, j, rows[row], ax2, fps, true, M2);
       }
     }
@@ -214,18 +214,18 @@ __global__ void k_rows_joint(DevBatch B) {
     cross3(q, ax1, ax2);
     const double sn = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]), cs = dot3(ax1, ax2);
     safe_normalize3(q);
-    set_ball2(rows, b1, *b2, j, ax1, fps * j.param[GZ_JP_SUSP_ERP], fps * erp);
+    set_ball2(rows, b1, *b2, j, ax1, fps * joint_ext(B, j)[GZ_JP_SUSP_ERP], fps * erp);
     for (int i = 0; i < 3; i++) { rows[3].J[3 + i] = q[i]; rows[3].J[9 + i] = -q[i]; }
-    rows[3].c = fps * erp * (j.param[GZ_JP_C0] * sn - j.param[GZ_JP_S0] * cs);
+    rows[3].c = fps * erp * (joint_ext(B, j)[GZ_JP_C0] * sn - joint_ext(B, j)[GZ_JP_S0] * cs);
     int row = 4;
     if (j.limit || j.param[GZ_JP_FMAX] > 0) row += add_limot(B, j, rows[row], ax1, fps, true);
-    if (j.param[GZ_JP_FMAX2] > 0) {
+    if (joint_ext(B, j)[GZ_JP_FMAX2] > 0) {
       Limot M2;   // dxJointLimitMotor::init (joint.cpp:470-484) with dParamVel2 / dParamFMax2 set
-      M2.lostop = -GZ_INF; M2.histop = GZ_INF; M2.vel = j.param[GZ_JP_VEL2]; M2.fmax = j.param[GZ_JP_FMAX2];
+      M2.lostop = -GZ_INF; M2.histop = GZ_INF; M2.vel = joint_ext(B, j)[GZ_JP_VEL2]; M2.fmax = joint_ext(B, j)[GZ_JP_FMAX2];
       M2.fudge = 1; M2.bounce = 0; M2.normal_cfm = B.p.cfm; M2.stop_erp = B.p.erp; M2.stop_cfm = B.p.cfm; M2.limit_err = 0; M2.limit = 0;
       add_limot(B, j, rows[row], ax2, fps, true, M2);
     }
-    rows[0].cfm = j.param[GZ_JP_SUSP_CFM];
+    rows[0].cfm = joint_ext(B, j)[GZ_JP_SUSP_CFM];
   } else if (j.type == GZ_JOINT_SLIDER) {
     // dxJointSlider::getInfo2 (slider.cpp:151-238); anchor1 holds dxJointSlider::offset
     if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 5; r++) rows[r].cfm = j.param[GZ_JP_CFM];

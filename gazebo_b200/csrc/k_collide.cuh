@@ -340,6 +340,24 @@ __global__ void k_narrow(DevBatch B) {
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) narrow_pair<CYL>(B, w, wi, k);
 }
 
+// Hertzian contact (ODEPhysics.cc:1186-1251): patch radius = the larger one, curvatures add, both surfaces must agree on
+// use_patch_radius; E* from the two moduli and Poisson's ratios.  
+__device__ inline void em_combine(const DevBatch &B, const int gi1, const int gi2, double &em, double &em_radius, int &em_surface) {
+  const double *x1 = B.geom_ext + (size_t)gi1 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT, *x2 = B.geom_ext + (size_t)gi2 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT;
+  const double patch = fmax(x1[GZ_SF_PATCH_RADIUS], x2[GZ_SF_PATCH_RADIUS]);
+  double curv1 = 0, curv2 = 0;
+  if (x1[GZ_SF_SURFACE_RADIUS] > 0) curv1 = 1 / x1[GZ_SF_SURFACE_RADIUS];
+  if (x2[GZ_SF_SURFACE_RADIUS] > 0) curv2 = 1 / x2[GZ_SF_SURFACE_RADIUS];
+  const double curv_sum = curv1 + curv2;
+  double surface_radius = 0;
+  if (curv_sum > 0) surface_radius = 1 / curv_sum;
+  const bool use_patch = x1[GZ_SF_USE_PATCH_RADIUS] != 0 && x2[GZ_SF_USE_PATCH_RADIUS] != 0;
+  const double nu1 = x1[GZ_SF_POISSON], nu2 = x2[GZ_SF_POISSON];
+  const double e1 = x1[GZ_SF_ELASTIC_MODULUS], e2 = x2[GZ_SF_ELASTIC_MODULUS];
+  const double es = 1.0 / ((1.0 - nu1 * nu1) / e1 + (1.0 - nu2 * nu2) / e2);
+  if (es > 0.0) { em = es; em_radius = use_patch ? patch : surface_radius; em_surface = use_patch ? 0 : 1; }
+}
+
 // The contacts of candidate pair k of a world (c of them, from k_narrow) at place `off` of the world's contact list,
 // with the combined surface parameters.
 __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldInfo &wi, const int k, const int c, const int off) {
@@ -373,21 +391,7 @@ __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldI
   // on use_patch_radius; E* from the two moduli and Poisson's ratios, only when both moduli are > 0
   double em = 0.0, em_radius = 0.0;
   int em_surface = 0;
-  if (g1.em_on && g2.em_on) {
-    const double *x1 = B.geom_ext + (size_t)gi1 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT, *x2 = B.geom_ext + (size_t)gi2 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT;
-    const double patch = fmax(x1[GZ_SF_PATCH_RADIUS], x2[GZ_SF_PATCH_RADIUS]);
-    double curv1 = 0, curv2 = 0;
-    if (x1[GZ_SF_SURFACE_RADIUS] > 0) curv1 = 1 / x1[GZ_SF_SURFACE_RADIUS];
-    if (x2[GZ_SF_SURFACE_RADIUS] > 0) curv2 = 1 / x2[GZ_SF_SURFACE_RADIUS];
-    const double curv_sum = curv1 + curv2;
-    double surface_radius = 0;
-    if (curv_sum > 0) surface_radius = 1 / curv_sum;
-    const bool use_patch = x1[GZ_SF_USE_PATCH_RADIUS] != 0 && x2[GZ_SF_USE_PATCH_RADIUS] != 0;
-    const double nu1 = x1[GZ_SF_POISSON], nu2 = x2[GZ_SF_POISSON];
-    const double e1 = x1[GZ_SF_ELASTIC_MODULUS], e2 = x2[GZ_SF_ELASTIC_MODULUS];
-    const double es = 1.0 / ((1.0 - nu1 * nu1) / e1 + (1.0 - nu2 * nu2) / e2);
-    if (es > 0.0) { em = es; em_radius = use_patch ? patch : surface_radius; em_surface = use_patch ? 0 : 1; }
-  }
+  if (g1.em_on && g2.em_on) em_combine(B, gi1, gi2, em, em_radius, em_surface);
   // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
   int b1 = g1.body, b2 = g2.body, reverse = 0;
   if (b1 < 0) { b1 = b2; b2 = -1; reverse = 1; }
@@ -409,7 +413,7 @@ __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldI
 
 // One CTA per world: exclusive scan of per-pair contact counts, then one thread per pair
 // writes its contacts at the scanned offset.
-__global__ void k_contacts(DevBatch B) {
+__global__ void __launch_bounds__(1024) k_contacts(DevBatch B) {
   const int w = blockIdx.x;
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];

@@ -434,7 +434,8 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
 
 // One CTA per world: auto-disable + islands, the body prologue of its bodies, row counts and offsets - three
 // phases that were three launches (k_island, k_bodyprep, k_info1), separated by block barriers.
-__global__ void k_assemble1(DevBatch B) {
+// (launch bounds: at most 64 registers - the rare joint types' angle code must not cost the common path its occupancy)
+__global__ void __launch_bounds__(1024) k_assemble1(DevBatch B) {
   island_world(B, blockIdx.x);
   __syncthreads();
   const WorldInfo wi = B.world[blockIdx.x];

@@ -76,6 +76,8 @@ struct gzcuda_batch {
   int pgsm_cluster = 1, pgsm_threads = 128;
   size_t pgsm_smem = 0;
   int *pgsm_done = nullptr;
+  int bsched_t = 128, bp_t_small = 128;   // (developer switches GZCUDA_BSCHED_T, GZCUDA_BP_T)
+  int small_t = 128;                  // threads of the one-CTA-per-world kernels (k_contacts, k_assemble1)
   bool large_kernels = false;         // k_contacts_large / k_assemble1_large (cooperative grid) instead of the one-CTA-per-world kernels
   int large_grid = 0;
   int *large_part = nullptr;
@@ -406,6 +408,12 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   // through L2 slots, one launch per world).  Batches of 8+ worlds of 257..512 bodies keep round 1's row-slot kernels
   // (all worlds in one launch); GZCUDA_PGS_IMPL=0 forces them for any batch of worlds up to 512 bodies.
   d.pgs_impl = (max_nb <= 256) ? 1 : ((max_nb <= 512 && W >= 8) ? 0 : 2);
+  // one-CTA-per-world kernels: a world of a few bodies keeps a few lanes busy, and the smaller the CTA the more worlds
+  // are resident at once (measured at C2: 32 threads 1.305 ms/step, 128 threads 1.327)
+  b->small_t = max_nb <= 16 ? 32 : (max_nb <= 48 ? 64 : 128);
+  if (const char *e = getenv("GZCUDA_SMALL_T")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128 || v == 256) b->small_t = v; }
+  if (const char *e = getenv("GZCUDA_BSCHED_T")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128) b->bsched_t = v; }
+  if (const char *e = getenv("GZCUDA_BP_T")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128) b->bp_t_small = v; }
   d.islands_hook = max_nb > 512;
   if (const char *e = getenv("GZCUDA_ISLANDS_HOOK")) d.islands_hook = atoi(e) != 0;   // developer / test switch
   if (const char *e = getenv("GZCUDA_PGS_IMPL")) {
@@ -629,7 +637,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     d.bp_sap_min = 64;
     if (const char *e = getenv("GZCUDA_BP_SAP_MIN")) d.bp_sap_min = std::max(2, atoi(e));
     b->bp_smem = (size_t)(max_ng + 1) * sizeof(int);
-    b->bp_threads = 128;
+    b->bp_threads = b->bp_t_small;
     if (max_ng >= d.bp_sap_min) {
       size_t npad = 32;
       while (npad < (size_t)max_ng) npad <<= 1;
@@ -813,7 +821,7 @@ static int launch_collision(gzcuda_batch *b) {
     }
     b->last_launches += W - 1;
   } else
-    k_contacts<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // (one CTA per world: a large world gets the largest CTA)
+    k_contacts<<<W, d.max_nb > 512 ? 1024 : b->small_t, 0, b->stream>>>(d);   // (one CTA per world: a large world gets the largest CTA)
   b->last_launches += 4;
   return 0;
 }
@@ -837,7 +845,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
     }
     b->last_launches += W - 1;
   } else
-    k_assemble1<<<W, d.max_nb > 512 ? 1024 : T, 0, b->stream>>>(d);   // islands, body prologue, row counts
+    k_assemble1<<<W, d.max_nb > 512 ? 1024 : b->small_t, 0, b->stream>>>(d);   // islands, body prologue, row counts
   dbg_point(b, "collision + k_assemble1");
   // the joint rows (one thread per joint: a long dependent chain on few threads) run beside the contact rows and
   // the schedule, which do not depend on them; k_rowfinish needs all three
@@ -862,7 +870,7 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
       }
       b->last_launches += W - 1;
     } else
-      k_bsched<<<W, 128, d.bs_glob ? 0 : b->bsched_smem, b->stream>>>(d);
+      k_bsched<<<W, b->bsched_t, d.bs_glob ? 0 : b->bsched_smem, b->stream>>>(d);
     k_border<<<cdiv(W, 256), 256, 0, b->stream>>>(d);
     dbg_point(b, "k_bsched + k_border");
     if (fork_joint) cudaStreamWaitEvent(b->stream, b->ev_aux_join, 0);

@@ -153,6 +153,9 @@ GZ_HD double norm_angle(double a) {
   if (r > 3.14159265358979323846) r -= 2.0 * 3.14159265358979323846;
   return r;
 }
+GZ_HD double shortest_angular_distance(double from, double to) {
+  return norm_angle(norm_angle_pos(norm_angle_pos(to) - norm_angle_pos(from)));
+}
 GZ_HD double shortest_angular_distance_update(double from, double to) {
   double result = norm_angle(norm_angle_pos(norm_angle_pos(to) - norm_angle_pos(from)));
   if (fabs(result) > 0.3) return to;

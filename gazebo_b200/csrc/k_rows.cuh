@@ -56,6 +56,14 @@ __device__ inline double hinge_angle(const DevBatch &B, const Joint &j) {
   return angle_from_relative_quat(qrel, j.axis1);
 }
 
+// getHingeAngle (joint.cpp:442-465) of a body against a reference body (global index, < 0: the world) - the gearbox joint
+__device__ inline double body_angle(const DevBatch &B, const int body, const int ref, const double *axis, const double *q0) {
+  double qrel[4];
+  if (ref >= 0) { double qq[4]; qmul1(qq, B.body[body].q, B.body[ref].q); qmul2(qrel, qq, q0); }
+  else qmul3(qrel, B.body[body].q, q0);
+  return angle_from_relative_quat(qrel, axis);
+}
+
 // dRFrom2Axes (rotation.cpp:95-136) + dRtoQ / dQfromR (:261-311): the frame whose x axis is a and whose y axis is b made
 // perpendicular to a, as a quaternion
 __device__ inline void quat_from_2_axes(double *q, const double *a_in, const double *b_in) {
@@ -352,6 +360,8 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
           m = 6;
         } else if (j.type == GZ_JOINT_BALL) {
           m = 3;
+        } else if (j.type == GZ_JOINT_GEARBOX) {
+          m = 1;   // dxJointGearbox::getInfo1 (gearbox.cpp:54-59)
         } else if (j.type == GZ_JOINT_HINGE2) {
           // dxJointHinge2::getInfo1 (hinge2.cpp:108-127)
           m = 4;

@@ -204,6 +204,22 @@ __global__ void k_rows_joint(DevBatch B) {
         add_limot(B, j, rows[row], ax2, fps, true, M2);
       }
     }
+  } else if (j.type == GZ_JOINT_GEARBOX) {
+    // dxJointGearbox::getInfo2 (gearbox.cpp:62-103): the two angles (cumulative, each against its reference body), one
+    // row on the angular velocities about the two axes; the world's erp (the joint's is not consulted)
+    const double *X = joint_ext(B, j);
+    const double ratio = X[GZ_JP_RATIO];
+    const int r1 = (int)X[GZ_JP_REFBODY1], r2 = (int)X[GZ_JP_REFBODY2];
+    double g1[3], g2[3];
+    mul0_331(g1, b1.R, j.axis1);
+    mul0_331(g2, b2->R, j.axis2);
+    const double ang1 = body_angle(B, j.b1, r1 >= 0 ? wi.body0 + r1 : -1, j.axis1, j.qrel);
+    const double ang2 = body_angle(B, j.b2, r2 >= 0 ? wi.body0 + r2 : -1, j.axis2, &X[GZ_JP_QREL2]);
+    j.cum_angle = shortest_angular_distance_update(j.cum_angle, ang1);
+    j.cum_angle2 = shortest_angular_distance_update(j.cum_angle2, ang2);
+    const double err = shortest_angular_distance(-ratio * j.cum_angle2, j.cum_angle);
+    for (int i = 0; i < 3; i++) { rows[0].J[3 + i] = g1[i]; rows[0].J[9 + i] = ratio * g2[i]; }
+    rows[0].c = -(fps * B.p.erp) * err;
   } else if (j.type == GZ_JOINT_HINGE2) {
     // dxJointHinge2::getInfo2 (hinge2.cpp:158-222): ball rows aligned with axis 1 (row 0 = the suspension), one row that
     // keeps the angle between the axes, then the limit / motor of axis 1 and the motor of axis 2

@@ -15,12 +15,13 @@ import sys
 import numpy as np
 
 GEOM_SPHERE, GEOM_BOX, GEOM_CAPSULE, GEOM_CYLINDER, GEOM_PLANE = range(5)
-JOINT_HINGE, JOINT_FIXED, JOINT_BALL, JOINT_SLIDER, JOINT_UNIVERSAL, JOINT_HINGE2 = 1, 2, 3, 4, 5, 6
+JOINT_HINGE, JOINT_FIXED, JOINT_BALL, JOINT_SLIDER, JOINT_UNIVERSAL, JOINT_HINGE2, JOINT_GEARBOX = 1, 2, 3, 4, 5, 6, 7
 BODY_NO_GRAVITY, BODY_AUTO_DISABLE, BODY_DISABLED, BODY_NO_GYRO = 1, 2, 4, 8
 JP_LOSTOP, JP_HISTOP, JP_VEL, JP_FMAX, JP_FUDGE, JP_BOUNCE, JP_NORMAL_CFM, \
     JP_STOP_ERP, JP_STOP_CFM, JP_ERP, JP_CFM = range(11)
 JP_VEL2, JP_FMAX2, JP_SUSP_ERP, JP_SUSP_CFM, JP_V1, JP_V2, JP_C0, JP_S0 = 12, 13, 14, 15, 16, 19, 22, 23
 JP_LOSTOP2, JP_HISTOP2, JP_FUDGE2, JP_BOUNCE2, JP_NORMAL_CFM2, JP_STOP_ERP2, JP_STOP_CFM2, JP_QREL2 = 24, 25, 26, 27, 28, 29, 30, 31
+JP_RATIO, JP_REFBODY1, JP_REFBODY2 = 35, 14, 15
 JP_COUNT = 36
 SF_MU, SF_MU2, SF_KP, SF_KD, SF_SLIP1, SF_SLIP2, SF_BOUNCE, SF_BOUNCE_VEL = range(8)
 SF_PATCH_RADIUS, SF_ELASTIC_MODULUS, SF_POISSON, SF_SURFACE_RADIUS, SF_USE_PATCH_RADIUS, SF_MU3 = 8, 9, 10, 11, 12, 13
@@ -369,6 +370,24 @@ class SceneBuilder:
         P[JP_NORMAL_CFM2], P[JP_STOP_ERP2], P[JP_STOP_CFM2] = normal_cfm2, stop_erp2, stop_cfm2
         P[JP_QREL2:JP_QREL2 + 4] = list(qrel2)
         self._push_joint(JOINT_UNIVERSAL, b1, b2, a1, a2, ax1, ax2, tuple(qrel1), P)
+        return self._nj - 1 - self._w_j0
+
+    def add_gearbox(self, b1, b2, axis1, axis2, ratio, ref1=-1, ref2=-1):
+        """dxJointGearbox (SDF gearbox): angle of b1 about axis1 (against reference body ref1) + ratio x angle of b2 about
+        axis2 (against ref2) is held at its initial value.  Axes in world coordinates at the current poses; ref = a body
+        of the world or -1 (the world).  qrel1 / qrel2 as dJointSetGearboxReferenceBody1 / 2 compute them."""
+        assert b2 >= 0, "a gearbox joint needs two bodies"
+        p1, q1 = self._body_pose(b1)
+        p2, q2 = self._body_pose(b2)
+        ax1 = q_to_R(q1).T @ (np.asarray(axis1, float) / np.linalg.norm(axis1))
+        ax2 = q_to_R(q2).T @ (np.asarray(axis2, float) / np.linalg.norm(axis2))
+        qrel1 = q_mul(q_conj(q1), self._body_pose(ref1)[1]) if ref1 >= 0 else q_conj(q1)
+        qrel2 = q_mul(q_conj(q2), self._body_pose(ref2)[1]) if ref2 >= 0 else q_conj(q2)
+        P = self.joint_params()
+        P[JP_RATIO], P[JP_REFBODY1], P[JP_REFBODY2] = float(ratio), float(ref1), float(ref2)
+        P[JP_QREL2:JP_QREL2 + 4] = list(qrel2)
+        z = np.zeros(3)
+        self._push_joint(JOINT_GEARBOX, b1, b2, z, z, ax1, ax2, tuple(qrel1), P)
         return self._nj - 1 - self._w_j0
 
     def add_slider(self, b1, b2, axis, **params):

@@ -35,8 +35,10 @@ enum { GZ_GEOM_SPHERE = 0, GZ_GEOM_BOX = 1, GZ_GEOM_CAPSULE = 2,
  * by the collide stage every step and never appear in the scene). */
 enum { GZ_JOINT_HINGE = 1, GZ_JOINT_FIXED = 2, GZ_JOINT_BALL = 3,
        GZ_JOINT_SLIDER = 4, GZ_JOINT_UNIVERSAL = 5,
-       GZ_JOINT_HINGE2 = 6 };  /* dxJointHinge2 (SDF revolute2): two bodies required; joint_anchor1/2, joint_axis1/2 in the
-                                * bodies' frames, the derived members v1, v2, c0, s0 in joint_param (below) */
+       GZ_JOINT_HINGE2 = 6,
+       GZ_JOINT_GEARBOX = 7 };  /* dxJointHinge2 (SDF revolute2): two bodies required; joint_anchor1/2, joint_axis1/2 in the
+                                * bodies' frames, the derived members v1, v2, c0, s0 in joint_param (below);
+                                * GZ_JOINT_GEARBOX = dxJointGearbox: two bodies required as well */
 
 /* body_flags bits */
 enum { GZ_BODY_NO_GRAVITY   = 1,   /* dxBodyNoGravity (ODELink::SetGravityMode(false)) */
@@ -63,6 +65,10 @@ enum { GZ_JP_LOSTOP = 0, GZ_JP_HISTOP = 1, GZ_JP_VEL = 2, GZ_JP_FMAX = 3,
        GZ_JP_LOSTOP2 = 24, GZ_JP_HISTOP2 = 25, GZ_JP_FUDGE2 = 26, GZ_JP_BOUNCE2 = 27, GZ_JP_NORMAL_CFM2 = 28,
        GZ_JP_STOP_ERP2 = 29, GZ_JP_STOP_CFM2 = 30,
        GZ_JP_QREL2 = 31,   /* qrel2[4]: 31..34 */
+       /* gearbox joints (joints/gearbox.cpp: one row that couples the angles of two bodies about their axes, each measured
+        * against a reference body): joint_axis1 / joint_axis2 in the bodies' frames, joint_qrel = qrel1, GZ_JP_QREL2 = qrel2,
+        * the gear ratio, and the reference bodies as world-local body indices (-1: the world) */
+       GZ_JP_RATIO = 35, GZ_JP_REFBODY1 = 14, GZ_JP_REFBODY2 = 15,   /* (the reference bodies overlay the hinge2-only suspension slots) */
        GZ_JP_COUNT = 36 };
 
 /* geom_surf[] slots (ODESurfaceParams + FrictionPyramid) */

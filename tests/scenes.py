@@ -353,6 +353,42 @@ def carts(n_worlds=3, seed=31):
     return sb.finish(), S.default_params(), None
 
 
+def gears(n_worlds=2, seed=67):
+    """Gearbox joints (dxJointGearbox, SDF gearbox): world 0 - two wheels hinged to the world on parallel axes, coupled 2 : 1,
+    one driven by its hinge motor; world 1 - the same pair on a free carrier body (the gearbox's reference body) that
+    falls onto the plane and tumbles, ratio -1.5, axes not parallel."""
+    sb = S.SceneBuilder()
+    for w in range(n_worlds):
+        rng = np.random.Generator(np.random.PCG64(seed + w))
+        sb.begin_world()
+        sb.add_ground_plane()
+        sp = sb.new_space()
+        if w % 2 == 0:
+            a = sb.add_body([0.0, 0.0, 1.0], S.q_from_rpy(1.5707963267948966, 0, 0), mass=1.0, inertia=S.cylinder_inertia(1.0, 0.2, 0.1))
+            sb.add_geom(S.GEOM_CYLINDER, (0.2, 0.1), sp, body=a)
+            b = sb.add_body([0.5, 0.0, 1.0], S.q_from_rpy(1.5707963267948966, 0, 0), mass=0.5, inertia=S.cylinder_inertia(0.5, 0.1, 0.1),
+                            avel=(0, 0.3, 0))
+            sb.add_geom(S.GEOM_CYLINDER, (0.1, 0.1), sp, body=b)
+            sb.add_hinge(a, -1, [0.0, 0.0, 1.0], [0, 1, 0], vel=2.0, fmax=0.4)
+            sb.add_hinge(b, -1, [0.5, 0.0, 1.0], [0, 1, 0])
+            sb.add_gearbox(a, b, [0, 1, 0], [0, 1, 0], 2.0)
+        else:
+            c = sb.add_body([0.0, 0.0, 0.8], S.q_from_rpy(0.2, -0.1, 0.3), mass=2.0, inertia=S.box_inertia(2.0, 0.8, 0.2, 0.1),
+                            avel=tuple(rng.uniform(-1, 1, 3)))
+            sb.add_geom(S.GEOM_BOX, (0.8, 0.2, 0.1), sp, body=c)
+            R = S.q_to_R(S.q_from_rpy(0.2, -0.1, 0.3))
+            pa, pb = np.array([0, 0, 0.8]) + R @ np.array([-0.25, 0, 0.15]), np.array([0, 0, 0.8]) + R @ np.array([0.25, 0, 0.15])
+            a = sb.add_body(pa, S.q_from_rpy(0.2, -0.1, 0.3), mass=0.6, inertia=S.sphere_inertia(0.6, 0.12), avel=(0, 0, 4.0))
+            sb.add_geom(S.GEOM_SPHERE, (0.12,), sp, body=a)
+            b = sb.add_body(pb, S.q_from_rpy(0.2, -0.1, 0.3), mass=0.4, inertia=S.sphere_inertia(0.4, 0.1))
+            sb.add_geom(S.GEOM_SPHERE, (0.1,), sp, body=b)
+            sb.add_hinge(c, a, pa, R @ np.array([0, 0, 1.0]))
+            sb.add_hinge(c, b, pb, R @ np.array([0, 0.6, 0.8]))
+            sb.add_gearbox(a, b, R @ np.array([0, 0, 1.0]), R @ np.array([0, 0.6, 0.8]), -1.5, ref1=c, ref2=c)
+        sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 def gimbals(n_worlds=2, seed=61):
     """Universal joints with stops and motors on both axes (dxJointUniversal limot1 / limot2, universal.cpp:268-389):
     an arm on the world swinging into the stops of both axes (bounce on one), a two-link arm whose second joint has a
@@ -473,4 +509,5 @@ GOLDEN = {
     "carts": (carts, 600),
     "hertz": (hertz, 700),
     "gimbals": (gimbals, 800),
+    "gears": (gears, 700),
 }

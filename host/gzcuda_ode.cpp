@@ -124,7 +124,7 @@ void limot_params(const dxJointLimitMotor &l, double *P) {
 }
 
 // the joint's parameter slots as the host holds them now; returns the GZ_JOINT_* type or 0 if unsupported
-int joint_params(dxJoint *j, double *P) {
+int joint_params(const Mirror *m, dxJoint *j, double *P) {
   for (int k = 0; k < GZ_JP_COUNT; k++) P[k] = 0;
   P[GZ_JP_LOSTOP] = -dInfinity; P[GZ_JP_HISTOP] = dInfinity; P[GZ_JP_FUDGE] = 1;
   P[GZ_JP_ERP] = j->erp; P[GZ_JP_CFM] = j->cfm;
@@ -142,6 +142,17 @@ int joint_params(dxJoint *j, double *P) {
       P[GZ_JP_STOP_ERP2] = l2.stop_erp; P[GZ_JP_STOP_CFM2] = l2.stop_cfm;
       for (int k = 0; k < 4; k++) P[GZ_JP_QREL2 + k] = uj->qrel2[k];
       return GZ_JOINT_UNIVERSAL;
+    }
+    case dJointTypeGearbox: {
+      const dxJointGearbox *gj = static_cast<dxJointGearbox *>(j);
+      P[GZ_JP_RATIO] = gj->ratio;
+      for (int k = 0; k < 4; k++) P[GZ_JP_QREL2 + k] = gj->qrel2[k];
+      P[GZ_JP_REFBODY1] = P[GZ_JP_REFBODY2] = -1;
+      for (size_t i = 0; i < m->bodies.size(); i++) {   // the reference bodies as indices of the mirror
+        if (m->bodies[i] == gj->refBody1) P[GZ_JP_REFBODY1] = (double)i;
+        if (m->bodies[i] == gj->refBody2) P[GZ_JP_REFBODY2] = (double)i;
+      }
+      return GZ_JOINT_GEARBOX;
     }
     case dJointTypeHinge2: {
       const dxJointHinge2 *h2 = static_cast<dxJointHinge2 *>(j);
@@ -268,8 +279,8 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
   m->jparam.assign((size_t)GZ_JP_COUNT * nj, 0.0);
   for (int i = 0; i < nj; i++) {
     dxJoint *j = m->joints[i];
-    jtype[i] = joint_params(j, &m->jparam[(size_t)GZ_JP_COUNT * i]);
-    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball, universal, hinge2");
+    jtype[i] = joint_params(m, j, &m->jparam[(size_t)GZ_JP_COUNT * i]);
+    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball, universal, hinge2, gearbox");
     if (!j->node[0].body) return fail(GZCUDA_E_INVALID, "a joint without bodies");
     auto i1 = bidx.find(j->node[0].body);
     if (i1 == bidx.end()) return fail(GZCUDA_E_INVALID, "a joint is attached to a body of another world");
@@ -289,6 +300,10 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
       const dxJointFixed *fj = static_cast<dxJointFixed *>(j);
       for (int k = 0; k < 3; k++) ja1[3 * i + k] = fj->offset[k];
       for (int k = 0; k < 4; k++) jq[4 * i + k] = fj->qrel[k];
+    } else if (jtype[i] == GZ_JOINT_GEARBOX) {
+      const dxJointGearbox *gj = static_cast<dxJointGearbox *>(j);
+      for (int k = 0; k < 3; k++) { jx1[3 * i + k] = gj->axis1[k]; jx2[3 * i + k] = gj->axis2[k]; }
+      for (int k = 0; k < 4; k++) jq[4 * i + k] = gj->qrel1[k];
     } else if (jtype[i] == GZ_JOINT_UNIVERSAL) {
       const dxJointUniversal *uj = static_cast<dxJointUniversal *>(j);
       for (int k = 0; k < 3; k++) { ja1[3 * i + k] = uj->anchor1[k]; ja2[3 * i + k] = uj->anchor2[k]; jx1[3 * i + k] = uj->axis1[k]; jx2[3 * i + k] = uj->axis2[k]; }
@@ -391,7 +406,7 @@ int upload(Mirror *m, bool with_wrench) {
     return fail_lib("gzcuda_batch_add_body_wrench");
   for (int i = 0; i < nj; i++) {   // dJointSetHingeParam / dJointSetSliderParam, joint erp / cfm
     double P[GZ_JP_COUNT];
-    joint_params(m->joints[i], P);
+    joint_params(m, m->joints[i], P);
     double *old = &m->jparam[(size_t)GZ_JP_COUNT * i];
     for (int k = 0; k < GZ_JP_COUNT; k++)
       if (P[k] != old[k] && !(P[k] != P[k] && old[k] != old[k])) {
@@ -439,6 +454,7 @@ int download(Mirror *m) {
       for (int k = 0; k < 6; k++) { j->lambda[k] = lam[6 * (size_t)i + k]; j->lambda_erp[k] = lam_erp[6 * (size_t)i + k]; }
       if (j->type() == dJointTypeHinge) static_cast<dxJointHinge *>(j)->cumulative_angle = cum[i];
       if (j->type() == dJointTypeUniversal) static_cast<dxJointUniversal *>(j)->cumulative_angle1 = cum[i];   // (axis 2's stays on the device)
+      if (j->type() == dJointTypeGearbox) static_cast<dxJointGearbox *>(j)->cumulative_angle1 = cum[i];
     }
   }
   return 0;

@@ -221,10 +221,12 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       Joint &J = hj[j];
       memset(&J, 0, sizeof(J));
       J.type = sc->joint_type[j];
-      if (J.type < GZ_JOINT_HINGE || J.type > GZ_JOINT_GEARBOX)
+      if (J.type < GZ_JOINT_HINGE || J.type > GZ_JOINT_SCREW)
         return fail(GZCUDA_E_INVALID, "unknown joint type");
       if ((J.type == GZ_JOINT_HINGE2 || J.type == GZ_JOINT_GEARBOX) && sc->joint_body2[j] < 0)
         return fail(GZCUDA_E_INVALID, "hinge2 and gearbox joints need two bodies (joints/hinge2.cpp:31, gearbox.cpp:67-68)");
+      if (J.type == GZ_JOINT_SCREW && sc->joint_param[GZ_JP_COUNT * j + GZ_JP_FMAX] > 0)
+        return fail(GZCUDA_E_INVALID, "a powered screw joint (fmax > 0) is not supported: the reference writes its row behind the joint's rows (screw.cpp:55-110, :419)");
       const int nbw = sc->body_off[w + 1] - sc->body_off[w];
       if (sc->joint_body1[j] < 0 || sc->joint_body1[j] >= nbw || sc->joint_body2[j] >= nbw)
         return fail(GZCUDA_E_INVALID, "joint body index out of range");

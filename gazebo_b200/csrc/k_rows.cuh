@@ -360,6 +360,17 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
           m = 6;
         } else if (j.type == GZ_JOINT_BALL) {
           m = 3;
+        } else if (j.type == GZ_JOINT_SCREW) {
+          // dxJointScrew::getInfo1 (screw.cpp:55-110): five rows, a sixth at a stop of the rotation
+          m = 5;
+          const double lo = j.param[GZ_JP_LOSTOP], hi = j.param[GZ_JP_HISTOP];
+          if (lo <= hi) {
+            const double angle = hinge_angle(B, j);
+            j.cum_angle = shortest_angular_distance_update(j.cum_angle, angle);
+            if (j.cum_angle <= lo) { j.limit = 1; j.limit_err = j.cum_angle - lo; m = 6; }
+            else if (j.cum_angle >= hi) { j.limit = 2; j.limit_err = j.cum_angle - hi; m = 6; }
+            else j.limit = 0;
+          }
         } else if (j.type == GZ_JOINT_GEARBOX) {
           m = 1;   // dxJointGearbox::getInfo1 (gearbox.cpp:54-59)
         } else if (j.type == GZ_JOINT_HINGE2) {

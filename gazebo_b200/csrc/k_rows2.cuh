@@ -204,6 +204,57 @@ __global__ void k_rows_joint(DevBatch B) {
         add_limot(B, j, rows[row], ax2, fps, true, M2);
       }
     }
+  } else if (j.type == GZ_JOINT_SCREW) {
+    // dxJointScrew::getInfo2 (screw.cpp:113-420): two rows keep the anchors together across the axis, one row couples
+    // the translation along the axis with the rotation about it (thread pitch, rad / m), two rows keep the axes aligned
+    // (as the hinge's), then the stop of the rotation
+    if (j.param[GZ_JP_CFM] >= 0) for (int r = 0; r < 5; r++) rows[r].cfm = j.param[GZ_JP_CFM];
+    const double *X = joint_ext(B, j);
+    const double pitch = X[GZ_JP_THREAD_PITCH];
+    double ax1[3], q[3], p[3], a1[3], a2[3] = {0, 0, 0}, t[3];
+    mul0_331(ax1, b1.R, j.axis1);
+    if (b2) {
+      mul0_331(q, b2->R, &X[GZ_JP_OFFSET]);
+      for (int i = 0; i < 3; i++) q[i] = b1.pos[i] - q[i] - b2->pos[i];
+    } else {
+      for (int i = 0; i < 3; i++) q[i] = b1.pos[i] - X[GZ_JP_OFFSET + i];
+    }
+    const double lin_disp = dot3(ax1, q);
+    const bool coarse = fabs(pitch) > 1.0;
+    const double lin_err = coarse ? -(lin_disp - j.cum_angle / pitch) : -(pitch * lin_disp - j.cum_angle);
+    plane_space(ax1, p, q);
+    for (int i = 0; i < 3; i++) { rows[0].J[i] = p[i]; rows[1].J[i] = q[i]; }
+    mul0_331(a1, b1.R, j.anchor1);
+    cross3(t, p, a1); for (int i = 0; i < 3; i++) rows[0].J[3 + i] = -t[i];
+    cross3(t, q, a1); for (int i = 0; i < 3; i++) rows[1].J[3 + i] = -t[i];
+    if (coarse) for (int i = 0; i < 3; i++) { rows[2].J[i] = ax1[i]; rows[2].J[3 + i] = -ax1[i] / pitch; }
+    else for (int i = 0; i < 3; i++) { rows[2].J[i] = ax1[i] * pitch; rows[2].J[3 + i] = -ax1[i]; }
+    const double k = fps * erp;
+    if (b2) {
+      for (int i = 0; i < 3; i++) { rows[0].J[6 + i] = -p[i]; rows[1].J[6 + i] = -q[i]; }
+      mul0_331(a2, b2->R, j.anchor2);
+      cross3(t, p, a2); for (int i = 0; i < 3; i++) rows[0].J[9 + i] = t[i];
+      cross3(t, q, a2); for (int i = 0; i < 3; i++) rows[1].J[9 + i] = t[i];
+      if (coarse) for (int i = 0; i < 3; i++) { rows[2].J[9 + i] = ax1[i] / pitch; rows[2].J[6 + i] = -ax1[i]; }
+      else for (int i = 0; i < 3; i++) { rows[2].J[9 + i] = ax1[i]; rows[2].J[6 + i] = -ax1[i] * pitch; }
+      double e[3];
+      for (int i = 0; i < 3; i++) e[i] = a2[i] + b2->pos[i] - a1[i] - b1.pos[i];
+      rows[0].c = k * dot3(e, p); rows[1].c = k * dot3(e, q);
+    } else {
+      double e[3];
+      for (int i = 0; i < 3; i++) e[i] = j.anchor2[i] - a1[i] - b1.pos[i];
+      rows[0].c = k * dot3(e, p); rows[1].c = k * dot3(e, q);
+    }
+    rows[2].c = k * lin_err;
+    for (int i = 0; i < 3; i++) { rows[3].J[3 + i] = p[i]; rows[4].J[3 + i] = q[i]; }
+    if (b2) for (int i = 0; i < 3; i++) { rows[3].J[9 + i] = -p[i]; rows[4].J[9 + i] = -q[i]; }
+    double ax2[3], bb[3];
+    if (b2) mul0_331(ax2, b2->R, j.axis2);
+    else { ax2[0] = j.axis2[0]; ax2[1] = j.axis2[1]; ax2[2] = j.axis2[2]; }
+    cross3(bb, ax1, ax2);
+    rows[3].c = k * dot3(bb, p);
+    rows[4].c = k * dot3(bb, q);
+    if (j.m == 6) add_limot(B, j, rows[5], ax1, fps, true);
   } else if (j.type == GZ_JOINT_GEARBOX) {
     // dxJointGearbox::getInfo2 (gearbox.cpp:62-103): the two angles (cumulative, each against its reference body), one
     // row on the angular velocities about the two axes; the world's erp (the joint's is not consulted)

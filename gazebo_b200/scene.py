@@ -15,13 +15,14 @@ import sys
 import numpy as np
 
 GEOM_SPHERE, GEOM_BOX, GEOM_CAPSULE, GEOM_CYLINDER, GEOM_PLANE = range(5)
-JOINT_HINGE, JOINT_FIXED, JOINT_BALL, JOINT_SLIDER, JOINT_UNIVERSAL, JOINT_HINGE2, JOINT_GEARBOX = 1, 2, 3, 4, 5, 6, 7
+JOINT_HINGE, JOINT_FIXED, JOINT_BALL, JOINT_SLIDER, JOINT_UNIVERSAL, JOINT_HINGE2, JOINT_GEARBOX, JOINT_SCREW = 1, 2, 3, 4, 5, 6, 7, 8
 BODY_NO_GRAVITY, BODY_AUTO_DISABLE, BODY_DISABLED, BODY_NO_GYRO = 1, 2, 4, 8
 JP_LOSTOP, JP_HISTOP, JP_VEL, JP_FMAX, JP_FUDGE, JP_BOUNCE, JP_NORMAL_CFM, \
     JP_STOP_ERP, JP_STOP_CFM, JP_ERP, JP_CFM = range(11)
 JP_VEL2, JP_FMAX2, JP_SUSP_ERP, JP_SUSP_CFM, JP_V1, JP_V2, JP_C0, JP_S0 = 12, 13, 14, 15, 16, 19, 22, 23
 JP_LOSTOP2, JP_HISTOP2, JP_FUDGE2, JP_BOUNCE2, JP_NORMAL_CFM2, JP_STOP_ERP2, JP_STOP_CFM2, JP_QREL2 = 24, 25, 26, 27, 28, 29, 30, 31
 JP_RATIO, JP_REFBODY1, JP_REFBODY2 = 35, 14, 15
+JP_THREAD_PITCH, JP_OFFSET = 35, 16
 JP_COUNT = 36
 SF_MU, SF_MU2, SF_KP, SF_KD, SF_SLIP1, SF_SLIP2, SF_BOUNCE, SF_BOUNCE_VEL = range(8)
 SF_PATCH_RADIUS, SF_ELASTIC_MODULUS, SF_POISSON, SF_SURFACE_RADIUS, SF_USE_PATCH_RADIUS, SF_MU3 = 8, 9, 10, 11, 12, 13
@@ -388,6 +389,29 @@ class SceneBuilder:
         P[JP_QREL2:JP_QREL2 + 4] = list(qrel2)
         z = np.zeros(3)
         self._push_joint(JOINT_GEARBOX, b1, b2, z, z, ax1, ax2, tuple(qrel1), P)
+        return self._nj - 1 - self._w_j0
+
+    def add_screw(self, b1, b2, anchor, axis, thread_pitch, **params):
+        """dxJointScrew (SDF screw): rotation about the axis and translation along it coupled by thread_pitch (rad / m).
+        Anchor and axis in world coordinates at the current poses; params = the stops of the rotation (a motor is refused:
+        the reference writes its row behind the joint's rows)."""
+        p1, q1 = self._body_pose(b1)
+        R1 = q_to_R(q1)
+        anchor = np.asarray(anchor, float)
+        axis = np.asarray(axis, float) / np.linalg.norm(axis)
+        a1, ax1 = R1.T @ (anchor - p1), R1.T @ axis
+        if b2 >= 0:
+            p2, q2 = self._body_pose(b2)
+            R2 = q_to_R(q2)
+            a2, ax2 = R2.T @ (anchor - p2), R2.T @ axis
+            qrel = q_mul(q_conj(q1), q2)
+            ofs = R2.T @ (p1 - p2)                 # computeOffset (screw.cpp:795-820)
+        else:
+            a2, ax2, qrel, ofs = anchor, axis, q_conj(q1), p1
+        P = self.joint_params(**params)
+        P[JP_THREAD_PITCH] = float(thread_pitch)
+        P[JP_OFFSET:JP_OFFSET + 3] = list(ofs)
+        self._push_joint(JOINT_SCREW, b1, b2, a1, a2, ax1, ax2, qrel, P)
         return self._nj - 1 - self._w_j0
 
     def add_slider(self, b1, b2, axis, **params):

@@ -143,6 +143,13 @@ int joint_params(const Mirror *m, dxJoint *j, double *P) {
       for (int k = 0; k < 4; k++) P[GZ_JP_QREL2 + k] = uj->qrel2[k];
       return GZ_JOINT_UNIVERSAL;
     }
+    case dJointTypeScrew: {
+      const dxJointScrew *sj = static_cast<dxJointScrew *>(j);
+      limot_params(sj->limot, P);
+      P[GZ_JP_THREAD_PITCH] = sj->thread_pitch;
+      for (int k = 0; k < 3; k++) P[GZ_JP_OFFSET + k] = sj->offset[k];
+      return GZ_JOINT_SCREW;
+    }
     case dJointTypeGearbox: {
       const dxJointGearbox *gj = static_cast<dxJointGearbox *>(j);
       P[GZ_JP_RATIO] = gj->ratio;
@@ -280,7 +287,7 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
   for (int i = 0; i < nj; i++) {
     dxJoint *j = m->joints[i];
     jtype[i] = joint_params(m, j, &m->jparam[(size_t)GZ_JP_COUNT * i]);
-    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball, universal, hinge2, gearbox");
+    if (!jtype[i]) return fail(GZCUDA_E_INVALID, "joint type is not one of hinge, slider, fixed, ball, universal, hinge2, gearbox, screw");
     if (!j->node[0].body) return fail(GZCUDA_E_INVALID, "a joint without bodies");
     auto i1 = bidx.find(j->node[0].body);
     if (i1 == bidx.end()) return fail(GZCUDA_E_INVALID, "a joint is attached to a body of another world");
@@ -300,6 +307,10 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
       const dxJointFixed *fj = static_cast<dxJointFixed *>(j);
       for (int k = 0; k < 3; k++) ja1[3 * i + k] = fj->offset[k];
       for (int k = 0; k < 4; k++) jq[4 * i + k] = fj->qrel[k];
+    } else if (jtype[i] == GZ_JOINT_SCREW) {
+      const dxJointScrew *sj = static_cast<dxJointScrew *>(j);
+      for (int k = 0; k < 3; k++) { ja1[3 * i + k] = sj->anchor1[k]; ja2[3 * i + k] = sj->anchor2[k]; jx1[3 * i + k] = sj->axis1[k]; jx2[3 * i + k] = sj->axis2[k]; }
+      for (int k = 0; k < 4; k++) jq[4 * i + k] = sj->qrel[k];
     } else if (jtype[i] == GZ_JOINT_GEARBOX) {
       const dxJointGearbox *gj = static_cast<dxJointGearbox *>(j);
       for (int k = 0; k < 3; k++) { jx1[3 * i + k] = gj->axis1[k]; jx2[3 * i + k] = gj->axis2[k]; }
@@ -455,6 +466,7 @@ int download(Mirror *m) {
       if (j->type() == dJointTypeHinge) static_cast<dxJointHinge *>(j)->cumulative_angle = cum[i];
       if (j->type() == dJointTypeUniversal) static_cast<dxJointUniversal *>(j)->cumulative_angle1 = cum[i];   // (axis 2's stays on the device)
       if (j->type() == dJointTypeGearbox) static_cast<dxJointGearbox *>(j)->cumulative_angle1 = cum[i];
+      if (j->type() == dJointTypeScrew) static_cast<dxJointScrew *>(j)->cumulative_angle = cum[i];
     }
   }
   return 0;

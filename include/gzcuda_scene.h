@@ -36,7 +36,9 @@ enum { GZ_GEOM_SPHERE = 0, GZ_GEOM_BOX = 1, GZ_GEOM_CAPSULE = 2,
 enum { GZ_JOINT_HINGE = 1, GZ_JOINT_FIXED = 2, GZ_JOINT_BALL = 3,
        GZ_JOINT_SLIDER = 4, GZ_JOINT_UNIVERSAL = 5,
        GZ_JOINT_HINGE2 = 6,
-       GZ_JOINT_GEARBOX = 7 };  /* dxJointHinge2 (SDF revolute2): two bodies required; joint_anchor1/2, joint_axis1/2 in the
+       GZ_JOINT_GEARBOX = 7,
+       GZ_JOINT_SCREW = 8 };    /* dxJointScrew (SDF screw): hinge + slider coupled by the thread pitch; joint_anchor1/2, joint_axis1/2,
+                                * joint_qrel as for a hinge, dxJointScrew::offset and thread_pitch in joint_param */  /* dxJointHinge2 (SDF revolute2): two bodies required; joint_anchor1/2, joint_axis1/2 in the
                                 * bodies' frames, the derived members v1, v2, c0, s0 in joint_param (below);
                                 * GZ_JOINT_GEARBOX = dxJointGearbox: two bodies required as well */
 
@@ -69,6 +71,10 @@ enum { GZ_JP_LOSTOP = 0, GZ_JP_HISTOP = 1, GZ_JP_VEL = 2, GZ_JP_FMAX = 3,
         * against a reference body): joint_axis1 / joint_axis2 in the bodies' frames, joint_qrel = qrel1, GZ_JP_QREL2 = qrel2,
         * the gear ratio, and the reference bodies as world-local body indices (-1: the world) */
        GZ_JP_RATIO = 35, GZ_JP_REFBODY1 = 14, GZ_JP_REFBODY2 = 15,   /* (the reference bodies overlay the hinge2-only suspension slots) */
+       /* screw joints (joints/screw.cpp): thread pitch (rad / m) and offset[3] (computeOffset, screw.cpp:795-820); the stops
+        * of the rotation are the joint's limit motor (slots 0..8); a POWERED screw (fmax > 0) is refused: the reference
+        * writes that row behind the joint's five rows (screw.cpp:55-110 never counts it, :419 writes it) */
+       GZ_JP_THREAD_PITCH = 35, GZ_JP_OFFSET = 16,   /* offset[3]: 16..18 (overlays hinge2's v1) */
        GZ_JP_COUNT = 36 };
 
 /* geom_surf[] slots (ODESurfaceParams + FrictionPyramid) */

@@ -682,6 +682,20 @@ void *gzref_create(const gz_scene *sc, const gz_params *p, int mode) {
         uj->limot2.lostop = P[GZ_JP_LOSTOP2]; uj->limot2.histop = P[GZ_JP_HISTOP2]; uj->limot2.vel = P[GZ_JP_VEL2]; uj->limot2.fmax = P[GZ_JP_FMAX2];
         uj->limot2.fudge_factor = P[GZ_JP_FUDGE2]; uj->limot2.bounce = P[GZ_JP_BOUNCE2]; uj->limot2.normal_cfm = P[GZ_JP_NORMAL_CFM2];
         uj->limot2.stop_erp = P[GZ_JP_STOP_ERP2]; uj->limot2.stop_cfm = P[GZ_JP_STOP_CFM2];
+      } else if (sc->joint_type[j] == GZ_JOINT_SCREW) {
+        jt = dJointCreateScrew(w->world, 0);
+        dJointAttach(jt, b1, b2);
+        dxJointScrew *sj = (dxJointScrew *)jt;
+        for (int k = 0; k < 3; k++) {
+          sj->anchor1[k] = sc->joint_anchor1[3 * j + k]; sj->anchor2[k] = sc->joint_anchor2[3 * j + k];
+          sj->axis1[k] = sc->joint_axis1[3 * j + k]; sj->axis2[k] = sc->joint_axis2[3 * j + k];
+          sj->offset[k] = P[GZ_JP_OFFSET + k];
+        }
+        for (int k = 0; k < 4; k++) sj->qrel[k] = sc->joint_qrel[4 * j + k];
+        sj->thread_pitch = P[GZ_JP_THREAD_PITCH];
+        sj->limot.lostop = P[GZ_JP_LOSTOP]; sj->limot.histop = P[GZ_JP_HISTOP]; sj->limot.vel = P[GZ_JP_VEL]; sj->limot.fmax = P[GZ_JP_FMAX];
+        sj->limot.fudge_factor = P[GZ_JP_FUDGE]; sj->limot.bounce = P[GZ_JP_BOUNCE]; sj->limot.normal_cfm = P[GZ_JP_NORMAL_CFM];
+        sj->limot.stop_erp = P[GZ_JP_STOP_ERP]; sj->limot.stop_cfm = P[GZ_JP_STOP_CFM];
       } else if (sc->joint_type[j] == GZ_JOINT_GEARBOX) {
         if (!b2) return nullptr;
         jt = dJointCreateGearbox(w->world, 0);
@@ -968,7 +982,8 @@ void gzref_get_joint_state(void *h, double *lambda, double *lambda_erp, double *
       for (int r = 0; r < 6; r++) { lambda[6 * j + r] = jt->lambda[r]; lambda_erp[6 * j + r] = jt->lambda_erp[r]; }
       cum_angle[j] = (w->joint_type[k] == GZ_JOINT_HINGE) ? ((dxJointHinge *)jt)->cumulative_angle :
                      (w->joint_type[k] == GZ_JOINT_UNIVERSAL) ? ((dxJointUniversal *)jt)->cumulative_angle1 :
-                     (w->joint_type[k] == GZ_JOINT_GEARBOX) ? ((dxJointGearbox *)jt)->cumulative_angle1 : 0.0;
+                     (w->joint_type[k] == GZ_JOINT_GEARBOX) ? ((dxJointGearbox *)jt)->cumulative_angle1 :
+                     (w->joint_type[k] == GZ_JOINT_SCREW) ? ((dxJointScrew *)jt)->cumulative_angle : 0.0;
       j++;
     }
 }

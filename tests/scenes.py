@@ -353,6 +353,32 @@ def carts(n_worlds=3, seed=31):
     return sb.finish(), S.default_params(), None
 
 
+def screws(n_worlds=2, seed=71):
+    """Screw joints (dxJointScrew, SDF screw): a nut on a vertical rod fixed in the world (thread pitch 30 rad / m: it
+    spins down under gravity until it lands on the plane), a nut on a tilted rod with a fine pitch (0.8 rad / m, the other
+    branch of screw.cpp:170-177) and stops on the rotation with bounce, and two free bodies screwed together that tumble
+    onto the plane."""
+    sb = S.SceneBuilder()
+    for w in range(n_worlds):
+        rng = np.random.Generator(np.random.PCG64(seed + w))
+        sb.begin_world()
+        sb.add_ground_plane()
+        a = sb.add_body([0.0, 0.0, 1.2], mass=1.0, inertia=S.box_inertia(1.0, 0.3, 0.3, 0.1), avel=(0, 0, 1.0 + w))
+        sb.add_geom(S.GEOM_BOX, (0.3, 0.3, 0.1), sb.new_space(), body=a)
+        sb.add_screw(a, -1, [0.0, 0.0, 1.2], [0, 0, 1], 30.0)
+        b = sb.add_body([1.5, 0.0, 1.0], S.q_from_rpy(0.3, 0.2, 0.0), mass=0.8, inertia=S.box_inertia(0.8, 0.2, 0.2, 0.2), avel=tuple(rng.uniform(-2, 2, 3)))
+        sb.add_geom(S.GEOM_BOX, (0.2, 0.2, 0.2), sb.new_space(), body=b)
+        sb.add_screw(b, -1, [1.5, 0.0, 1.0], [0.3, 0.1, 1.0], 0.8, lostop=-0.6, histop=0.5, bounce=0.3, stop_erp=0.3, stop_cfm=1e-5)
+        sp = sb.new_space()
+        c = sb.add_body([0.0, 2.0, 0.9], S.q_random(rng), mass=1.2, inertia=S.box_inertia(1.2, 0.4, 0.15, 0.15), lvel=(0.3, 0, 0))
+        sb.add_geom(S.GEOM_BOX, (0.4, 0.15, 0.15), sp, body=c)
+        d = sb.add_body([0.3, 2.0, 0.9], S.q_random(rng), mass=0.7, inertia=S.sphere_inertia(0.7, 0.1), avel=(3.0, 0, 0))
+        sb.add_geom(S.GEOM_SPHERE, (0.1,), sp, body=d)
+        sb.add_screw(c, d, [0.15, 2.0, 0.9], [1, 0, 0], 12.0, erp=0.3, cfm=1e-6)
+        sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 def gears(n_worlds=2, seed=67):
     """Gearbox joints (dxJointGearbox, SDF gearbox): world 0 - two wheels hinged to the world on parallel axes, coupled 2 : 1,
     one driven by its hinge motor; world 1 - the same pair on a free carrier body (the gearbox's reference body) that
@@ -510,4 +536,5 @@ GOLDEN = {
     "hertz": (hertz, 700),
     "gimbals": (gimbals, 800),
     "gears": (gears, 700),
+    "screws": (screws, 900),
 }

@@ -118,6 +118,13 @@ def test_adapter_universal_joints_with_stops_and_motors(adapter, oracle):
 
 
 @pytest.mark.gpu
+def test_adapter_screw_joints(adapter, oracle):
+    """dxJointScrew objects mirrored from the live world: thread pitch, offset, the stops of the rotation."""
+    sc, p, _ = scenes.screws()
+    _run(adapter, oracle, sc, p, steps=400, every=100)
+
+
+@pytest.mark.gpu
 def test_adapter_gearbox_joints(adapter, oracle):
     """dxJointGearbox objects mirrored from the live world: axes, qrel1 / qrel2, ratio, the reference bodies by index."""
     sc, p, _ = scenes.gears()

@@ -72,6 +72,7 @@ struct gzcuda_batch {
   size_t pgsc_smem = 0;
   void *ray_buf = nullptr;            // gzcuda_batch_ray_query's device buffers
   int ray_cap = 0;
+  std::vector<std::pair<char *, size_t>> guards;   // GZCUDA_GUARD: the guard regions behind the device buffers
   bool pgsm = false;                  // k_pgsm: a world of up to 2048 bodies on one cluster, on chip (k_pgsd when it does not fit)
   int pgsm_cluster = 1, pgsm_threads = 128;
   size_t pgsm_smem = 0;
@@ -139,8 +140,17 @@ static inline int cdiv_host(int a, int b) { return (a + b - 1) / b; }
 template <class T>
 static int dev_alloc(gzcuda_batch *b, T **p, size_t n) {
   if (n == 0) n = 1;
-  CK(cudaMalloc((void **)p, n * sizeof(T)));
-  CK(cudaMemset(*p, 0, n * sizeof(T)));
+  // developer switch GZCUDA_GUARD=1 (compute-sanitizer is not available on the GPU boxes): every buffer is followed by
+  // a guard of 0x7F bytes - an index read from beyond a buffer is then a wild one and faults at once instead of
+  // reading a zero that happens to work, and gzcuda_batch_destroy reports guards that were written to
+  static const bool guard = getenv("GZCUDA_GUARD") && atoi(getenv("GZCUDA_GUARD")) != 0;
+  const size_t bytes = n * sizeof(T), gb = guard ? 4096 : 0;
+  CK(cudaMalloc((void **)p, bytes + gb));
+  CK(cudaMemset(*p, 0, bytes));
+  if (guard) {
+    CK(cudaMemset(reinterpret_cast<char *>(*p) + bytes, 0x7F, gb));
+    b->guards.push_back(std::make_pair(reinterpret_cast<char *>(*p) + bytes, gb));
+  }
   b->allocs.push_back(*p);
   return 0;
 }
@@ -166,6 +176,15 @@ void gzcuda_batch_destroy(gzcuda_batch *b) {
   if (!b) return;
   cudaSetDevice(b->device);
   if (b->stream) cudaStreamSynchronize(b->stream);
+  if (!b->guards.empty()) {   // GZCUDA_GUARD: a guard that is no longer all 0x7F was written by somebody
+    std::vector<unsigned char> h(4096);
+    int bad = 0;
+    for (auto &g : b->guards) {
+      if (cudaMemcpy(h.data(), g.first, g.second, cudaMemcpyDeviceToHost) != cudaSuccess) { bad = -1; break; }
+      for (size_t k = 0; k < g.second; k++) if (h[k] != 0x7F) { bad++; break; }
+    }
+    if (bad) { fprintf(stderr, "gzcuda guard: %d of %zu buffers were written beyond their end\n", bad, b->guards.size()); fflush(stderr); }
+  }
   for (void *p : b->allocs) cudaFree(p);
   if (b->h_sticky) cudaFreeHost(b->h_sticky);
   if (b->ev0) cudaEventDestroy(b->ev0);

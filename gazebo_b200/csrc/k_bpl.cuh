@@ -15,8 +15,8 @@
 //   k_bpl_tail      the queue: all warps share the followers of each queued position (without it the plane's warp
 //                   walked all 20 000 geoms alone and WAS the kernel's duration)
 //   k_bpl_scan      one CTA: exclusive scan of the counts, n_pairs, capacity flag
-//   k_bpl_emit      one warp per geom: puts its partners in ascending order - short lists by counting, long lists
-//                   (the plane's: thousands) through a bitmap over the geoms and its prefix popcount
+//   k_bpl_emit      one warp per geom: puts its partners in ascending order by counting; long lists (the plane's:
+//                   thousands) go to k_bpl_emit_big: one CTA each, a bitmap over the geoms and its prefix popcount
 #pragma once
 
 namespace gz {
@@ -28,9 +28,10 @@ namespace gz {
 
 struct BplBuf {
   double *key, *maxx, *tkey;
+  double *yz;   // [n][4] lower / upper y and z bounds in sorted order: the sweep's pre-filter reads them coalesced
   int *idx, *cnt, *fill, *tmp, *tidx;
   int *queue;   // [2 * n] (sorted position, first follower not tested yet)
-  int *ctl;     // [0] queue length, [1] bitmaps claimed
+  int *ctl;     // [0] queue length, [1] long lists claimed, [2 ..] their geoms
   int *bits;    // [GZ_BPL_NBIG][2][(n + 31) / 32 + 1] bitmap and its exclusive prefix popcount
   int npad;
   int chunks, big;   // GZ_BPL_CHUNKS, GZ_BPL_BIG unless a developer switch says otherwise
@@ -85,15 +86,22 @@ __global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_merge(DevBatch B, const int
     rank += lo;
   }
   Q.key[rank] = k; Q.idx[rank] = i;
-  if (i < n) Q.maxx[rank] = G[i].aabb[1];   // (real geoms take the places below n: padding sorts last)
+  if (i < n) {   // (real geoms take the places below n: padding sorts last)
+    Q.maxx[rank] = G[i].aabb[1];
+    for (int c = 0; c < 4; c++) Q.yz[4 * (size_t)rank + c] = G[i].aabb[2 + c];
+  }
 }
 
 // the full test of sorted position q against position p's geom ip; returns whether q is still inside p's x interval
 template <int PASS>
 __device__ __forceinline__ bool bpl_follow(const DevBatch &B, const WorldInfo &wi, const Geom *G, const BplBuf &Q, const int ip,
-                                           const double mx, const int q, const int n) {
+                                           const double mx, const double *pyz, const int q, const int n) {
   const bool in = (q < n) && Q.key[q] <= mx;
   if (in) {
+    // y and z first, from the sorted side array (collideAABBs' own comparisons, collision_space_internal.h:66-72: of the
+    // ~1 200 followers that overlap a pile's geom on x, a few dozen overlap it on y and z as well)
+    const double *c = Q.yz + 4 * (size_t)q;
+    if (pyz[0] > c[1] || pyz[1] < c[0] || pyz[2] > c[3] || pyz[3] < c[2]) return true;
     const int iq = Q.idx[q];
     const int lo = min(ip, iq), hi = max(ip, iq);
     if (pair_passes(B, G[lo], G[hi])) {
@@ -116,13 +124,14 @@ __global__ void __launch_bounds__(256) k_bpl_sweep(DevBatch B, const int w, BplB
   for (int p = warp; p < n - 1; p += nwarp) {
     const int ip = Q.idx[p];
     const double mx = Q.maxx[p];
+    const double pyz[4] = {Q.yz[4 * (size_t)p], Q.yz[4 * (size_t)p + 1], Q.yz[4 * (size_t)p + 2], Q.yz[4 * (size_t)p + 3]};
     int c = 0;
     for (int q0 = p + 1; q0 < n; q0 += 32, c++) {
       if (c == Q.chunks) {   // a long interval: the rest goes to k_bpl_tail (queued once, by pass 0)
         if (PASS == 0 && lane == 0) { const int at = atomicAdd(&Q.ctl[0], 1); Q.queue[2 * at] = p; Q.queue[2 * at + 1] = q0; }
         break;
       }
-      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, q0 + lane, n);
+      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
       if (!__all_sync(0xffffffffu, in)) break;   // sorted: nothing further overlaps p on x
     }
   }
@@ -139,8 +148,9 @@ __global__ void __launch_bounds__(256) k_bpl_tail(DevBatch B, const int w, BplBu
     const int p = Q.queue[2 * e], qs = Q.queue[2 * e + 1];
     const int ip = Q.idx[p];
     const double mx = Q.maxx[p];
+    const double pyz[4] = {Q.yz[4 * (size_t)p], Q.yz[4 * (size_t)p + 1], Q.yz[4 * (size_t)p + 2], Q.yz[4 * (size_t)p + 3]};
     for (int q0 = qs + 32 * warp; q0 < n; q0 += 32 * nwarp) {
-      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, q0 + lane, n);
+      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
       if (!__all_sync(0xffffffffu, in)) break;   // sorted: this warp's later chunks are outside as well
     }
   }
@@ -183,40 +193,16 @@ __global__ void __launch_bounds__(1024) k_bpl_scan(DevBatch B, const int w, BplB
 
 __global__ void __launch_bounds__(256) k_bpl_emit(DevBatch B, const int w, BplBuf Q) {
   const WorldInfo wi = B.world[w];
-  const int n = wi.ng, lane = threadIdx.x & 31, nwords = (n + 31) / 32 + 1;
+  const int n = wi.ng, lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarp = (gridDim.x * blockDim.x) >> 5;
   for (int lo = warp; lo < n; lo += nwarp) {
     const int base = Q.cnt[lo], L = min(Q.cnt[lo + 1], wi.pair_cap) - base;
-    int slot = -1;
-    if (L >= Q.big) {
+    if (L >= Q.big) {   // a long list (the plane's: thousands): a whole CTA orders it, k_bpl_emit_big
+      int slot = -1;
       if (lane == 0) slot = atomicAdd(&Q.ctl[1], 1);
       slot = __shfl_sync(0xffffffffu, slot, 0);
-      if (slot >= GZ_BPL_NBIG) slot = -1;   // (more long lists than bitmaps: counting still gives the right order)
-    }
-    if (slot >= 0) {
-      // partners of a geom are distinct: rank = number of set bits below the partner's
-      int *bits = Q.bits + (size_t)slot * 2 * nwords, *pre = bits + nwords;
-      for (int k = lane; k < nwords; k += 32) bits[k] = 0;
-      __syncwarp();
-      for (int e = lane; e < L; e += 32) { const int hi = Q.tmp[base + e]; atomicOr(&bits[hi >> 5], 1 << (hi & 31)); }
-      __syncwarp();
-      int carry = 0;
-      for (int k0 = 0; k0 < nwords; k0 += 32) {
-        const int k = k0 + lane;
-        const int c = k < nwords ? __popc(__ldcg(&bits[k])) : 0;
-        int v = c;
-        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
-        if (k < nwords) pre[k] = carry + v - c;
-        carry += __shfl_sync(0xffffffffu, v, 31);
-      }
-      __syncwarp();
-      for (int e = lane; e < L; e += 32) {
-        const int hi = Q.tmp[base + e];
-        const int rank = pre[hi >> 5] + __popc(__ldcg(&bits[hi >> 5]) & ((1u << (hi & 31)) - 1u));
-        B.pair[2 * (wi.pair0 + base + rank)] = wi.geom0 + lo;
-        B.pair[2 * (wi.pair0 + base + rank) + 1] = wi.geom0 + hi;
-      }
-      continue;
+      if (slot < GZ_BPL_NBIG) { if (lane == 0) Q.ctl[2 + slot] = lo; continue; }
+      // (more long lists than bitmaps: counting still gives the right order)
     }
     for (int e = lane; e < L; e += 32) {
       const int hi = Q.tmp[base + e];
@@ -225,6 +211,49 @@ __global__ void __launch_bounds__(256) k_bpl_emit(DevBatch B, const int w, BplBu
       B.pair[2 * (wi.pair0 + base + rank)] = wi.geom0 + lo;
       B.pair[2 * (wi.pair0 + base + rank) + 1] = wi.geom0 + hi;
     }
+  }
+}
+
+// One CTA per long partner list: a bitmap over the geoms, its prefix popcount (block scan), rank = set bits below the
+// partner's (partners of a geom are distinct).
+__global__ void __launch_bounds__(1024) k_bpl_emit_big(DevBatch B, const int w, BplBuf Q) {
+  __shared__ int wsum[32];
+  __shared__ int carry_s;
+  const int slot = blockIdx.x;
+  if (slot >= min(Q.ctl[1], GZ_BPL_NBIG)) return;
+  const WorldInfo wi = B.world[w];
+  const int n = wi.ng, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwords = (n + 31) / 32 + 1;
+  const int lo = Q.ctl[2 + slot];
+  const int base = Q.cnt[lo], L = min(Q.cnt[lo + 1], wi.pair_cap) - base;
+  int *bits = Q.bits + (size_t)slot * 2 * nwords, *pre = bits + nwords;
+  for (int k = tid; k < nwords; k += 1024) bits[k] = 0;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int e = tid; e < L; e += 1024) { const int hi = Q.tmp[base + e]; atomicOr(&bits[hi >> 5], 1 << (hi & 31)); }
+  __syncthreads();
+  for (int k0 = 0; k0 < nwords; k0 += 1024) {
+    const int k = k0 + tid;
+    const int c = k < nwords ? __popc(__ldcg(&bits[k])) : 0;
+    int v = c;
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
+    if (lane == 31) wsum[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+      int sx = wsum[lane];
+      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, sx, d); if (lane >= d) sx += t; }
+      wsum[lane] = sx;
+    }
+    __syncthreads();
+    if (k < nwords) pre[k] = carry_s + (warp > 0 ? wsum[warp - 1] : 0) + v - c;
+    __syncthreads();
+    if (tid == 0) carry_s += wsum[31];
+    __syncthreads();
+  }
+  for (int e = tid; e < L; e += 1024) {
+    const int hi = Q.tmp[base + e];
+    const int rank = pre[hi >> 5] + __popc(__ldcg(&bits[hi >> 5]) & ((1u << (hi & 31)) - 1u));
+    B.pair[2 * (wi.pair0 + base + rank)] = wi.geom0 + lo;
+    B.pair[2 * (wi.pair0 + base + rank) + 1] = wi.geom0 + hi;
   }
 }
 

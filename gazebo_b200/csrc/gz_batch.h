@@ -68,7 +68,7 @@ struct Geom {
   unsigned cat, col, scat, scol;  // geom bits and the bits of its space (ODECollision.cc:161-176)
   unsigned bitmask;
   int max_contacts;
-  int em_on, pad_;     // elastic modulus > 0 (ODEPhysics.cc:1241-1251 needs it on BOTH geoms of a pair)
+  int em_on, tors_on;  // elastic modulus > 0 (ODEPhysics.cc:1241-1251 needs it on BOTH geoms of a pair); tors_on: bit 0 mu3 > 0 (likewise, :1168), bit 1 patch radius > 0 or use_patch_radius off
 };
 
 struct Joint {
@@ -99,6 +99,10 @@ struct Contact {
   int reverse;       // dJOINT_REVERSE
   int has_fdir1;
   int row0, em_surface;   // em_surface: the pair does not use the patch radius (contact.cpp:166-172)
+  // torsional friction (dContactMu3, contact.cpp:362-437): tors 0 = the pair has no such row (in a world of four-row
+  // contacts its fourth row is a placeholder that is never swept), 1 = patch radius, 2 = sqrt(surface radius x depth)
+  double mu3, tors_radius, slip3;   // slip3 > 0: dContactSlip3
+  int tors, pad_;
 };
 
 // One constraint row as the assembly kernels leave it: 24 doubles = 192 B.  (What the sweeps read is the
@@ -120,6 +124,7 @@ struct WorldInfo {
   int body0, nb, geom0, ng, joint0, nj;
   int pair0, pair_cap, contact0, contact_cap, row0, row_cap;
   int slot0, slot_cap;   // packed-record slab of the world (schedule slots), see k_pgs.cuh
+  int rpc, pad_;         // rows per contact: 3, or 4 when a surface of the world has torsional friction (mu3 > 0)
 };
 
 struct WorldStep {
@@ -177,7 +182,7 @@ struct DevBatch {
   int pgsc_bpw;          // k_pgsc: bodies per warp (<= 16; the other lanes of the warp idle: a warp is ONE instruction stream
                          // that runs its bodies' rows one after the other, so fewer bodies per warp = more streams)
   double *joint_ext;     // [nj][GZ_JP_COUNT - GZ_JP_HOT] the joint_param slots only hinge2 / universal joints read
-  double *geom_ext;      // [ng][GZ_SF_COUNT - GZ_SF_HOT] patch radius, elastic modulus, Poisson's ratio, surface radius, use_patch_radius, mu3
+  double *geom_ext;      // [ng][GZ_SF_COUNT - GZ_SF_HOT] patch radius, elastic modulus, Poisson's ratio, surface radius, use_patch_radius, mu3, slip3
   int *cta_e0;           // [n_worlds][GZ_PGSC_TAB] first entry of every CTA of k_pgsc (then the world's end), else null
   int *bs_clist;         // [2 * contacts] k_bsched_large's per-body contact lists (large worlds only, else null)
   int *bs_glob;          // [5][max_nb] k_bsched's per-body tables for worlds too large for shared memory (else null)

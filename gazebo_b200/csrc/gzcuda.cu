@@ -294,6 +294,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     }
   }
   int max_nb = 0, max_ng = 0, max_nj = 0, max_pc = 0, max_cc = 0, max_rc = 0;
+  bool any_tors = false;
   long pair_tot = 0, contact_tot = 0, row_tot = 0, slot_tot = 0;
   for (int w = 0; w < W; w++) {
     const int g0 = sc->geom_off[w], g1 = sc->geom_off[w + 1];
@@ -328,8 +329,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       for (int k = 0; k < GZ_SF_HOT; k++) G.surf[k] = sc->geom_surf[GZ_SF_COUNT * g + k];
       for (int k = GZ_SF_HOT; k < GZ_SF_COUNT; k++) hgx[(size_t)(GZ_SF_COUNT - GZ_SF_HOT) * g + k - GZ_SF_HOT] = sc->geom_surf[GZ_SF_COUNT * g + k];
       G.em_on = sc->geom_surf[GZ_SF_COUNT * g + GZ_SF_ELASTIC_MODULUS] > 0 ? 1 : 0;
-      if (sc->geom_surf[GZ_SF_COUNT * g + GZ_SF_MU3] > 0)
-        return fail(GZCUDA_E_INVALID, "torsional friction (mu3 > 0: a fourth contact row) is not supported");
+      {   // bit 0: mu3 > 0 (needed on both surfaces of a pair); bit 1: a radius that can switch the row on (on either)
+        const double *sf = sc->geom_surf + (size_t)GZ_SF_COUNT * g;
+        G.tors_on = (sf[GZ_SF_MU3] > 0 ? 1 : 0) | ((sf[GZ_SF_PATCH_RADIUS] > 0 || sf[GZ_SF_USE_PATCH_RADIUS] == 0) ? 2 : 0);
+      }
       G.cat = sc->geom_category_bits[g]; G.col = sc->geom_collide_bits[g];
       G.scat = scat[G.space]; G.scol = scol[G.space];
       G.bitmask = sc->geom_collide_bitmask[g];
@@ -355,7 +358,11 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     wi.joint0 = sc->joint_off[w]; wi.nj = sc->joint_off[w + 1] - wi.joint0;
     wi.pair_cap = (int)std::max(1L, std::min(np, np_limit));
     wi.contact_cap = std::min(8 * wi.pair_cap, std::max(64, 24 * n));
-    wi.row_cap = 6 * wi.nj + 3 * wi.contact_cap;
+    int n_tors = 0, tors_radius = 0;   // a pair has a torsional row only when BOTH surfaces have mu3 > 0 (the smaller one counts)
+    for (int i = g0; i < g1; i++) { n_tors += hg[i].tors_on & 1; tors_radius |= hg[i].tors_on & 2; }
+    wi.rpc = (n_tors >= 2 && tors_radius) ? 4 : 3;
+    any_tors = any_tors || wi.rpc == 4;
+    wi.row_cap = 6 * wi.nj + wi.rpc * wi.contact_cap;
     // test hooks: shrink the slabs so that a step overflows them (tests/test_parity_gpu.py::test_capacity_overflow_is_sticky)
     if (const char *e = getenv("GZCUDA_TEST_PAIR_CAP")) wi.pair_cap = std::max(1, std::min(wi.pair_cap, atoi(e)));
     if (const char *e = getenv("GZCUDA_TEST_CONTACT_CAP")) wi.contact_cap = std::max(1, std::min(wi.contact_cap, atoi(e)));
@@ -442,6 +449,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if (v == 0 && max_nb <= 512) d.pgs_impl = 0;
     if (v == 2) d.pgs_impl = 2;
   }
+  if (any_tors && d.pgs_impl != 1)   // (the four-row contact layout is known to k_bsched / k_pgsb only)
+    return fail(GZCUDA_E_INVALID, "torsional friction (mu3 > 0 on two surfaces of a world) is built for worlds of up to 256 bodies");
   if (d.pgs_impl == 2) {
     // one lane per (body, solve) of the largest world, all CTAs resident (cooperative launch)
     int n_sm = 148, per_sm = 0;
@@ -1424,7 +1433,15 @@ int gzcuda_batch_get_stats(gzcuda_batch *b, double *rms_residual, int *num_conta
   for (int w = 0; w < b->d.n_worlds; w++) {
     if (rms_residual) for (int k = 0; k < 4; k++) rms_residual[4 * w + k] = ws[w].rms_residual[k];
     if (num_contacts) num_contacts[w] = ws[w].n_contacts;
-    if (num_rows) num_rows[w] = ws[w].m;
+    if (num_rows) {
+      num_rows[w] = ws[w].m;
+      const WorldInfo &wi = b->h_world[w];
+      if (wi.rpc == 4 && ws[w].m > 0 && ws[w].n_contacts > 0) {   // the placeholder rows of pairs without torsional friction are not rows
+        std::vector<Contact> hc(ws[w].n_contacts);
+        CK(cudaMemcpy(hc.data(), b->d.contact + wi.contact0, hc.size() * sizeof(Contact), cudaMemcpyDeviceToHost));
+        for (const Contact &c : hc) num_rows[w] -= c.tors ? 0 : 1;
+      }
+    }
   }
   return 0;
 }

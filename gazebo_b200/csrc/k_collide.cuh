@@ -358,6 +358,28 @@ __device__ inline void em_combine(const DevBatch &B, const int gi1, const int gi
   if (es > 0.0) { em = es; em_radius = use_patch ? patch : surface_radius; em_surface = use_patch ? 0 : 1; }
 }
 
+// Torsional friction of a pair (ODEPhysics.cc:1168-1232): mu3 = the smaller one, slip3 = the sum x contacts, the radii as
+// for Hertzian contact; the row exists (dContactMu3) when mu3 > 0 and the radius the pair uses is > 0.
+__device__ inline void tors_combine(const DevBatch &B, const int gi1, const int gi2, const int numc, double &mu3, double &radius, double &slip3, int &tors) {
+  const double *x1 = B.geom_ext + (size_t)gi1 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT, *x2 = B.geom_ext + (size_t)gi2 * (GZ_SF_COUNT - GZ_SF_HOT) - GZ_SF_HOT;
+  mu3 = fmin(x1[GZ_SF_MU3], x2[GZ_SF_MU3]);
+  slip3 = x1[GZ_SF_SLIP3] + x2[GZ_SF_SLIP3];
+  slip3 *= numc;
+  const double patch = fmax(x1[GZ_SF_PATCH_RADIUS], x2[GZ_SF_PATCH_RADIUS]);
+  double curv1 = 0, curv2 = 0;
+  if (x1[GZ_SF_SURFACE_RADIUS] > 0) curv1 = 1 / x1[GZ_SF_SURFACE_RADIUS];
+  if (x2[GZ_SF_SURFACE_RADIUS] > 0) curv2 = 1 / x2[GZ_SF_SURFACE_RADIUS];
+  const double curv_sum = curv1 + curv2;
+  double surface_radius = 0;
+  if (curv_sum > 0) surface_radius = 1 / curv_sum;
+  const bool use_patch = x1[GZ_SF_USE_PATCH_RADIUS] != 0 && x2[GZ_SF_USE_PATCH_RADIUS] != 0;
+  tors = 0;
+  if (mu3 > 0) {
+    if (use_patch && patch > 0) { tors = 1; radius = patch; }
+    else if (!use_patch && surface_radius > 0) { tors = 2; radius = surface_radius; }
+  }
+}
+
 // The contacts of candidate pair k of a world (c of them, from k_narrow) at place `off` of the world's contact list,
 // with the combined surface parameters.
 __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldInfo &wi, const int k, const int c, const int off) {
@@ -392,6 +414,9 @@ __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldI
   double em = 0.0, em_radius = 0.0;
   int em_surface = 0;
   if (g1.em_on && g2.em_on) em_combine(B, gi1, gi2, em, em_radius, em_surface);
+  double mu3 = 0.0, tors_radius = 0.0, slip3 = 0.0;
+  int tors = 0;
+  if ((g1.tors_on & g2.tors_on & 1) && ((g1.tors_on | g2.tors_on) & 2)) tors_combine(B, gi1, gi2, c, mu3, tors_radius, slip3, tors);
   // dJointAttach(contact, b1, b2): a null first body swaps and sets dJOINT_REVERSE
   int b1 = g1.body, b2 = g2.body, reverse = 0;
   if (b1 < 0) { b1 = b2; b2 = -1; reverse = 1; }
@@ -405,6 +430,7 @@ __device__ __forceinline__ void contacts_of_pair(const DevBatch &B, const WorldI
     C.mu = mu; C.mu2 = mu2; C.soft_erp = soft_erp; C.soft_cfm = soft_cfm;
     C.slip1 = slip1; C.slip2 = slip2; C.bounce = bounce; C.bounce_vel = bounce_vel;
     C.em = em; C.em_radius = em_radius; C.em_surface = em_surface;
+    C.mu3 = mu3; C.tors_radius = tors_radius; C.slip3 = slip3; C.tors = tors;
     C.g1 = gi1; C.g2 = gi2; C.b1 = b1; C.b2 = b2; C.reverse = reverse; C.has_fdir1 = fdset ? 1 : 0;
   }
   if (b1 >= 0) B.bstep[b1].has_contact = 1;

@@ -500,15 +500,15 @@ __device__ __forceinline__ void rowfinish_one(DevBatch &B, const int w, const Wo
   r.lambda = lam; r.lambda_erp = lam_erp;
   if (B.pgs_impl >= 1) {
     // body-owner sweeps (k_pgsb.cuh, k_pgsl.cuh): one entry per body of the row, at the place k_bsched gave it
-    const int nc = B.wstep[w].n_contacts, mj = B.wstep[w].m - 3 * nc;
+    const int nc = B.wstep[w].n_contacts, mj = B.wstep[w].m - wi.rpc * nc;
     const WScratchB S = wscratchb(B, w);
-    const int pos = order_pos(i, mj, nc);
+    const int pos = order_pos(i, mj, nc, wi.rpc);
     const int off = S.off[pos];
     if (off < 0) return;   // a row of an island that is not stepped, or a world the entry pool could not take
     const int cls = r.findex == -1 ? 0 : (r.findex == -2 ? 1 : 2);
     int back1 = 0, back2 = 0;
     if (cls == 2) {
-      const int pn = order_pos(r.findex, mj, nc);
+      const int pn = order_pos(r.findex, mj, nc, wi.rpc);
       back1 = S.idx1[pos] - S.idx1[pn];
       if (r.b2 >= 0) back2 = S.idx2[pos] - S.idx2[pn];
     }
@@ -531,7 +531,9 @@ __device__ __forceinline__ void rowfinish_one(DevBatch &B, const int w, const Wo
       e2[6] = make_double2(rhsA, lam);
       e2[7] = make_double2(rhsA_erp, lam_erp);
       e2[8] = make_double2(adcfm, r.lo);
-      const int mx = off | (cls << 27) | (h << 29);
+      // bit 30: a torsional row ("index - constraint_index >= 3", quickstep_pgs_lcp.cpp:554-566): its limits follow the
+      // normal force under the box model too
+      const int mx = off | (cls << 27) | (h << 29) | ((cls == 2 && i - r.findex >= 3) ? (1 << 30) : 0);
       const int partner = h ? r.b1 : (r.b2 >= 0 ? r.b2 : GZ_ENT_NOPART);
       const int my = partner | ((h ? back2 : back1) << 16);
       e2[9] = make_double2(r.hi, __hiloint2double(my, mx));
@@ -633,7 +635,7 @@ __global__ void k_feedback_contact(DevBatch B, int world, double *out) {
   if (ci >= B.wstep[world].n_contacts) return;
   const Contact &C = B.contact[wi.contact0 + ci];
   const bool live = B.wstep[world].m > 0 && B.bstep[C.b1].active;
-  feedback_rows(B.row + wi.row0 + C.row0, live ? 3 : 0, C.b2 >= 0, out + 12 * (size_t)ci);
+  feedback_rows(B.row + wi.row0 + C.row0, live ? (C.tors ? 4 : 3) : 0, C.b2 >= 0, out + 12 * (size_t)ci);
 }
 
 // One thread per body: dxUpdateBodies + dxStepBody.

@@ -61,10 +61,12 @@ __device__ inline WScratchB wscratchb(const DevBatch &B, int w) {
 
 // order[] position of row i (quickstep_pgs_lcp.cpp:1115-1150 with row_reorder1): bilateral rows in index
 // order, contact normals in REVERSE index order, friction rows in index order.  mj = persistent-joint rows.
-__device__ __forceinline__ int order_pos(int i, int mj, int nc) {
+// rpc = rows per contact (3; 4 in a world with torsional friction: the torsional row follows the contact's two
+// friction rows).
+__device__ __forceinline__ int order_pos(int i, int mj, int nc, int rpc) {
   if (i < mj) return i;
-  const int c = (i - mj) / 3, f = (i - mj) % 3;
-  return f == 0 ? mj + (nc - 1 - c) : mj + nc + 2 * c + (f - 1);
+  const int c = (i - mj) / rpc, f = (i - mj) % rpc;
+  return f == 0 ? mj + (nc - 1 - c) : mj + nc + (rpc - 1) * c + (f - 1);
 }
 
 // One CTA per world: bodies of the rows by order[] position (parallel), then ONE serial pass that gives
@@ -76,7 +78,7 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
   const int w = blockIdx.x, tid = threadIdx.x;
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
-  const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc;
+  const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, rpc = wi.rpc, mj = m - rpc * nc;
   int *const tab = B.bs_glob ? B.bs_glob + (size_t)w * 5 * B.max_nb : bs_sh;   // (large worlds: the tables live in global memory)
   int *last = tab, *first = tab + B.max_nb, *cnt = tab + 2 * B.max_nb, *fr0 = tab + 3 * B.max_nb, *base = tab + 4 * B.max_nb;
   __shared__ int s_R, s_maxoff, s_nent, s_wbase;
@@ -104,10 +106,11 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
       // a contact whose island is not stepped this step has rows (getInfo1 counted them) but they are never swept
       const bool live = B.bstep[C.b1].active != 0;
       const int b1 = live ? C.b1 - wi.body0 : -2, b2 = C.b2 >= 0 ? C.b2 - wi.body0 : -1;
-      const int pn = mj + (nc - 1 - c), pf = mj + nc + 2 * c;
+      const int pn = mj + (nc - 1 - c), pf = mj + nc + (rpc - 1) * c;
       S.rb1[pn] = b1; S.rb2[pn] = b2;
       S.rb1[pf] = b1; S.rb2[pf] = b2;
       S.rb1[pf + 1] = b1; S.rb2[pf + 1] = b2;
+      if (rpc == 4) { S.rb1[pf + 2] = C.tors ? b1 : -2; S.rb2[pf + 2] = b2; }   // (a pair without torsional friction: a placeholder, never swept)
     }
   }
   __syncthreads();
@@ -315,7 +318,8 @@ __device__ __forceinline__ int pgsb_sweeps(const DevBatch &B, double *lp_g, cons
     // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594);
     // (the distance to the normal row is 0 for the other classes: they read their own lambda and ignore it)
     double nlam = 1.0;
-    if (!BOX) nlam = (pc - (size_t)((unsigned)C.my >> 16) * STR)[13 + 2 * S];
+    // a torsional row (bit 30) follows the normal force under either model (:554-566)
+    if (!BOX || ((C.mx >> 30) & 1)) nlam = (pc - (size_t)((unsigned)C.my >> 16) * STR)[13 + 2 * S];
     // this body's half of the dot product, term by term in the reference's left-to-right order
     double d = a[0] * C.J[0];
 #pragma unroll

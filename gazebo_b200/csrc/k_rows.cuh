@@ -439,9 +439,9 @@ __device__ __forceinline__ void info1_world(const DevBatch &B, const int w) {
     __syncthreads();
   }
   const int mj = carry;
-  for (int c = threadIdx.x; c < ws.n_contacts; c += blockDim.x) B.contact[wi.contact0 + c].row0 = mj + 3 * c;
+  for (int c = threadIdx.x; c < ws.n_contacts; c += blockDim.x) B.contact[wi.contact0 + c].row0 = mj + wi.rpc * c;
   if (threadIdx.x == 0) {
-    int m = mj + 3 * ws.n_contacts;
+    int m = mj + wi.rpc * ws.n_contacts;
     if (m > wi.row_cap) { ws.overflow |= 4; m = 0; }
     ws.m = m;
     ws.n_fric = 0;   // reused by k_pgs as a cycle counter (instrumentation)

@@ -355,7 +355,7 @@ __device__ __forceinline__ void rows_contact_one(DevBatch &B, const int w, const
   const Body *b2 = C.b2 >= 0 ? &B.body[C.b2] : nullptr;
   const int lb1 = C.b1 - wi.body0, lb2 = C.b2 >= 0 ? C.b2 - wi.body0 : -1;
   const double fps = 1.0 / B.p.step_size;
-  for (int r = 0; r < 3; r++)
+  for (int r = 0; r < wi.rpc; r++)
     row_init(rows[r], lb1, lb2, B.p.cfm, B.p.contact_max_correcting_vel, ~(wi.contact0 + ci));
   double normal[3];
   if (C.reverse) { normal[0] = -C.normal[0]; normal[1] = -C.normal[1]; normal[2] = -C.normal[2]; }
@@ -429,6 +429,22 @@ __device__ __forceinline__ void rows_contact_one(DevBatch &B, const int w, const
     r.lo = -m; r.hi = m;
     r.findex = abs_normal_row;
     r.cfm = f ? C.slip2 : C.slip1;
+  }
+  if (wi.rpc == 4) {
+    // torsional friction (contact.cpp:362-437): a moment about the normal, limits +-(3 pi a mu3 / 16) x the normal force
+    // (findex = the normal row: dContactApprox3, ODEPhysics.cc:1099), a = the patch radius or sqrt(R x depth).
+    // A pair without it keeps an empty placeholder (no body entries are made for it, k_bsched).
+    Row &r = rows[3];
+    r.findex = abs_normal_row;
+    r.lo = 0; r.hi = 0;
+    if (C.tors) {
+      for (int i = 0; i < 3; i++) { r.J[i] = 0.0; r.J[3 + i] = normal[i]; }
+      if (b2) for (int i = 0; i < 3; i++) { r.J[6 + i] = -0.0; r.J[9 + i] = -normal[i]; }
+      const double patch_radius = C.tors == 2 ? sqrt(C.tors_radius * depth) : C.tors_radius;
+      const double lim = (3 * 3.14159265358979323846 * patch_radius * C.mu3) / 16;
+      r.lo = -lim; r.hi = lim;
+      if (C.slip3 > 0) r.cfm = C.slip3;
+    }
   }
 }
 

@@ -25,8 +25,8 @@ JP_RATIO, JP_REFBODY1, JP_REFBODY2 = 35, 14, 15
 JP_THREAD_PITCH, JP_OFFSET = 35, 16
 JP_COUNT = 36
 SF_MU, SF_MU2, SF_KP, SF_KD, SF_SLIP1, SF_SLIP2, SF_BOUNCE, SF_BOUNCE_VEL = range(8)
-SF_PATCH_RADIUS, SF_ELASTIC_MODULUS, SF_POISSON, SF_SURFACE_RADIUS, SF_USE_PATCH_RADIUS, SF_MU3 = 8, 9, 10, 11, 12, 13
-SF_COUNT = 14
+SF_PATCH_RADIUS, SF_ELASTIC_MODULUS, SF_POISSON, SF_SURFACE_RADIUS, SF_USE_PATCH_RADIUS, SF_MU3, SF_SLIP3 = 8, 9, 10, 11, 12, 13, 14
+SF_COUNT = 15
 GZ_ALL_COLLIDE = 0x0FFFFFFF
 GZ_FIXED_COLLIDE = 0x00000001
 
@@ -154,7 +154,7 @@ def cylinder_inertia(mass, r, l):
 
 DEFAULT_SURFACE = dict(mu=1.0, mu2=1.0, kp=1e12, kd=1.0, slip1=0.0, slip2=0.0,
                        bounce=0.0, bounce_vel=100000.0, patch_radius=0.0, elastic_modulus=0.0,
-                       poissons_ratio=0.3, surface_radius=sys.float_info.max, use_patch_radius=1.0, mu3=0.0)
+                       poissons_ratio=0.3, surface_radius=sys.float_info.max, use_patch_radius=1.0, mu3=0.0, slip3=0.0)
 
 
 class SceneBuilder:
@@ -231,7 +231,7 @@ class SceneBuilder:
         self.g["maxc"].append(int(max_contacts))
         self.g["surf"].append([s["mu"], s["mu2"], s["kp"], s["kd"], s["slip1"], s["slip2"],
                                s["bounce"], s["bounce_vel"], s["patch_radius"], s["elastic_modulus"],
-                               s["poissons_ratio"], s["surface_radius"], s["use_patch_radius"], s["mu3"]])
+                               s["poissons_ratio"], s["surface_radius"], s["use_patch_radius"], s["mu3"], s["slip3"]])
         self.g["fdir1"].append(list(map(float, fdir1)))
         self._ng += 1
         return self._ng - 1 - self._w_g0

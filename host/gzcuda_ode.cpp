@@ -197,7 +197,7 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
     gzcuda_surface s;
     memset(&s, 0, sizeof(s));
     s.mu = s.mu2 = 1.0; s.kp = 1e12; s.kd = 1.0; s.bounce_vel = 1e5; s.collide_bitmask = 0xFFFF; s.max_contacts = 20;
-    s.poissons_ratio = 0.3; s.surface_radius = DBL_MAX; s.use_patch_radius = 1; s.mu3 = 0.0;
+    s.poissons_ratio = 0.3; s.surface_radius = DBL_MAX; s.use_patch_radius = 1; s.mu3 = 1.0;
     s.order_key = (long)i;
     if (m->surface_fn && m->surface_fn(raw[i], &s, m->surface_user) != 0)
       return fail(GZCUDA_E_INVALID, "surface callback failed for a geom");
@@ -274,7 +274,7 @@ int build_mirror(Mirror *m, dxSpace *top, double h) {
     S[GZ_SF_SLIP2] = s.slip2; S[GZ_SF_BOUNCE] = s.bounce; S[GZ_SF_BOUNCE_VEL] = s.bounce_vel;
     S[GZ_SF_PATCH_RADIUS] = s.patch_radius; S[GZ_SF_ELASTIC_MODULUS] = s.elastic_modulus;
     S[GZ_SF_POISSON] = s.poissons_ratio; S[GZ_SF_SURFACE_RADIUS] = s.surface_radius;
-    S[GZ_SF_USE_PATCH_RADIUS] = s.use_patch_radius ? 1.0 : 0.0; S[GZ_SF_MU3] = s.mu3;
+    S[GZ_SF_USE_PATCH_RADIUS] = s.use_patch_radius ? 1.0 : 0.0; S[GZ_SF_MU3] = s.mu3; S[GZ_SF_SLIP3] = s.slip3;
     for (int k = 0; k < 3; k++) gfd[3 * i + k] = s.fdir1[k];
   }
   {   // geoms that sit directly in the top-level space form "spaces" of their own

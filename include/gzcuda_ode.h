@@ -36,9 +36,11 @@ typedef struct gzcuda_surface {
   int max_contacts;
   long order_key;
   /* FrictionPyramid::PoissonsRatio / SurfaceRadius / UsePatchRadius / MuTorsion; pre-set to Gazebo's defaults
-   * (0.3, DBL_MAX, 1, 0) before the callback runs.  mu3 > 0 (torsional friction) is refused: not built. */
+   * (0.3, DBL_MAX, 1, 1) before the callback runs.  Torsional friction is then switched on by a patch radius > 0
+   * (or use_patch_radius = 0), as in Gazebo (ODEPhysics.cc:1216-1232). */
   double poissons_ratio, surface_radius, mu3;
   int use_patch_radius;
+  double slip3;   /* ODESurfaceParams::slipTorsion */
 } gzcuda_surface;
 typedef int (*gzcuda_surface_fn)(struct dxGeom *geom, gzcuda_surface *out, void *user);
 

@@ -87,10 +87,13 @@ enum { GZ_SF_MU = 0, GZ_SF_MU2 = 1, GZ_SF_KP = 2, GZ_SF_KD = 3,
         * Poisson's ratio 0.3, surface radius DBL_MAX, use_patch_radius 1 (SurfaceParams.cc:28-32). */
        GZ_SF_PATCH_RADIUS = 8, GZ_SF_ELASTIC_MODULUS = 9, GZ_SF_POISSON = 10, GZ_SF_SURFACE_RADIUS = 11,
        GZ_SF_USE_PATCH_RADIUS = 12,
-       /* torsional friction (a fourth contact row, dContactMu3, contact.cpp:365-437) is NOT built: a scene that sets
-        * mu3 > 0 on a surface is refused by gzcuda_batch_create with GZCUDA_E_INVALID instead of being stepped without it */
-       GZ_SF_MU3 = 13,
-       GZ_SF_COUNT = 14 };
+       /* torsional friction (FrictionPyramid::MuTorsion / slipTorsion, ODEPhysics.cc:1168-1232): a pair gets a fourth
+        * contact row (dContactMu3, contact.cpp:362-437: a moment about the normal, limits +-3 pi a mu3 / 16 x the normal
+        * force, a = the patch radius or sqrt(surface radius x depth)) when min(mu3) > 0 and the radius it uses is > 0.
+        * NOTE Gazebo's own default for MuTorsion is 1 (torsion is then switched by the patch radius); this format's
+        * default is 0 = off.  Worlds of more than 256 bodies with mu3 > 0 are refused (GZCUDA_E_INVALID). */
+       GZ_SF_MU3 = 13, GZ_SF_SLIP3 = 14,
+       GZ_SF_COUNT = 15 };
 
 /* World-level parameters, shared by every world of a batch
  * (ODEPhysics::Load, gazebo/physics/ode/ODEPhysics.cc:175-243; dWorldCreate

@@ -218,15 +218,15 @@ void collide_pair(RefBatch *B, RefWorld *w, int i1, int i2) {
 
   contact.surface.mu = std::min(s1.s[GZ_SF_MU], s2.s[GZ_SF_MU]);
   contact.surface.mu2 = std::min(s1.s[GZ_SF_MU2], s2.s[GZ_SF_MU2]);
-  contact.surface.mu3 = 1.0;  // MuTorsion default; dContactMu3 stays off (patch radius 0)
+  contact.surface.mu3 = std::min(s1.s[GZ_SF_MU3], s2.s[GZ_SF_MU3]);   // (the scene format's default is 0 = off; Gazebo's MuTorsion default is 1)
   contact.surface.slip1 = s1.s[GZ_SF_SLIP1] + s2.s[GZ_SF_SLIP1];
   contact.surface.slip2 = s1.s[GZ_SF_SLIP2] + s2.s[GZ_SF_SLIP2];
-  contact.surface.slip3 = 0;
+  contact.surface.slip3 = s1.s[GZ_SF_SLIP3] + s2.s[GZ_SF_SLIP3];
   contact.surface.slip1 *= numc;
   contact.surface.slip2 *= numc;
   contact.surface.slip3 *= numc;
-  // ODEPhysics.cc:1186-1251: patch radius, curvatures, use_patch_radius; dContactMu3 stays off (the scene format refuses
-  // mu3 > 0); Hertzian contact (dContactEM) when both surfaces have an elastic modulus
+  // ODEPhysics.cc:1186-1251: patch radius, curvatures, use_patch_radius; torsional friction (dContactMu3) when mu3 > 0
+  // and the radius in use is > 0; Hertzian contact (dContactEM) when both surfaces have an elastic modulus
   contact.surface.patch_radius = std::max(s1.s[GZ_SF_PATCH_RADIUS], s2.s[GZ_SF_PATCH_RADIUS]);
   {
     double curv1 = 0, curv2 = 0;
@@ -236,6 +236,13 @@ void collide_pair(RefBatch *B, RefWorld *w, int i1, int i2) {
     contact.surface.surface_radius = 0;
     if (curvSum > 0) contact.surface.surface_radius = 1 / curvSum;
     contact.surface.use_patch_radius = s1.s[GZ_SF_USE_PATCH_RADIUS] != 0 && s2.s[GZ_SF_USE_PATCH_RADIUS] != 0;
+    if (contact.surface.mu3 > 0) {
+      if ((contact.surface.use_patch_radius && contact.surface.patch_radius > 0) ||
+          (!contact.surface.use_patch_radius && contact.surface.surface_radius > 0)) {
+        contact.surface.mode |= dContactMu3;
+        if (contact.surface.slip3 > 0) contact.surface.mode |= dContactSlip3;
+      }
+    }
     const double nu1 = s1.s[GZ_SF_POISSON], nu2 = s2.s[GZ_SF_POISSON];
     const double e1 = s1.s[GZ_SF_ELASTIC_MODULUS], e2 = s2.s[GZ_SF_ELASTIC_MODULUS];
     if (e1 > 0 && e2 > 0) {
@@ -882,6 +889,7 @@ struct AdapterSurface {
   double mu, mu2, kp, kd, slip1, slip2, bounce, bounce_vel, patch_radius, elastic_modulus, fdir1[3];
   unsigned collide_bitmask; int max_contacts; long order_key;
   double poissons_ratio, surface_radius, mu3; int use_patch_radius;
+  double slip3;
 };
 int gzref_surface_cb(dGeomID g, AdapterSurface *o, void *user) {
   RefWorld *w = static_cast<RefWorld *>(user);
@@ -892,7 +900,7 @@ int gzref_surface_cb(dGeomID g, AdapterSurface *o, void *user) {
   o->slip1 = s.s[GZ_SF_SLIP1]; o->slip2 = s.s[GZ_SF_SLIP2]; o->bounce = s.s[GZ_SF_BOUNCE]; o->bounce_vel = s.s[GZ_SF_BOUNCE_VEL];
   o->patch_radius = s.s[GZ_SF_PATCH_RADIUS]; o->elastic_modulus = s.s[GZ_SF_ELASTIC_MODULUS];
   o->poissons_ratio = s.s[GZ_SF_POISSON]; o->surface_radius = s.s[GZ_SF_SURFACE_RADIUS];
-  o->use_patch_radius = s.s[GZ_SF_USE_PATCH_RADIUS] != 0; o->mu3 = s.s[GZ_SF_MU3];
+  o->use_patch_radius = s.s[GZ_SF_USE_PATCH_RADIUS] != 0; o->mu3 = s.s[GZ_SF_MU3]; o->slip3 = s.s[GZ_SF_SLIP3];
   for (int k = 0; k < 3; k++) o->fdir1[k] = s.fdir1[k];
   o->collide_bitmask = s.collide_bitmask; o->max_contacts = s.max_contacts;
   o->order_key = i;   // Gazebo's creation order of the collisions = the scene's geom order

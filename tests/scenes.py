@@ -479,6 +479,45 @@ def hertz(n_worlds=2, seed=53):
     return sb.finish(), S.default_params(), None
 
 
+def spinners(n_worlds=3, seed=91):
+    """Torsional friction (dContactMu3: a fourth contact row, contact.cpp:362-437; switched on per pair as in
+    ODEPhysics.cc:1168-1232): spheres, upright cylinders, capsules and boxes set down spinning about the vertical on a
+    plane with mu3 = 0.8.  Two thirds use the patch radius (0.02..0.12 m), the others sqrt(surface radius x depth);
+    every fifth body has mu3 = 0 (its contacts keep three rows among four-row contacts), every fourth a torsional slip.
+    A few bodies are stacked so that torsional rows join two dynamic bodies."""
+    sb = S.SceneBuilder()
+    for w in range(n_worlds):
+        rng = np.random.Generator(np.random.PCG64(seed + w))
+        sb.begin_world()
+        sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), mu=1.0, mu2=1.0, mu3=0.8, patch_radius=0.05,
+                    use_patch_radius=1.0)
+        for k in range(12):
+            col, lvl = k % 6, k // 6
+            pos = np.array([1.2 * (col - 2.5), 0.0, 0.0])
+            spin = rng.uniform(4.0, 15.0) * (1 if k % 2 else -1)
+            kw = dict(mu3=0.0 if k % 5 == 4 else rng.uniform(0.2, 1.5), patch_radius=rng.uniform(0.02, 0.12),
+                      use_patch_radius=0.0 if (k + w) % 3 == 2 else 1.0, slip3=0.05 if k % 4 == 3 else 0.0, kp=1e6, kd=100.0)
+            t = k % 4
+            if t == 0:
+                r = rng.uniform(0.15, 0.3); pos[2] = r + 0.9 * lvl + 0.002
+                b = sb.add_body(pos, (1, 0, 0, 0), 1.0, S.sphere_inertia(1.0, r), avel=(0, 0, spin))
+                sb.add_geom(S.GEOM_SPHERE, (r,), sb.new_space(), body=b, surface_radius=r, **kw)
+            elif t == 1:
+                r, l = rng.uniform(0.15, 0.3), rng.uniform(0.2, 0.4); pos[2] = 0.5 * l + 0.9 * lvl + 0.002
+                b = sb.add_body(pos, (1, 0, 0, 0), 1.0, S.cylinder_inertia(1.0, r, l), avel=(0, 0, spin))
+                sb.add_geom(S.GEOM_CYLINDER, (r, l), sb.new_space(), body=b, surface_radius=5.0, **kw)
+            elif t == 2:
+                d = tuple(rng.uniform(0.3, 0.5, 3)); pos[2] = 0.5 * d[2] + 0.9 * lvl + 0.002
+                b = sb.add_body(pos, (1, 0, 0, 0), 1.0, S.box_inertia(1.0, *d), avel=(0, 0, spin))
+                sb.add_geom(S.GEOM_BOX, d, sb.new_space(), body=b, surface_radius=2.0, **kw)
+            else:
+                r, l = rng.uniform(0.12, 0.2), rng.uniform(0.2, 0.4); pos[2] = 0.5 * l + r + 0.9 * lvl + 0.002
+                b = sb.add_body(pos, (1, 0, 0, 0), 1.0, S.cylinder_inertia(1.0, r, l), avel=(0.3, 0, spin))
+                sb.add_geom(S.GEOM_CAPSULE, (r, l), sb.new_space(), body=b, surface_radius=r, **kw)
+        sb.end_world()
+    return sb.finish(), S.default_params(), None
+
+
 def ray_targets(n_worlds=2, per_type=6, seed=77):
     """Worlds for the laser: a ground plane and, floating at rest (no gravity flag needed: they are never stepped far), boxes,
     spheres, capsules and cylinders at random poses inside a 6 m cube, one sensor-category geom that rays must not see."""
@@ -537,4 +576,5 @@ GOLDEN = {
     "gimbals": (gimbals, 800),
     "gears": (gears, 700),
     "screws": (screws, 900),
+    "spinners": (spinners, 800),
 }

@@ -139,6 +139,13 @@ def test_adapter_hertzian_contacts(adapter, oracle):
 
 
 @pytest.mark.gpu
+def test_adapter_torsional_friction(adapter, oracle):
+    """MuTorsion, slipTorsion and the radii travel through the surface callback; four-row contacts over live ODE objects."""
+    sc, p, _ = scenes.spinners()
+    _run(adapter, oracle, sc, p, steps=400, every=100)
+
+
+@pytest.mark.gpu
 def test_adapter_laser_over_live_ode_objects(adapter, oracle):
     """gzcuda_dworld_ray_query: the laser against a LIVE ODE world (what ODEMultiRayShape::UpdateRays does with
     dSpaceCollide2) - ranges bit-exact against the reference's own ray colliders on the same objects, and the dxGeom

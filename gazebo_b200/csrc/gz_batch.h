@@ -182,6 +182,7 @@ struct DevBatch {
   int pgsc_bpw;          // k_pgsc: bodies per warp (<= 16; the other lanes of the warp idle: a warp is ONE instruction stream
                          // that runs its bodies' rows one after the other, so fewer bodies per warp = more streams)
   double *joint_ext;     // [nj][GZ_JP_COUNT - GZ_JP_HOT] the joint_param slots only hinge2 / universal joints read
+  int *bs_cntt;          // [nb] k_bsched_large: torsional rows per body (null unless a large world has four-row contacts)
   double *geom_ext;      // [ng][GZ_SF_COUNT - GZ_SF_HOT] patch radius, elastic modulus, Poisson's ratio, surface radius, use_patch_radius, mu3, slip3
   int *cta_e0;           // [n_worlds][GZ_PGSC_TAB] first entry of every CTA of k_pgsc (then the world's end), else null
   int *bs_clist;         // [2 * contacts] k_bsched_large's per-body contact lists (large worlds only, else null)

@@ -449,8 +449,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if (v == 0 && max_nb <= 512) d.pgs_impl = 0;
     if (v == 2) d.pgs_impl = 2;
   }
-  if (any_tors && d.pgs_impl != 1)   // (the four-row contact layout is known to k_bsched / k_pgsb only)
-    return fail(GZCUDA_E_INVALID, "torsional friction (mu3 > 0 on two surfaces of a world) is built for worlds of up to 256 bodies");
+  if (any_tors && d.pgs_impl == 0)   // (the round-1 row-owner path, batches of 257..512-body worlds, does not know the four-row contact layout)
+    d.pgs_impl = 2;
   if (d.pgs_impl == 2) {
     // one lane per (body, solve) of the largest world, all CTAs resident (cooperative launch)
     int n_sm = 148, per_sm = 0;
@@ -484,6 +484,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       else if ((rc = dev_alloc(b, &b->large_part, (size_t)b->large_grid + 1))) return rc;
     }
     if ((rc = dev_alloc(b, &d.bs_glob, (size_t)W * 5 * std::max(max_nb, 1)))) return rc;
+    if (any_tors && (rc = dev_alloc(b, &d.bs_cntt, (size_t)std::max(nb, 1)))) return rc;
   }
   if (d.pgs_impl >= 1) {
     b->bsched_smem = (size_t)5 * std::max(max_nb, 1) * sizeof(int);

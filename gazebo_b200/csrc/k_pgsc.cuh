@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(256, 2) k_pgsc(DevBatch B, const int w, unsign
       const int cls = (r_mx >> 27) & 3;
       const bool isb2 = (r_mx >> 29) & 1;
       // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594)
-      const double nlam = (!BOX && cls == 2) ? r_nlam : 1.0;
+      const double nlam = (cls == 2 && (!BOX || ((r_mx >> 30) & 1))) ? r_nlam : 1.0;   // (bit 30: a torsional row)
       const double old_lambda = r_lam;
       double delta = r_rhs - old_lambda * r_adcfm;
       const double hl = r_hi * nlam;

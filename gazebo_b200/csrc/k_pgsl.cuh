@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256) k_pgsl(DevBatch B, const int w, double *x
       rhs = v[6 + S].x; old_lambda = v[6 + S].y; adcfm = v[8].x; lo = v[8].y; hi = v[9].x;
       mx = __double2loint(v[9].y); my = __double2hiint(v[9].y);
       // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594)
-      if (!BOX && ((mx >> 27) & 3) == 2) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_ENT)[13 + 2 * S];
+      if (((mx >> 27) & 3) == 2 && (!BOX || ((mx >> 30) & 1))) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_ENT)[13 + 2 * S];
       // this body's half of the dot product, term by term in the reference's left-to-right order
       d = a[0] * J[0];
 #pragma unroll
@@ -200,8 +200,9 @@ __global__ void __launch_bounds__(256) k_bsched_large(DevBatch B, const int w, u
   const int gt = blockIdx.x * blockDim.x + threadIdx.x, GT = gridDim.x * blockDim.x;
   const WorldInfo wi = B.world[w];
   WorldStep &ws = B.wstep[w];
-  const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, mj = m - 3 * nc, pfric = mj + nc;
+  const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, rpc = wi.rpc, mj = m - rpc * nc, pfric = mj + nc;
   int *tab = B.bs_glob + (size_t)w * 5 * B.max_nb;
+  int *cntt = rpc == 4 ? B.bs_cntt + wi.body0 : nullptr;   // torsional rows per body (worlds of four-row contacts)
   int *cntc = tab, *njr = tab + B.max_nb, *base = tab + 2 * B.max_nb, *cbase = tab + 3 * B.max_nb, *fill = tab + 4 * B.max_nb;
   const WScratchB S = wscratchb(B, w);
   int *lp = S.idx2 + B.max_row_cap;   // [2 * max_row_cap]
@@ -214,6 +215,7 @@ __global__ void __launch_bounds__(256) k_bsched_large(DevBatch B, const int w, u
   // ---- 1
   for (int b = gt; b < nb; b += GT) {
     cntc[b] = 0; fill[b] = 0;
+    if (cntt) cntt[b] = 0;
     const Body &bd = B.body[wi.body0 + b];
     int r = 0;
     if (m > 0) for (int q = bd.joint_begin; q < bd.joint_end; q++) r += B.joint[B.body_joint[q]].m;
@@ -230,9 +232,11 @@ __global__ void __launch_bounds__(256) k_bsched_large(DevBatch B, const int w, u
     const Contact &C = B.contact[wi.contact0 + c];
     const bool live = B.bstep[C.b1].active != 0;   // a contact of an island that is not stepped: rows without entries
     const int b1 = live ? C.b1 - wi.body0 : -2, b2 = C.b2 >= 0 ? C.b2 - wi.body0 : -1;
-    const int pn = mj + (nc - 1 - c), pf = pfric + 2 * c;
+    const int pn = mj + (nc - 1 - c), pf = pfric + (rpc - 1) * c;
     S.rb1[pn] = b1; S.rb2[pn] = b2; S.rb1[pf] = b1; S.rb2[pf] = b2; S.rb1[pf + 1] = b1; S.rb2[pf + 1] = b2;
+    if (rpc == 4) { S.rb1[pf + 2] = C.tors ? b1 : -2; S.rb2[pf + 2] = b2; }   // (no torsional friction: a placeholder, never swept)
     if (live) { atomicAdd(&cntc[b1], 1); if (b2 >= 0) atomicAdd(&cntc[b2], 1); }
+    if (live && cntt && C.tors) { atomicAdd(&cntt[b1], 1); if (b2 >= 0) atomicAdd(&cntt[b2], 1); }
   }
   pgsl_barrier(bar, bar_target);
   // ---- 2 (CTA 0): base = exclusive scan of njr + 3 cntc, cbase = exclusive scan of cntc
@@ -243,7 +247,7 @@ __global__ void __launch_bounds__(256) k_bsched_large(DevBatch B, const int w, u
     for (int b0 = 0; b0 < nb; b0 += 256) {
       const int b = b0 + t;
       for (int which = 0; which < 2; which++) {
-        const int c = b < nb ? (which ? cntc[b] : njr[b] + 3 * cntc[b]) : 0;
+        const int c = b < nb ? (which ? cntc[b] : njr[b] + 3 * cntc[b] + (cntt ? cntt[b] : 0)) : 0;
         int v = c;
         for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += u; }
         if (lane == 31) s_scan[wp] = v;
@@ -302,17 +306,20 @@ __global__ void __launch_bounds__(256) k_bsched_large(DevBatch B, const int w, u
         const bool is1 = (j.b1 - wi.body0) == b;
         for (int r = 0; r < j.m; r++) { (is1 ? S.idx1 : S.idx2)[j.row0 + r] = at; lpb[at] = j.row0 + r; at++; }
       }
+    int tb = 0;   // torsional rows of the body's earlier contacts
     for (int k = 0; k < ncb; k++) {
       const int c = cl[k];
-      const bool is1 = (B.contact[wi.contact0 + c].b1 - wi.body0) == b;
+      const Contact &C = B.contact[wi.contact0 + c];
+      const bool is1 = (C.b1 - wi.body0) == b;
       int *idx = is1 ? S.idx1 : S.idx2;
-      const int pn = mj + (nc - 1 - c), pf = pfric + 2 * c;
-      const int in = nj_rows + (ncb - 1 - k), if0 = nj_rows + ncb + 2 * k;
+      const int pn = mj + (nc - 1 - c), pf = pfric + (rpc - 1) * c;
+      const int in = nj_rows + (ncb - 1 - k), if0 = nj_rows + ncb + 2 * k + tb;
       idx[pn] = in; lpb[in] = pn;
       idx[pf] = if0; lpb[if0] = pf;
       idx[pf + 1] = if0 + 1; lpb[if0 + 1] = pf + 1;
+      if (rpc == 4 && C.tors) { idx[pf + 2] = if0 + 2; lpb[if0 + 2] = pf + 2; tb++; }
     }
-    B.bsched[wi.body0 + b] = nent > 0 ? make_int4(wbase + base[b], nj_rows + 3 * ncb, nj_rows + ncb, 0) : make_int4(0, 0, 0, 0);
+    B.bsched[wi.body0 + b] = nent > 0 ? make_int4(wbase + base[b], nj_rows + 3 * ncb + tb, nj_rows + ncb, 0) : make_int4(0, 0, 0, 0);
   }
   for (int pos = gt; pos < m; pos += GT) S.off[pos] = (nent > 0 && S.rb1[pos] >= 0) ? 0 : -1;
   if (B.cta_e0)   // k_pgsc: where the entries of every 256 bodies begin
@@ -451,7 +458,7 @@ __global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned 
     cls = (mx >> 27) & 3; isb2 = (mx >> 29) & 1;
     // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594)
     double nlam = 1.0;
-    if (!BOX && cls == 2) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_ENT)[13 + 2 * S];
+    if (cls == 2 && (!BOX || ((mx >> 30) & 1))) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_ENT)[13 + 2 * S];   // (bit 30: a torsional row)
     old_lambda = vs.y;
     delta0 = vs.x - old_lambda * v8.x;
     const double hl = v9.x * nlam;

@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(256, 1) k_pgsm(DevBatch B, const int w, const 
     cls = (mx >> 27) & 3; isb2 = (mx >> 29) & 1;
     // pyramid friction: limits +-|mu * lambda_normal| (quickstep_pgs_lcp.cpp:572-582); box: +-mu (:588-594)
     double nlam = 1.0;
-    if (!BOX && cls == 2) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_PGSM_STRIDE)[13 + 2 * S];
+    if (cls == 2 && (!BOX || ((mx >> 30) & 1))) nlam = (p - (size_t)((unsigned)my >> 16) * GZ_PGSM_STRIDE)[13 + 2 * S];
     old_lambda = vs.y;
     delta0 = vs.x - old_lambda * v8.x;
     const double hl = v9.x * nlam;

@@ -698,7 +698,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         if ((rc = dev_alloc(b, &Q.fill, (size_t)max_ng))) return rc;
         if ((rc = dev_alloc(b, &Q.tmp, (size_t)std::max(max_pc, 1)))) return rc;
         if ((rc = dev_alloc(b, &Q.queue, (size_t)2 * max_ng + 2))) return rc;
-        if ((rc = dev_alloc(b, &Q.ctl, (size_t)2 + GZ_BPL_NBIG))) return rc;
+        if ((rc = dev_alloc(b, &Q.ctl, (size_t)3 + GZ_BPL_NBIG))) return rc;
         if ((rc = dev_alloc(b, &Q.yz, (size_t)4 * nt))) return rc;
         if ((rc = dev_alloc(b, &Q.bits, (size_t)GZ_BPL_NBIG * 2 * nwords))) return rc;
         b->bp_smem = 16;
@@ -834,15 +834,14 @@ static int launch_collision(gzcuda_batch *b) {
       const int ntile = cdiv(b->h_world[w].ng + 1, GZ_BPL_TILE);
       k_bpl_tilesort<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_merge<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
-      k_bpl_sweep<0><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
-      k_bpl_tail<0><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_sweep<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_tail<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_scan<<<1, 1024, 0, b->stream>>>(d, w, b->bpl);
-      k_bpl_sweep<1><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
-      k_bpl_tail<1><<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_place<<<148, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_emit<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_emit_big<<<GZ_BPL_NBIG, 1024, 0, b->stream>>>(d, w, b->bpl);
     }
-    b->last_launches += 9 * W - 1;
+    b->last_launches += 8 * W - 1;
   } else k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
   if (b->has_cylinders) k_narrow<true><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
   else k_narrow<false><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);

@@ -8,13 +8,15 @@
 //   k_bpl_tilesort  one CTA per 1024 geoms: bitonic sort of (lower x bound, geom) in shared memory
 //   k_bpl_merge     one thread per geom: its final place = its place in its tile + the number of smaller elements in
 //                   every other tile (binary searches); writes the sorted arrays and the upper bounds in sorted order
-//   k_bpl_sweep     one warp per sorted position, all SMs; pass 0 counts the pairs of every lower-index geom,
-//                   pass 1 stores the higher-index partners at the places the scan assigned.  A position whose x
-//                   interval covers more than GZ_BPL_CHUNKS x 32 followers (the ground plane, the pen's walls) hands
-//                   the rest to the queue
+//   k_bpl_sweep     one warp per sorted position, all SMs: y / z bounds of the followers from a side array in sorted
+//                   order (coalesced), the full test for the survivors; a pair is counted under its lower-index geom
+//                   and logged.  A position whose x interval covers more than GZ_BPL_CHUNKS x 32 followers (the
+//                   ground plane, the pen's walls) hands the rest to the queue
 //   k_bpl_tail      the queue: all warps share the followers of each queued position (without it the plane's warp
 //                   walked all 20 000 geoms alone and WAS the kernel's duration)
 //   k_bpl_scan      one CTA: exclusive scan of the counts, n_pairs, capacity flag
+//   k_bpl_place     one thread per logged pair: the higher-index partner to its place in the lower geom's list
+//                   (first version: a second sweep, 0.19 ms at C4)
 //   k_bpl_emit      one warp per geom: puts its partners in ascending order by counting; long lists (the plane's:
 //                   thousands) go to k_bpl_emit_big: one CTA each, a bitmap over the geoms and its prefix popcount
 #pragma once
@@ -31,7 +33,7 @@ struct BplBuf {
   double *yz;   // [n][4] lower / upper y and z bounds in sorted order: the sweep's pre-filter reads them coalesced
   int *idx, *cnt, *fill, *tmp, *tidx;
   int *queue;   // [2 * n] (sorted position, first follower not tested yet)
-  int *ctl;     // [0] queue length, [1] long lists claimed, [2 ..] their geoms
+  int *ctl;     // [0] queue length, [1] long lists claimed, [2 ..] their geoms, [2 + GZ_BPL_NBIG] pairs logged
   int *bits;    // [GZ_BPL_NBIG][2][(n + 31) / 32 + 1] bitmap and its exclusive prefix popcount
   int npad;
   int chunks, big;   // GZ_BPL_CHUNKS, GZ_BPL_BIG unless a developer switch says otherwise
@@ -51,7 +53,7 @@ __global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_tilesort(DevBatch B, const 
   sk[tid] = key;
   si[tid] = g;
   if (g <= n) { Q.cnt[g] = 0; if (g < n) Q.fill[g] = 0; }
-  if (g == 0) { Q.ctl[0] = 0; Q.ctl[1] = 0; B.wstep[w].overflow = 0; }   // (k_broadphase's role: the step's capacity mask starts here)
+  if (g == 0) { Q.ctl[0] = 0; Q.ctl[1] = 0; Q.ctl[2 + GZ_BPL_NBIG] = 0; B.wstep[w].overflow = 0; }   // (k_broadphase's role: the step's capacity mask starts here)
   __syncthreads();
   for (int k = 2; k <= GZ_BPL_TILE; k <<= 1)
     for (int j = k >> 1; j > 0; j >>= 1) {
@@ -93,7 +95,8 @@ __global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_merge(DevBatch B, const int
 }
 
 // the full test of sorted position q against position p's geom ip; returns whether q is still inside p's x interval
-template <int PASS>
+// A pair that passes is counted under its lower geom and logged (in the world's slice of B.pair, which k_bpl_emit fills
+// only later): k_bpl_place puts the logged pairs into the per-geom lists once the counts are scanned - the sweep runs once.
 __device__ __forceinline__ bool bpl_follow(const DevBatch &B, const WorldInfo &wi, const Geom *G, const BplBuf &Q, const int ip,
                                            const double mx, const double *pyz, const int q, const int n) {
   const bool in = (q < n) && Q.key[q] <= mx;
@@ -105,17 +108,14 @@ __device__ __forceinline__ bool bpl_follow(const DevBatch &B, const WorldInfo &w
     const int iq = Q.idx[q];
     const int lo = min(ip, iq), hi = max(ip, iq);
     if (pair_passes(B, G[lo], G[hi])) {
-      if (PASS == 0) atomicAdd(&Q.cnt[lo], 1);
-      else {
-        const int at = Q.cnt[lo] + atomicAdd(&Q.fill[lo], 1);   // cnt holds the exclusive scan now
-        if (at < wi.pair_cap) Q.tmp[at] = hi;
-      }
+      atomicAdd(&Q.cnt[lo], 1);
+      const int at = atomicAdd(&Q.ctl[2 + GZ_BPL_NBIG], 1);
+      if (at < wi.pair_cap) { B.pair[2 * (wi.pair0 + at)] = lo; B.pair[2 * (wi.pair0 + at) + 1] = hi; }   // (beyond: k_bpl_scan raises the flag)
     }
   }
   return in;
 }
 
-template <int PASS>
 __global__ void __launch_bounds__(256) k_bpl_sweep(DevBatch B, const int w, BplBuf Q) {
   const WorldInfo wi = B.world[w];
   const int n = wi.ng, lane = threadIdx.x & 31;
@@ -127,17 +127,16 @@ __global__ void __launch_bounds__(256) k_bpl_sweep(DevBatch B, const int w, BplB
     const double pyz[4] = {Q.yz[4 * (size_t)p], Q.yz[4 * (size_t)p + 1], Q.yz[4 * (size_t)p + 2], Q.yz[4 * (size_t)p + 3]};
     int c = 0;
     for (int q0 = p + 1; q0 < n; q0 += 32, c++) {
-      if (c == Q.chunks) {   // a long interval: the rest goes to k_bpl_tail (queued once, by pass 0)
-        if (PASS == 0 && lane == 0) { const int at = atomicAdd(&Q.ctl[0], 1); Q.queue[2 * at] = p; Q.queue[2 * at + 1] = q0; }
+      if (c == Q.chunks) {   // a long interval: the rest goes to k_bpl_tail
+        if (lane == 0) { const int at = atomicAdd(&Q.ctl[0], 1); Q.queue[2 * at] = p; Q.queue[2 * at + 1] = q0; }
         break;
       }
-      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
+      const bool in = bpl_follow(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
       if (!__all_sync(0xffffffffu, in)) break;   // sorted: nothing further overlaps p on x
     }
   }
 }
 
-template <int PASS>
 __global__ void __launch_bounds__(256) k_bpl_tail(DevBatch B, const int w, BplBuf Q) {
   const WorldInfo wi = B.world[w];
   const int n = wi.ng, lane = threadIdx.x & 31;
@@ -150,7 +149,7 @@ __global__ void __launch_bounds__(256) k_bpl_tail(DevBatch B, const int w, BplBu
     const double mx = Q.maxx[p];
     const double pyz[4] = {Q.yz[4 * (size_t)p], Q.yz[4 * (size_t)p + 1], Q.yz[4 * (size_t)p + 2], Q.yz[4 * (size_t)p + 3]};
     for (int q0 = qs + 32 * warp; q0 < n; q0 += 32 * nwarp) {
-      const bool in = bpl_follow<PASS>(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
+      const bool in = bpl_follow(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
       if (!__all_sync(0xffffffffu, in)) break;   // sorted: this warp's later chunks are outside as well
     }
   }
@@ -188,6 +187,17 @@ __global__ void __launch_bounds__(1024) k_bpl_scan(DevBatch B, const int w, BplB
     WorldStep &ws = B.wstep[w];
     if (total > wi.pair_cap) { ws.overflow |= 1; total = wi.pair_cap; }
     ws.n_pairs = total;
+  }
+}
+
+// One thread per logged pair: its place in the list of its lower geom (cnt holds the exclusive scan now).
+__global__ void __launch_bounds__(256) k_bpl_place(DevBatch B, const int w, BplBuf Q) {
+  const WorldInfo wi = B.world[w];
+  const int total = min(Q.ctl[2 + GZ_BPL_NBIG], wi.pair_cap);
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const int lo = B.pair[2 * (wi.pair0 + e)], hi = B.pair[2 * (wi.pair0 + e) + 1];
+    const int at = Q.cnt[lo] + atomicAdd(&Q.fill[lo], 1);
+    if (at < wi.pair_cap) Q.tmp[at] = hi;
   }
 }
 

@@ -471,9 +471,10 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
     if ((rc = dev_alloc(b, &d.xch_g, (size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid + 8))) return rc;
     CK(cudaMemset(d.xch_g, 0, ((size_t)2 * b->pgsl_grid * 256 + (size_t)9 * b->pgsl_grid + 8) * sizeof(double)));
     if ((rc = dev_alloc(b, &d.bs_clist, (size_t)2 * contact_tot + 2))) return rc;
-    // the one-CTA-per-world kernels of the step spread over a cooperative grid: worlds beyond 512 bodies (test switch
-    // GZCUDA_LARGE_KERNELS forces them onto small worlds)
-    b->large_kernels = max_nb > 512;
+    // the one-CTA-per-world kernels of the step spread over a cooperative grid: worlds beyond 512 bodies, and batches of
+    // up to four worlds of more than 256 (C1, 500 boxes in one world: collide + assemble 0.45 -> 0.26 ms); the test switch
+    // GZCUDA_LARGE_KERNELS forces them onto small worlds
+    b->large_kernels = max_nb > 512 || W <= 4;
     if (const char *el = getenv("GZCUDA_LARGE_KERNELS")) b->large_kernels = atoi(el) != 0;
     if (b->large_kernels) {
       int p1 = 0, p2 = 0;
@@ -673,7 +674,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
       size_t npad = 32;
       while (npad < (size_t)max_ng) npad <<= 1;
       const size_t need = npad * 20 + ((size_t)max_ng + 1) * 4 + (size_t)max_ng * (((size_t)max_ng + 31) / 32) * 4 + 16;
-      const bool force_large = getenv("GZCUDA_BP_LARGE") && atoi(getenv("GZCUDA_BP_LARGE")) != 0;   // test hook
+      bool force_large = d.pgs_impl == 2 && W <= 4;   // a few worlds of hundreds of geoms: one CTA each leaves the GPU idle (C1: 0.26 -> 0.14 ms)
+      if (const char *e = getenv("GZCUDA_BP_LARGE")) force_large = atoi(e) != 0;   // test hook
       if (need <= (size_t)220 * 1024 && !force_large) {
         b->bp_smem = std::max(b->bp_smem, need);
         b->bp_threads = 512;

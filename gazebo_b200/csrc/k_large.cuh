@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(256) k_assemble1_large(DevBatch B, const int w
   }
   pgsl_barrier(bar, bar_target);
   for (int i = gt; i < wi.nb; i += GT) bodyprep_body(B, wi.body0 + i);
-  if (blockIdx.x == 0) info1_world(B, w);   // (joint rows need a scan over the joints: one CTA; contacts are 3 rows each)
+  if (blockIdx.x == 0) info1_world(B, w);   // (joint rows need a scan over the joints: one CTA; contacts are 3 or 4 rows each)
 }
 
 }  // namespace gz

@@ -688,8 +688,9 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         const size_t nt = ((size_t)max_ng + 1 + GZ_BPL_TILE - 1) / GZ_BPL_TILE * GZ_BPL_TILE;   // whole tiles, at least one padding element
         const size_t nwords = ((size_t)max_ng + 31) / 32 + 1;
         Q.npad = (int)nt;
-        Q.chunks = GZ_BPL_CHUNKS; Q.big = GZ_BPL_BIG;
-        if (const char *e = getenv("GZCUDA_BPL_CHUNKS")) Q.chunks = std::max(1, atoi(e));   // developer / test switches
+        Q.big = GZ_BPL_BIG;
+        Q.item_cap = (int)std::min<size_t>(8 * nt, (size_t)1 << 30);
+        if (const char *e = getenv("GZCUDA_BPL_ITEM_CAP")) Q.item_cap = std::max(0, std::min(Q.item_cap, atoi(e)));   // developer / test switches (a small table: everything through the queue)
         if (const char *e = getenv("GZCUDA_BPL_BIG")) Q.big = std::max(1, atoi(e));
         if ((rc = dev_alloc(b, &Q.key, nt))) return rc;
         if ((rc = dev_alloc(b, &Q.tkey, nt))) return rc;
@@ -700,7 +701,8 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
         if ((rc = dev_alloc(b, &Q.fill, (size_t)max_ng))) return rc;
         if ((rc = dev_alloc(b, &Q.tmp, (size_t)std::max(max_pc, 1)))) return rc;
         if ((rc = dev_alloc(b, &Q.queue, (size_t)2 * max_ng + 2))) return rc;
-        if ((rc = dev_alloc(b, &Q.ctl, (size_t)3 + GZ_BPL_NBIG))) return rc;
+        if ((rc = dev_alloc(b, &Q.ctl, (size_t)4 + GZ_BPL_NBIG))) return rc;
+        if ((rc = dev_alloc(b, &Q.item, (size_t)std::max(Q.item_cap, 1)))) return rc;
         if ((rc = dev_alloc(b, &Q.yz, (size_t)4 * nt))) return rc;
         if ((rc = dev_alloc(b, &Q.bits, (size_t)GZ_BPL_NBIG * 2 * nwords))) return rc;
         b->bp_smem = 16;
@@ -836,14 +838,15 @@ static int launch_collision(gzcuda_batch *b) {
       const int ntile = cdiv(b->h_world[w].ng + 1, GZ_BPL_TILE);
       k_bpl_tilesort<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_merge<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
-      k_bpl_sweep<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_span<<<cdiv(nwarps, 256), 256, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_sweep<<<std::min(148 * 8, cdiv(4 * nwarps, 8)), 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_tail<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_scan<<<1, 1024, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_place<<<148, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_emit<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_emit_big<<<GZ_BPL_NBIG, 1024, 0, b->stream>>>(d, w, b->bpl);
     }
-    b->last_launches += 8 * W - 1;
+    b->last_launches += 9 * W - 1;
   } else k_broadphase<<<W, b->bp_threads, b->bp_smem, b->stream>>>(d);
   if (b->has_cylinders) k_narrow<true><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);
   else k_narrow<false><<<dim3(item_blocks(d.max_pair_cap, 32, W), W), 32, 0, b->stream>>>(d);

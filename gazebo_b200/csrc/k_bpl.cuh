@@ -8,10 +8,12 @@
 //   k_bpl_tilesort  one CTA per 1024 geoms: bitonic sort of (lower x bound, geom) in shared memory
 //   k_bpl_merge     one thread per geom: its final place = its place in its tile + the number of smaller elements in
 //                   every other tile (binary searches); writes the sorted arrays and the upper bounds in sorted order
-//   k_bpl_sweep     one warp per sorted position, all SMs: y / z bounds of the followers from a side array in sorted
-//                   order (coalesced), the full test for the survivors; a pair is counted under its lower-index geom
-//                   and logged.  A position whose x interval covers more than GZ_BPL_CHUNKS x 32 followers (the
-//                   ground plane, the pen's walls) hands the rest to the queue
+//   k_bpl_span      one thread per sorted position: the end of its x interval (binary search), its followers cut into
+//                   work items of GZ_BPL_SEG; intervals of more than 32 items (the ground plane, the pen's walls) go to
+//                   the queue
+//   k_bpl_sweep     one warp per work item, all SMs: y / z bounds of the followers from a side array in sorted order
+//                   (coalesced, four per lane in flight), the full test for the survivors; a pair is counted under its
+//                   lower-index geom and logged
 //   k_bpl_tail      the queue: all warps share the followers of each queued position (without it the plane's warp
 //                   walked all 20 000 geoms alone and WAS the kernel's duration)
 //   k_bpl_scan      one CTA: exclusive scan of the counts, n_pairs, capacity flag
@@ -24,7 +26,7 @@
 namespace gz {
 
 #define GZ_BPL_TILE 1024
-#define GZ_BPL_CHUNKS 64    // followers a warp of k_bpl_sweep tests by itself, in units of 32
+#define GZ_BPL_SEG 512      // followers per work item of k_bpl_sweep (a multiple of 32 x GZ_BPL_U)
 #define GZ_BPL_NBIG 8       // lists k_bpl_emit can order through a bitmap at the same time
 #define GZ_BPL_BIG 256      // ... from this length on
 
@@ -33,10 +35,11 @@ struct BplBuf {
   double *yz;   // [n][4] lower / upper y and z bounds in sorted order: the sweep's pre-filter reads them coalesced
   int *idx, *cnt, *fill, *tmp, *tidx;
   int *queue;   // [2 * n] (sorted position, first follower not tested yet)
-  int *ctl;     // [0] queue length, [1] long lists claimed, [2 ..] their geoms, [2 + GZ_BPL_NBIG] pairs logged
+  int *ctl;     // [0] queue length, [1] long lists claimed, [2 ..] their geoms, [2 + GZ_BPL_NBIG] pairs logged, [3 + GZ_BPL_NBIG] work items
   int *bits;    // [GZ_BPL_NBIG][2][(n + 31) / 32 + 1] bitmap and its exclusive prefix popcount
   int npad;
-  int chunks, big;   // GZ_BPL_CHUNKS, GZ_BPL_BIG unless a developer switch says otherwise
+  int *item;    // [item_cap] k_bpl_sweep's work items: sorted position | segment << 27
+  int item_cap, big;   // big: GZ_BPL_BIG unless a developer switch says otherwise
 };
 
 // total order of the sort: by key, ties by geom index (padding: key +inf, index >= n, sorts last)
@@ -53,7 +56,7 @@ __global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_tilesort(DevBatch B, const 
   sk[tid] = key;
   si[tid] = g;
   if (g <= n) { Q.cnt[g] = 0; if (g < n) Q.fill[g] = 0; }
-  if (g == 0) { Q.ctl[0] = 0; Q.ctl[1] = 0; Q.ctl[2 + GZ_BPL_NBIG] = 0; B.wstep[w].overflow = 0; }   // (k_broadphase's role: the step's capacity mask starts here)
+  if (g == 0) { Q.ctl[0] = 0; Q.ctl[1] = 0; Q.ctl[2 + GZ_BPL_NBIG] = 0; Q.ctl[3 + GZ_BPL_NBIG] = 0; B.wstep[w].overflow = 0; }   // (k_broadphase's role: the step's capacity mask starts here)
   __syncthreads();
   for (int k = 2; k <= GZ_BPL_TILE; k <<= 1)
     for (int j = k >> 1; j > 0; j >>= 1) {
@@ -94,17 +97,33 @@ __global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_merge(DevBatch B, const int
   }
 }
 
-// the full test of sorted position q against position p's geom ip; returns whether q is still inside p's x interval
-// A pair that passes is counted under its lower geom and logged (in the world's slice of B.pair, which k_bpl_emit fills
-// only later): k_bpl_place puts the logged pairs into the per-geom lists once the counts are scanned - the sweep runs once.
+#define GZ_BPL_U 4   // followers per lane and trip: their keys and bounds are loaded together (a trip is one L2 latency, not four)
+
+// Sorted positions q0 + 32 u + lane (u < GZ_BPL_U) against position p's geom ip: x from the sorted keys, y and z from the
+// sorted side array (collideAABBs' own comparisons, collision_space_internal.h:66-72: of the ~800 followers that overlap a
+// pile's geom on x, a few dozen overlap it on y and z as well), the full test for the survivors.  A pair that passes is
+// counted under its lower geom and logged (in the world's slice of B.pair, which k_bpl_emit fills only later):
+// k_bpl_place puts the logged pairs into the per-geom lists once the counts are scanned - the sweep runs once.
+// Returns whether all of this lane's positions are still inside p's x interval.
 __device__ __forceinline__ bool bpl_follow(const DevBatch &B, const WorldInfo &wi, const Geom *G, const BplBuf &Q, const int ip,
-                                           const double mx, const double *pyz, const int q, const int n) {
-  const bool in = (q < n) && Q.key[q] <= mx;
-  if (in) {
-    // y and z first, from the sorted side array (collideAABBs' own comparisons, collision_space_internal.h:66-72: of the
-    // ~1 200 followers that overlap a pile's geom on x, a few dozen overlap it on y and z as well)
-    const double *c = Q.yz + 4 * (size_t)q;
-    if (pyz[0] > c[1] || pyz[1] < c[0] || pyz[2] > c[3] || pyz[3] < c[2]) return true;
+                                           const double mx, const double *pyz, const int q0, const int n) {
+  double k[GZ_BPL_U];
+  double2 lo2[GZ_BPL_U], hi2[GZ_BPL_U];
+#pragma unroll
+  for (int u = 0; u < GZ_BPL_U; u++) {
+    const int q = min(q0 + 32 * u, n - 1);
+    k[u] = Q.key[q];
+    lo2[u] = reinterpret_cast<const double2 *>(Q.yz)[2 * (size_t)q];       // y bounds
+    hi2[u] = reinterpret_cast<const double2 *>(Q.yz)[2 * (size_t)q + 1];   // z bounds
+  }
+  bool all_in = true;
+#pragma unroll
+  for (int u = 0; u < GZ_BPL_U; u++) {
+    const int q = q0 + 32 * u;
+    const bool in = (q < n) && k[u] <= mx;
+    all_in = all_in && in;
+    if (!in) continue;
+    if (pyz[0] > lo2[u].y || pyz[1] < lo2[u].x || pyz[2] > hi2[u].y || pyz[3] < hi2[u].x) continue;
     const int iq = Q.idx[q];
     const int lo = min(ip, iq), hi = max(ip, iq);
     if (pair_passes(B, G[lo], G[hi])) {
@@ -113,24 +132,43 @@ __device__ __forceinline__ bool bpl_follow(const DevBatch &B, const WorldInfo &w
       if (at < wi.pair_cap) { B.pair[2 * (wi.pair0 + at)] = lo; B.pair[2 * (wi.pair0 + at) + 1] = hi; }   // (beyond: k_bpl_scan raises the flag)
     }
   }
-  return in;
+  return all_in;
 }
 
+// One thread per sorted position: where its x interval ends (binary search: the keys are sorted), and its followers cut
+// into work items of GZ_BPL_SEG; an interval of more than 32 items (the ground plane, the pen's walls), or one the item
+// table cannot take, goes to the queue of k_bpl_tail.
+__global__ void __launch_bounds__(256) k_bpl_span(DevBatch B, const int w, BplBuf Q) {
+  const int n = B.world[w].ng;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n - 1; p += gridDim.x * blockDim.x) {
+    const double mx = Q.maxx[p];
+    int lo = p + 1, hi = n;   // first position in (p, n) whose key is > mx
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (Q.key[mid] <= mx) lo = mid + 1; else hi = mid; }
+    const int len = lo - (p + 1);
+    if (len <= 0) continue;
+    const int s = (len + GZ_BPL_SEG - 1) / GZ_BPL_SEG;
+    int at = -1;
+    if (s <= 32) { at = atomicAdd(&Q.ctl[3 + GZ_BPL_NBIG], s); if (at + s > Q.item_cap) at = -1; }
+    if (at < 0) { const int e = atomicAdd(&Q.ctl[0], 1); Q.queue[2 * e] = p; Q.queue[2 * e + 1] = p + 1; continue; }
+    for (int k = 0; k < s; k++) Q.item[at + k] = p | (k << 27);
+  }
+}
+
+// One warp per work item, all SMs (first version: one warp per position walking its whole interval - the warps of the
+// longest intervals were the kernel's duration, 0.18 ms at C4 with the SMs 5 % busy).
 __global__ void __launch_bounds__(256) k_bpl_sweep(DevBatch B, const int w, BplBuf Q) {
   const WorldInfo wi = B.world[w];
   const int n = wi.ng, lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarp = (gridDim.x * blockDim.x) >> 5;
   const Geom *G = B.geom + wi.geom0;
-  for (int p = warp; p < n - 1; p += nwarp) {
+  const int nitem = min(Q.ctl[3 + GZ_BPL_NBIG], Q.item_cap);
+  for (int it = warp; it < nitem; it += nwarp) {
+    const int code = Q.item[it], p = code & ((1 << 27) - 1), k = (unsigned)code >> 27;
     const int ip = Q.idx[p];
     const double mx = Q.maxx[p];
     const double pyz[4] = {Q.yz[4 * (size_t)p], Q.yz[4 * (size_t)p + 1], Q.yz[4 * (size_t)p + 2], Q.yz[4 * (size_t)p + 3]};
-    int c = 0;
-    for (int q0 = p + 1; q0 < n; q0 += 32, c++) {
-      if (c == Q.chunks) {   // a long interval: the rest goes to k_bpl_tail
-        if (lane == 0) { const int at = atomicAdd(&Q.ctl[0], 1); Q.queue[2 * at] = p; Q.queue[2 * at + 1] = q0; }
-        break;
-      }
+    const int qb = p + 1 + k * GZ_BPL_SEG;
+    for (int q0 = qb; q0 < min(qb + GZ_BPL_SEG, n); q0 += 32 * GZ_BPL_U) {
       const bool in = bpl_follow(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
       if (!__all_sync(0xffffffffu, in)) break;   // sorted: nothing further overlaps p on x
     }
@@ -148,7 +186,7 @@ __global__ void __launch_bounds__(256) k_bpl_tail(DevBatch B, const int w, BplBu
     const int ip = Q.idx[p];
     const double mx = Q.maxx[p];
     const double pyz[4] = {Q.yz[4 * (size_t)p], Q.yz[4 * (size_t)p + 1], Q.yz[4 * (size_t)p + 2], Q.yz[4 * (size_t)p + 3]};
-    for (int q0 = qs + 32 * warp; q0 < n; q0 += 32 * nwarp) {
+    for (int q0 = qs + 32 * GZ_BPL_U * warp; q0 < n; q0 += 32 * GZ_BPL_U * nwarp) {
       const bool in = bpl_follow(B, wi, G, Q, ip, mx, pyz, q0 + lane, n);
       if (!__all_sync(0xffffffffu, in)) break;   // sorted: this warp's later chunks are outside as well
     }

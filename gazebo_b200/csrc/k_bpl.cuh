@@ -79,16 +79,26 @@ __global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_merge(DevBatch B, const int
   const double k = Q.tkey[t * GZ_BPL_TILE + tid];
   const int i = Q.tidx[t * GZ_BPL_TILE + tid];
   int rank = tid;
-  for (int u = 0; u < ntile; u++) {
-    if (u == t) continue;
-    const double *uk = Q.tkey + u * GZ_BPL_TILE;
-    const int *ui = Q.tidx + u * GZ_BPL_TILE;
-    int lo = 0, hi = GZ_BPL_TILE;   // number of elements of tile u below (k, i)
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (bpl_less(uk[mid], ui[mid], k, i)) lo = mid + 1; else hi = mid;
+  // binary searches of four tiles at a time, step by step side by side: a search is ten dependent loads from L2
+  // (one tile after the other: 70 us at C4's 20 tiles)
+  for (int u0 = 0; u0 < ntile; u0 += 4) {
+    const double *uk[4];
+    const int *ui[4];
+    int lo[4];
+#pragma unroll
+    for (int x = 0; x < 4; x++) {
+      const int u = min(u0 + x, ntile - 1);
+      uk[x] = Q.tkey + u * GZ_BPL_TILE; ui[x] = Q.tidx + u * GZ_BPL_TILE; lo[x] = 0;
     }
-    rank += lo;
+    for (int st = GZ_BPL_TILE >> 1; st > 0; st >>= 1) {
+#pragma unroll
+      for (int x = 0; x < 4; x++) { const int m = lo[x] + st - 1; if (bpl_less(uk[x][m], ui[x][m], k, i)) lo[x] += st; }
+    }
+#pragma unroll
+    for (int x = 0; x < 4; x++) {   // lo = elements of the tile below (k, i), at most TILE - 1 so far
+      if (bpl_less(uk[x][lo[x]], ui[x][lo[x]], k, i)) lo[x]++;
+      if (u0 + x < ntile && u0 + x != t) rank += lo[x];
+    }
   }
   Q.key[rank] = k; Q.idx[rank] = i;
   if (i < n) {   // (real geoms take the places below n: padding sorts last)

@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256) k_contacts_large(DevBatch B, const int w,
   }
 }
 
-// k_assemble1 for a large world: auto-disable, islands (hooking + pointer jumping, see island_world), which islands are
+// k_assemble1 for a large world: auto-disable, islands (lock-free union-find over the joints and contacts), which islands are
 // stepped, the body prologue, row counts and offsets.
 __global__ void __launch_bounds__(256) k_assemble1_large(DevBatch B, const int w, unsigned *bar) {
   namespace cg = cooperative_groups;
@@ -85,31 +85,33 @@ __global__ void __launch_bounds__(256) k_assemble1_large(DevBatch B, const int w
   const WorldInfo wi = B.world[w];
   const WorldStep &ws = B.wstep[w];
   const int gt = blockIdx.x * blockDim.x + threadIdx.x, GT = gridDim.x * blockDim.x;
-  int *flag = reinterpret_cast<int *>(bar) + 1;   // three rotating "an edge joined two roots" flags (as k_bsched_large's)
-  if (gt == 0) { flag[0] = flag[1] = flag[2] = 0; }
   for (int i = gt; i < wi.nb; i += GT) autodisable_body(B, wi, i);
   pgsl_barrier(bar, bar_target);
   int *const lab0 = &B.bstep[wi.body0].label;
   const size_t ls = sizeof(BodyStep) / sizeof(int);
   auto root = [&](int x) { for (;;) { const int l = __ldcg(lab0 + (size_t)x * ls); if (l == x) return x; x = l; } };
   const int ne = wi.nj + ws.n_contacts;
-  for (int it = 0;; it++) {
-    bool hooked = false;
-    for (int k = gt; k < ne; k += GT) {
-      int b1, b2;
-      if (k < wi.nj) { const Joint &j = B.joint[wi.joint0 + k]; b1 = j.b1; b2 = j.b2; }
-      else { const Contact &c = B.contact[wi.contact0 + (k - wi.nj)]; b1 = c.b1; b2 = c.b2; }
-      if (b2 < 0) continue;
-      const int r1 = root(b1 - wi.body0), r2 = root(b2 - wi.body0);
-      if (r1 != r2) { atomicMin(lab0 + (size_t)max(r1, r2) * ls, min(r1, r2)); hooked = true; }
+  // lock-free union-find: an edge links the larger of its two current roots under the smaller one by compare-and-swap
+  // (only a body that still is a root is ever re-parented, so no link is lost and ONE pass over the edges suffices;
+  // labels only ever decrease, so there are no cycles and a component's root ends up its smallest body).  First version:
+  // hooking by atomicMin in passes until nothing changed - two grid barriers a pass, ~8 passes for a pile.
+  for (int k = gt; k < ne; k += GT) {
+    int b1, b2;
+    if (k < wi.nj) { const Joint &j = B.joint[wi.joint0 + k]; b1 = j.b1; b2 = j.b2; }
+    else { const Contact &c = B.contact[wi.contact0 + (k - wi.nj)]; b1 = c.b1; b2 = c.b2; }
+    if (b2 < 0) continue;
+    int r1 = root(b1 - wi.body0), r2 = root(b2 - wi.body0);
+    while (r1 != r2) {
+      const int hi = max(r1, r2), lo = min(r1, r2);
+      const int old = atomicCAS(lab0 + (size_t)hi * ls, hi, lo);
+      if (old == hi) break;
+      r1 = root(old); r2 = root(lo);   // somebody else re-parented hi first: go on from the new roots
     }
-    if (hooked) flag[it % 3] = 1;
-    pgsl_barrier(bar, bar_target);
-    for (int i = gt; i < wi.nb; i += GT) { const int r = root(i); B.bstep[wi.body0 + i].label = r; }
-    if (gt == 0) flag[(it + 2) % 3] = 0;   // (last read after the previous pass's barrier, next raised two passes on)
-    pgsl_barrier(bar, bar_target);
-    if (__ldcg(&flag[it % 3]) == 0) break;
   }
+  pgsl_barrier(bar, bar_target);
+  // flatten (a label overwritten by its root while another thread walks through it still leads to the same root)
+  for (int i = gt; i < wi.nb; i += GT) { const int r = root(i); B.bstep[wi.body0 + i].label = r; }
+  pgsl_barrier(bar, bar_target);
   // a component is stepped iff it holds an enabled body; every body in it is re-enabled
   for (int i = gt; i < wi.nb; i += GT) B.bstep[wi.body0 + i].active = 0;
   pgsl_barrier(bar, bar_target);

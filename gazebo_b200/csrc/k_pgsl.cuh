@@ -239,32 +239,47 @@ __global__ void __launch_bounds__(256) k_bsched_large(DevBatch B, const int w, u
     if (live && cntt && C.tors) { atomicAdd(&cntt[b1], 1); if (b2 >= 0) atomicAdd(&cntt[b2], 1); }
   }
   pgsl_barrier(bar, bar_target);
-  // ---- 2 (CTA 0): base = exclusive scan of njr + 3 cntc, cbase = exclusive scan of cntc
+  // ---- 2 (CTA 0): base = exclusive scan of njr + 3 cntc (+ cntt), cbase = exclusive scan of cntc; both scans in one
+  // pass, eight bodies per thread and trip (one body per thread and scan: 632 block barriers at C4, 50 us)
   if (blockIdx.x == 0) {
     const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
-    if (t < 2) s_carry[t] = 0;
-    __syncthreads();
-    for (int b0 = 0; b0 < nb; b0 += 256) {
-      const int b = b0 + t;
-      for (int which = 0; which < 2; which++) {
-        const int c = b < nb ? (which ? cntc[b] : njr[b] + 3 * cntc[b] + (cntt ? cntt[b] : 0)) : 0;
-        int v = c;
-        for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += u; }
-        if (lane == 31) s_scan[wp] = v;
-        __syncthreads();
-        if (wp == 0) {
-          int s = lane < 8 ? s_scan[lane] : 0;
-          for (int d = 1; d < 8; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, s, d); if (lane >= d) s += u; }
-          if (lane < 8) s_scan[lane] = s;
-        }
-        __syncthreads();
-        const int before = s_carry[which] + (wp > 0 ? s_scan[wp - 1] : 0) + v - c;
-        if (b < nb) (which ? cbase : base)[b] = before;
-        __syncthreads();
-        if (t == 0) s_carry[which] += s_scan[7];
-        __syncthreads();
+    int carry0 = 0, carry1 = 0;   // (the same in every thread)
+    for (int b0 = 0; b0 < nb; b0 += 256 * 8) {
+      const int bb = b0 + t * 8;
+      int e[8], c[8];
+#pragma unroll
+      for (int x = 0; x < 8; x++) {
+        const int b = bb + x;
+        c[x] = b < nb ? cntc[b] : 0;
+        e[x] = b < nb ? njr[b] + 3 * c[x] + (cntt ? cntt[b] : 0) : 0;
       }
+      int se = 0, sc_ = 0;
+#pragma unroll
+      for (int x = 0; x < 8; x++) { const int ee = e[x], cc = c[x]; e[x] = se; c[x] = sc_; se += ee; sc_ += cc; }   // exclusive, local
+      int v0 = se, v1 = sc_;
+      for (int d = 1; d < 32; d <<= 1) {
+        const int u0 = __shfl_up_sync(0xffffffffu, v0, d), u1 = __shfl_up_sync(0xffffffffu, v1, d);
+        if (lane >= d) { v0 += u0; v1 += u1; }
+      }
+      if (lane == 31) { s_scan[wp] = v0; s_scan[8 + wp] = v1; }
+      __syncthreads();
+      if (wp == 0) {
+        int s0 = lane < 8 ? s_scan[lane] : 0, s1 = lane < 8 ? s_scan[8 + lane] : 0;
+        for (int d = 1; d < 8; d <<= 1) {
+          const int u0 = __shfl_up_sync(0xffffffffu, s0, d), u1 = __shfl_up_sync(0xffffffffu, s1, d);
+          if (lane >= d) { s0 += u0; s1 += u1; }
+        }
+        if (lane < 8) { s_scan[lane] = s0; s_scan[8 + lane] = s1; }
+      }
+      __syncthreads();
+      const int before0 = carry0 + (wp > 0 ? s_scan[wp - 1] : 0) + v0 - se;
+      const int before1 = carry1 + (wp > 0 ? s_scan[8 + wp - 1] : 0) + v1 - sc_;
+#pragma unroll
+      for (int x = 0; x < 8; x++) { const int b = bb + x; if (b < nb) { base[b] = before0 + e[x]; cbase[b] = before1 + c[x]; } }
+      carry0 += s_scan[7]; carry1 += s_scan[15];
+      __syncthreads();   // (s_scan is rewritten by the next trip)
     }
+    if (t == 0) s_carry[0] = carry0;
     if (t == 0) {
       int nent = s_carry[0];
       long long wbase = 0;

@@ -837,7 +837,7 @@ static int launch_collision(gzcuda_batch *b) {
       const int nwarps = std::max(1, b->h_world[w].ng), blocks = std::min(cdiv(nwarps, 8), 148 * 8);
       const int ntile = cdiv(b->h_world[w].ng + 1, GZ_BPL_TILE);
       k_bpl_tilesort<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
-      k_bpl_merge<<<ntile, GZ_BPL_TILE, 0, b->stream>>>(d, w, b->bpl);
+      k_bpl_merge<<<4 * ntile, 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_span<<<cdiv(nwarps, 256), 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_sweep<<<std::min(148 * 8, cdiv(4 * nwarps, 8)), 256, 0, b->stream>>>(d, w, b->bpl);
       k_bpl_tail<<<blocks, 256, 0, b->stream>>>(d, w, b->bpl);

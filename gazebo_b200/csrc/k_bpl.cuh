@@ -72,9 +72,10 @@ __global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_tilesort(DevBatch B, const 
   Q.tkey[g] = sk[tid]; Q.tidx[g] = si[tid];
 }
 
-__global__ void __launch_bounds__(GZ_BPL_TILE) k_bpl_merge(DevBatch B, const int w, BplBuf Q) {
+// (four CTAs of 256 per tile: 20 CTAs of 1024 kept 20 of the 148 SMs busy)
+__global__ void __launch_bounds__(256) k_bpl_merge(DevBatch B, const int w, BplBuf Q) {
   const WorldInfo wi = B.world[w];
-  const int n = wi.ng, tid = threadIdx.x, t = blockIdx.x, ntile = gridDim.x;
+  const int n = wi.ng, tid = (blockIdx.x & 3) * 256 + threadIdx.x, t = blockIdx.x >> 2, ntile = gridDim.x >> 2;
   const Geom *G = B.geom + wi.geom0;
   const double k = Q.tkey[t * GZ_BPL_TILE + tid];
   const int i = Q.tidx[t * GZ_BPL_TILE + tid];
@@ -205,15 +206,18 @@ __global__ void __launch_bounds__(256) k_bpl_tail(DevBatch B, const int w, BplBu
 
 __global__ void __launch_bounds__(1024) k_bpl_scan(DevBatch B, const int w, BplBuf Q) {
   __shared__ int wsum[32];
-  __shared__ int carry_s;
   const WorldInfo wi = B.world[w];
   const int n = wi.ng, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) carry_s = 0;
-  __syncthreads();
-  for (int i0 = 0; i0 < n; i0 += 1024) {
-    const int i = i0 + tid;
-    const int c = (i < n) ? Q.cnt[i] : 0;
-    int v = c;
+  int carry = 0;   // (the same in every thread)
+  for (int i0 = 0; i0 < n; i0 += 1024 * 8) {   // eight counts per thread and trip
+    const int ib = i0 + tid * 8;
+    int c[8];
+#pragma unroll
+    for (int x = 0; x < 8; x++) c[x] = (ib + x < n) ? Q.cnt[ib + x] : 0;
+    int sum = 0;
+#pragma unroll
+    for (int x = 0; x < 8; x++) { const int cc = c[x]; c[x] = sum; sum += cc; }
+    int v = sum;
     for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += t; }
     if (lane == 31) wsum[warp] = v;
     __syncthreads();
@@ -223,14 +227,14 @@ __global__ void __launch_bounds__(1024) k_bpl_scan(DevBatch B, const int w, BplB
       wsum[lane] = s;
     }
     __syncthreads();
-    const int before = carry_s + (warp > 0 ? wsum[warp - 1] : 0) + v - c;
-    if (i < n) Q.cnt[i] = before;
-    __syncthreads();
-    if (tid == 0) carry_s += wsum[31];
+    const int before = carry + (warp > 0 ? wsum[warp - 1] : 0) + v - sum;
+#pragma unroll
+    for (int x = 0; x < 8; x++) if (ib + x < n) Q.cnt[ib + x] = before + c[x];
+    carry += wsum[31];
     __syncthreads();
   }
   if (tid == 0) {
-    int total = carry_s;
+    int total = carry;
     Q.cnt[n] = total;
     WorldStep &ws = B.wstep[w];
     if (total > wi.pair_cap) { ws.overflow |= 1; total = wi.pair_cap; }

@@ -127,6 +127,13 @@ struct WorldInfo {
   int rpc, pad_;         // rows per contact: 3, or 4 when a surface of the world has torsional friction (mu3 > 0)
 };
 
+// validity tag of the row-slot path's records (k_pgs.cuh): 1 .. 2^24 - 1, never 0
+#define GZ_EPOCH_PERIOD 0xFFFFFFL
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+static inline unsigned gz_epoch(long step_index) { return (unsigned)(step_index % GZ_EPOCH_PERIOD) + 1u; }
+
 struct WorldStep {
   int n_pairs, n_contacts, m, n_fric;
   int overflow;     // bit0 pairs, bit1 contacts, bit2 rows

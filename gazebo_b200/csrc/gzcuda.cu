@@ -61,6 +61,7 @@ struct gzcuda_batch {
   size_t bp_smem = 0;                 // k_broadphase: dynamic shared memory and CTA size
   int bp_threads = 128;
   PgsCfg pgs, pgs_chain[GZ_CHAIN_NCLS];
+  long row_tot = 0;                   // rows of all worlds' slabs (runrec)
   bool bp_large = false;              // worlds too large for the one-CTA broadphase: k_bpl_* (sort, sweep, scan, emit)
   BplBuf bpl = {};
   int pgsl_grid = 0;                  // CTAs of k_pgsl's cooperative grid
@@ -226,6 +227,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   DevBatch &d = b->d;
   memset(&d, 0, sizeof(d));
   d.n_worlds = W; d.nb = nb; d.ng = ng; d.nj = nj; d.p = *p; d.step_index = 0;
+  if (const char *e = getenv("GZCUDA_TEST_STEP_INDEX0")) d.step_index = atol(e);   // test hook: start near the record epochs' wrap
 
   std::vector<Body> hb(nb);
   std::vector<Geom> hg(ng);
@@ -399,6 +401,7 @@ static int build(gzcuda_batch *b, const gz_scene *sc, const gz_params *p) {
   if ((rc = dev_alloc(b, &d.order, (size_t)row_tot))) return rc;
   if ((rc = dev_alloc(b, &d.scratch, (size_t)W * ((size_t)7 * max_rc)))) return rc;
   if ((rc = dev_alloc(b, &d.runrec, (size_t)GZ_REC * row_tot))) return rc;
+  b->row_tot = row_tot;
   // record pool of the PGS warps: every world's slots, rounded up to whole warps (16 lane pairs per
   // round), plus one partly filled warp per bucket in use; clamped to a share of device memory
   {
@@ -1009,6 +1012,10 @@ static int launch_physics(gzcuda_batch *b, bool stage_events, int prof_slot = -1
   }
   const size_t sch_smem = (size_t)3 * std::max(d.max_nb, 1) * sizeof(int) + (size_t)d.sch_rcap * sizeof(unsigned short) + 16 +
                           (d.sch_rpar > 0 ? (size_t)32 * (2 * std::max(d.max_nb, 1) * sizeof(int) + d.sch_rpar * sizeof(unsigned short)) : 0);
+  if (d.step_index > 0 && gz_epoch(d.step_index) == 1u) {   // the epochs start over (every 2^24 - 1 steps): no record of the last period may survive
+    cudaMemsetAsync(d.prec, 0, (size_t)GZ_REC * d.prec_cap * sizeof(double), b->stream);
+    cudaMemsetAsync(d.runrec, 0, (size_t)GZ_REC * std::max<size_t>(b->row_tot, 1) * sizeof(double), b->stream);
+  }
   k_schedule<<<W, 32, sch_smem, b->stream>>>(d);
   k_slab<<<1 + cdiv((W + GZ_NBUCKET) * 16, GZ_SLAB_T * 8), GZ_SLAB_T, 0, b->stream>>>(d);
   if (d.p.dynamic_inertia && d.nj > 0) { k_dyn_inertia<<<cdiv(W, 64), 64, 0, b->stream>>>(d); b->last_launches++; }

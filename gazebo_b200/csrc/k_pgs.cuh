@@ -51,7 +51,9 @@ __device__ inline WScratch wscratch(const DevBatch &B, int w) {
 // [29] 1/Ad^2 (statistics)  [30..31] RecInts (16 bytes, 16-byte aligned)  [32..33] padding: the
 // 272-byte stride puts the 16 records a warp reads per round in distinct shared-memory banks.
 // A warp's slab holds R rounds of 16 records: record of (slot s, lane pair p) at (s * 16 + p).
-// A record is live only if its epoch equals the current step's (slabs are never cleared).
+// A record is live only if its epoch equals the current step's.  Epochs run 1 .. 2^24 - 1 (0 is what a never-written slot
+// holds); when they start over the host clears the record pool (launch_physics), so a record of 2^24 - 1 steps ago cannot
+// pass for a live one.
 #define GZ_REC 34
 #define GZ_REC_INTS 30
 #define GZ_ROUND_DOUBLES (16 * GZ_REC)
@@ -546,7 +548,7 @@ __device__ __forceinline__ void rowfinish_one(DevBatch &B, const int w, const Wo
   const WSlab sl = wslab(B, sc);
   if (sl.warp < 0) return;
   if (i == 0) B.warp_world[sl.warp * 16 + sl.wslot] = w;
-  const unsigned epoch_sh = ((unsigned)B.step_index + 1u) << 8;
+  const unsigned epoch_sh = gz_epoch(B.step_index) << 8;
   // the row's record: its own slab slot, or its place in the world's run array (chain mode)
   double *rec = (r.t2a < 0) ? slab_rec(sl, r.next_f) : B.runrec + ((size_t)wi.row0 + r.t2a) * GZ_REC;
   double2 *rec2 = reinterpret_cast<double2 *>(rec);

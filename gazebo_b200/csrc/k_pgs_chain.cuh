@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(32) k_pgs_chain(DevBatch B, PgsCfg cfg, int cl
     for (unsigned o = 0; o < bytes; o += chunk)
       bulk_g2s(dst + o, reinterpret_cast<const char *>(runrec_g) + o, min(chunk, bytes - o), bar_s);
   }
-  const unsigned epoch = ((unsigned)B.step_index + 1u) & 0xFFFFFFu;
+  const unsigned epoch = gz_epoch(B.step_index);
   for (int i = lane; i < ca_doubles + 320; i += 32) shd[i] = 0.0;
   for (int i = lane; i < nheads; i += 32) {   // a head whose epoch is not this step's is an empty slot
     int4 h = *reinterpret_cast<const int4 *>(heads_g + i);

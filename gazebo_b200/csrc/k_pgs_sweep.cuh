@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(32) k_pgs(DevBatch B, PgsCfg cfg) {
   const unsigned bar_s = ring_s + GZ_RING_D * GZ_STAGE_DOUBLES * 8;
   if (lane < GZ_RING_D) mbar_init(bar_s + 8 * lane, 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  const unsigned epoch = ((unsigned)B.step_index + 1u) & 0xFFFFFFu;
+  const unsigned epoch = gz_epoch(B.step_index);
   WSlab sl;
   sl.base = const_cast<double *>(slab); sl.k = k; sl.wslot = wslot; sl.warp = cta; sl.width = 16;
   // ---- lambda0 and the accumulators

@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
   const int nb = wi.nb, m = ws.m, nc = ws.n_contacts, rpc = wi.rpc, mj = m - rpc * nc;
   int *const tab = B.bs_glob ? B.bs_glob + (size_t)w * 5 * B.max_nb : bs_sh;   // (large worlds: the tables live in global memory)
   int *last = tab, *first = tab + B.max_nb, *cnt = tab + 2 * B.max_nb, *fr0 = tab + 3 * B.max_nb, *base = tab + 4 * B.max_nb;
-  __shared__ int s_R, s_maxoff, s_nent, s_wbase;
+  __shared__ int s_nent, s_wbase;
   const WScratchB G = wscratchb(B, w);
   // the serial pass below walks these arrays with dependent accesses: worlds of up to GZ_BS_SM rows keep them in
   // shared memory (the row offsets and list places go out to global memory in parallel afterwards)
@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(128) k_bsched(DevBatch B) {
         nent = 0;
       }
     }
-    s_R = R; s_maxoff = maxoff; s_nent = nent; s_wbase = (int)wbase;
+    s_nent = nent; s_wbase = (int)wbase;
     B.wsb[w] = make_int4(R, maxoff < 0 ? 0 : maxoff / R + 1, (int)wbase, nent);
     // k_border sorts the worlds by their number of entries (in steps of 4), largest first: that is their shared-
     // memory need, so the CTAs of a class are filled tightly, and it follows the duration of the sweeps closely,

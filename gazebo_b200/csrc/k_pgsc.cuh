@@ -65,7 +65,6 @@ __global__ void __launch_bounds__(256, 2) k_pgsc(DevBatch B, const int w, unsign
   if (bl < wi.nb && nent > 0) { const int4 bs = B.bsched[wi.body0 + bl]; e0 = bs.x; cnt = bs.y; fric0 = bs.z; }
   double *const lp = B.ent + (size_t)e0 * GZ_ENT;
   double *const dl = B.ent_dl + 2 * (size_t)e0 + S;
-  const int *const part = B.ent_part + e0;
   // initial caccel = iMJ * lambda0 over the warm-started (persistent-joint) rows (multiply_invM_JT, quickstep_util.cpp:101-119)
   double a[6] = {0, 0, 0, 0, 0, 0};
   if (B.p.warm_start > 0) {

@@ -493,6 +493,10 @@ __global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned 
     if (pe >= 0) slot_put(slots + 2 * (((size_t)(e0 + i) * 2 + S) * 2 + (sweep & 1)), d, tag0 + (unsigned)sweep);
     load_rest(i);
   }
+  // where and for what the lane polls: kept in registers across the poll loop (left to the compiler, the loop
+  // recomputed S from the thread index, the slot address and the tag on every trip: 26 instructions a poll)
+  const unsigned long long *pslot = slots + 2 * (((size_t)max(pe, 0) * 2 + S) * 2 + (sweep & 1));
+  unsigned ptag = tag0 + (unsigned)sweep;
   // The warp stays together: ALL its lanes poll back to back until some lane can finish its row (a waiting lane's
   // poll interval is one L2 trip, not one pass of its neighbours through the row code), then those lanes finish.
   int n_outer = 0, n_spin = 0;   // developer counters: passes of this warp through the row code, polls
@@ -504,7 +508,7 @@ __global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned 
     do {
       n_spin++;
       ready = alive;
-      if (alive && pe >= 0) ready = slot_get(slots + 2 * (((size_t)pe * 2 + S) * 2 + (sweep & 1)), tag0 + (unsigned)sweep, pd);
+      if (alive && pe >= 0) ready = slot_get(pslot, ptag, pd);
     } while (!__any_sync(0xffffffffu, ready));
     if (ready) {
       // this body's half and the partner's, subtracted in the row's body order (body 1 first)
@@ -532,6 +536,7 @@ __global__ void __launch_bounds__(256) k_pgsd(DevBatch B, const int w, unsigned 
       lp[(size_t)i * GZ_ENT + 13 + 2 * S] = (S == 0 && cls != 0) ? sm : nl;
       dl[2 * (size_t)i] = delta;
       i = ni; sweep = nsweep; alive = has_next; d = dn; pe = pen;
+      pslot = slots + 2 * (((size_t)max(pe, 0) * 2 + S) * 2 + (sweep & 1)); ptag = tag0 + (unsigned)sweep;
       if (alive) load_rest(i);
     }
   }

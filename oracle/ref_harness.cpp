@@ -807,6 +807,20 @@ void gzref_set_joint_velocity_cmd(void *h, const double *vel) {
   }
 }
 
+// Link::AddForce / AddTorque before a step (dBodyAddForce / dBodyAddTorque: world frame, cleared by the step):
+// force[nb][3], torque[nb][3], either may be null.
+void gzref_add_body_wrench(void *h, const double *force, const double *torque) {
+  RefBatch *B = static_cast<RefBatch *>(h);
+  for (size_t wi = 0; wi < B->worlds.size(); wi++) {
+    RefWorld *w = B->worlds[wi];
+    for (size_t k = 0; k < w->bodies.size(); k++) {
+      const size_t b = (size_t)B->body_off[wi] + k;
+      if (force) dBodyAddForce(w->bodies[k], force[3 * b], force[3 * b + 1], force[3 * b + 2]);
+      if (torque) dBodyAddTorque(w->bodies[k], torque[3 * b], torque[3 * b + 1], torque[3 * b + 2]);
+    }
+  }
+}
+
 int gzref_step(void *h, int nsteps) {
   RefBatch *B = static_cast<RefBatch *>(h);
   dAllocateODEDataForThread(dAllocateMaskAll);

@@ -42,6 +42,7 @@ def _load(flavour):
     lib.gzref_destroy.argtypes = [C.c_void_p]
     lib.gzref_set_hinge_pd.argtypes = [C.c_void_p, C.c_void_p]
     lib.gzref_step.argtypes = [C.c_void_p, C.c_int]
+    lib.gzref_add_body_wrench.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gzref_ray_query.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gzref_step_mt.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.gzref_collide.argtypes = [C.c_void_p, C.c_int]
@@ -89,6 +90,12 @@ class RefBatch:
     def set_hinge_pd(self, pd):
         pd = np.ascontiguousarray(pd, dtype=np.float64).reshape(self.scene.nj, 6)
         self.lib.gzref_set_hinge_pd(self.h, _p(pd))
+
+    def add_body_wrench(self, force=None, torque=None):
+        """Link::AddForce / AddTorque (world frame) for the next step; [nb][3] each."""
+        f = None if force is None else np.ascontiguousarray(force, dtype=np.float64).reshape(self.scene.nb, 3)
+        t = None if torque is None else np.ascontiguousarray(torque, dtype=np.float64).reshape(self.scene.nb, 3)
+        self.lib.gzref_add_body_wrench(self.h, None if f is None else _p(f), None if t is None else _p(t))
 
     def step(self, n=1, threads=0):
         if threads and threads > 1:

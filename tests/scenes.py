@@ -518,6 +518,23 @@ def spinners(n_worlds=3, seed=91):
     return sb.finish(), S.default_params(), None
 
 
+def torsion_spheres():
+    """test/worlds/torsional_friction_test.world restated (the reference's PhysicsTorsionalFrictionTest.CoefficientTest,
+    test/integration/physics_torsional_friction.cc:283-381): ten 0.1 m spheres of 11.31 kg (izz 0.04524) with kp = 5e5 on the
+    stock ground plane (MuTorsion 1, no patch radius of its own): five with patch radius 2 m and coefficients 0 .. 0.1,
+    five with coefficient 0.005 and patch radii 0 .. 1 m.  Returns the scene, the parameters and (coefficient, patch)."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), mu=100.0, mu2=50.0, mu3=1.0)
+    spec = [(c, 2.0) for c in (0.0, 0.001, 0.005, 0.01, 0.1)] + [(0.005, a) for a in (0.0, 0.01, 0.1, 0.5, 1.0)]
+    mass, izz = 11.309733552923259, 0.045238934211693047
+    for k, (c, a) in enumerate(spec):
+        b = sb.add_body([0.4 * (k % 5 + 1), 1.0 + k // 5, 0.1], mass=mass, inertia=(izz, izz, izz, 0, 0, 0))   # (allow_auto_disable 0)
+        sb.add_geom(S.GEOM_SPHERE, (0.1,), sb.new_space(), body=b, mu3=c, patch_radius=a, kp=5e5)
+    sb.end_world()
+    return sb.finish(), S.default_params(), spec
+
+
 def ray_targets(n_worlds=2, per_type=6, seed=77):
     """Worlds for the laser: a ground plane and, floating at rest (no gravity flag needed: they are never stepped far), boxes,
     spheres, capsules and cylinders at random poses inside a 6 m cube, one sensor-category geom that rays must not see."""

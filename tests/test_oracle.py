@@ -40,6 +40,37 @@ def test_oracle_reproduces_golden(oracle, name):
     assert np.array_equal(r.body_flags(), g["flags"])
 
 
+def test_torsional_friction_coefficient_test(oracle):
+    """PhysicsTorsionalFrictionTest.CoefficientTest (test/integration/physics_torsional_friction.cc:283-381) on the
+    oracle: spheres settle for 1 000 steps, then 1 000 N m about the vertical every step for 10 steps; the angular
+    acceleration is (torque - friction torque) / izz with friction torque = m g x mu3 x 3 pi / 16 x patch radius, or
+    zero when the friction holds; tolerance 1e-3 as in the reference's test (:29)."""
+    sc, p, spec = scenes.torsion_spheres()
+    r = oracle.RefBatch(sc, p, mode=1)
+    _coefficient_test(r, sc, spec)
+
+
+def _coefficient_test(r, sc, spec):
+    mass, izz, applied = 11.309733552923259, 0.045238934211693047, 1000.0
+    r.step(1000)
+    torque = np.zeros((sc.nb, 3)); torque[:, 2] = applied
+    err = np.zeros(sc.nb)
+    moved = 0
+    for _ in range(10):
+        w0 = r.body_state()[3].copy()
+        r.add_body_wrench(torque=torque)
+        r.step(1)
+        acc = (r.body_state()[3] - w0) / 0.001
+        assert np.abs(acc[:, :2]).max() < 1e-3
+        for k, (c, a) in enumerate(spec):
+            friction = mass * 9.8 * c * 3 * np.pi / 16 * a
+            if applied <= friction:
+                assert abs(acc[k, 2]) < 1e-3
+            else:
+                err[k] = max(err[k], abs(acc[k, 2] - (applied - friction) / izz)); moved += 1
+    assert moved == 100 and err.max() < 1e-3, err
+
+
 def test_free_fall_then_rest(oracle):
     """PhysicsTest.DropStuffODE (test/integration/physics.cc:919-1062): free fall follows
     v += g dt; z += v dt exactly, the box settles at z = 0.5, and stays there."""

@@ -535,6 +535,52 @@ def torsion_spheres():
     return sb.finish(), S.default_params(), spec
 
 
+def elastic_modulus_contact():
+    """test/worlds/elastic_modulus_contact_test.world restated (PhysicsTest.ElasticModulusContact,
+    test/integration/elastic_modulus.cc:60-225): gravity -100 along x, 300 iterations, sor 1; a static 1 m box at the origin
+    (E = 5e5, nu = 0.3, surface radius 0.08) and a 3 kg sphere of radius 0.5 (E = 6e5, nu = 0.4, surface radius 0.06, min
+    depth 0.001) that falls onto the box's +x face; both surfaces: kp 1, kd 100, torsional coefficient 1 on the surface
+    radius.  The reference's test holds the converged numbers (:115-117): the only golden vector in its tests for this path."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    common = dict(mu=1.0, mu2=1.0, kp=1.0, kd=100.0, mu3=1.0, use_patch_radius=0.0)
+    sb.add_geom(S.GEOM_BOX, (1, 1, 1), sb.new_space(), pos=(0, 0, 0), poissons_ratio=0.3, elastic_modulus=5e5,
+                surface_radius=0.08, **common)
+    b = sb.add_body([2, 0.3, 0.2], mass=3.0, inertia=(1, 1, 1, 0, 0, 0), max_vel=100.0, min_depth=0.001)
+    sb.add_geom(S.GEOM_SPHERE, (0.5,), sb.new_space(), body=b, poissons_ratio=0.4, elastic_modulus=6e5,
+                surface_radius=0.06, **common)
+    sb.end_world()
+    p = S.default_params(gravity=(-100.0, 0, 0), iters=300, sor_w=1.0, cfm=0.0, erp=0.5,
+                         contact_max_correcting_vel=1000.0, contact_surface_layer=0.0)
+    return sb.finish(), p, None
+
+
+def check_elastic_modulus_contact(r):
+    """The assertions of elastic_modulus.cc:108-190 on a stepper with .step / .contacts / .body_state."""
+    d_converged, k_converged, k_lin_converged = 0.0258629, 71454.617, 11491.286   # :115-117
+    nu1, e1, m1, r1, nu2, e2, r2 = 0.4, 600000.0, 3.0, 0.06, 0.3, 500000.0, 0.08
+    e_star = 1.0 / ((1.0 - nu1 * nu1) / e1 + (1.0 - nu2 * nu2) / e2)
+    r_star = 1.0 / (1.0 / r1 + 1.0 / r2)
+    f1 = 100.0 * m1
+    float_eq = lambda a, b: abs(np.float32(a) - np.float32(b)) <= 4 * np.spacing(np.float32(b))   # EXPECT_FLOAT_EQ: 4 ULPs
+    r.step(3000)
+    for _ in range(10):
+        r.step(1)
+        cg, cd = r.contacts(0)
+        assert len(cg) == 1
+        min_depth = min(0.0015, 0.001)
+        d1 = cd[0, 6] - min_depth
+        assert d1 < d_converged and abs((d1 - d_converged) / d_converged) < 1e-2
+        d2 = 1.0 - r.body_state()[0][0, 0] - min_depth
+        assert float_eq(d1, d2)
+        d3 = (f1 / (4.0 / 3.0 * e_star * np.sqrt(np.sqrt(r_star)))) ** (1.0 / 1.75)
+        assert abs(d1 - d3) / d3 < 1e-2
+        patch_radius = np.sqrt(r_star * d1)
+        assert float_eq(4.0 / 3.0 * e_star * np.sqrt(patch_radius), k_converged)
+        assert float_eq(4.0 / 3.0 * e_star * np.sqrt(patch_radius * d1), k_lin_converged)
+    return d1
+
+
 def ray_targets(n_worlds=2, per_type=6, seed=77):
     """Worlds for the laser: a ground plane and, floating at rest (no gravity flag needed: they are never stepped far), boxes,
     spheres, capsules and cylinders at random poses inside a 6 m cube, one sensor-category geom that rays must not see."""

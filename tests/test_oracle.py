@@ -40,6 +40,15 @@ def test_oracle_reproduces_golden(oracle, name):
     assert np.array_equal(r.body_flags(), g["flags"])
 
 
+def test_elastic_modulus_contact_golden_numbers(oracle):
+    """PhysicsTest.ElasticModulusContact (test/integration/elastic_modulus.cc:60-225): the converged depth and Hertzian
+    stiffnesses the reference's own test holds (k = 71454.617, k_lin = 11491.286 to float precision) come out of the
+    oracle - the one golden vector the reference has for this path pins the harness' surface combination, the
+    elastic-modulus normal row, min_depth and the solver."""
+    sc, p, _ = scenes.elastic_modulus_contact()
+    scenes.check_elastic_modulus_contact(oracle.RefBatch(sc, p, mode=1))
+
+
 def test_torsional_friction_coefficient_test(oracle):
     """PhysicsTorsionalFrictionTest.CoefficientTest (test/integration/physics_torsional_friction.cc:283-381) on the
     oracle: spheres settle for 1 000 steps, then 1 000 N m about the vertical every step for 10 steps; the angular

@@ -535,6 +535,41 @@ def torsion_spheres():
     return sb.finish(), S.default_params(), spec
 
 
+def inertia_ratio_pendulum(dynamic_inertia=1):
+    """test/worlds/inertia_ratio_pendulum.world restated (PhysicsTest.InertiaRatioPendulum,
+    test/integration/physics_inertia_ratio.cc:39-84): a 27 g upper link on a hinge to the world carrying a 3.375 kg lower
+    link on a second hinge (inertia ratio ~3 000 along the constrained axes), both about x, released at 45 / 90 degrees
+    with gravity (0.1, 0, -9.81): 250 iterations, sor 1.4, use_dynamic_moi_rescaling."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sp = sb.new_space()
+    a = np.pi / 4
+    up = sb.add_body([0, 0.05 * np.sin(a), 0.9 - 0.05 * np.cos(a)], S.q_from_rpy(a, 0, 0), mass=0.02700000000000001,
+                     inertia=(2.272500000000001e-05, 2.272500000000001e-05, 4.5000000000000035e-07, 0, 0, 0))
+    sb.add_geom(S.GEOM_BOX, (0.010000000000000002, 0.010000000000000002, 0.1), sp, body=up)
+    y, z = 0.17677669529663687, -0.2767766952966369
+    lo = sb.add_body([0, y * np.cos(a) - z * np.sin(a), 0.9 + y * np.sin(a) + z * np.cos(a)], S.q_from_rpy(2 * a, 0, 0),
+                     mass=3.375, inertia=(0.071015625, 0.071015625, 0.0014062500000000004, 0, 0, 0))
+    sb.add_geom(S.GEOM_BOX, (0.05, 0.05, 0.5), sp, body=lo)
+    sb.add_hinge(up, -1, [0, 0, 0.9], [1, 0, 0])
+    sb.add_hinge(lo, up, [0, 0.1 * np.sin(a), 0.9 - 0.1 * np.cos(a)], [1, 0, 0])
+    sb.end_world()
+    p = S.default_params(gravity=(0.1, 0, -9.81), iters=250, sor_w=1.4, cfm=0.0, erp=0.2, contact_max_correcting_vel=0.0,
+                         contact_surface_layer=0.0, dynamic_inertia=dynamic_inertia)
+    return sb.finish(), p, None
+
+
+def max_out_of_plane_angles(r, steps=3000, every=10):
+    """max |Euler Y|, max |Euler Z| of all links over the run (physics_inertia_ratio.cc:66-78)."""
+    my = mz = 0.0
+    for _ in range(steps // every):
+        r.step(every)
+        w, x, y, z = r.body_state()[1].T
+        my = max(my, float(np.abs(np.arcsin(np.clip(2 * (w * y - z * x), -1, 1))).max()))
+        mz = max(mz, float(np.abs(np.arctan2(2 * (w * z + x * y), 1 - 2 * (y * y + z * z))).max()))
+    return my, mz
+
+
 def elastic_modulus_contact():
     """test/worlds/elastic_modulus_contact_test.world restated (PhysicsTest.ElasticModulusContact,
     test/integration/elastic_modulus.cc:60-225): gravity -100 along x, 300 iterations, sor 1; a static 1 m box at the origin

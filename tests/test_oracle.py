@@ -40,6 +40,18 @@ def test_oracle_reproduces_golden(oracle, name):
     assert np.array_equal(r.body_flags(), g["flags"])
 
 
+def test_inertia_ratio_pendulum(oracle):
+    """PhysicsTest.InertiaRatioPendulum (test/integration/physics_inertia_ratio.cc:39-84): with use_dynamic_moi_rescaling
+    the out-of-plane angles of both links stay below g_angle_y_tol = 0.21 / g_angle_z_tol = 0.23 (:30-31) for 3 000 steps;
+    without it the light link is thrown out of the plane (which is what the reference's test guards against)."""
+    sc, p, _ = scenes.inertia_ratio_pendulum(1)
+    my, mz = scenes.max_out_of_plane_angles(oracle.RefBatch(sc, p, mode=1))
+    assert my < 0.21 and mz < 0.23, (my, mz)
+    sc, p, _ = scenes.inertia_ratio_pendulum(0)
+    my0, mz0 = scenes.max_out_of_plane_angles(oracle.RefBatch(sc, p, mode=1))
+    assert my0 > 0.21 and my0 > 1.5 * my, (my0, mz0)
+
+
 def test_elastic_modulus_contact_golden_numbers(oracle):
     """PhysicsTest.ElasticModulusContact (test/integration/elastic_modulus.cc:60-225): the converged depth and Hertzian
     stiffnesses the reference's own test holds (k = 71454.617, k_lin = 11491.286 to float precision) come out of the

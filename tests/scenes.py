@@ -535,6 +535,23 @@ def torsion_spheres():
     return sb.finish(), S.default_params(), spec
 
 
+def torsion_radius_spheres():
+    """The sphere_radius_1..5 models of torsional_friction_test.world (PhysicsTorsionalFrictionTest.RadiusTest,
+    physics_torsional_friction.cc:383-479): spheres of radius 0.01 .. 10 m, coefficient 0.005, use_patch_radius false and
+    their own radius as surface radius: the patch is sqrt(R x depth), the plane's curvature being zero.
+    Returns the scene, the parameters and the radii."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), mu=100.0, mu2=50.0, mu3=1.0)
+    radii = (0.01, 0.1, 0.8, 2.0, 10.0)
+    mass, izz = 11.309733552923259, 0.045238934211693047
+    for k, rad in enumerate(radii):
+        b = sb.add_body([(0.04, 0.8, 9.6, 32.0, 200.0)[k], 3.0, rad], mass=mass, inertia=(izz, izz, izz, 0, 0, 0))
+        sb.add_geom(S.GEOM_SPHERE, (rad,), sb.new_space(), body=b, mu3=0.005, surface_radius=rad, use_patch_radius=0.0, kp=5e5)
+    sb.end_world()
+    return sb.finish(), S.default_params(), radii
+
+
 def inertia_ratio_pendulum(dynamic_inertia=1):
     """test/worlds/inertia_ratio_pendulum.world restated (PhysicsTest.InertiaRatioPendulum,
     test/integration/physics_inertia_ratio.cc:39-84): a 27 g upper link on a hinge to the world carrying a 3.375 kg lower

@@ -71,6 +71,32 @@ def test_torsional_friction_coefficient_test(oracle):
     _coefficient_test(r, sc, spec)
 
 
+def test_torsional_friction_radius_test(oracle):
+    """PhysicsTorsionalFrictionTest.RadiusTest (physics_torsional_friction.cc:383-479): the patch radius from the surface
+    radius and the depth at equilibrium, a = sqrt(R m g / kp); angular acceleration within 1 % (:475)."""
+    sc, p, radii = scenes.torsion_radius_spheres()
+    _radius_test(oracle.RefBatch(sc, p, mode=1), sc, radii)
+
+
+def _radius_test(r, sc, radii):
+    mass, izz, applied, kp = 11.309733552923259, 0.045238934211693047, 1000.0, 500000.0
+    r.step(1000)
+    torque = np.zeros((sc.nb, 3)); torque[:, 2] = applied
+    for _ in range(10):
+        w0 = r.body_state()[3].copy()
+        r.add_body_wrench(torque=torque)
+        r.step(1)
+        acc = (r.body_state()[3] - w0) / 0.001
+        assert np.abs(acc[:, :2]).max() < 1e-3
+        for k, rad in enumerate(radii):
+            patch = np.sqrt(rad * mass * 9.8 / kp)
+            friction = mass * 9.8 * 0.005 * 3 * np.pi * patch / 16
+            assert applied > friction
+            expected = (applied - friction) / izz
+            assert abs(acc[k, 2] - expected) / expected < 0.01
+            assert acc[k, 2] < applied / izz   # (and the friction does brake: the reference's 1 % alone would not see it)
+
+
 def _coefficient_test(r, sc, spec):
     mass, izz, applied = 11.309733552923259, 0.045238934211693047, 1000.0
     r.step(1000)

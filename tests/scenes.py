@@ -535,6 +535,33 @@ def torsion_spheres():
     return sb.finish(), S.default_params(), spec
 
 
+def friction_demo():
+    """worlds/friction_demo.world restated (PhysicsFrictionTest.FrictionDemo, test/integration/physics_friction.cc:183-286):
+    gravity (0, -1, -1); six 1 kg unit boxes (inertia 10, centre of mass on the bottom face so that they cannot tip) with
+    mu = 0.998 .. 1.01 on a plane with mu = 50.  Returns the scene, the parameters and the friction coefficients."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), mu=50.0, mu2=50.0, kp=1e9, kd=1.0)
+    mus = (0.998, 0.9985, 0.999, 0.9995, 1.0, 1.01)
+    for k, mu in enumerate(mus):
+        b = sb.add_body([2.0 * (k + 1), 8.0, 0.0], mass=1.0, inertia=(10, 10, 10, 0, 0, 0), max_vel=100.0, min_depth=0.001)
+        sb.add_geom(S.GEOM_BOX, (1, 1, 1), sb.new_space(), body=b, pos=(0, 0, 0.5), mu=mu, mu2=mu, kp=1e5, kd=1.0)
+    sb.end_world()
+    return sb.finish(), S.default_params(gravity=(0.0, -1.0, -1.0)), mus
+
+
+def check_friction_demo(r, mus):
+    """physics_friction.cc:239-281: every 500 steps for 10 s, v_x = v_z = 0 and v_y = (g_y + mu) t below mu = 1, 0 from
+    there on, all within g_friction_tolerance = 1e-3."""
+    for k in range(20):
+        r.step(500)
+        t = 0.5 * (k + 1)
+        v = r.body_state()[2]
+        assert np.abs(v[:, 0]).max() < 1e-3 and np.abs(v[:, 2]).max() < 1e-3
+        for i, mu in enumerate(mus):
+            assert abs(v[i, 1] - (0.0 if mu >= 1.0 else (-1.0 + mu) * t)) < 1e-3, (t, mu, v[i, 1])
+
+
 def torsion_radius_spheres():
     """The sphere_radius_1..5 models of torsional_friction_test.world (PhysicsTorsionalFrictionTest.RadiusTest,
     physics_torsional_friction.cc:383-479): spheres of radius 0.01 .. 10 m, coefficient 0.005, use_patch_radius false and

@@ -40,6 +40,14 @@ def test_oracle_reproduces_golden(oracle, name):
     assert np.array_equal(r.body_flags(), g["flags"])
 
 
+def test_friction_demo(oracle):
+    """PhysicsFrictionTest.FrictionDemo (test/integration/physics_friction.cc:183-286): the pyramid friction's sliding
+    threshold to a part in a thousand - boxes with mu just below 1 under gravity (0, -1, -1) accelerate at g_y + mu, those
+    with mu >= 1 stay."""
+    sc, p, mus = scenes.friction_demo()
+    scenes.check_friction_demo(oracle.RefBatch(sc, p, mode=1), mus)
+
+
 def test_inertia_ratio_pendulum(oracle):
     """PhysicsTest.InertiaRatioPendulum (test/integration/physics_inertia_ratio.cc:39-84): with use_dynamic_moi_rescaling
     the out-of-plane angles of both links stay below g_angle_y_tol = 0.21 / g_angle_z_tol = 0.23 (:30-31) for 3 000 steps;

@@ -562,6 +562,56 @@ def check_friction_demo(r, mus):
             assert abs(v[i, 1] - (0.0 if mu >= 1.0 else (-1.0 + mu) * t)) < 1e-3, (t, mu, v[i, 1])
 
 
+def friction_spheres():
+    """test/worlds/friction_spheres.world.erb restated (PhysicsFrictionTest.SphereSlip,
+    test/integration/physics_friction.cc:529-666): gravity (0, 2, -9.81); links of one ("lowball": centre of mass hanging
+    0.3 m below the ball so that it slides), two and three collision spheres of radius 0.2, and boxes of edge 0.4, each
+    in six mass / slip combinations (mass x slip = 0.2, 0.4, 0.6 twice), mu = 0.5, on the stock ground plane.
+    Returns the scene, the parameters and per body (mass x slip, number of collision shapes sharing the load)."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_ground_plane()
+    rad, alt = 0.2, 0.5
+    side = alt / (np.sqrt(3) / 2.0)
+    kinds = [("lowball", [(0, 0, 0)], (0, 0, -0.3)),
+             ("twoball", [(0, side / 2, 0), (0, -side / 2, 0)], (0, 0, 0)),
+             ("triball", [(2 / 3 * alt, 0, 0), (-1 / 3 * alt, side / 2, 0), (-1 / 3 * alt, -side / 2, 0)], (0, 0, 0))]
+    mass_slip = [(1.0, 0.2), (2.0, 0.1), (2.0, 0.2), (4.0, 0.1), (3.0, 0.2), (6.0, 0.1)]
+    expect = []
+    for i, (_, balls, off) in enumerate(kinds):
+        n = len(balls)
+        for ii, (mass, slip) in enumerate(mass_slip):
+            bm = mass / n
+            I = np.diag([n * 0.4 * bm * rad ** 2] * 3)
+            for (dx, dy, dz) in balls:   # (the balls' centre is the origin for all three kinds)
+                I += bm * np.array([[dy * dy + dz * dz, -dx * dy, -dx * dz], [-dx * dy, dz * dz + dx * dx, -dy * dz],
+                                    [-dx * dz, -dy * dz, dx * dx + dy * dy]])
+            b = sb.add_body([2.0 * ii + off[0], -2.0 * i + off[1], rad + off[2]], mass=mass,
+                            inertia=(I[0, 0], I[1, 1], I[2, 2], I[0, 1], I[0, 2], I[1, 2]))
+            sp = sb.new_space()
+            for (x, y, z) in balls:
+                sb.add_geom(S.GEOM_SPHERE, (rad,), sp, body=b, pos=(x - off[0], y - off[1], z - off[2]), mu=0.5, mu2=0.5,
+                            slip1=slip, slip2=slip)
+            expect.append((mass * slip, float(n)))
+    for ii, (mass, slip) in enumerate(mass_slip):
+        ixx = 1.0 / 12.0 * mass * 2 * (2 * rad) ** 2
+        b = sb.add_body([2.0 * (ii + 0.5), 0.0, rad], mass=mass, inertia=(ixx, ixx, ixx, 0, 0, 0))
+        sb.add_geom(S.GEOM_BOX, (2 * rad,) * 3, sb.new_space(), body=b, mu=0.5, mu2=0.5, slip1=slip, slip2=slip)
+        expect.append((mass * slip, 1.0))   # (the slip of a pair is multiplied by its number of contacts, ODEPhysics.cc:1175-1185)
+    sb.end_world()
+    return sb.finish(), S.default_params(gravity=(0.0, 2.0, -9.81)), expect
+
+
+def check_friction_spheres(r, expect):
+    """physics_friction.cc:604-665: after 5 000 steps v_x = v_z = 0 (1e-3) and v_y = g_y x mass x slip / shapes within 1.5 %."""
+    r.step(5000)
+    v = r.body_state()[2]
+    assert np.abs(v[:, 0]).max() < 1e-3 and np.abs(v[:, 2]).max() < 1e-3
+    for k, (ms, n) in enumerate(expect):
+        ve = 2.0 * ms / n
+        assert abs(v[k, 1] - ve) < 0.015 * ve, (k, v[k, 1], ve)
+
+
 def torsion_radius_spheres():
     """The sphere_radius_1..5 models of torsional_friction_test.world (PhysicsTorsionalFrictionTest.RadiusTest,
     physics_torsional_friction.cc:383-479): spheres of radius 0.01 .. 10 m, coefficient 0.005, use_patch_radius false and

@@ -40,6 +40,13 @@ def test_oracle_reproduces_golden(oracle, name):
     assert np.array_equal(r.body_flags(), g["flags"])
 
 
+def test_sphere_slip(oracle):
+    """PhysicsFrictionTest.SphereSlip (test/integration/physics_friction.cc:529-666): slip1 / slip2 as a viscous creep -
+    a link pushed sideways by gravity on non-sliding contacts drifts at g_y x mass x slip / shapes (1.5 %)."""
+    sc, p, expect = scenes.friction_spheres()
+    scenes.check_friction_spheres(oracle.RefBatch(sc, p, mode=1), expect)
+
+
 def test_friction_demo(oracle):
     """PhysicsFrictionTest.FrictionDemo (test/integration/physics_friction.cc:183-286): the pyramid friction's sliding
     threshold to a part in a thousand - boxes with mu just below 1 under gravity (0, -1, -1) accelerate at g_y + mu, those

@@ -612,6 +612,35 @@ def check_friction_spheres(r, expect):
         assert abs(v[k, 1] - ve) < 0.015 * ve, (k, v[k, 1], ve)
 
 
+def depth_spheres():
+    """The sphere_mass_1..5 models of torsional_friction_test.world (PhysicsTorsionalFrictionTest.DepthTest,
+    physics_torsional_friction.cc:147-281): 0.1 m spheres of 0.42 .. 41.9 kg, kp = 5e5, max_vel 10 000.  Returns the
+    scene, the parameters and the masses."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    sb.add_geom(S.GEOM_PLANE, (0, 0, 1, 0), sb.new_space(), mu=100.0, mu2=50.0, mu3=1.0)
+    masses = (0.41887902047863923, 4.188790204786391, 11.309733552923259, 20.94395102393196, 41.88790204786392)
+    izzs = (0.0016755160819145573, 0.01675516081914557, 0.045238934211693047, 0.08377580409572787, 0.16755160819145573)
+    for k, (m, izz) in enumerate(zip(masses, izzs)):
+        b = sb.add_body([0.4 * (k + 1), 0.0, 0.1], mass=m, inertia=(izz, izz, izz, 0, 0, 0), max_vel=10000.0)
+        sb.add_geom(S.GEOM_SPHERE, (0.1,), sb.new_space(), body=b, mu3=0.005, kp=5e5)
+    sb.end_world()
+    return sb.finish(), S.default_params(), masses
+
+
+def check_depth_spheres(r, masses):
+    """physics_torsional_friction.cc:226-273: after 1 000 steps every sphere's contact has the normal +z exactly and the
+    depth m g / kp within 1 %."""
+    r.step(1000)
+    cg, cd = r.contacts(0)
+    assert len(cg) == len(masses)
+    for (g1, g2), c in zip(cg, cd):
+        m = masses[max(g1, g2) - 1]
+        assert c[3] == 0.0 and c[4] == 0.0 and abs(c[5]) == 1.0   # (exactly along z; its sign follows the pair's geom order)
+        expected = m * 9.8 / 500000.0
+        assert abs(c[6] - expected) / expected < 0.01, (m, c[6], expected)
+
+
 def torsion_radius_spheres():
     """The sphere_radius_1..5 models of torsional_friction_test.world (PhysicsTorsionalFrictionTest.RadiusTest,
     physics_torsional_friction.cc:383-479): spheres of radius 0.01 .. 10 m, coefficient 0.005, use_patch_radius false and

@@ -86,6 +86,12 @@ def test_torsional_friction_coefficient_test(oracle):
     _coefficient_test(r, sc, spec)
 
 
+def test_torsional_friction_depth_test(oracle):
+    """PhysicsTorsionalFrictionTest.DepthTest (physics_torsional_friction.cc:147-281): equilibrium depth m g / kp (1 %)."""
+    sc, p, masses = scenes.depth_spheres()
+    scenes.check_depth_spheres(oracle.RefBatch(sc, p, mode=1), masses)
+
+
 def test_torsional_friction_radius_test(oracle):
     """PhysicsTorsionalFrictionTest.RadiusTest (physics_torsional_friction.cc:383-479): the patch radius from the surface
     radius and the depth at equilibrium, a = sqrt(R m g / kp); angular acceleration within 1 % (:475)."""

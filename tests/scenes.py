@@ -612,6 +612,57 @@ def check_friction_spheres(r, expect):
         assert abs(v[k, 1] - ve) < 0.015 * ve, (k, v[k, 1], ve)
 
 
+def gearbox_world():
+    """test/worlds/gearbox.world restated (ODEGearboxJoint_TEST.GearboxTest, test/integration/joint_gearbox.cc:36-112): no
+    gravity, 200 iterations, sor 1, erp 1; link_2 on a hinge to the world, link_1 and link_3 on hinges (about x) to link_2, a
+    gearbox of ratio -1.5 between link_1 (parent) and link_3 (child: ODE's body 1) with link_2 as reference body.
+    Returns the scene, the parameters and (link_1, link_2, link_3, joint_12, joint_23)."""
+    sb = S.SceneBuilder()
+    sb.begin_world()
+    q = S.q_from_rpy(-1.57079, 0, 0)
+    R, T = S.q_to_R(q), np.array([0, 0, 2.1])
+    sp = sb.new_space()
+    I = (1, 1, 1, 0, 0, 0)
+    l1 = sb.add_body(T + R @ np.array([0, 0, -0.5]), q, mass=10.0, inertia=I)          # (bodies sit at the centres of mass)
+    sb.add_geom(S.GEOM_CYLINDER, (0.1, 1.0), sp, body=l1)
+    l2 = sb.add_body(T + R @ np.array([0.5, 0, -0.5]), q, mass=10.0, inertia=I)
+    sb.add_geom(S.GEOM_BOX, (0.2, 0.2, 0.2), sp, body=l2, pos=(0, 0, 0.5))
+    l3 = sb.add_body(T + R @ np.array([1, 1, 0.5]), q, mass=10.0, inertia=I)
+    sb.add_geom(S.GEOM_CYLINDER, (0.1, 1.0), sp, body=l3)
+    x = np.array([1.0, 0, 0])
+    sb.add_hinge(l2, -1, T + R @ np.array([0.5, 0, 0]), R @ np.array([0, 0, 1.0]))
+    j12 = sb.add_hinge(l1, l2, T, x)
+    j23 = sb.add_hinge(l3, l2, T + R @ np.array([1, 1, 1.0]), x)
+    sb.add_gearbox(l3, l1, x, x, -1.5, ref1=l2, ref2=l2)
+    sb.end_world()
+    p = S.default_params(gravity=(0, 0, 0), iters=200, sor_w=1.0, cfm=0.0, erp=1.0)
+    return sb.finish(), p, (l1, l2, l3, j12, j23)
+
+
+def check_gearbox(r, sc, ids, steps=2000):
+    """joint_gearbox.cc:52-110 for the joint_02 angle 0 (2 000 of its 10 000 steps per phase): hinge torques in the
+    gearbox's own proportion (force1 = ratio x force3) hold everything still to 1e-6; with -1 / +1 both joints turn forwards
+    and velocity1 x ratio = -velocity3, position1 x ratio = -position3 to 1e-6."""
+    l1, l2, l3, j12, j23 = ids
+    x, ratio = np.array([1.0, 0, 0]), -1.5
+
+    def drive(f1, f3):   # Joint::SetForce = dJointAddHingeTorque: +f on the child, -f on the parent, about the axis
+        for _ in range(steps):
+            tq = np.zeros((sc.nb, 3))
+            tq[l1] += f1 * x; tq[l2] -= f1 * x
+            tq[l3] += f3 * x; tq[l2] -= f3 * x
+            r.add_body_wrench(torque=tq)
+            r.step(1)
+        av, cum = r.body_state()[3], r.joint_state()[2]
+        return (av[l1] - av[l2]) @ x, (av[l3] - av[l2]) @ x, cum[j12], cum[j23]
+    v1, v3, p1, p3 = drive(1.0 * ratio, 1.0)
+    assert max(abs(v1), abs(v3), abs(p1), abs(p3)) < 1e-6
+    v1, v3, p1, p3 = drive(-1.0, 1.0)
+    assert min(v1, v3, p1, p3) > 0
+    assert abs(v1 * ratio + v3) < 1e-6 and abs(p1 * ratio + p3) < 1e-6
+    return v1, v3, p1, p3
+
+
 def depth_spheres():
     """The sphere_mass_1..5 models of torsional_friction_test.world (PhysicsTorsionalFrictionTest.DepthTest,
     physics_torsional_friction.cc:147-281): 0.1 m spheres of 0.42 .. 41.9 kg, kp = 5e5, max_vel 10 000.  Returns the

@@ -40,6 +40,13 @@ def test_oracle_reproduces_golden(oracle, name):
     assert np.array_equal(r.body_flags(), g["flags"])
 
 
+def test_gearbox_test(oracle):
+    """ODEGearboxJoint_TEST.GearboxTest (test/integration/joint_gearbox.cc:36-112) on the oracle: pins the harness'
+    gearbox joint (created by field injection: the reference's C API has no public constructor arguments for it)."""
+    sc, p, ids = scenes.gearbox_world()
+    scenes.check_gearbox(oracle.RefBatch(sc, p, mode=1), sc, ids)
+
+
 def test_sphere_slip(oracle):
     """PhysicsFrictionTest.SphereSlip (test/integration/physics_friction.cc:529-666): slip1 / slip2 as a viscous creep -
     a link pushed sideways by gravity on non-sliding contacts drifts at g_y x mass x slip / shapes (1.5 %)."""
